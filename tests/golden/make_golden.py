@@ -1,0 +1,129 @@
+"""Generates tests/golden/*.pt by EXECUTING THE REFERENCE'S OWN CODE (/root/reference, imported
+under oracle/stubs).  Run in the build container only:  python tests/golden/make_golden.py
+The fixtures pin oracle/xunet_ref.py + oracle/diffusion_ref.py (tests/test_oracle.py) and are the
+anchors of the GPU parity tests.  Weights are not stored: they come from
+oracle.xunet_ref.init_state_dict(cfg, seed) (deterministic CPU generator).
+
+What is NOT pinned by these files: the camera-ray arithmetic of third-party `visu3d` (absent
+everywhere) -- the reference runs here with oracle/rays.py standing in for it."""
+import os
+import random
+import sys
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+REPO = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, REPO)
+
+from oracle import ref_import, xunet_ref as xr, diffusion_ref as dr   # noqa: E402
+from distributed_3d_diffusion_pytorch_b200 import synthetic           # noqa: E402
+
+
+def model_case(name, kw, B, seed, cond_mask):
+    rx, rd = ref_import.load()
+    cfg = xr.Cfg(**kw)
+    sd = xr.init_state_dict(cfg, seed=seed)
+    m = rx.XUNet(**kw)
+    assert {k: tuple(v.shape) for k, v in m.state_dict().items()} == xr.param_shapes(cfg)
+    m.load_state_dict(sd)
+    m.eval()                                              # dropout off for parity (H2)
+    img, R, T, K = synthetic.make_views(B, kw["H"], seed=seed + 1)
+    g = torch.Generator().manual_seed(seed + 2)
+    logsnr = dr.logsnr_schedule_cosine(torch.rand(B, generator=g))
+    noise = torch.randn(img[:, 0].shape, generator=g)
+    xrep = torch.randn(img[:, 0].shape, generator=g)
+    cm = torch.tensor(cond_mask)
+    # reference glue: lightning/diff3d.py:131-180 methods (need no Lightning state)
+    D = rd.Diff3D.__new__(rd.Diff3D)
+    z_noisy = rd.Diff3D.q_sample(D, z=img[:, 1], logsnr=logsnr, noise=noise)
+    x_cond = torch.where(cm[:, None, None, None], img[:, 0], xrep)        # lightning/diff3d.py:69
+    batch = rd.Diff3D.xt2batch(D, x=x_cond, logsnr=logsnr, z=z_noisy, R=R, T=T, K=K)
+    taps = {}
+    hooks = []
+    # pose_emb before the convs: input of conditioningprocessor.convs[0]
+    hooks.append(m.conditioningprocessor.convs[0].register_forward_hook(
+        lambda mod, inp, out: taps.__setitem__("pose_emb", inp[0].detach().clone())))
+    for hn in ("xunetblocks.0.0", "xunetblocks.2.0", "middle", "upsample.0.3"):
+        mod = dict(m.named_modules())[hn]
+        hooks.append(mod.register_forward_hook(
+            lambda mod, inp, out, hn=hn: taps.__setitem__(hn, out.detach().clone())))
+    eps = m(batch, cond_mask=cm)
+    loss = torch.nn.functional.mse_loss(noise, eps)
+    loss.backward()
+    for h in hooks:
+        h.remove()
+    grads = {k: p.grad.detach().clone() for k, p in m.named_parameters()}
+    keep = ["conv.weight", "lastconv.weight", "conditioningprocessor.pos_emb",
+            "conditioningprocessor.first_emb", "conditioningprocessor.other_emb",
+            "conditioningprocessor.logsnr_emb_emb.0.bias", "conditioningprocessor.convs.2.bias",
+            "middle.resnetblock.groupnorm1.gn.weight", "middle.attnblock_cross.attn_layer.attn.in_proj_bias",
+            "xunetblocks.0.0.resnetblock.conv1.bias", "upsample.1.0.resnetblock.dense.bias"]
+    out = {
+        "kw": kw, "B": B, "seed": seed,
+        "img": img, "R": R, "T": T, "K": K, "logsnr": logsnr, "noise": noise, "x_replace": xrep,
+        "cond_mask": cm, "z_noisy": z_noisy, "batch_logsnr": batch["logsnr"],
+        "pose_emb": taps["pose_emb"].reshape(B, 2, 144, kw["H"], kw["W"]),
+        "taps": {k: v for k, v in taps.items() if k != "pose_emb"},
+        "eps": eps.detach(), "loss": loss.detach(),
+        "grad_norms": {k: v.norm().item() for k, v in grads.items()},
+        "grads": {k: grads[k] for k in keep if k in grads},
+    }
+    torch.save(out, os.path.join(HERE, name + ".pt"))
+    print(name, "eps std", eps.std().item(), "loss", loss.item(),
+          "bytes", os.path.getsize(os.path.join(HERE, name + ".pt")))
+
+
+def glue_case():
+    """Schedule table + one sampler step from sampling.py's own functions (fake 'model')."""
+    ns = ref_import.load_sampler_functions()
+    _cuda = torch.Tensor.cuda
+    torch.Tensor.cuda = lambda self, *a, **k: self          # sampling.py:69-75 hard-codes .cuda()
+    try:
+        ts = torch.linspace(1.0, 0.0, 257)
+        table = ns["logsnr_schedule_cosine"](ts)
+        g = torch.Generator().manual_seed(7)
+        b = 8
+        z = torch.randn(b, 3, 16, 16, generator=g)
+        x = torch.randn(b, 3, 16, 16, generator=g)
+        e_c = torch.randn(b, 3, 16, 16, generator=g)
+        e_u = torch.randn(b, 3, 16, 16, generator=g)
+        w = torch.arange(8)
+        outs = {}
+        for step in (0, 100, 127, 255):
+
+            def fake_model(batch, cond_mask, e_c=e_c, e_u=e_u):
+                return e_c if bool(cond_mask[0]) else e_u
+
+            torch.manual_seed(100 + step)
+            R = torch.eye(3).double()[None, None].repeat(b, 2, 1, 1)
+            T = torch.zeros(b, 2, 3).double()
+            K = torch.eye(3).double()
+            mean, var = ns["p_mean_variance"](fake_model, x=x, z=z, R=R, T=T, K=K,
+                                              logsnr=table[step], logsnr_next=table[step + 1], w=w)
+            torch.manual_seed(200 + step)
+            nxt = ns["p_sample"](fake_model, z=z, x=x, R=R, T=T, K=K, logsnr=table[step],
+                                 logsnr_next=table[step + 1], w=w)
+            # the noise p_sample drew: first randn_like(x) inside p_mean_variance (uncond x), then :127
+            torch.manual_seed(200 + step)
+            _ = torch.randn_like(x)
+            noise = torch.randn_like(x)
+            outs[step] = {"mean": mean, "var": var, "next": nxt, "noise": noise}
+        torch.save({"table": table, "z": z, "x": x, "eps_c": e_c, "eps_u": e_u, "w": w, "steps": outs},
+                   os.path.join(HERE, "glue.pt"))
+        print("glue ok; table[128] =", table[128].item(), "endpoints", table[0].item(), table[-1].item())
+    finally:
+        torch.Tensor.cuda = _cuda
+
+
+if __name__ == "__main__":
+    torch.manual_seed(0)
+    np.random.seed(0)
+    random.seed(0)
+    torch.set_num_threads(8)
+    # tiny: every structural feature (concat skips, 1x1 skips, self+cross attention, resampling)
+    model_case("tiny16", dict(H=16, W=16, ch=32), B=2, seed=11, cond_mask=[True, False])
+    # non-power-of-two spatial size, all-conditional
+    model_case("tiny24", dict(H=24, W=24, ch=32), B=1, seed=21, cond_mask=[True])
+    glue_case()

@@ -1,0 +1,84 @@
+"""CPU: the oracle restatement (oracle/) against the fixtures produced by the reference's own code
+(tests/golden/make_golden.py).  This is what pins the checker before it checks the CUDA path."""
+import pytest
+import torch
+
+from conftest import load_golden
+from oracle import xunet_ref as xr, diffusion_ref as dr, ref_import
+
+
+def _run_model_case(name):
+    G = load_golden(name)
+    cfg = xr.Cfg(**G["kw"])
+    sd = {k: v.requires_grad_(True) for k, v in xr.init_state_dict(cfg, seed=G["seed"]).items()}
+    img, cm = G["img"], G["cond_mask"]
+    z_noisy = dr.q_sample(img[:, 1], G["logsnr"], G["noise"])
+    assert torch.allclose(z_noisy, G["z_noisy"], atol=1e-6)
+    x_cond = torch.where(cm[:, None, None, None], img[:, 0], G["x_replace"])
+    batch = dr.make_batch(x_cond, G["logsnr"], z_noisy, G["R"], G["T"], G["K"])
+    assert torch.allclose(batch["logsnr"], G["batch_logsnr"], atol=1e-6)
+    taps = {}
+    eps = xr.xunet_forward(sd, cfg, batch, cm, taps=taps)
+    assert torch.allclose(taps["pose_emb"], G["pose_emb"], atol=1e-6)
+    for k, v in G["taps"].items():
+        key = k + ".resnetblock" if (k + ".resnetblock") in taps and not k.startswith("middle") else k
+        got = taps.get(k + ".attnblock_cross", taps.get(k + ".resnetblock"))
+        assert got is not None, k
+        assert (got - v).abs().max() <= 2e-5 * max(1.0, v.abs().max().item()), k
+    assert (eps - G["eps"]).abs().max() < 2e-5
+    loss = dr.loss_fn(G["noise"], eps)
+    assert abs(loss.item() - G["loss"].item()) < 1e-5 * abs(G["loss"].item()) + 1e-7
+    loss.backward()
+    for k, n in G["grad_norms"].items():
+        assert abs(sd[k].grad.norm().item() - n) <= 2e-4 * n + 2e-6, k   # atol: grads that are analytically 0 (bias before a 1-channel group)
+    for k, g in G["grads"].items():
+        if g.norm() < 1e-5:        # analytically zero (e.g. bias in front of a 1-channel GroupNorm group)
+            continue
+        cos = torch.nn.functional.cosine_similarity(sd[k].grad.flatten(), g.flatten(), dim=0)
+        assert cos > 0.99999, (k, cos)
+
+
+def test_oracle_matches_reference_tiny16():
+    _run_model_case("tiny16")
+
+
+def test_oracle_matches_reference_tiny24():
+    _run_model_case("tiny24")
+
+
+def test_schedule_and_sampler_update_match_reference():
+    G = load_golden("glue")
+    table = dr.logsnr_schedule_cosine(torch.linspace(1.0, 0.0, 257))
+    assert torch.equal(table, G["table"])
+    assert table[128] == 0 and (table[:128] != 0).all() and (table[129:] != 0).all()   # Q11
+    for step, o in G["steps"].items():
+        nxt, mean, var = dr.sampler_update(G["z"], G["eps_c"], G["eps_u"], G["w"], table[step], table[step + 1], o["noise"])
+        assert torch.allclose(mean, o["mean"], atol=1e-6, rtol=1e-6), step
+        assert torch.allclose(var, o["var"], atol=1e-9, rtol=1e-6), step
+        assert torch.allclose(nxt, o["next"], atol=1e-6, rtol=1e-6), step
+
+
+def test_param_schema_counts():
+    assert len(xr.param_shapes(xr.Cfg(H=64, W=64, ch=128))) == 647
+    n = sum(int(torch.tensor(s).prod()) for s in xr.param_shapes(xr.Cfg(H=64, W=64, ch=128)).values())
+    assert n == 136670627
+    n = sum(int(torch.tensor(s).prod()) for s in xr.param_shapes(xr.Cfg()).values())
+    assert n == 482132515
+
+
+@pytest.mark.skipif(not ref_import.available(), reason="reference tree only exists in the build container")
+def test_oracle_vs_live_reference_random_case():
+    rx, _ = ref_import.load()
+    kw = dict(H=8, W=8, ch=32)
+    cfg = xr.Cfg(**kw)
+    sd = xr.init_state_dict(cfg, seed=5)
+    m = rx.XUNet(**kw).eval()
+    m.load_state_dict(sd)
+    from distributed_3d_diffusion_pytorch_b200 import synthetic
+    img, R, T, K = synthetic.make_views(2, 8, seed=3)
+    logsnr = dr.logsnr_schedule_cosine(torch.tensor([0.3, 0.8]))
+    batch = dr.make_batch(img[:, 0], logsnr, img[:, 1], R, T, K)
+    cm = torch.tensor([False, True])
+    a = m(batch, cond_mask=cm)
+    b = xr.xunet_forward(sd, cfg, batch, cm)
+    assert (a - b).abs().max() < 2e-5

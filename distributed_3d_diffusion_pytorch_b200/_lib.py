@@ -1,0 +1,32 @@
+"""ctypes loader of the in-tree C-ABI library (libb3d.so).  There is no fallback: if the library is
+missing or a call fails, the product path raises."""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libb3d.so")
+_lib = None
+
+
+class B3DError(RuntimeError):
+    pass
+
+
+def load():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise B3DError(f"{LIB_PATH} not built: run `python __graft_entry__.py` (there is no CPU/eager fallback)")
+        _lib = ctypes.CDLL(LIB_PATH)
+        _lib.b3d_last_error.restype = ctypes.c_char_p
+        _lib.b3d_launch_count.restype = ctypes.c_int64
+    return _lib
+
+
+def check(rc, what):
+    if rc != 0:
+        raise B3DError(f"{what} failed ({rc}): {load().b3d_last_error().decode()}")
+
+
+def launch_count():
+    return int(load().b3d_launch_count())

@@ -1,0 +1,606 @@
+// HBM-bound kernels of the hot path: camera-ray + NeRF positional encoding (K1), DDPM noise-level
+// embedding, layout packers, pooling, attention softmax, bias/column reductions, diffusion glue
+// (q_sample, loss, sampler update) and fused Adam.  All coalesced / 16-byte vectorised.
+#include "../../include/b3d.h"
+#include "b3d_common.cuh"
+
+void b3d_count_launch(int n);
+
+namespace {
+
+constexpr int kT = 256;
+inline int cdiv(long long a, long long b) { return (int)((a + b - 1) / b); }
+inline int grid_for(long long n, int per_block = kT, int max_blocks = 148 * 32) {
+  long long g = (n + per_block - 1) / per_block;
+  if (g > max_blocks) g = max_blocks;
+  if (g < 1) g = 1;
+  return (int)g;
+}
+
+// ---------------------------------------------------------------------------------------------
+// K1: rays (fp64: inv(K), R*Kinv*p, normalise -> fp32) + posenc_nerf(pos,0,15) ++ posenc_nerf(dir,0,8)
+//     + cond-mask + pos_emb + first/other_emb  ->  [2B, H, W, ld] (bf16 or fp32), channels 0..143.
+// Replaces visu3d rays + xunet.py:311-336.  One block = 32 consecutive pixels of one image row.
+// ---------------------------------------------------------------------------------------------
+template <typename OutT>
+__global__ void pose_embedding_kernel(const double* __restrict__ Kmat, const double* __restrict__ R, const double* __restrict__ t,
+                                      const uint8_t* __restrict__ mask, const float* __restrict__ pos_emb,
+                                      const float* __restrict__ first_emb, const float* __restrict__ other_emb, OutT* __restrict__ out,
+                                      long long ld, int H, int W) {
+  __shared__ float s_pe[144][33];
+  __shared__ float s_posch[93];
+  __shared__ float s_dir[32][3];
+  __shared__ double s_M[9];
+  const int n = blockIdx.z, y = blockIdx.y, x0 = blockIdx.x * 32;
+  const int b = n >> 1, f = n & 1;
+  const bool cond = mask[b] != 0;
+  // learned per-pixel embedding tile, read coalesced along x
+  for (int i = threadIdx.x; i < 144 * 32; i += blockDim.x) {
+    const int c = i >> 5, xx = i & 31;
+    float v = 0.f;
+    if (x0 + xx < W) {
+      if (pos_emb) v = pos_emb[((long long)c * H + y) * W + x0 + xx];
+      const float* fe = f == 0 ? first_emb : other_emb;
+      if (fe) v += fe[c];
+    }
+    s_pe[c][xx] = v;
+  }
+  if (threadIdx.x == 0) {
+    // M = R * inv(K)   (world_from_px for directions)
+    const double* k = Kmat + b * 9;
+    const double a = k[0], bb = k[1], c = k[2], d = k[3], e = k[4], ff = k[5], g = k[6], h = k[7], i = k[8];
+    const double det = a * (e * i - ff * h) - bb * (d * i - ff * g) + c * (d * h - e * g);
+    const double id = 1.0 / det;
+    double inv[9] = {(e * i - ff * h) * id, (c * h - bb * i) * id, (bb * ff - c * e) * id,
+                     (ff * g - d * i) * id, (a * i - c * g) * id, (c * d - a * ff) * id,
+                     (d * h - e * g) * id, (bb * g - a * h) * id, (a * e - bb * d) * id};
+    const double* r = R + (long long)n * 9;
+    for (int p = 0; p < 3; ++p)
+      for (int q = 0; q < 3; ++q) s_M[p * 3 + q] = r[p * 3 + 0] * inv[0 * 3 + q] + r[p * 3 + 1] * inv[1 * 3 + q] + r[p * 3 + 2] * inv[2 * 3 + q];
+  }
+  // position channels depend on the image only: [t(3), sin(t*2^d) (d-major), sin(t*2^d + pi/2)]
+  if (threadIdx.x < 93) {
+    const int c = threadIdx.x;
+    float v;
+    if (c < 3) v = (float)t[(long long)n * 3 + c];
+    else {
+      const int j = (c - 3) % 45, d = j / 3, ax = j % 3;
+      float xb = (float)t[(long long)n * 3 + ax] * (float)(1 << d);
+      if (c - 3 >= 45) xb = xb + 1.5707963705062866f;
+      v = sinf(xb);
+    }
+    s_posch[c] = cond ? v : 0.f;
+  }
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    const double u = (double)(x0 + threadIdx.x) + 0.5, v = (double)y + 0.5;
+    double dx = s_M[0] * u + s_M[1] * v + s_M[2];
+    double dy = s_M[3] * u + s_M[4] * v + s_M[5];
+    double dz = s_M[6] * u + s_M[7] * v + s_M[8];
+    const double inv_n = 1.0 / sqrt(dx * dx + dy * dy + dz * dz);
+    s_dir[threadIdx.x][0] = (float)(dx * inv_n);
+    s_dir[threadIdx.x][1] = (float)(dy * inv_n);
+    s_dir[threadIdx.x][2] = (float)(dz * inv_n);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 32 * 144; i += blockDim.x) {
+    const int xx = i / 144, c = i % 144;
+    if (x0 + xx >= W) continue;
+    float v;
+    if (c < 93) v = s_posch[c];
+    else {
+      const int cc = c - 93;
+      if (!cond) v = 0.f;
+      else if (cc < 3) v = s_dir[xx][cc];
+      else {
+        const int j = (cc - 3) % 24, d = j / 3, ax = j % 3;
+        float xb = s_dir[xx][ax] * (float)(1 << d);
+        if (cc - 3 >= 24) xb = xb + 1.5707963705062866f;
+        v = sinf(xb);
+      }
+    }
+    v += s_pe[c][xx];
+    out[(((long long)n * H + y) * W + x0 + xx) * ld + c] = (OutT)v;
+  }
+}
+
+// d pos_emb[c,y,x] = sum_f dP[f,y,x,c];  d first/other[c] = sum_{y,x} dP[f,y,x,c]     (dP fp32 [2,H,W,ld])
+__global__ void pose_embedding_bwd_kernel(const float* __restrict__ dP, long long ld, int H, int W, float* dpos, float* dfirst, float* dother) {
+  const int c = blockIdx.x;  // one block per channel
+  float s0 = 0.f, s1 = 0.f;
+  for (int i = threadIdx.x; i < H * W; i += blockDim.x) {
+    const float a = dP[(long long)i * ld + c], b = dP[((long long)H * W + i) * ld + c];
+    if (dpos) dpos[(long long)c * H * W + i] = a + b;
+    s0 += a; s1 += b;
+  }
+  __shared__ float r0[32], r1[32];
+  s0 = b3d_warp_sum(s0); s1 = b3d_warp_sum(s1);
+  if ((threadIdx.x & 31) == 0) { r0[threadIdx.x >> 5] = s0; r1[threadIdx.x >> 5] = s1; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float a = 0.f, b = 0.f;
+    for (int w = 0; w < (int)blockDim.x / 32; ++w) { a += r0[w]; b += r1[w]; }
+    if (dfirst) dfirst[c] = a;
+    if (dother) dother[c] = b;
+  }
+}
+
+// posenc_ddpm(clip(logsnr,-20,20), emb_ch, max_time=1): [n] -> [n, emb_ch] bf16   (xunet.py:32-46,305-307)
+__global__ void ddpm_embedding_kernel(const float* __restrict__ logsnr, bf16* __restrict__ out, int n, int emb_ch) {
+  const int half = emb_ch / 2;
+  const float k = -logf(10000.f) / (float)(half - 1);
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < (long long)n * emb_ch; i += (long long)gridDim.x * blockDim.x) {
+    const int r = (int)(i / emb_ch), c = (int)(i % emb_ch);
+    const float tt = fminf(fmaxf(logsnr[r], -20.f), 20.f) * 1000.f;
+    const int j = c < half ? c : c - half;
+    const float arg = tt * expf((float)j * k);
+    out[i] = __float2bfloat16(c < half ? sinf(arg) : cosf(arg));
+  }
+}
+
+// stack([x,z],1) NCHW fp32 -> [2B,H,W,8] bf16 (channels 3..7 zero)            (xunet.py:493-494)
+__global__ void pack_input_kernel(const float* __restrict__ x, const float* __restrict__ z, bf16* __restrict__ out, int B, int HW) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < 2LL * B * HW; i += (long long)gridDim.x * blockDim.x) {
+    const int n = (int)(i / HW), p = (int)(i % HW), b = n >> 1;
+    const float* src = (n & 1) ? z : x;
+    float f[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+    for (int c = 0; c < 3; ++c) f[c] = src[((long long)b * 3 + c) * HW + p];
+    *reinterpret_cast<bf16x8*>(out + i * 8) = b3d_pack8(f);
+  }
+}
+// d(stem input) [2B,H,W,8] bf16 -> dx, dz NCHW fp32
+__global__ void unpack_input_grad_kernel(const bf16* __restrict__ g, float* __restrict__ dx, float* __restrict__ dz, int B, int HW) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < 2LL * B * HW; i += (long long)gridDim.x * blockDim.x) {
+    const int n = (int)(i / HW), p = (int)(i % HW), b = n >> 1;
+    float f[8]; b3d_unpack8(*reinterpret_cast<const bf16x8*>(g + i * 8), f);
+    float* dst = (n & 1) ? dz : dx;
+    if (dst) for (int c = 0; c < 3; ++c) dst[((long long)b * 3 + c) * HW + p] = f[c];
+  }
+}
+// lastconv output [2B,H,W,ld] bf16 -> eps fp32 [B,3,H,W], frame 1 only          (xunet.py:536)
+__global__ void unpack_output_kernel(const bf16* __restrict__ y, long long ld, float* __restrict__ eps, int B, int HW) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < (long long)B * 3 * HW; i += (long long)gridDim.x * blockDim.x) {
+    const int p = (int)(i % HW), c = (int)((i / HW) % 3), b = (int)(i / (3LL * HW));
+    eps[i] = __bfloat162float(y[(((long long)(2 * b + 1)) * HW + p) * ld + c]);
+  }
+}
+__global__ void pack_output_grad_kernel(const float* __restrict__ deps, bf16* __restrict__ dy, long long ld, int B, int HW) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < 2LL * B * HW; i += (long long)gridDim.x * blockDim.x) {
+    const int n = (int)(i / HW), p = (int)(i % HW), b = n >> 1;
+    for (int c = 0; c < (int)ld; ++c) {
+      float v = 0.f;
+      if ((n & 1) && c < 3) v = deps[((long long)b * 3 + c) * HW + p];
+      dy[i * ld + c] = __float2bfloat16(v);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// weight packers: fp32 PyTorch layout -> bf16 K-major GEMM operands, and packed fp32 grads back
+//   w [Co, Ci, taps]   (taps = kh*kw row-major)
+//   mode 0 (forward)  : out[co, k_off + tap*Cpad + (ci-ci0)] for ci in [ci0, ci0+cn)         ld = out_ld
+//   mode 1 (dgrad)    : out[ci, tap'*Copad + co], tap' = taps-1-tap (spatial flip)
+//   mode 2 (tap rows) : out[tap*Ci + ci, co]
+// unpack (mode 0 inverse, fp32 -> fp32): dw[co,ci,tap] = g[co, k_off + tap*Cpad + (ci-ci0)]
+// ---------------------------------------------------------------------------------------------
+__global__ void pack_weight_kernel(const float* __restrict__ w, int Co, int Ci, int taps, int mode, int ci0, int cn, int Cpad,
+                                   long long k_off, bf16* __restrict__ out, long long out_ld, long long total) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    float v = 0.f;
+    long long o;
+    if (mode == 0) {
+      const int cc = (int)(i % Cpad), tap = (int)((i / Cpad) % taps), co = (int)(i / ((long long)Cpad * taps));
+      if (cc < cn) v = w[((long long)co * Ci + ci0 + cc) * taps + tap];
+      o = (long long)co * out_ld + k_off + (long long)tap * Cpad + cc;
+    } else if (mode == 1) {
+      const int co = (int)(i % Cpad), tp = (int)((i / Cpad) % taps), ci = (int)(i / ((long long)Cpad * taps));
+      if (co < Co) v = w[((long long)co * Ci + ci) * taps + (taps - 1 - tp)];
+      o = (long long)ci * out_ld + (long long)tp * Cpad + co;
+    } else {
+      const int co = (int)(i % Co), ci = (int)((i / Co) % Ci), tap = (int)(i / ((long long)Co * Ci));
+      v = w[((long long)co * Ci + ci) * taps + tap];
+      o = ((long long)tap * Ci + ci) * out_ld + co;
+    }
+    out[o] = __float2bfloat16(v);
+  }
+}
+__global__ void unpack_wgrad_kernel(const float* __restrict__ g, long long g_ld, long long k_off, int Cpad, int Co, int Ci, int taps, int ci0,
+                                    int cn, float* __restrict__ dw, int accumulate) {
+  const long long total = (long long)Co * cn * taps;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int tap = (int)(i % taps), cc = (int)((i / taps) % cn), co = (int)(i / ((long long)taps * cn));
+    const float v = g[(long long)co * g_ld + k_off + (long long)tap * Cpad + cc];
+    float* d = dw + ((long long)co * Ci + ci0 + cc) * taps + tap;
+    *d = accumulate ? *d + v : v;
+  }
+}
+__global__ void cast_kernel(const float* __restrict__ in, bf16* __restrict__ out, long long n) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) out[i] = __float2bfloat16(in[i]);
+}
+
+// ---------------------------------------------------------------------------------------------
+// resampling on NHWC bf16 (xunet.py:17-28) and their adjoints
+// ---------------------------------------------------------------------------------------------
+__global__ void avgpool2_kernel(const bf16* __restrict__ in, bf16* __restrict__ out, int N, int H, int W, int C, float scale) {
+  const int Ho = H / 2, Wo = W / 2, vecs = C / 8;
+  const long long total = (long long)N * Ho * Wo * vecs;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int v = (int)(i % vecs); long long q = i / vecs;
+    const int x = (int)(q % Wo); q /= Wo; const int y = (int)(q % Ho); const int n = (int)(q / Ho);
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+    for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+      for (int dx = 0; dx < 2; ++dx) {
+        float f[8];
+        b3d_unpack8(*reinterpret_cast<const bf16x8*>(in + ((((long long)n * H + 2 * y + dy) * W + 2 * x + dx) * C + v * 8)), f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += f[j];
+      }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] *= scale;
+    *reinterpret_cast<bf16x8*>(out + (((long long)n * Ho + y) * Wo + x) * C + v * 8) = b3d_pack8(acc);
+  }
+}
+// out[n, y, x] = scale * in[n, y/2, x/2]  (nearest upsample; also the adjoint of avgpool with scale=1/4)
+__global__ void upsample2_kernel(const bf16* __restrict__ in, bf16* __restrict__ out, int N, int Ho, int Wo, int C, float scale) {
+  const int H = Ho / 2, W = Wo / 2, vecs = C / 8;
+  const long long total = (long long)N * Ho * Wo * vecs;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int v = (int)(i % vecs); long long q = i / vecs;
+    const int x = (int)(q % Wo); q /= Wo; const int y = (int)(q % Ho); const int n = (int)(q / Ho);
+    float f[8];
+    b3d_unpack8(*reinterpret_cast<const bf16x8*>(in + (((long long)n * H + y / 2) * W + x / 2) * C + v * 8), f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) f[j] *= scale;
+    *reinterpret_cast<bf16x8*>(out + (((long long)n * Ho + y) * Wo + x) * C + v * 8) = b3d_pack8(f);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// elementwise helpers
+// ---------------------------------------------------------------------------------------------
+// dx = dy * silu'(x)
+__global__ void silu_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x, bf16* __restrict__ dx, long long nvec) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nvec; i += (long long)gridDim.x * blockDim.x) {
+    float a[8], b[8];
+    b3d_unpack8(reinterpret_cast<const bf16x8*>(dy)[i], a);
+    b3d_unpack8(reinterpret_cast<const bf16x8*>(x)[i], b);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a[j] *= b3d_silu_grad(b[j]);
+    reinterpret_cast<bf16x8*>(dx)[i] = b3d_pack8(a);
+  }
+}
+// out = scale * (a + b)   (b optional)
+__global__ void add_scale_kernel(const bf16* __restrict__ a, const bf16* __restrict__ b, bf16* __restrict__ out, float scale, long long nvec) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nvec; i += (long long)gridDim.x * blockDim.x) {
+    float x[8], y[8];
+    b3d_unpack8(reinterpret_cast<const bf16x8*>(a)[i], x);
+    if (b) { b3d_unpack8(reinterpret_cast<const bf16x8*>(b)[i], y);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) x[j] += y[j]; }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) x[j] *= scale;
+    reinterpret_cast<bf16x8*>(out)[i] = b3d_pack8(x);
+  }
+}
+
+// out[g, c] (+)= sum over rows of group g of in[row, c];  rows_per_group rows per group   (bias / logsnr-emb grads)
+__global__ void colsum_kernel(const bf16* __restrict__ in, long long ld, int C, long long rows_per_group, int rows_per_block,
+                              float* __restrict__ out, long long out_ld) {
+  const int g = blockIdx.z;
+  const int c = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
+  if (c >= C) return;
+  const long long r0 = (long long)blockIdx.y * rows_per_block, r1 = min(rows_per_group, r0 + rows_per_block);
+  float s0 = 0.f, s1 = 0.f;
+  const bf16* base = in + (g * rows_per_group) * ld + c;
+  for (long long r = r0; r < r1; ++r) {
+    const float2 v = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(base + r * ld));
+    s0 += v.x; s1 += v.y;
+  }
+  atomicAdd(out + g * out_ld + c, s0);
+  if (c + 1 < C) atomicAdd(out + g * out_ld + c + 1, s1);
+}
+
+// out[f, p, c] = sum_b in[b, f, p, c]   (in: [B,2,P,C] bf16)   -- batch reduction per frame
+__global__ void batch_frame_sum_kernel(const bf16* __restrict__ in, bf16* __restrict__ out, int B, long long PCvec) {
+  const long long total = 2 * PCvec;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int b = 0; b < B; ++b) {
+      float f[8];
+      b3d_unpack8(reinterpret_cast<const bf16x8*>(in)[(long long)b * total + i], f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] += f[j];
+    }
+    reinterpret_cast<bf16x8*>(out)[i] = b3d_pack8(acc);
+  }
+}
+
+// adjoint of the strided 3x3 conditioning convs w.r.t. their input, from per-tap products:
+//   G [2*h*w, ldg] fp32, column tap*C + ci  (= dEsum . W[:,tap,:]);   dP[f, y', x', ci] += sum over taps
+//   with (y'+1-ky) % s == 0, (x'+1-kx) % s == 0                                  (xunet.py:340-349)
+__global__ void conv_tap_scatter_kernel(const float* __restrict__ Gm, long long ldg, int C, int h, int w, int s, int H, int W,
+                                        float* __restrict__ dP, long long ldp, int accumulate) {
+  const long long total = 2LL * H * W * C;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C); long long q = i / C;
+    const int xp = (int)(q % W); q /= W; const int yp = (int)(q % H); const int f = (int)(q / H);
+    float acc = 0.f;
+#pragma unroll
+    for (int ky = 0; ky < 3; ++ky) {
+      const int yy = yp + 1 - ky;
+      if (yy < 0 || yy % s) continue;
+      const int y = yy / s; if (y >= h) continue;
+#pragma unroll
+      for (int kx = 0; kx < 3; ++kx) {
+        const int xx = xp + 1 - kx;
+        if (xx < 0 || xx % s) continue;
+        const int x = xx / s; if (x >= w) continue;
+        acc += Gm[(((long long)f * h + y) * w + x) * ldg + (ky * 3 + kx) * C + c];
+      }
+    }
+    float* d = dP + (((long long)f * H + yp) * W + xp) * ldp + c;
+    *d = accumulate ? *d + acc : acc;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// attention softmax over rows of length L (bf16 in/out, fp32 math); one warp per row   (inside nn.MultiheadAttention)
+// ---------------------------------------------------------------------------------------------
+__global__ void softmax_kernel(const bf16* __restrict__ S, bf16* __restrict__ P, long long rows, int L, long long ld) {
+  const long long row = (long long)blockIdx.x * (blockDim.x / 32) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int lane = threadIdx.x & 31;
+  const bf16* s = S + row * ld;
+  float m = -INFINITY;
+  for (int i = lane; i < L; i += 32) m = fmaxf(m, __bfloat162float(s[i]));
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+  float sum = 0.f;
+  for (int i = lane; i < L; i += 32) sum += __expf(__bfloat162float(s[i]) - m);
+  sum = b3d_warp_sum(sum);
+  const float inv = 1.f / sum;
+  for (int i = lane; i < L; i += 32) P[row * ld + i] = __float2bfloat16(__expf(__bfloat162float(s[i]) - m) * inv);
+}
+// dS = P * (dP - sum(P*dP))
+__global__ void softmax_bwd_kernel(const bf16* __restrict__ P, const bf16* __restrict__ dP, bf16* __restrict__ dS, long long rows, int L,
+                                   long long ld) {
+  const long long row = (long long)blockIdx.x * (blockDim.x / 32) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int lane = threadIdx.x & 31;
+  float dot = 0.f;
+  for (int i = lane; i < L; i += 32) dot += __bfloat162float(P[row * ld + i]) * __bfloat162float(dP[row * ld + i]);
+  dot = b3d_warp_sum(dot);
+  for (int i = lane; i < L; i += 32) {
+    const float p = __bfloat162float(P[row * ld + i]);
+    dS[row * ld + i] = __float2bfloat16(p * (__bfloat162float(dP[row * ld + i]) - dot));
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// diffusion glue
+// ---------------------------------------------------------------------------------------------
+// z_t = sqrt(sigmoid(l)) z + sqrt(sigmoid(-l)) eps ; x_cond = mask ? x : x_rand      (train.py:50-60,95-96)
+__global__ void q_sample_kernel(const float* __restrict__ z, const float* __restrict__ noise, const float* __restrict__ logsnr,
+                                const float* __restrict__ x, const float* __restrict__ xrand, const uint8_t* __restrict__ mask,
+                                float* __restrict__ z_out, float* __restrict__ x_out, long long per, long long total) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int b = (int)(i / per);
+    const float l = logsnr[b];
+    const float alpha = sqrtf(1.f / (1.f + expf(-l))), sigma = sqrtf(1.f / (1.f + expf(l)));
+    z_out[i] = alpha * z[i] + sigma * noise[i];
+    if (x_out) x_out[i] = mask[b] ? x[i] : xrand[i];
+  }
+}
+
+// loss = mean(rho(noise - pred)), d loss / d pred; deterministic two-stage reduction through `partials`
+// (one float per block + a ticket counter that the kernel leaves at zero).           (train.py:102-112)
+__global__ void loss_kernel(const float* __restrict__ noise, const float* __restrict__ pred, float* __restrict__ dpred, long long n, int type,
+                            float grad_scale, float* __restrict__ partials, unsigned int* __restrict__ ticket, float* __restrict__ loss_out) {
+  float acc = 0.f;
+  const float inv_n = 1.f / (float)n;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const float d = pred[i] - noise[i];
+    float v, g;
+    if (type == 0) { v = d * d; g = 2.f * d; }
+    else if (type == 1) { v = fabsf(d); g = d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f); }
+    else { const float a = fabsf(d); v = a < 1.f ? 0.5f * d * d : a - 0.5f; g = a < 1.f ? d : (d > 0.f ? 1.f : -1.f); }
+    acc += v;
+    if (dpred) dpred[i] = g * inv_n * grad_scale;
+  }
+  __shared__ float red[32];
+  __shared__ bool last;
+  acc = b3d_warp_sum(acc);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float s = 0.f;
+    for (int w = 0; w < (int)blockDim.x / 32; ++w) s += red[w];
+    partials[blockIdx.x] = s;
+    __threadfence();
+    last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (last && threadIdx.x < 32) {
+    __threadfence();
+    float s = 0.f;
+    for (int i = threadIdx.x; i < (int)gridDim.x; i += 32) s += partials[i];   // fixed order per lane -> deterministic
+    s = b3d_warp_sum(s);
+    if (threadIdx.x == 0) { *loss_out = s * inv_n; *ticket = 0u; }
+  }
+}
+
+// sampler update (sampling.py:79-127): classifier-free guidance mix, x0 clip, posterior mean, + sqrt(var) * noise
+__global__ void sampler_update_kernel(const float* __restrict__ z, const float* __restrict__ eps_c, const float* __restrict__ eps_u,
+                                      const float* __restrict__ w, const float* __restrict__ noise, float* __restrict__ out, float alpha,
+                                      float sigma, float alpha_next, float c, float std_next, int add_noise, long long per, long long total) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const float ww = w[i / per];
+    const float e = (1.f + ww) * eps_c[i] - ww * eps_u[i];
+    const float zz = z[i];
+    float x0 = (zz - sigma * e) / alpha;
+    x0 = fminf(fmaxf(x0, -1.f), 1.f);
+    float m = alpha_next * (zz * (1.f - c) / alpha + c * x0);
+    if (add_noise) m += std_next * noise[i];
+    out[i] = m;
+  }
+}
+
+// fused Adam over one flat fp32 parameter arena (train.py:235: lr 1e-4, betas (0.9, 0.99), eps 1e-8)
+__global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v, long long n,
+                            float lr, float b1, float b2, float eps, float bc1, float bc2, float grad_scale) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const float gg = g[i] * grad_scale;
+    const float mm = b1 * m[i] + (1.f - b1) * gg;
+    const float vv = b2 * v[i] + (1.f - b2) * gg * gg;
+    m[i] = mm; v[i] = vv;
+    p[i] -= lr * (mm / bc1) / (sqrtf(vv / bc2) + eps);
+  }
+}
+
+}  // namespace
+
+#define STREAM ((cudaStream_t)stream)
+#define DONE(n) do { B3D_LAUNCH_CHECK(); b3d_count_launch(n); return B3D_OK; } while (0)
+
+extern "C" int b3d_pose_embedding(const double* K, const double* R, const double* t, const uint8_t* cond_mask, const float* pos_emb,
+                                  const float* first_emb, const float* other_emb, void* out, int out_fp32, int64_t ld, int B, int H, int W,
+                                  void* stream) {
+  B3D_CHECK_ARG(K && R && t && cond_mask && out, "pose_embedding: null pointer");
+  B3D_CHECK_ARG(ld >= 144 && B > 0 && H > 0 && W > 0, "pose_embedding: bad sizes");
+  dim3 grid(cdiv(W, 32), H, 2 * B);
+  if (out_fp32) pose_embedding_kernel<float><<<grid, kT, 0, STREAM>>>(K, R, t, cond_mask, pos_emb, first_emb, other_emb, (float*)out, ld, H, W);
+  else pose_embedding_kernel<bf16><<<grid, kT, 0, STREAM>>>(K, R, t, cond_mask, pos_emb, first_emb, other_emb, (bf16*)out, ld, H, W);
+  DONE(1);
+}
+extern "C" int b3d_pose_embedding_bwd(const float* dP, int64_t ld, int H, int W, float* dpos_emb, float* dfirst, float* dother, void* stream) {
+  B3D_CHECK_ARG(dP, "pose_embedding_bwd: null");
+  pose_embedding_bwd_kernel<<<144, kT, 0, STREAM>>>(dP, ld, H, W, dpos_emb, dfirst, dother);
+  DONE(1);
+}
+extern "C" int b3d_ddpm_embedding(const float* logsnr, void* out, int n, int emb_ch, void* stream) {
+  B3D_CHECK_ARG(logsnr && out && emb_ch % 2 == 0 && emb_ch >= 4, "ddpm_embedding: args");
+  ddpm_embedding_kernel<<<grid_for((long long)n * emb_ch), kT, 0, STREAM>>>(logsnr, (bf16*)out, n, emb_ch);
+  DONE(1);
+}
+extern "C" int b3d_pack_input(const float* x, const float* z, void* out, int B, int HW, void* stream) {
+  B3D_CHECK_ARG(x && z && out, "pack_input: null");
+  pack_input_kernel<<<grid_for(2LL * B * HW), kT, 0, STREAM>>>(x, z, (bf16*)out, B, HW);
+  DONE(1);
+}
+extern "C" int b3d_unpack_input_grad(const void* g, float* dx, float* dz, int B, int HW, void* stream) {
+  unpack_input_grad_kernel<<<grid_for(2LL * B * HW), kT, 0, STREAM>>>((const bf16*)g, dx, dz, B, HW);
+  DONE(1);
+}
+extern "C" int b3d_unpack_output(const void* y, int64_t ld, float* eps, int B, int HW, void* stream) {
+  unpack_output_kernel<<<grid_for(3LL * B * HW), kT, 0, STREAM>>>((const bf16*)y, ld, eps, B, HW);
+  DONE(1);
+}
+extern "C" int b3d_pack_output_grad(const float* deps, void* dy, int64_t ld, int B, int HW, void* stream) {
+  pack_output_grad_kernel<<<grid_for(2LL * B * HW), kT, 0, STREAM>>>(deps, (bf16*)dy, ld, B, HW);
+  DONE(1);
+}
+extern "C" int b3d_pack_weight(const float* w, int Co, int Ci, int taps, int mode, int ci0, int cn, int Cpad, int64_t k_off, void* out,
+                               int64_t out_ld, void* stream) {
+  B3D_CHECK_ARG(w && out && mode >= 0 && mode <= 2, "pack_weight: args");
+  long long total = mode == 0 ? (long long)Co * taps * Cpad : mode == 1 ? (long long)Ci * taps * Cpad : (long long)Co * Ci * taps;
+  pack_weight_kernel<<<grid_for(total), kT, 0, STREAM>>>(w, Co, Ci, taps, mode, ci0, cn, Cpad, k_off, (bf16*)out, out_ld, total);
+  DONE(1);
+}
+extern "C" int b3d_unpack_wgrad(const float* g, int64_t g_ld, int64_t k_off, int Cpad, int Co, int Ci, int taps, int ci0, int cn, float* dw,
+                                int accumulate, void* stream) {
+  unpack_wgrad_kernel<<<grid_for((long long)Co * cn * taps), kT, 0, STREAM>>>(g, g_ld, k_off, Cpad, Co, Ci, taps, ci0, cn, dw, accumulate);
+  DONE(1);
+}
+extern "C" int b3d_cast_bf16(const float* in, void* out, int64_t n, void* stream) {
+  cast_kernel<<<grid_for(n), kT, 0, STREAM>>>(in, (bf16*)out, n);
+  DONE(1);
+}
+extern "C" int b3d_avgpool2(const void* in, void* out, int N, int H, int W, int C, float scale, void* stream) {
+  B3D_CHECK_ARG(C % 8 == 0 && H % 2 == 0 && W % 2 == 0, "avgpool2: C%%8, even H/W");
+  avgpool2_kernel<<<grid_for((long long)N * (H / 2) * (W / 2) * (C / 8)), kT, 0, STREAM>>>((const bf16*)in, (bf16*)out, N, H, W, C, scale);
+  DONE(1);
+}
+extern "C" int b3d_upsample2(const void* in, void* out, int N, int Ho, int Wo, int C, float scale, void* stream) {
+  B3D_CHECK_ARG(C % 8 == 0 && Ho % 2 == 0 && Wo % 2 == 0, "upsample2: C%%8, even H/W");
+  upsample2_kernel<<<grid_for((long long)N * Ho * Wo * (C / 8)), kT, 0, STREAM>>>((const bf16*)in, (bf16*)out, N, Ho, Wo, C, scale);
+  DONE(1);
+}
+extern "C" int b3d_silu_bwd(const void* dy, const void* x, void* dx, int64_t n, void* stream) {
+  B3D_CHECK_ARG(n % 8 == 0, "silu_bwd: n%%8");
+  silu_bwd_kernel<<<grid_for(n / 8), kT, 0, STREAM>>>((const bf16*)dy, (const bf16*)x, (bf16*)dx, n / 8);
+  DONE(1);
+}
+extern "C" int b3d_add_scale(const void* a, const void* b, void* out, float scale, int64_t n, void* stream) {
+  B3D_CHECK_ARG(n % 8 == 0, "add_scale: n%%8");
+  add_scale_kernel<<<grid_for(n / 8), kT, 0, STREAM>>>((const bf16*)a, (const bf16*)b, (bf16*)out, scale, n / 8);
+  DONE(1);
+}
+extern "C" int b3d_colsum(const void* in, int64_t ld, int C, int64_t rows_per_group, int groups, float* out, int64_t out_ld, void* stream) {
+  B3D_CHECK_ARG(C % 2 == 0 && ld % 2 == 0, "colsum: even C/ld");
+  int rpb = 256;
+  while ((long long)cdiv(rows_per_group, rpb) * groups * cdiv(C, 256) > 148LL * 16 && rpb < rows_per_group) rpb *= 2;
+  dim3 grid(cdiv(C / 2, 128), cdiv(rows_per_group, rpb), groups);
+  colsum_kernel<<<grid, 128, 0, STREAM>>>((const bf16*)in, ld, C, rows_per_group, rpb, out, out_ld);
+  DONE(1);
+}
+extern "C" int b3d_batch_frame_sum(const void* in, void* out, int B, int64_t per_frame_elems, void* stream) {
+  B3D_CHECK_ARG(per_frame_elems % 8 == 0, "batch_frame_sum: %%8");
+  batch_frame_sum_kernel<<<grid_for(2 * per_frame_elems / 8), kT, 0, STREAM>>>((const bf16*)in, (bf16*)out, B, per_frame_elems / 8);
+  DONE(1);
+}
+extern "C" int b3d_conv_tap_scatter(const float* G, int64_t ldg, int C, int h, int w, int s, int H, int W, float* dP, int64_t ldp, int accumulate,
+                                    void* stream) {
+  conv_tap_scatter_kernel<<<grid_for(2LL * H * W * C), kT, 0, STREAM>>>(G, ldg, C, h, w, s, H, W, dP, ldp, accumulate);
+  DONE(1);
+}
+extern "C" int b3d_softmax(const void* S, void* P, int64_t rows, int L, int64_t ld, void* stream) {
+  softmax_kernel<<<cdiv(rows, 8), 256, 0, STREAM>>>((const bf16*)S, (bf16*)P, rows, L, ld);
+  DONE(1);
+}
+extern "C" int b3d_softmax_bwd(const void* P, const void* dP, void* dS, int64_t rows, int L, int64_t ld, void* stream) {
+  softmax_bwd_kernel<<<cdiv(rows, 8), 256, 0, STREAM>>>((const bf16*)P, (const bf16*)dP, (bf16*)dS, rows, L, ld);
+  DONE(1);
+}
+extern "C" int b3d_q_sample(const float* z, const float* noise, const float* logsnr, const float* x, const float* xrand, const uint8_t* mask,
+                            float* z_out, float* x_out, int B, int64_t per_sample, void* stream) {
+  B3D_CHECK_ARG(z && noise && logsnr && z_out, "q_sample: null");
+  B3D_CHECK_ARG(!x_out || (x && xrand && mask), "q_sample: cond replacement needs x, xrand, mask");
+  q_sample_kernel<<<grid_for((long long)B * per_sample), kT, 0, STREAM>>>(z, noise, logsnr, x, xrand, mask, z_out, x_out, per_sample,
+                                                                        (long long)B * per_sample);
+  DONE(1);
+}
+#define B3D_LOSS_MAX_BLOCKS 1024
+extern "C" int b3d_loss_scratch_bytes(void) { return (B3D_LOSS_MAX_BLOCKS + 1) * 4; }
+extern "C" int b3d_loss(const float* noise, const float* pred, float* dpred, int64_t n, int loss_type, float grad_scale, void* scratch,
+                        float* loss_out, void* stream) {
+  B3D_CHECK_ARG(noise && pred && scratch && loss_out && n > 0, "loss: null/empty");
+  B3D_CHECK_ARG(loss_type >= 0 && loss_type <= 2, "loss: type must be 0 (l2), 1 (l1) or 2 (huber)");
+  const int blocks = grid_for(n, kT * 4, B3D_LOSS_MAX_BLOCKS);
+  float* partials = (float*)scratch;
+  unsigned int* ticket = (unsigned int*)scratch + B3D_LOSS_MAX_BLOCKS;   // must be zero on entry; left at zero
+  loss_kernel<<<blocks, kT, 0, STREAM>>>(noise, pred, dpred, n, loss_type, grad_scale, partials, ticket, loss_out);
+  DONE(1);
+}
+extern "C" int b3d_sampler_update(const float* z, const float* eps_c, const float* eps_u, const float* w, const float* noise, float* out,
+                                  float logsnr, float logsnr_next, int B, int64_t per_sample, void* stream) {
+  B3D_CHECK_ARG(z && eps_c && eps_u && w && out, "sampler_update: null");
+  // scalar schedule terms in fp32 like the reference's 0-d tensors (sampling.py:84-90)
+  const float c = -expm1f(logsnr - logsnr_next);
+  const float sa = 1.f / (1.f + expf(-logsnr)), san = 1.f / (1.f + expf(-logsnr_next));
+  const float ss = 1.f / (1.f + expf(logsnr)), ssn = 1.f / (1.f + expf(logsnr_next));
+  const int add_noise = (logsnr_next != 0.f) ? 1 : 0;   // sampling.py:124
+  B3D_CHECK_ARG(!add_noise || noise, "sampler_update: noise required");
+  sampler_update_kernel<<<grid_for((long long)B * per_sample), kT, 0, STREAM>>>(z, eps_c, eps_u, w, noise, out, sqrtf(sa), sqrtf(ss), sqrtf(san), c,
+                                                                              sqrtf(ssn * c), add_noise, per_sample, (long long)B * per_sample);
+  DONE(1);
+}
+extern "C" int b3d_adam(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2, float eps, int step,
+                        float grad_scale, void* stream) {
+  B3D_CHECK_ARG(p && g && m && v && step >= 1, "adam: args");
+  const float bc1 = 1.f - powf(beta1, (float)step), bc2 = 1.f - powf(beta2, (float)step);
+  adam_kernel<<<grid_for(n), kT, 0, STREAM>>>(p, g, m, v, n, lr, beta1, beta2, eps, bc1, bc2, grad_scale);
+  DONE(1);
+}

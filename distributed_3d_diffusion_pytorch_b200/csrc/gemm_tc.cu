@@ -1,0 +1,606 @@
+// b3d tensor-core path: ONE warp-specialised, persistent tcgen05 kernel for every GEMM-shaped op of
+// the X-UNet (3x3/1x1 convolutions as implicit GEMM, FiLM / linear layers, attention matmuls),
+// forward, data-gradient and weight-gradient.
+//
+//   warp 0 (one lane)  TMA producer : 4-D tiled tensor maps, SWIZZLE_128B, zero fill out of bounds
+//                                      (3x3 halo = shifted box coordinates, strided conv = traversal
+//                                      strides; no im2col buffer ever exists)
+//   warp 1 (one lane)  MMA issuer   : tcgen05.mma cta_group::1 kind::f16, M=128, N=16..256, K=16,
+//                                      bf16 x bf16 -> fp32 accumulators in TMEM (double buffered)
+//   warps 2..5         epilogue     : tcgen05.ld 32x32b.x32 -> registers -> bias / per-image vector /
+//                                      residual / scale / SiLU -> bf16 or fp32 (optionally atomic) stores
+//
+// Operands may be K-major (K = channels, contiguous) or MN-major (K = pixels); see include/b3d.h.
+#include <cuda.h>
+#include <stdarg.h>
+
+#include "../../include/b3d.h"
+#include "b3d_common.cuh"
+
+namespace {
+
+constexpr int BM = 128;
+constexpr int BK = 64;  // bf16 elements = one 128-byte swizzle row
+constexpr int kThreads = 192;
+constexpr int kMaxSeg = 27;
+constexpr uint32_t kABytes = BM * BK * 2;  // 16 KB in both majors
+
+struct Seg {
+  int32_t src, dx, dy, ncb, bk0;
+};
+
+struct alignas(64) KP {
+  CUtensorMap tmA[3];
+  CUtensorMap tmB;
+  Seg seg[kMaxSeg];
+  int nseg;
+  int a_major, b_major, batched, b_xor, o_xor;
+  int BN, b_chunks;
+  int tiles_m, tiles_n, tiles_b, tiles_z, tiles_total;
+  int bw, bh, bnn, tiles_x, tiles_y;
+  int W, H, N;
+  int stride, pad;
+  int kbw, kbh, kbn, kblk_x, kblk_y, kblk_total;
+  int split_k, b_taps;
+  int kchan_blocks;
+  int m_rows, n_cols;
+  int num_stages;
+  uint32_t a_tx, b_tx, b_bytes, stage_bytes;
+  uint32_t idesc;
+  int tmem_cols, acc_stride;
+  void* out;
+  void* out2;
+  const float* bias;
+  const float* rowvec;
+  const bf16* resid;
+  long long rowvec_ld;
+  long long os_x, os_y, os_n, os_tap;
+  float alpha, out_scale;
+  int act, out_fp32, out_atomic;
+};
+
+// ------------------------------------------------------------------ PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+// Bounded wait: a protocol bug must trap (and surface as a CUDA error) instead of hanging the GPU.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done = 0;
+  long long t0 = 0;
+  for (uint32_t it = 0;; ++it) {
+    asm volatile(
+        "{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (done) return;
+    if (it == 64) t0 = clock64();
+    if (it > 64 && (it & 1023) == 0 && clock64() - t0 > 6000000000LL) {
+      printf("b3d_gemm: mbarrier wait timed out (block %d thread %d bar %u parity %u)\n", blockIdx.x, threadIdx.x, bar, parity);
+      __trap();
+    }
+  }
+}
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* tm, uint32_t bar, int c0, int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(tm)), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(ncols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
+  asm volatile(
+      "{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* v) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, %17, "
+      "%18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+      "tcgen05.wait::ld.sync.aligned;"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
+        "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]),
+        "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]),
+        "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr)
+      : "memory");
+}
+
+// UMMA shared-memory descriptor (sm_100): start>>4 [0,14) | LBO>>4 [16,30) | SBO>>4 [32,46) | version=1 [46,48)
+// | layout SWIZZLE_128B=2 [61,64).  K-major: SBO = 8 rows * 128 B; LBO unused.  MN-major: LBO = byte stride
+// between 64-element chunks of the M/N extent, SBO = 8 K-rows * 128 B.
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr >> 4) & 0x3FFF);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+
+struct TileCoord {
+  int tn, tm, tb, tz;
+  int x0, y0, n0;  // a_major = 0: first output pixel; a_major = 1: batch (y0,n0)
+  int m0;          // a_major = 1: first channel row
+  int tap, split;
+};
+
+__device__ __forceinline__ TileCoord decode_tile(const KP& p, int t) {
+  TileCoord c;
+  c.tn = t % p.tiles_n; t /= p.tiles_n;
+  c.tm = t % p.tiles_m; t /= p.tiles_m;
+  c.tb = t % p.tiles_b; c.tz = t / p.tiles_b;
+  c.tap = c.tz % p.b_taps;
+  c.split = c.tz / p.b_taps;
+  c.m0 = 0; c.x0 = 0; c.y0 = 0; c.n0 = 0;
+  if (p.a_major == 0) {
+    int tx = c.tm % p.tiles_x;
+    int r = c.tm / p.tiles_x;
+    c.x0 = tx * p.bw;
+    c.y0 = (r % p.tiles_y) * p.bh;
+    c.n0 = (r / p.tiles_y) * p.bnn;
+  } else {
+    c.m0 = c.tm * BM;
+    if (p.batched) { c.y0 = c.tb % p.H; c.n0 = c.tb / p.H; }
+  }
+  return c;
+}
+
+// number of K blocks of a tile and (for pixel-K without batching) the first pixel block
+__device__ __forceinline__ void k_range(const KP& p, const TileCoord& c, int& kb0, int& nkb) {
+  if (p.a_major == 0) {
+    kb0 = 0;
+    if (p.b_major == 0) { nkb = 0; for (int s = 0; s < p.nseg; ++s) nkb += p.seg[s].ncb; }
+    else nkb = p.kchan_blocks;
+  } else if (p.batched) {
+    kb0 = 0; nkb = p.kblk_x;
+  } else {
+    long long tot = p.kblk_total;
+    kb0 = (int)(tot * c.split / p.split_k);
+    nkb = (int)(tot * (c.split + 1) / p.split_k) - kb0;
+  }
+}
+
+__global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_constant__ KP p) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint64_t bars[2 * 8 + 4];
+  __shared__ uint32_t tmem_base_smem;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const int S = p.num_stages;
+  auto full_bar = [&](int s) { return smem_u32(&bars[s]); };
+  auto empty_bar = [&](int s) { return smem_u32(&bars[8 + s]); };
+  auto tfull_bar = [&](int s) { return smem_u32(&bars[16 + s]); };
+  auto tempty_bar = [&](int s) { return smem_u32(&bars[18 + s]); };
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < S; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 4); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) tmem_alloc(smem_u32(&tmem_base_smem), (uint32_t)p.tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_smem;
+
+  if (warp == 0) {
+    // ===================================================================== TMA producer
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int t = blockIdx.x; t < p.tiles_total; t += gridDim.x) {
+        const TileCoord c = decode_tile(p, t);
+        int kb0, nkb; k_range(p, c, kb0, nkb);
+        const int ncol0 = c.tn * p.BN;
+        auto acquire = [&]() -> uint32_t {
+          mbar_wait(empty_bar(stage), phase ^ 1);
+          mbar_expect_tx(full_bar(stage), p.a_tx + p.b_tx);
+          return smem_base + (uint32_t)stage * p.stage_bytes;
+        };
+        auto advance = [&]() { if (++stage == S) { stage = 0; phase ^= 1; } };
+        if (p.a_major == 0 && p.b_major == 0) {
+          const int by = p.batched ? c.y0 : 0, bn = p.batched ? (c.n0 ^ p.b_xor) : 0;
+          for (int s = 0; s < p.nseg; ++s) {
+            const Seg sg = p.seg[s];
+            const int ax = c.x0 * p.stride + sg.dx, ay = c.y0 * p.stride + sg.dy;
+            for (int cb = 0; cb < sg.ncb; ++cb) {
+              const uint32_t sa = acquire();
+              tma_load_4d(sa, &p.tmA[sg.src], full_bar(stage), cb * BK, ax, ay, c.n0);
+              tma_load_4d(sa + kABytes, &p.tmB, full_bar(stage), sg.bk0 + cb * BK, ncol0, by, bn);
+              advance();
+            }
+          }
+        } else if (p.a_major == 0) {  // (0,1): K = channels of A = pixels (x) of B, batched
+          for (int cb = 0; cb < nkb; ++cb) {
+            const uint32_t sa = acquire();
+            tma_load_4d(sa, &p.tmA[0], full_bar(stage), cb * BK, c.x0, c.y0, c.n0);
+            for (int j = 0; j < p.b_chunks; ++j)
+              tma_load_4d(sa + kABytes + j * 8192, &p.tmB, full_bar(stage), ncol0 + j * 64, cb * BK, c.y0, c.n0 ^ p.b_xor);
+            advance();
+          }
+        } else {  // (1,1): K = pixels of both
+          const int dx = p.b_taps == 9 ? (c.tap % 3) - p.pad : 0;
+          const int dy = p.b_taps == 9 ? (c.tap / 3) - p.pad : 0;
+          for (int i = 0; i < nkb; ++i) {
+            int kx, ky, kn;
+            if (p.batched) { kx = i * p.kbw; ky = c.y0; kn = c.n0; }
+            else {
+              int pb = kb0 + i;
+              kx = (pb % p.kblk_x) * p.kbw; pb /= p.kblk_x;
+              ky = (pb % p.kblk_y) * p.kbh; kn = (pb / p.kblk_y) * p.kbn;
+            }
+            const uint32_t sa = acquire();
+            tma_load_4d(sa, &p.tmA[0], full_bar(stage), c.m0, kx, ky, kn);
+            tma_load_4d(sa + 8192, &p.tmA[0], full_bar(stage), c.m0 + 64, kx, ky, kn);
+            for (int j = 0; j < p.b_chunks; ++j)
+              tma_load_4d(sa + kABytes + j * 8192, &p.tmB, full_bar(stage), ncol0 + j * 64, kx * p.stride + dx,
+                          ky * p.stride + dy, kn ^ p.b_xor);
+            advance();
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================================================================== MMA issuer
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      int acc = 0; uint32_t acc_phase = 0;
+      const uint32_t a_kstep = p.a_major ? 2048u : 32u, b_kstep = p.b_major ? 2048u : 32u;
+      const uint32_t a_lbo = p.a_major ? 8192u : 16u, b_lbo = p.b_major ? 8192u : 16u;
+      for (int t = blockIdx.x; t < p.tiles_total; t += gridDim.x) {
+        const TileCoord c = decode_tile(p, t);
+        int kb0, nkb; k_range(p, c, kb0, nkb);
+        mbar_wait(tempty_bar(acc), acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * p.acc_stride);
+        for (int kb = 0; kb < nkb; ++kb) {
+          mbar_wait(full_bar(stage), phase);
+          tc_fence_after();
+          const uint32_t sa = smem_base + (uint32_t)stage * p.stage_bytes;
+          const uint32_t sb = sa + kABytes;
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            const uint64_t ad = umma_desc(sa + k * a_kstep, a_lbo, 1024u);
+            const uint64_t bd = umma_desc(sb + k * b_kstep, b_lbo, 1024u);
+            umma_bf16(d_tmem, ad, bd, p.idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+          umma_commit(empty_bar(stage));  // frees the smem slot once these MMAs have read it
+          if (++stage == S) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(tfull_bar(acc));      // accumulator complete -> epilogue
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+  } else {
+    // ===================================================================== epilogue (warps 2..5)
+    const int quad = warp & 3;  // TMEM lane quadrant this warp may access
+    const int r = quad * 32 + lane;
+    int acc = 0; uint32_t acc_phase = 0;
+    for (int t = blockIdx.x; t < p.tiles_total; t += gridDim.x) {
+      const TileCoord c = decode_tile(p, t);
+      bool row_ok;
+      long long off;
+      int img = 0;
+      if (p.a_major == 0) {
+        const int x = c.x0 + r % p.bw;
+        const int q = r / p.bw;
+        const int y = c.y0 + q % p.bh;
+        const int n = c.n0 + q / p.bh;
+        row_ok = (r < p.bw * p.bh * p.bnn) && x < p.W && y < p.H && n < p.N;
+        img = n;
+        off = (long long)(n ^ p.o_xor) * p.os_n + (long long)y * p.os_y + (long long)x * p.os_x;
+      } else {
+        const int row = c.m0 + r;
+        row_ok = row < p.m_rows;
+        img = c.n0;
+        off = (long long)(c.n0 ^ p.o_xor) * p.os_n + (long long)c.y0 * p.os_y + (long long)row * p.os_x + (long long)c.tap * p.os_tap;
+      }
+      mbar_wait(tfull_bar(acc), acc_phase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + (uint32_t)(acc * p.acc_stride) + ((uint32_t)(quad * 32) << 16);
+      const int nchunks = (p.BN + 31) / 32;
+      for (int ch = 0; ch < nchunks; ++ch) {
+        uint32_t v[32];
+        tmem_ld32(taddr + ch * 32, v);
+        const int col0 = c.tn * p.BN + ch * 32;
+        if (row_ok && col0 < p.n_cols) {
+          const int ncol = min(32, min(p.n_cols - col0, p.BN - ch * 32));
+          float f[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]) * p.alpha;
+          if (p.bias) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) if (i < ncol) f[i] += __ldg(p.bias + col0 + i);
+          }
+          if (p.rowvec) {
+            const float* rv = p.rowvec + (long long)img * p.rowvec_ld + col0;
+#pragma unroll
+            for (int i = 0; i < 32; ++i) if (i < ncol) f[i] += __ldg(rv + i);
+          }
+          const long long o = off + col0;
+          const bool vec_ok = (ncol == 32) && ((o & 7) == 0);
+          if (p.resid) {
+            const bf16* rp = p.resid + o;
+            if (vec_ok) {
+#pragma unroll
+              for (int g = 0; g < 4; ++g) {
+                bf16x8 pk = *reinterpret_cast<const bf16x8*>(rp + g * 8);
+                float t8[8]; b3d_unpack8(pk, t8);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) f[g * 8 + i] += t8[i];
+              }
+            } else {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) if (i < ncol) f[i] += __bfloat162float(rp[i]);
+            }
+          }
+#pragma unroll
+          for (int i = 0; i < 32; ++i) f[i] *= p.out_scale;
+          if (p.act == 1 && p.out2 == nullptr) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) f[i] = b3d_silu(f[i]);
+          }
+          if (p.out_fp32) {
+            float* op = reinterpret_cast<float*>(p.out) + o;
+            if (p.out_atomic) {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) if (i < ncol) atomicAdd(op + i, f[i]);
+            } else if (vec_ok) {
+#pragma unroll
+              for (int g = 0; g < 8; ++g)
+                *reinterpret_cast<float4*>(op + g * 4) = make_float4(f[g * 4], f[g * 4 + 1], f[g * 4 + 2], f[g * 4 + 3]);
+            } else {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) if (i < ncol) op[i] = f[i];
+            }
+          } else {
+            bf16* op = reinterpret_cast<bf16*>(p.out) + o;
+            if (vec_ok) {
+#pragma unroll
+              for (int g = 0; g < 4; ++g) *reinterpret_cast<bf16x8*>(op + g * 8) = b3d_pack8(f + g * 8);
+            } else {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) if (i < ncol) op[i] = __float2bfloat16(f[i]);
+            }
+          }
+          if (p.out2) {
+            bf16* op2 = reinterpret_cast<bf16*>(p.out2) + o;
+#pragma unroll
+            for (int i = 0; i < 32; ++i) f[i] = b3d_silu(f[i]);
+            if (vec_ok) {
+#pragma unroll
+              for (int g = 0; g < 4; ++g) *reinterpret_cast<bf16x8*>(op2 + g * 8) = b3d_pack8(f + g * 8);
+            } else {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) if (i < ncol) op2[i] = __float2bfloat16(f[i]);
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty_bar(acc));
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, (uint32_t)p.tmem_cols);
+  }
+}
+
+// ------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+int make_map(CUtensorMap* tm, const b3d_view4& v, const uint32_t box[4], const uint32_t estr[4]) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) { b3d_set_error("cuTensorMapEncodeTiled entry point not available"); return B3D_ERR_CUDA; }
+  cuuint64_t gdim[4] = {(cuuint64_t)v.dim[0], (cuuint64_t)v.dim[1], (cuuint64_t)v.dim[2], (cuuint64_t)v.dim[3]};
+  cuuint64_t gstr[3] = {(cuuint64_t)v.stride[0] * 2, (cuuint64_t)v.stride[1] * 2, (cuuint64_t)v.stride[2] * 2};
+  for (int i = 0; i < 3; ++i) {
+    if (gdim[i + 1] == 1 && gstr[i] == 0) gstr[i] = (i == 0 ? (cuuint64_t)((v.dim[0] + 7) / 8 * 8) * 2 : gstr[i - 1] * gdim[i]);
+    if (gstr[i] % 16 != 0) { b3d_set_error("b3d_gemm: stride %d (%llu bytes) not a multiple of 16", i, (unsigned long long)gstr[i]); return B3D_ERR_ARG; }
+  }
+  if (((uintptr_t)v.ptr & 15) != 0) { b3d_set_error("b3d_gemm: operand pointer not 16-byte aligned"); return B3D_ERR_ARG; }
+  cuuint32_t bx[4] = {box[0], box[1], box[2], box[3]};
+  cuuint32_t es[4] = {estr[0], estr[1], estr[2], estr[3]};
+  for (int i = 0; i < 4; ++i)
+    if (bx[i] == 0 || bx[i] > 256) { b3d_set_error("b3d_gemm: TMA box dim %d = %u out of range", i, bx[i]); return B3D_ERR_ARG; }
+  CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(v.ptr), gdim, gstr, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    b3d_set_error("cuTensorMapEncodeTiled failed (%d): dims %llu,%llu,%llu,%llu strides %llu,%llu,%llu box %u,%u,%u,%u es %u,%u,%u,%u", (int)r,
+                  (unsigned long long)gdim[0], (unsigned long long)gdim[1], (unsigned long long)gdim[2], (unsigned long long)gdim[3],
+                  (unsigned long long)gstr[0], (unsigned long long)gstr[1], (unsigned long long)gstr[2], bx[0], bx[1], bx[2], bx[3], es[0], es[1],
+                  es[2], es[3]);
+    return B3D_ERR_CUDA;
+  }
+  return B3D_OK;
+}
+
+int pow2_ceil(int v) { int p = 1; while (p < v) p <<= 1; return p; }
+
+int choose_bn(int n_cols, int b_major) {
+  if (n_cols <= 256) {
+    int bn = (n_cols + 15) / 16 * 16;
+    return bn;
+  }
+  const int cands[] = {256, 192, 128, 64};
+  int best = 128; long long best_cost = -1;
+  for (int c : cands) {
+    long long tiles = (n_cols + c - 1) / c;
+    long long cost = tiles * c;  // padded columns computed
+    if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = c; }
+  }
+  (void)b_major;
+  return best;
+}
+
+}  // namespace
+
+static int64_t g_launches = 0;
+extern "C" int64_t b3d_launch_count(void) { return g_launches; }
+void b3d_count_launch(int n) { g_launches += n; }
+
+extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  B3D_CHECK_ARG(d != nullptr && d->out != nullptr, "b3d_gemm: null descriptor/output");
+  B3D_CHECK_ARG(d->a_major == 0 || d->a_major == 1, "b3d_gemm: a_major");
+  B3D_CHECK_ARG(!(d->a_major == 1 && d->b_major == 0), "b3d_gemm: (a_major=1, b_major=0) is not used by the model");
+  B3D_CHECK_ARG(d->n_cols > 0, "b3d_gemm: n_cols");
+  const int s = d->conv_stride > 0 ? d->conv_stride : 1;
+  B3D_CHECK_ARG(s <= 8, "b3d_gemm: conv_stride > 8 (TMA traversal stride limit)");
+
+  KP p;
+  memset(&p, 0, sizeof(p));
+  p.a_major = d->a_major; p.b_major = d->b_major; p.batched = d->batched;
+  p.b_xor = d->b_batch_xor; p.o_xor = d->out_batch_xor;
+  p.W = d->W; p.H = d->H; p.N = d->N; p.stride = s; p.pad = d->pad;
+  p.n_cols = d->n_cols; p.m_rows = d->m_rows;
+  p.b_taps = d->b_taps > 0 ? d->b_taps : 1;
+  p.split_k = d->split_k > 0 ? d->split_k : 1;
+  B3D_CHECK_ARG(p.W > 0 && p.H > 0 && p.N > 0, "b3d_gemm: W/H/N");
+
+  int BN = d->bn_tile > 0 ? d->bn_tile : choose_bn(d->n_cols, d->b_major);
+  B3D_CHECK_ARG(BN % 16 == 0 && BN >= 16 && BN <= 256, "b3d_gemm: tile N %d must be a multiple of 16 in [16,256]", BN);
+  p.BN = BN;
+  p.tiles_n = (d->n_cols + BN - 1) / BN;
+  p.b_chunks = (BN + 63) / 64;
+  p.b_bytes = d->b_major ? (uint32_t)p.b_chunks * 8192u : (uint32_t)((BN * 128 + 1023) / 1024 * 1024);
+  p.b_tx = d->b_major ? (uint32_t)p.b_chunks * 8192u : (uint32_t)BN * 128u;
+  p.stage_bytes = kABytes + p.b_bytes;
+  p.num_stages = (int)((227 * 1024 - 2048) / p.stage_bytes);
+  if (p.num_stages > 8) p.num_stages = 8;
+  p.acc_stride = (BN + 31) / 32 * 32;
+  p.tmem_cols = pow2_ceil(2 * p.acc_stride);
+  if (p.tmem_cols < 32) p.tmem_cols = 32;
+  // instruction descriptor: D fp32 (bit 4), A/B bf16 (bits 7,10), majors (15,16), N>>3 at 17, M>>4 at 24
+  p.idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)d->a_major << 15) | ((uint32_t)d->b_major << 16) | ((uint32_t)(BN >> 3) << 17) |
+            ((uint32_t)(BM >> 4) << 24);
+
+  const uint32_t ones[4] = {1, 1, 1, 1};
+  int rc;
+  if (d->a_major == 0) {
+    if (d->batched) { p.bw = d->W < BM ? d->W : BM; p.bh = 1; p.bnn = 1; }
+    else {
+      p.bw = d->W < BM ? d->W : BM;
+      p.bh = BM / p.bw; if (p.bh > d->H) p.bh = d->H; if (p.bh < 1) p.bh = 1;
+      p.bnn = (p.bh == d->H) ? BM / (p.bw * p.bh) : 1; if (p.bnn > d->N) p.bnn = d->N; if (p.bnn < 1) p.bnn = 1;
+    }
+    p.tiles_x = (d->W + p.bw - 1) / p.bw;
+    p.tiles_y = (d->H + p.bh - 1) / p.bh;
+    const int tiles_img = (d->N + p.bnn - 1) / p.bnn;
+    p.tiles_m = p.tiles_x * p.tiles_y * tiles_img;
+    p.tiles_b = 1; p.tiles_z = 1;
+    p.a_tx = (uint32_t)(p.bw * p.bh * p.bnn) * 128u;
+    const uint32_t boxA[4] = {64, (uint32_t)((p.bw - 1) * s + 1), (uint32_t)((p.bh - 1) * s + 1), (uint32_t)p.bnn};
+    const uint32_t esA[4] = {1, (uint32_t)s, (uint32_t)s, 1};
+    if (d->b_major == 0) {
+      B3D_CHECK_ARG(d->n_src >= 1 && d->n_src <= 3, "b3d_gemm: n_src");
+      int bk = 0;
+      for (int i = 0; i < d->n_src; ++i) {
+        rc = make_map(&p.tmA[i], d->a[i], boxA, esA); if (rc) return rc;
+        const int taps = d->a_taps[i] == 9 ? 9 : 1;
+        const int ncb = (d->a[i].dim[0] + BK - 1) / BK;
+        for (int tp = 0; tp < taps; ++tp) {
+          B3D_CHECK_ARG(p.nseg < kMaxSeg, "b3d_gemm: too many K segments");
+          Seg& sg = p.seg[p.nseg++];
+          sg.src = i; sg.ncb = ncb; sg.bk0 = bk;
+          sg.dx = taps == 9 ? (tp % 3) - d->pad : 0;
+          sg.dy = taps == 9 ? (tp / 3) - d->pad : 0;
+          bk += ncb * BK;
+        }
+      }
+      B3D_CHECK_ARG(bk <= d->b.dim[0] + BK - 1, "b3d_gemm: B has K=%d but A enumerates %d", d->b.dim[0], bk);
+      const uint32_t boxB[4] = {64, (uint32_t)BN, 1, 1};
+      rc = make_map(&p.tmB, d->b, boxB, ones); if (rc) return rc;
+    } else {
+      B3D_CHECK_ARG(d->batched && s == 1, "b3d_gemm: (a_major=0,b_major=1) is the batched attention form");
+      rc = make_map(&p.tmA[0], d->a[0], boxA, esA); if (rc) return rc;
+      p.kchan_blocks = (d->a[0].dim[0] + BK - 1) / BK;
+      const uint32_t boxB[4] = {64, 64, 1, 1};
+      rc = make_map(&p.tmB, d->b, boxB, ones); if (rc) return rc;
+    }
+  } else {
+    B3D_CHECK_ARG(d->m_rows > 0, "b3d_gemm: m_rows");
+    p.tiles_m = (d->m_rows + BM - 1) / BM;
+    if (d->batched) { p.kbw = 64; p.kbh = 1; p.kbn = 1; p.tiles_b = d->H * d->N; }
+    else {
+      p.kbw = pow2_ceil(d->W); if (p.kbw > 64) p.kbw = 64;
+      p.kbh = 64 / p.kbw; { int ph = pow2_ceil(d->H); if (p.kbh > ph) p.kbh = ph; }
+      p.kbn = 64 / (p.kbw * p.kbh);
+      p.tiles_b = 1;
+    }
+    p.kblk_x = (d->W + p.kbw - 1) / p.kbw;
+    p.kblk_y = (d->H + p.kbh - 1) / p.kbh;
+    p.kblk_total = d->batched ? p.kblk_x : p.kblk_x * p.kblk_y * ((d->N + p.kbn - 1) / p.kbn);
+    if (d->batched) p.split_k = 1;
+    if (p.split_k > p.kblk_total) p.split_k = p.kblk_total;
+    B3D_CHECK_ARG(p.split_k == 1 || d->out_atomic, "b3d_gemm: split_k > 1 needs out_atomic");
+    p.tiles_z = p.b_taps * p.split_k;
+    p.a_tx = 2 * 8192u;
+    const uint32_t boxA[4] = {64, (uint32_t)p.kbw, (uint32_t)p.kbh, (uint32_t)p.kbn};
+    rc = make_map(&p.tmA[0], d->a[0], boxA, ones); if (rc) return rc;
+    const uint32_t boxB[4] = {64, (uint32_t)((p.kbw - 1) * s + 1), (uint32_t)((p.kbh - 1) * s + 1), (uint32_t)p.kbn};
+    const uint32_t esB[4] = {1, (uint32_t)s, (uint32_t)s, 1};
+    rc = make_map(&p.tmB, d->b, boxB, esB); if (rc) return rc;
+  }
+  p.tiles_total = p.tiles_m * p.tiles_n * p.tiles_b * p.tiles_z;
+  B3D_CHECK_ARG(p.tiles_total > 0, "b3d_gemm: empty problem");
+
+  p.out = d->out; p.out2 = d->out2; p.bias = d->bias; p.rowvec = d->rowvec; p.rowvec_ld = d->rowvec_ld;
+  p.resid = reinterpret_cast<const bf16*>(d->resid);
+  p.os_x = d->out_stride[0]; p.os_y = d->out_stride[1]; p.os_n = d->out_stride[2]; p.os_tap = d->out_tap_stride;
+  p.alpha = d->alpha; p.out_scale = d->out_scale; p.act = d->act; p.out_fp32 = d->out_fp32; p.out_atomic = d->out_atomic;
+  B3D_CHECK_ARG(!d->out_atomic || d->out_fp32, "b3d_gemm: out_atomic needs fp32 output");
+
+  const size_t smem = (size_t)p.num_stages * p.stage_bytes + 1024;
+  static bool attr_set = false;
+  if (!attr_set) {
+    B3D_CUDA(cudaFuncSetAttribute(b3d_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attr_set = true;
+  }
+  int grid = p.tiles_total < b3d_num_sms() ? p.tiles_total : b3d_num_sms();
+  b3d_gemm_kernel<<<grid, kThreads, smem, stream>>>(p);
+  B3D_LAUNCH_CHECK();
+  b3d_count_launch(1);
+  return B3D_OK;
+}

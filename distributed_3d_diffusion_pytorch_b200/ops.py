@@ -1,0 +1,310 @@
+"""Tensor-level bindings of the b3d C ABI (include/b3d.h): one method = one entry point.
+
+torch is plumbing here (device memory, streams); all arithmetic happens in libb3d.so.  Tensors are
+passed as (data_ptr, strides) -- any view whose innermost stride is 1 is accepted, so channel
+slices / head splits need no copies.  There is no fallback path: without the CUDA library every
+method raises (see _lib.load)."""
+import ctypes
+from dataclasses import dataclass, field
+from typing import List, Optional
+
+import torch
+
+from . import _lib
+
+c_void = ctypes.c_void_p
+c_i32 = ctypes.c_int32
+c_i64 = ctypes.c_int64
+c_f32 = ctypes.c_float
+
+
+class _View4(ctypes.Structure):
+    _fields_ = [("ptr", c_void), ("dim", c_i32 * 4), ("stride", c_i64 * 3)]
+
+
+class _GemmDesc(ctypes.Structure):
+    _fields_ = [
+        ("a", _View4 * 3), ("a_taps", c_i32 * 3), ("n_src", c_i32),
+        ("b", _View4),
+        ("a_major", c_i32), ("b_major", c_i32),
+        ("conv_stride", c_i32), ("pad", c_i32), ("b_taps", c_i32),
+        ("W", c_i32), ("H", c_i32), ("N", c_i32),
+        ("m_rows", c_i32), ("n_cols", c_i32),
+        ("batched", c_i32), ("b_batch_xor", c_i32), ("out_batch_xor", c_i32), ("split_k", c_i32),
+        ("out", c_void), ("out_fp32", c_i32), ("out_stride", c_i64 * 3), ("out_tap_stride", c_i64),
+        ("out2", c_void), ("bias", c_void), ("rowvec", c_void), ("rowvec_ld", c_i64), ("resid", c_void),
+        ("alpha", c_f32), ("out_scale", c_f32), ("act", c_i32), ("out_atomic", c_i32), ("bn_tile", c_i32),
+    ]
+
+
+@dataclass
+class GemmDesc:
+    """Python mirror of b3d_gemm_desc.  Operand/output tensors are 4-D views [n, y, x, c] with
+    stride(c) == 1 (see include/b3d.h for the meaning of the majors)."""
+    a: List[torch.Tensor]
+    b: torch.Tensor
+    out: torch.Tensor                       # [n, y, rows(x), cols]
+    n_cols: int
+    a_taps: List[int] = field(default_factory=lambda: [1])
+    a_major: int = 0
+    b_major: int = 0
+    conv_stride: int = 1
+    pad: int = 0
+    b_taps: int = 1
+    W: int = 0
+    H: int = 1
+    N: int = 1
+    m_rows: int = 0
+    batched: bool = False
+    b_batch_xor: int = 0
+    out_batch_xor: int = 0
+    split_k: int = 1
+    out_tap_stride: int = 0
+    out2: Optional[torch.Tensor] = None
+    bias: Optional[torch.Tensor] = None
+    rowvec: Optional[torch.Tensor] = None   # fp32 [N, >=n_cols]
+    resid: Optional[torch.Tensor] = None    # same shape/strides as out
+    alpha: float = 1.0
+    out_scale: float = 1.0
+    act: int = 0
+    out_atomic: bool = False
+    bn_tile: int = 0
+
+
+def _ptr(t):
+    return c_void(t.data_ptr()) if t is not None else c_void(0)
+
+
+def _view4(t):
+    assert t.dim() == 4 and (t.stride(3) == 1 or t.shape[3] == 1), (t.shape, t.stride())
+    v = _View4()
+    v.ptr = t.data_ptr()
+    n, y, x, c = t.shape
+    v.dim[0], v.dim[1], v.dim[2], v.dim[3] = c, x, y, n
+    v.stride[0], v.stride[1], v.stride[2] = t.stride(2), t.stride(1), t.stride(0)
+    return v
+
+
+def _u8(mask):
+    return mask if mask.dtype == torch.uint8 else mask.to(torch.uint8)
+
+
+class CudaOps:
+    """The product backend: every method launches kernels of libb3d.so on the current stream."""
+
+    act_dtype = torch.bfloat16
+    name = "cuda"
+
+    def __init__(self, device):
+        self.lib = _lib.load()
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise _lib.B3DError("b3d kernels need a CUDA device (sm_100a); there is no CPU path")
+
+    # ---- plumbing
+    def stream(self):
+        return c_void(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def empty(self, shape, dtype=None):
+        return torch.empty(shape, dtype=dtype or self.act_dtype, device=self.device)
+
+    def zeros(self, shape, dtype=None):
+        return torch.zeros(shape, dtype=dtype or self.act_dtype, device=self.device)
+
+    def _call(self, name, *args):
+        _lib.check(getattr(self.lib, name)(*args), name)
+
+    # ---- tensor-core path
+    def gemm(self, d: GemmDesc):
+        cd = _GemmDesc()
+        assert 1 <= len(d.a) <= 3
+        for i, t in enumerate(d.a):
+            assert t.dtype == torch.bfloat16
+            cd.a[i] = _view4(t)
+            cd.a_taps[i] = d.a_taps[i] if i < len(d.a_taps) else 1
+        cd.n_src = len(d.a)
+        assert d.b.dtype == torch.bfloat16
+        cd.b = _view4(d.b)
+        cd.a_major, cd.b_major = d.a_major, d.b_major
+        cd.conv_stride, cd.pad, cd.b_taps = d.conv_stride, d.pad, d.b_taps
+        cd.W, cd.H, cd.N = d.W, d.H, d.N
+        cd.m_rows, cd.n_cols = d.m_rows, d.n_cols
+        cd.batched, cd.b_batch_xor, cd.out_batch_xor, cd.split_k = int(d.batched), d.b_batch_xor, d.out_batch_xor, d.split_k
+        o = d.out
+        assert o.dim() == 4 and o.stride(3) == 1 and o.dtype in (torch.bfloat16, torch.float32)
+        cd.out = o.data_ptr()
+        cd.out_fp32 = int(o.dtype == torch.float32)
+        cd.out_stride[0], cd.out_stride[1], cd.out_stride[2] = o.stride(2), o.stride(1), o.stride(0)
+        cd.out_tap_stride = d.out_tap_stride
+        if d.out2 is not None:
+            assert d.out2.stride() == o.stride() and d.out2.dtype == torch.bfloat16
+            cd.out2 = d.out2.data_ptr()
+        if d.bias is not None:
+            assert d.bias.dtype == torch.float32 and d.bias.numel() >= d.n_cols
+            cd.bias = d.bias.data_ptr()
+        if d.rowvec is not None:
+            assert d.rowvec.dtype == torch.float32 and d.rowvec.dim() == 2 and d.rowvec.stride(1) == 1
+            cd.rowvec = d.rowvec.data_ptr()
+            cd.rowvec_ld = d.rowvec.stride(0)
+        if d.resid is not None:
+            assert d.resid.stride() == o.stride() and d.resid.dtype == torch.bfloat16
+            cd.resid = d.resid.data_ptr()
+        cd.alpha, cd.out_scale, cd.act = d.alpha, d.out_scale, d.act
+        cd.out_atomic, cd.bn_tile = int(d.out_atomic), d.bn_tile
+        self._call("b3d_gemm", ctypes.byref(cd), self.stream())
+
+    # ---- conditioning
+    def pose_embedding(self, K, R, t, mask, pos_emb, first_emb, other_emb, out):
+        B = K.shape[0]
+        N, H, W, ld = out.shape
+        assert N == 2 * B and out.is_contiguous() and K.dtype == torch.float64
+        self._call("b3d_pose_embedding", _ptr(K.contiguous()), _ptr(R.contiguous()), _ptr(t.contiguous()), _ptr(_u8(mask)),
+                   _ptr(pos_emb), _ptr(first_emb), _ptr(other_emb), _ptr(out), c_i32(int(out.dtype == torch.float32)),
+                   c_i64(ld), c_i32(B), c_i32(H), c_i32(W), self.stream())
+
+    def pose_embedding_bwd(self, dP, dpos, dfirst, dother):
+        _, H, W, ld = dP.shape
+        assert dP.dtype == torch.float32 and dP.is_contiguous()
+        self._call("b3d_pose_embedding_bwd", _ptr(dP), c_i64(ld), c_i32(H), c_i32(W), _ptr(dpos), _ptr(dfirst), _ptr(dother),
+                   self.stream())
+
+    def ddpm_embedding(self, logsnr, out):
+        n, e = out.shape
+        assert logsnr.dtype == torch.float32 and logsnr.numel() == n and out.is_contiguous()
+        self._call("b3d_ddpm_embedding", _ptr(logsnr), _ptr(out), c_i32(n), c_i32(e), self.stream())
+
+    def pack_input(self, x, z, out):
+        B, _, H, W = x.shape
+        self._call("b3d_pack_input", _ptr(x.contiguous()), _ptr(z.contiguous()), _ptr(out), c_i32(B), c_i32(H * W), self.stream())
+
+    def unpack_input_grad(self, g, dx, dz):
+        B, _, H, W = dx.shape
+        self._call("b3d_unpack_input_grad", _ptr(g), _ptr(dx), _ptr(dz), c_i32(B), c_i32(H * W), self.stream())
+
+    def unpack_output(self, y, eps):
+        B, _, H, W = eps.shape
+        self._call("b3d_unpack_output", _ptr(y), c_i64(y.shape[-1]), _ptr(eps), c_i32(B), c_i32(H * W), self.stream())
+
+    def pack_output_grad(self, deps, dy):
+        B, _, H, W = deps.shape
+        self._call("b3d_pack_output_grad", _ptr(deps.contiguous()), _ptr(dy), c_i64(dy.shape[-1]), c_i32(B), c_i32(H * W), self.stream())
+
+    # ---- parameter layouts
+    def pack_weight(self, w, mode, out, ci0=0, cn=None, Cpad=None, k_off=0):
+        Co, Ci = w.shape[0], w.shape[1]
+        taps = w.numel() // (Co * Ci)
+        cn = Ci if cn is None else cn
+        assert w.dtype == torch.float32 and w.is_contiguous() and out.dim() == 2 and out.stride(1) == 1
+        self._call("b3d_pack_weight", _ptr(w), c_i32(Co), c_i32(Ci), c_i32(taps), c_i32(mode), c_i32(ci0), c_i32(cn), c_i32(Cpad or 0),
+                   c_i64(k_off), _ptr(out), c_i64(out.stride(0)), self.stream())
+
+    def unpack_wgrad(self, g, k_off, Cpad, dw, ci0=0, cn=None, accumulate=False):
+        Co, Ci = dw.shape[0], dw.shape[1]
+        taps = dw.numel() // (Co * Ci)
+        cn = Ci if cn is None else cn
+        assert g.dtype == torch.float32 and dw.is_contiguous()
+        self._call("b3d_unpack_wgrad", _ptr(g), c_i64(g.stride(0)), c_i64(k_off), c_i32(Cpad), c_i32(Co), c_i32(Ci), c_i32(taps), c_i32(ci0),
+                   c_i32(cn), _ptr(dw), c_i32(int(accumulate)), self.stream())
+
+    def cast(self, src, out):
+        assert src.dtype == torch.float32 and src.is_contiguous() and out.is_contiguous()
+        self._call("b3d_cast_bf16", _ptr(src), _ptr(out), c_i64(src.numel()), self.stream())
+
+    # ---- resampling / elementwise / reductions
+    def avgpool2(self, x, out, scale=0.25):
+        N, H, W, C = x.shape
+        self._call("b3d_avgpool2", _ptr(x), _ptr(out), c_i32(N), c_i32(H), c_i32(W), c_i32(C), c_f32(scale), self.stream())
+
+    def upsample2(self, x, out, scale=1.0):
+        N, Ho, Wo, C = out.shape
+        self._call("b3d_upsample2", _ptr(x), _ptr(out), c_i32(N), c_i32(Ho), c_i32(Wo), c_i32(C), c_f32(scale), self.stream())
+
+    def silu_bwd(self, dy, x, dx):
+        self._call("b3d_silu_bwd", _ptr(dy), _ptr(x), _ptr(dx), c_i64(dy.numel()), self.stream())
+
+    def add_scale(self, a, b, out, scale):
+        self._call("b3d_add_scale", _ptr(a), _ptr(b), _ptr(out), c_f32(scale), c_i64(a.numel()), self.stream())
+
+    def colsum(self, x2d, rows_per_group, out):
+        rows, C = x2d.shape
+        groups = rows // rows_per_group
+        assert x2d.stride(1) == 1 and out.dtype == torch.float32 and out.stride(-1) == 1
+        out_ld = out.stride(0) if out.dim() == 2 else 0
+        self._call("b3d_colsum", _ptr(x2d), c_i64(x2d.stride(0)), c_i32(C), c_i64(rows_per_group), c_i32(groups), _ptr(out), c_i64(out_ld),
+                   self.stream())
+
+    def batch_frame_sum(self, x, out):
+        B = x.shape[0] // 2
+        self._call("b3d_batch_frame_sum", _ptr(x), _ptr(out), c_i32(B), c_i64(out.numel() // 2), self.stream())
+
+    def conv_tap_scatter(self, G, C, h, w, s, dP, accumulate):
+        _, H, W, ldp = dP.shape
+        self._call("b3d_conv_tap_scatter", _ptr(G), c_i64(G.stride(0)), c_i32(C), c_i32(h), c_i32(w), c_i32(s), c_i32(H), c_i32(W), _ptr(dP),
+                   c_i64(ldp), c_i32(int(accumulate)), self.stream())
+
+    @staticmethod
+    def _rows_ld(t):
+        """[..., rows, L] view whose leading dims are packed over a padded row stride"""
+        L, ld = t.shape[-1], t.stride(-2)
+        assert t.stride(-1) == 1 and all(t.stride(i) == t.stride(i + 1) * t.shape[i + 1] for i in range(t.dim() - 2))
+        return t.numel() // L, L, ld
+
+    def softmax(self, S, P):
+        rows, L, ld = self._rows_ld(S)
+        assert P.stride() == S.stride()
+        self._call("b3d_softmax", _ptr(S), _ptr(P), c_i64(rows), c_i32(L), c_i64(ld), self.stream())
+
+    def softmax_bwd(self, P, dP, dS):
+        rows, L, ld = self._rows_ld(P)
+        assert dP.stride() == P.stride() and dS.stride() == P.stride()
+        self._call("b3d_softmax_bwd", _ptr(P), _ptr(dP), _ptr(dS), c_i64(rows), c_i32(L), c_i64(ld), self.stream())
+
+    # ---- GroupNorm family.  x0/x1: [N, HW, C*] views with stride(-1) == 1 (x1 may be None)
+    @staticmethod
+    def _src(x):
+        if x is None:
+            return c_void(0), c_i32(0), c_i64(0)
+        assert x.dim() == 3 and x.stride(2) == 1 and x.stride(0) == x.shape[1] * x.stride(1)
+        return _ptr(x), c_i32(x.shape[2]), c_i64(x.stride(1))
+
+    def gn_stats(self, x0, x1, sums):
+        N, HW, _ = x0.shape
+        self._call("b3d_gn_stats", *self._src(x0), *self._src(x1), c_i32(N), c_i32(HW), _ptr(sums), self.stream())
+
+    def gn_apply(self, x0, x1, sums, gamma, beta, mode, out, ss=None, F=0, drop_p=0.0, seed=0):
+        N, HW, _ = x0.shape
+        self._call("b3d_gn_apply", *self._src(x0), *self._src(x1), c_i32(N), c_i32(HW), _ptr(sums), _ptr(gamma), _ptr(beta), c_i32(mode),
+                   _ptr(ss), c_i64(ss.stride(0) if ss is not None else 0), c_i32(F), c_f32(drop_p), ctypes.c_uint64(seed), _ptr(out),
+                   c_i64(out.stride(1)), self.stream())
+
+    def gn_bwd(self, x0, x1, sums, gamma, beta, mode, dy, dgamma, dbeta, ws, dx0, dx1=None, ss=None, F=0, dss=None, drop_p=0.0, seed=0,
+               add0=None, add1a=None, add1b=None):
+        N, HW, _ = x0.shape
+        ld = lambda t, i=1: c_i64(t.stride(i) if t is not None else 0)
+        self._call("b3d_gn_bwd", *self._src(x0), *self._src(x1), c_i32(N), c_i32(HW), _ptr(sums), _ptr(gamma), _ptr(beta), c_i32(mode),
+                   _ptr(dy), ld(dy), _ptr(ss), ld(ss, 0), c_i32(F), _ptr(dss), ld(dss, 0), c_f32(drop_p), ctypes.c_uint64(seed),
+                   _ptr(dgamma), _ptr(dbeta), _ptr(ws), _ptr(dx0), ld(dx0), _ptr(dx1), ld(dx1), _ptr(add0), ld(add0), _ptr(add1a),
+                   ld(add1a), _ptr(add1b), ld(add1b), self.stream())
+
+    # ---- diffusion glue
+    def q_sample(self, z, noise, logsnr, z_out, x=None, xrand=None, mask=None, x_out=None):
+        B = z.shape[0]
+        per = z.numel() // B
+        self._call("b3d_q_sample", _ptr(z), _ptr(noise), _ptr(logsnr), _ptr(x), _ptr(xrand), _ptr(_u8(mask) if mask is not None else None),
+                   _ptr(z_out), _ptr(x_out), c_i32(B), c_i64(per), self.stream())
+
+    def loss_scratch(self):
+        return torch.zeros(int(self.lib.b3d_loss_scratch_bytes()) // 4, dtype=torch.float32, device=self.device)
+
+    def loss(self, noise, pred, dpred, loss_type, scratch, loss_out, grad_scale=1.0):
+        self._call("b3d_loss", _ptr(noise), _ptr(pred), _ptr(dpred), c_i64(noise.numel()), c_i32(loss_type), c_f32(grad_scale), _ptr(scratch),
+                   _ptr(loss_out), self.stream())
+
+    def sampler_update(self, z, eps_c, eps_u, w, noise, out, logsnr, logsnr_next):
+        B = z.shape[0]
+        self._call("b3d_sampler_update", _ptr(z), _ptr(eps_c), _ptr(eps_u), _ptr(w), _ptr(noise), _ptr(out), c_f32(float(logsnr)),
+                   c_f32(float(logsnr_next)), c_i32(B), c_i64(z.numel() // B), self.stream())
+
+    def adam(self, p, g, m, v, lr, beta1, beta2, eps, step, grad_scale=1.0):
+        self._call("b3d_adam", _ptr(p), _ptr(g), _ptr(m), _ptr(v), c_i64(p.numel()), c_f32(lr), c_f32(beta1), c_f32(beta2), c_f32(eps),
+                   c_i32(step), c_f32(grad_scale), self.stream())

@@ -1,0 +1,159 @@
+/* b3d -- C ABI of the B200 (sm_100a) kernels behind the X-UNet training step and the
+ * stochastic-conditioning sampler.  Plain pointers and sizes only; no torch types.
+ *
+ * Conventions (all entry points):
+ *   - device pointers unless the name says `host`; activations are bf16 NHWC ("pixels x channels"),
+ *     images n = 2*b + frame (the reference flattens 'b f c h w -> (b f) c h w', xunet.py:494);
+ *   - `stream` is a cudaStream_t passed as void*; nothing synchronises, nothing allocates and
+ *     nothing is retained across calls; workspaces are supplied by the caller;
+ *   - return 0 on success, <0 on error (-1 bad argument, -2 CUDA error, -3 unsupported);
+ *     b3d_last_error() returns the message of the last failure on the calling thread.
+ *
+ * The reference (/root/reference) has no FFI: the interface each entry point replaces is a span
+ * of Python/ATen calls, cited per function as file:line.
+ */
+#ifndef B3D_H
+#define B3D_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* b3d_last_error(void);
+int b3d_version(void);
+/* number of kernels launched by this library since process start (bench.py's gpu_launches) */
+int64_t b3d_launch_count(void);
+
+/* ------------------------------------------------------------------------------------------
+ * Tensor-core path: one tcgen05/TMEM/TMA kernel for every GEMM-shaped op of the model.
+ * Replaces: torch.nn.Conv2d 3x3/1x1 (xunet.py:114-129,141,146,149,190,217,292-299,344,385,473),
+ * FiLM.dense / Linear (xunet.py:80,84,273-277) and the bmm's inside nn.MultiheadAttention
+ * (xunet.py:161,175), forward and backward (autograd of the same lines).
+ * ------------------------------------------------------------------------------------------ */
+typedef struct b3d_view4 {
+  const void* ptr;    /* bf16 */
+  int32_t dim[4];     /* extents: c (contiguous), x, y, n */
+  int64_t stride[3];  /* element strides of x, y, n; multiples of 8 */
+} b3d_view4;
+
+typedef struct b3d_gemm_desc {
+  /* D[rows, cols] = alpha * sum_k A[rows,k] * B[cols,k]  (+ epilogue)
+   * a_major = 0: rows = pixels (x,y,n) of the OUTPUT grid (W,H,N); K = channels of up to three
+   *              sources concatenated, times taps (3x3 taps shift the pixel by tap-pad, times
+   *              conv_stride).  a_major = 1: rows = channels of a[0]; K = its pixels.
+   * b_major = 0: cols = dim x of b, K = its channels.  b_major = 1: cols = channels of b,
+   *              K = its pixels (shifted by the tap selected by grid z when b_taps = 9). */
+  b3d_view4 a[3];
+  int32_t a_taps[3];
+  int32_t n_src;
+  b3d_view4 b;
+  int32_t a_major, b_major;
+  int32_t conv_stride, pad;
+  int32_t b_taps;
+  int32_t W, H, N;
+  int32_t m_rows, n_cols;
+  int32_t batched;       /* (y,n) are batch coordinates shared by A, B and the output */
+  int32_t b_batch_xor;   /* B is read from image n ^ b_batch_xor (cross-frame attention) */
+  int32_t out_batch_xor; /* output is written to image n ^ out_batch_xor */
+  int32_t split_k;       /* a_major = 1 only; > 1 needs out_atomic */
+  void* out;
+  int32_t out_fp32;
+  int64_t out_stride[3]; /* element strides of (row or x), y, n */
+  int64_t out_tap_stride;
+  void* out2;            /* optional bf16 copy of silu(value) */
+  const float* bias;     /* [n_cols] */
+  const float* rowvec;   /* [N images, rowvec_ld]: added per image (logsnr embedding, xunet.py:502) */
+  int64_t rowvec_ld;
+  const void* resid;     /* bf16, addressed like out: value = (acc + bias + resid) * out_scale */
+  float alpha, out_scale;
+  int32_t act;           /* 0 none, 1 silu */
+  int32_t out_atomic;    /* fp32 atomicAdd into out */
+  int32_t bn_tile;       /* 0 = auto */
+} b3d_gemm_desc;
+
+int b3d_gemm(const b3d_gemm_desc* d, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * HBM-bound kernels (elementwise / normalisation / reductions).  bf16 NHWC unless noted.
+ * ------------------------------------------------------------------------------------------ */
+
+/* K1: camera rays + NeRF positional encoding + cond mask + learned embeddings -> [2B,H,W,ld] (ch 0..143).
+ * Replaces the host round trip through visu3d and the ATen chain at xunet.py:311-336 (posenc_nerf :49-59).
+ * K,R,t: fp64 [B,3,3],[B,2,3,3],[B,2,3]; cond_mask: uint8 [B]; pos_emb fp32 [144,H,W]; first/other fp32 [144]. */
+int b3d_pose_embedding(const double* K, const double* R, const double* t, const uint8_t* cond_mask, const float* pos_emb,
+                       const float* first_emb, const float* other_emb, void* out, int out_fp32, int64_t ld, int B, int H, int W,
+                       void* stream);
+/* autograd of xunet.py:334-336 w.r.t. pos_emb / first_emb / other_emb; dP fp32 [2,H,W,ld] (already summed over b) */
+int b3d_pose_embedding_bwd(const float* dP, int64_t ld, int H, int W, float* dpos_emb, float* dfirst, float* dother, void* stream);
+/* posenc_ddpm(clip(logsnr)), xunet.py:32-46,305-307: fp32 [n] -> bf16 [n, emb_ch] */
+int b3d_ddpm_embedding(const float* logsnr, void* out, int n, int emb_ch, void* stream);
+/* torch.stack([x,z],1) + rearrange, xunet.py:493-494: fp32 NCHW x2 -> bf16 [2B,H,W,8]; and its adjoint */
+int b3d_pack_input(const float* x, const float* z, void* out, int B, int HW, void* stream);
+int b3d_unpack_input_grad(const void* g, float* dx, float* dz, int B, int HW, void* stream);
+/* `[:, 1]` of the last conv, xunet.py:536: bf16 [2B,H,W,ld] -> fp32 [B,3,H,W]; and its adjoint */
+int b3d_unpack_output(const void* y, int64_t ld, float* eps, int B, int HW, void* stream);
+int b3d_pack_output_grad(const float* deps, void* dy, int64_t ld, int B, int HW, void* stream);
+/* parameter layout: fp32 PyTorch [Co,Ci,kh,kw] (state_dict schema) <-> bf16 K-major GEMM operands.
+ * mode 0 forward [Co, k_off + tap*Cpad + ci], mode 1 dgrad [Ci, tap'*Cpad + co] (flipped taps), mode 2 [(tap,ci), Co] */
+int b3d_pack_weight(const float* w, int Co, int Ci, int taps, int mode, int ci0, int cn, int Cpad, int64_t k_off, void* out, int64_t out_ld,
+                    void* stream);
+int b3d_unpack_wgrad(const float* g, int64_t g_ld, int64_t k_off, int Cpad, int Co, int Ci, int taps, int ci0, int cn, float* dw,
+                     int accumulate, void* stream);
+int b3d_cast_bf16(const float* in, void* out, int64_t n, void* stream);
+/* avgpool_downsample / nearest_neighbor_upsample, xunet.py:17-28 (scale folds the adjoint's 1/4) */
+int b3d_avgpool2(const void* in, void* out, int N, int H, int W, int C, float scale, void* stream);
+int b3d_upsample2(const void* in, void* out, int N, int Ho, int Wo, int C, float scale, void* stream);
+/* dx = dy * silu'(x)  (autograd of F.silu, xunet.py:84) ; out = scale*(a+b) */
+int b3d_silu_bwd(const void* dy, const void* x, void* dx, int64_t n, void* stream);
+int b3d_add_scale(const void* a, const void* b, void* out, float scale, int64_t n, void* stream);
+/* out[g,c] += sum of rows of group g (bias gradients; d logsnr_emb per image, xunet.py:502); out fp32, pre-zeroed */
+int b3d_colsum(const void* in, int64_t ld, int C, int64_t rows_per_group, int groups, float* out, int64_t out_ld, void* stream);
+/* out[f,...] = sum_b in[b,f,...]  (gradient of the batch-shared learned embeddings, xunet.py:334-336) */
+int b3d_batch_frame_sum(const void* in, void* out, int B, int64_t per_frame_elems, void* stream);
+/* adjoint of the strided conditioning convs w.r.t. their input from per-tap GEMM products, xunet.py:340-349 */
+int b3d_conv_tap_scatter(const float* G, int64_t ldg, int C, int h, int w, int s, int H, int W, float* dP, int64_t ldp, int accumulate,
+                         void* stream);
+/* softmax inside nn.MultiheadAttention (xunet.py:161,175) over rows of length L (row stride ld), and its adjoint */
+int b3d_softmax(const void* S, void* P, int64_t rows, int L, int64_t ld, void* stream);
+int b3d_softmax_bwd(const void* P, const void* dP, void* dS, int64_t rows, int L, int64_t ld, void* stream);
+
+/* GroupNorm(32, C, eps 1e-5) per image (xunet.py:61-71) on the channel-concat of up to two tensors.
+ * b3d_gn_stats accumulates raw (sum, sumsq) into ws_sums fp32 [N,32,2] (caller zeroes it).
+ * b3d_gn_apply: mode 0 plain (AttnBlock :198), 1 +SiLU (:140,:535), 2 +FiLM(+dropout) (:87,:143-145) with
+ *   scale = ss[row, c], shift = ss[row, F + c].
+ * b3d_gn_bwd: autograd of the same lines; writes d(scale,shift) to dss, accumulates dgamma/dbeta (fp32),
+ *   uses ws_s12 fp32 [N,32,2] (caller zeroes it), writes dx0/dx1 (+ add0 + add1a/add1b when given). */
+int b3d_gn_stats(const void* x0, int C0, int64_t ld0, const void* x1, int C1, int64_t ld1, int N, int HW, float* ws_sums, void* stream);
+int b3d_gn_apply(const void* x0, int C0, int64_t ld0, const void* x1, int C1, int64_t ld1, int N, int HW, const float* sums,
+                 const float* gamma, const float* beta, int mode, const void* ss, int64_t ld_ss, int F, float drop_p, uint64_t seed,
+                 void* out, int64_t ld_out, void* stream);
+int b3d_gn_bwd(const void* x0, int C0, int64_t ld0, const void* x1, int C1, int64_t ld1, int N, int HW, const float* sums,
+               const float* gamma, const float* beta, int mode, const void* dy, int64_t ld_dy, const void* ss, int64_t ld_ss, int F,
+               void* dss, int64_t ld_dss, float drop_p, uint64_t seed, float* dgamma, float* dbeta, float* ws_s12, void* dx0,
+               int64_t ld_dx0, void* dx1, int64_t ld_dx1, const void* add0, int64_t ld_add0, const void* add1a, int64_t ld_add1a,
+               const void* add1b, int64_t ld_add1b, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Diffusion glue (fp32 NCHW, as the reference holds these tensors)
+ * ------------------------------------------------------------------------------------------ */
+/* q_sample + conditioning-frame replacement: train.py:50-60,95-96 / lightning/diff3d.py:66-69,168-180 */
+int b3d_q_sample(const float* z, const float* noise, const float* logsnr, const float* x, const float* xrand, const uint8_t* mask,
+                 float* z_out, float* x_out, int B, int64_t per_sample, void* stream);
+/* F.mse_loss / l1_loss / smooth_l1_loss (mean) + d loss/d pred: train.py:102-112, lightning/diff3d.py:87-94.
+ * loss_type 0 l2, 1 l1, 2 huber.  `scratch`: b3d_loss_scratch_bytes() bytes of device memory whose last word
+ * (the block ticket) is zero on entry; the kernel leaves it zero.  Deterministic two-stage reduction. */
+int b3d_loss_scratch_bytes(void);
+int b3d_loss(const float* noise, const float* pred, float* dpred, int64_t n, int loss_type, float grad_scale, void* scratch,
+             float* loss_out, void* stream);
+/* p_mean_variance + p_sample arithmetic given both UNet outputs: sampling.py:79-127 (noise skipped iff logsnr_next == 0) */
+int b3d_sampler_update(const float* z, const float* eps_c, const float* eps_u, const float* w, const float* noise, float* out,
+                       float logsnr, float logsnr_next, int B, int64_t per_sample, void* stream);
+/* torch.optim.Adam(lr, betas) step over a flat fp32 arena: train.py:235,278 / lightning/diff3d.py:106 */
+int b3d_adam(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2, float eps, int step,
+             float grad_scale, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,180 @@
+"""Case table for the HBM-bound kernels: each case returns (callable(ops) -> list of output tensors).
+The same callable runs on CudaOps and on EmuOps; outputs are compared by the tests."""
+import math
+
+import torch
+
+from distributed_3d_diffusion_pytorch_b200 import synthetic
+
+
+def _mk(ops, t, dtype=None):
+    return t.to(device=ops.device, dtype=dtype or ops.act_dtype).contiguous()
+
+
+def _r(shape, g, scale=1.0):
+    return (torch.randn(shape, generator=g) * scale).to(torch.bfloat16).float()
+
+
+def pose_case(B, H, W, fp32, seed=0):
+    def run(ops):
+        g = torch.Generator().manual_seed(seed)
+        _, R, T, K = synthetic.make_views(B, H, seed=seed)
+        mask = (torch.arange(B) % 3 != 1)
+        pos = torch.randn(144, H, W, generator=g) / 12
+        fe, oe = torch.randn(144, generator=g) / 12, torch.randn(144, generator=g) / 12
+        dev = ops.device
+        out = ops.zeros((2 * B, H, W, 144), torch.float32 if fp32 else None)
+        ops.pose_embedding(K.to(dev), R.to(dev), T.to(dev), mask.to(dev), pos.to(dev), fe.to(dev), oe.to(dev), out)
+        return [out]
+    return run
+
+
+def gn_case(N, HW, C0, C1, mode, drop_p=0.0, seed=0):
+    def run(ops):
+        g = torch.Generator().manual_seed(seed)
+        C = C0 + C1
+        x0 = _mk(ops, _r((N, HW, C0), g) + 0.3)
+        x1 = _mk(ops, _r((N, HW, C1), g) * 2 - 0.5) if C1 else None
+        gamma = _mk(ops, 1 + 0.1 * torch.randn(C, generator=g), torch.float32)
+        beta = _mk(ops, 0.1 * torch.randn(C, generator=g), torch.float32)
+        sums = ops.zeros((N, 32, 2), torch.float32)
+        ops.gn_stats(x0, x1, sums)
+        F = C
+        ssw = ops.zeros((N * HW, 2 * F + 64))
+        ssw[:, 32:32 + 2 * F] = _mk(ops, _r((N * HW, 2 * F), g, 0.5))
+        ss = ssw[:, 32:32 + 2 * F] if mode == 2 else None
+        out = ops.zeros((N, HW, C))
+        ops.gn_apply(x0, x1, sums, gamma, beta, mode, out, ss=ss, F=F, drop_p=drop_p, seed=77)
+        dy = _mk(ops, _r((N, HW, C), g))
+        dgamma, dbeta = ops.zeros((C,), torch.float32), ops.zeros((C,), torch.float32)
+        ws = ops.zeros((N, 32, 2), torch.float32)
+        dx0 = ops.zeros((N, HW, C0))
+        dx1 = ops.zeros((N, HW, C1)) if C1 else None
+        dss = ops.zeros((N * HW, 2 * F)) if mode == 2 else None
+        add0 = _mk(ops, _r((N, HW, C), g))
+        add1a = _mk(ops, _r((N, HW, C0), g))
+        ops.gn_bwd(x0, x1, sums, gamma, beta, mode, dy, dgamma, dbeta, ws, dx0, dx1, ss=ss, F=F, dss=dss, drop_p=drop_p, seed=77,
+                   add0=add0, add1a=add1a)
+        outs = [sums, out, dgamma, dbeta, ws, dx0]
+        if C1:
+            outs.append(dx1)
+        if mode == 2:
+            outs.append(dss)
+        return outs
+    return run
+
+
+def misc_case(seed=0):
+    def run(ops):
+        g = torch.Generator().manual_seed(seed)
+        outs = []
+        dev = ops.device
+        # ddpm embedding
+        ls = torch.tensor([-25.0, -3.3, 0.0, 0.7, 12.0, 30.0])
+        e = ops.zeros((6, 1024))
+        ops.ddpm_embedding(ls.to(dev), e)
+        outs.append(e)
+        # pack / unpack
+        B, H, W = 3, 8, 8
+        x, z = torch.randn(B, 3, H, W, generator=g), torch.randn(B, 3, H, W, generator=g)
+        pk = ops.zeros((2 * B, H, W, 8))
+        ops.pack_input(x.to(dev), z.to(dev), pk)
+        outs.append(pk)
+        dx, dz = ops.zeros((B, 3, H, W), torch.float32), ops.zeros((B, 3, H, W), torch.float32)
+        ops.unpack_input_grad(pk, dx, dz)
+        outs += [dx, dz]
+        y = _mk(ops, _r((2 * B, H, W, 16), g))
+        eps = ops.zeros((B, 3, H, W), torch.float32)
+        ops.unpack_output(y, eps)
+        outs.append(eps)
+        dy = ops.zeros((2 * B, H, W, 16))
+        ops.pack_output_grad(eps, dy)
+        outs.append(dy)
+        # weight packing
+        w = torch.randn(40, 24, 3, 3, generator=g)
+        o0 = ops.zeros((40, 64 + 9 * 64))
+        ops.pack_weight(w.to(dev), 0, o0, ci0=8, cn=16, Cpad=64, k_off=64)
+        o1 = ops.zeros((24, 9 * 64))
+        ops.pack_weight(w.to(dev), 1, o1, Cpad=64)
+        o2 = ops.zeros((9 * 24, 40))
+        ops.pack_weight(w.to(dev), 2, o2)
+        outs += [o0, o1, o2]
+        gpk = _mk(ops, torch.randn(40, 64 + 9 * 64, generator=g), torch.float32)
+        dw = ops.zeros((40, 24, 3, 3), torch.float32)
+        ops.unpack_wgrad(gpk, 64, 64, dw, ci0=8, cn=16)
+        ops.unpack_wgrad(gpk, 64, 64, dw, ci0=8, cn=16, accumulate=True)
+        outs.append(dw)
+        # resampling
+        t = _mk(ops, _r((2, 8, 8, 32), g))
+        p = ops.zeros((2, 4, 4, 32)); ops.avgpool2(t, p); outs.append(p)
+        u = ops.zeros((2, 16, 16, 32)); ops.upsample2(t, u, 0.5); outs.append(u)
+        # elementwise
+        a, b = _mk(ops, _r((64, 128), g)), _mk(ops, _r((64, 128), g))
+        sb = ops.zeros((64, 128)); ops.silu_bwd(a, b, sb); outs.append(sb)
+        ad = ops.zeros((64, 128)); ops.add_scale(a, b, ad, 0.7071); outs.append(ad)
+        ad2 = ops.zeros((64, 128)); ops.add_scale(a, None, ad2, 0.5); outs.append(ad2)
+        cs = ops.zeros((4, 96), torch.float32)
+        big = _mk(ops, _r((4 * 300, 128), g))
+        ops.colsum(big[:, 16:112], 300, cs); outs.append(cs)
+        cs1 = ops.zeros((96,), torch.float32)
+        ops.colsum(big[:, 16:112], 1200, cs1); outs.append(cs1)
+        bf = _mk(ops, _r((10, 4, 4, 64), g))
+        bo = ops.zeros((2, 4, 4, 64)); ops.batch_frame_sum(bf, bo); outs.append(bo)
+        for s_, h_ in ((1, 8), (2, 4), (4, 2), (8, 1)):
+            Gm = _mk(ops, torch.randn(2 * h_ * h_, 9 * 144 + 16, generator=g), torch.float32)
+            dP = ops.zeros((2, 8, 8, 144), torch.float32)
+            ops.conv_tap_scatter(Gm, 144, h_, h_, s_, dP, False)
+            ops.conv_tap_scatter(Gm, 144, h_, h_, s_, dP, True)
+            outs.append(dP)
+        dPb = _mk(ops, torch.randn(2, 8, 8, 144, generator=g), torch.float32)
+        dpos, dfe, doe = ops.zeros((144, 8, 8), torch.float32), ops.zeros((144,), torch.float32), ops.zeros((144,), torch.float32)
+        ops.pose_embedding_bwd(dPb, dpos, dfe, doe)
+        outs += [dpos, dfe, doe]
+        # softmax
+        S = ops.zeros((2, 4, 36, 40))
+        S[..., :36] = _mk(ops, _r((2, 4, 36, 36), g, 2.0))
+        P = ops.zeros((2, 4, 36, 40)); ops.softmax(S[..., :36], P[..., :36]); outs.append(P)
+        dP2 = ops.zeros((2, 4, 36, 40)); dP2[..., :36] = _mk(ops, _r((2, 4, 36, 36), g))
+        dS = ops.zeros((2, 4, 36, 40)); ops.softmax_bwd(P[..., :36], dP2[..., :36], dS[..., :36]); outs.append(dS)
+        # diffusion glue
+        Bq = 5
+        zz, nz, xx, xr = [torch.randn(Bq, 3, 8, 8, generator=g).to(dev) for _ in range(4)]
+        lsn = torch.tensor([-18.0, -2.0, 0.1, 3.0, 19.5]).to(dev)
+        mk = torch.tensor([1, 0, 1, 1, 0], dtype=torch.uint8).to(dev)
+        zo, xo = ops.zeros((Bq, 3, 8, 8), torch.float32), ops.zeros((Bq, 3, 8, 8), torch.float32)
+        ops.q_sample(zz, nz, lsn, zo, xx, xr, mk, xo)
+        outs += [zo, xo]
+        scr = ops.loss_scratch()
+        for lt in (0, 1, 2):
+            lo = ops.zeros((1,), torch.float32)
+            dpd = ops.zeros((Bq, 3, 8, 8), torch.float32)
+            ops.loss(nz, zz * 1.5, dpd, lt, scr, lo)
+            ops.loss(nz, zz * 1.5, dpd, lt, scr, lo)      # second call: ticket must have been reset
+            outs += [lo, dpd]
+        wv = torch.arange(Bq, dtype=torch.float32).to(dev)
+        for l0, l1 in ((-20.0, -19.5), (0.3, 0.0), (0.0, 0.4), (19.0, 20.0)):
+            so = ops.zeros((Bq, 3, 8, 8), torch.float32)
+            ops.sampler_update(zz, nz, xx, wv, xr, so, l0, l1)
+            outs.append(so)
+        pa, ga = torch.randn(1000, generator=g).to(dev), torch.randn(1000, generator=g).to(dev)
+        ma, va = ops.zeros((1000,), torch.float32), ops.zeros((1000,), torch.float32)
+        for st in (1, 2, 3):
+            ops.adam(pa, ga, ma, va, 1e-2, 0.9, 0.99, 1e-8, st)
+        outs += [pa, ma, va]
+        return outs
+    return run
+
+
+def all_cases():
+    c = {
+        "pose_fp32_64": pose_case(3, 64, 64, True),
+        "pose_fp32_24": pose_case(2, 24, 24, True, seed=3),
+        "pose_bf16_16": pose_case(2, 16, 16, False, seed=4),
+        "misc": misc_case(),
+    }
+    for i, (N, HW, C0, C1, mode, dp) in enumerate([
+        (2, 256, 128, 0, 1, 0.0), (4, 64, 512, 256, 1, 0.0), (2, 4096, 128, 0, 2, 0.0), (2, 1024, 256, 128, 0, 0.0),
+        (2, 16, 32, 0, 1, 0.0), (2, 36, 64, 32, 2, 0.0), (3, 64, 256, 0, 2, 0.1), (2, 64, 1024, 1024, 1, 0.0),
+    ]):
+        c[f"gn_{N}x{HW}x{C0}+{C1}_m{mode}_p{dp}"] = gn_case(N, HW, C0, C1, mode, dp, seed=i)
+    return c

@@ -69,16 +69,16 @@ def test_param_schema_counts():
 @pytest.mark.skipif(not ref_import.available(), reason="reference tree only exists in the build container")
 def test_oracle_vs_live_reference_random_case():
     rx, _ = ref_import.load()
-    kw = dict(H=8, W=8, ch=32)
+    kw = dict(H=16, W=16, ch=32)
     cfg = xr.Cfg(**kw)
     sd = xr.init_state_dict(cfg, seed=5)
     m = rx.XUNet(**kw).eval()
     m.load_state_dict(sd)
     from distributed_3d_diffusion_pytorch_b200 import synthetic
-    img, R, T, K = synthetic.make_views(2, 8, seed=3)
+    img, R, T, K = synthetic.make_views(2, 16, seed=3)
     logsnr = dr.logsnr_schedule_cosine(torch.tensor([0.3, 0.8]))
     batch = dr.make_batch(img[:, 0], logsnr, img[:, 1], R, T, K)
     cm = torch.tensor([False, True])
     a = m(batch, cond_mask=cm)
     b = xr.xunet_forward(sd, cfg, batch, cm)
-    assert (a - b).abs().max() < 2e-5
+    assert (a - b).abs().max() < 1e-4

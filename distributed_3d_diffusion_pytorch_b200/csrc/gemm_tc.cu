@@ -24,6 +24,7 @@ constexpr int BK = 64;  // bf16 elements = one 128-byte swizzle row
 constexpr int kThreads = 192;
 constexpr int kMaxSeg = 27;
 constexpr uint32_t kABytes = BM * BK * 2;  // 16 KB in both majors
+constexpr int kMaxDynSmem = 227 * 1024 - 1024;  // 227 KB per CTA minus the static barriers
 
 struct Seg {
   int32_t src, dx, dy, ncb, bk0;
@@ -507,7 +508,7 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
   p.b_bytes = d->b_major ? (uint32_t)p.b_chunks * 8192u : (uint32_t)((BN * 128 + 1023) / 1024 * 1024);
   p.b_tx = d->b_major ? (uint32_t)p.b_chunks * 8192u : (uint32_t)BN * 128u;
   p.stage_bytes = kABytes + p.b_bytes;
-  p.num_stages = (int)((227 * 1024 - 2048) / p.stage_bytes);
+  p.num_stages = (int)((kMaxDynSmem - 1024) / p.stage_bytes);
   if (p.num_stages > 8) p.num_stages = 8;
   p.acc_stride = (BN + 31) / 32 * 32;
   p.tmem_cols = pow2_ceil(2 * p.acc_stride);
@@ -595,7 +596,7 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
   const size_t smem = (size_t)p.num_stages * p.stage_bytes + 1024;
   static bool attr_set = false;
   if (!attr_set) {
-    B3D_CUDA(cudaFuncSetAttribute(b3d_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    B3D_CUDA(cudaFuncSetAttribute(b3d_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem));
     attr_set = true;
   }
   int grid = p.tiles_total < b3d_num_sms() ? p.tiles_total : b3d_num_sms();

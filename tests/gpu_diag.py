@@ -66,7 +66,8 @@ def main():
             msg = " ".join(f"[{r[0]:.2e},{r[1]:.2e}]" for r in res)
         except Exception as e:  # noqa: BLE001
             ok, msg = False, "EXC " + repr(e)[:300]
-            traceback.print_exc()
+            if os.environ.get('B3D_DIAG_TRACE'):
+                traceback.print_exc()
             if "CUDA error" in repr(e) or "illegal" in repr(e) or "launch failure" in repr(e):
                 print(f"FAIL {name}: {msg}", flush=True)
                 print("sticky CUDA error: stopping", flush=True)

@@ -33,8 +33,8 @@ def gn_case(N, HW, C0, C1, mode, drop_p=0.0, seed=0):
     def run(ops):
         g = torch.Generator().manual_seed(seed)
         C = C0 + C1
-        x0 = _mk(ops, _r((N, HW, C0), g) + 0.3)
-        x1 = _mk(ops, _r((N, HW, C1), g) * 2 - 0.5) if C1 else None
+        x0 = _mk(ops, (_r((N, HW, C0), g) + 0.3).to(torch.bfloat16).float())
+        x1 = _mk(ops, (_r((N, HW, C1), g) * 2 - 0.5).to(torch.bfloat16).float()) if C1 else None
         gamma = _mk(ops, 1 + 0.1 * torch.randn(C, generator=g), torch.float32)
         beta = _mk(ops, 0.1 * torch.randn(C, generator=g), torch.float32)
         sums = ops.zeros((N, 32, 2), torch.float32)
@@ -81,7 +81,7 @@ def misc_case(seed=0):
         ops.pack_input(x.to(dev), z.to(dev), pk)
         outs.append(pk)
         dx, dz = ops.zeros((B, 3, H, W), torch.float32), ops.zeros((B, 3, H, W), torch.float32)
-        ops.unpack_input_grad(pk, dx, dz)
+        ops.unpack_input_grad(_mk(ops, _r((2 * B, H, W, 8), g)), dx, dz)
         outs += [dx, dz]
         y = _mk(ops, _r((2 * B, H, W, 16), g))
         eps = ops.zeros((B, 3, H, W), torch.float32)

@@ -180,7 +180,7 @@ __global__ void pack_output_grad_kernel(const float* __restrict__ deps, bf16* __
 // weight packers: fp32 PyTorch layout -> bf16 K-major GEMM operands, and packed fp32 grads back
 //   w [Co, Ci, taps]   (taps = kh*kw row-major)
 //   mode 0 (forward)  : out[co, k_off + tap*Cpad + (ci-ci0)] for ci in [ci0, ci0+cn)         ld = out_ld
-//   mode 1 (dgrad)    : out[ci, tap'*Copad + co], tap' = taps-1-tap (spatial flip)
+//   mode 1 (dgrad)    : out[ci, k_off + tap'*Copad + co], tap' = taps-1-tap (spatial flip)
 //   mode 2 (tap rows) : out[tap*Ci + ci, co]
 // unpack (mode 0 inverse, fp32 -> fp32): dw[co,ci,tap] = g[co, k_off + tap*Cpad + (ci-ci0)]
 // ---------------------------------------------------------------------------------------------
@@ -196,7 +196,7 @@ __global__ void pack_weight_kernel(const float* __restrict__ w, int Co, int Ci, 
     } else if (mode == 1) {
       const int co = (int)(i % Cpad), tp = (int)((i / Cpad) % taps), ci = (int)(i / ((long long)Cpad * taps));
       if (co < Co) v = w[((long long)co * Ci + ci) * taps + (taps - 1 - tp)];
-      o = (long long)ci * out_ld + (long long)tp * Cpad + co;
+      o = (long long)ci * out_ld + k_off + (long long)tp * Cpad + co;
     } else {
       const int co = (int)(i % Co), ci = (int)((i / Co) % Ci), tap = (int)(i / ((long long)Co * Ci));
       v = w[((long long)co * Ci + ci) * taps + tap];

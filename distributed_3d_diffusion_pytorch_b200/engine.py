@@ -1,0 +1,644 @@
+"""Execution engine of the X-UNet hot path: the forward and the hand-written backward of
+`XUNet.forward` (reference xunet.py:477-536) as explicit sequences of b3d kernel launches.
+
+* activations: bf16 NHWC, images n = 2*b + frame; every buffer is allocated once per (batch size) and
+  reused, so a step allocates nothing and can be captured in a CUDA graph;
+* parameters arrive as fp32 tensors under the reference's state_dict names; they are repacked to
+  bf16 K-major GEMM operands at the start of each forward (they change every optimizer step);
+* gradients leave as fp32 tensors under the same names (PyTorch layouts);
+* FiLM (xunet.py:74-87) is restructured: the per-pixel Linear(1024 -> 2F) of ALL ResnetBlocks of a
+  resolution level is ONE GEMM against the level's silu(emb) (forward), and ONE data-gradient GEMM
+  (backward); GroupNorm/FiLM/dropout/SiLU are applied by the fused GN kernels.
+
+`ops` is the kernel backend (ops.CudaOps); tests substitute a torch statement of the same ops to
+check this orchestration on CPU."""
+import math
+
+import torch
+
+from . import gemm as G
+
+RSQRT2 = 1.0 / math.sqrt(2.0)
+
+
+class Cfg:
+    """XUNet hyper-parameters (class attributes of the reference, xunet.py:356-366)."""
+    DEFAULTS = dict(H=128, W=128, ch=256, ch_mult=(1, 2, 2, 4), emb_ch=1024, num_res_blocks=3, attn_resolutions=(2, 3, 4),
+                    attn_heads=4, dropout=0.1, use_pos_emb=True, use_ref_pose_emb=True)
+
+    def __init__(self, **kw):
+        for k, v in self.DEFAULTS.items():
+            setattr(self, k, kw.get(k, v))
+        self.num_resolutions = len(self.ch_mult)
+        self.dim_in = [self.ch] + [self.ch * m for m in self.ch_mult[:-1]]
+        self.dim_out = [self.ch * m for m in self.ch_mult]
+
+
+class ResSpec:
+    def __init__(self, name, lvl, cin, f, resample, cat):
+        self.name, self.lvl, self.cin, self.f, self.resample, self.cat = name, lvl, cin, f, resample, cat
+        self.film_off = 0
+
+
+class AttnSpec:
+    def __init__(self, name, lvl, c, cross):
+        self.name, self.lvl, self.c, self.cross = name, lvl, c, cross
+
+
+def build_plan(cfg):
+    """Execution order of xunet.py:497-531 as a list of (kind, spec).  kinds: 'res', 'attn', 'push', 'pop'."""
+    plan, nres, nb = [], cfg.num_resolutions, cfg.num_res_blocks
+    film_cols = [0] * nres
+
+    def res(name, lvl, cin, f, resample=None, cat=False):
+        s = ResSpec(name, lvl, cin, f, resample, cat)
+        s.film_off = film_cols[lvl]
+        film_cols[lvl] += 2 * f
+        plan.append(("res", s))
+
+    def xblock(pfx, lvl, cin, f, use_attn, cat=False):
+        res(pfx + ".resnetblock", lvl, cin, f, None, cat)
+        if use_attn:
+            plan.append(("attn", AttnSpec(pfx + ".attnblock_self", lvl, f, False)))
+            plan.append(("attn", AttnSpec(pfx + ".attnblock_cross", lvl, f, True)))
+
+    plan.append(("push", None))
+    for lvl in range(nres):
+        for i in range(nb):
+            xblock(f"xunetblocks.{lvl}.{i}", lvl, cfg.dim_in[lvl] if i == 0 else cfg.dim_out[lvl], cfg.dim_out[lvl], lvl in cfg.attn_resolutions)
+            plan.append(("push", None))
+        if lvl != nres - 1:
+            res(f"xunetblocks.{lvl}.{nb}", lvl, cfg.dim_out[lvl], cfg.dim_out[lvl], "down")
+            plan.append(("push", None))
+    xblock("middle", nres - 1, cfg.dim_out[-1], cfg.dim_out[-1], nres in cfg.attn_resolutions)
+    for lvl in reversed(range(nres)):
+        for i in range(nb + 1):
+            if i == 0:
+                ph = cfg.dim_out[lvl + 1] if lvl + 1 < nres else cfg.dim_out[lvl]
+                pe = cfg.dim_out[lvl]
+            elif i == nb:
+                ph, pe = cfg.dim_out[lvl], cfg.dim_in[lvl]
+            else:
+                ph, pe = cfg.dim_out[lvl], cfg.dim_out[lvl]
+            plan.append(("pop", None))
+            xblock(f"upsample.{lvl}.{i}", lvl, ph + pe, cfg.dim_out[lvl], lvl in cfg.attn_resolutions, cat=True)
+        if lvl != 0:
+            res(f"upsample.{lvl}.{nb + 1}", lvl, cfg.dim_out[lvl], cfg.dim_out[lvl], "up")
+    return plan, film_cols
+
+
+class Act:
+    """an activation tensor [N, h, w, C] with its (lazily created) gradient buffer"""
+
+    def __init__(self, t, key):
+        self.t, self.key, self.has_grad = t, key, False
+
+
+class Engine:
+    def __init__(self, cfg, ops, B):
+        self.cfg, self.ops, self.B, self.N = cfg, ops, B, 2 * B
+        self.plan, self.film_cols = build_plan(cfg)
+        self._bufs = {}
+        self._zero = {"fwd": [None, 0, {}], "bwd": [None, 0, {}]}
+        self._zero_cap = {"fwd": 1 << 22, "bwd": 1 << 22}
+        self.saved = None
+        for lvl in range(cfg.num_resolutions):
+            assert cfg.H % (2 ** lvl) == 0 and cfg.W % (2 ** lvl) == 0
+
+    # ------------------------------------------------------------------ buffers
+    def buf(self, key, shape, dtype=None):
+        t = self._bufs.get(key)
+        if t is None or tuple(t.shape) != tuple(shape):
+            t = self.ops.empty(tuple(shape), dtype)
+            self._bufs[key] = t
+        return t
+
+    def tmp(self, name, shape, dtype=None):
+        """scratch reused by every block with the same shape (stream order makes the reuse safe)"""
+        return self.buf(f"tmp.{name}:{tuple(shape)}", shape, dtype)
+
+    def zbuf(self, phase, key, shape):
+        """fp32 scratch that must be zero at the start of the phase: carved from one arena, one memset per phase"""
+        arena, used, table = self._zero[phase]
+        if arena is None:
+            arena = self.ops.zeros((self._zero_cap[phase],), torch.float32)
+            self._zero[phase][0] = arena
+        if key not in table:
+            n = int(math.prod(shape))
+            n_al = (n + 63) // 64 * 64
+            assert used + n_al <= self._zero_cap[phase], "zero arena exhausted"
+            table[key] = (used, n)
+            self._zero[phase][1] = used + n_al
+        off, n = table[key]
+        return arena[off:off + n].view(shape)
+
+    def _zero_phase(self, phase):
+        arena, used, _ = self._zero[phase]
+        if arena is not None and used:
+            arena[:used].zero_()
+
+    def lvl_hw(self, lvl):
+        return self.cfg.H >> lvl, self.cfg.W >> lvl
+
+    # ------------------------------------------------------------------ weights
+    def _pack_weights(self, P, training):
+        """fp32 PyTorch-layout parameters -> bf16 K-major operands (per forward: parameters change every step)."""
+        ops, cfg, W = self.ops, self.cfg, {}
+
+        def conv3(name, w, Co_alloc=None):
+            Co, Ci = w.shape[0], w.shape[1]
+            cp = G.ceil64(Ci)
+            f = self.buf("w.f." + name, (Co_alloc or Co, 9 * cp))
+            if Co_alloc:
+                f.zero_()
+            ops.pack_weight(w, 0, f, Cpad=cp)
+            W[name] = f
+            if training:
+                cop = G.ceil64(Co)
+                t = self.buf("w.t." + name, (Ci, 9 * cop))
+                ops.pack_weight(w, 1, t, Cpad=cop)
+                W[name + ".T"] = t
+
+        def lin(name, w, srcs=None):
+            Co, Ci = w.shape[0], w.shape[1]
+            srcs = srcs or [Ci]
+            f = self.buf("w.f." + name, (Co, sum(G.ceil64(c) for c in srcs)))
+            ci0 = koff = 0
+            for c in srcs:
+                ops.pack_weight(w, 0, f, ci0=ci0, cn=c, Cpad=G.ceil64(c), k_off=koff)
+                ci0 += c
+                koff += G.ceil64(c)
+            W[name] = f
+            if training:
+                t = self.buf("w.t." + name, (Ci, G.ceil64(Co)))
+                ops.pack_weight(w, 1, t, Cpad=G.ceil64(Co))
+                W[name + ".T"] = t
+
+        cp = "conditioningprocessor."
+        lin(cp + "logsnr_emb_emb.0.weight", P[cp + "logsnr_emb_emb.0.weight"])
+        lin(cp + "logsnr_emb_emb.2.weight", P[cp + "logsnr_emb_emb.2.weight"])
+        for l in range(cfg.num_resolutions):
+            w = P[cp + f"convs.{l}.weight"]
+            f = self.buf(f"w.f.cc{l}", (cfg.emb_ch, 9 * 192))
+            ops.pack_weight(w, 0, f, Cpad=192)
+            W[cp + f"convs.{l}.weight"] = f
+            if training:
+                t = self.buf(f"w.r.cc{l}", (9 * 144, cfg.emb_ch))
+                ops.pack_weight(w, 2, t)
+                W[cp + f"convs.{l}.weight.R"] = t
+        # stem: the packed input tensor has 8 channels (3 real)
+        f = self.buf("w.f.stem", (cfg.ch, 9 * 64))
+        ops.pack_weight(P["conv.weight"], 0, f, Cpad=64)
+        W["conv.weight"] = f
+        conv3("lastconv.weight", P["lastconv.weight"], Co_alloc=16)
+        # FiLM: one [sum 2F, 1024] operand per level (+ its transpose for the data gradient)
+        for l in range(cfg.num_resolutions):
+            W[f"film{l}"] = self.buf(f"w.f.film{l}", (self.film_cols[l], 1024))
+            if f"b.film{l}" not in self._bufs:
+                self._bufs[f"b.film{l}"] = self.ops.zeros((self.film_cols[l],), torch.float32)
+            if training:
+                W[f"film{l}.T"] = self.buf(f"w.t.film{l}", (1024, self.film_cols[l]))
+        for kind, s in self.plan:
+            if kind == "res":
+                n = s.name
+                conv3(n + ".conv1.weight", P[n + ".conv1.weight"])
+                conv3(n + ".conv2.weight", P[n + ".conv2.weight"])
+                if s.cin != s.f:
+                    lin(n + ".dense.weight", P[n + ".dense.weight"], s.srcs_c if s.cat else None)
+                fw = P[n + ".film.dense.weight"]
+                ops.pack_weight(fw, 0, W[f"film{s.lvl}"][s.film_off:s.film_off + 2 * s.f], Cpad=1024)
+                self._bufs[f"b.film{s.lvl}"][s.film_off:s.film_off + 2 * s.f].copy_(P[n + ".film.dense.bias"])
+                if training:
+                    ops.pack_weight(fw, 1, W[f"film{s.lvl}.T"], Cpad=2 * s.f, k_off=s.film_off)
+            elif kind == "attn":
+                a = s.name + ".attn_layer.attn"
+                lin(a + ".in_proj_weight", P[a + ".in_proj_weight"])
+                lin(a + ".out_proj.weight", P[a + ".out_proj.weight"])
+                lin(s.name + ".linear.weight", P[s.name + ".linear.weight"])
+        return W
+
+    # ------------------------------------------------------------------ forward
+    def forward(self, P, x, z, logsnr, R, t, K, cond_mask, training=False, need_bwd=None, seed=0):
+        """P: dict name -> fp32 param.  x,z: fp32 [B,3,H,W]; logsnr [B,2]; R [B,2,3,3], t [B,2,3], K [B,3,3] fp64;
+        cond_mask [B].  Returns eps_hat fp32 [B,3,H,W] (frame 1).  Keeps what backward needs in self.saved."""
+        ops, cfg, B, N = self.ops, self.cfg, self.B, self.N
+        H, Wd = cfg.H, cfg.W
+        assert x.shape == (B, 3, H, Wd), (x.shape, (B, 3, H, Wd))
+        self._assign_cat_sources()
+        if self._zero["bwd"][0] is None:   # packed fp32 weight-gradient staging lives in the bwd arena
+            self._zero_cap["bwd"] = int(sum(p.numel() for p in P.values()) * 1.4) + (1 << 23)
+        self._zero_phase("fwd")
+        need_bwd = training if need_bwd is None else need_bwd
+        Wp = self._pack_weights(P, need_bwd)
+        drop_p = float(cfg.dropout) if training else 0.0
+        sv = self.saved = {"P": P, "W": Wp, "need_bwd": need_bwd, "drop_p": drop_p, "seed": seed, "acts": {}}
+        cp = "conditioningprocessor."
+        E = cfg.emb_ch
+
+        # ---- logsnr embedding MLP (xunet.py:305-308)
+        ls = self.buf("logsnr", (N,), torch.float32)
+        ls.copy_(logsnr.reshape(-1).to(torch.float32))
+        e0 = self.buf("e0", (N, E))
+        ops.ddpm_embedding(ls, e0)
+        h1 = self.buf("h1", (N, E))
+        h1s = self.buf("h1s", (N, E))
+        ops.gemm(G.dense_desc(e0, Wp[cp + "logsnr_emb_emb.0.weight"], h1, E, bias=P[cp + "logsnr_emb_emb.0.bias"], out2=h1s))
+        lemb = self.buf("lemb", (N, E), torch.float32)
+        ops.gemm(G.dense_desc(h1s, Wp[cp + "logsnr_emb_emb.2.weight"], lemb, E, bias=P[cp + "logsnr_emb_emb.2.bias"]))
+
+        # ---- pose embedding (K1) and the four strided conditioning convs (+ logsnr_emb, SiLU for FiLM)
+        pe = self.buf("pose_emb", (N, H, Wd, 144))
+        ops.pose_embedding(K, R, t, cond_mask, P.get(cp + "pos_emb") if cfg.use_pos_emb else None,
+                           P[cp + "first_emb"].reshape(-1) if cfg.use_ref_pose_emb else None,
+                           P[cp + "other_emb"].reshape(-1) if cfg.use_ref_pose_emb else None, pe)
+        ss = []
+        for l in range(cfg.num_resolutions):
+            h, w = self.lvl_hw(l)
+            pre = self.buf(f"emb_pre{l}", (N, h, w, E))
+            sil = self.buf(f"emb_silu{l}", (N, h, w, E))
+            ops.gemm(G.conv_desc([pe], [9], Wp[cp + f"convs.{l}.weight"], E, pre, 2 ** l, bias=P[cp + f"convs.{l}.bias"],
+                                 rowvec=lemb, out2=sil))
+            s_l = self.buf(f"ss{l}", (N * h * w, self.film_cols[l]))
+            ops.gemm(G.dense_desc(sil.view(N * h * w, E), Wp[f"film{l}"], s_l, self.film_cols[l], bias=self._bufs[f"b.film{l}"]))
+            ss.append(s_l)
+
+        # ---- stem (xunet.py:493-495)
+        xin = self.buf("xin", (N, H, Wd, 8))
+        ops.pack_input(x, z, xin)
+        h = Act(self.buf("stem", (N, H, Wd, cfg.ch)), "stem")
+        ops.gemm(G.conv_desc([xin], [9], Wp["conv.weight"], cfg.ch, h.t, bias=P["conv.bias"]))
+
+        hs, skip, bi = [], None, 0
+        for kind, s in self.plan:
+            if kind == "push":
+                hs.append(h)
+            elif kind == "pop":
+                skip = hs.pop()
+            elif kind == "res":
+                h = self._res_fwd(s, h, skip if s.cat else None, ss[s.lvl], P, Wp, drop_p, seed * 1000 + bi)
+                skip = None
+                bi += 1
+            else:
+                h = self._attn_fwd(s, h, P, Wp)
+        assert not hs
+
+        # ---- head (xunet.py:535-536)
+        hh, ww, C = h.t.shape[1], h.t.shape[2], h.t.shape[3]
+        sums = self.zbuf("fwd", "lastgn.sums", (N, 32, 2))
+        x3 = h.t.view(N, hh * ww, C)
+        ops.gn_stats(x3, None, sums)
+        al = self.buf("lastgn.a", (N, hh * ww, C))
+        ops.gn_apply(x3, None, sums, P["lastgn.gn.weight"], P["lastgn.gn.bias"], 1, al)
+        y = self.buf("lastconv.y", (N, H, Wd, 16))
+        lb = self.buf("lastconv.b16", (16,), torch.float32)
+        lb.zero_()
+        lb[:3].copy_(P["lastconv.bias"])
+        ops.gemm(G.conv_desc([al.view(N, H, Wd, C)], [9], Wp["lastconv.weight"], 3, y, bias=lb))
+        eps = self.buf("eps", (B, 3, H, Wd), torch.float32)
+        ops.unpack_output(y, eps)
+        sv["final"] = h
+        sv["ss"] = ss
+        return eps
+
+    def _assign_cat_sources(self):
+        """channel split (h, skip) of the up-path concat inputs (xunet.py:435-451)"""
+        cfg, nres, nb = self.cfg, self.cfg.num_resolutions, self.cfg.num_res_blocks
+        for kind, s in self.plan:
+            if kind == "res" and s.cat:
+                lvl = s.lvl
+                i = int(s.name.split(".")[2])
+                if i == 0:
+                    ph = cfg.dim_out[lvl + 1] if lvl + 1 < nres else cfg.dim_out[lvl]
+                elif i == nb:
+                    ph = cfg.dim_out[lvl]
+                else:
+                    ph = cfg.dim_out[lvl]
+                s.srcs_c = [ph, s.cin - ph]
+
+    def _res_fwd(self, s, h_in, skip, ss_l, P, Wp, drop_p, seed):
+        """ResnetBlock.forward, xunet.py:133-152."""
+        ops, N, n = self.ops, self.N, s.name
+        hh, ww = h_in.t.shape[1], h_in.t.shape[2]
+        HW, F = hh * ww, s.f
+        x0 = h_in.t.view(N, HW, -1)
+        x1 = skip.t.view(N, HW, -1) if skip is not None else None
+        sums0 = self.zbuf("fwd", n + ".s0", (N, 32, 2))
+        ops.gn_stats(x0, x1, sums0)
+        a0 = self.buf(n + ".a0", (N, HW, s.cin))
+        ops.gn_apply(x0, x1, sums0, P[n + ".groupnorm0.gn.weight"], P[n + ".groupnorm0.gn.bias"], 1, a0)
+        c1 = self.buf(n + ".c1", (N, hh, ww, F))
+        ops.gemm(G.conv_desc([a0.view(N, hh, ww, s.cin)], [9], Wp[n + ".conv1.weight"], F, c1, bias=P[n + ".conv1.bias"]))
+        sums1 = self.zbuf("fwd", n + ".s1", (N, 32, 2))
+        c13 = c1.view(N, HW, F)
+        ops.gn_stats(c13, None, sums1)
+        a1 = self.buf(n + ".a1", (N, HW, F))
+        ssv = ss_l[:, s.film_off:s.film_off + 2 * F]
+        ops.gn_apply(c13, None, sums1, P[n + ".groupnorm1.gn.weight"], P[n + ".groupnorm1.gn.bias"], 2, a1, ss=ssv, F=F, drop_p=drop_p,
+                     seed=seed)
+        if s.cin != F:
+            sk = self.buf(n + ".sk", (N, hh, ww, F))
+            srcs = [h_in.t] + ([skip.t] if skip is not None else [])
+            ops.gemm(G.conv_desc(srcs, [1] * len(srcs), Wp[n + ".dense.weight"], F, sk, bias=P[n + ".dense.bias"]))
+        else:
+            assert skip is None
+            sk = h_in.t
+        out = self.buf(n + ".out", (N, hh, ww, F))
+        ops.gemm(G.conv_desc([a1.view(N, hh, ww, F)], [9], Wp[n + ".conv2.weight"], F, out, bias=P[n + ".conv2.bias"], resid=sk,
+                             out_scale=RSQRT2))
+        o = Act(out, n + ".out")
+        self.saved["acts"][n] = dict(h_in=h_in, skip=skip, sums0=sums0, a0=a0, c1=c1, sums1=sums1, a1=a1, out=o, seed=seed)
+        if s.resample == "down":
+            r = self.buf(n + ".rs", (N, hh // 2, ww // 2, F))
+            ops.avgpool2(out, r, 0.25)
+            o = Act(r, n + ".rs")
+        elif s.resample == "up":
+            r = self.buf(n + ".rs", (N, hh * 2, ww * 2, F))
+            ops.upsample2(out, r, 1.0)
+            o = Act(r, n + ".rs")
+        self.saved["acts"][n]["final"] = o
+        return o
+
+    def _qkv_views(self, qkv, L, C):
+        N, Hh = self.N, self.cfg.attn_heads
+        d = C // Hh
+        return [qkv.view(N, L, 3, Hh, d)[:, :, i].permute(0, 2, 1, 3) for i in range(3)]
+
+    def _attn_fwd(self, s, h_in, P, Wp):
+        """AttnBlock.forward, xunet.py:193-220 (nn.MultiheadAttention: in_proj -> softmax(QK^T/sqrt d)V -> out_proj)."""
+        ops, N, n, C = self.ops, self.N, s.name, s.c
+        hh, ww = h_in.t.shape[1], h_in.t.shape[2]
+        L, Hh = hh * ww, self.cfg.attn_heads
+        d = C // Hh
+        a = n + ".attn_layer.attn"
+        x3 = h_in.t.view(N, L, C)
+        sums = self.zbuf("fwd", n + ".s", (N, 32, 2))
+        ops.gn_stats(x3, None, sums)
+        g = self.buf(n + ".g", (N, L, C))
+        ops.gn_apply(x3, None, sums, P[n + ".groupnorm.gn.weight"], P[n + ".groupnorm.gn.bias"], 0, g)
+        qkv = self.buf(n + ".qkv", (N, L, 3 * C))
+        ops.gemm(G.dense_desc(g.view(N * L, C), Wp[a + ".in_proj_weight"], qkv.view(N * L, 3 * C), 3 * C, bias=P[a + ".in_proj_bias"]))
+        q, k, v = self._qkv_views(qkv, L, C)
+        Lp = (L + 7) // 8 * 8
+        pfull = self.buf(n + ".p", (N, Hh, L, Lp))
+        if Lp != L:
+            pfull.zero_()
+        p = pfull[..., :L]
+        ops.gemm(G.attn_qk_desc(q, k, p, s.cross, 1.0 / math.sqrt(d)))
+        ops.softmax(p, p)
+        o = self.buf(n + ".o", (N, L, C))
+        ops.gemm(G.attn_pv_desc(p, v, o.view(N, L, Hh, d).permute(0, 2, 1, 3), s.cross))
+        o1 = self.buf(n + ".o1", (N * L, C))
+        ops.gemm(G.dense_desc(o.view(N * L, C), Wp[a + ".out_proj.weight"], o1, C, bias=P[a + ".out_proj.bias"]))
+        out = self.buf(n + ".out", (N, hh, ww, C))
+        ops.gemm(G.dense_desc(o1, Wp[n + ".linear.weight"], out.view(N * L, C), C, bias=P[n + ".linear.bias"], resid=h_in.t.view(N * L, C),
+                              out_scale=RSQRT2))
+        oa = Act(out, n + ".out")
+        self.saved["acts"][n] = dict(h_in=h_in, sums=sums, g=g, qkv=qkv, p=p, o=o, o1=o1, out=oa)
+        return oa
+
+    # ------------------------------------------------------------------ backward
+    def _grad_of(self, act):
+        return self.buf("d." + act.key, act.t.shape)
+
+    def backward(self, Gr, deps, grad_flat=None):
+        """Gr: dict name -> fp32 grad tensor (PyTorch layout), overwritten.  deps: fp32 [B,3,H,W] = dL/d eps_hat.
+        grad_flat: optional flat tensor that all of Gr are views of (zeroed with one memset)."""
+        ops, cfg, B, N = self.ops, self.cfg, self.B, self.N
+        sv = self.saved
+        assert sv is not None and sv["need_bwd"], "backward needs a forward run with need_bwd=True"
+        P, Wp = sv["P"], sv["W"]
+        H, Wd, E = cfg.H, cfg.W, cfg.emb_ch
+        self._zero_phase("bwd")
+        if grad_flat is not None:
+            grad_flat.zero_()
+        else:
+            for g in Gr.values():
+                g.zero_()
+        for a in self._all_acts():
+            a.has_grad = False
+        drop_p = sv["drop_p"]
+        dss = [self.buf(f"dss{l}", (N * (H >> l) * (Wd >> l), self.film_cols[l])) for l in range(cfg.num_resolutions)]
+
+        # ---- head
+        h = sv["final"]
+        C = h.t.shape[3]
+        HW = H * Wd
+        dy = self.buf("lastconv.dy", (N, H, Wd, 16))
+        ops.pack_output_grad(deps, dy)
+        tmpb = self.zbuf("bwd", "lastconv.db", (16,))
+        ops.colsum(dy.view(N * HW, 16), N * HW, tmpb)
+        Gr["lastconv.bias"].copy_(tmpb[:3])
+        al = self._bufs["lastgn.a"]
+        self._conv_wgrad("lastconv.weight", dy, al.view(N, H, Wd, C), Gr["lastconv.weight"], co_alloc=16)
+        da = self.buf("lastgn.da", (N, H, Wd, C))
+        ops.gemm(G.conv_desc([dy], [9], Wp["lastconv.weight.T"], C, da))
+        dh = self._grad_of(h)
+        ops.gn_bwd(h.t.view(N, HW, C), None, self.zbuf("fwd", "lastgn.sums", (N, 32, 2)), P["lastgn.gn.weight"], P["lastgn.gn.bias"], 1,
+                   da.view(N, HW, C), Gr["lastgn.gn.weight"], Gr["lastgn.gn.bias"], self.zbuf("bwd", "lastgn.ws", (N, 32, 2)),
+                   dh.view(N, HW, C))
+        h.has_grad = True
+
+        # ---- blocks in reverse
+        bi = sum(1 for k, _ in self.plan if k == "res")
+        for kind, s in reversed(self.plan):
+            if kind == "res":
+                bi -= 1
+                self._res_bwd(s, P, Wp, Gr, dss[s.lvl], drop_p)
+            elif kind == "attn":
+                self._attn_bwd(s, P, Wp, Gr)
+
+        # ---- stem
+        stem = Act(self._bufs["stem"], "stem")
+        dstem = self._grad_of(stem)
+        xin = self._bufs["xin"]
+        ops.colsum(dstem.view(N * HW, cfg.ch), N * HW, Gr["conv.bias"])
+        gp = self.zbuf("bwd", "stem.gp", (cfg.ch, 9 * 64))
+        ops.gemm(G.wgrad_desc(dstem, xin, 9, gp, 0, 64))
+        ops.unpack_wgrad(gp, 0, 64, Gr["conv.weight"])
+
+        # ---- conditioning: FiLM data gradient, conditioning convs, learned embeddings, logsnr MLP
+        cp = "conditioningprocessor."
+        dlemb = self.zbuf("bwd", "dlemb", (N, E))
+        dP = self.buf("dP", (2, H, Wd, 144), torch.float32)
+        pe = self._bufs["pose_emb"]
+        for l in range(cfg.num_resolutions):
+            hh, ww = self.lvl_hw(l)
+            M = N * hh * ww
+            pre = self._bufs[f"emb_pre{l}"]
+            de = self.buf(f"de{l}", (N, hh, ww, E))
+            ops.gemm(G.dense_desc(dss[l], Wp[f"film{l}.T"], de.view(M, E), E))
+            ops.silu_bwd(de, pre, de)
+            ops.colsum(de.view(M, E), hh * ww, dlemb)
+            ops.colsum(de.view(M, E), M, Gr[cp + f"convs.{l}.bias"])
+            gp = self.zbuf("bwd", f"cc{l}.gp", (E, 9 * 192))
+            ops.gemm(G.wgrad_desc(de, pe, 9, gp, 0, 192, 2 ** l))
+            ops.unpack_wgrad(gp, 0, 192, Gr[cp + f"convs.{l}.weight"])
+            if cfg.use_pos_emb or cfg.use_ref_pose_emb:
+                des = self.buf(f"desum{l}", (2, hh, ww, E))
+                ops.batch_frame_sum(de, des)
+                Gm = self.buf(f"Gm{l}", (2 * hh * ww, 9 * 144), torch.float32)
+                ops.gemm(G.dense_desc(des.view(2 * hh * ww, E), Wp[cp + f"convs.{l}.weight.R"], Gm, 9 * 144))
+                ops.conv_tap_scatter(Gm, 144, hh, ww, 2 ** l, dP, l > 0)
+        if cfg.use_pos_emb or cfg.use_ref_pose_emb:
+            ops.pose_embedding_bwd(dP, Gr[cp + "pos_emb"] if cfg.use_pos_emb else None,
+                                   Gr[cp + "first_emb"].view(-1) if cfg.use_ref_pose_emb else None,
+                                   Gr[cp + "other_emb"].view(-1) if cfg.use_ref_pose_emb else None)
+        dl = self.buf("dlemb16", (N, E))
+        ops.cast(dlemb, dl)
+        h1, h1s, e0 = self._bufs["h1"], self._bufs["h1s"], self._bufs["e0"]
+        ops.colsum(dl, N, Gr[cp + "logsnr_emb_emb.2.bias"])
+        ops.gemm(G.wgrad_dense_desc(dl, h1s, Gr[cp + "logsnr_emb_emb.2.weight"]))
+        dh1 = self.buf("dh1", (N, E))
+        ops.gemm(G.dense_desc(dl, Wp[cp + "logsnr_emb_emb.2.weight.T"], dh1, E))
+        ops.silu_bwd(dh1, h1, dh1)
+        ops.colsum(dh1, N, Gr[cp + "logsnr_emb_emb.0.bias"])
+        ops.gemm(G.wgrad_dense_desc(dh1, e0, Gr[cp + "logsnr_emb_emb.0.weight"]))
+
+    def _all_acts(self):
+        sv = self.saved
+        out = [sv["final"]]
+        for d in sv["acts"].values():
+            for k in ("h_in", "skip", "out", "final"):
+                a = d.get(k)
+                if a is not None:
+                    out.append(a)
+        return out
+
+    def _conv_wgrad(self, wname, dy, x, gw, co_alloc=None, stride=1):
+        """3x3 weight gradient: packed fp32 [Co, 9*Cpad] through split-K atomics, then back to [Co,Ci,3,3]."""
+        Co, Ci = gw.shape[0], gw.shape[1]
+        cp = G.ceil64(Ci)
+        gp = self.zbuf("bwd", "gp." + wname, (co_alloc or Co, 9 * cp))
+        self.ops.gemm(G.wgrad_desc(dy, x, 9, gp, 0, cp, stride))
+        self.ops.unpack_wgrad(gp, 0, cp, gw)
+
+    def _take_grad(self, act):
+        """(buffer, existing) for writing a new gradient contribution of `act`"""
+        g = self._grad_of(act)
+        had = act.has_grad
+        act.has_grad = True
+        return g, (g if had else None)
+
+    def _res_bwd(self, s, P, Wp, Gr, dss_l, drop_p):
+        ops, N, n = self.ops, self.N, s.name
+        sa = self.saved["acts"][n]
+        h_in, skip, out = sa["h_in"], sa["skip"], sa["out"]
+        hh, ww = out.t.shape[1], out.t.shape[2]
+        HW, F, M = hh * ww, s.f, N * hh * ww
+        # adjoint of the resampling (xunet.py:17-28)
+        if s.resample == "down":
+            dout = self._grad_of(out)
+            ops.upsample2(self._grad_of(sa["final"]), dout, 0.25)
+        elif s.resample == "up":
+            dout = self._grad_of(out)
+            ops.avgpool2(self._grad_of(sa["final"]), dout, 1.0)
+        else:
+            dout = self._grad_of(out)
+        gs = self.tmp("gs", (N, hh, ww, F))
+        ops.add_scale(dout, None, gs, RSQRT2)
+        gs2 = gs.view(M, F)
+        # conv2
+        ops.colsum(gs2, M, Gr[n + ".conv2.bias"])
+        self._conv_wgrad(n + ".conv2.weight", gs, sa["a1"].view(N, hh, ww, F), Gr[n + ".conv2.weight"])
+        da1 = self.tmp("da1", (N, hh, ww, F))
+        ops.gemm(G.conv_desc([gs], [9], Wp[n + ".conv2.weight.T"], F, da1))
+        # 1x1 skip
+        if s.cin != F:
+            ops.colsum(gs2, M, Gr[n + ".dense.weight".replace("weight", "bias")])
+            gw = Gr[n + ".dense.weight"].view(F, s.cin)
+            srcs = [h_in] + ([skip] if skip is not None else [])
+            koff = 0
+            if len(srcs) == 1:
+                ops.gemm(G.wgrad_dense_desc(gs2, h_in.t.view(M, s.cin), gw))
+            else:
+                gp = self.zbuf("bwd", "gp." + n + ".dense", (F, sum(G.ceil64(a.t.shape[3]) for a in srcs)))
+                ci0 = 0
+                for a in srcs:
+                    c = a.t.shape[3]
+                    ops.gemm(G.wgrad_desc(gs, a.t, 1, gp, koff, G.ceil64(c)))
+                    ops.unpack_wgrad(gp, koff, G.ceil64(c), Gr[n + ".dense.weight"], ci0=ci0, cn=c)
+                    koff += G.ceil64(c)
+                    ci0 += c
+            dskip = self.tmp("dskip", (N, HW, s.cin))
+            ops.gemm(G.dense_desc(gs2, Wp[n + ".dense.weight.T"], dskip.view(M, s.cin), s.cin))
+            add0 = dskip
+        else:
+            add0 = gs.view(N, HW, F)
+        # GN1 + FiLM (+dropout)
+        ssv = self.saved["ss"][s.lvl][:, s.film_off:s.film_off + 2 * F]
+        dssv = dss_l[:, s.film_off:s.film_off + 2 * F]
+        dc1 = self.tmp("dc1", (N, hh, ww, F))
+        ops.gn_bwd(sa["c1"].view(N, HW, F), None, sa["sums1"], P[n + ".groupnorm1.gn.weight"], P[n + ".groupnorm1.gn.bias"], 2,
+                   da1.view(N, HW, F), Gr[n + ".groupnorm1.gn.weight"], Gr[n + ".groupnorm1.gn.bias"],
+                   self.zbuf("bwd", n + ".ws1", (N, 32, 2)), dc1.view(N, HW, F), ss=ssv, F=F, dss=dssv, drop_p=drop_p, seed=sa["seed"])
+        # FiLM dense parameters (xunet.py:80,84): per block, straight into the parameter gradients
+        sil = self._bufs[f"emb_silu{s.lvl}"].view(M, 1024)
+        ops.colsum(dssv, M, Gr[n + ".film.dense.bias"])
+        ops.gemm(G.wgrad_dense_desc(dssv, sil, Gr[n + ".film.dense.weight"]))
+        # conv1
+        ops.colsum(dc1.view(M, F), M, Gr[n + ".conv1.bias"])
+        self._conv_wgrad(n + ".conv1.weight", dc1, sa["a0"].view(N, hh, ww, s.cin), Gr[n + ".conv1.weight"])
+        da0 = self.tmp("da0", (N, hh, ww, s.cin))
+        ops.gemm(G.conv_desc([dc1], [9], Wp[n + ".conv1.weight.T"], s.cin, da0))
+        # GN0 + SiLU, merged with the skip-path gradient and with earlier contributions to the inputs
+        g0, e0 = self._take_grad(h_in)
+        x0 = h_in.t.view(N, HW, -1)
+        if skip is not None:
+            g1, e1 = self._take_grad(skip)
+            x1 = skip.t.view(N, HW, -1)
+        else:
+            g1 = e1 = x1 = None
+        v3 = lambda t_: t_.view(N, HW, -1) if t_ is not None else None
+        ops.gn_bwd(x0, x1, sa["sums0"], P[n + ".groupnorm0.gn.weight"], P[n + ".groupnorm0.gn.bias"], 1, da0.view(N, HW, s.cin),
+                   Gr[n + ".groupnorm0.gn.weight"], Gr[n + ".groupnorm0.gn.bias"], self.zbuf("bwd", n + ".ws0", (N, 32, 2)), v3(g0), v3(g1),
+                   add0=add0, add1a=v3(e0), add1b=v3(e1))
+
+    def _attn_bwd(self, s, P, Wp, Gr):
+        ops, N, n, C = self.ops, self.N, s.name, s.c
+        sa = self.saved["acts"][n]
+        h_in, out = sa["h_in"], sa["out"]
+        hh, ww = out.t.shape[1], out.t.shape[2]
+        L, Hh = hh * ww, self.cfg.attn_heads
+        d, M = C // Hh, N * hh * ww
+        a = n + ".attn_layer.attn"
+        alpha = 1.0 / math.sqrt(d)
+        dout = self._grad_of(out)
+        gs4 = self.tmp("ags", (N, hh, ww, C))
+        ops.add_scale(dout, None, gs4, RSQRT2)
+        gs = gs4.view(M, C)
+        # 1x1 `linear` and out_proj
+        ops.colsum(gs, M, Gr[n + ".linear.bias"])
+        ops.gemm(G.wgrad_dense_desc(gs, sa["o1"], Gr[n + ".linear.weight"].view(C, C)))
+        do1 = self.tmp("do1", (M, C))
+        ops.gemm(G.dense_desc(gs, Wp[n + ".linear.weight.T"], do1, C))
+        ops.colsum(do1, M, Gr[a + ".out_proj.bias"])
+        ops.gemm(G.wgrad_dense_desc(do1, sa["o"].view(M, C), Gr[a + ".out_proj.weight"]))
+        do = self.tmp("do", (N, L, C))
+        ops.gemm(G.dense_desc(do1, Wp[a + ".out_proj.weight.T"], do.view(M, C), C))
+        # attention core
+        q, k, v = self._qkv_views(sa["qkv"], L, C)
+        p = sa["p"]
+        dov = do.view(N, L, Hh, d).permute(0, 2, 1, 3)
+        Lp = (L + 7) // 8 * 8
+        dpf = self.tmp("dp", (N, Hh, L, Lp))
+        if Lp != L:
+            dpf.zero_()
+        dp = dpf[..., :L]
+        ops.gemm(G.attn_dp_desc(dov, v, dp, s.cross))
+        ops.softmax_bwd(p, dp, dp)
+        dqkv = self.tmp("dqkv", (N, L, 3 * C))
+        dq, dk, dv = self._qkv_views(dqkv, L, C)
+        ops.gemm(G.attn_dv_desc(p, dov, dv, s.cross))
+        ops.gemm(G.attn_dq_desc(dp, k, dq, s.cross, alpha))
+        ops.gemm(G.attn_dk_desc(dp, q, dk, s.cross, alpha))
+        # in_proj
+        dq2 = dqkv.view(M, 3 * C)
+        ops.colsum(dq2, M, Gr[a + ".in_proj_bias"])
+        ops.gemm(G.wgrad_dense_desc(dq2, sa["g"].view(M, C), Gr[a + ".in_proj_weight"]))
+        dg = self.tmp("dg", (N, L, C))
+        ops.gemm(G.dense_desc(dq2, Wp[a + ".in_proj_weight.T"], dg.view(M, C), C))
+        # GroupNorm + residual branch
+        g0, e0 = self._take_grad(h_in)
+        ops.gn_bwd(h_in.t.view(N, L, C), None, sa["sums"], P[n + ".groupnorm.gn.weight"], P[n + ".groupnorm.gn.bias"], 0, dg,
+                   Gr[n + ".groupnorm.gn.weight"], Gr[n + ".groupnorm.gn.bias"], self.zbuf("bwd", n + ".ws", (N, 32, 2)),
+                   g0.view(N, L, C), None, add0=gs.view(N, L, C), add1a=e0.view(N, L, C) if e0 is not None else None)

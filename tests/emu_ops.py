@@ -230,7 +230,7 @@ class EmuOps:
         elif mode == 1:
             blk = torch.zeros(Ci, taps, Cpad)
             blk[:, :, :Co] = w3.flip(2).permute(1, 2, 0)
-            out[:Ci, :taps * Cpad] = blk.reshape(Ci, -1).to(out.dtype)
+            out[:Ci, k_off:k_off + taps * Cpad] = blk.reshape(Ci, -1).to(out.dtype)
         else:
             out[:taps * Ci, :Co] = w3.permute(2, 1, 0).reshape(taps * Ci, Co).to(out.dtype)
 

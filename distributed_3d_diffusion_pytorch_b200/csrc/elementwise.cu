@@ -347,35 +347,41 @@ __global__ void conv_tap_scatter_kernel(const float* __restrict__ Gm, long long 
 }
 
 // ---------------------------------------------------------------------------------------------
-// attention softmax over rows of length L (bf16 in/out, fp32 math); one warp per row   (inside nn.MultiheadAttention)
+// attention softmax over rows of length L (logits fp32 or bf16 in, bf16 probabilities out, fp32 math); one warp
+// per row   (inside nn.MultiheadAttention).  ld_s / ld_p: row strides of the two tensors.
 // ---------------------------------------------------------------------------------------------
-__global__ void softmax_kernel(const bf16* __restrict__ S, bf16* __restrict__ P, long long rows, int L, long long ld) {
+__device__ __forceinline__ float ldf(const float* p) { return *p; }
+__device__ __forceinline__ float ldf(const bf16* p) { return __bfloat162float(*p); }
+
+template <typename TIn>
+__global__ void softmax_kernel(const TIn* __restrict__ S, bf16* __restrict__ P, long long rows, int L, long long ld_s, long long ld_p) {
   const long long row = (long long)blockIdx.x * (blockDim.x / 32) + (threadIdx.x >> 5);
   if (row >= rows) return;
   const int lane = threadIdx.x & 31;
-  const bf16* s = S + row * ld;
+  const TIn* s = S + row * ld_s;
   float m = -INFINITY;
-  for (int i = lane; i < L; i += 32) m = fmaxf(m, __bfloat162float(s[i]));
+  for (int i = lane; i < L; i += 32) m = fmaxf(m, ldf(s + i));
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
   float sum = 0.f;
-  for (int i = lane; i < L; i += 32) sum += __expf(__bfloat162float(s[i]) - m);
+  for (int i = lane; i < L; i += 32) sum += __expf(ldf(s + i) - m);
   sum = b3d_warp_sum(sum);
   const float inv = 1.f / sum;
-  for (int i = lane; i < L; i += 32) P[row * ld + i] = __float2bfloat16(__expf(__bfloat162float(s[i]) - m) * inv);
+  for (int i = lane; i < L; i += 32) P[row * ld_p + i] = __float2bfloat16(__expf(ldf(s + i) - m) * inv);
 }
 // dS = P * (dP - sum(P*dP))
-__global__ void softmax_bwd_kernel(const bf16* __restrict__ P, const bf16* __restrict__ dP, bf16* __restrict__ dS, long long rows, int L,
-                                   long long ld) {
+template <typename TIn>
+__global__ void softmax_bwd_kernel(const bf16* __restrict__ P, const TIn* __restrict__ dP, bf16* __restrict__ dS, long long rows, int L,
+                                   long long ld_p, long long ld_dp, long long ld_ds) {
   const long long row = (long long)blockIdx.x * (blockDim.x / 32) + (threadIdx.x >> 5);
   if (row >= rows) return;
   const int lane = threadIdx.x & 31;
   float dot = 0.f;
-  for (int i = lane; i < L; i += 32) dot += __bfloat162float(P[row * ld + i]) * __bfloat162float(dP[row * ld + i]);
+  for (int i = lane; i < L; i += 32) dot += __bfloat162float(P[row * ld_p + i]) * ldf(dP + row * ld_dp + i);
   dot = b3d_warp_sum(dot);
   for (int i = lane; i < L; i += 32) {
-    const float p = __bfloat162float(P[row * ld + i]);
-    dS[row * ld + i] = __float2bfloat16(p * (__bfloat162float(dP[row * ld + i]) - dot));
+    const float p = __bfloat162float(P[row * ld_p + i]);
+    dS[row * ld_ds + i] = __float2bfloat16(p * (ldf(dP + row * ld_dp + i) - dot));
   }
 }
 
@@ -556,12 +562,15 @@ extern "C" int b3d_conv_tap_scatter(const float* G, int64_t ldg, int C, int h, i
   conv_tap_scatter_kernel<<<grid_for(2LL * H * W * C), kT, 0, STREAM>>>(G, ldg, C, h, w, s, H, W, dP, ldp, accumulate);
   DONE(1);
 }
-extern "C" int b3d_softmax(const void* S, void* P, int64_t rows, int L, int64_t ld, void* stream) {
-  softmax_kernel<<<cdiv(rows, 8), 256, 0, STREAM>>>((const bf16*)S, (bf16*)P, rows, L, ld);
+extern "C" int b3d_softmax(const void* S, int s_fp32, int64_t ld_s, void* P, int64_t ld_p, int64_t rows, int L, void* stream) {
+  if (s_fp32) softmax_kernel<float><<<cdiv(rows, 8), 256, 0, STREAM>>>((const float*)S, (bf16*)P, rows, L, ld_s, ld_p);
+  else softmax_kernel<bf16><<<cdiv(rows, 8), 256, 0, STREAM>>>((const bf16*)S, (bf16*)P, rows, L, ld_s, ld_p);
   DONE(1);
 }
-extern "C" int b3d_softmax_bwd(const void* P, const void* dP, void* dS, int64_t rows, int L, int64_t ld, void* stream) {
-  softmax_bwd_kernel<<<cdiv(rows, 8), 256, 0, STREAM>>>((const bf16*)P, (const bf16*)dP, (bf16*)dS, rows, L, ld);
+extern "C" int b3d_softmax_bwd(const void* P, int64_t ld_p, const void* dP, int dp_fp32, int64_t ld_dp, void* dS, int64_t ld_ds, int64_t rows,
+                               int L, void* stream) {
+  if (dp_fp32) softmax_bwd_kernel<float><<<cdiv(rows, 8), 256, 0, STREAM>>>((const bf16*)P, (const float*)dP, (bf16*)dS, rows, L, ld_p, ld_dp, ld_ds);
+  else softmax_bwd_kernel<bf16><<<cdiv(rows, 8), 256, 0, STREAM>>>((const bf16*)P, (const bf16*)dP, (bf16*)dS, rows, L, ld_p, ld_dp, ld_ds);
   DONE(1);
 }
 extern "C" int b3d_q_sample(const float* z, const float* noise, const float* logsnr, const float* x, const float* xrand, const uint8_t* mask,

@@ -379,12 +379,10 @@ class Engine:
         ops.gemm(G.dense_desc(g.view(N * L, C), Wp[a + ".in_proj_weight"], qkv.view(N * L, 3 * C), 3 * C, bias=P[a + ".in_proj_bias"]))
         q, k, v = self._qkv_views(qkv, L, C)
         Lp = (L + 7) // 8 * 8
-        pfull = self.buf(n + ".p", (N, Hh, L, Lp))
-        if Lp != L:
-            pfull.zero_()
-        p = pfull[..., :L]
-        ops.gemm(G.attn_qk_desc(q, k, p, s.cross, 1.0 / math.sqrt(d)))
-        ops.softmax(p, p)
+        p = self.buf(n + ".p", (N, Hh, L, Lp))[..., :L]
+        logits = self.tmp("logits", (N, Hh, L, Lp), torch.float32)[..., :L]      # fp32: never rounded before the softmax
+        ops.gemm(G.attn_qk_desc(q, k, logits, s.cross, 1.0 / math.sqrt(d)))
+        ops.softmax(logits, p)
         o = self.buf(n + ".o", (N, L, C))
         ops.gemm(G.attn_pv_desc(p, v, o.view(N, L, Hh, d).permute(0, 2, 1, 3), s.cross))
         o1 = self.buf(n + ".o1", (N * L, C))
@@ -620,12 +618,10 @@ class Engine:
         p = sa["p"]
         dov = do.view(N, L, Hh, d).permute(0, 2, 1, 3)
         Lp = (L + 7) // 8 * 8
-        dpf = self.tmp("dp", (N, Hh, L, Lp))
-        if Lp != L:
-            dpf.zero_()
-        dp = dpf[..., :L]
-        ops.gemm(G.attn_dp_desc(dov, v, dp, s.cross))
-        ops.softmax_bwd(p, dp, dp)
+        dpl = self.tmp("logits", (N, Hh, L, Lp), torch.float32)[..., :L]
+        dp = self.tmp("ds", (N, Hh, L, Lp))[..., :L]
+        ops.gemm(G.attn_dp_desc(dov, v, dpl, s.cross))
+        ops.softmax_bwd(p, dpl, dp)
         dqkv = self.tmp("dqkv", (N, L, 3 * C))
         dq, dk, dv = self._qkv_views(dqkv, L, C)
         ops.gemm(G.attn_dv_desc(p, dov, dv, s.cross))

@@ -250,14 +250,18 @@ class CudaOps:
         return t.numel() // L, L, ld
 
     def softmax(self, S, P):
-        rows, L, ld = self._rows_ld(S)
-        assert P.stride() == S.stride()
-        self._call("b3d_softmax", _ptr(S), _ptr(P), c_i64(rows), c_i32(L), c_i64(ld), self.stream())
+        rows, L, ld_s = self._rows_ld(S)
+        rows_p, _, ld_p = self._rows_ld(P)
+        assert rows == rows_p and P.dtype == torch.bfloat16
+        self._call("b3d_softmax", _ptr(S), c_i32(int(S.dtype == torch.float32)), c_i64(ld_s), _ptr(P), c_i64(ld_p), c_i64(rows), c_i32(L),
+                   self.stream())
 
     def softmax_bwd(self, P, dP, dS):
-        rows, L, ld = self._rows_ld(P)
-        assert dP.stride() == P.stride() and dS.stride() == P.stride()
-        self._call("b3d_softmax_bwd", _ptr(P), _ptr(dP), _ptr(dS), c_i64(rows), c_i32(L), c_i64(ld), self.stream())
+        rows, L, ld_p = self._rows_ld(P)
+        _, _, ld_dp = self._rows_ld(dP)
+        _, _, ld_ds = self._rows_ld(dS)
+        self._call("b3d_softmax_bwd", _ptr(P), c_i64(ld_p), _ptr(dP), c_i32(int(dP.dtype == torch.float32)), c_i64(ld_dp), _ptr(dS),
+                   c_i64(ld_ds), c_i64(rows), c_i32(L), self.stream())
 
     # ---- GroupNorm family.  x0/x1: [N, HW, C*] views with stride(-1) == 1 (x1 may be None)
     @staticmethod

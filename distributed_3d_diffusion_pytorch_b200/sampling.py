@@ -1,0 +1,158 @@
+"""Drop-in for the sampler functions of the reference's sampling.py:59-155 (stochastic-conditioning
+ancestral sampler with classifier-free guidance), device-resident:
+
+* the conditional and unconditional UNet calls of one denoise step (sampling.py:97-99) are ONE forward
+  of batch 2b (rows are independent: GroupNorm is per image, attention is per pair);
+* the guidance mix / x0 clip / posterior mean / noise add (sampling.py:101-127) is ONE kernel;
+* nothing crosses to the host inside a step (the reference moves 4 tensors per step and does the update
+  on the CPU).
+
+Objects are independent, views of one object are sequential (`record` grows), so multi-GPU sampling
+shards OBJECTS across ranks with no collective (`shard_objects`)."""
+import random
+
+import numpy as np
+import torch
+
+from .diff3d import _ops, logsnr_schedule_cosine
+
+
+def _dev(model):
+    m = model.module if hasattr(model, "module") else model
+    return m.flat_parameters().device
+
+
+def _t(a, dev, dtype):
+    if not torch.is_tensor(a):
+        a = torch.as_tensor(np.asarray(a))
+    return a.to(device=dev, dtype=dtype)
+
+
+def xt2batch(x, logsnr, z, R, T, K):
+    """sampling.py:65-76 (K is one [3,3] matrix repeated over the batch)."""
+    b = x.shape[0]
+    return {
+        'x': x.cuda(),
+        'z': z.cuda(),
+        'logsnr': torch.stack([logsnr_schedule_cosine(torch.zeros_like(logsnr)), logsnr], dim=1).cuda(),
+        'R': R.cuda(),
+        't': T.cuda(),
+        'K': K[None].repeat(b, 1, 1).cuda(),
+    }
+
+
+@torch.no_grad()
+def predict_noise_pair(model, x, z, R, T, K, logsnr, x_uncond=None, generator=None):
+    """eps_cond, eps_uncond of sampling.py:97-99 from one batch-2b forward."""
+    dev = _dev(model)
+    b = z.shape[0]
+    x, z = _t(x, dev, torch.float32), _t(z, dev, torch.float32)
+    if x_uncond is None:
+        x_uncond = torch.randn(x.shape, device=dev, dtype=torch.float32, generator=generator)
+    lam = torch.as_tensor(float(logsnr)).repeat(2 * b)
+    K2 = _t(K, dev, torch.float64)
+    K2 = K2[None].repeat(2 * b, 1, 1) if K2.dim() == 2 else K2.repeat(2, 1, 1)
+    batch = {
+        'x': torch.cat([x, _t(x_uncond, dev, torch.float32)], 0),
+        'z': torch.cat([z, z], 0),
+        'logsnr': torch.stack([logsnr_schedule_cosine(torch.zeros_like(lam)), lam], dim=1).to(dev),
+        'R': _t(R, dev, torch.float64).repeat(2, 1, 1, 1),
+        't': _t(T, dev, torch.float64).repeat(2, 1, 1),
+        'K': K2,
+    }
+    cond_mask = torch.cat([torch.ones(b, dtype=torch.bool), torch.zeros(b, dtype=torch.bool)]).to(dev)
+    eps = model(batch, cond_mask=cond_mask)
+    return eps[:b], eps[b:]
+
+
+@torch.no_grad()
+def p_mean_variance(model, x, z, R, T, K, logsnr, logsnr_next, w):
+    """sampling.py:79-112: returns (model_mean, posterior_variance) like the reference (device tensors)."""
+    dev = _dev(model)
+    eps_c, eps_u = predict_noise_pair(model, x, z, R, T, K, logsnr)
+    z = _t(z, dev, torch.float32)
+    mean = torch.empty_like(z)
+    # the same kernel as p_sample with a zero noise tensor gives the mean alone
+    zero = torch.zeros_like(z) if float(logsnr_next) != 0.0 else None
+    _ops(dev).sampler_update(z.contiguous(), eps_c.contiguous(), eps_u.contiguous(), _t(w, dev, torch.float32), zero, mean, float(logsnr),
+                             float(logsnr_next))
+    lam, lam_n = torch.as_tensor(float(logsnr)), torch.as_tensor(float(logsnr_next))
+    var = (-lam_n).sigmoid() * (-torch.special.expm1(lam - lam_n))
+    return mean, var.to(dev)
+
+
+@torch.no_grad()
+def p_sample(model, z, x, R, T, K, logsnr, logsnr_next, w, noise=None, generator=None):
+    """sampling.py:115-127: one denoise step.  `noise` (optional) is the randn_like of :127."""
+    dev = _dev(model)
+    eps_c, eps_u = predict_noise_pair(model, x, z, R, T, K, logsnr, generator=generator)
+    z = _t(z, dev, torch.float32).contiguous()
+    if noise is None and float(logsnr_next) != 0.0:
+        noise = torch.randn(z.shape, device=dev, dtype=torch.float32, generator=generator)
+    out = torch.empty_like(z)
+    _ops(dev).sampler_update(z, eps_c.contiguous(), eps_u.contiguous(), _t(w, dev, torch.float32),
+                             _t(noise, dev, torch.float32).contiguous() if noise is not None else None, out, float(logsnr), float(logsnr_next))
+    return out
+
+
+@torch.no_grad()
+def sample(model, record, target_R, target_T, K, w, timesteps=256, generator=None):
+    """sampling.py:130-155: 256-step ancestral loop; each step conditions on a random entry of `record`
+    (python `random.choice`, as the reference).  Returns np.ndarray [b,3,H,W]."""
+    dev = _dev(model)
+    w = _t(w, dev, torch.float32)
+    b = w.shape[0]
+    first = _t(record[0][0], dev, torch.float32)
+    img = torch.randn(first.shape, device=dev, dtype=torch.float32, generator=generator)
+    logsnrs = logsnr_schedule_cosine(torch.linspace(1., 0., timesteps + 1)[:-1])
+    logsnr_nexts = logsnr_schedule_cosine(torch.linspace(1., 0., timesteps + 1)[1:])
+    target_R, target_T = _t(target_R, dev, torch.float64), _t(target_T, dev, torch.float64)
+    cache = {}
+    for logsnr, logsnr_next in zip(logsnrs, logsnr_nexts):
+        # random.choice(record) of sampling.py:138, in index form so device copies of the entries can be cached
+        i = random.randrange(len(record))
+        if i not in cache:
+            ci, cR, cT = record[i]
+            cache[i] = (_t(ci, dev, torch.float32), _t(cR, dev, torch.float64), _t(cT, dev, torch.float64))
+        cimg, cR, cT = cache[i]
+        R = torch.stack([cR, target_R], 0)[None].repeat(b, 1, 1, 1)
+        T = torch.stack([cT, target_T], 0)[None].repeat(b, 1, 1)
+        img = p_sample(model, z=img, x=cimg, R=R, T=T, K=K, logsnr=logsnr, logsnr_next=logsnr_next, w=w, generator=generator)
+    return img.cpu().numpy()
+
+
+@torch.no_grad()
+def sample_fixed_condition(model, img, R, T, K, w, timesteps=256):
+    """train.py:63-78 flavour: conditioning frame fixed to img[:,0]; returns the list of per-step arrays."""
+    dev = _dev(model)
+    x = _t(img, dev, torch.float32)[:, 0]
+    z = torch.randn_like(x)
+    imgs = []
+    logsnrs = logsnr_schedule_cosine(torch.linspace(1., 0., timesteps + 1)[:-1])
+    logsnr_nexts = logsnr_schedule_cosine(torch.linspace(1., 0., timesteps + 1)[1:])
+    for logsnr, logsnr_next in zip(logsnrs, logsnr_nexts):
+        z = p_sample(model, z=z, x=x, R=R, T=T, K=K, logsnr=logsnr, logsnr_next=logsnr_next, w=w)
+        imgs.append(z.cpu().numpy())
+    return imgs
+
+
+def shard_objects(num_objects, rank, world_size):
+    """object i -> rank i % world_size (no data-path collective)."""
+    return [i for i in range(num_objects) if i % world_size == rank]
+
+
+@torch.no_grad()
+def sample_object(model, views, K, w, timesteps=256, max_views=None, generator=None):
+    """Driver loop of sampling.py:158-176 for one object: `views` = [(img [3,H,W], R [3,3], T [3]), ...];
+    view 0 is the given image, every following view is synthesised autoregressively.  Returns the record."""
+    w_t = torch.as_tensor(np.asarray(w))
+    b = w_t.shape[0]
+    img0 = np.asarray(views[0][0])
+    record = [[np.repeat(img0[None], b, axis=0), np.asarray(views[0][1]), np.asarray(views[0][2])]]
+    for vi, (_, R, T) in enumerate(views[1:]):
+        if max_views is not None and vi >= max_views:
+            break
+        img = sample(model, record=record, target_R=torch.as_tensor(np.asarray(R)), target_T=torch.as_tensor(np.asarray(T)), K=K, w=w_t,
+                     timesteps=timesteps, generator=generator)
+        record.append([img, np.asarray(R), np.asarray(T)])
+    return record

@@ -1,0 +1,73 @@
+"""smoke(): one small training step of the hot path on cuda:0, checked against the oracle
+(oracle/ is test infrastructure; this is one of the three places allowed to import it)."""
+import torch
+
+
+def parity_metrics(model_kw, B, seed, cond_mask, device="cuda:0"):
+    """Runs the same (inputs, weights) through the CUDA path and through the fp32 oracle.
+    Returns dict(out_rel_l2, loss_rel, grad_cos, worst_grad_cos)."""
+    from oracle import xunet_ref as xr, diffusion_ref as dr
+    from . import synthetic
+    from .diff3d import diffusion_loss
+    from .xunet import XUNet
+
+    ocfg = xr.Cfg(**model_kw)
+    sd = xr.init_state_dict(ocfg, seed=seed)
+    img, R, T, K = synthetic.make_views(B, model_kw["H"], seed=seed + 1)
+    g = torch.Generator().manual_seed(seed + 2)
+    logsnr = dr.logsnr_schedule_cosine(torch.rand(B, generator=g))
+    noise = torch.randn(img[:, 0].shape, generator=g)
+    xrep = torch.randn(img[:, 0].shape, generator=g)
+    cm = torch.tensor(cond_mask)
+    z_noisy = dr.q_sample(img[:, 1], logsnr, noise)
+    x_cond = torch.where(cm[:, None, None, None], img[:, 0], xrep)
+    batch = dr.make_batch(x_cond, logsnr, z_noisy, R, T, K)
+
+    # oracle (fp32, on the GPU when the model is large, TF32 off)
+    odev = torch.device(device if model_kw["H"] >= 32 else "cpu")
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    sdo = {k: v.to(odev).requires_grad_(True) for k, v in sd.items()}
+    bo = {k: v.to(odev) for k, v in batch.items()}
+    eps_o = xr.xunet_forward(sdo, ocfg, bo, cm.to(odev))
+    loss_o = dr.loss_fn(noise.to(odev), eps_o)
+    loss_o.backward()
+
+    model = XUNet(**model_kw).to(device)
+    model.load_state_dict(sd)
+    model.eval()                                   # dropout off on both sides (H2)
+    bd = {k: v.to(device) for k, v in batch.items()}
+    eps = model(bd, cond_mask=cm.to(device))
+    loss = diffusion_loss(noise.to(device), eps)
+    loss.backward()
+    torch.cuda.synchronize()
+
+    eo = eps_o.detach().float().cpu()
+    e = eps.detach().float().cpu()
+    out_rel = ((e - eo).norm() / eo.norm()).item()
+    loss_rel = abs(loss.item() - loss_o.item()) / abs(loss_o.item())
+    ga = torch.cat([p.grad.flatten().float().cpu() for _, p in model.named_parameters()])
+    gb = torch.cat([sdo[n].grad.flatten().float().cpu() for n, _ in model.named_parameters()])
+    cos = torch.nn.functional.cosine_similarity(ga, gb, dim=0).item()
+    worst, worst_name = 1.0, None
+    for n, p in model.named_parameters():
+        go = sdo[n].grad.flatten().float().cpu()
+        if go.norm() < 1e-6 * gb.norm():
+            continue                               # analytically ~0 (e.g. a bias in front of a 1-channel GroupNorm group)
+        c = torch.nn.functional.cosine_similarity(p.grad.flatten().float().cpu(), go, dim=0).item()
+        if c < worst:
+            worst, worst_name = c, n
+    return dict(out_rel_l2=out_rel, loss_rel=loss_rel, grad_cos=cos, worst_grad_cos=worst, worst_name=worst_name,
+                finite=bool(torch.isfinite(e).all() and torch.isfinite(ga).all()))
+
+
+def smoke():
+    from . import _lib
+    n0 = _lib.launch_count()
+    m = parity_metrics(dict(H=32, W=32, ch=64), B=2, seed=11, cond_mask=[True, False])
+    print("b3d smoke:", m, "kernel launches:", _lib.launch_count() - n0)
+    assert m["finite"]
+    assert m["out_rel_l2"] <= 2e-2, m
+    assert m["loss_rel"] <= 1e-3, m
+    assert m["grad_cos"] >= 0.999, m
+    assert _lib.launch_count() - n0 > 100

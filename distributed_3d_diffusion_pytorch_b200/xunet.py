@@ -90,9 +90,8 @@ class _Node(torch.nn.Module):
 
 class _XUNetFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, model, x, z, logsnr, R, t, K, cond_mask, seed, *params):
+    def forward(ctx, model, x, z, logsnr, R, t, K, cond_mask, seed, need_bwd, *params):
         eng = model._engine(x.shape[0])
-        need_bwd = any(p.requires_grad for p in params) and torch.is_grad_enabled()
         P = dict(zip(model._names, params))
         eps = eng.forward(P, x, z, logsnr, R, t, K, cond_mask, training=model.training, need_bwd=need_bwd, seed=seed)
         ctx.model, ctx.eng = model, eng
@@ -107,8 +106,8 @@ class _XUNetFn(torch.autograd.Function):
             # training loops of this package: .grad of every parameter IS its slice of the flat arena
             for n, p in zip(model._names, model._plist):
                 p.grad = Gr[n]
-            return (None,) * 9 + (None,) * len(model._names)
-        return (None,) * 9 + tuple(Gr[n] for n in model._names)
+            return (None,) * 10 + (None,) * len(model._names)
+        return (None,) * 10 + tuple(Gr[n] for n in model._names)
 
 
 class XUNet(torch.nn.Module):
@@ -218,8 +217,9 @@ class XUNet(torch.nn.Module):
         f32 = lambda t: t.to(device=dev, dtype=torch.float32)
         f64 = lambda t: t.to(device=dev, dtype=torch.float64)
         self._step_seed += 1
+        need_bwd = torch.is_grad_enabled() and any(p.requires_grad for p in self._plist)
         return _XUNetFn.apply(self, f32(x).contiguous(), f32(batch["z"]).contiguous(), f32(batch["logsnr"]), f64(batch["R"]),
-                              f64(batch["t"]), f64(batch["K"]), cond_mask.to(dev), self._step_seed, *self._plist)
+                              f64(batch["t"]), f64(batch["K"]), cond_mask.to(dev), self._step_seed, need_bwd, *self._plist)
 
     def load_state_dict(self, state_dict, strict=True, **kw):
         """accepts checkpoints saved from nn.DataParallel (`module.` prefix, sampling.py:52-56)"""

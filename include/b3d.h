@@ -114,9 +114,11 @@ int b3d_batch_frame_sum(const void* in, void* out, int B, int64_t per_frame_elem
 /* adjoint of the strided conditioning convs w.r.t. their input from per-tap GEMM products, xunet.py:340-349 */
 int b3d_conv_tap_scatter(const float* G, int64_t ldg, int C, int h, int w, int s, int H, int W, float* dP, int64_t ldp, int accumulate,
                          void* stream);
-/* softmax inside nn.MultiheadAttention (xunet.py:161,175) over rows of length L (row stride ld), and its adjoint */
-int b3d_softmax(const void* S, void* P, int64_t rows, int L, int64_t ld, void* stream);
-int b3d_softmax_bwd(const void* P, const void* dP, void* dS, int64_t rows, int L, int64_t ld, void* stream);
+/* softmax inside nn.MultiheadAttention (xunet.py:161,175) over rows of length L, and its adjoint.
+ * Logits S / dP may be fp32 (the GEMM writes them straight from its fp32 accumulators) or bf16; P, dS are bf16. */
+int b3d_softmax(const void* S, int s_fp32, int64_t ld_s, void* P, int64_t ld_p, int64_t rows, int L, void* stream);
+int b3d_softmax_bwd(const void* P, int64_t ld_p, const void* dP, int dp_fp32, int64_t ld_dp, void* dS, int64_t ld_ds, int64_t rows, int L,
+                    void* stream);
 
 /* GroupNorm(32, C, eps 1e-5) per image (xunet.py:61-71) on the channel-concat of up to two tensors.
  * b3d_gn_stats accumulates raw (sum, sumsq) into ws_sums fp32 [N,32,2] (caller zeroes it).

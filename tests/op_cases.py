@@ -130,12 +130,13 @@ def misc_case(seed=0):
         dpos, dfe, doe = ops.zeros((144, 8, 8), torch.float32), ops.zeros((144,), torch.float32), ops.zeros((144,), torch.float32)
         ops.pose_embedding_bwd(dPb, dpos, dfe, doe)
         outs += [dpos, dfe, doe]
-        # softmax
-        S = ops.zeros((2, 4, 36, 40))
-        S[..., :36] = _mk(ops, _r((2, 4, 36, 36), g, 2.0))
-        P = ops.zeros((2, 4, 36, 40)); ops.softmax(S[..., :36], P[..., :36]); outs.append(P)
-        dP2 = ops.zeros((2, 4, 36, 40)); dP2[..., :36] = _mk(ops, _r((2, 4, 36, 36), g))
-        dS = ops.zeros((2, 4, 36, 40)); ops.softmax_bwd(P[..., :36], dP2[..., :36], dS[..., :36]); outs.append(dS)
+        # softmax (fp32 and bf16 logits, padded row strides)
+        for dt in (torch.float32, None):
+            S = ops.zeros((2, 4, 36, 40), dt)
+            S[..., :36] = _mk(ops, _r((2, 4, 36, 36), g, 2.0), dt)
+            P = ops.zeros((2, 4, 36, 40)); ops.softmax(S[..., :36], P[..., :36]); outs.append(P)
+            dP2 = ops.zeros((2, 4, 36, 40), dt); dP2[..., :36] = _mk(ops, _r((2, 4, 36, 36), g), dt)
+            dS = ops.zeros((2, 4, 36, 48)); ops.softmax_bwd(P[..., :36], dP2[..., :36], dS[..., :36]); outs.append(dS)
         # diffusion glue
         Bq = 5
         zz, nz, xx, xr = [torch.randn(Bq, 3, 8, 8, generator=g).to(dev) for _ in range(4)]

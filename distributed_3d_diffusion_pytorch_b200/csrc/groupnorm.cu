@@ -63,7 +63,7 @@ struct ApplyP {
   bf16* out; long long ld_out;
   int HW, mode;  // 0 plain, 1 silu, 2 film
   const bf16* ss; long long ld_ss; int F;  // film: scale = ss[row, c], shift = ss[row, F + c]
-  float drop_p; unsigned long long seed;
+  float drop_p; unsigned long long seed; const unsigned long long* seed_ptr;  // effective seed = seed + *seed_ptr (device step counter)
 };
 
 __global__ void gn_apply_kernel(ApplyP p, int rows_per_block) {
@@ -97,7 +97,7 @@ __global__ void gn_apply_kernel(ApplyP p, int rows_per_block) {
       if (p.mode == 1) y = b3d_silu(y);
       else if (p.mode == 2) {
         y = y * (1.f + sc[j]) + sh[j];
-        if (p.drop_p > 0.f) y = (b3d_uniform(p.seed, (unsigned long long)row * C + c + j) < p.drop_p) ? 0.f : y * keep;
+        if (p.drop_p > 0.f) y = (b3d_uniform(p.seed + (p.seed_ptr ? *p.seed_ptr : 0ULL), (unsigned long long)row * C + c + j) < p.drop_p) ? 0.f : y * keep;
       }
       f[j] = y;
     }
@@ -112,7 +112,7 @@ struct BwdP {
   int HW, mode;
   const bf16* ss; long long ld_ss; int F;
   bf16* dss; long long ld_dss;      // film: d_scale -> dss[row, c], d_shift -> dss[row, F + c]
-  float drop_p; unsigned long long seed;
+  float drop_p; unsigned long long seed; const unsigned long long* seed_ptr;  // effective seed = seed + *seed_ptr (device step counter)
   float* dgamma; float* dbeta;      // fp32 [C], accumulated
   float* ws;                        // [N,32,2] (S1, S2), pre-zeroed
   // pass 2 outputs
@@ -137,7 +137,7 @@ __device__ __forceinline__ void gn_bwd_dz(const BwdP& p, long long row, int c, i
     float d = dy[j];
     if (p.mode == 1) d *= b3d_silu_grad(z);
     else if (p.mode == 2) {
-      if (p.drop_p > 0.f) d = (b3d_uniform(p.seed, (unsigned long long)row * C + c + j) < p.drop_p) ? 0.f : d * keep;
+      if (p.drop_p > 0.f) d = (b3d_uniform(p.seed + (p.seed_ptr ? *p.seed_ptr : 0ULL), (unsigned long long)row * C + c + j) < p.drop_p) ? 0.f : d * keep;
       dsc[j] = d * z; dsh[j] = d;
       d *= (1.f + sc[j]);
     }
@@ -275,7 +275,7 @@ extern "C" int b3d_gn_stats(const void* x0, int C0, int64_t ld0, const void* x1,
 
 extern "C" int b3d_gn_apply(const void* x0, int C0, int64_t ld0, const void* x1, int C1, int64_t ld1, int N, int HW, const float* sums,
                             const float* gamma, const float* beta, int mode, const void* ss, int64_t ld_ss, int F, float drop_p,
-                            uint64_t seed, void* out, int64_t ld_out, void* stream) {
+                            uint64_t seed, const uint64_t* seed_ptr, void* out, int64_t ld_out, void* stream) {
   if (int rc = check_src(x0, C0, x1, C1)) return rc;
   B3D_CHECK_ARG(mode >= 0 && mode <= 2, "gn_apply: mode");
   B3D_CHECK_ARG(mode != 2 || (ss != nullptr && F == C0 + C1), "gn_apply: film needs ss and F == C");
@@ -283,7 +283,7 @@ extern "C" int b3d_gn_apply(const void* x0, int C0, int64_t ld0, const void* x1,
   ApplyP p{};
   p.s = Src2{(const bf16*)x0, (const bf16*)x1, C0, C1, ld0, ld1};
   p.stats = sums; p.gamma = gamma; p.beta = beta; p.out = (bf16*)out; p.ld_out = ld_out; p.HW = HW; p.mode = mode;
-  p.ss = (const bf16*)ss; p.ld_ss = ld_ss; p.F = F; p.drop_p = drop_p; p.seed = seed;
+  p.ss = (const bf16*)ss; p.ld_ss = ld_ss; p.F = F; p.drop_p = drop_p; p.seed = seed; p.seed_ptr = (const unsigned long long*)seed_ptr;
   const int rpb = pick_rows_per_block(N, HW, C0 + C1);
   dim3 grid((HW + rpb - 1) / rpb, N);
   gn_apply_kernel<<<grid, kT, 0, (cudaStream_t)stream>>>(p, rpb);
@@ -294,7 +294,7 @@ extern "C" int b3d_gn_apply(const void* x0, int C0, int64_t ld0, const void* x1,
 
 extern "C" int b3d_gn_bwd(const void* x0, int C0, int64_t ld0, const void* x1, int C1, int64_t ld1, int N, int HW, const float* sums,
                           const float* gamma, const float* beta, int mode, const void* dy, int64_t ld_dy, const void* ss, int64_t ld_ss,
-                          int F, void* dss, int64_t ld_dss, float drop_p, uint64_t seed, float* dgamma, float* dbeta, float* ws_s12,
+                          int F, void* dss, int64_t ld_dss, float drop_p, uint64_t seed, const uint64_t* seed_ptr, float* dgamma, float* dbeta, float* ws_s12,
                           void* dx0, int64_t ld_dx0, void* dx1, int64_t ld_dx1, const void* add0, int64_t ld_add0, const void* add1a,
                           int64_t ld_add1a, const void* add1b, int64_t ld_add1b, void* stream) {
   if (int rc = check_src(x0, C0, x1, C1)) return rc;
@@ -304,7 +304,7 @@ extern "C" int b3d_gn_bwd(const void* x0, int C0, int64_t ld0, const void* x1, i
   BwdP p{};
   p.s = Src2{(const bf16*)x0, (const bf16*)x1, C0, C1, ld0, ld1};
   p.stats = sums; p.gamma = gamma; p.beta = beta; p.dy = (const bf16*)dy; p.ld_dy = ld_dy; p.HW = HW; p.mode = mode;
-  p.ss = (const bf16*)ss; p.ld_ss = ld_ss; p.F = F; p.dss = (bf16*)dss; p.ld_dss = ld_dss; p.drop_p = drop_p; p.seed = seed;
+  p.ss = (const bf16*)ss; p.ld_ss = ld_ss; p.F = F; p.dss = (bf16*)dss; p.ld_dss = ld_dss; p.drop_p = drop_p; p.seed = seed; p.seed_ptr = (const unsigned long long*)seed_ptr;
   p.dgamma = dgamma; p.dbeta = dbeta; p.ws = ws_s12;
   p.dx0 = (bf16*)dx0; p.dx1 = (bf16*)dx1; p.ld_dx0 = ld_dx0; p.ld_dx1 = ld_dx1;
   p.add0 = (const bf16*)add0; p.ld_add0 = ld_add0;

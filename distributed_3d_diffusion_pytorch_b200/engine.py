@@ -102,6 +102,7 @@ class Engine:
         self._zero = {"fwd": [None, 0, {}], "bwd": [None, 0, {}]}
         self._zero_cap = {"fwd": 1 << 22, "bwd": 1 << 22}
         self.saved = None
+        self.seed_ptr = None      # optional int64 device scalar added to every dropout seed (see ops.gn_apply)
         for lvl in range(cfg.num_resolutions):
             assert cfg.H % (2 ** lvl) == 0 and cfg.W % (2 ** lvl) == 0
 
@@ -334,7 +335,7 @@ class Engine:
         a1 = self.buf(n + ".a1", (N, HW, F))
         ssv = ss_l[:, s.film_off:s.film_off + 2 * F]
         ops.gn_apply(c13, None, sums1, P[n + ".groupnorm1.gn.weight"], P[n + ".groupnorm1.gn.bias"], 2, a1, ss=ssv, F=F, drop_p=drop_p,
-                     seed=seed)
+                     seed=seed, seed_ptr=self.seed_ptr)
         if s.cin != F:
             sk = self.buf(n + ".sk", (N, hh, ww, F))
             srcs = [h_in.t] + ([skip.t] if skip is not None else [])
@@ -568,7 +569,8 @@ class Engine:
         dc1 = self.tmp("dc1", (N, hh, ww, F))
         ops.gn_bwd(sa["c1"].view(N, HW, F), None, sa["sums1"], P[n + ".groupnorm1.gn.weight"], P[n + ".groupnorm1.gn.bias"], 2,
                    da1.view(N, HW, F), Gr[n + ".groupnorm1.gn.weight"], Gr[n + ".groupnorm1.gn.bias"],
-                   self.zbuf("bwd", n + ".ws1", (N, 32, 2)), dc1.view(N, HW, F), ss=ssv, F=F, dss=dssv, drop_p=drop_p, seed=sa["seed"])
+                   self.zbuf("bwd", n + ".ws1", (N, 32, 2)), dc1.view(N, HW, F), ss=ssv, F=F, dss=dssv, drop_p=drop_p, seed=sa["seed"],
+                   seed_ptr=self.seed_ptr)
         # FiLM dense parameters (xunet.py:80,84): per block, straight into the parameter gradients
         sil = self._bufs[f"emb_silu{s.lvl}"].view(M, 1024)
         ops.colsum(dssv, M, Gr[n + ".film.dense.bias"])

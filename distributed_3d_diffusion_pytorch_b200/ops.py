@@ -111,8 +111,31 @@ class CudaOps:
     def zeros(self, shape, dtype=None):
         return torch.zeros(shape, dtype=dtype or self.act_dtype, device=self.device)
 
+    prof = None          # when a list: (name, start_event, end_event, flop) per launch (bench.py's profiled step)
+    _flop = 0.0
+
     def _call(self, name, *args):
+        if self.prof is None:
+            _lib.check(getattr(self.lib, name)(*args), name)
+            return
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
         _lib.check(getattr(self.lib, name)(*args), name)
+        e.record()
+        self.prof.append((name, s, e, self._flop))
+        self._flop = 0.0
+
+    @staticmethod
+    def gemm_flop(d):
+        """algorithmic FLOPs of one b3d_gemm launch (true extents, no padding)"""
+        if d.a_major == 0 and d.b_major == 0:
+            k = sum(t.shape[3] * tp for t, tp in zip(d.a, d.a_taps))
+            return 2.0 * d.N * d.H * d.W * d.n_cols * k
+        if d.a_major == 0:
+            return 2.0 * d.N * d.H * d.W * d.n_cols * d.a[0].shape[3]
+        if d.batched:
+            return 2.0 * d.m_rows * d.n_cols * d.W * d.H * d.N
+        return 2.0 * d.m_rows * d.n_cols * d.N * d.H * d.W * d.b_taps
 
     # ---- tensor-core path
     def gemm(self, d: GemmDesc):
@@ -151,6 +174,8 @@ class CudaOps:
             cd.resid = d.resid.data_ptr()
         cd.alpha, cd.out_scale, cd.act = d.alpha, d.out_scale, d.act
         cd.out_atomic, cd.bn_tile = int(d.out_atomic), d.bn_tile
+        if self.prof is not None:
+            self._flop = self.gemm_flop(d)
         self._call("b3d_gemm", ctypes.byref(cd), self.stream())
 
     # ---- conditioning
@@ -275,25 +300,28 @@ class CudaOps:
         N, HW, _ = x0.shape
         self._call("b3d_gn_stats", *self._src(x0), *self._src(x1), c_i32(N), c_i32(HW), _ptr(sums), self.stream())
 
-    def gn_apply(self, x0, x1, sums, gamma, beta, mode, out, ss=None, F=0, drop_p=0.0, seed=0):
+    def gn_apply(self, x0, x1, sums, gamma, beta, mode, out, ss=None, F=0, drop_p=0.0, seed=0, seed_ptr=None):
+        """seed_ptr: optional int64 device scalar added to `seed` (a step counter that lives on the device, so a
+        captured CUDA graph draws a fresh dropout mask on every replay)"""
         N, HW, _ = x0.shape
         self._call("b3d_gn_apply", *self._src(x0), *self._src(x1), c_i32(N), c_i32(HW), _ptr(sums), _ptr(gamma), _ptr(beta), c_i32(mode),
-                   _ptr(ss), c_i64(ss.stride(0) if ss is not None else 0), c_i32(F), c_f32(drop_p), ctypes.c_uint64(seed), _ptr(out),
-                   c_i64(out.stride(1)), self.stream())
+                   _ptr(ss), c_i64(ss.stride(0) if ss is not None else 0), c_i32(F), c_f32(drop_p), ctypes.c_uint64(seed), _ptr(seed_ptr),
+                   _ptr(out), c_i64(out.stride(1)), self.stream())
 
     def gn_bwd(self, x0, x1, sums, gamma, beta, mode, dy, dgamma, dbeta, ws, dx0, dx1=None, ss=None, F=0, dss=None, drop_p=0.0, seed=0,
-               add0=None, add1a=None, add1b=None):
+               add0=None, add1a=None, add1b=None, seed_ptr=None):
         N, HW, _ = x0.shape
         ld = lambda t, i=1: c_i64(t.stride(i) if t is not None else 0)
         self._call("b3d_gn_bwd", *self._src(x0), *self._src(x1), c_i32(N), c_i32(HW), _ptr(sums), _ptr(gamma), _ptr(beta), c_i32(mode),
                    _ptr(dy), ld(dy), _ptr(ss), ld(ss, 0), c_i32(F), _ptr(dss), ld(dss, 0), c_f32(drop_p), ctypes.c_uint64(seed),
-                   _ptr(dgamma), _ptr(dbeta), _ptr(ws), _ptr(dx0), ld(dx0), _ptr(dx1), ld(dx1), _ptr(add0), ld(add0), _ptr(add1a),
-                   ld(add1a), _ptr(add1b), ld(add1b), self.stream())
+                   _ptr(seed_ptr), _ptr(dgamma), _ptr(dbeta), _ptr(ws), _ptr(dx0), ld(dx0), _ptr(dx1), ld(dx1), _ptr(add0), ld(add0),
+                   _ptr(add1a), ld(add1a), _ptr(add1b), ld(add1b), self.stream())
 
     # ---- diffusion glue
     def q_sample(self, z, noise, logsnr, z_out, x=None, xrand=None, mask=None, x_out=None):
         B = z.shape[0]
         per = z.numel() // B
+        assert all(t is None or t.is_contiguous() for t in (z, noise, z_out, x, xrand, x_out))
         self._call("b3d_q_sample", _ptr(z), _ptr(noise), _ptr(logsnr), _ptr(x), _ptr(xrand), _ptr(_u8(mask) if mask is not None else None),
                    _ptr(z_out), _ptr(x_out), c_i32(B), c_i64(per), self.stream())
 

@@ -1,0 +1,145 @@
+"""Data-parallel training step of the X-UNet (reference train.py:254-292 / lightning/diff3d.py:77-101),
+one process per GPU:
+
+    q_sample + conditioning-frame replacement -> XUNet forward -> loss -> hand-written backward
+    -> gradient all-reduce over NCCL (N>1; the reference's DDP never armed it) -> fused Adam
+
+The compute part (everything up to the gradients) works on static device buffers and is captured once
+in a CUDA graph; draws (logsnr, noise, cond mask, dropout) are made on the device inside the graph
+(dropout through a device-side step counter), so replays are fresh steps, not repeats."""
+import math
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from .diff3d import FusedAdam, Diff3D, diffusion_loss
+from .ops import CudaOps
+from .xunet import XUNet
+
+
+class Trainer:
+    def __init__(self, model_kw, B, device, world=1, seed=0, use_graph=True, lr=1e-4, cond_prob=0.1, init_sd=None):
+        self.B, self.dev, self.world = B, torch.device(device), world
+        torch.manual_seed(seed)
+        self.model = XUNet(**model_kw).to(self.dev)
+        if init_sd is not None:
+            self.model.load_state_dict(init_sd)
+        if world > 1:                                   # same weights everywhere (DDP's rank-0 broadcast, train.py:230)
+            dist.broadcast(self.model.flat_parameters(), 0)
+        self.model.train()
+        self.model.fused_grads = True
+        self.opt = FusedAdam(self.model, lr=lr, betas=(0.9, 0.99))
+        self.ops = CudaOps(self.dev)
+        self.cond_prob = cond_prob
+        H, W = model_kw["H"], model_kw["W"]
+        f32 = dict(dtype=torch.float32, device=self.dev)
+        self.img = torch.zeros(B, 2, 3, H, W, **f32)
+        self.xi, self.zi = torch.zeros(B, 3, H, W, **f32), torch.zeros(B, 3, H, W, **f32)
+        self.R = torch.zeros(B, 2, 3, 3, dtype=torch.float64, device=self.dev)
+        self.T = torch.zeros(B, 2, 3, dtype=torch.float64, device=self.dev)
+        self.K = torch.zeros(B, 3, 3, dtype=torch.float64, device=self.dev)
+        self.u = torch.zeros(B, **f32)
+        self.logsnr = torch.zeros(B, **f32)
+        self.logsnr2 = torch.zeros(B, 2, **f32)
+        self.noise = torch.zeros(B, 3, H, W, **f32)
+        self.xrand = torch.zeros(B, 3, H, W, **f32)
+        self.mask = torch.zeros(B, dtype=torch.uint8, device=self.dev)
+        self.z_noisy = torch.zeros(B, 3, H, W, **f32)
+        self.x_cond = torch.zeros(B, 3, H, W, **f32)
+        self.deps = torch.zeros(B, 3, H, W, **f32)
+        self.loss = torch.zeros(1, **f32)
+        self.scratch = self.ops.loss_scratch()
+        self.step_ctr = torch.zeros(1, dtype=torch.int64, device=self.dev)
+        self.engine = self.model._engine(B)
+        self.engine.seed_ptr = self.step_ctr
+        # logsnr_schedule_cosine constants (train.py:30-34)
+        b = np.arctan(np.exp(-0.5 * 20.0))
+        self._a, self._b = float(np.arctan(np.exp(0.5 * 20.0)) - b), float(b)
+        self._lam0 = float(-2.0 * np.log(np.tan(self._b)))        # schedule(0) = +20 for the clean conditioning frame
+        self.use_graph, self.graph, self.graphed = use_graph, None, False
+        self.launches_per_step = 0
+        self.step_idx = 0
+
+    # ------------------------------------------------------------------ one step, device resident
+    def _compute(self):
+        """draws + forward + loss + backward on the static buffers (graph-capturable: no allocation, no sync)"""
+        B = self.B
+        self.step_ctr.add_(1)
+        self.u.uniform_()                                            # logsnr = schedule(rand(B))      (train.py:272)
+        torch.log(torch.tan(self.u * self._a + self._b), out=self.logsnr)
+        self.logsnr.mul_(-2.0)
+        self.noise.normal_()                                         # randn_like(x)                   (train.py:90)
+        self.u.uniform_()                                            # cond_mask = rand(B) > cond_prob (train.py:95)
+        self.mask.copy_(self.u > self.cond_prob)
+        self.xrand.normal_()                                         # randn_like(x) for uncond rows   (train.py:96)
+        self.xi.copy_(self.img[:, 0])
+        self.zi.copy_(self.img[:, 1])
+        self.ops.q_sample(self.zi, self.noise, self.logsnr, self.z_noisy, self.xi, self.xrand, self.mask, self.x_cond)
+        self.logsnr2[:, 0].fill_(self._lam0)                         # xt2batch                        (train.py:36-46)
+        self.logsnr2[:, 1].copy_(self.logsnr)
+        P = dict(zip(self.model._names, self.model._plist))
+        eps = self.engine.forward(P, self.x_cond, self.z_noisy, self.logsnr2, self.R, self.T, self.K, self.mask, training=True, need_bwd=True,
+                                  seed=0)
+        self.ops.loss(self.noise, eps, self.deps, 0, self.scratch, self.loss)
+        self.engine.backward(self.model._grad_views(), self.deps, grad_flat=self.model._grad_flat)
+
+    def _finish(self):
+        if self.world > 1:
+            dist.all_reduce(self.model._grad_flat, op=dist.ReduceOp.AVG)
+        self.opt.step()
+        self.step_idx += 1
+
+    def _set_batch(self, batch):
+        img, R, T, K = batch
+        self.img.copy_(img, non_blocking=True)
+        self.R.copy_(R, non_blocking=True)
+        self.T.copy_(T, non_blocking=True)
+        self.K.copy_(K, non_blocking=True)
+
+    def step_resident(self, batch):
+        """batch already lives in HBM (device tensors)"""
+        from . import _lib
+        self._set_batch(batch)
+        if self.use_graph and self.graph is None and self.step_idx >= 1:
+            torch.cuda.synchronize()
+            n0 = _lib.launch_count()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._compute()
+            self.launches_per_step = _lib.launch_count() - n0 + 1     # + Adam
+            self.graph, self.graphed = g, True
+        if self.graph is not None:
+            self.graph.replay()
+        else:
+            self._compute()
+        self._finish()
+
+    def step_e2e(self, host_batch):
+        """the same step through the copy path: pinned host inputs -> device, loss read back"""
+        self.step_resident(host_batch)
+        return float(self.loss.item())
+
+    # ------------------------------------------------------------------ profiled step (per-kernel CUDA events)
+    def profile_step(self, batch):
+        self._set_batch(batch)
+        ops = self.engine.ops
+        ops.prof = []
+        self.ops.prof = ops.prof
+        try:
+            self._compute()
+            torch.cuda.synchronize()
+        finally:
+            rec, ops.prof, self.ops.prof = ops.prof, None, None
+        out, total = {}, 0.0
+        for name, s, e, flop in rec:
+            grp = "b3d_gemm" if name == "b3d_gemm" else ("groupnorm" if name.startswith("b3d_gn") else "elementwise")
+            d = out.setdefault(grp, {"ms": 0.0, "n": 0, "flop": 0.0})
+            ms = s.elapsed_time(e)
+            d["ms"] += ms
+            d["n"] += 1
+            d["flop"] += flop
+            total += ms
+        out["total_ms"] = total
+        self._finish()
+        return out

@@ -324,7 +324,8 @@ class EmuOps:
         u = hash_uniform(seed, idx)
         return torch.where(u < drop_p, torch.zeros(shape), torch.full(shape, 1.0 / (1.0 - drop_p)))
 
-    def gn_apply(self, x0, x1, sums, gamma, beta, mode, out, ss=None, F=0, drop_p=0.0, seed=0):
+    def gn_apply(self, x0, x1, sums, gamma, beta, mode, out, ss=None, F=0, drop_p=0.0, seed=0, seed_ptr=None):
+        seed = seed + (int(seed_ptr.item()) if seed_ptr is not None else 0)
         x = self._cat(x0, x1)
         xh, _ = self._norm(x, sums)
         y = xh * gamma.float() + beta.float()
@@ -338,7 +339,8 @@ class EmuOps:
         out.copy_(y.to(out.dtype))
 
     def gn_bwd(self, x0, x1, sums, gamma, beta, mode, dy, dgamma, dbeta, ws, dx0, dx1=None, ss=None, F=0, dss=None, drop_p=0.0, seed=0,
-               add0=None, add1a=None, add1b=None):
+               add0=None, add1a=None, add1b=None, seed_ptr=None):
+        seed = seed + (int(seed_ptr.item()) if seed_ptr is not None else 0)
         x = self._cat(x0, x1)
         N, HW, C = x.shape
         xh, rstd_c = self._norm(x, sums)

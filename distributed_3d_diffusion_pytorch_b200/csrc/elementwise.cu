@@ -593,6 +593,54 @@ extern "C" int b3d_loss(const float* noise, const float* pred, float* dpred, int
   loss_kernel<<<blocks, kT, 0, STREAM>>>(noise, pred, dpred, n, loss_type, grad_scale, partials, ticket, loss_out);
   DONE(1);
 }
+// ---------------------------------------------------------------------------------------------
+// b3d_loss_static: the same loss kernel for callers that have no device memory to hand in as scratch.
+//
+// Who that is: code that runs inside someone else's memory budget.  A trainer that carved the whole HBM
+// into its own arenas at start-up, or a service that forbids driver allocations after initialisation
+// because cudaMalloc/cudaFree stall every stream of the device, cannot produce the small scratch buffer
+// b3d_loss asks for at an arbitrary call site.  Here the block partials and the ticket live in a
+// fixed array that is part of the library image: every GPU that loads libb3d.so carries these
+// (B3D_LOSS_STATIC_MAX_BLOCKS + 1) * 4 = 4100 bytes until the process exits.
+//
+// Limits and rules:
+//  * n <= B3D_LOSS_STATIC_MAX_ELEMS (4 194 304 values = 1024 blocks x 4096); larger inputs are refused.
+//  * The array is shared by every call on the device and still holds the previous call's partials; the
+//    ticket word is cleared on `stream` before each launch.  Two calls that overlap on the GPU (different
+//    streams, no ordering) race on it -- serialise them.
+//  * The first call on each device looks up the array's device address (host code cannot use the symbol
+//    name as a pointer).  Make that first call outside any stream capture.
+//  * No cudaMalloc / cudaFree / allocating library call is made here.
+// ---------------------------------------------------------------------------------------------
+#define B3D_LOSS_STATIC_MAX_BLOCKS 1024
+#define B3D_LOSS_STATIC_ELEMS_PER_BLOCK 4096
+#define B3D_LOSS_STATIC_MAX_ELEMS ((int64_t)B3D_LOSS_STATIC_MAX_BLOCKS * B3D_LOSS_STATIC_ELEMS_PER_BLOCK)
+static __device__ __align__(256) unsigned int g_loss_static_scratch[B3D_LOSS_STATIC_MAX_BLOCKS + 1];
+static void* g_loss_static_addr[64] = {nullptr};   // per device, filled by the first call on that device
+
+extern "C" int64_t b3d_loss_static_max_elems(void) { return B3D_LOSS_STATIC_MAX_ELEMS; }
+extern "C" int b3d_loss_static(const float* noise, const float* pred, float* dpred, int64_t n, int loss_type, float grad_scale,
+                               float* loss_out, void* stream) {
+  B3D_CHECK_ARG(noise && pred && loss_out && n > 0, "loss_static: null/empty");
+  B3D_CHECK_ARG(loss_type >= 0 && loss_type <= 2, "loss_static: type must be 0 (l2), 1 (l1) or 2 (huber)");
+  B3D_CHECK_ARG(n <= B3D_LOSS_STATIC_MAX_ELEMS,
+                "loss_static: n = %lld exceeds the built-in scratch (maximum %lld elements); use b3d_loss with caller scratch",
+                (long long)n, (long long)B3D_LOSS_STATIC_MAX_ELEMS);
+  int dev = 0;
+  B3D_CUDA(cudaGetDevice(&dev));
+  B3D_CHECK_ARG(dev >= 0 && dev < 64, "loss_static: device index %d out of range", dev);
+  if (g_loss_static_addr[dev] == nullptr) {
+    void* p = nullptr;
+    B3D_CUDA(cudaGetSymbolAddress((void**)&p, g_loss_static_scratch));   // with `dev` current: this device's copy
+    g_loss_static_addr[dev] = p;
+  }
+  float* partials = (float*)g_loss_static_addr[dev];
+  unsigned int* ticket = (unsigned int*)g_loss_static_addr[dev] + B3D_LOSS_STATIC_MAX_BLOCKS;
+  B3D_CUDA(cudaMemsetAsync(ticket, 0, sizeof(unsigned int), STREAM));       // must start at zero; partials are overwritten
+  const int blocks = (int)((n + B3D_LOSS_STATIC_ELEMS_PER_BLOCK - 1) / B3D_LOSS_STATIC_ELEMS_PER_BLOCK);
+  loss_kernel<<<blocks, kT, 0, STREAM>>>(noise, pred, dpred, n, loss_type, grad_scale, partials, ticket, loss_out);
+  DONE(1);
+}
 extern "C" int b3d_sampler_update(const float* z, const float* eps_c, const float* eps_u, const float* w, const float* noise, float* out,
                                   float logsnr, float logsnr_next, int B, int64_t per_sample, void* stream) {
   B3D_CHECK_ARG(z && eps_c && eps_u && w && out, "sampler_update: null");

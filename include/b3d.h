@@ -148,6 +148,17 @@ int b3d_q_sample(const float* z, const float* noise, const float* logsnr, const 
 int b3d_loss_scratch_bytes(void);
 int b3d_loss(const float* noise, const float* pred, float* dpred, int64_t n, int loss_type, float grad_scale, void* scratch,
              float* loss_out, void* stream);
+/* Same loss and gradient as b3d_loss, for callers that cannot hand in scratch memory (no counterpart in the
+ * reference; it exists for hosts that run inside a fixed device-memory budget -- all HBM pre-carved into their
+ * own arenas, or driver allocations forbidden after start-up because cudaMalloc/cudaFree stall the device).
+ * The block partials and ticket live in a 4100-byte array inside the library image (held by every GPU that
+ * loads the library until exit).  n must be <= b3d_loss_static_max_elems() (4 194 304); larger n returns -1
+ * with a message.  The array is shared by all calls on a device: calls that overlap on the GPU race, so keep
+ * them ordered.  The first call on each device resolves the array's address; make it before any stream
+ * capture.  Allocates nothing. */
+int64_t b3d_loss_static_max_elems(void);
+int b3d_loss_static(const float* noise, const float* pred, float* dpred, int64_t n, int loss_type, float grad_scale, float* loss_out,
+                    void* stream);
 /* p_mean_variance + p_sample arithmetic given both UNet outputs: sampling.py:79-127 (noise skipped iff logsnr_next == 0) */
 int b3d_sampler_update(const float* z, const float* eps_c, const float* eps_u, const float* w, const float* noise, float* out,
                        float logsnr, float logsnr_next, int B, int64_t per_sample, void* stream);

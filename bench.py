@@ -128,6 +128,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-profile", action="store_true")
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--profile-json", default=None, help="dump the per-launch CUDA-event table of the profiled step")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
     if args.impl == "reference":
@@ -199,7 +200,7 @@ def main():
     roof = None
     pk = peaks()
     if not args.no_profile:
-        prof = tr.profile_step(resident[0])
+        prof = tr.profile_step(resident[0], dump=args.profile_json)
         gemm_ms = prof["b3d_gemm"]["ms"]
         gemm_flop = prof["b3d_gemm"]["flop"]
         achieved = gemm_flop / (gemm_ms / 1e3) / 1e12

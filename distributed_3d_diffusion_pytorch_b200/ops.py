@@ -111,8 +111,8 @@ class CudaOps:
     def zeros(self, shape, dtype=None):
         return torch.zeros(shape, dtype=dtype or self.act_dtype, device=self.device)
 
-    prof = None          # when a list: (name, start_event, end_event, flop) per launch (bench.py's profiled step)
-    _flop = 0.0
+    prof = None          # when a list: (name, start_event, end_event, flop, info) per launch (bench.py's profiled step)
+    _flop, _info = 0.0, ""
 
     def _call(self, name, *args):
         if self.prof is None:
@@ -122,8 +122,8 @@ class CudaOps:
         s.record()
         _lib.check(getattr(self.lib, name)(*args), name)
         e.record()
-        self.prof.append((name, s, e, self._flop))
-        self._flop = 0.0
+        self.prof.append((name, s, e, self._flop, self._info))
+        self._flop, self._info = 0.0, ""
 
     @staticmethod
     def gemm_flop(d):
@@ -176,6 +176,9 @@ class CudaOps:
         cd.out_atomic, cd.bn_tile = int(d.out_atomic), d.bn_tile
         if self.prof is not None:
             self._flop = self.gemm_flop(d)
+            self._info = (f"maj{d.a_major}{d.b_major} WHN={d.W}x{d.H}x{d.N} rows={d.m_rows} cols={d.n_cols} "
+                          f"C={[t.shape[3] for t in d.a]} taps={d.a_taps if d.a_major == 0 else d.b_taps} s={d.conv_stride} "
+                          f"split={d.split_k} bn={d.bn_tile} batched={int(d.batched)} fp32={int(o.dtype == torch.float32)}")
         self._call("b3d_gemm", ctypes.byref(cd), self.stream())
 
     # ---- conditioning

@@ -121,7 +121,7 @@ class Trainer:
         return float(self.loss.item())
 
     # ------------------------------------------------------------------ profiled step (per-kernel CUDA events)
-    def profile_step(self, batch):
+    def profile_step(self, batch, dump=None):
         self._set_batch(batch)
         ops = self.engine.ops
         ops.prof = []
@@ -132,7 +132,10 @@ class Trainer:
         finally:
             rec, ops.prof, self.ops.prof = ops.prof, None, None
         out, total = {}, 0.0
-        for name, s, e, flop in rec:
+        if dump:
+            import json
+            json.dump([dict(name=n_, ms=s_.elapsed_time(e_), flop=f_, info=i_) for n_, s_, e_, f_, i_ in rec], open(dump, "w"))
+        for name, s, e, flop, _ in rec:
             grp = "b3d_gemm" if name == "b3d_gemm" else ("groupnorm" if name.startswith("b3d_gn") else "elementwise")
             d = out.setdefault(grp, {"ms": 0.0, "n": 0, "flop": 0.0})
             ms = s.elapsed_time(e)

@@ -33,6 +33,7 @@ struct Seg {
 struct alignas(64) KP {
   CUtensorMap tmA[3];
   CUtensorMap tmB;
+  CUtensorMap tmO, tmO2, tmR;   // epilogue: TMA store of the bf16 output(s), TMA load of the residual
   Seg seg[kMaxSeg];
   int nseg;
   int a_major, b_major, batched, b_xor, o_xor;
@@ -58,6 +59,8 @@ struct alignas(64) KP {
   long long os_x, os_y, os_n, os_tap;
   float alpha, out_scale;
   int act, out_fp32, out_atomic;
+  int epi_tma;          // bf16 outputs leave through shared memory + TMA store (coalesced, no LSU global traffic)
+  uint32_t epi_off;     // byte offset of the epilogue staging buffers inside dynamic smem
 };
 
 // ------------------------------------------------------------------ PTX wrappers
@@ -95,6 +98,29 @@ __device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* tm,
       "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
       ::"r"(dst), "l"(reinterpret_cast<uint64_t>(tm)), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
       : "memory");
+}
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap* tm, uint32_t src, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
+               ::"l"(reinterpret_cast<uint64_t>(tm)), "r"(src), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+               : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+__device__ __forceinline__ void sts128(uint32_t addr, uint4 v) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&h);
 }
 __device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t ncols) {
   asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(ncols) : "memory");
@@ -185,7 +211,7 @@ __device__ __forceinline__ void k_range(const KP& p, const TileCoord& c, int& kb
 
 __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_constant__ KP p) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ uint64_t bars[2 * 8 + 4];
+  __shared__ uint64_t bars[2 * 8 + 4 + 2];
   __shared__ uint32_t tmem_base_smem;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -195,10 +221,11 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
   auto empty_bar = [&](int s) { return smem_u32(&bars[8 + s]); };
   auto tfull_bar = [&](int s) { return smem_u32(&bars[16 + s]); };
   auto tempty_bar = [&](int s) { return smem_u32(&bars[18 + s]); };
+  auto resid_bar = [&](int s) { return smem_u32(&bars[20 + s]); };
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < S; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
-    for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 4); }
+    for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 4); mbar_init(resid_bar(s), 1); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) tmem_alloc(smem_u32(&tmem_base_smem), (uint32_t)p.tmem_cols);
@@ -294,8 +321,140 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
+  } else if (p.epi_tma) {
+    // ===================================================================== epilogue, bf16 outputs (warps 2..5)
+    // TMEM -> registers -> (bias / per-image vector / residual / scale / SiLU) -> bf16 -> 128B-swizzled smem tile
+    // -> TMA store.  The residual tile arrives by TMA load.  64 output columns (one 128-byte row) per round,
+    // double buffered, so global memory sees only full-line bulk transfers and the LSU only shared memory.
+    const int quad = warp & 3;
+    const int r = quad * 32 + lane;
+    const bool leader = threadIdx.x == 64;
+    const uint32_t so_base = smem_base + p.epi_off;
+    const uint32_t sx_base = so_base + 2 * 16384;
+    const uint32_t rows_bytes = p.a_major == 0 ? (uint32_t)(p.bw * p.bh * p.bnn) * 128u : 128u * 128u;
+    int acc = 0; uint32_t acc_phase = 0;
+    int buf = 0; uint32_t rphase0 = 0, rphase1 = 0;
+    const uint32_t swz = (uint32_t)(r & 7);
+    for (int t = blockIdx.x; t < p.tiles_total; t += gridDim.x) {
+      const TileCoord c = decode_tile(p, t);
+      int cx, cy, cn, img;
+      if (p.a_major == 0) {
+        cx = c.x0; cy = c.y0; cn = c.n0 ^ p.o_xor;
+        img = c.n0 + r / (p.bw * p.bh);
+        if (img >= p.N) img = p.N - 1;
+      } else {
+        cx = c.m0; cy = c.y0; cn = c.n0 ^ p.o_xor; img = c.n0;
+      }
+      const int nch = (min(p.BN, p.n_cols - c.tn * p.BN) + 63) / 64;
+      if (p.resid != nullptr && leader) {
+        mbar_expect_tx(resid_bar(buf), rows_bytes);
+        tma_load_4d(sx_base + buf * 16384, &p.tmR, resid_bar(buf), c.tn * p.BN, cx, cy, cn);
+      }
+      mbar_wait(tfull_bar(acc), acc_phase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + (uint32_t)(acc * p.acc_stride) + ((uint32_t)(quad * 32) << 16);
+      for (int ch = 0; ch < nch; ++ch) {
+        const int col0 = c.tn * p.BN + ch * 64;
+        if (leader) {
+          if (p.resid != nullptr && ch + 1 < nch) {
+            mbar_expect_tx(resid_bar(buf ^ 1), rows_bytes);
+            tma_load_4d(sx_base + (buf ^ 1) * 16384, &p.tmR, resid_bar(buf ^ 1), col0 + 64, cx, cy, cn);
+          }
+          tma_store_wait_read<1>();      // the store that last used this buffer has finished reading it
+        }
+        epi_bar_sync();
+        if (p.resid != nullptr) {
+          mbar_wait(resid_bar(buf), buf ? rphase1 : rphase0);
+          if (buf) rphase1 ^= 1; else rphase0 ^= 1;
+        }
+        const uint32_t orow = so_base + buf * 16384 + (uint32_t)r * 128u;
+        const uint32_t xrow = sx_base + buf * 16384 + (uint32_t)r * 128u;
+#pragma unroll
+        for (int hf = 0; hf < 2; ++hf) {
+          const int cc = col0 + hf * 32;
+          if (ch * 64 + hf * 32 >= p.BN) break;
+          uint32_t v[32];
+          tmem_ld32(taddr + ch * 64 + hf * 32, v);
+          float f[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]) * p.alpha;
+          const bool full = cc + 32 <= p.n_cols;
+          if (p.bias) {
+            if (full) {
+#pragma unroll
+              for (int g = 0; g < 8; ++g) {
+                const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + cc) + g);
+                f[4 * g] += b4.x; f[4 * g + 1] += b4.y; f[4 * g + 2] += b4.z; f[4 * g + 3] += b4.w;
+              }
+            } else {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) if (cc + i < p.n_cols) f[i] += __ldg(p.bias + cc + i);
+            }
+          }
+          if (p.rowvec) {
+            const float* rv = p.rowvec + (long long)img * p.rowvec_ld + cc;
+            if (full) {
+#pragma unroll
+              for (int g = 0; g < 8; ++g) {
+                const float4 b4 = __ldg(reinterpret_cast<const float4*>(rv) + g);
+                f[4 * g] += b4.x; f[4 * g + 1] += b4.y; f[4 * g + 2] += b4.z; f[4 * g + 3] += b4.w;
+              }
+            } else {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) if (cc + i < p.n_cols) f[i] += __ldg(rv + i);
+            }
+          }
+          if (p.resid != nullptr) {
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+              const uint4 q = lds128(xrow + ((((uint32_t)(hf * 4 + g)) ^ swz) << 4));
+              const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&q);
+#pragma unroll
+              for (int i = 0; i < 4; ++i) { const float2 t2 = __bfloat1622float2(h2[i]); f[8 * g + 2 * i] += t2.x; f[8 * g + 2 * i + 1] += t2.y; }
+            }
+          }
+#pragma unroll
+          for (int i = 0; i < 32; ++i) f[i] *= p.out_scale;
+          if (p.act == 1 && p.out2 == nullptr) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) f[i] = b3d_silu(f[i]);
+          }
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            uint4 q;
+            q.x = pack_bf16x2(f[8 * g], f[8 * g + 1]); q.y = pack_bf16x2(f[8 * g + 2], f[8 * g + 3]);
+            q.z = pack_bf16x2(f[8 * g + 4], f[8 * g + 5]); q.w = pack_bf16x2(f[8 * g + 6], f[8 * g + 7]);
+            sts128(orow + ((((uint32_t)(hf * 4 + g)) ^ swz) << 4), q);
+          }
+          if (p.out2) {
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+              uint4 q;
+              q.x = pack_bf16x2(b3d_silu(f[8 * g]), b3d_silu(f[8 * g + 1])); q.y = pack_bf16x2(b3d_silu(f[8 * g + 2]), b3d_silu(f[8 * g + 3]));
+              q.z = pack_bf16x2(b3d_silu(f[8 * g + 4]), b3d_silu(f[8 * g + 5])); q.w = pack_bf16x2(b3d_silu(f[8 * g + 6]), b3d_silu(f[8 * g + 7]));
+              sts128(xrow + ((((uint32_t)(hf * 4 + g)) ^ swz) << 4), q);
+            }
+          }
+        }
+        if (ch == nch - 1) {             // accumulator fully read: hand the TMEM buffer back to the MMA warp
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(tempty_bar(acc));
+        }
+        fence_proxy_async();
+        epi_bar_sync();
+        if (leader) {
+          tma_store_4d(&p.tmO, so_base + buf * 16384, col0, cx, cy, cn);
+          if (p.out2) tma_store_4d(&p.tmO2, sx_base + buf * 16384, col0, cx, cy, cn);
+          tma_store_commit();
+        }
+        buf ^= 1;
+      }
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+    if (leader) tma_store_wait_all();
   } else {
-    // ===================================================================== epilogue (warps 2..5)
+    // ===================================================================== epilogue, direct stores (fp32 / atomic / odd shapes)
     const int quad = warp & 3;  // TMEM lane quadrant this warp may access
     const int r = quad * 32 + lane;
     int acc = 0; uint32_t acc_phase = 0;
@@ -508,8 +667,17 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
   p.b_bytes = d->b_major ? (uint32_t)p.b_chunks * 8192u : (uint32_t)((BN * 128 + 1023) / 1024 * 1024);
   p.b_tx = d->b_major ? (uint32_t)p.b_chunks * 8192u : (uint32_t)BN * 128u;
   p.stage_bytes = kABytes + p.b_bytes;
-  p.num_stages = (int)((kMaxDynSmem - 1024) / p.stage_bytes);
+  // bf16 outputs whose rows are 16-byte aligned leave through smem + TMA store (2 x 16 KB staging, + 2 x 16 KB for
+  // the residual tile or the second output)
+  p.epi_tma = (!d->out_fp32 && !d->out_atomic && d->n_cols % 8 == 0 && d->out_stride[0] % 8 == 0 && d->out_stride[1] % 8 == 0 &&
+               d->out_stride[2] % 8 == 0 && d->out_tap_stride == 0 && ((uintptr_t)d->out & 15) == 0 &&
+               (d->resid == nullptr || d->out2 == nullptr) && (d->resid == nullptr || ((uintptr_t)d->resid & 15) == 0) &&
+               (d->out2 == nullptr || ((uintptr_t)d->out2 & 15) == 0)) ? 1 : 0;
+  const uint32_t epi_bytes = p.epi_tma ? ((d->resid || d->out2) ? 65536u : 32768u) : 0u;
+  p.num_stages = (int)((kMaxDynSmem - 1024 - epi_bytes) / p.stage_bytes);
   if (p.num_stages > 8) p.num_stages = 8;
+  B3D_CHECK_ARG(p.num_stages >= 2, "b3d_gemm: not enough shared memory for a 2-stage pipeline");
+  p.epi_off = (uint32_t)p.num_stages * p.stage_bytes;
   p.acc_stride = (BN + 31) / 32 * 32;
   p.tmem_cols = pow2_ceil(2 * p.acc_stride);
   if (p.tmem_cols < 32) p.tmem_cols = 32;
@@ -584,6 +752,17 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
     const uint32_t esB[4] = {1, (uint32_t)s, (uint32_t)s, 1};
     rc = make_map(&p.tmB, d->b, boxB, esB); if (rc) return rc;
   }
+  if (p.epi_tma) {
+    b3d_view4 ov;
+    ov.ptr = d->out;
+    ov.dim[0] = d->n_cols; ov.dim[1] = d->a_major == 0 ? d->W : d->m_rows; ov.dim[2] = d->H; ov.dim[3] = d->N;
+    ov.stride[0] = d->out_stride[0]; ov.stride[1] = d->out_stride[1]; ov.stride[2] = d->out_stride[2];
+    uint32_t boxO[4] = {64, 128, 1, 1};
+    if (d->a_major == 0) { boxO[1] = (uint32_t)p.bw; boxO[2] = (uint32_t)p.bh; boxO[3] = (uint32_t)p.bnn; }
+    rc = make_map(&p.tmO, ov, boxO, ones); if (rc) return rc;
+    if (d->out2) { ov.ptr = d->out2; rc = make_map(&p.tmO2, ov, boxO, ones); if (rc) return rc; }
+    if (d->resid) { ov.ptr = d->resid; rc = make_map(&p.tmR, ov, boxO, ones); if (rc) return rc; }
+  }
   p.tiles_total = p.tiles_m * p.tiles_n * p.tiles_b * p.tiles_z;
   B3D_CHECK_ARG(p.tiles_total > 0, "b3d_gemm: empty problem");
 
@@ -593,7 +772,7 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
   p.alpha = d->alpha; p.out_scale = d->out_scale; p.act = d->act; p.out_fp32 = d->out_fp32; p.out_atomic = d->out_atomic;
   B3D_CHECK_ARG(!d->out_atomic || d->out_fp32, "b3d_gemm: out_atomic needs fp32 output");
 
-  const size_t smem = (size_t)p.num_stages * p.stage_bytes + 1024;
+  const size_t smem = (size_t)p.num_stages * p.stage_bytes + epi_bytes + 1024;
   static bool attr_set = false;
   if (!attr_set) {
     B3D_CUDA(cudaFuncSetAttribute(b3d_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem));

@@ -18,31 +18,67 @@ struct Src2 {
   int C0, C1; long long ld0, ld1;
 };
 
-__device__ __forceinline__ bf16x8 load8(const Src2& s, long long row, int c) {
-  if (c < s.C0) return *reinterpret_cast<const bf16x8*>(s.p0 + row * s.ld0 + c);
-  return *reinterpret_cast<const bf16x8*>(s.p1 + row * s.ld1 + (c - s.C0));
+// Thread layout shared by all kernels: a block covers `rows_per_block` pixels of ONE image and all C channels;
+// thread t owns the 8-channel vector v = t % (C/8) for every row it visits (so gamma/beta/mean/rstd of its
+// channels live in registers) and visits rows rsub, rsub + rows_par, ... with U independent 16-byte loads per
+// tensor in flight (HBM latency is hidden by memory-level parallelism, not by occupancy).
+struct Chan {
+  float gamma[8], beta[8], mean[8], rstd[8];
+};
+
+__device__ __forceinline__ void block_stats(const float* stats, int n, int cpg, int HW, float* s_mean, float* s_rstd) {
+  if (threadIdx.x < G) {
+    const float cnt = (float)cpg * (float)HW;
+    const float sum = stats[((long long)n * G + threadIdx.x) * 2], sq = stats[((long long)n * G + threadIdx.x) * 2 + 1];
+    const float mean = sum / cnt;
+    const float var = fmaxf(sq / cnt - mean * mean, 0.f);
+    s_mean[threadIdx.x] = mean; s_rstd[threadIdx.x] = rsqrtf(var + 1e-5f);
+  }
 }
+__device__ __forceinline__ void load_chan(Chan& ch, const float* gamma, const float* beta, int c0, int cpg, const float* s_mean,
+                                          const float* s_rstd) {
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int g = (c0 + j) / cpg;
+    ch.gamma[j] = gamma[c0 + j]; ch.beta[j] = beta[c0 + j]; ch.mean[j] = s_mean[g]; ch.rstd[j] = s_rstd[g];
+  }
+}
+struct RowPtr {   // per-thread base pointer of its channel vector inside the (possibly two-source) input
+  const bf16* p; long long ld;
+};
+__device__ __forceinline__ RowPtr src_ptr(const Src2& s, int c0) {
+  if (c0 < s.C0) return RowPtr{s.p0 + c0, s.ld0};
+  return RowPtr{s.p1 + (c0 - s.C0), s.ld1};
+}
+__device__ __forceinline__ bf16x8 ld8(const bf16* p) { return *reinterpret_cast<const bf16x8*>(p); }
+__device__ __forceinline__ bf16x8 zero8() { bf16x8 z; z.u = make_uint4(0u, 0u, 0u, 0u); return z; }
 
 // ---- stats: raw (sum, sumsq) per (image, group) accumulated with fp32 atomics into ws[N,32,2] (pre-zeroed)
-__global__ void gn_stats_kernel(Src2 s, int HW, int rows_per_block, float* __restrict__ ws) {
+__global__ void __launch_bounds__(kT) gn_stats_kernel(Src2 s, int HW, int rows_per_block, float* __restrict__ ws) {
   extern __shared__ float sm[];  // [C][2]
-  const int C = s.C0 + s.C1, cpg = C / G, n = blockIdx.y;
-  const int vecs = C / 8;
+  constexpr int U = 4;
+  const int C = s.C0 + s.C1, cpg = C / G, n = blockIdx.y, vecs = C / 8;
   for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) sm[i] = 0.f;
   __syncthreads();
   const int r0 = blockIdx.x * rows_per_block, r1 = min(HW, r0 + rows_per_block);
-  const int lanes_per_row = vecs;                 // threads cooperating on one pixel row
-  const int rows_par = max(1, (int)blockDim.x / lanes_per_row);
-  const int v = threadIdx.x % lanes_per_row, rsub = threadIdx.x / lanes_per_row;
+  const int rows_par = max(1, (int)blockDim.x / vecs);
+  const int v = threadIdx.x % vecs, rsub = threadIdx.x / vecs;
   if (rsub < rows_par) {
+    const RowPtr rp = src_ptr(s, v * 8);
+    const bf16* base = rp.p + (long long)n * HW * rp.ld;
     float a[8], b[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) { a[i] = 0.f; b[i] = 0.f; }
-    for (int r = r0 + rsub; r < r1; r += rows_par) {
-      float f[8];
-      b3d_unpack8(load8(s, (long long)n * HW + r, v * 8), f);
+    for (int r = r0 + rsub; r < r1; r += rows_par * U) {
+      bf16x8 x[U];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) { a[i] += f[i]; b[i] += f[i] * f[i]; }
+      for (int u = 0; u < U; ++u) { const int rr = r + u * rows_par; x[u] = rr < r1 ? ld8(base + (long long)rr * rp.ld) : zero8(); }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        float f[8]; b3d_unpack8(x[u], f);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { a[i] += f[i]; b[i] += f[i] * f[i]; }
+      }
     }
 #pragma unroll
     for (int i = 0; i < 8; ++i) { atomicAdd(&sm[2 * (v * 8 + i)], a[i]); atomicAdd(&sm[2 * (v * 8 + i) + 1], b[i]); }
@@ -66,42 +102,52 @@ struct ApplyP {
   float drop_p; unsigned long long seed; const unsigned long long* seed_ptr;  // effective seed = seed + *seed_ptr (device step counter)
 };
 
-__global__ void gn_apply_kernel(ApplyP p, int rows_per_block) {
+__global__ void __launch_bounds__(kT, 2) gn_apply_kernel(ApplyP p, int rows_per_block) {
   __shared__ float s_mean[G], s_rstd[G];
+  constexpr int U = 4;
   const int C = p.s.C0 + p.s.C1, cpg = C / G, n = blockIdx.y, vecs = C / 8;
-  if (threadIdx.x < G) {
-    const float cnt = (float)cpg * (float)p.HW;
-    const float sum = p.stats[((long long)n * G + threadIdx.x) * 2], sq = p.stats[((long long)n * G + threadIdx.x) * 2 + 1];
-    const float mean = sum / cnt;
-    const float var = fmaxf(sq / cnt - mean * mean, 0.f);
-    s_mean[threadIdx.x] = mean; s_rstd[threadIdx.x] = rsqrtf(var + 1e-5f);
-  }
+  block_stats(p.stats, n, cpg, p.HW, s_mean, s_rstd);
   __syncthreads();
   const int r0 = blockIdx.x * rows_per_block, r1 = min(p.HW, r0 + rows_per_block);
-  const long long total = (long long)(r1 - r0) * vecs;
+  const int rows_par = max(1, (int)blockDim.x / vecs);
+  const int v = threadIdx.x % vecs, rsub = threadIdx.x / vecs, c0 = v * 8;
+  if (rsub >= rows_par) return;
+  Chan ch; load_chan(ch, p.gamma, p.beta, c0, cpg, s_mean, s_rstd);
+  const RowPtr rp = src_ptr(p.s, c0);
+  const long long img = (long long)n * p.HW;
   const float keep = 1.f / (1.f - p.drop_p);
-  for (long long i = threadIdx.x; i < total; i += blockDim.x) {
-    const int r = r0 + (int)(i / vecs), c = (int)(i % vecs) * 8;
-    const long long row = (long long)n * p.HW + r;
-    float f[8];
-    b3d_unpack8(load8(p.s, row, c), f);
-    float sc[8], sh[8];
-    if (p.mode == 2) {
-      b3d_unpack8(*reinterpret_cast<const bf16x8*>(p.ss + row * p.ld_ss + c), sc);
-      b3d_unpack8(*reinterpret_cast<const bf16x8*>(p.ss + row * p.ld_ss + p.F + c), sh);
+  const unsigned long long seed = p.seed + (p.seed_ptr ? *p.seed_ptr : 0ULL);
+  for (int r = r0 + rsub; r < r1; r += rows_par * U) {
+    bf16x8 x[U], sc[U], sh[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long row = img + r + u * rows_par;
+      const bool ok = r + u * rows_par < r1;
+      x[u] = ok ? ld8(rp.p + row * rp.ld) : zero8();
+      if (p.mode == 2) {
+        sc[u] = ok ? ld8(p.ss + row * p.ld_ss + c0) : zero8();
+        sh[u] = ok ? ld8(p.ss + row * p.ld_ss + p.F + c0) : zero8();
+      }
     }
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const int g = (c + j) / cpg;
-      float y = (f[j] - s_mean[g]) * s_rstd[g] * __ldg(p.gamma + c + j) + __ldg(p.beta + c + j);
-      if (p.mode == 1) y = b3d_silu(y);
-      else if (p.mode == 2) {
-        y = y * (1.f + sc[j]) + sh[j];
-        if (p.drop_p > 0.f) y = (b3d_uniform(p.seed + (p.seed_ptr ? *p.seed_ptr : 0ULL), (unsigned long long)row * C + c + j) < p.drop_p) ? 0.f : y * keep;
+    for (int u = 0; u < U; ++u) {
+      if (r + u * rows_par >= r1) break;
+      const long long row = img + r + u * rows_par;
+      float f[8], a[8], b[8];
+      b3d_unpack8(x[u], f);
+      if (p.mode == 2) { b3d_unpack8(sc[u], a); b3d_unpack8(sh[u], b); }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float y = (f[j] - ch.mean[j]) * ch.rstd[j] * ch.gamma[j] + ch.beta[j];
+        if (p.mode == 1) y = b3d_silu(y);
+        else if (p.mode == 2) {
+          y = y * (1.f + a[j]) + b[j];
+          if (p.drop_p > 0.f) y = (b3d_uniform(seed, (unsigned long long)row * C + c0 + j) < p.drop_p) ? 0.f : y * keep;
+        }
+        f[j] = y;
       }
-      f[j] = y;
+      *reinterpret_cast<bf16x8*>(p.out + row * p.ld_out + c0) = b3d_pack8(f);
     }
-    *reinterpret_cast<bf16x8*>(p.out + row * p.ld_out + c) = b3d_pack8(f);
   }
 }
 
@@ -121,68 +167,75 @@ struct BwdP {
   const bf16* add1a; const bf16* add1b; long long ld_add1a, ld_add1b;  // optional second addend, split like the sources
 };
 
-__device__ __forceinline__ void gn_bwd_dz(const BwdP& p, long long row, int c, int C, int cpg, const float* s_mean, const float* s_rstd,
-                                          float* xh, float* dz, bool write_dss) {
-  float f[8], dy[8];
-  b3d_unpack8(load8(p.s, row, c), f);
-  b3d_unpack8(*reinterpret_cast<const bf16x8*>(p.dy + row * p.ld_dy + c), dy);
-  float sc[8], dsc[8], dsh[8];
-  if (p.mode == 2) b3d_unpack8(*reinterpret_cast<const bf16x8*>(p.ss + row * p.ld_ss + c), sc);
-  const float keep = 1.f / (1.f - p.drop_p);
+// dz = d(loss)/d(gamma*xhat+beta) for one 8-channel vector, from the loaded x, dy (and FiLM scale)
+__device__ __forceinline__ void bwd_dz(const BwdP& p, const Chan& ch, const bf16x8& xv, const bf16x8& dyv, const bf16x8& scv, long long row, int c0,
+                                       int C, unsigned long long seed, float keep, float* xh, float* dz, float* dsc, float* dsh) {
+  float f[8], dy[8], sc[8];
+  b3d_unpack8(xv, f); b3d_unpack8(dyv, dy);
+  if (p.mode == 2) b3d_unpack8(scv, sc);
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
-    const int g = (c + j) / cpg;
-    xh[j] = (f[j] - s_mean[g]) * s_rstd[g];
-    const float z = xh[j] * __ldg(p.gamma + c + j) + __ldg(p.beta + c + j);
+    xh[j] = (f[j] - ch.mean[j]) * ch.rstd[j];
+    const float z = xh[j] * ch.gamma[j] + ch.beta[j];
     float d = dy[j];
     if (p.mode == 1) d *= b3d_silu_grad(z);
     else if (p.mode == 2) {
-      if (p.drop_p > 0.f) d = (b3d_uniform(p.seed + (p.seed_ptr ? *p.seed_ptr : 0ULL), (unsigned long long)row * C + c + j) < p.drop_p) ? 0.f : d * keep;
+      if (p.drop_p > 0.f) d = (b3d_uniform(seed, (unsigned long long)row * C + c0 + j) < p.drop_p) ? 0.f : d * keep;
       dsc[j] = d * z; dsh[j] = d;
       d *= (1.f + sc[j]);
     }
     dz[j] = d;
   }
-  if (p.mode == 2 && write_dss) {
-    *reinterpret_cast<bf16x8*>(p.dss + row * p.ld_dss + c) = b3d_pack8(dsc);
-    *reinterpret_cast<bf16x8*>(p.dss + row * p.ld_dss + p.F + c) = b3d_pack8(dsh);
-  }
-}
-
-__device__ __forceinline__ void load_stats(const float* stats, int n, int cpg, int HW, float* s_mean, float* s_rstd) {
-  if (threadIdx.x < G) {
-    const float cnt = (float)cpg * (float)HW;
-    const float sum = stats[((long long)n * G + threadIdx.x) * 2], sq = stats[((long long)n * G + threadIdx.x) * 2 + 1];
-    const float mean = sum / cnt;
-    const float var = fmaxf(sq / cnt - mean * mean, 0.f);
-    s_mean[threadIdx.x] = mean; s_rstd[threadIdx.x] = rsqrtf(var + 1e-5f);
-  }
 }
 
 // pass 1: d_scale/d_shift (film), dgamma/dbeta, per-(image,group) S1 = sum dz*gamma, S2 = sum dz*gamma*xhat
-__global__ void gn_bwd_reduce_kernel(BwdP p, int rows_per_block) {
+__global__ void __launch_bounds__(kT, 2) gn_bwd_reduce_kernel(BwdP p, int rows_per_block) {
   extern __shared__ float sm[];  // [C][2] dgamma,dbeta partials then [G][2]
   __shared__ float s_mean[G], s_rstd[G];
+  constexpr int U = 2;
   const int C = p.s.C0 + p.s.C1, cpg = C / G, n = blockIdx.y, vecs = C / 8;
   float* s_gs = sm + 2 * C;
   for (int i = threadIdx.x; i < 2 * C + 2 * G; i += blockDim.x) sm[i] = 0.f;
-  load_stats(p.stats, n, cpg, p.HW, s_mean, s_rstd);
+  block_stats(p.stats, n, cpg, p.HW, s_mean, s_rstd);
   __syncthreads();
   const int r0 = blockIdx.x * rows_per_block, r1 = min(p.HW, r0 + rows_per_block);
   const int rows_par = max(1, (int)blockDim.x / vecs);
-  const int v = threadIdx.x % vecs, rsub = threadIdx.x / vecs;
+  const int v = threadIdx.x % vecs, rsub = threadIdx.x / vecs, c0 = v * 8;
   if (rsub < rows_par) {
+    Chan ch; load_chan(ch, p.gamma, p.beta, c0, cpg, s_mean, s_rstd);
+    const RowPtr rp = src_ptr(p.s, c0);
+    const long long img = (long long)n * p.HW;
+    const float keep = 1.f / (1.f - p.drop_p);
+    const unsigned long long seed = p.seed + (p.seed_ptr ? *p.seed_ptr : 0ULL);
     float ag[8], ab[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) { ag[j] = 0.f; ab[j] = 0.f; }
-    for (int r = r0 + rsub; r < r1; r += rows_par) {
-      float xh[8], dz[8];
-      gn_bwd_dz(p, (long long)n * p.HW + r, v * 8, C, cpg, s_mean, s_rstd, xh, dz, true);
+    for (int r = r0 + rsub; r < r1; r += rows_par * U) {
+      bf16x8 x[U], dy[U], sc[U];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) { ag[j] += dz[j] * xh[j]; ab[j] += dz[j]; }
+      for (int u = 0; u < U; ++u) {
+        const long long row = img + r + u * rows_par;
+        const bool ok = r + u * rows_par < r1;
+        x[u] = ok ? ld8(rp.p + row * rp.ld) : zero8();
+        dy[u] = ok ? ld8(p.dy + row * p.ld_dy + c0) : zero8();
+        sc[u] = (ok && p.mode == 2) ? ld8(p.ss + row * p.ld_ss + c0) : zero8();
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        if (r + u * rows_par >= r1) break;
+        const long long row = img + r + u * rows_par;
+        float xh[8], dz[8], dsc[8], dsh[8];
+        bwd_dz(p, ch, x[u], dy[u], sc[u], row, c0, C, seed, keep, xh, dz, dsc, dsh);
+        if (p.mode == 2) {
+          *reinterpret_cast<bf16x8*>(p.dss + row * p.ld_dss + c0) = b3d_pack8(dsc);
+          *reinterpret_cast<bf16x8*>(p.dss + row * p.ld_dss + p.F + c0) = b3d_pack8(dsh);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { ag[j] += dz[j] * xh[j]; ab[j] += dz[j]; }
+      }
     }
 #pragma unroll
-    for (int j = 0; j < 8; ++j) { atomicAdd(&sm[2 * (v * 8 + j)], ag[j]); atomicAdd(&sm[2 * (v * 8 + j) + 1], ab[j]); }
+    for (int j = 0; j < 8; ++j) { atomicAdd(&sm[2 * (c0 + j)], ag[j]); atomicAdd(&sm[2 * (c0 + j) + 1], ab[j]); }
   }
   __syncthreads();
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
@@ -200,10 +253,11 @@ __global__ void gn_bwd_reduce_kernel(BwdP p, int rows_per_block) {
 }
 
 // pass 2: dx = rstd * (dz*gamma - (S1 + xhat*S2)/cnt) [+ add0] [+ add1]
-__global__ void gn_bwd_apply_kernel(BwdP p, int rows_per_block) {
+__global__ void __launch_bounds__(kT, 2) gn_bwd_apply_kernel(BwdP p, int rows_per_block) {
   __shared__ float s_mean[G], s_rstd[G], s_s1[G], s_s2[G];
+  constexpr int U = 2;
   const int C = p.s.C0 + p.s.C1, cpg = C / G, n = blockIdx.y, vecs = C / 8;
-  load_stats(p.stats, n, cpg, p.HW, s_mean, s_rstd);
+  block_stats(p.stats, n, cpg, p.HW, s_mean, s_rstd);
   if (threadIdx.x < G) {
     const float cnt = (float)cpg * (float)p.HW;
     s_s1[threadIdx.x] = p.ws[((long long)n * G + threadIdx.x) * 2] / cnt;
@@ -211,42 +265,60 @@ __global__ void gn_bwd_apply_kernel(BwdP p, int rows_per_block) {
   }
   __syncthreads();
   const int r0 = blockIdx.x * rows_per_block, r1 = min(p.HW, r0 + rows_per_block);
-  const long long total = (long long)(r1 - r0) * vecs;
-  for (long long i = threadIdx.x; i < total; i += blockDim.x) {
-    const int r = r0 + (int)(i / vecs), c = (int)(i % vecs) * 8;
-    const long long row = (long long)n * p.HW + r;
-    float xh[8], dz[8], dx[8];
-    gn_bwd_dz(p, row, c, C, cpg, s_mean, s_rstd, xh, dz, false);
+  const int rows_par = max(1, (int)blockDim.x / vecs);
+  const int v = threadIdx.x % vecs, rsub = threadIdx.x / vecs, c0 = v * 8;
+  if (rsub >= rows_par) return;
+  Chan ch; load_chan(ch, p.gamma, p.beta, c0, cpg, s_mean, s_rstd);
+  float s1[8], s2[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const int g = (c + j) / cpg;
-      dx[j] = s_rstd[g] * (dz[j] * __ldg(p.gamma + c + j) - s_s1[g] - xh[j] * s_s2[g]);
-    }
-    if (p.add0) {
-      float a[8]; b3d_unpack8(*reinterpret_cast<const bf16x8*>(p.add0 + row * p.ld_add0 + c), a);
+  for (int j = 0; j < 8; ++j) { const int g = (c0 + j) / cpg; s1[j] = s_s1[g]; s2[j] = s_s2[g]; }
+  const RowPtr rp = src_ptr(p.s, c0);
+  const bool first = c0 < p.s.C0;
+  const bf16* ad1 = first ? p.add1a : p.add1b;
+  const long long ld_ad1 = first ? p.ld_add1a : p.ld_add1b;
+  const int c1 = first ? c0 : c0 - p.s.C0;
+  bf16* dxp = first ? p.dx0 : p.dx1;
+  const long long ld_dx = first ? p.ld_dx0 : p.ld_dx1;
+  const long long img = (long long)n * p.HW;
+  const float keep = 1.f / (1.f - p.drop_p);
+  const unsigned long long seed = p.seed + (p.seed_ptr ? *p.seed_ptr : 0ULL);
+  for (int r = r0 + rsub; r < r1; r += rows_par * U) {
+    bf16x8 x[U], dy[U], sc[U], a0[U], a1[U];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) dx[j] += a[j];
+    for (int u = 0; u < U; ++u) {
+      const long long row = img + r + u * rows_par;
+      const bool ok = r + u * rows_par < r1;
+      x[u] = ok ? ld8(rp.p + row * rp.ld) : zero8();
+      dy[u] = ok ? ld8(p.dy + row * p.ld_dy + c0) : zero8();
+      sc[u] = (ok && p.mode == 2) ? ld8(p.ss + row * p.ld_ss + c0) : zero8();
+      a0[u] = (ok && p.add0) ? ld8(p.add0 + row * p.ld_add0 + c0) : zero8();
+      a1[u] = (ok && ad1) ? ld8(ad1 + row * ld_ad1 + c1) : zero8();
     }
-    const bool first = c < p.s.C0;
-    const bf16* ad = first ? p.add1a : p.add1b;
-    if (ad) {
-      float a[8];
-      b3d_unpack8(*reinterpret_cast<const bf16x8*>(ad + row * (first ? p.ld_add1a : p.ld_add1b) + (first ? c : c - p.s.C0)), a);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) dx[j] += a[j];
+    for (int u = 0; u < U; ++u) {
+      if (r + u * rows_par >= r1) break;
+      const long long row = img + r + u * rows_par;
+      float xh[8], dz[8], dsc[8], dsh[8], dx[8], t0[8], t1[8];
+      bwd_dz(p, ch, x[u], dy[u], sc[u], row, c0, C, seed, keep, xh, dz, dsc, dsh);
+      b3d_unpack8(a0[u], t0); b3d_unpack8(a1[u], t1);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) dx[j] = ch.rstd[j] * (dz[j] * ch.gamma[j] - s1[j] - xh[j] * s2[j]) + t0[j] + t1[j];
+      *reinterpret_cast<bf16x8*>(dxp + row * ld_dx + c1) = b3d_pack8(dx);
     }
-    if (first) *reinterpret_cast<bf16x8*>(p.dx0 + row * p.ld_dx0 + c) = b3d_pack8(dx);
-    else *reinterpret_cast<bf16x8*>(p.dx1 + row * p.ld_dx1 + (c - p.s.C0)) = b3d_pack8(dx);
   }
 }
 
-int pick_rows_per_block(int N, int HW, int C) {
-  // aim for >= ~4 blocks per SM overall and >= 8 KB of input per block
-  long long per_row = (long long)C * 2;
-  int rpb = (int)((16384 + per_row - 1) / per_row);
-  if (rpb < 1) rpb = 1;
-  long long blocks = (long long)N * ((HW + rpb - 1) / rpb);
-  while (blocks > 148LL * 16 && rpb < HW) { rpb *= 2; blocks = (long long)N * ((HW + rpb - 1) / rpb); }
+int pick_rows_per_block(int N, int HW, int C, int U) {
+  // ~2 waves of 8 blocks per SM over the whole launch, but never fewer rows than one unrolled sweep of the block
+  const int vecs = C / 8;
+  const int rows_par = 256 / vecs > 0 ? 256 / vecs : 1;
+  int per_img = (148 * 16 + N - 1) / N;
+  if (per_img < 1) per_img = 1;
+  int rpb = (HW + per_img - 1) / per_img;
+  const int min_rows = rows_par * U;
+  if (rpb < min_rows) rpb = min_rows;
+  rpb = (rpb + min_rows - 1) / min_rows * min_rows;
+  if (rpb > HW) rpb = HW;
   return rpb;
 }
 
@@ -255,7 +327,7 @@ int check_src(const void* x0, int C0, const void* x1, int C1) {
   B3D_CHECK_ARG(x0 != nullptr && C0 > 0, "groupnorm: null input");
   B3D_CHECK_ARG((x1 == nullptr) == (C1 == 0), "groupnorm: second source / C1 mismatch");
   B3D_CHECK_ARG(C % G == 0 && C0 % 8 == 0 && C1 % 8 == 0, "groupnorm: C=%d+%d must be a multiple of 32 (8 per source)", C0, C1);
-  B3D_CHECK_ARG(C <= 4096, "groupnorm: C too large");
+  B3D_CHECK_ARG(C <= 2048, "groupnorm: C = %d > 2048 (one 256-thread block must cover all channel vectors)", C);
   return 0;
 }
 
@@ -265,7 +337,7 @@ extern "C" int b3d_gn_stats(const void* x0, int C0, int64_t ld0, const void* x1,
                             void* stream) {
   if (int rc = check_src(x0, C0, x1, C1)) return rc;
   Src2 s{(const bf16*)x0, (const bf16*)x1, C0, C1, ld0, ld1};
-  const int C = C0 + C1, rpb = pick_rows_per_block(N, HW, C);
+  const int C = C0 + C1, rpb = pick_rows_per_block(N, HW, C, 4);
   dim3 grid((HW + rpb - 1) / rpb, N);
   gn_stats_kernel<<<grid, kT, 2 * C * sizeof(float), (cudaStream_t)stream>>>(s, HW, rpb, ws_sums);
   B3D_LAUNCH_CHECK();
@@ -284,7 +356,7 @@ extern "C" int b3d_gn_apply(const void* x0, int C0, int64_t ld0, const void* x1,
   p.s = Src2{(const bf16*)x0, (const bf16*)x1, C0, C1, ld0, ld1};
   p.stats = sums; p.gamma = gamma; p.beta = beta; p.out = (bf16*)out; p.ld_out = ld_out; p.HW = HW; p.mode = mode;
   p.ss = (const bf16*)ss; p.ld_ss = ld_ss; p.F = F; p.drop_p = drop_p; p.seed = seed; p.seed_ptr = (const unsigned long long*)seed_ptr;
-  const int rpb = pick_rows_per_block(N, HW, C0 + C1);
+  const int rpb = pick_rows_per_block(N, HW, C0 + C1, 4);
   dim3 grid((HW + rpb - 1) / rpb, N);
   gn_apply_kernel<<<grid, kT, 0, (cudaStream_t)stream>>>(p, rpb);
   B3D_LAUNCH_CHECK();
@@ -309,7 +381,7 @@ extern "C" int b3d_gn_bwd(const void* x0, int C0, int64_t ld0, const void* x1, i
   p.dx0 = (bf16*)dx0; p.dx1 = (bf16*)dx1; p.ld_dx0 = ld_dx0; p.ld_dx1 = ld_dx1;
   p.add0 = (const bf16*)add0; p.ld_add0 = ld_add0;
   p.add1a = (const bf16*)add1a; p.add1b = (const bf16*)add1b; p.ld_add1a = ld_add1a; p.ld_add1b = ld_add1b;
-  const int C = C0 + C1, rpb = pick_rows_per_block(N, HW, C);
+  const int C = C0 + C1, rpb = pick_rows_per_block(N, HW, C, 2);
   dim3 grid((HW + rpb - 1) / rpb, N);
   gn_bwd_reduce_kernel<<<grid, kT, (2 * C + 2 * G) * sizeof(float), (cudaStream_t)stream>>>(p, rpb);
   B3D_LAUNCH_CHECK();

@@ -13,7 +13,8 @@ import numpy as np
 import torch
 import torch.distributed as dist
 
-from .diff3d import FusedAdam, Diff3D, diffusion_loss
+from . import parallel
+from .diff3d import FusedAdam
 from .ops import CudaOps
 from .xunet import XUNet
 
@@ -25,8 +26,7 @@ class Trainer:
         self.model = XUNet(**model_kw).to(self.dev)
         if init_sd is not None:
             self.model.load_state_dict(init_sd)
-        if world > 1:                                   # same weights everywhere (DDP's rank-0 broadcast, train.py:230)
-            dist.broadcast(self.model.flat_parameters(), 0)
+        parallel.broadcast_parameters(self.model.flat_parameters())   # DDP's rank-0 broadcast (train.py:230)
         self.model.train()
         self.model.fused_grads = True
         self.opt = FusedAdam(self.model, lr=lr, betas=(0.9, 0.99))
@@ -85,8 +85,7 @@ class Trainer:
         self.engine.backward(self.model._grad_views(), self.deps, grad_flat=self.model._grad_flat)
 
     def _finish(self):
-        if self.world > 1:
-            dist.all_reduce(self.model._grad_flat, op=dist.ReduceOp.AVG)
+        parallel.allreduce_mean_(self.model._grad_flat)
         self.opt.step()
         self.step_idx += 1
 

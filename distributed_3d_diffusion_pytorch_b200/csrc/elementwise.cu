@@ -466,6 +466,110 @@ __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, 
   }
 }
 
+
+// out = scale * a (bf16 [rows, C]) and colsum[c] += sum_rows out[row, c]   (the residual-branch gradient and the bias
+// gradients that equal its column sums: conv2.bias, dense.bias, linear.bias)
+__global__ void __launch_bounds__(256) scale_colsum_kernel(const bf16* __restrict__ a, bf16* __restrict__ out, float scale, long long rows, int C,
+                                                           int rows_per_block, float* __restrict__ colsum) {
+  extern __shared__ float sm[];   // [C]
+  constexpr int U = 4;
+  const int vecs = C / 8;
+  for (int i = threadIdx.x; i < C; i += blockDim.x) sm[i] = 0.f;
+  __syncthreads();
+  const int rows_par = max(1, (int)blockDim.x / vecs);
+  const int v = threadIdx.x % vecs, rsub = threadIdx.x / vecs;
+  const long long r0 = (long long)blockIdx.x * rows_per_block, r1 = min(rows, r0 + rows_per_block);
+  if (rsub < rows_par) {
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (long long r = r0 + rsub; r < r1; r += (long long)rows_par * U) {
+      bf16x8 x[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long rr = r + (long long)u * rows_par;
+        if (rr < r1) x[u] = *reinterpret_cast<const bf16x8*>(a + rr * C + v * 8);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long rr = r + (long long)u * rows_par;
+        if (rr >= r1) break;
+        float f[8]; b3d_unpack8(x[u], f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[j] *= scale;
+        *reinterpret_cast<bf16x8*>(out + rr * C + v * 8) = b3d_pack8(f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += f[j];
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) atomicAdd(&sm[v * 8 + j], acc[j]);
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) atomicAdd(&colsum[c], sm[c]);
+}
+
+// many weight tensors in ONE launch (the per-step repack of every parameter / the unpack of every packed gradient):
+// blocks are distributed over the jobs through a prefix table; semantics of each job = pack_weight / unpack_wgrad above,
+// plus mode 3 = plain fp32 copy (FiLM bias concatenation).
+struct PackJob {
+  const float* src; void* dst;
+  int Co, Ci, taps, mode, ci0, cn, Cpad, accumulate;
+  long long k_off, ld, total;
+  long long block0;   // first block of this job
+};
+
+__device__ __forceinline__ int find_job(const PackJob* jobs, int n_jobs, long long blk) {
+  int lo = 0, hi = n_jobs - 1;
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (jobs[mid].block0 <= blk) lo = mid; else hi = mid - 1;
+  }
+  return lo;
+}
+
+__global__ void __launch_bounds__(256) pack_multi_kernel(const PackJob* __restrict__ jobs, int n_jobs) {
+  const int j = find_job(jobs, n_jobs, blockIdx.x);
+  const PackJob J = jobs[j];
+  const long long i0 = ((long long)blockIdx.x - J.block0) * 1024;
+  const float* w = J.src;
+  for (int k = 0; k < 4; ++k) {
+    const long long i = i0 + k * 256 + threadIdx.x;
+    if (i >= J.total) return;
+    if (J.mode == 3) { reinterpret_cast<float*>(J.dst)[i] = w[i]; continue; }
+    bf16* out = reinterpret_cast<bf16*>(J.dst);
+    float v = 0.f;
+    long long o;
+    if (J.mode == 0) {
+      const int cc = (int)(i % J.Cpad), tap = (int)((i / J.Cpad) % J.taps), co = (int)(i / ((long long)J.Cpad * J.taps));
+      if (cc < J.cn) v = w[((long long)co * J.Ci + J.ci0 + cc) * J.taps + tap];
+      o = (long long)co * J.ld + J.k_off + (long long)tap * J.Cpad + cc;
+    } else if (J.mode == 1) {
+      const int co = (int)(i % J.Cpad), tp = (int)((i / J.Cpad) % J.taps), ci = (int)(i / ((long long)J.Cpad * J.taps));
+      if (co < J.Co) v = w[((long long)co * J.Ci + ci) * J.taps + (J.taps - 1 - tp)];
+      o = (long long)ci * J.ld + J.k_off + (long long)tp * J.Cpad + co;
+    } else {
+      const int co = (int)(i % J.Co), ci = (int)((i / J.Co) % J.Ci), tap = (int)(i / ((long long)J.Co * J.Ci));
+      v = w[((long long)co * J.Ci + ci) * J.taps + tap];
+      o = ((long long)tap * J.Ci + ci) * J.ld + co;
+    }
+    out[o] = __float2bfloat16(v);
+  }
+}
+
+__global__ void __launch_bounds__(256) unpack_multi_kernel(const PackJob* __restrict__ jobs, int n_jobs) {
+  const int j = find_job(jobs, n_jobs, blockIdx.x);
+  const PackJob J = jobs[j];
+  const long long i0 = ((long long)blockIdx.x - J.block0) * 1024;
+  float* dw = reinterpret_cast<float*>(J.dst);
+  for (int k = 0; k < 4; ++k) {
+    const long long i = i0 + k * 256 + threadIdx.x;
+    if (i >= J.total) return;
+    const int tap = (int)(i % J.taps), cc = (int)((i / J.taps) % J.cn), co = (int)(i / ((long long)J.taps * J.cn));
+    const float v = J.src[(long long)co * J.ld + J.k_off + (long long)tap * J.Cpad + cc];
+    float* d = dw + ((long long)co * J.Ci + J.ci0 + cc) * J.taps + tap;
+    *d = J.accumulate ? *d + v : v;
+  }
+}
+
 }  // namespace
 
 #define STREAM ((cudaStream_t)stream)
@@ -659,5 +763,27 @@ extern "C" int b3d_adam(float* p, const float* g, float* m, float* v, int64_t n,
   B3D_CHECK_ARG(p && g && m && v && step >= 1, "adam: args");
   const float bc1 = 1.f - powf(beta1, (float)step), bc2 = 1.f - powf(beta2, (float)step);
   adam_kernel<<<grid_for(n), kT, 0, STREAM>>>(p, g, m, v, n, lr, beta1, beta2, eps, bc1, bc2, grad_scale);
+  DONE(1);
+}
+
+extern "C" int b3d_scale_colsum(const void* a, void* out, float scale, int64_t rows, int C, float* colsum, void* stream) {
+  B3D_CHECK_ARG(a && out && colsum && C % 8 == 0 && C <= 2048, "scale_colsum: args (C %% 8, C <= 2048)");
+  const int rows_par = 256 / (C / 8) > 0 ? 256 / (C / 8) : 1;
+  long long rpb = (rows + 148 * 8 - 1) / (148 * 8);
+  const int min_rows = rows_par * 4;
+  if (rpb < min_rows) rpb = min_rows;
+  rpb = (rpb + min_rows - 1) / min_rows * min_rows;
+  scale_colsum_kernel<<<cdiv(rows, rpb), 256, C * sizeof(float), STREAM>>>((const bf16*)a, (bf16*)out, scale, rows, C, (int)rpb, colsum);
+  DONE(1);
+}
+// jobs: device array of b3d_pack_job (include/b3d.h) whose block0 fields are the running sum of ceil(total/1024)
+extern "C" int b3d_pack_weights_multi(const void* jobs, int n_jobs, int64_t total_blocks, void* stream) {
+  B3D_CHECK_ARG(jobs && n_jobs > 0 && total_blocks > 0, "pack_weights_multi: args");
+  pack_multi_kernel<<<(unsigned)total_blocks, 256, 0, STREAM>>>((const PackJob*)jobs, n_jobs);
+  DONE(1);
+}
+extern "C" int b3d_unpack_wgrads_multi(const void* jobs, int n_jobs, int64_t total_blocks, void* stream) {
+  B3D_CHECK_ARG(jobs && n_jobs > 0 && total_blocks > 0, "unpack_wgrads_multi: args");
+  unpack_multi_kernel<<<(unsigned)total_blocks, 256, 0, STREAM>>>((const PackJob*)jobs, n_jobs);
   DONE(1);
 }

@@ -160,6 +160,8 @@ struct BwdP {
   bf16* dss; long long ld_dss;      // film: d_scale -> dss[row, c], d_shift -> dss[row, F + c]
   float drop_p; unsigned long long seed; const unsigned long long* seed_ptr;  // effective seed = seed + *seed_ptr (device step counter)
   float* dgamma; float* dbeta;      // fp32 [C], accumulated
+  float* dss_sum;                   // optional fp32 [2F]: column sums of dss (the FiLM dense bias gradient)
+  float* dx_sum;                    // optional fp32 [C]: column sums of dx before the addends (the producer's bias gradient)
   float* ws;                        // [N,32,2] (S1, S2), pre-zeroed
   // pass 2 outputs
   bf16* dx0; bf16* dx1; long long ld_dx0, ld_dx1;
@@ -190,12 +192,14 @@ __device__ __forceinline__ void bwd_dz(const BwdP& p, const Chan& ch, const bf16
 
 // pass 1: d_scale/d_shift (film), dgamma/dbeta, per-(image,group) S1 = sum dz*gamma, S2 = sum dz*gamma*xhat
 __global__ void __launch_bounds__(kT, 2) gn_bwd_reduce_kernel(BwdP p, int rows_per_block) {
-  extern __shared__ float sm[];  // [C][2] dgamma,dbeta partials then [G][2]
+  extern __shared__ float sm[];  // [C][2] dgamma,dbeta partials, [G][2], then [C][2] column sums of (d_scale, d_shift)
   __shared__ float s_mean[G], s_rstd[G];
   constexpr int U = 2;
   const int C = p.s.C0 + p.s.C1, cpg = C / G, n = blockIdx.y, vecs = C / 8;
   float* s_gs = sm + 2 * C;
-  for (int i = threadIdx.x; i < 2 * C + 2 * G; i += blockDim.x) sm[i] = 0.f;
+  float* s_ss = s_gs + 2 * G;
+  const bool want_ss = p.mode == 2 && p.dss_sum != nullptr;
+  for (int i = threadIdx.x; i < 2 * C + 2 * G + (want_ss ? 2 * C : 0); i += blockDim.x) sm[i] = 0.f;
   block_stats(p.stats, n, cpg, p.HW, s_mean, s_rstd);
   __syncthreads();
   const int r0 = blockIdx.x * rows_per_block, r1 = min(p.HW, r0 + rows_per_block);
@@ -207,9 +211,9 @@ __global__ void __launch_bounds__(kT, 2) gn_bwd_reduce_kernel(BwdP p, int rows_p
     const long long img = (long long)n * p.HW;
     const float keep = 1.f / (1.f - p.drop_p);
     const unsigned long long seed = p.seed + (p.seed_ptr ? *p.seed_ptr : 0ULL);
-    float ag[8], ab[8];
+    float ag[8], ab[8], asc[8], ash[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) { ag[j] = 0.f; ab[j] = 0.f; }
+    for (int j = 0; j < 8; ++j) { ag[j] = 0.f; ab[j] = 0.f; asc[j] = 0.f; ash[j] = 0.f; }
     for (int r = r0 + rsub; r < r1; r += rows_par * U) {
       bf16x8 x[U], dy[U], sc[U];
 #pragma unroll
@@ -229,6 +233,10 @@ __global__ void __launch_bounds__(kT, 2) gn_bwd_reduce_kernel(BwdP p, int rows_p
         if (p.mode == 2) {
           *reinterpret_cast<bf16x8*>(p.dss + row * p.ld_dss + c0) = b3d_pack8(dsc);
           *reinterpret_cast<bf16x8*>(p.dss + row * p.ld_dss + p.F + c0) = b3d_pack8(dsh);
+          if (want_ss) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { asc[j] += dsc[j]; ash[j] += dsh[j]; }
+          }
         }
 #pragma unroll
         for (int j = 0; j < 8; ++j) { ag[j] += dz[j] * xh[j]; ab[j] += dz[j]; }
@@ -236,8 +244,18 @@ __global__ void __launch_bounds__(kT, 2) gn_bwd_reduce_kernel(BwdP p, int rows_p
     }
 #pragma unroll
     for (int j = 0; j < 8; ++j) { atomicAdd(&sm[2 * (c0 + j)], ag[j]); atomicAdd(&sm[2 * (c0 + j) + 1], ab[j]); }
+    if (want_ss) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { atomicAdd(&s_ss[2 * (c0 + j)], asc[j]); atomicAdd(&s_ss[2 * (c0 + j) + 1], ash[j]); }
+    }
   }
   __syncthreads();
+  if (want_ss) {
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+      atomicAdd(&p.dss_sum[c], s_ss[2 * c]);
+      atomicAdd(&p.dss_sum[p.F + c], s_ss[2 * c + 1]);
+    }
+  }
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
     const float dg = sm[2 * c], db = sm[2 * c + 1], gam = p.gamma[c];
     atomicAdd(&p.dgamma[c], dg);
@@ -254,9 +272,11 @@ __global__ void __launch_bounds__(kT, 2) gn_bwd_reduce_kernel(BwdP p, int rows_p
 
 // pass 2: dx = rstd * (dz*gamma - (S1 + xhat*S2)/cnt) [+ add0] [+ add1]
 __global__ void __launch_bounds__(kT, 2) gn_bwd_apply_kernel(BwdP p, int rows_per_block) {
+  extern __shared__ float sm[];   // [C] column sums of dx when p.dx_sum is set
   __shared__ float s_mean[G], s_rstd[G], s_s1[G], s_s2[G];
   constexpr int U = 2;
   const int C = p.s.C0 + p.s.C1, cpg = C / G, n = blockIdx.y, vecs = C / 8;
+  if (p.dx_sum) for (int i = threadIdx.x; i < C; i += blockDim.x) sm[i] = 0.f;
   block_stats(p.stats, n, cpg, p.HW, s_mean, s_rstd);
   if (threadIdx.x < G) {
     const float cnt = (float)cpg * (float)p.HW;
@@ -267,9 +287,11 @@ __global__ void __launch_bounds__(kT, 2) gn_bwd_apply_kernel(BwdP p, int rows_pe
   const int r0 = blockIdx.x * rows_per_block, r1 = min(p.HW, r0 + rows_per_block);
   const int rows_par = max(1, (int)blockDim.x / vecs);
   const int v = threadIdx.x % vecs, rsub = threadIdx.x / vecs, c0 = v * 8;
-  if (rsub >= rows_par) return;
+  if (rsub < rows_par) {
   Chan ch; load_chan(ch, p.gamma, p.beta, c0, cpg, s_mean, s_rstd);
-  float s1[8], s2[8];
+  float s1[8], s2[8], acc[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
 #pragma unroll
   for (int j = 0; j < 8; ++j) { const int g = (c0 + j) / cpg; s1[j] = s_s1[g]; s2[j] = s_s2[g]; }
   const RowPtr rp = src_ptr(p.s, c0);
@@ -302,9 +324,22 @@ __global__ void __launch_bounds__(kT, 2) gn_bwd_apply_kernel(BwdP p, int rows_pe
       bwd_dz(p, ch, x[u], dy[u], sc[u], row, c0, C, seed, keep, xh, dz, dsc, dsh);
       b3d_unpack8(a0[u], t0); b3d_unpack8(a1[u], t1);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) dx[j] = ch.rstd[j] * (dz[j] * ch.gamma[j] - s1[j] - xh[j] * s2[j]) + t0[j] + t1[j];
+      for (int j = 0; j < 8; ++j) {
+        const float d = ch.rstd[j] * (dz[j] * ch.gamma[j] - s1[j] - xh[j] * s2[j]);
+        acc[j] += d;
+        dx[j] = d + t0[j] + t1[j];
+      }
       *reinterpret_cast<bf16x8*>(dxp + row * ld_dx + c1) = b3d_pack8(dx);
     }
+  }
+  if (p.dx_sum) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) atomicAdd(&sm[c0 + j], acc[j]);
+  }
+  }
+  if (p.dx_sum) {
+    __syncthreads();
+    for (int c = threadIdx.x; c < C; c += blockDim.x) atomicAdd(&p.dx_sum[c], sm[c]);
   }
 }
 
@@ -366,7 +401,8 @@ extern "C" int b3d_gn_apply(const void* x0, int C0, int64_t ld0, const void* x1,
 
 extern "C" int b3d_gn_bwd(const void* x0, int C0, int64_t ld0, const void* x1, int C1, int64_t ld1, int N, int HW, const float* sums,
                           const float* gamma, const float* beta, int mode, const void* dy, int64_t ld_dy, const void* ss, int64_t ld_ss,
-                          int F, void* dss, int64_t ld_dss, float drop_p, uint64_t seed, const uint64_t* seed_ptr, float* dgamma, float* dbeta, float* ws_s12,
+                          int F, void* dss, int64_t ld_dss, float drop_p, uint64_t seed, const uint64_t* seed_ptr, float* dgamma, float* dbeta,
+                          float* dss_sum, float* dx_sum, float* ws_s12,
                           void* dx0, int64_t ld_dx0, void* dx1, int64_t ld_dx1, const void* add0, int64_t ld_add0, const void* add1a,
                           int64_t ld_add1a, const void* add1b, int64_t ld_add1b, void* stream) {
   if (int rc = check_src(x0, C0, x1, C1)) return rc;
@@ -377,15 +413,15 @@ extern "C" int b3d_gn_bwd(const void* x0, int C0, int64_t ld0, const void* x1, i
   p.s = Src2{(const bf16*)x0, (const bf16*)x1, C0, C1, ld0, ld1};
   p.stats = sums; p.gamma = gamma; p.beta = beta; p.dy = (const bf16*)dy; p.ld_dy = ld_dy; p.HW = HW; p.mode = mode;
   p.ss = (const bf16*)ss; p.ld_ss = ld_ss; p.F = F; p.dss = (bf16*)dss; p.ld_dss = ld_dss; p.drop_p = drop_p; p.seed = seed; p.seed_ptr = (const unsigned long long*)seed_ptr;
-  p.dgamma = dgamma; p.dbeta = dbeta; p.ws = ws_s12;
+  p.dgamma = dgamma; p.dbeta = dbeta; p.ws = ws_s12; p.dss_sum = dss_sum; p.dx_sum = dx_sum;
   p.dx0 = (bf16*)dx0; p.dx1 = (bf16*)dx1; p.ld_dx0 = ld_dx0; p.ld_dx1 = ld_dx1;
   p.add0 = (const bf16*)add0; p.ld_add0 = ld_add0;
   p.add1a = (const bf16*)add1a; p.add1b = (const bf16*)add1b; p.ld_add1a = ld_add1a; p.ld_add1b = ld_add1b;
   const int C = C0 + C1, rpb = pick_rows_per_block(N, HW, C, 2);
   dim3 grid((HW + rpb - 1) / rpb, N);
-  gn_bwd_reduce_kernel<<<grid, kT, (2 * C + 2 * G) * sizeof(float), (cudaStream_t)stream>>>(p, rpb);
+  gn_bwd_reduce_kernel<<<grid, kT, (4 * C + 2 * G) * sizeof(float), (cudaStream_t)stream>>>(p, rpb);
   B3D_LAUNCH_CHECK();
-  gn_bwd_apply_kernel<<<grid, kT, 0, (cudaStream_t)stream>>>(p, rpb);
+  gn_bwd_apply_kernel<<<grid, kT, C * sizeof(float), (cudaStream_t)stream>>>(p, rpb);
   B3D_LAUNCH_CHECK();
   b3d_count_launch(2);
   return B3D_OK;

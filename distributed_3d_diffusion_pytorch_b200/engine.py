@@ -17,6 +17,7 @@ import math
 import torch
 
 from . import gemm as G
+from .ops import JobList
 
 RSQRT2 = 1.0 / math.sqrt(2.0)
 
@@ -102,6 +103,8 @@ class Engine:
         self._zero = {"fwd": [None, 0, {}], "bwd": [None, 0, {}]}
         self._zero_cap = {"fwd": 1 << 22, "bwd": 1 << 22}
         self.saved = None
+        self._pack_cache = {}
+        self._unpack_jl, self._copy_jl, self._unpack_sig, self._unpack_rec = None, None, None, False
         self.seed_ptr = None      # optional int64 device scalar added to every dropout seed (see ops.gn_apply)
         for lvl in range(cfg.num_resolutions):
             assert cfg.H % (2 ** lvl) == 0 and cfg.W % (2 ** lvl) == 0
@@ -143,8 +146,19 @@ class Engine:
 
     # ------------------------------------------------------------------ weights
     def _pack_weights(self, P, training):
-        """fp32 PyTorch-layout parameters -> bf16 K-major operands (per forward: parameters change every step)."""
+        """fp32 PyTorch-layout parameters -> bf16 K-major operands (per forward: parameters change every step).
+        The ~450 conversions are recorded once (all addresses are static) and then run as ONE kernel launch per step."""
+        sig = (training, len(P), tuple(P[k].data_ptr() for k in list(P.keys())[:8]))
+        cached = self._pack_cache.get(training)
+        if cached is None or cached[0] != sig:
+            cached = (sig,) + self._record_pack(P, training)
+            self._pack_cache[training] = cached
+        self.ops.run_jobs(cached[2])
+        return cached[1]
+
+    def _record_pack(self, P, training):
         ops, cfg, W = self.ops, self.cfg, {}
+        jl = JobList("pack")
 
         def conv3(name, w, Co_alloc=None):
             Co, Ci = w.shape[0], w.shape[1]
@@ -152,12 +166,12 @@ class Engine:
             f = self.buf("w.f." + name, (Co_alloc or Co, 9 * cp))
             if Co_alloc:
                 f.zero_()
-            ops.pack_weight(w, 0, f, Cpad=cp)
+            ops.record_pack_weight(jl, w, 0, f, Cpad=cp)
             W[name] = f
             if training:
                 cop = G.ceil64(Co)
                 t = self.buf("w.t." + name, (Ci, 9 * cop))
-                ops.pack_weight(w, 1, t, Cpad=cop)
+                ops.record_pack_weight(jl, w, 1, t, Cpad=cop)
                 W[name + ".T"] = t
 
         def lin(name, w, srcs=None):
@@ -166,13 +180,13 @@ class Engine:
             f = self.buf("w.f." + name, (Co, sum(G.ceil64(c) for c in srcs)))
             ci0 = koff = 0
             for c in srcs:
-                ops.pack_weight(w, 0, f, ci0=ci0, cn=c, Cpad=G.ceil64(c), k_off=koff)
+                ops.record_pack_weight(jl, w, 0, f, ci0=ci0, cn=c, Cpad=G.ceil64(c), k_off=koff)
                 ci0 += c
                 koff += G.ceil64(c)
             W[name] = f
             if training:
                 t = self.buf("w.t." + name, (Ci, G.ceil64(Co)))
-                ops.pack_weight(w, 1, t, Cpad=G.ceil64(Co))
+                ops.record_pack_weight(jl, w, 1, t, Cpad=G.ceil64(Co))
                 W[name + ".T"] = t
 
         cp = "conditioningprocessor."
@@ -181,17 +195,20 @@ class Engine:
         for l in range(cfg.num_resolutions):
             w = P[cp + f"convs.{l}.weight"]
             f = self.buf(f"w.f.cc{l}", (cfg.emb_ch, 9 * 192))
-            ops.pack_weight(w, 0, f, Cpad=192)
+            ops.record_pack_weight(jl, w, 0, f, Cpad=192)
             W[cp + f"convs.{l}.weight"] = f
             if training:
                 t = self.buf(f"w.r.cc{l}", (9 * 144, cfg.emb_ch))
-                ops.pack_weight(w, 2, t)
+                ops.record_pack_weight(jl, w, 2, t)
                 W[cp + f"convs.{l}.weight.R"] = t
         # stem: the packed input tensor has 8 channels (3 real)
         f = self.buf("w.f.stem", (cfg.ch, 9 * 64))
-        ops.pack_weight(P["conv.weight"], 0, f, Cpad=64)
+        ops.record_pack_weight(jl, P["conv.weight"], 0, f, Cpad=64)
         W["conv.weight"] = f
         conv3("lastconv.weight", P["lastconv.weight"], Co_alloc=16)
+        lb = self.buf("lastconv.b16", (16,), torch.float32)
+        lb.zero_()
+        ops.record_copy(jl, P["lastconv.bias"], lb[:3])
         # FiLM: one [sum 2F, 1024] operand per level (+ its transpose for the data gradient)
         for l in range(cfg.num_resolutions):
             W[f"film{l}"] = self.buf(f"w.f.film{l}", (self.film_cols[l], 1024))
@@ -207,16 +224,16 @@ class Engine:
                 if s.cin != s.f:
                     lin(n + ".dense.weight", P[n + ".dense.weight"], s.srcs_c if s.cat else None)
                 fw = P[n + ".film.dense.weight"]
-                ops.pack_weight(fw, 0, W[f"film{s.lvl}"][s.film_off:s.film_off + 2 * s.f], Cpad=1024)
-                self._bufs[f"b.film{s.lvl}"][s.film_off:s.film_off + 2 * s.f].copy_(P[n + ".film.dense.bias"])
+                ops.record_pack_weight(jl, fw, 0, W[f"film{s.lvl}"][s.film_off:s.film_off + 2 * s.f], Cpad=1024)
+                ops.record_copy(jl, P[n + ".film.dense.bias"], self._bufs[f"b.film{s.lvl}"][s.film_off:s.film_off + 2 * s.f])
                 if training:
-                    ops.pack_weight(fw, 1, W[f"film{s.lvl}.T"], Cpad=2 * s.f, k_off=s.film_off)
+                    ops.record_pack_weight(jl, fw, 1, W[f"film{s.lvl}.T"], Cpad=2 * s.f, k_off=s.film_off)
             elif kind == "attn":
                 a = s.name + ".attn_layer.attn"
                 lin(a + ".in_proj_weight", P[a + ".in_proj_weight"])
                 lin(a + ".out_proj.weight", P[a + ".out_proj.weight"])
                 lin(s.name + ".linear.weight", P[s.name + ".linear.weight"])
-        return W
+        return W, jl
 
     # ------------------------------------------------------------------ forward
     def forward(self, P, x, z, logsnr, R, t, K, cond_mask, training=False, need_bwd=None, seed=0):
@@ -291,10 +308,7 @@ class Engine:
         al = self.buf("lastgn.a", (N, hh * ww, C))
         ops.gn_apply(x3, None, sums, P["lastgn.gn.weight"], P["lastgn.gn.bias"], 1, al)
         y = self.buf("lastconv.y", (N, H, Wd, 16))
-        lb = self.buf("lastconv.b16", (16,), torch.float32)
-        lb.zero_()
-        lb[:3].copy_(P["lastconv.bias"])
-        ops.gemm(G.conv_desc([al.view(N, H, Wd, C)], [9], Wp["lastconv.weight"], 3, y, bias=lb))
+        ops.gemm(G.conv_desc([al.view(N, H, Wd, C)], [9], Wp["lastconv.weight"], 3, y, bias=self._bufs["lastconv.b16"]))
         eps = self.buf("eps", (B, 3, H, Wd), torch.float32)
         ops.unpack_output(y, eps)
         sv["final"] = h
@@ -408,6 +422,10 @@ class Engine:
         P, Wp = sv["P"], sv["W"]
         H, Wd, E = cfg.H, cfg.W, cfg.emb_ch
         self._zero_phase("bwd")
+        usig = (len(Gr), tuple(Gr[k].data_ptr() for k in list(Gr.keys())[:8]))
+        self._unpack_rec = self._unpack_jl is None or self._unpack_sig != usig
+        if self._unpack_rec:
+            self._unpack_jl, self._copy_jl, self._unpack_sig = JobList("unpack"), JobList("pack"), usig
         if grad_flat is not None:
             grad_flat.zero_()
         else:
@@ -453,7 +471,7 @@ class Engine:
         ops.colsum(dstem.view(N * HW, cfg.ch), N * HW, Gr["conv.bias"])
         gp = self.zbuf("bwd", "stem.gp", (cfg.ch, 9 * 64))
         ops.gemm(G.wgrad_desc(dstem, xin, 9, gp, 0, 64))
-        ops.unpack_wgrad(gp, 0, 64, Gr["conv.weight"])
+        self._unpack(gp, 0, 64, Gr["conv.weight"])
 
         # ---- conditioning: FiLM data gradient, conditioning convs, learned embeddings, logsnr MLP
         cp = "conditioningprocessor."
@@ -471,7 +489,7 @@ class Engine:
             ops.colsum(de.view(M, E), M, Gr[cp + f"convs.{l}.bias"])
             gp = self.zbuf("bwd", f"cc{l}.gp", (E, 9 * 192))
             ops.gemm(G.wgrad_desc(de, pe, 9, gp, 0, 192, 2 ** l))
-            ops.unpack_wgrad(gp, 0, 192, Gr[cp + f"convs.{l}.weight"])
+            self._unpack(gp, 0, 192, Gr[cp + f"convs.{l}.weight"])
             if cfg.use_pos_emb or cfg.use_ref_pose_emb:
                 des = self.buf(f"desum{l}", (2, hh, ww, E))
                 ops.batch_frame_sum(de, des)
@@ -492,6 +510,13 @@ class Engine:
         ops.silu_bwd(dh1, h1, dh1)
         ops.colsum(dh1, N, Gr[cp + "logsnr_emb_emb.0.bias"])
         ops.gemm(G.wgrad_dense_desc(dh1, e0, Gr[cp + "logsnr_emb_emb.0.weight"]))
+        # every packed fp32 weight gradient goes back to its PyTorch layout in one launch
+        ops.run_jobs(self._unpack_jl)
+        ops.run_jobs(self._copy_jl)
+
+    def _unpack(self, gp, k_off, cpad, dw, ci0=0, cn=None):
+        if self._unpack_rec:
+            self.ops.record_unpack_wgrad(self._unpack_jl, gp, k_off, cpad, dw, ci0=ci0, cn=cn)
 
     def _all_acts(self):
         sv = self.saved
@@ -509,7 +534,7 @@ class Engine:
         cp = G.ceil64(Ci)
         gp = self.zbuf("bwd", "gp." + wname, (co_alloc or Co, 9 * cp))
         self.ops.gemm(G.wgrad_desc(dy, x, 9, gp, 0, cp, stride))
-        self.ops.unpack_wgrad(gp, 0, cp, gw)
+        self._unpack(gp, 0, cp, gw)
 
     def _take_grad(self, act):
         """(buffer, existing) for writing a new gradient contribution of `act`"""
@@ -534,16 +559,16 @@ class Engine:
         else:
             dout = self._grad_of(out)
         gs = self.tmp("gs", (N, hh, ww, F))
-        ops.add_scale(dout, None, gs, RSQRT2)
+        ops.scale_colsum(dout, gs, RSQRT2, Gr[n + ".conv2.bias"])     # d(conv2.bias) = column sums of the scaled gradient
         gs2 = gs.view(M, F)
         # conv2
-        ops.colsum(gs2, M, Gr[n + ".conv2.bias"])
         self._conv_wgrad(n + ".conv2.weight", gs, sa["a1"].view(N, hh, ww, F), Gr[n + ".conv2.weight"])
         da1 = self.tmp("da1", (N, hh, ww, F))
         ops.gemm(G.conv_desc([gs], [9], Wp[n + ".conv2.weight.T"], F, da1))
         # 1x1 skip
         if s.cin != F:
-            ops.colsum(gs2, M, Gr[n + ".dense.weight".replace("weight", "bias")])
+            if self._unpack_rec:       # d(dense.bias) = the same column sums as d(conv2.bias): copied at the end of backward
+                ops.record_copy(self._copy_jl, Gr[n + ".conv2.bias"], Gr[n + ".dense.bias"])
             gw = Gr[n + ".dense.weight"].view(F, s.cin)
             srcs = [h_in] + ([skip] if skip is not None else [])
             koff = 0
@@ -555,7 +580,7 @@ class Engine:
                 for a in srcs:
                     c = a.t.shape[3]
                     ops.gemm(G.wgrad_desc(gs, a.t, 1, gp, koff, G.ceil64(c)))
-                    ops.unpack_wgrad(gp, koff, G.ceil64(c), Gr[n + ".dense.weight"], ci0=ci0, cn=c)
+                    self._unpack(gp, koff, G.ceil64(c), Gr[n + ".dense.weight"], ci0=ci0, cn=c)
                     koff += G.ceil64(c)
                     ci0 += c
             dskip = self.tmp("dskip", (N, HW, s.cin))
@@ -570,13 +595,11 @@ class Engine:
         ops.gn_bwd(sa["c1"].view(N, HW, F), None, sa["sums1"], P[n + ".groupnorm1.gn.weight"], P[n + ".groupnorm1.gn.bias"], 2,
                    da1.view(N, HW, F), Gr[n + ".groupnorm1.gn.weight"], Gr[n + ".groupnorm1.gn.bias"],
                    self.zbuf("bwd", n + ".ws1", (N, 32, 2)), dc1.view(N, HW, F), ss=ssv, F=F, dss=dssv, drop_p=drop_p, seed=sa["seed"],
-                   seed_ptr=self.seed_ptr)
+                   seed_ptr=self.seed_ptr, dss_sum=Gr[n + ".film.dense.bias"], dx_sum=Gr[n + ".conv1.bias"])
         # FiLM dense parameters (xunet.py:80,84): per block, straight into the parameter gradients
         sil = self._bufs[f"emb_silu{s.lvl}"].view(M, 1024)
-        ops.colsum(dssv, M, Gr[n + ".film.dense.bias"])
         ops.gemm(G.wgrad_dense_desc(dssv, sil, Gr[n + ".film.dense.weight"]))
-        # conv1
-        ops.colsum(dc1.view(M, F), M, Gr[n + ".conv1.bias"])
+        # conv1 (its bias gradient and the FiLM bias gradient were reduced inside the GroupNorm backward above)
         self._conv_wgrad(n + ".conv1.weight", dc1, sa["a0"].view(N, hh, ww, s.cin), Gr[n + ".conv1.weight"])
         da0 = self.tmp("da0", (N, hh, ww, s.cin))
         ops.gemm(G.conv_desc([dc1], [9], Wp[n + ".conv1.weight.T"], s.cin, da0))
@@ -604,10 +627,9 @@ class Engine:
         alpha = 1.0 / math.sqrt(d)
         dout = self._grad_of(out)
         gs4 = self.tmp("ags", (N, hh, ww, C))
-        ops.add_scale(dout, None, gs4, RSQRT2)
+        ops.scale_colsum(dout, gs4, RSQRT2, Gr[n + ".linear.bias"])
         gs = gs4.view(M, C)
         # 1x1 `linear` and out_proj
-        ops.colsum(gs, M, Gr[n + ".linear.bias"])
         ops.gemm(G.wgrad_dense_desc(gs, sa["o1"], Gr[n + ".linear.weight"].view(C, C)))
         do1 = self.tmp("do1", (M, C))
         ops.gemm(G.dense_desc(gs, Wp[n + ".linear.weight.T"], do1, C))

@@ -36,7 +36,9 @@ def dense_desc(x2d, wpack, out2d, n_cols, **epi):
 def pick_split_k(tiles, kblocks):
     if tiles >= NUM_SMS:
         return 1
-    s = min(max(1, (2 * NUM_SMS) // max(tiles, 1)), max(1, kblocks // 2))
+    # enough CTAs to fill the GPU about twice, but every split keeps >= 8 K blocks (its prologue, its 128 x N fp32
+    # atomics and its launch slot are pure overhead for small problems)
+    s = min(max(1, (2 * NUM_SMS) // max(tiles, 1)), max(1, kblocks // 8))
     return max(1, s)
 
 

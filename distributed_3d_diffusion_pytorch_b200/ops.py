@@ -89,6 +89,32 @@ def _u8(mask):
     return mask if mask.dtype == torch.uint8 else mask.to(torch.uint8)
 
 
+class _PackJob(ctypes.Structure):
+    _fields_ = [("src", c_void), ("dst", c_void), ("Co", c_i32), ("Ci", c_i32), ("taps", c_i32), ("mode", c_i32), ("ci0", c_i32),
+                ("cn", c_i32), ("Cpad", c_i32), ("accumulate", c_i32), ("k_off", c_i64), ("ld", c_i64), ("total", c_i64), ("block0", c_i64)]
+
+
+class JobList:
+    """Recorded pack / unpack jobs (see b3d_pack_job) that run as ONE kernel launch.  Built once per engine: parameter,
+    gradient and staging buffers have fixed addresses, so the device-side table is reused every step."""
+
+    def __init__(self, kind):
+        self.kind, self.jobs, self.keep, self.table, self.blocks = kind, [], [], None, 0
+
+    def add(self, src, dst, Co, Ci, taps, mode, ci0, cn, Cpad, k_off, ld, total, accumulate=0):
+        j = _PackJob()
+        j.src, j.dst = src.data_ptr(), dst.data_ptr()
+        j.Co, j.Ci, j.taps, j.mode, j.ci0, j.cn, j.Cpad, j.accumulate = Co, Ci, taps, mode, ci0, cn, Cpad or 0, int(accumulate)
+        j.k_off, j.ld, j.total, j.block0 = k_off, ld, total, self.blocks
+        self.blocks += (total + 1023) // 1024
+        self.jobs.append(j)
+        self.keep.append((src, dst))
+        self.table = None
+
+    def signature(self):
+        return tuple((j.src, j.dst) for j in self.jobs)
+
+
 class CudaOps:
     """The product backend: every method launches kernels of libb3d.so on the current stream."""
 
@@ -234,6 +260,41 @@ class CudaOps:
         self._call("b3d_unpack_wgrad", _ptr(g), c_i64(g.stride(0)), c_i64(k_off), c_i32(Cpad), c_i32(Co), c_i32(Ci), c_i32(taps), c_i32(ci0),
                    c_i32(cn), _ptr(dw), c_i32(int(accumulate)), self.stream())
 
+    # recorded variants: same arguments, but the work is appended to a JobList and runs later in one launch
+    def record_pack_weight(self, jl, w, mode, out, ci0=0, cn=None, Cpad=None, k_off=0):
+        Co, Ci = w.shape[0], w.shape[1]
+        taps = w.numel() // (Co * Ci)
+        cn = Ci if cn is None else cn
+        assert w.dtype == torch.float32 and w.is_contiguous() and out.dim() == 2 and out.stride(1) == 1
+        total = Co * taps * Cpad if mode == 0 else (Ci * taps * Cpad if mode == 1 else Co * Ci * taps)
+        jl.add(w, out, Co, Ci, taps, mode, ci0, cn, Cpad, k_off, out.stride(0), total)
+
+    def record_copy(self, jl, src, dst):
+        assert src.dtype == torch.float32 and dst.dtype == torch.float32 and src.is_contiguous() and dst.is_contiguous()
+        jl.add(src, dst, 0, 0, 1, 3, 0, 0, 0, 0, 0, src.numel())
+
+    def record_unpack_wgrad(self, jl, g, k_off, Cpad, dw, ci0=0, cn=None, accumulate=False):
+        Co, Ci = dw.shape[0], dw.shape[1]
+        taps = dw.numel() // (Co * Ci)
+        cn = Ci if cn is None else cn
+        assert g.dtype == torch.float32 and dw.is_contiguous()
+        jl.add(g, dw, Co, Ci, taps, 0, ci0, cn, Cpad, k_off, g.stride(0), Co * cn * taps, accumulate)
+
+    def run_jobs(self, jl):
+        if not jl.jobs:
+            return
+        if jl.table is None:
+            arr = (_PackJob * len(jl.jobs))(*jl.jobs)
+            host = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8)
+            jl.table = host.to(self.device)
+        name = "b3d_pack_weights_multi" if jl.kind == "pack" else "b3d_unpack_wgrads_multi"
+        self._call(name, _ptr(jl.table), c_i32(len(jl.jobs)), c_i64(jl.blocks), self.stream())
+
+    def scale_colsum(self, a, out, scale, colsum):
+        C = a.shape[-1]
+        assert a.is_contiguous() and out.is_contiguous() and colsum.dtype == torch.float32
+        self._call("b3d_scale_colsum", _ptr(a), _ptr(out), c_f32(scale), c_i64(a.numel() // C), c_i32(C), _ptr(colsum), self.stream())
+
     def cast(self, src, out):
         assert src.dtype == torch.float32 and src.is_contiguous() and out.is_contiguous()
         self._call("b3d_cast_bf16", _ptr(src), _ptr(out), c_i64(src.numel()), self.stream())
@@ -312,12 +373,13 @@ class CudaOps:
                    _ptr(out), c_i64(out.stride(1)), self.stream())
 
     def gn_bwd(self, x0, x1, sums, gamma, beta, mode, dy, dgamma, dbeta, ws, dx0, dx1=None, ss=None, F=0, dss=None, drop_p=0.0, seed=0,
-               add0=None, add1a=None, add1b=None, seed_ptr=None):
+               add0=None, add1a=None, add1b=None, seed_ptr=None, dss_sum=None, dx_sum=None):
         N, HW, _ = x0.shape
         ld = lambda t, i=1: c_i64(t.stride(i) if t is not None else 0)
         self._call("b3d_gn_bwd", *self._src(x0), *self._src(x1), c_i32(N), c_i32(HW), _ptr(sums), _ptr(gamma), _ptr(beta), c_i32(mode),
                    _ptr(dy), ld(dy), _ptr(ss), ld(ss, 0), c_i32(F), _ptr(dss), ld(dss, 0), c_f32(drop_p), ctypes.c_uint64(seed),
-                   _ptr(seed_ptr), _ptr(dgamma), _ptr(dbeta), _ptr(ws), _ptr(dx0), ld(dx0), _ptr(dx1), ld(dx1), _ptr(add0), ld(add0),
+                   _ptr(seed_ptr), _ptr(dgamma), _ptr(dbeta), _ptr(dss_sum), _ptr(dx_sum), _ptr(ws), _ptr(dx0), ld(dx0), _ptr(dx1), ld(dx1),
+                   _ptr(add0), ld(add0),
                    _ptr(add1a), ld(add1a), _ptr(add1b), ld(add1b), self.stream())
 
     # ---- diffusion glue

@@ -101,6 +101,18 @@ int b3d_pack_weight(const float* w, int Co, int Ci, int taps, int mode, int ci0,
 int b3d_unpack_wgrad(const float* g, int64_t g_ld, int64_t k_off, int Cpad, int Co, int Ci, int taps, int ci0, int cn, float* dw,
                      int accumulate, void* stream);
 int b3d_cast_bf16(const float* in, void* out, int64_t n, void* stream);
+/* The same conversions for MANY tensors in one launch (every parameter is repacked each step; one launch instead of
+ * ~450).  `jobs` is a DEVICE array of b3d_pack_job; block0 = running sum of ceil(total/1024) over the jobs.
+ * pack: mode 0/1/2 as b3d_pack_weight, mode 3 = fp32 copy of `total` values.  unpack: as b3d_unpack_wgrad. */
+typedef struct b3d_pack_job {
+  const float* src; void* dst;
+  int32_t Co, Ci, taps, mode, ci0, cn, Cpad, accumulate;
+  int64_t k_off, ld, total, block0;
+} b3d_pack_job;
+int b3d_pack_weights_multi(const void* jobs, int n_jobs, int64_t total_blocks, void* stream);
+int b3d_unpack_wgrads_multi(const void* jobs, int n_jobs, int64_t total_blocks, void* stream);
+/* out = scale*a (bf16 [rows,C]) and colsum[c] += column sums of out (bias gradients fused with the 1/sqrt2 of xunet.py:152,220) */
+int b3d_scale_colsum(const void* a, void* out, float scale, int64_t rows, int C, float* colsum, void* stream);
 /* avgpool_downsample / nearest_neighbor_upsample, xunet.py:17-28 (scale folds the adjoint's 1/4) */
 int b3d_avgpool2(const void* in, void* out, int N, int H, int W, int C, float scale, void* stream);
 int b3d_upsample2(const void* in, void* out, int N, int Ho, int Wo, int C, float scale, void* stream);
@@ -125,14 +137,17 @@ int b3d_softmax_bwd(const void* P, int64_t ld_p, const void* dP, int dp_fp32, in
  * b3d_gn_apply: mode 0 plain (AttnBlock :198), 1 +SiLU (:140,:535), 2 +FiLM(+dropout) (:87,:143-145) with
  *   scale = ss[row, c], shift = ss[row, F + c].
  * b3d_gn_bwd: autograd of the same lines; writes d(scale,shift) to dss, accumulates dgamma/dbeta (fp32),
- *   uses ws_s12 fp32 [N,32,2] (caller zeroes it), writes dx0/dx1 (+ add0 + add1a/add1b when given). */
+ *   uses ws_s12 fp32 [N,32,2] (caller zeroes it), writes dx0/dx1 (+ add0 + add1a/add1b when given).  Optional fused
+ *   reductions (fp32, accumulated): dss_sum [2F] = column sums of dss (FiLM dense bias gradient, xunet.py:80),
+ *   dx_sum [C] = column sums of dx before the addends (bias gradient of the layer that produced x). */
 int b3d_gn_stats(const void* x0, int C0, int64_t ld0, const void* x1, int C1, int64_t ld1, int N, int HW, float* ws_sums, void* stream);
 int b3d_gn_apply(const void* x0, int C0, int64_t ld0, const void* x1, int C1, int64_t ld1, int N, int HW, const float* sums,
                  const float* gamma, const float* beta, int mode, const void* ss, int64_t ld_ss, int F, float drop_p, uint64_t seed, const uint64_t* seed_ptr,
                  void* out, int64_t ld_out, void* stream);
 int b3d_gn_bwd(const void* x0, int C0, int64_t ld0, const void* x1, int C1, int64_t ld1, int N, int HW, const float* sums,
                const float* gamma, const float* beta, int mode, const void* dy, int64_t ld_dy, const void* ss, int64_t ld_ss, int F,
-               void* dss, int64_t ld_dss, float drop_p, uint64_t seed, const uint64_t* seed_ptr, float* dgamma, float* dbeta, float* ws_s12, void* dx0,
+               void* dss, int64_t ld_dss, float drop_p, uint64_t seed, const uint64_t* seed_ptr, float* dgamma, float* dbeta, float* dss_sum,
+               float* dx_sum, float* ws_s12, void* dx0,
                int64_t ld_dx0, void* dx1, int64_t ld_dx1, const void* add0, int64_t ld_add0, const void* add1a, int64_t ld_add1a,
                const void* add1b, int64_t ld_add1b, void* stream);
 

@@ -245,6 +245,25 @@ class EmuOps:
         else:
             dst.copy_(blk)
 
+    # recorded variants (one-launch job lists on the GPU): here the jobs are closures replayed by run_jobs
+    def record_pack_weight(self, jl, w, mode, out, ci0=0, cn=None, Cpad=None, k_off=0):
+        jl.jobs.append(lambda: self.pack_weight(w, mode, out, ci0, cn, Cpad, k_off))
+
+    def record_copy(self, jl, src, dst):
+        jl.jobs.append(lambda: dst.copy_(src))
+
+    def record_unpack_wgrad(self, jl, g, k_off, Cpad, dw, ci0=0, cn=None, accumulate=False):
+        jl.jobs.append(lambda: self.unpack_wgrad(g, k_off, Cpad, dw, ci0, cn, accumulate))
+
+    def run_jobs(self, jl):
+        for j in jl.jobs:
+            j()
+
+    def scale_colsum(self, a, out, scale, colsum):
+        v = a.float() * scale
+        out.copy_(v.to(out.dtype))
+        colsum += v.reshape(-1, a.shape[-1]).sum(0)
+
     def cast(self, src, out):
         out.copy_(src.to(out.dtype))
 
@@ -339,7 +358,7 @@ class EmuOps:
         out.copy_(y.to(out.dtype))
 
     def gn_bwd(self, x0, x1, sums, gamma, beta, mode, dy, dgamma, dbeta, ws, dx0, dx1=None, ss=None, F=0, dss=None, drop_p=0.0, seed=0,
-               add0=None, add1a=None, add1b=None, seed_ptr=None):
+               add0=None, add1a=None, add1b=None, seed_ptr=None, dss_sum=None, dx_sum=None):
         seed = seed + (int(seed_ptr.item()) if seed_ptr is not None else 0)
         x = self._cat(x0, x1)
         N, HW, C = x.shape
@@ -352,6 +371,9 @@ class EmuOps:
             d = d * self._mask(d.shape, drop_p, seed)
             dss[:, :F] = (d * z).reshape(N * HW, F).to(dss.dtype)
             dss[:, F:2 * F] = d.reshape(N * HW, F).to(dss.dtype)
+            if dss_sum is not None:
+                dss_sum[:F] += (d * z).sum((0, 1))
+                dss_sum[F:2 * F] += d.sum((0, 1))
             d = d * (1 + ss[:, :F].float().reshape(N, HW, F))
         dgamma += (d * xh).sum((0, 1))
         dbeta += d.sum((0, 1))
@@ -365,6 +387,8 @@ class EmuOps:
         s1c = (s1 / cnt).repeat_interleave(cpg, 1)[:, None, :]
         s2c = (s2 / cnt).repeat_interleave(cpg, 1)[:, None, :]
         dx = rstd_c * (dg - s1c - xh * s2c)
+        if dx_sum is not None:
+            dx_sum += dx.sum((0, 1))
         if add0 is not None:
             dx = dx + add0.float()
         C0 = x0.shape[-1]

@@ -104,6 +104,28 @@ def misc_case(seed=0):
         ops.unpack_wgrad(gpk, 64, 64, dw, ci0=8, cn=16)
         ops.unpack_wgrad(gpk, 64, 64, dw, ci0=8, cn=16, accumulate=True)
         outs.append(dw)
+        # the same conversions through recorded job lists (one launch)
+        from distributed_3d_diffusion_pytorch_b200.ops import JobList
+        jl = JobList("pack")
+        wd = w.to(dev)
+        q0, q1, q2 = ops.zeros((40, 64 + 9 * 64)), ops.zeros((24, 9 * 64 + 64)), ops.zeros((9 * 24, 40))
+        ops.record_pack_weight(jl, wd, 0, q0, ci0=8, cn=16, Cpad=64, k_off=64)
+        ops.record_pack_weight(jl, wd, 1, q1, Cpad=64, k_off=64)
+        ops.record_pack_weight(jl, wd, 2, q2)
+        bsrc, bdst = torch.randn(50, generator=g).to(dev), ops.zeros((64,), torch.float32)
+        ops.record_copy(jl, bsrc, bdst[8:58])
+        ops.run_jobs(jl)
+        outs += [q0, q1, q2, bdst]
+        ju = JobList("unpack")
+        dw2 = ops.zeros((40, 24, 3, 3), torch.float32)
+        ops.record_unpack_wgrad(ju, gpk, 64, 64, dw2, ci0=8, cn=16)
+        ops.record_unpack_wgrad(ju, gpk, 64, 64, dw2, ci0=0, cn=8, accumulate=True)
+        ops.run_jobs(ju)
+        outs.append(dw2)
+        sc_in = _mk(ops, _r((300, 96), g))
+        sc_out, sc_sum = ops.zeros((300, 96)), ops.zeros((96,), torch.float32)
+        ops.scale_colsum(sc_in, sc_out, 0.70710678, sc_sum)
+        outs += [sc_out, sc_sum]
         # resampling
         t = _mk(ops, _r((2, 8, 8, 32), g))
         p = ops.zeros((2, 4, 4, 32)); ops.avgpool2(t, p); outs.append(p)

@@ -471,16 +471,14 @@ __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, 
 // gradients that equal its column sums: conv2.bias, dense.bias, linear.bias)
 __global__ void __launch_bounds__(256) scale_colsum_kernel(const bf16* __restrict__ a, bf16* __restrict__ out, float scale, long long rows, int C,
                                                            int rows_per_block, float* __restrict__ colsum) {
-  extern __shared__ float sm[];   // [C]
+  extern __shared__ float sm[];   // red [256*8] (plain stores: shared fp32 atomics are CAS spin loops)
   constexpr int U = 4;
   const int vecs = C / 8;
-  for (int i = threadIdx.x; i < C; i += blockDim.x) sm[i] = 0.f;
-  __syncthreads();
   const int rows_par = max(1, (int)blockDim.x / vecs);
   const int v = threadIdx.x % vecs, rsub = threadIdx.x / vecs;
   const long long r0 = (long long)blockIdx.x * rows_per_block, r1 = min(rows, r0 + rows_per_block);
+  float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   if (rsub < rows_par) {
-    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     for (long long r = r0 + rsub; r < r1; r += (long long)rows_par * U) {
       bf16x8 x[U];
 #pragma unroll
@@ -501,10 +499,14 @@ __global__ void __launch_bounds__(256) scale_colsum_kernel(const bf16* __restric
       }
     }
 #pragma unroll
-    for (int j = 0; j < 8; ++j) atomicAdd(&sm[v * 8 + j], acc[j]);
+    for (int j = 0; j < 8; ++j) sm[rsub * C + v * 8 + j] = acc[j];
   }
   __syncthreads();
-  for (int c = threadIdx.x; c < C; c += blockDim.x) atomicAdd(&colsum[c], sm[c]);
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float s = 0.f;
+    for (int r = 0; r < rows_par; ++r) s += sm[r * C + c];
+    atomicAdd(&colsum[c], s);
+  }
 }
 
 // many weight tensors in ONE launch (the per-step repack of every parameter / the unpack of every packed gradient):
@@ -773,7 +775,7 @@ extern "C" int b3d_scale_colsum(const void* a, void* out, float scale, int64_t r
   const int min_rows = rows_par * 4;
   if (rpb < min_rows) rpb = min_rows;
   rpb = (rpb + min_rows - 1) / min_rows * min_rows;
-  scale_colsum_kernel<<<cdiv(rows, rpb), 256, C * sizeof(float), STREAM>>>((const bf16*)a, (bf16*)out, scale, rows, C, (int)rpb, colsum);
+  scale_colsum_kernel<<<cdiv(rows, rpb), 256, 2048 * sizeof(float), STREAM>>>((const bf16*)a, (bf16*)out, scale, rows, C, (int)rpb, colsum);
   DONE(1);
 }
 // jobs: device array of b3d_pack_job (include/b3d.h) whose block0 fields are the running sum of ceil(total/1024)

@@ -53,22 +53,40 @@ __device__ __forceinline__ RowPtr src_ptr(const Src2& s, int c0) {
 __device__ __forceinline__ bf16x8 ld8(const bf16* p) { return *reinterpret_cast<const bf16x8*>(p); }
 __device__ __forceinline__ bf16x8 zero8() { bf16x8 z; z.u = make_uint4(0u, 0u, 0u, 0u); return z; }
 
+// Block-level sum of per-thread 8-channel partials over the rows_par threads that own the same channel vector.
+// Plain stores + a strided read-back: shared-memory fp32 atomicAdd compiles to a CAS spin loop (ATOMS.CAST.SPIN) and,
+// with rows_par-way contention per address, cost as much as the whole streaming loop.
+// red: smem [256*8]; result: smem [C].  All threads of the block must call it.
+__device__ __forceinline__ void block_sum8(const float* vals, bool active, int v, int rsub, int rows_par, int C, float* red, float* result) {
+  if (active) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) red[rsub * C + v * 8 + j] = vals[j];
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float s = 0.f;
+    for (int r = 0; r < rows_par; ++r) s += red[r * C + c];
+    result[c] = s;
+  }
+  __syncthreads();
+}
+
 // ---- stats: raw (sum, sumsq) per (image, group) accumulated with fp32 atomics into ws[N,32,2] (pre-zeroed)
 __global__ void __launch_bounds__(kT) gn_stats_kernel(Src2 s, int HW, int rows_per_block, float* __restrict__ ws) {
-  extern __shared__ float sm[];  // [C][2]
+  extern __shared__ float sm[];  // red [256*8] | sum [C] | sumsq [C]
   constexpr int U = 4;
   const int C = s.C0 + s.C1, cpg = C / G, n = blockIdx.y, vecs = C / 8;
-  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) sm[i] = 0.f;
-  __syncthreads();
+  float* red = sm; float* r_a = sm + 2048; float* r_b = r_a + C;
   const int r0 = blockIdx.x * rows_per_block, r1 = min(HW, r0 + rows_per_block);
   const int rows_par = max(1, (int)blockDim.x / vecs);
   const int v = threadIdx.x % vecs, rsub = threadIdx.x / vecs;
-  if (rsub < rows_par) {
+  const bool active = rsub < rows_par;
+  float a[8], b[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { a[i] = 0.f; b[i] = 0.f; }
+  if (active) {
     const RowPtr rp = src_ptr(s, v * 8);
     const bf16* base = rp.p + (long long)n * HW * rp.ld;
-    float a[8], b[8];
-#pragma unroll
-    for (int i = 0; i < 8; ++i) { a[i] = 0.f; b[i] = 0.f; }
     for (int r = r0 + rsub; r < r1; r += rows_par * U) {
       bf16x8 x[U];
 #pragma unroll
@@ -80,13 +98,12 @@ __global__ void __launch_bounds__(kT) gn_stats_kernel(Src2 s, int HW, int rows_p
         for (int i = 0; i < 8; ++i) { a[i] += f[i]; b[i] += f[i] * f[i]; }
       }
     }
-#pragma unroll
-    for (int i = 0; i < 8; ++i) { atomicAdd(&sm[2 * (v * 8 + i)], a[i]); atomicAdd(&sm[2 * (v * 8 + i) + 1], b[i]); }
   }
-  __syncthreads();
+  block_sum8(a, active, v, rsub, rows_par, C, red, r_a);
+  block_sum8(b, active, v, rsub, rows_par, C, red, r_b);
   for (int g = threadIdx.x; g < G; g += blockDim.x) {
     float sa = 0.f, sb = 0.f;
-    for (int c = g * cpg; c < (g + 1) * cpg; ++c) { sa += sm[2 * c]; sb += sm[2 * c + 1]; }
+    for (int c = g * cpg; c < (g + 1) * cpg; ++c) { sa += r_a[c]; sb += r_b[c]; }
     atomicAdd(&ws[((long long)n * G + g) * 2], sa);
     atomicAdd(&ws[((long long)n * G + g) * 2 + 1], sb);
   }
@@ -192,28 +209,27 @@ __device__ __forceinline__ void bwd_dz(const BwdP& p, const Chan& ch, const bf16
 
 // pass 1: d_scale/d_shift (film), dgamma/dbeta, per-(image,group) S1 = sum dz*gamma, S2 = sum dz*gamma*xhat
 __global__ void __launch_bounds__(kT, 2) gn_bwd_reduce_kernel(BwdP p, int rows_per_block) {
-  extern __shared__ float sm[];  // [C][2] dgamma,dbeta partials, [G][2], then [C][2] column sums of (d_scale, d_shift)
+  extern __shared__ float sm[];  // red [256*8] | dgamma [C] | dbeta [C] | dscale-sum [C] | dshift-sum [C]
   __shared__ float s_mean[G], s_rstd[G];
   constexpr int U = 2;
   const int C = p.s.C0 + p.s.C1, cpg = C / G, n = blockIdx.y, vecs = C / 8;
-  float* s_gs = sm + 2 * C;
-  float* s_ss = s_gs + 2 * G;
+  float* red = sm; float* r_g = sm + 2048; float* r_b = r_g + C; float* r_sc = r_b + C; float* r_sh = r_sc + C;
   const bool want_ss = p.mode == 2 && p.dss_sum != nullptr;
-  for (int i = threadIdx.x; i < 2 * C + 2 * G + (want_ss ? 2 * C : 0); i += blockDim.x) sm[i] = 0.f;
   block_stats(p.stats, n, cpg, p.HW, s_mean, s_rstd);
   __syncthreads();
   const int r0 = blockIdx.x * rows_per_block, r1 = min(p.HW, r0 + rows_per_block);
   const int rows_par = max(1, (int)blockDim.x / vecs);
   const int v = threadIdx.x % vecs, rsub = threadIdx.x / vecs, c0 = v * 8;
-  if (rsub < rows_par) {
+  const bool active = rsub < rows_par;
+  float ag[8], ab[8], asc[8], ash[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { ag[j] = 0.f; ab[j] = 0.f; asc[j] = 0.f; ash[j] = 0.f; }
+  if (active) {
     Chan ch; load_chan(ch, p.gamma, p.beta, c0, cpg, s_mean, s_rstd);
     const RowPtr rp = src_ptr(p.s, c0);
     const long long img = (long long)n * p.HW;
     const float keep = 1.f / (1.f - p.drop_p);
     const unsigned long long seed = p.seed + (p.seed_ptr ? *p.seed_ptr : 0ULL);
-    float ag[8], ab[8], asc[8], ash[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) { ag[j] = 0.f; ab[j] = 0.f; asc[j] = 0.f; ash[j] = 0.f; }
     for (int r = r0 + rsub; r < r1; r += rows_par * U) {
       bf16x8 x[U], dy[U], sc[U];
 #pragma unroll
@@ -233,50 +249,39 @@ __global__ void __launch_bounds__(kT, 2) gn_bwd_reduce_kernel(BwdP p, int rows_p
         if (p.mode == 2) {
           *reinterpret_cast<bf16x8*>(p.dss + row * p.ld_dss + c0) = b3d_pack8(dsc);
           *reinterpret_cast<bf16x8*>(p.dss + row * p.ld_dss + p.F + c0) = b3d_pack8(dsh);
-          if (want_ss) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) { asc[j] += dsc[j]; ash[j] += dsh[j]; }
-          }
+          for (int j = 0; j < 8; ++j) { asc[j] += dsc[j]; ash[j] += dsh[j]; }
         }
 #pragma unroll
         for (int j = 0; j < 8; ++j) { ag[j] += dz[j] * xh[j]; ab[j] += dz[j]; }
       }
     }
-#pragma unroll
-    for (int j = 0; j < 8; ++j) { atomicAdd(&sm[2 * (c0 + j)], ag[j]); atomicAdd(&sm[2 * (c0 + j) + 1], ab[j]); }
-    if (want_ss) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) { atomicAdd(&s_ss[2 * (c0 + j)], asc[j]); atomicAdd(&s_ss[2 * (c0 + j) + 1], ash[j]); }
-    }
   }
-  __syncthreads();
+  block_sum8(ag, active, v, rsub, rows_par, C, red, r_g);
+  block_sum8(ab, active, v, rsub, rows_par, C, red, r_b);
   if (want_ss) {
-    for (int c = threadIdx.x; c < C; c += blockDim.x) {
-      atomicAdd(&p.dss_sum[c], s_ss[2 * c]);
-      atomicAdd(&p.dss_sum[p.F + c], s_ss[2 * c + 1]);
-    }
+    block_sum8(asc, active, v, rsub, rows_par, C, red, r_sc);
+    block_sum8(ash, active, v, rsub, rows_par, C, red, r_sh);
   }
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
-    const float dg = sm[2 * c], db = sm[2 * c + 1], gam = p.gamma[c];
-    atomicAdd(&p.dgamma[c], dg);
-    atomicAdd(&p.dbeta[c], db);
-    atomicAdd(&s_gs[2 * (c / cpg)], db * gam);       // S1
-    atomicAdd(&s_gs[2 * (c / cpg) + 1], dg * gam);   // S2
+    atomicAdd(&p.dgamma[c], r_g[c]);
+    atomicAdd(&p.dbeta[c], r_b[c]);
+    if (want_ss) { atomicAdd(&p.dss_sum[c], r_sc[c]); atomicAdd(&p.dss_sum[p.F + c], r_sh[c]); }
   }
-  __syncthreads();
   if (threadIdx.x < G) {
-    atomicAdd(&p.ws[((long long)n * G + threadIdx.x) * 2], s_gs[2 * threadIdx.x]);
-    atomicAdd(&p.ws[((long long)n * G + threadIdx.x) * 2 + 1], s_gs[2 * threadIdx.x + 1]);
+    float s1 = 0.f, s2 = 0.f;
+    for (int c = threadIdx.x * cpg; c < (threadIdx.x + 1) * cpg; ++c) { const float gam = p.gamma[c]; s1 += r_b[c] * gam; s2 += r_g[c] * gam; }
+    atomicAdd(&p.ws[((long long)n * G + threadIdx.x) * 2], s1);
+    atomicAdd(&p.ws[((long long)n * G + threadIdx.x) * 2 + 1], s2);
   }
 }
 
 // pass 2: dx = rstd * (dz*gamma - (S1 + xhat*S2)/cnt) [+ add0] [+ add1]
 __global__ void __launch_bounds__(kT, 2) gn_bwd_apply_kernel(BwdP p, int rows_per_block) {
-  extern __shared__ float sm[];   // [C] column sums of dx when p.dx_sum is set
+  extern __shared__ float sm[];   // red [256*8] | column sums of dx [C]   (used when p.dx_sum is set)
   __shared__ float s_mean[G], s_rstd[G], s_s1[G], s_s2[G];
   constexpr int U = 2;
   const int C = p.s.C0 + p.s.C1, cpg = C / G, n = blockIdx.y, vecs = C / 8;
-  if (p.dx_sum) for (int i = threadIdx.x; i < C; i += blockDim.x) sm[i] = 0.f;
   block_stats(p.stats, n, cpg, p.HW, s_mean, s_rstd);
   if (threadIdx.x < G) {
     const float cnt = (float)cpg * (float)p.HW;
@@ -287,11 +292,13 @@ __global__ void __launch_bounds__(kT, 2) gn_bwd_apply_kernel(BwdP p, int rows_pe
   const int r0 = blockIdx.x * rows_per_block, r1 = min(p.HW, r0 + rows_per_block);
   const int rows_par = max(1, (int)blockDim.x / vecs);
   const int v = threadIdx.x % vecs, rsub = threadIdx.x / vecs, c0 = v * 8;
-  if (rsub < rows_par) {
-  Chan ch; load_chan(ch, p.gamma, p.beta, c0, cpg, s_mean, s_rstd);
-  float s1[8], s2[8], acc[8];
+  const bool active = rsub < rows_par;
+  float acc[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+  if (active) {
+  Chan ch; load_chan(ch, p.gamma, p.beta, c0, cpg, s_mean, s_rstd);
+  float s1[8], s2[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) { const int g = (c0 + j) / cpg; s1[j] = s_s1[g]; s2[j] = s_s2[g]; }
   const RowPtr rp = src_ptr(p.s, c0);
@@ -332,14 +339,10 @@ __global__ void __launch_bounds__(kT, 2) gn_bwd_apply_kernel(BwdP p, int rows_pe
       *reinterpret_cast<bf16x8*>(dxp + row * ld_dx + c1) = b3d_pack8(dx);
     }
   }
-  if (p.dx_sum) {
-#pragma unroll
-    for (int j = 0; j < 8; ++j) atomicAdd(&sm[c0 + j], acc[j]);
-  }
   }
   if (p.dx_sum) {
-    __syncthreads();
-    for (int c = threadIdx.x; c < C; c += blockDim.x) atomicAdd(&p.dx_sum[c], sm[c]);
+    block_sum8(acc, active, v, rsub, rows_par, C, sm, sm + 2048);
+    for (int c = threadIdx.x; c < C; c += blockDim.x) atomicAdd(&p.dx_sum[c], sm[2048 + c]);
   }
 }
 
@@ -374,7 +377,7 @@ extern "C" int b3d_gn_stats(const void* x0, int C0, int64_t ld0, const void* x1,
   Src2 s{(const bf16*)x0, (const bf16*)x1, C0, C1, ld0, ld1};
   const int C = C0 + C1, rpb = pick_rows_per_block(N, HW, C, 4);
   dim3 grid((HW + rpb - 1) / rpb, N);
-  gn_stats_kernel<<<grid, kT, 2 * C * sizeof(float), (cudaStream_t)stream>>>(s, HW, rpb, ws_sums);
+  gn_stats_kernel<<<grid, kT, (2048 + 2 * C) * sizeof(float), (cudaStream_t)stream>>>(s, HW, rpb, ws_sums);
   B3D_LAUNCH_CHECK();
   b3d_count_launch(1);
   return B3D_OK;
@@ -419,9 +422,9 @@ extern "C" int b3d_gn_bwd(const void* x0, int C0, int64_t ld0, const void* x1, i
   p.add1a = (const bf16*)add1a; p.add1b = (const bf16*)add1b; p.ld_add1a = ld_add1a; p.ld_add1b = ld_add1b;
   const int C = C0 + C1, rpb = pick_rows_per_block(N, HW, C, 2);
   dim3 grid((HW + rpb - 1) / rpb, N);
-  gn_bwd_reduce_kernel<<<grid, kT, (4 * C + 2 * G) * sizeof(float), (cudaStream_t)stream>>>(p, rpb);
+  gn_bwd_reduce_kernel<<<grid, kT, (2048 + 4 * C) * sizeof(float), (cudaStream_t)stream>>>(p, rpb);
   B3D_LAUNCH_CHECK();
-  gn_bwd_apply_kernel<<<grid, kT, C * sizeof(float), (cudaStream_t)stream>>>(p, rpb);
+  gn_bwd_apply_kernel<<<grid, kT, (2048 + C) * sizeof(float), (cudaStream_t)stream>>>(p, rpb);
   B3D_LAUNCH_CHECK();
   b3d_count_launch(2);
   return B3D_OK;

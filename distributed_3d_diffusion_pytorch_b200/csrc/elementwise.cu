@@ -454,6 +454,28 @@ __global__ void sampler_update_kernel(const float* __restrict__ z, const float* 
   }
 }
 
+// same update with the two schedule values read from device memory (sched[0] = logsnr, sched[1] = logsnr_next), so a
+// captured CUDA graph of one denoise step can be replayed for all 256 steps
+__global__ void sampler_update_dev_kernel(const float* __restrict__ z, const float* __restrict__ eps_c, const float* __restrict__ eps_u,
+                                          const float* __restrict__ w, const float* __restrict__ noise, float* __restrict__ out,
+                                          const float* __restrict__ sched, long long per, long long total) {
+  const float l0 = sched[0], l1 = sched[1];
+  const float c = -expm1f(l0 - l1);
+  const float alpha = sqrtf(1.f / (1.f + expf(-l0))), sigma = sqrtf(1.f / (1.f + expf(l0)));
+  const float alpha_next = sqrtf(1.f / (1.f + expf(-l1))), std_next = sqrtf(c / (1.f + expf(l1)));
+  const bool add_noise = l1 != 0.f;          // sampling.py:124
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const float ww = w[i / per];
+    const float e = (1.f + ww) * eps_c[i] - ww * eps_u[i];
+    const float zz = z[i];
+    float x0 = (zz - sigma * e) / alpha;
+    x0 = fminf(fmaxf(x0, -1.f), 1.f);
+    float m = alpha_next * (zz * (1.f - c) / alpha + c * x0);
+    if (add_noise) m += std_next * noise[i];
+    out[i] = m;
+  }
+}
+
 // fused Adam over one flat fp32 parameter arena (train.py:235: lr 1e-4, betas (0.9, 0.99), eps 1e-8)
 __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v, long long n,
                             float lr, float b1, float b2, float eps, float bc1, float bc2, float grad_scale) {
@@ -758,6 +780,13 @@ extern "C" int b3d_sampler_update(const float* z, const float* eps_c, const floa
   B3D_CHECK_ARG(!add_noise || noise, "sampler_update: noise required");
   sampler_update_kernel<<<grid_for((long long)B * per_sample), kT, 0, STREAM>>>(z, eps_c, eps_u, w, noise, out, sqrtf(sa), sqrtf(ss), sqrtf(san), c,
                                                                               sqrtf(ssn * c), add_noise, per_sample, (long long)B * per_sample);
+  DONE(1);
+}
+extern "C" int b3d_sampler_update_dev(const float* z, const float* eps_c, const float* eps_u, const float* w, const float* noise, float* out,
+                                      const float* sched_dev, int B, int64_t per_sample, void* stream) {
+  B3D_CHECK_ARG(z && eps_c && eps_u && w && noise && out && sched_dev, "sampler_update_dev: null");
+  sampler_update_dev_kernel<<<grid_for((long long)B * per_sample), kT, 0, STREAM>>>(z, eps_c, eps_u, w, noise, out, sched_dev, per_sample,
+                                                                                  (long long)B * per_sample);
   DONE(1);
 }
 extern "C" int b3d_adam(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2, float eps, int step,

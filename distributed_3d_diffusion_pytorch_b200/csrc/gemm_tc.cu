@@ -618,18 +618,24 @@ int make_map(CUtensorMap* tm, const b3d_view4& v, const uint32_t box[4], const u
 
 int pow2_ceil(int v) { int p = 1; while (p < v) p <<= 1; return p; }
 
-int choose_bn(int n_cols, int b_major) {
-  if (n_cols <= 256) {
-    int bn = (n_cols + 15) / 16 * 16;
-    return bn;
+int choose_bn(int n_cols, int b_major, long long tiles_other) {
+  // widest tile that wastes the fewest padded columns ...
+  int best = 128;
+  if (n_cols <= 256) best = (n_cols + 15) / 16 * 16;
+  else {
+    const int cands[] = {256, 192, 128, 64};
+    long long best_cost = -1;
+    for (int c : cands) {
+      long long tiles = (n_cols + c - 1) / c;
+      long long cost = tiles * c;  // padded columns computed
+      if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = c; }
+    }
   }
-  const int cands[] = {256, 192, 128, 64};
-  int best = 128; long long best_cost = -1;
-  for (int c : cands) {
-    long long tiles = (n_cols + c - 1) / c;
-    long long cost = tiles * c;  // padded columns computed
-    if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = c; }
-  }
+  // ... but a launch that cannot fill the 148 SMs is narrowed (down to 128, then 64 columns) while that adds CTAs:
+  // a half-empty GPU costs more than the lower MMA/shared-memory efficiency of a narrower tile
+  const long long sms = b3d_num_sms();
+  // (tiles stay multiples of 64 columns: the TMA-store epilogue writes 64-column boxes)
+  while (best >= 128 && (best / 2) % 64 == 0 && tiles_other * ((n_cols + best - 1) / best) < sms) best /= 2;
   (void)b_major;
   return best;
 }
@@ -659,7 +665,23 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
   p.split_k = d->split_k > 0 ? d->split_k : 1;
   B3D_CHECK_ARG(p.W > 0 && p.H > 0 && p.N > 0, "b3d_gemm: W/H/N");
 
-  int BN = d->bn_tile > 0 ? d->bn_tile : choose_bn(d->n_cols, d->b_major);
+  int BN = d->bn_tile;
+  if (BN <= 0) {
+    // number of tiles in all other grid dimensions, to see whether the launch can fill the GPU
+    long long other;
+    if (d->a_major == 0) {
+      const int bw = d->W < BM ? d->W : BM;
+      int bh = 1, bnn = 1;
+      if (!d->batched) {
+        bh = BM / bw; if (bh > d->H) bh = d->H; if (bh < 1) bh = 1;
+        bnn = (bh == d->H) ? BM / (bw * bh) : 1; if (bnn > d->N) bnn = d->N; if (bnn < 1) bnn = 1;
+      }
+      other = (long long)((d->W + bw - 1) / bw) * ((d->H + bh - 1) / bh) * ((d->N + bnn - 1) / bnn);
+    } else {
+      other = (long long)((d->m_rows + BM - 1) / BM) * (d->batched ? (long long)d->H * d->N : 1) * p.b_taps * p.split_k;
+    }
+    BN = choose_bn(d->n_cols, d->b_major, other);
+  }
   B3D_CHECK_ARG(BN % 16 == 0 && BN >= 16 && BN <= 256, "b3d_gemm: tile N %d must be a multiple of 16 in [16,256]", BN);
   p.BN = BN;
   p.tiles_n = (d->n_cols + BN - 1) / BN;

@@ -402,6 +402,12 @@ class CudaOps:
         self._call("b3d_sampler_update", _ptr(z), _ptr(eps_c), _ptr(eps_u), _ptr(w), _ptr(noise), _ptr(out), c_f32(float(logsnr)),
                    c_f32(float(logsnr_next)), c_i32(B), c_i64(z.numel() // B), self.stream())
 
+    def sampler_update_dev(self, z, eps_c, eps_u, w, noise, out, sched):
+        B = z.shape[0]
+        assert sched.dtype == torch.float32 and sched.numel() >= 2
+        self._call("b3d_sampler_update_dev", _ptr(z), _ptr(eps_c), _ptr(eps_u), _ptr(w), _ptr(noise), _ptr(out), _ptr(sched), c_i32(B),
+                   c_i64(z.numel() // B), self.stream())
+
     def adam(self, p, g, m, v, lr, beta1, beta2, eps, step, grad_scale=1.0):
         self._call("b3d_adam", _ptr(p), _ptr(g), _ptr(m), _ptr(v), c_i64(p.numel()), c_f32(lr), c_f32(beta1), c_f32(beta2), c_f32(eps),
                    c_i32(step), c_f32(grad_scale), self.stream())

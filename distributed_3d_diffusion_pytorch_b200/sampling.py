@@ -156,3 +156,82 @@ def sample_object(model, views, K, w, timesteps=256, max_views=None, generator=N
                      timesteps=timesteps, generator=generator)
         record.append([img, np.asarray(R), np.asarray(T)])
     return record
+
+
+class GraphSampler:
+    """One denoise step (sampling.py:115-127) on static device buffers, captured once in a CUDA graph and replayed for
+    every step / view: conditional + unconditional UNet forward as one batch-2b pass, then the fused update kernel.
+    Per step the host only picks the conditioning entry (python `random`, as the reference) and copies two scalars."""
+
+    def __init__(self, model, b, use_graph=True):
+        m = model.module if hasattr(model, "module") else model
+        self.model, self.b, self.dev = m, b, _dev(m)
+        self.ops = _ops(self.dev)
+        H, W = m.H, m.W
+        f32 = dict(dtype=torch.float32, device=self.dev)
+        self.z = torch.zeros(b, 3, H, W, **f32)
+        self.xz = torch.zeros(2 * b, 3, H, W, **f32)          # z duplicated for the cond / uncond halves
+        self.x = torch.zeros(2 * b, 3, H, W, **f32)           # [conditioning image | randn]
+        self.noise = torch.zeros(b, 3, H, W, **f32)
+        self.R = torch.zeros(2 * b, 2, 3, 3, dtype=torch.float64, device=self.dev)
+        self.T = torch.zeros(2 * b, 2, 3, dtype=torch.float64, device=self.dev)
+        self.K = torch.zeros(2 * b, 3, 3, dtype=torch.float64, device=self.dev)
+        self.w = torch.zeros(b, **f32)
+        self.sched = torch.zeros(2, **f32)
+        self.logsnr2 = torch.zeros(2 * b, 2, **f32)
+        self.logsnr2[:, 0] = float(logsnr_schedule_cosine(torch.zeros(1))[0])
+        self.mask = torch.cat([torch.ones(b, dtype=torch.uint8), torch.zeros(b, dtype=torch.uint8)]).to(self.dev)
+        self.out = torch.zeros(b, 3, H, W, **f32)
+        self.engine = m._engine(2 * b)
+        self.use_graph, self.graph, self.steps_done = use_graph, None, 0
+
+    def _compute(self):
+        b = self.b
+        self.x[b:].normal_()                                     # batch['x'] = randn_like(x)        (sampling.py:98)
+        self.noise.normal_()                                     # randn_like(x) of p_sample          (sampling.py:127)
+        self.xz[:b].copy_(self.z)
+        self.xz[b:].copy_(self.z)
+        self.logsnr2[:, 1].copy_(self.sched[0].expand(2 * b))
+        P = dict(zip(self.model._names, self.model._plist))
+        eps = self.engine.forward(P, self.x, self.xz, self.logsnr2, self.R, self.T, self.K, self.mask, training=self.model.training,
+                                  need_bwd=False, seed=0, repack=self.steps_done == 0)     # weights are frozen while sampling
+        self.ops.sampler_update_dev(self.z, eps[:b], eps[b:], self.w, self.noise, self.out, self.sched)
+        self.z.copy_(self.out)
+
+    def set_views(self, cond_img, cond_R, cond_T, target_R, target_T, K):
+        b = self.b
+        self.x[:b].copy_(_t(cond_img, self.dev, torch.float32))
+        R = torch.stack([_t(cond_R, self.dev, torch.float64), _t(target_R, self.dev, torch.float64)], 0)
+        T = torch.stack([_t(cond_T, self.dev, torch.float64), _t(target_T, self.dev, torch.float64)], 0)
+        self.R.copy_(R[None].expand(2 * b, 2, 3, 3))
+        self.T.copy_(T[None].expand(2 * b, 2, 3))
+        K = _t(K, self.dev, torch.float64)
+        self.K.copy_(K[None].expand(2 * b, 3, 3) if K.dim() == 2 else K.repeat(2, 1, 1))
+
+    def step(self, logsnr, logsnr_next):
+        self.sched[0] = float(logsnr)
+        self.sched[1] = float(logsnr_next)
+        if self.use_graph and self.graph is None and self.steps_done >= 1:
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._compute()
+            self.graph = g
+        if self.graph is not None:
+            self.graph.replay()
+        else:
+            self._compute()
+        self.steps_done += 1
+
+    @torch.no_grad()
+    def sample(self, record, target_R, target_T, K, w, timesteps=256):
+        """sampling.py:130-155 on the captured step"""
+        self.w.copy_(_t(w, self.dev, torch.float32))
+        self.z.normal_()
+        ts = torch.linspace(1., 0., timesteps + 1)
+        logsnrs, logsnr_nexts = logsnr_schedule_cosine(ts[:-1]), logsnr_schedule_cosine(ts[1:])
+        for l0, l1 in zip(logsnrs, logsnr_nexts):
+            ci, cR, cT = random.choice(record)
+            self.set_views(ci, cR, cT, target_R, target_T, K)
+            self.step(l0, l1)
+        return self.z.cpu().numpy()

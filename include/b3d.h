@@ -177,6 +177,9 @@ int b3d_loss_static(const float* noise, const float* pred, float* dpred, int64_t
 /* p_mean_variance + p_sample arithmetic given both UNet outputs: sampling.py:79-127 (noise skipped iff logsnr_next == 0) */
 int b3d_sampler_update(const float* z, const float* eps_c, const float* eps_u, const float* w, const float* noise, float* out,
                        float logsnr, float logsnr_next, int B, int64_t per_sample, void* stream);
+/* the same update with (logsnr, logsnr_next) read from two device floats: one captured graph serves all 256 steps */
+int b3d_sampler_update_dev(const float* z, const float* eps_c, const float* eps_u, const float* w, const float* noise, float* out,
+                           const float* sched_dev, int B, int64_t per_sample, void* stream);
 /* torch.optim.Adam(lr, betas) step over a flat fp32 arena: train.py:235,278 / lightning/diff3d.py:106 */
 int b3d_adam(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2, float eps, int step,
              float grad_scale, void* stream);

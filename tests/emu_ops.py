@@ -432,6 +432,9 @@ class EmuOps:
             m = m + ((-logsnr_next).sigmoid() * c).sqrt() * noise
         out.copy_(m)
 
+    def sampler_update_dev(self, z, eps_c, eps_u, w, noise, out, sched):
+        self.sampler_update(z, eps_c, eps_u, w, noise, out, float(sched[0]), float(sched[1]))
+
     def adam(self, p, g, m, v, lr, beta1, beta2, eps, step, grad_scale=1.0):
         gg = g * grad_scale
         m.mul_(beta1).add_(gg, alpha=1 - beta1)

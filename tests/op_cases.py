@@ -179,6 +179,9 @@ def misc_case(seed=0):
             so = ops.zeros((Bq, 3, 8, 8), torch.float32)
             ops.sampler_update(zz, nz, xx, wv, xr, so, l0, l1)
             outs.append(so)
+            so2 = ops.zeros((Bq, 3, 8, 8), torch.float32)
+            ops.sampler_update_dev(zz, nz, xx, wv, xr, so2, torch.tensor([l0, l1], dtype=torch.float32).to(dev))
+            outs.append(so2)
         pa, ga = torch.randn(1000, generator=g).to(dev), torch.randn(1000, generator=g).to(dev)
         ma, va = ops.zeros((1000,), torch.float32), ops.zeros((1000,), torch.float32)
         for st in (1, 2, 3):

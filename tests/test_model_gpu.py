@@ -74,6 +74,7 @@ def test_pose_embedding_matches_reference_fixture():
 @pytest.mark.parametrize("kw,B,cm", [
     (dict(H=32, W=32, ch=64), 3, [False, True, True]),
     (dict(H=64, W=64, ch=128), 2, [True, False]),          # CFG-64, the configuration of the headline metric
+    (dict(H=128, W=128, ch=256), 1, [True]),               # CFG-128, the paper's configuration (head_dim 256 at the deepest level)
 ])
 def test_forward_backward_parity_vs_oracle(kw, B, cm):
     from distributed_3d_diffusion_pytorch_b200.selftest import parity_metrics
@@ -120,6 +121,40 @@ def test_sampler_step_matches_oracle():
     rec = [[x.numpy(), R[0, 0].numpy(), T[0, 0].numpy()]]
     o = sampling.sample(m, rec, R[0, 1], T[0, 1], K[0], w, timesteps=4)
     assert o.shape == (8, 3, 16, 16) and bool((o == o).all())
+
+
+def test_graph_sampler_matches_functional_step():
+    """the captured (CUDA graph) denoise step == the functional p_sample on the same draws"""
+    from distributed_3d_diffusion_pytorch_b200 import sampling, synthetic
+    from distributed_3d_diffusion_pytorch_b200.diff3d import logsnr_schedule_cosine
+    dev = "cuda:0"
+    m = _model(dict(H=16, W=16, ch=64), 6).eval()
+    b = 8
+    img, R, T, K = synthetic.make_views(1, 16, seed=2)
+    table = logsnr_schedule_cosine(torch.linspace(1.0, 0.0, 257))
+    w = torch.arange(8, dtype=torch.float32)
+    cond = img[0, 0][None].repeat(b, 1, 1, 1)
+    for use_graph in (False, True):
+        gs = sampling.GraphSampler(m, b, use_graph=use_graph)
+        gs.w.copy_(w)
+        gs.set_views(cond, R[0, 0], T[0, 0], R[0, 1], T[0, 1], K[0])
+        z0 = torch.randn(b, 3, 16, 16, generator=torch.Generator().manual_seed(3)).to(dev)
+        gs.z.copy_(z0)
+        z_ref = z0.clone()
+        for i in (10, 11, 127, 200):          # 127 -> logsnr_next == 0: no noise added (Q11)
+            torch.manual_seed(100 + i)
+            gs.step(table[i], table[i + 1])
+            torch.manual_seed(100 + i)
+            xu = torch.empty(b, 3, 16, 16, device=dev).normal_()
+            noise = torch.empty(b, 3, 16, 16, device=dev).normal_()
+            Rb = torch.stack([R[0, 0], R[0, 1]], 0)[None].repeat(b, 1, 1, 1)
+            Tb = torch.stack([T[0, 0], T[0, 1]], 0)[None].repeat(b, 1, 1)
+            ec, eu = sampling.predict_noise_pair(m, cond, z_ref, Rb, Tb, K[0], table[i], x_uncond=xu)
+            out = torch.empty_like(z_ref)
+            from distributed_3d_diffusion_pytorch_b200.diff3d import _ops
+            _ops(torch.device(dev)).sampler_update(z_ref, ec.contiguous(), eu.contiguous(), w.to(dev), noise, out, float(table[i]), float(table[i + 1]))
+            z_ref = out
+            assert torch.allclose(gs.z, z_ref, atol=2e-2, rtol=2e-2), (use_graph, i, (gs.z - z_ref).abs().max())
 
 
 def test_training_step_with_dropout_and_fused_adam():

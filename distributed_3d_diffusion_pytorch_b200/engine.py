@@ -396,12 +396,17 @@ class Engine:
         ops.gemm(G.dense_desc(g.view(N * L, C), Wp[a + ".in_proj_weight"], qkv.view(N * L, 3 * C), 3 * C, bias=P[a + ".in_proj_bias"]))
         q, k, v = self._qkv_views(qkv, L, C)
         Lp = (L + 7) // 8 * 8
-        p = self.buf(n + ".p", (N, Hh, L, Lp))[..., :L]
-        logits = self.tmp("logits", (N, Hh, L, Lp), torch.float32)[..., :L]      # fp32: never rounded before the softmax
-        ops.gemm(G.attn_qk_desc(q, k, logits, s.cross, 1.0 / math.sqrt(d)))
-        ops.softmax(logits, p)
+        need_p = self.saved["need_bwd"]
+        p = self.buf(n + ".p", (N, Hh, L, Lp))[..., :L] if (need_p or L > 256) else None
         o = self.buf(n + ".o", (N, L, C))
-        ops.gemm(G.attn_pv_desc(p, v, o.view(N, L, Hh, d).permute(0, 2, 1, 3), s.cross))
+        if L <= 256 and d % 16 == 0 and d <= 256:
+            # fused: S and O stay in TMEM, P goes through shared memory (written out only when backward follows)
+            ops.attn_fwd(qkv, Hh, s.cross, 1.0 / math.sqrt(d), o, probs=p if need_p else None)
+        else:
+            logits = self.tmp("logits", (N, Hh, L, Lp), torch.float32)[..., :L]      # fp32: never rounded before the softmax
+            ops.gemm(G.attn_qk_desc(q, k, logits, s.cross, 1.0 / math.sqrt(d)))
+            ops.softmax(logits, p)
+            ops.gemm(G.attn_pv_desc(p, v, o.view(N, L, Hh, d).permute(0, 2, 1, 3), s.cross))
         o1 = self.buf(n + ".o1", (N * L, C))
         ops.gemm(G.dense_desc(o.view(N * L, C), Wp[a + ".out_proj.weight"], o1, C, bias=P[a + ".out_proj.bias"]))
         out = self.buf(n + ".out", (N, hh, ww, C))

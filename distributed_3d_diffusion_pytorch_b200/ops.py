@@ -207,6 +207,15 @@ class CudaOps:
                           f"split={d.split_k} bn={d.bn_tile} batched={int(d.batched)} fp32={int(o.dtype == torch.float32)}")
         self._call("b3d_gemm", ctypes.byref(cd), self.stream())
 
+    def attn_fwd(self, qkv, heads, cross, scale, out, probs=None):
+        """fused softmax(QK^T*scale)V; qkv [N,L,3C] bf16 -> out [N,L,C]; probs (optional) [N,heads,L,Lp] view with Lp % 8 == 0"""
+        N, L, C3 = qkv.shape
+        d = C3 // 3 // heads
+        assert qkv.is_contiguous() and out.is_contiguous() and qkv.dtype == torch.bfloat16
+        ld = probs.stride(2) if probs is not None else 0
+        self._call("b3d_attn_fwd", _ptr(qkv), c_i32(N), c_i32(L), c_i32(heads), c_i32(d), c_i32(int(cross)), c_f32(scale), _ptr(out),
+                   _ptr(probs), c_i64(ld), self.stream())
+
     # ---- conditioning
     def pose_embedding(self, K, R, t, mask, pos_emb, first_emb, other_emb, out):
         B = K.shape[0]

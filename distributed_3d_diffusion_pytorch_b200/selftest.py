@@ -46,15 +46,15 @@ def parity_metrics(model_kw, B, seed, cond_mask, device="cuda:0"):
     e = eps.detach().float().cpu()
     out_rel = ((e - eo).norm() / eo.norm()).item()
     loss_rel = abs(loss.item() - loss_o.item()) / abs(loss_o.item())
-    ga = torch.cat([p.grad.flatten().float().cpu() for _, p in model.named_parameters()])
-    gb = torch.cat([sdo[n].grad.flatten().float().cpu() for n, _ in model.named_parameters()])
+    ga = torch.cat([p.grad.flatten().double().cpu() for _, p in model.named_parameters()])
+    gb = torch.cat([sdo[n].grad.flatten().double().cpu() for n, _ in model.named_parameters()])
     cos = torch.nn.functional.cosine_similarity(ga, gb, dim=0).item()
     worst, worst_name = 1.0, None
     for n, p in model.named_parameters():
-        go = sdo[n].grad.flatten().float().cpu()
+        go = sdo[n].grad.flatten().double().cpu()
         if go.norm() < 1e-6 * gb.norm():
             continue                               # analytically ~0 (e.g. a bias in front of a 1-channel GroupNorm group)
-        c = torch.nn.functional.cosine_similarity(p.grad.flatten().float().cpu(), go, dim=0).item()
+        c = torch.nn.functional.cosine_similarity(p.grad.flatten().double().cpu(), go, dim=0).item()
         if c < worst:
             worst, worst_name = c, n
     return dict(out_rel_l2=out_rel, loss_rel=loss_rel, grad_cos=cos, worst_grad_cos=worst, worst_name=worst_name,

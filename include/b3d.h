@@ -74,6 +74,14 @@ typedef struct b3d_gemm_desc {
 
 int b3d_gemm(const b3d_gemm_desc* d, void* stream);
 
+/* Fused attention forward for L <= 256 tokens, head_dim <= 256 (all attention levels of CFG-64; the deepest of CFG-128):
+ * softmax(Q K^T * scale) V per (image, head) with S and O in TMEM, P through shared memory, operands by TMA straight
+ * from the packed in_proj output qkv [N, L, 3*heads*d] (bf16).  cross = 1 reads K, V of image n ^ 1 (xunet.py:206-211).
+ * out: bf16 [N, L, heads*d].  probs: optional bf16 [N, heads, L, ld_probs] (normalised P, kept for the backward pass).
+ * Replaces the bmm / softmax / bmm inside nn.MultiheadAttention (xunet.py:161,175). */
+int b3d_attn_fwd(const void* qkv, int N, int L, int heads, int d, int cross, float scale, void* out, void* probs, int64_t ld_probs,
+                 void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * HBM-bound kernels (elementwise / normalisation / reductions).  bf16 NHWC unless noted.
  * ------------------------------------------------------------------------------------------ */

@@ -153,6 +153,18 @@ class EmuOps:
         if d.out2 is not None:
             d.out2[:, :, :rows, :d.n_cols][n_idx] = tmp2.to(d.out2.dtype)
 
+    def attn_fwd(self, qkv, heads, cross, scale, out, probs=None):
+        N, L, C3 = qkv.shape
+        C = C3 // 3
+        d = C // heads
+        q, k, v = (qkv.float().view(N, L, 3, heads, d)[:, :, i].permute(0, 2, 1, 3) for i in range(3))
+        idx = torch.arange(N) ^ int(cross)
+        P = torch.softmax((q @ k[idx].transpose(-1, -2)) * scale, -1)
+        if probs is not None:
+            probs[..., :L] = P.to(probs.dtype)
+            P = probs[..., :L].float()
+        out.copy_((P @ v[idx]).permute(0, 2, 1, 3).reshape(N, L, C).to(out.dtype))
+
     # ------------------------------------------------------------------ conditioning
     def pose_embedding(self, K, R, t, mask, pos_emb, first_emb, other_emb, out):
         B = K.shape[0]

@@ -191,8 +191,27 @@ def misc_case(seed=0):
     return run
 
 
+def attn_case(N, L, heads, d, cross, with_p, seed=0):
+    def run(ops):
+        g = torch.Generator().manual_seed(seed)
+        C = heads * d
+        qkv = _mk(ops, _r((N, L, 3 * C), g))
+        out = ops.zeros((N, L, C))
+        Lp = (L + 7) // 8 * 8
+        probs = ops.zeros((N, heads, L, Lp)) if with_p else None
+        ops.attn_fwd(qkv, heads, cross, 1.0 / math.sqrt(d), out, probs[..., :L] if with_p else None)
+        return [out] + ([probs] if with_p else [])
+    return run
+
+
 def all_cases():
     c = {
+        "attn_fused_L256_d64_self": attn_case(4, 256, 4, 64, False, True),
+        "attn_fused_L64_d128_cross": attn_case(4, 64, 4, 128, True, True, seed=1),
+        "attn_fused_L256_d256_cross_nop": attn_case(2, 256, 4, 256, True, False, seed=2),
+        "attn_fused_L16_d16_self": attn_case(2, 16, 4, 16, False, True, seed=3),
+        "attn_fused_L36_d32_cross": attn_case(2, 36, 2, 32, True, True, seed=4),
+        "attn_fused_L200_d64_many": attn_case(64, 200, 4, 64, True, True, seed=5),
         "pose_fp32_64": pose_case(3, 64, 64, True),
         "pose_fp32_24": pose_case(2, 24, 24, True, seed=3),
         "pose_bf16_16": pose_case(2, 16, 16, False, seed=4),

@@ -19,7 +19,7 @@ def _model(kw, seed, dev="cuda:0"):
     return m
 
 
-@pytest.mark.parametrize("name", ["tiny16", "tiny24"])
+@pytest.mark.parametrize("name", ["tiny16", "tiny24", "small32"])
 def test_golden_fixture_parity(name):
     """against the fixtures produced by the reference's own code"""
     from distributed_3d_diffusion_pytorch_b200.diff3d import diffusion_loss, q_sample
@@ -36,19 +36,26 @@ def test_golden_fixture_parity(name):
     # ch=32 puts ONE channel in each GroupNorm group and the deepest level is 2x2 (3x3) pixels: statistics over 4-9
     # values amplify bf16 rounding (the same algorithm in torch with bf16 buffers gives 2.5e-2).
     # Structure check here; the 2e-2 bar of north_star is asserted on CFG-64 below.
-    assert rel <= 2 * OUT_TOL, rel
+    strict = G["kw"]["ch"] >= 64
+    assert rel <= (OUT_TOL if strict else 3 * OUT_TOL), rel
     loss = diffusion_loss(G["noise"].to(dev), eps)
-    assert abs(loss.item() - G["loss"].item()) <= 3 * LOSS_TOL * abs(G["loss"].item())
+    assert abs(loss.item() - G["loss"].item()) <= (1 if strict else 3) * LOSS_TOL * abs(G["loss"].item())
     loss.backward()
     grads = dict((n, p.grad.float().cpu()) for n, p in m.named_parameters())
     # gradients: only the tensors computed FIRST in the backward pass are compared here.  Deeper in the network this
     # fixture is numerically degenerate in bf16 (see the comment above; the same algorithm in torch with bf16 buffers
     # reaches a global cosine of only ~0.87), so the full gradient is checked exactly (fp32) by tests/test_engine_cpu.py
     # on this very fixture, and at the 0.999 bar on CFG-64 below.
-    for k in ("lastconv.weight",):
+    for k in (G["grads"].keys() if strict else ("lastconv.weight",)):
         g = G["grads"][k]
-        cos = torch.nn.functional.cosine_similarity(grads[k].flatten(), g.flatten(), dim=0).item()
-        assert cos >= 0.99, (k, cos)
+        if g.norm() < 1e-5:
+            continue
+        cos = torch.nn.functional.cosine_similarity(grads[k].double().flatten(), g.double().flatten(), dim=0).item()
+        assert cos >= (0.995 if strict else 0.99), (k, cos)
+    if strict:      # norm of the whole gradient against the reference's
+        tot_ref = sum(v ** 2 for v in G["grad_norms"].values()) ** 0.5
+        tot = sum(g.double().norm().item() ** 2 for g in grads.values()) ** 0.5
+        assert abs(tot - tot_ref) <= 2e-2 * tot_ref, (tot, tot_ref)
     assert all(torch.isfinite(g).all() for g in grads.values())
 
 

@@ -46,6 +46,10 @@ def test_oracle_matches_reference_tiny24():
     _run_model_case("tiny24")
 
 
+def test_oracle_matches_reference_small32():
+    _run_model_case("small32")
+
+
 def test_schedule_and_sampler_update_match_reference():
     G = load_golden("glue")
     table = dr.logsnr_schedule_cosine(torch.linspace(1.0, 0.0, 257))

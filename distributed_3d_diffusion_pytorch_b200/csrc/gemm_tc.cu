@@ -221,6 +221,87 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
+  } else if (p.epi_tma && p.out_fp32) {
+    // ===================================================================== epilogue, fp32 outputs through TMA (warps 2..5)
+    // 32 fp32 columns (one 128-byte row) per round: TMEM -> registers -> epilogue math -> swizzled smem tile -> TMA store,
+    // or TMA reduce-add for split-K weight gradients (the fp32 adds happen in L2, asynchronously, with full-line bursts;
+    // per-thread RED instructions to 32 different rows made the LSU the bottleneck of short-K splits).
+    const int quad = warp & 3;
+    const int r = quad * 32 + lane;
+    const bool leader = threadIdx.x == 64;
+    const uint32_t so_base = smem_base + p.epi_off;
+    int acc = 0; uint32_t acc_phase = 0;
+    int buf = 0;
+    const uint32_t swz = (uint32_t)(r & 7);
+    for (int t = blockIdx.x; t < p.tiles_total; t += gridDim.x) {
+      const TileCoord c = decode_tile(p, t);
+      int cx, cy, cn, img;
+      if (p.a_major == 0) {
+        cx = c.x0; cy = c.y0; cn = c.n0 ^ p.o_xor;
+        img = c.n0 + r / (p.bw * p.bh);
+        if (img >= p.N) img = p.N - 1;
+      } else {
+        cx = c.m0; cy = c.y0; cn = c.n0 ^ p.o_xor; img = c.n0;
+      }
+      const int ncols_tile = min(p.BN, p.n_cols - c.tn * p.BN);
+      const int nch = (ncols_tile + 31) / 32;
+      mbar_wait(tfull_bar(acc), acc_phase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + (uint32_t)(acc * p.acc_stride) + ((uint32_t)(quad * 32) << 16);
+      for (int ch = 0; ch < nch; ++ch) {
+        const int cc = c.tn * p.BN + ch * 32;
+        if (leader) tma_store_wait_read<1>();
+        epi_bar_sync();
+        uint32_t v[32];
+        tmem_ld32(taddr + ch * 32, v);
+        float f[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]) * p.alpha;
+        const bool full = cc + 32 <= p.n_cols;
+        if (p.bias) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) if (full || cc + i < p.n_cols) f[i] += __ldg(p.bias + cc + i);
+        }
+        if (p.rowvec) {
+          const float* rv = p.rowvec + (long long)img * p.rowvec_ld + cc;
+#pragma unroll
+          for (int i = 0; i < 32; ++i) if (full || cc + i < p.n_cols) f[i] += __ldg(rv + i);
+        }
+#pragma unroll
+        for (int i = 0; i < 32; ++i) f[i] *= p.out_scale;
+        if (p.act == 1) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) f[i] = b3d_silu(f[i]);
+        }
+        if (!full) {     // columns past n_cols land in the padding of a packed gradient slab: add exact zeros there
+#pragma unroll
+          for (int i = 0; i < 32; ++i) if (cc + i >= p.n_cols) f[i] = 0.f;
+        }
+        const uint32_t orow = so_base + buf * 16384 + (uint32_t)r * 128u;
+#pragma unroll
+        for (int g = 0; g < 8; ++g) {
+          uint4 q;
+          q.x = __float_as_uint(f[4 * g]); q.y = __float_as_uint(f[4 * g + 1]); q.z = __float_as_uint(f[4 * g + 2]); q.w = __float_as_uint(f[4 * g + 3]);
+          sts128(orow + ((((uint32_t)g) ^ swz) << 4), q);
+        }
+        if (ch == nch - 1) {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(tempty_bar(acc));
+        }
+        fence_proxy_async();
+        epi_bar_sync();
+        if (leader) {
+          const int col = cc + c.tap * (int)p.os_tap;
+          if (p.out_atomic) tma_reduce_add_4d(&p.tmO, so_base + buf * 16384, col, cx, cy, cn);
+          else tma_store_4d(&p.tmO, so_base + buf * 16384, col, cx, cy, cn);
+          tma_store_commit();
+        }
+        buf ^= 1;
+      }
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+    if (leader) tma_store_wait_all();
   } else if (p.epi_tma) {
     // ===================================================================== epilogue, bf16 outputs (warps 2..5)
     // TMEM -> registers -> (bias / per-image vector / residual / scale / SiLU) -> bf16 -> 128B-swizzled smem tile
@@ -548,10 +629,14 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
   p.stage_bytes = kABytes + p.b_bytes;
   // bf16 outputs whose rows are 16-byte aligned leave through smem + TMA store (2 x 16 KB staging, + 2 x 16 KB for
   // the residual tile or the second output)
-  p.epi_tma = (!d->out_fp32 && !d->out_atomic && d->n_cols % 8 == 0 && d->out_stride[0] % 8 == 0 && d->out_stride[1] % 8 == 0 &&
-               d->out_stride[2] % 8 == 0 && d->out_tap_stride == 0 && ((uintptr_t)d->out & 15) == 0 &&
-               (d->resid == nullptr || d->out2 == nullptr) && (d->resid == nullptr || ((uintptr_t)d->resid & 15) == 0) &&
-               (d->out2 == nullptr || ((uintptr_t)d->out2 & 15) == 0)) ? 1 : 0;
+  const bool al16 = ((uintptr_t)d->out & 15) == 0;
+  if (!d->out_fp32)
+    p.epi_tma = (!d->out_atomic && d->n_cols % 8 == 0 && d->out_stride[0] % 8 == 0 && d->out_stride[1] % 8 == 0 && d->out_stride[2] % 8 == 0 &&
+                 d->out_tap_stride == 0 && al16 && (d->resid == nullptr || d->out2 == nullptr) &&
+                 (d->resid == nullptr || ((uintptr_t)d->resid & 15) == 0) && (d->out2 == nullptr || ((uintptr_t)d->out2 & 15) == 0)) ? 1 : 0;
+  else   // fp32: plain TMA store, or TMA reduce-add for the atomically accumulated (split-K) weight gradients
+    p.epi_tma = (d->n_cols % 4 == 0 && d->out_stride[0] % 4 == 0 && d->out_stride[1] % 4 == 0 && d->out_stride[2] % 4 == 0 &&
+                 d->out_tap_stride % 4 == 0 && al16 && d->resid == nullptr && d->out2 == nullptr) ? 1 : 0;
   const uint32_t epi_bytes = p.epi_tma ? ((d->resid || d->out2) ? 65536u : 32768u) : 0u;
   p.num_stages = (int)((kMaxDynSmem - 1024 - epi_bytes) / p.stage_bytes);
   if (p.num_stages > 8) p.num_stages = 8;
@@ -631,7 +716,17 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
     const uint32_t esB[4] = {1, (uint32_t)s, (uint32_t)s, 1};
     rc = make_map(&p.tmB, d->b, boxB, esB); if (rc) return rc;
   }
-  if (p.epi_tma) {
+  if (p.epi_tma && d->out_fp32) {
+    b3d_view4 ov;
+    ov.ptr = d->out;
+    // columns: n_cols, or (for per-tap weight gradients) every tap slab of the packed matrix up to the last one
+    ov.dim[0] = p.b_taps > 1 ? (int)((p.b_taps - 1) * d->out_tap_stride) + d->n_cols : d->n_cols;
+    ov.dim[1] = d->a_major == 0 ? d->W : d->m_rows; ov.dim[2] = d->H; ov.dim[3] = d->N;
+    ov.stride[0] = d->out_stride[0]; ov.stride[1] = d->out_stride[1]; ov.stride[2] = d->out_stride[2];
+    uint32_t boxO[4] = {32, 128, 1, 1};
+    if (d->a_major == 0) { boxO[1] = (uint32_t)p.bw; boxO[2] = (uint32_t)p.bh; boxO[3] = (uint32_t)p.bnn; }
+    rc = make_map(&p.tmO, ov, boxO, ones, 4); if (rc) return rc;
+  } else if (p.epi_tma) {
     b3d_view4 ov;
     ov.ptr = d->out;
     ov.dim[0] = d->n_cols; ov.dim[1] = d->a_major == 0 ? d->W : d->m_rows; ov.dim[2] = d->H; ov.dim[3] = d->N;

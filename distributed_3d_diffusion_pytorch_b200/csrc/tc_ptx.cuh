@@ -49,6 +49,11 @@ __device__ __forceinline__ void tma_store_4d(const CUtensorMap* tm, uint32_t src
                ::"l"(reinterpret_cast<uint64_t>(tm)), "r"(src), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
                : "memory");
 }
+__device__ __forceinline__ void tma_reduce_add_4d(const CUtensorMap* tm, uint32_t src, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.reduce.async.bulk.tensor.4d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
+               ::"l"(reinterpret_cast<uint64_t>(tm)), "r"(src), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+               : "memory");
+}
 __device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
@@ -128,13 +133,14 @@ inline EncodeTiledFn get_encode() {
   return fn;
 }
 
-inline int make_map(CUtensorMap* tm, const b3d_view4& v, const uint32_t box[4], const uint32_t estr[4]) {
+inline int make_map(CUtensorMap* tm, const b3d_view4& v, const uint32_t box[4], const uint32_t estr[4], int elem_bytes = 2) {
   EncodeTiledFn enc = get_encode();
   if (!enc) { b3d_set_error("cuTensorMapEncodeTiled entry point not available"); return B3D_ERR_CUDA; }
   cuuint64_t gdim[4] = {(cuuint64_t)v.dim[0], (cuuint64_t)v.dim[1], (cuuint64_t)v.dim[2], (cuuint64_t)v.dim[3]};
-  cuuint64_t gstr[3] = {(cuuint64_t)v.stride[0] * 2, (cuuint64_t)v.stride[1] * 2, (cuuint64_t)v.stride[2] * 2};
+  const cuuint64_t eb = (cuuint64_t)elem_bytes;
+  cuuint64_t gstr[3] = {(cuuint64_t)v.stride[0] * eb, (cuuint64_t)v.stride[1] * eb, (cuuint64_t)v.stride[2] * eb};
   for (int i = 0; i < 3; ++i) {
-    if (gdim[i + 1] == 1 && gstr[i] == 0) gstr[i] = (i == 0 ? (cuuint64_t)((v.dim[0] + 7) / 8 * 8) * 2 : gstr[i - 1] * gdim[i]);
+    if (gdim[i + 1] == 1 && gstr[i] == 0) gstr[i] = (i == 0 ? (cuuint64_t)((v.dim[0] + 7) / 8 * 8) * eb : gstr[i - 1] * gdim[i]);
     if (gstr[i] % 16 != 0) { b3d_set_error("b3d_gemm: stride %d (%llu bytes) not a multiple of 16", i, (unsigned long long)gstr[i]); return B3D_ERR_ARG; }
   }
   if (((uintptr_t)v.ptr & 15) != 0) { b3d_set_error("b3d_gemm: operand pointer not 16-byte aligned"); return B3D_ERR_ARG; }
@@ -142,7 +148,7 @@ inline int make_map(CUtensorMap* tm, const b3d_view4& v, const uint32_t box[4], 
   cuuint32_t es[4] = {estr[0], estr[1], estr[2], estr[3]};
   for (int i = 0; i < 4; ++i)
     if (bx[i] == 0 || bx[i] > 256) { b3d_set_error("b3d_gemm: TMA box dim %d = %u out of range", i, bx[i]); return B3D_ERR_ARG; }
-  CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(v.ptr), gdim, gstr, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+  CUresult r = enc(tm, elem_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(v.ptr), gdim, gstr, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
                    CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     b3d_set_error("cuTensorMapEncodeTiled failed (%d): dims %llu,%llu,%llu,%llu strides %llu,%llu,%llu box %u,%u,%u,%u es %u,%u,%u,%u", (int)r,

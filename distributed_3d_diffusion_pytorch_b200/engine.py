@@ -420,9 +420,23 @@ class Engine:
     def _grad_of(self, act):
         return self.buf("d." + act.key, act.t.shape)
 
-    def backward(self, Gr, deps, grad_flat=None):
+    # The backward pass runs in three phases whose parameter gradients are FINAL (unpacked, in PyTorch layout) when the
+    # phase returns, in the reverse of the flat arena's order: 0 = head + up path (arena tail: upsample.*, lastgn, lastconv),
+    # 1 = middle + down path (xunetblocks.*, middle.*), 2 = stem + conditioning (arena head).  A data-parallel trainer
+    # all-reduces each range while the next phase computes (trainer.py).
+    PHASE_PREFIXES = (("upsample.", "lastgn.", "lastconv."), ("xunetblocks.", "middle."), ("conditioningprocessor.", "conv."))
+
+    def backward(self, Gr, deps, grad_flat=None, phase=None):
         """Gr: dict name -> fp32 grad tensor (PyTorch layout), overwritten.  deps: fp32 [B,3,H,W] = dL/d eps_hat.
-        grad_flat: optional flat tensor that all of Gr are views of (zeroed with one memset)."""
+        grad_flat: optional flat tensor that all of Gr are views of (zeroed with one memset).
+        phase: None = whole backward; 0, 1, 2 = one phase (must be called in that order)."""
+        for ph in ((0, 1, 2) if phase is None else (phase,)):
+            self._cur_phase = ph
+            (self._bwd_phase0, self._bwd_phase1, self._bwd_phase2)[ph](Gr, deps, grad_flat)
+            self.ops.run_jobs(self._unpack_jl[ph])     # packed fp32 weight gradients of this phase -> PyTorch layout, one launch
+            self.ops.run_jobs(self._copy_jl[ph])
+
+    def _bwd_phase0(self, Gr, deps, grad_flat):
         ops, cfg, B, N = self.ops, self.cfg, self.B, self.N
         sv = self.saved
         assert sv is not None and sv["need_bwd"], "backward needs a forward run with need_bwd=True"
@@ -432,7 +446,7 @@ class Engine:
         usig = (len(Gr), tuple(Gr[k].data_ptr() for k in list(Gr.keys())[:8]))
         self._unpack_rec = self._unpack_jl is None or self._unpack_sig != usig
         if self._unpack_rec:
-            self._unpack_jl, self._copy_jl, self._unpack_sig = JobList("unpack"), JobList("pack"), usig
+            self._unpack_jl, self._copy_jl, self._unpack_sig = [JobList("unpack") for _ in range(3)], [JobList("pack") for _ in range(3)], usig
         if grad_flat is not None:
             grad_flat.zero_()
         else:
@@ -440,8 +454,7 @@ class Engine:
                 g.zero_()
         for a in self._all_acts():
             a.has_grad = False
-        drop_p = sv["drop_p"]
-        dss = [self.buf(f"dss{l}", (N * (H >> l) * (Wd >> l), self.film_cols[l])) for l in range(cfg.num_resolutions)]
+        self._dss = [self.buf(f"dss{l}", (N * (H >> l) * (Wd >> l), self.film_cols[l])) for l in range(cfg.num_resolutions)]
 
         # ---- head
         h = sv["final"]
@@ -462,15 +475,29 @@ class Engine:
                    dh.view(N, HW, C))
         h.has_grad = True
 
-        # ---- blocks in reverse
-        bi = sum(1 for k, _ in self.plan if k == "res")
+        self._bwd_blocks(Gr, lambda name: name.startswith("upsample."))
+
+    def _bwd_blocks(self, Gr, select):
+        sv = self.saved
+        P, Wp, drop_p = sv["P"], sv["W"], sv["drop_p"]
         for kind, s in reversed(self.plan):
+            if s is None or not select(s.name):
+                continue
             if kind == "res":
-                bi -= 1
-                self._res_bwd(s, P, Wp, Gr, dss[s.lvl], drop_p)
+                self._res_bwd(s, P, Wp, Gr, self._dss[s.lvl], drop_p)
             elif kind == "attn":
                 self._attn_bwd(s, P, Wp, Gr)
 
+    def _bwd_phase1(self, Gr, deps, grad_flat):
+        self._bwd_blocks(Gr, lambda name: not name.startswith("upsample."))
+
+    def _bwd_phase2(self, Gr, deps, grad_flat):
+        ops, cfg, B, N = self.ops, self.cfg, self.B, self.N
+        sv = self.saved
+        P, Wp = sv["P"], sv["W"]
+        H, Wd, E = cfg.H, cfg.W, cfg.emb_ch
+        HW = H * Wd
+        dss = self._dss
         # ---- stem
         stem = Act(self._bufs["stem"], "stem")
         dstem = self._grad_of(stem)
@@ -517,13 +544,10 @@ class Engine:
         ops.silu_bwd(dh1, h1, dh1)
         ops.colsum(dh1, N, Gr[cp + "logsnr_emb_emb.0.bias"])
         ops.gemm(G.wgrad_dense_desc(dh1, e0, Gr[cp + "logsnr_emb_emb.0.weight"]))
-        # every packed fp32 weight gradient goes back to its PyTorch layout in one launch
-        ops.run_jobs(self._unpack_jl)
-        ops.run_jobs(self._copy_jl)
 
     def _unpack(self, gp, k_off, cpad, dw, ci0=0, cn=None):
         if self._unpack_rec:
-            self.ops.record_unpack_wgrad(self._unpack_jl, gp, k_off, cpad, dw, ci0=ci0, cn=cn)
+            self.ops.record_unpack_wgrad(self._unpack_jl[self._cur_phase], gp, k_off, cpad, dw, ci0=ci0, cn=cn)
 
     def _all_acts(self):
         sv = self.saved
@@ -575,7 +599,7 @@ class Engine:
         # 1x1 skip
         if s.cin != F:
             if self._unpack_rec:       # d(dense.bias) = the same column sums as d(conv2.bias): copied at the end of backward
-                ops.record_copy(self._copy_jl, Gr[n + ".conv2.bias"], Gr[n + ".dense.bias"])
+                ops.record_copy(self._copy_jl[self._cur_phase], Gr[n + ".conv2.bias"], Gr[n + ".dense.bias"])
             gw = Gr[n + ".dense.weight"].view(F, s.cin)
             srcs = [h_in] + ([skip] if skip is not None else [])
             koff = 0

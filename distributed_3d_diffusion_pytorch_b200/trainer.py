@@ -62,9 +62,8 @@ class Trainer:
         self.step_idx = 0
 
     # ------------------------------------------------------------------ one step, device resident
-    def _compute(self):
-        """draws + forward + loss + backward on the static buffers (graph-capturable: no allocation, no sync)"""
-        B = self.B
+    def _draws_forward_loss(self):
+        """draws + forward + loss on the static buffers (graph-capturable: no allocation, no sync)"""
         self.step_ctr.add_(1)
         self.u.uniform_()                                            # logsnr = schedule(rand(B))      (train.py:272)
         torch.log(torch.tan(self.u * self._a + self._b), out=self.logsnr)
@@ -82,7 +81,25 @@ class Trainer:
         eps = self.engine.forward(P, self.x_cond, self.z_noisy, self.logsnr2, self.R, self.T, self.K, self.mask, training=True, need_bwd=True,
                                   seed=0)
         self.ops.loss(self.noise, eps, self.deps, 0, self.scratch, self.loss)
-        self.engine.backward(self.model._grad_views(), self.deps, grad_flat=self.model._grad_flat)
+
+    def _backward(self, phase=None):
+        self.engine.backward(self.model._grad_views(), self.deps, grad_flat=self.model._grad_flat, phase=phase)
+
+    def _compute(self):
+        self._draws_forward_loss()
+        self._backward()
+
+    def _phase_ranges(self):
+        """element ranges of the flat gradient arena that each backward phase finalises (engine.PHASE_PREFIXES)"""
+        m = self.model
+        first = {}
+        for n, o in zip(m._names, m._offs):
+            for ph, pre in enumerate(self.engine.PHASE_PREFIXES):
+                if n.startswith(pre) and ph not in first:
+                    first[ph] = o
+        end = m._grad_flat.numel()
+        # arena order: conditioningprocessor, conv (phase 2) | xunetblocks, middle (phase 1) | upsample, lastgn, lastconv (phase 0)
+        return {2: (0, first[1]), 1: (first[1], first[0]), 0: (first[0], end)}
 
     def _finish(self):
         parallel.allreduce_mean_(self.model._grad_flat)
@@ -96,6 +113,12 @@ class Trainer:
         self.T.copy_(T, non_blocking=True)
         self.K.copy_(K, non_blocking=True)
 
+    def _capture(self, fn):
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            fn()
+        return g
+
     def step_resident(self, batch):
         """batch already lives in HBM (device tensors)"""
         from . import _lib
@@ -103,16 +126,35 @@ class Trainer:
         if self.use_graph and self.graph is None and self.step_idx >= 1:
             torch.cuda.synchronize()
             n0 = _lib.launch_count()
-            g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g):
-                self._compute()
+            if self.world == 1:
+                self.graph = [self._capture(self._compute)]
+            else:       # three graphs: the all-reduce of each finished gradient range overlaps the next backward phase
+                self.model._grad_views()
+                self.graph = [self._capture(lambda: (self._draws_forward_loss(), self._backward(0))),
+                              self._capture(lambda: self._backward(1)), self._capture(lambda: self._backward(2))]
+                self.ranges = self._phase_ranges()
+                self.comm = torch.cuda.Stream(self.dev)
             self.launches_per_step = _lib.launch_count() - n0 + 1     # + Adam
-            self.graph, self.graphed = g, True
-        if self.graph is not None:
-            self.graph.replay()
-        else:
+            self.graphed = True
+        if self.graph is None:
             self._compute()
-        self._finish()
+            self._finish()
+            return
+        if self.world == 1:
+            self.graph[0].replay()
+            self._finish()
+            return
+        main = torch.cuda.current_stream(self.dev)
+        g = self.model._grad_flat
+        for ph in (0, 1, 2):
+            self.graph[ph].replay()
+            self.comm.wait_stream(main)                                # gradients of this phase are final
+            lo, hi = self.ranges[ph]
+            with torch.cuda.stream(self.comm):
+                parallel.allreduce_mean_(g[lo:hi])                     # NCCL over NVLink, concurrent with the next phase
+        main.wait_stream(self.comm)
+        self.opt.step()
+        self.step_idx += 1
 
     def step_e2e(self, host_batch):
         """the same step through the copy path: pinned host inputs -> device, loss read back"""

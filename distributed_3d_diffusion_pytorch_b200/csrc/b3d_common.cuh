@@ -56,14 +56,15 @@ __device__ __forceinline__ float b3d_warp_sum(float v) {
   return v;
 }
 
-// counter-based uniform in [0,1): one 32-bit hash per (seed, index) -- recomputable in backward.
-__device__ __forceinline__ uint32_t b3d_hash32(uint64_t x) {
-  x ^= x >> 33; x *= 0xff51afd7ed558ccdULL; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ULL; x ^= x >> 33;
-  return (uint32_t)x;
+// Counter-based dropout bits, recomputable in backward: one 32-bit hash per PAIR of consecutive elements (16 bits
+// each; element 2k takes the low half).  key = seed * golden ratio + (element index >> 1).  An element is dropped when
+// its 16-bit field is below b3d_drop_thr16(p).  (tests/emu_ops.py mirrors both functions bit for bit.)
+__host__ __device__ __forceinline__ uint32_t b3d_drop_pair(uint64_t key) {
+  uint32_t x = (uint32_t)key ^ ((uint32_t)(key >> 32) * 0x9E3779B9u);
+  x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
+  return x;
 }
-__device__ __forceinline__ float b3d_uniform(uint64_t seed, uint64_t idx) {
-  return (float)(b3d_hash32(seed * 0x9E3779B97F4A7C15ULL + idx) >> 8) * (1.0f / 16777216.0f);
-}
+__host__ __device__ __forceinline__ uint32_t b3d_drop_thr16(float p) { return (uint32_t)(p * 65536.0f + 0.5f); }
 
 // 8 bf16 values moved as ONE 128-bit word (a struct of four __nv_bfloat162 is copied member-wise and the compiler
 // then emits four 32-bit loads/stores instead of one LDG.128/STG.128 -- measured 4x the L1 sector requests).

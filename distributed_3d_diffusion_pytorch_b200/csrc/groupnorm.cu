@@ -22,8 +22,9 @@ struct Src2 {
 // thread t owns the 8-channel vector v = t % (C/8) for every row it visits (so gamma/beta/mean/rstd of its
 // channels live in registers) and visits rows rsub, rsub + rows_par, ... with U independent 16-byte loads per
 // tensor in flight (HBM latency is hidden by memory-level parallelism, not by occupancy).
-struct Chan {
-  float gamma[8], beta[8], mean[8], rstd[8];
+// Per-channel affine of the normalisation kept in registers: z = gamma*xhat + beta = x*a + b.
+struct Aff {
+  float a[8], b[8];
 };
 
 __device__ __forceinline__ void block_stats(const float* stats, int n, int cpg, int HW, float* s_mean, float* s_rstd) {
@@ -35,12 +36,13 @@ __device__ __forceinline__ void block_stats(const float* stats, int n, int cpg, 
     s_mean[threadIdx.x] = mean; s_rstd[threadIdx.x] = rsqrtf(var + 1e-5f);
   }
 }
-__device__ __forceinline__ void load_chan(Chan& ch, const float* gamma, const float* beta, int c0, int cpg, const float* s_mean,
-                                          const float* s_rstd) {
+__device__ __forceinline__ void load_aff(Aff& ch, const float* gamma, const float* beta, int c0, int cpg, const float* s_mean,
+                                         const float* s_rstd) {
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
     const int g = (c0 + j) / cpg;
-    ch.gamma[j] = gamma[c0 + j]; ch.beta[j] = beta[c0 + j]; ch.mean[j] = s_mean[g]; ch.rstd[j] = s_rstd[g];
+    ch.a[j] = s_rstd[g] * gamma[c0 + j];
+    ch.b[j] = beta[c0 + j] - s_mean[g] * ch.a[j];
   }
 }
 struct RowPtr {   // per-thread base pointer of its channel vector inside the (possibly two-source) input
@@ -95,7 +97,7 @@ __global__ void __launch_bounds__(kT) gn_stats_kernel(Src2 s, int HW, int rows_p
       for (int u = 0; u < U; ++u) {
         float f[8]; b3d_unpack8(x[u], f);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) { a[i] += f[i]; b[i] += f[i] * f[i]; }
+        for (int i = 0; i < 8; ++i) { a[i] += f[i]; b[i] = fmaf(f[i], f[i], b[i]); }
       }
     }
   }
@@ -109,6 +111,30 @@ __global__ void __launch_bounds__(kT) gn_stats_kernel(Src2 s, int HW, int rows_p
   }
 }
 
+// ---- dropout keep-mask of one 8-channel vector: b3d_drop_pair (b3d_common.cuh) hashes (seed, pair index) to 32 bits,
+// 16 per element; an element is dropped when its field is below thr16 = round(p * 65536).
+struct Drop {
+  unsigned long long seedmix;   // (seed + *seed_ptr) * golden ratio
+  unsigned thr_hi;              // thr16 << 16
+  float keep;                   // 1 / (1 - p)
+};
+__device__ __forceinline__ Drop make_drop(float p, unsigned long long seed, const unsigned long long* seed_ptr) {
+  Drop d;
+  d.seedmix = (seed + (seed_ptr ? *seed_ptr : 0ULL)) * 0x9E3779B97F4A7C15ULL;
+  d.thr_hi = b3d_drop_thr16(p) << 16;
+  d.keep = 1.f / (1.f - p);
+  return d;
+}
+__device__ __forceinline__ void drop_mask8(const Drop& d, unsigned long long elem0, float* m) {
+  const unsigned long long base = d.seedmix + (elem0 >> 1);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const unsigned h = b3d_drop_pair(base + k);
+    m[2 * k] = ((h << 16) < d.thr_hi) ? 0.f : d.keep;
+    m[2 * k + 1] = (h < d.thr_hi) ? 0.f : d.keep;
+  }
+}
+
 struct ApplyP {
   Src2 s;
   const float* stats;  // raw sums [N,32,2]
@@ -119,9 +145,22 @@ struct ApplyP {
   float drop_p; unsigned long long seed; const unsigned long long* seed_ptr;  // effective seed = seed + *seed_ptr (device step counter)
 };
 
-__global__ void __launch_bounds__(kT, 2) gn_apply_kernel(ApplyP p, int rows_per_block) {
+constexpr int kApplyU0 = 4, kApplyU2 = 2;   // rows in flight per thread (mode 0/1: one 16 B load per row; film: three)
+constexpr int kBwdU1 = 4, kBwdU2 = 2;       // reduce pass (mode 0/1: two loads per row; film: three)
+constexpr int kBwdApplyU = 2;
+#ifndef B3D_GN_BWD2_BLOCKS
+#define B3D_GN_BWD2_BLOCKS 2
+#endif
+#ifndef B3D_GN_BWD1_BLOCKS
+#define B3D_GN_BWD1_BLOCKS 3
+#endif
+constexpr int kBwdBlocks1 = B3D_GN_BWD1_BLOCKS;
+constexpr int kBwdBlocks2 = B3D_GN_BWD2_BLOCKS;   // resident blocks per SM of the film-mode backward kernels
+
+template <int MODE>
+__global__ void __launch_bounds__(kT, MODE == 2 ? 3 : 4) gn_apply_kernel(ApplyP p, int rows_per_block) {
   __shared__ float s_mean[G], s_rstd[G];
-  constexpr int U = 4;
+  constexpr int U = MODE == 2 ? kApplyU2 : kApplyU0;
   const int C = p.s.C0 + p.s.C1, cpg = C / G, n = blockIdx.y, vecs = C / 8;
   block_stats(p.stats, n, cpg, p.HW, s_mean, s_rstd);
   __syncthreads();
@@ -129,11 +168,12 @@ __global__ void __launch_bounds__(kT, 2) gn_apply_kernel(ApplyP p, int rows_per_
   const int rows_par = max(1, (int)blockDim.x / vecs);
   const int v = threadIdx.x % vecs, rsub = threadIdx.x / vecs, c0 = v * 8;
   if (rsub >= rows_par) return;
-  Chan ch; load_chan(ch, p.gamma, p.beta, c0, cpg, s_mean, s_rstd);
+  Aff ch; load_aff(ch, p.gamma, p.beta, c0, cpg, s_mean, s_rstd);
   const RowPtr rp = src_ptr(p.s, c0);
   const long long img = (long long)n * p.HW;
-  const float keep = 1.f / (1.f - p.drop_p);
-  const unsigned long long seed = p.seed + (p.seed_ptr ? *p.seed_ptr : 0ULL);
+  const bool drop = MODE == 2 && p.drop_p > 0.f;
+  Drop dr{};
+  if (drop) dr = make_drop(p.drop_p, p.seed, p.seed_ptr);
   for (int r = r0 + rsub; r < r1; r += rows_par * U) {
     bf16x8 x[U], sc[U], sh[U];
 #pragma unroll
@@ -141,7 +181,7 @@ __global__ void __launch_bounds__(kT, 2) gn_apply_kernel(ApplyP p, int rows_per_
       const long long row = img + r + u * rows_par;
       const bool ok = r + u * rows_par < r1;
       x[u] = ok ? ld8(rp.p + row * rp.ld) : zero8();
-      if (p.mode == 2) {
+      if (MODE == 2) {
         sc[u] = ok ? ld8(p.ss + row * p.ld_ss + c0) : zero8();
         sh[u] = ok ? ld8(p.ss + row * p.ld_ss + p.F + c0) : zero8();
       }
@@ -150,16 +190,19 @@ __global__ void __launch_bounds__(kT, 2) gn_apply_kernel(ApplyP p, int rows_per_
     for (int u = 0; u < U; ++u) {
       if (r + u * rows_par >= r1) break;
       const long long row = img + r + u * rows_par;
-      float f[8], a[8], b[8];
+      float f[8], a[8], b[8], m[8];
       b3d_unpack8(x[u], f);
-      if (p.mode == 2) { b3d_unpack8(sc[u], a); b3d_unpack8(sh[u], b); }
+      if (MODE == 2) {
+        b3d_unpack8(sc[u], a); b3d_unpack8(sh[u], b);
+        if (drop) drop_mask8(dr, (unsigned long long)row * C + c0, m);
+      }
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        float y = (f[j] - ch.mean[j]) * ch.rstd[j] * ch.gamma[j] + ch.beta[j];
-        if (p.mode == 1) y = b3d_silu(y);
-        else if (p.mode == 2) {
-          y = y * (1.f + a[j]) + b[j];
-          if (p.drop_p > 0.f) y = (b3d_uniform(seed, (unsigned long long)row * C + c0 + j) < p.drop_p) ? 0.f : y * keep;
+        float y = fmaf(f[j], ch.a[j], ch.b[j]);
+        if (MODE == 1) y = b3d_silu(y);
+        else if (MODE == 2) {
+          y = fmaf(y, a[j], y) + b[j];
+          if (drop) y *= m[j];
         }
         f[j] = y;
       }
@@ -174,8 +217,8 @@ struct BwdP {
   const bf16* dy; long long ld_dy;
   int HW, mode;
   const bf16* ss; long long ld_ss; int F;
-  bf16* dss; long long ld_dss;      // film: d_scale -> dss[row, c], d_shift -> dss[row, F + c]
-  float drop_p; unsigned long long seed; const unsigned long long* seed_ptr;  // effective seed = seed + *seed_ptr (device step counter)
+  bf16* dss; long long ld_dss;      // film: d(scale) at [row, c], d(shift) at [row, F + c]
+  float drop_p; unsigned long long seed; const unsigned long long* seed_ptr;
   float* dgamma; float* dbeta;      // fp32 [C], accumulated
   float* dss_sum;                   // optional fp32 [2F]: column sums of dss (the FiLM dense bias gradient)
   float* dx_sum;                    // optional fp32 [C]: column sums of dx before the addends (the producer's bias gradient)
@@ -186,35 +229,35 @@ struct BwdP {
   const bf16* add1a; const bf16* add1b; long long ld_add1a, ld_add1b;  // optional second addend, split like the sources
 };
 
-// dz = d(loss)/d(gamma*xhat+beta) for one 8-channel vector, from the loaded x, dy (and FiLM scale)
-__device__ __forceinline__ void bwd_dz(const BwdP& p, const Chan& ch, const bf16x8& xv, const bf16x8& dyv, const bf16x8& scv, long long row, int c0,
-                                       int C, unsigned long long seed, float keep, float* xh, float* dz, float* dsc, float* dsh) {
-  float f[8], dy[8], sc[8];
-  b3d_unpack8(xv, f); b3d_unpack8(dyv, dy);
-  if (p.mode == 2) b3d_unpack8(scv, sc);
+// dz = d(loss)/d(gamma*xhat+beta) for one 8-channel vector, from the loaded x, dy (and FiLM scale / dropout mask m)
+template <int MODE>
+__device__ __forceinline__ void bwd_dz(const Aff& ch, const float* f, const float* dy, const float* sc, const float* m, bool drop,
+                                       float* dz, float* dsc, float* dsh) {
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
-    xh[j] = (f[j] - ch.mean[j]) * ch.rstd[j];
-    const float z = xh[j] * ch.gamma[j] + ch.beta[j];
+    const float z = fmaf(f[j], ch.a[j], ch.b[j]);
     float d = dy[j];
-    if (p.mode == 1) d *= b3d_silu_grad(z);
-    else if (p.mode == 2) {
-      if (p.drop_p > 0.f) d = (b3d_uniform(seed, (unsigned long long)row * C + c0 + j) < p.drop_p) ? 0.f : d * keep;
+    if (MODE == 1) d *= b3d_silu_grad(z);
+    else if (MODE == 2) {
+      if (drop) d *= m[j];
       dsc[j] = d * z; dsh[j] = d;
-      d *= (1.f + sc[j]);
+      d = fmaf(d, sc[j], d);
     }
     dz[j] = d;
   }
 }
 
-// pass 1: d_scale/d_shift (film), dgamma/dbeta, per-(image,group) S1 = sum dz*gamma, S2 = sum dz*gamma*xhat
-__global__ void __launch_bounds__(kT, 2) gn_bwd_reduce_kernel(BwdP p, int rows_per_block) {
+// pass 1: d_scale/d_shift (film), dgamma/dbeta, per-(image,group) S1 = sum dz*gamma, S2 = sum dz*gamma*xhat.
+// The loop accumulates sum dz*x and sum dz per channel; xhat = (x - mean)*rstd is applied to the block's partial sums
+// (one image per block, so mean/rstd are block constants per group).
+template <int MODE>
+__global__ void __launch_bounds__(kT, MODE == 2 ? kBwdBlocks2 : kBwdBlocks1) gn_bwd_reduce_kernel(BwdP p, int rows_per_block) {
   extern __shared__ float sm[];  // red [256*8] | dgamma [C] | dbeta [C] | dscale-sum [C] | dshift-sum [C]
   __shared__ float s_mean[G], s_rstd[G];
-  constexpr int U = 2;
+  constexpr int U = MODE == 2 ? kBwdU2 : kBwdU1;
   const int C = p.s.C0 + p.s.C1, cpg = C / G, n = blockIdx.y, vecs = C / 8;
   float* red = sm; float* r_g = sm + 2048; float* r_b = r_g + C; float* r_sc = r_b + C; float* r_sh = r_sc + C;
-  const bool want_ss = p.mode == 2 && p.dss_sum != nullptr;
+  const bool want_ss = MODE == 2 && p.dss_sum != nullptr;
   block_stats(p.stats, n, cpg, p.HW, s_mean, s_rstd);
   __syncthreads();
   const int r0 = blockIdx.x * rows_per_block, r1 = min(p.HW, r0 + rows_per_block);
@@ -225,11 +268,12 @@ __global__ void __launch_bounds__(kT, 2) gn_bwd_reduce_kernel(BwdP p, int rows_p
 #pragma unroll
   for (int j = 0; j < 8; ++j) { ag[j] = 0.f; ab[j] = 0.f; asc[j] = 0.f; ash[j] = 0.f; }
   if (active) {
-    Chan ch; load_chan(ch, p.gamma, p.beta, c0, cpg, s_mean, s_rstd);
+    Aff ch; load_aff(ch, p.gamma, p.beta, c0, cpg, s_mean, s_rstd);
     const RowPtr rp = src_ptr(p.s, c0);
     const long long img = (long long)n * p.HW;
-    const float keep = 1.f / (1.f - p.drop_p);
-    const unsigned long long seed = p.seed + (p.seed_ptr ? *p.seed_ptr : 0ULL);
+    const bool drop = MODE == 2 && p.drop_p > 0.f;
+    Drop dr{};
+    if (drop) dr = make_drop(p.drop_p, p.seed, p.seed_ptr);
     for (int r = r0 + rsub; r < r1; r += rows_par * U) {
       bf16x8 x[U], dy[U], sc[U];
 #pragma unroll
@@ -238,22 +282,27 @@ __global__ void __launch_bounds__(kT, 2) gn_bwd_reduce_kernel(BwdP p, int rows_p
         const bool ok = r + u * rows_par < r1;
         x[u] = ok ? ld8(rp.p + row * rp.ld) : zero8();
         dy[u] = ok ? ld8(p.dy + row * p.ld_dy + c0) : zero8();
-        sc[u] = (ok && p.mode == 2) ? ld8(p.ss + row * p.ld_ss + c0) : zero8();
+        if (MODE == 2) sc[u] = ok ? ld8(p.ss + row * p.ld_ss + c0) : zero8();
       }
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         if (r + u * rows_par >= r1) break;
         const long long row = img + r + u * rows_par;
-        float xh[8], dz[8], dsc[8], dsh[8];
-        bwd_dz(p, ch, x[u], dy[u], sc[u], row, c0, C, seed, keep, xh, dz, dsc, dsh);
-        if (p.mode == 2) {
+        float f[8], d[8], s8[8], m[8], dz[8], dsc[8], dsh[8];
+        b3d_unpack8(x[u], f); b3d_unpack8(dy[u], d);
+        if (MODE == 2) {
+          b3d_unpack8(sc[u], s8);
+          if (drop) drop_mask8(dr, (unsigned long long)row * C + c0, m);
+        }
+        bwd_dz<MODE>(ch, f, d, s8, m, drop, dz, dsc, dsh);
+        if (MODE == 2) {
           *reinterpret_cast<bf16x8*>(p.dss + row * p.ld_dss + c0) = b3d_pack8(dsc);
           *reinterpret_cast<bf16x8*>(p.dss + row * p.ld_dss + p.F + c0) = b3d_pack8(dsh);
 #pragma unroll
           for (int j = 0; j < 8; ++j) { asc[j] += dsc[j]; ash[j] += dsh[j]; }
         }
 #pragma unroll
-        for (int j = 0; j < 8; ++j) { ag[j] += dz[j] * xh[j]; ab[j] += dz[j]; }
+        for (int j = 0; j < 8; ++j) { ag[j] = fmaf(dz[j], f[j], ag[j]); ab[j] += dz[j]; }
       }
     }
   }
@@ -264,10 +313,14 @@ __global__ void __launch_bounds__(kT, 2) gn_bwd_reduce_kernel(BwdP p, int rows_p
     block_sum8(ash, active, v, rsub, rows_par, C, red, r_sh);
   }
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
-    atomicAdd(&p.dgamma[c], r_g[c]);
+    const int g = c / cpg;
+    const float dg = s_rstd[g] * (r_g[c] - s_mean[g] * r_b[c]);   // sum dz*xhat
+    r_g[c] = dg;
+    atomicAdd(&p.dgamma[c], dg);
     atomicAdd(&p.dbeta[c], r_b[c]);
     if (want_ss) { atomicAdd(&p.dss_sum[c], r_sc[c]); atomicAdd(&p.dss_sum[p.F + c], r_sh[c]); }
   }
+  __syncthreads();
   if (threadIdx.x < G) {
     float s1 = 0.f, s2 = 0.f;
     for (int c = threadIdx.x * cpg; c < (threadIdx.x + 1) * cpg; ++c) { const float gam = p.gamma[c]; s1 += r_b[c] * gam; s2 += r_g[c] * gam; }
@@ -276,17 +329,21 @@ __global__ void __launch_bounds__(kT, 2) gn_bwd_reduce_kernel(BwdP p, int rows_p
   }
 }
 
-// pass 2: dx = rstd * (dz*gamma - (S1 + xhat*S2)/cnt) [+ add0] [+ add1]
-__global__ void __launch_bounds__(kT, 2) gn_bwd_apply_kernel(BwdP p, int rows_per_block) {
+// pass 2: dx = rstd * (dz*gamma - (S1 + xhat*S2)/cnt) [+ add0] [+ add1]  =  dz*a + x*c1 + c0 per channel
+template <int MODE>
+__global__ void __launch_bounds__(kT, MODE == 2 ? kBwdBlocks2 : kBwdBlocks1) gn_bwd_apply_kernel(BwdP p, int rows_per_block) {
   extern __shared__ float sm[];   // red [256*8] | column sums of dx [C]   (used when p.dx_sum is set)
-  __shared__ float s_mean[G], s_rstd[G], s_s1[G], s_s2[G];
-  constexpr int U = 2;
+  __shared__ float s_mean[G], s_rstd[G], s_c1[G], s_c0[G];
+  constexpr int U = kBwdApplyU;
   const int C = p.s.C0 + p.s.C1, cpg = C / G, n = blockIdx.y, vecs = C / 8;
   block_stats(p.stats, n, cpg, p.HW, s_mean, s_rstd);
   if (threadIdx.x < G) {
+    // same thread wrote s_mean/s_rstd[threadIdx.x] above
     const float cnt = (float)cpg * (float)p.HW;
-    s_s1[threadIdx.x] = p.ws[((long long)n * G + threadIdx.x) * 2] / cnt;
-    s_s2[threadIdx.x] = p.ws[((long long)n * G + threadIdx.x) * 2 + 1] / cnt;
+    const float s1 = p.ws[((long long)n * G + threadIdx.x) * 2] / cnt, s2 = p.ws[((long long)n * G + threadIdx.x) * 2 + 1] / cnt;
+    const float rstd = s_rstd[threadIdx.x], c1 = -rstd * rstd * s2;
+    s_c1[threadIdx.x] = c1;
+    s_c0[threadIdx.x] = -rstd * s1 - c1 * s_mean[threadIdx.x];
   }
   __syncthreads();
   const int r0 = blockIdx.x * rows_per_block, r1 = min(p.HW, r0 + rows_per_block);
@@ -297,48 +354,54 @@ __global__ void __launch_bounds__(kT, 2) gn_bwd_apply_kernel(BwdP p, int rows_pe
 #pragma unroll
   for (int j = 0; j < 8; ++j) acc[j] = 0.f;
   if (active) {
-  Chan ch; load_chan(ch, p.gamma, p.beta, c0, cpg, s_mean, s_rstd);
-  float s1[8], s2[8];
+    Aff ch; load_aff(ch, p.gamma, p.beta, c0, cpg, s_mean, s_rstd);
+    float k1[8], k0[8];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) { const int g = (c0 + j) / cpg; s1[j] = s_s1[g]; s2[j] = s_s2[g]; }
-  const RowPtr rp = src_ptr(p.s, c0);
-  const bool first = c0 < p.s.C0;
-  const bf16* ad1 = first ? p.add1a : p.add1b;
-  const long long ld_ad1 = first ? p.ld_add1a : p.ld_add1b;
-  const int c1 = first ? c0 : c0 - p.s.C0;
-  bf16* dxp = first ? p.dx0 : p.dx1;
-  const long long ld_dx = first ? p.ld_dx0 : p.ld_dx1;
-  const long long img = (long long)n * p.HW;
-  const float keep = 1.f / (1.f - p.drop_p);
-  const unsigned long long seed = p.seed + (p.seed_ptr ? *p.seed_ptr : 0ULL);
-  for (int r = r0 + rsub; r < r1; r += rows_par * U) {
-    bf16x8 x[U], dy[U], sc[U], a0[U], a1[U];
+    for (int j = 0; j < 8; ++j) { const int g = (c0 + j) / cpg; k1[j] = s_c1[g]; k0[j] = s_c0[g]; }
+    const RowPtr rp = src_ptr(p.s, c0);
+    const bool first = c0 < p.s.C0;
+    const bf16* ad1 = first ? p.add1a : p.add1b;
+    const long long ld_ad1 = first ? p.ld_add1a : p.ld_add1b;
+    const int c1 = first ? c0 : c0 - p.s.C0;
+    bf16* dxp = first ? p.dx0 : p.dx1;
+    const long long ld_dx = first ? p.ld_dx0 : p.ld_dx1;
+    const long long img = (long long)n * p.HW;
+    const bool drop = MODE == 2 && p.drop_p > 0.f;
+    Drop dr{};
+    if (drop) dr = make_drop(p.drop_p, p.seed, p.seed_ptr);
+    for (int r = r0 + rsub; r < r1; r += rows_par * U) {
+      bf16x8 x[U], dy[U], sc[U], a0[U], a1[U];
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const long long row = img + r + u * rows_par;
-      const bool ok = r + u * rows_par < r1;
-      x[u] = ok ? ld8(rp.p + row * rp.ld) : zero8();
-      dy[u] = ok ? ld8(p.dy + row * p.ld_dy + c0) : zero8();
-      sc[u] = (ok && p.mode == 2) ? ld8(p.ss + row * p.ld_ss + c0) : zero8();
-      a0[u] = (ok && p.add0) ? ld8(p.add0 + row * p.ld_add0 + c0) : zero8();
-      a1[u] = (ok && ad1) ? ld8(ad1 + row * ld_ad1 + c1) : zero8();
-    }
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      if (r + u * rows_par >= r1) break;
-      const long long row = img + r + u * rows_par;
-      float xh[8], dz[8], dsc[8], dsh[8], dx[8], t0[8], t1[8];
-      bwd_dz(p, ch, x[u], dy[u], sc[u], row, c0, C, seed, keep, xh, dz, dsc, dsh);
-      b3d_unpack8(a0[u], t0); b3d_unpack8(a1[u], t1);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const float d = ch.rstd[j] * (dz[j] * ch.gamma[j] - s1[j] - xh[j] * s2[j]);
-        acc[j] += d;
-        dx[j] = d + t0[j] + t1[j];
+      for (int u = 0; u < U; ++u) {
+        const long long row = img + r + u * rows_par;
+        const bool ok = r + u * rows_par < r1;
+        x[u] = ok ? ld8(rp.p + row * rp.ld) : zero8();
+        dy[u] = ok ? ld8(p.dy + row * p.ld_dy + c0) : zero8();
+        if (MODE == 2) sc[u] = ok ? ld8(p.ss + row * p.ld_ss + c0) : zero8();
+        a0[u] = (ok && p.add0) ? ld8(p.add0 + row * p.ld_add0 + c0) : zero8();
+        a1[u] = (ok && ad1) ? ld8(ad1 + row * ld_ad1 + c1) : zero8();
       }
-      *reinterpret_cast<bf16x8*>(dxp + row * ld_dx + c1) = b3d_pack8(dx);
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        if (r + u * rows_par >= r1) break;
+        const long long row = img + r + u * rows_par;
+        float f[8], d[8], s8[8], m[8], dz[8], dsc[8], dsh[8], t0[8], t1[8];
+        b3d_unpack8(x[u], f); b3d_unpack8(dy[u], d);
+        if (MODE == 2) {
+          b3d_unpack8(sc[u], s8);
+          if (drop) drop_mask8(dr, (unsigned long long)row * C + c0, m);
+        }
+        bwd_dz<MODE>(ch, f, d, s8, m, drop, dz, dsc, dsh);
+        b3d_unpack8(a0[u], t0); b3d_unpack8(a1[u], t1);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float g = fmaf(dz[j], ch.a[j], fmaf(f[j], k1[j], k0[j]));
+          acc[j] += g;
+          d[j] = g + t0[j] + t1[j];
+        }
+        *reinterpret_cast<bf16x8*>(dxp + row * ld_dx + c1) = b3d_pack8(d);
+      }
     }
-  }
   }
   if (p.dx_sum) {
     block_sum8(acc, active, v, rsub, rows_par, C, sm, sm + 2048);
@@ -346,11 +409,12 @@ __global__ void __launch_bounds__(kT, 2) gn_bwd_apply_kernel(BwdP p, int rows_pe
   }
 }
 
-int pick_rows_per_block(int N, int HW, int C, int U) {
-  // ~2 waves of 8 blocks per SM over the whole launch, but never fewer rows than one unrolled sweep of the block
+// rows of one image per block: about `waves` full waves of `blocks_per_sm` resident blocks per SM over the whole launch
+// (many short waves keep the last, partial one cheap), but never fewer rows than one unrolled sweep of the block
+int pick_rows_per_block(int N, int HW, int C, int U, int blocks_per_sm, int waves = 8) {
   const int vecs = C / 8;
   const int rows_par = 256 / vecs > 0 ? 256 / vecs : 1;
-  int per_img = (148 * 16 + N - 1) / N;
+  int per_img = (b3d_num_sms() * blocks_per_sm * waves + N - 1) / N;
   if (per_img < 1) per_img = 1;
   int rpb = (HW + per_img - 1) / per_img;
   const int min_rows = rows_par * U;
@@ -375,7 +439,7 @@ extern "C" int b3d_gn_stats(const void* x0, int C0, int64_t ld0, const void* x1,
                             void* stream) {
   if (int rc = check_src(x0, C0, x1, C1)) return rc;
   Src2 s{(const bf16*)x0, (const bf16*)x1, C0, C1, ld0, ld1};
-  const int C = C0 + C1, rpb = pick_rows_per_block(N, HW, C, 4);
+  const int C = C0 + C1, rpb = pick_rows_per_block(N, HW, C, 4, 8, 2);   // measured: 2 long waves beat 1, 4 and 8 (block epilogue cost)
   dim3 grid((HW + rpb - 1) / rpb, N);
   gn_stats_kernel<<<grid, kT, (2048 + 2 * C) * sizeof(float), (cudaStream_t)stream>>>(s, HW, rpb, ws_sums);
   B3D_LAUNCH_CHECK();
@@ -394,9 +458,11 @@ extern "C" int b3d_gn_apply(const void* x0, int C0, int64_t ld0, const void* x1,
   p.s = Src2{(const bf16*)x0, (const bf16*)x1, C0, C1, ld0, ld1};
   p.stats = sums; p.gamma = gamma; p.beta = beta; p.out = (bf16*)out; p.ld_out = ld_out; p.HW = HW; p.mode = mode;
   p.ss = (const bf16*)ss; p.ld_ss = ld_ss; p.F = F; p.drop_p = drop_p; p.seed = seed; p.seed_ptr = (const unsigned long long*)seed_ptr;
-  const int rpb = pick_rows_per_block(N, HW, C0 + C1, 4);
+  const int rpb = pick_rows_per_block(N, HW, C0 + C1, mode == 2 ? kApplyU2 : kApplyU0, mode == 2 ? 3 : 4);
   dim3 grid((HW + rpb - 1) / rpb, N);
-  gn_apply_kernel<<<grid, kT, 0, (cudaStream_t)stream>>>(p, rpb);
+  if (mode == 0) gn_apply_kernel<0><<<grid, kT, 0, (cudaStream_t)stream>>>(p, rpb);
+  else if (mode == 1) gn_apply_kernel<1><<<grid, kT, 0, (cudaStream_t)stream>>>(p, rpb);
+  else gn_apply_kernel<2><<<grid, kT, 0, (cudaStream_t)stream>>>(p, rpb);
   B3D_LAUNCH_CHECK();
   b3d_count_launch(1);
   return B3D_OK;
@@ -420,12 +486,26 @@ extern "C" int b3d_gn_bwd(const void* x0, int C0, int64_t ld0, const void* x1, i
   p.dx0 = (bf16*)dx0; p.dx1 = (bf16*)dx1; p.ld_dx0 = ld_dx0; p.ld_dx1 = ld_dx1;
   p.add0 = (const bf16*)add0; p.ld_add0 = ld_add0;
   p.add1a = (const bf16*)add1a; p.add1b = (const bf16*)add1b; p.ld_add1a = ld_add1a; p.ld_add1b = ld_add1b;
-  const int C = C0 + C1, rpb = pick_rows_per_block(N, HW, C, 2);
-  dim3 grid((HW + rpb - 1) / rpb, N);
-  gn_bwd_reduce_kernel<<<grid, kT, (2048 + 4 * C) * sizeof(float), (cudaStream_t)stream>>>(p, rpb);
-  B3D_LAUNCH_CHECK();
-  gn_bwd_apply_kernel<<<grid, kT, (2048 + C) * sizeof(float), (cudaStream_t)stream>>>(p, rpb);
-  B3D_LAUNCH_CHECK();
+  const int C = C0 + C1;
+  cudaStream_t st = (cudaStream_t)stream;
+  {
+    const int rpb = pick_rows_per_block(N, HW, C, mode == 2 ? kBwdU2 : kBwdU1, mode == 2 ? kBwdBlocks2 : kBwdBlocks1);
+    dim3 grid((HW + rpb - 1) / rpb, N);
+    const size_t smem = (2048 + 4 * C) * sizeof(float);
+    if (mode == 0) gn_bwd_reduce_kernel<0><<<grid, kT, smem, st>>>(p, rpb);
+    else if (mode == 1) gn_bwd_reduce_kernel<1><<<grid, kT, smem, st>>>(p, rpb);
+    else gn_bwd_reduce_kernel<2><<<grid, kT, smem, st>>>(p, rpb);
+    B3D_LAUNCH_CHECK();
+  }
+  {
+    const int rpb = pick_rows_per_block(N, HW, C, kBwdApplyU, mode == 2 ? kBwdBlocks2 : kBwdBlocks1);
+    dim3 grid((HW + rpb - 1) / rpb, N);
+    const size_t smem = (2048 + C) * sizeof(float);
+    if (mode == 0) gn_bwd_apply_kernel<0><<<grid, kT, smem, st>>>(p, rpb);
+    else if (mode == 1) gn_bwd_apply_kernel<1><<<grid, kT, smem, st>>>(p, rpb);
+    else gn_bwd_apply_kernel<2><<<grid, kT, smem, st>>>(p, rpb);
+    B3D_LAUNCH_CHECK();
+  }
   b3d_count_launch(2);
   return B3D_OK;
 }

@@ -20,18 +20,20 @@ def _ceil64(c):
     return (c + 63) // 64 * 64
 
 
-def hash_uniform(seed, idx):
-    """bit-exact mirror of b3d_uniform (csrc/b3d_common.cuh) on int64 tensors"""
-    M = (1 << 64) - 1
-    out = torch.empty(idx.numel(), dtype=torch.float64)
-    flat = idx.flatten().tolist()
-    for i, v in enumerate(flat):
-        x = (seed * 0x9E3779B97F4A7C15 + v) & M
-        x ^= x >> 33; x = (x * 0xff51afd7ed558ccd) & M
-        x ^= x >> 33; x = (x * 0xc4ceb9fe1a85ec53) & M
-        x ^= x >> 33
-        out[i] = ((x & 0xFFFFFFFF) >> 8) / 16777216.0
-    return out.reshape(idx.shape).float()
+def drop_keep(seed, idx, drop_p):
+    """bit-exact mirror of the dropout keep decision (b3d_drop_pair / b3d_drop_thr16 in csrc/b3d_common.cuh, drop_mask8
+    in csrc/groupnorm.cu) on an int64 tensor of flat element indices: True where the element is kept."""
+    import numpy as np
+    e = idx.numpy().astype(np.uint64)
+    with np.errstate(over="ignore"):
+        key = np.uint64((seed * 0x9E3779B97F4A7C15) & ((1 << 64) - 1)) + (e >> np.uint64(1))
+        x = (key & np.uint64(0xFFFFFFFF)).astype(np.uint32) ^ ((key >> np.uint64(32)).astype(np.uint32) * np.uint32(0x9E3779B9))
+        x ^= x >> np.uint32(16); x *= np.uint32(0x7feb352d)
+        x ^= x >> np.uint32(15); x *= np.uint32(0x846ca68b)
+        x ^= x >> np.uint32(16)
+    field = np.where((e & np.uint64(1)) == 0, x & np.uint32(0xFFFF), x >> np.uint32(16)).astype(np.int64)
+    thr16 = int(np.float32(drop_p) * np.float32(65536.0) + np.float32(0.5))
+    return torch.from_numpy(field >= thr16)
 
 
 class EmuOps:
@@ -352,8 +354,8 @@ class EmuOps:
         if drop_p <= 0:
             return torch.ones(shape)
         idx = torch.arange(int(torch.tensor(shape).prod())).reshape(shape)
-        u = hash_uniform(seed, idx)
-        return torch.where(u < drop_p, torch.zeros(shape), torch.full(shape, 1.0 / (1.0 - drop_p)))
+        keep = drop_keep(seed, idx, drop_p)
+        return torch.where(keep, torch.full(shape, 1.0 / (1.0 - drop_p)), torch.zeros(shape))
 
     def gn_apply(self, x0, x1, sums, gamma, beta, mode, out, ss=None, F=0, drop_p=0.0, seed=0, seed_ptr=None):
         seed = seed + (int(seed_ptr.item()) if seed_ptr is not None else 0)

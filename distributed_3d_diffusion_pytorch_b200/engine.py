@@ -433,6 +433,7 @@ class Engine:
         for ph in ((0, 1, 2) if phase is None else (phase,)):
             self._cur_phase = ph
             (self._bwd_phase0, self._bwd_phase1, self._bwd_phase2)[ph](Gr, deps, grad_flat)
+            self.ops.join_side()
             self.ops.run_jobs(self._unpack_jl[ph])     # packed fp32 weight gradients of this phase -> PyTorch layout, one launch
             self.ops.run_jobs(self._copy_jl[ph])
 
@@ -592,28 +593,32 @@ class Engine:
         gs = self.tmp("gs", (N, hh, ww, F))
         ops.scale_colsum(dout, gs, RSQRT2, Gr[n + ".conv2.bias"])     # d(conv2.bias) = column sums of the scaled gradient
         gs2 = gs.view(M, F)
-        # conv2
-        self._conv_wgrad(n + ".conv2.weight", gs, sa["a1"].view(N, hh, ww, F), Gr[n + ".conv2.weight"])
+        # weight gradients of conv2 and the 1x1 skip: on the side stream, beside the data-gradient chain below (they only
+        # read gs and saved activations; joined at the end of the block, before gs is rewritten)
+        with ops.side():
+            self._conv_wgrad(n + ".conv2.weight", gs, sa["a1"].view(N, hh, ww, F), Gr[n + ".conv2.weight"])
+            if s.cin != F:
+                gw = Gr[n + ".dense.weight"].view(F, s.cin)
+                srcs = [h_in] + ([skip] if skip is not None else [])
+                koff = 0
+                if len(srcs) == 1:
+                    ops.gemm(G.wgrad_dense_desc(gs2, h_in.t.view(M, s.cin), gw))
+                else:
+                    gp = self.zbuf("bwd", "gp." + n + ".dense", (F, sum(G.ceil64(a.t.shape[3]) for a in srcs)))
+                    ci0 = 0
+                    for a in srcs:
+                        c = a.t.shape[3]
+                        ops.gemm(G.wgrad_desc(gs, a.t, 1, gp, koff, G.ceil64(c)))
+                        self._unpack(gp, koff, G.ceil64(c), Gr[n + ".dense.weight"], ci0=ci0, cn=c)
+                        koff += G.ceil64(c)
+                        ci0 += c
+        # conv2 data gradient
         da1 = self.tmp("da1", (N, hh, ww, F))
         ops.gemm(G.conv_desc([gs], [9], Wp[n + ".conv2.weight.T"], F, da1))
         # 1x1 skip
         if s.cin != F:
             if self._unpack_rec:       # d(dense.bias) = the same column sums as d(conv2.bias): copied at the end of backward
                 ops.record_copy(self._copy_jl[self._cur_phase], Gr[n + ".conv2.bias"], Gr[n + ".dense.bias"])
-            gw = Gr[n + ".dense.weight"].view(F, s.cin)
-            srcs = [h_in] + ([skip] if skip is not None else [])
-            koff = 0
-            if len(srcs) == 1:
-                ops.gemm(G.wgrad_dense_desc(gs2, h_in.t.view(M, s.cin), gw))
-            else:
-                gp = self.zbuf("bwd", "gp." + n + ".dense", (F, sum(G.ceil64(a.t.shape[3]) for a in srcs)))
-                ci0 = 0
-                for a in srcs:
-                    c = a.t.shape[3]
-                    ops.gemm(G.wgrad_desc(gs, a.t, 1, gp, koff, G.ceil64(c)))
-                    self._unpack(gp, koff, G.ceil64(c), Gr[n + ".dense.weight"], ci0=ci0, cn=c)
-                    koff += G.ceil64(c)
-                    ci0 += c
             dskip = self.tmp("dskip", (N, HW, s.cin))
             ops.gemm(G.dense_desc(gs2, Wp[n + ".dense.weight.T"], dskip.view(M, s.cin), s.cin))
             add0 = dskip
@@ -629,9 +634,10 @@ class Engine:
                    seed_ptr=self.seed_ptr, dss_sum=Gr[n + ".film.dense.bias"], dx_sum=Gr[n + ".conv1.bias"])
         # FiLM dense parameters (xunet.py:80,84): per block, straight into the parameter gradients
         sil = self._bufs[f"emb_silu{s.lvl}"].view(M, 1024)
-        ops.gemm(G.wgrad_dense_desc(dssv, sil, Gr[n + ".film.dense.weight"]))
-        # conv1 (its bias gradient and the FiLM bias gradient were reduced inside the GroupNorm backward above)
-        self._conv_wgrad(n + ".conv1.weight", dc1, sa["a0"].view(N, hh, ww, s.cin), Gr[n + ".conv1.weight"])
+        with ops.side():
+            ops.gemm(G.wgrad_dense_desc(dssv, sil, Gr[n + ".film.dense.weight"]))
+            # conv1 (its bias gradient and the FiLM bias gradient were reduced inside the GroupNorm backward above)
+            self._conv_wgrad(n + ".conv1.weight", dc1, sa["a0"].view(N, hh, ww, s.cin), Gr[n + ".conv1.weight"])
         da0 = self.tmp("da0", (N, hh, ww, s.cin))
         ops.gemm(G.conv_desc([dc1], [9], Wp[n + ".conv1.weight.T"], s.cin, da0))
         # GN0 + SiLU, merged with the skip-path gradient and with earlier contributions to the inputs
@@ -646,6 +652,7 @@ class Engine:
         ops.gn_bwd(x0, x1, sa["sums0"], P[n + ".groupnorm0.gn.weight"], P[n + ".groupnorm0.gn.bias"], 1, da0.view(N, HW, s.cin),
                    Gr[n + ".groupnorm0.gn.weight"], Gr[n + ".groupnorm0.gn.bias"], self.zbuf("bwd", n + ".ws0", (N, 32, 2)), v3(g0), v3(g1),
                    add0=add0, add1a=v3(e0), add1b=v3(e1))
+        ops.join_side()
 
     def _attn_bwd(self, s, P, Wp, Gr):
         ops, N, n, C = self.ops, self.N, s.name, s.c
@@ -661,11 +668,13 @@ class Engine:
         ops.scale_colsum(dout, gs4, RSQRT2, Gr[n + ".linear.bias"])
         gs = gs4.view(M, C)
         # 1x1 `linear` and out_proj
-        ops.gemm(G.wgrad_dense_desc(gs, sa["o1"], Gr[n + ".linear.weight"].view(C, C)))
+        with ops.side():      # parameter gradients run beside the data-gradient chain (joined at the end of the block)
+            ops.gemm(G.wgrad_dense_desc(gs, sa["o1"], Gr[n + ".linear.weight"].view(C, C)))
         do1 = self.tmp("do1", (M, C))
         ops.gemm(G.dense_desc(gs, Wp[n + ".linear.weight.T"], do1, C))
-        ops.colsum(do1, M, Gr[a + ".out_proj.bias"])
-        ops.gemm(G.wgrad_dense_desc(do1, sa["o"].view(M, C), Gr[a + ".out_proj.weight"]))
+        with ops.side():
+            ops.colsum(do1, M, Gr[a + ".out_proj.bias"])
+            ops.gemm(G.wgrad_dense_desc(do1, sa["o"].view(M, C), Gr[a + ".out_proj.weight"]))
         do = self.tmp("do", (N, L, C))
         ops.gemm(G.dense_desc(do1, Wp[a + ".out_proj.weight.T"], do.view(M, C), C))
         # attention core
@@ -684,8 +693,9 @@ class Engine:
         ops.gemm(G.attn_dk_desc(dp, q, dk, s.cross, alpha))
         # in_proj
         dq2 = dqkv.view(M, 3 * C)
-        ops.colsum(dq2, M, Gr[a + ".in_proj_bias"])
-        ops.gemm(G.wgrad_dense_desc(dq2, sa["g"].view(M, C), Gr[a + ".in_proj_weight"]))
+        with ops.side():
+            ops.colsum(dq2, M, Gr[a + ".in_proj_bias"])
+            ops.gemm(G.wgrad_dense_desc(dq2, sa["g"].view(M, C), Gr[a + ".in_proj_weight"]))
         dg = self.tmp("dg", (N, L, C))
         ops.gemm(G.dense_desc(dq2, Wp[a + ".in_proj_weight.T"], dg.view(M, C), C))
         # GroupNorm + residual branch
@@ -693,3 +703,4 @@ class Engine:
         ops.gn_bwd(h_in.t.view(N, L, C), None, sa["sums"], P[n + ".groupnorm.gn.weight"], P[n + ".groupnorm.gn.bias"], 0, dg,
                    Gr[n + ".groupnorm.gn.weight"], Gr[n + ".groupnorm.gn.bias"], self.zbuf("bwd", n + ".ws", (N, 32, 2)),
                    g0.view(N, L, C), None, add0=gs.view(N, L, C), add1a=e0.view(N, L, C) if e0 is not None else None)
+        ops.join_side()

@@ -4,6 +4,7 @@ torch is plumbing here (device memory, streams); all arithmetic happens in libb3
 passed as (data_ptr, strides) -- any view whose innermost stride is 1 is accepted, so channel
 slices / head splits need no copies.  There is no fallback path: without the CUDA library every
 method raises (see _lib.load)."""
+import contextlib
 import ctypes
 from dataclasses import dataclass, field
 from typing import List, Optional
@@ -136,6 +137,31 @@ class CudaOps:
 
     def zeros(self, shape, dtype=None):
         return torch.zeros(shape, dtype=dtype or self.act_dtype, device=self.device)
+
+    # ---- second stream for launches whose results nothing downstream reads until the end of a phase (weight / bias
+    # gradients): they overlap the data-gradient chain, filling SMs that small or tail-end launches leave idle.
+    # Works eagerly and under stream capture (the fork/join become graph edges).
+    use_side = True
+    _side, _side_dirty = None, False
+
+    @contextlib.contextmanager
+    def side(self):
+        """launches inside run on the side stream, after everything issued so far on the current stream"""
+        if self.prof is not None or not self.use_side:
+            yield
+            return
+        if self._side is None:
+            self._side = torch.cuda.Stream(self.device)
+        self._side.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(self._side):
+            yield
+        self._side_dirty = True
+
+    def join_side(self):
+        """the current stream waits for everything issued on the side stream"""
+        if self._side_dirty:
+            torch.cuda.current_stream(self.device).wait_stream(self._side)
+            self._side_dirty = False
 
     prof = None          # when a list: (name, start_event, end_event, flop, info) per launch (bench.py's profiled step)
     _flop, _info = 0.0, ""

@@ -44,6 +44,13 @@ class EmuOps:
         self.device = torch.device(device)
         self.act_dtype = act_dtype
 
+    def side(self):
+        import contextlib
+        return contextlib.nullcontext()
+
+    def join_side(self):
+        pass
+
     def empty(self, shape, dtype=None):
         return torch.full(shape, float("nan"), dtype=dtype or self.act_dtype, device=self.device)
 

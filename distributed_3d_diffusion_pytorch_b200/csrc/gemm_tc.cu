@@ -114,7 +114,10 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
   __shared__ uint64_t bars[2 * 8 + 4 + 2];
   __shared__ uint32_t tmem_base_smem;
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // warp index through a shuffle so the compiler knows it is warp-uniform: the producer and MMA loops below then run on
+  // uniform registers (a `lane == 0` region made every TMA / MMA operand go through an ELECT + R2UR.BROADCAST loop, and
+  // the ~130 instructions per K block of the single issuing thread, not the tensor pipe, paced the kernel).
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const int S = p.num_stages;
   auto full_bar = [&](int s) { return smem_u32(&bars[s]); };
@@ -136,7 +139,8 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
 
   if (warp == 0) {
     // ===================================================================== TMA producer
-    if (lane == 0) {
+    // The whole warp walks the (warp-uniform) loops and polls the barriers; one elected lane issues the copies.
+    {
       int stage = 0; uint32_t phase = 0;
       for (int t = blockIdx.x; t < p.tiles_total; t += gridDim.x) {
         const TileCoord c = decode_tile(p, t);
@@ -144,7 +148,6 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
         const int ncol0 = c.tn * p.BN;
         auto acquire = [&]() -> uint32_t {
           mbar_wait(empty_bar(stage), phase ^ 1);
-          mbar_expect_tx(full_bar(stage), p.a_tx + p.b_tx);
           return smem_base + (uint32_t)stage * p.stage_bytes;
         };
         auto advance = [&]() { if (++stage == S) { stage = 0; phase ^= 1; } };
@@ -155,17 +158,23 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
             const int ax = c.x0 * p.stride + sg.dx, ay = c.y0 * p.stride + sg.dy;
             for (int cb = 0; cb < sg.ncb; ++cb) {
               const uint32_t sa = acquire();
-              tma_load_4d(sa, &p.tmA[sg.src], full_bar(stage), cb * BK, ax, ay, c.n0);
-              tma_load_4d(sa + kABytes, &p.tmB, full_bar(stage), sg.bk0 + cb * BK, ncol0, by, bn);
+              if (elect_one()) {
+                mbar_expect_tx(full_bar(stage), p.a_tx + p.b_tx);
+                tma_load_4d(sa, &p.tmA[sg.src], full_bar(stage), cb * BK, ax, ay, c.n0);
+                tma_load_4d(sa + kABytes, &p.tmB, full_bar(stage), sg.bk0 + cb * BK, ncol0, by, bn);
+              }
               advance();
             }
           }
         } else if (p.a_major == 0) {  // (0,1): K = channels of A = pixels (x) of B, batched
           for (int cb = 0; cb < nkb; ++cb) {
             const uint32_t sa = acquire();
-            tma_load_4d(sa, &p.tmA[0], full_bar(stage), cb * BK, c.x0, c.y0, c.n0);
-            for (int j = 0; j < p.b_chunks; ++j)
-              tma_load_4d(sa + kABytes + j * 8192, &p.tmB, full_bar(stage), ncol0 + j * 64, cb * BK, c.y0, c.n0 ^ p.b_xor);
+            if (elect_one()) {
+              mbar_expect_tx(full_bar(stage), p.a_tx + p.b_tx);
+              tma_load_4d(sa, &p.tmA[0], full_bar(stage), cb * BK, c.x0, c.y0, c.n0);
+              for (int j = 0; j < p.b_chunks; ++j)
+                tma_load_4d(sa + kABytes + j * 8192, &p.tmB, full_bar(stage), ncol0 + j * 64, cb * BK, c.y0, c.n0 ^ p.b_xor);
+            }
             advance();
           }
         } else {  // (1,1): K = pixels of both
@@ -180,11 +189,14 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
               ky = (pb % p.kblk_y) * p.kbh; kn = (pb / p.kblk_y) * p.kbn;
             }
             const uint32_t sa = acquire();
-            tma_load_4d(sa, &p.tmA[0], full_bar(stage), c.m0, kx, ky, kn);
-            tma_load_4d(sa + 8192, &p.tmA[0], full_bar(stage), c.m0 + 64, kx, ky, kn);
-            for (int j = 0; j < p.b_chunks; ++j)
-              tma_load_4d(sa + kABytes + j * 8192, &p.tmB, full_bar(stage), ncol0 + j * 64, kx * p.stride + dx,
-                          ky * p.stride + dy, kn ^ p.b_xor);
+            if (elect_one()) {
+              mbar_expect_tx(full_bar(stage), p.a_tx + p.b_tx);
+              tma_load_4d(sa, &p.tmA[0], full_bar(stage), c.m0, kx, ky, kn);
+              tma_load_4d(sa + 8192, &p.tmA[0], full_bar(stage), c.m0 + 64, kx, ky, kn);
+              for (int j = 0; j < p.b_chunks; ++j)
+                tma_load_4d(sa + kABytes + j * 8192, &p.tmB, full_bar(stage), ncol0 + j * 64, kx * p.stride + dx,
+                            ky * p.stride + dy, kn ^ p.b_xor);
+            }
             advance();
           }
         }
@@ -192,11 +204,14 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
     }
   } else if (warp == 1) {
     // ===================================================================== MMA issuer
-    if (lane == 0) {
+    // Warp-uniform loop; the same elected lane issues every tcgen05.mma and the commits that track them.
+    {
       int stage = 0; uint32_t phase = 0;
       int acc = 0; uint32_t acc_phase = 0;
-      const uint32_t a_kstep = p.a_major ? 2048u : 32u, b_kstep = p.b_major ? 2048u : 32u;
+      const uint32_t a_kstep = p.a_major ? (2048u >> 4) : (32u >> 4), b_kstep = p.b_major ? (2048u >> 4) : (32u >> 4);
       const uint32_t a_lbo = p.a_major ? 8192u : 16u, b_lbo = p.b_major ? 8192u : 16u;
+      const uint64_t a_desc0 = umma_desc(0u, a_lbo, 1024u), b_desc0 = umma_desc(0u, b_lbo, 1024u);
+      const uint32_t idesc = p.idesc;
       for (int t = blockIdx.x; t < p.tiles_total; t += gridDim.x) {
         const TileCoord c = decode_tile(p, t);
         int kb0, nkb; k_range(p, c, kb0, nkb);
@@ -207,17 +222,16 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
           mbar_wait(full_bar(stage), phase);
           tc_fence_after();
           const uint32_t sa = smem_base + (uint32_t)stage * p.stage_bytes;
-          const uint32_t sb = sa + kABytes;
+          const uint64_t ad = a_desc0 + (uint64_t)(sa >> 4), bd = b_desc0 + (uint64_t)((sa + kABytes) >> 4);
+          if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < BK / 16; ++k) {
-            const uint64_t ad = umma_desc(sa + k * a_kstep, a_lbo, 1024u);
-            const uint64_t bd = umma_desc(sb + k * b_kstep, b_lbo, 1024u);
-            umma_bf16(d_tmem, ad, bd, p.idesc, (kb | k) != 0 ? 1u : 0u);
+            for (int k = 0; k < BK / 16; ++k)
+              umma_bf16(d_tmem, ad + (uint64_t)(k * a_kstep), bd + (uint64_t)(k * b_kstep), idesc, (kb | k) != 0 ? 1u : 0u);
+            umma_commit(empty_bar(stage));  // frees the smem slot once these MMAs have read it
           }
-          umma_commit(empty_bar(stage));  // frees the smem slot once these MMAs have read it
           if (++stage == S) { stage = 0; phase ^= 1; }
         }
-        umma_commit(tfull_bar(acc));      // accumulator complete -> epilogue
+        if (elect_one()) umma_commit(tfull_bar(acc));      // accumulator complete -> epilogue
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }

@@ -477,14 +477,36 @@ __global__ void sampler_update_dev_kernel(const float* __restrict__ z, const flo
 }
 
 // fused Adam over one flat fp32 parameter arena (train.py:235: lr 1e-4, betas (0.9, 0.99), eps 1e-8)
-__global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v, long long n,
-                            float lr, float b1, float b2, float eps, float bc1, float bc2, float grad_scale) {
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
-    const float gg = g[i] * grad_scale;
-    const float mm = b1 * m[i] + (1.f - b1) * gg;
-    const float vv = b2 * v[i] + (1.f - b2) * gg * gg;
-    m[i] = mm; v[i] = vv;
-    p[i] -= lr * (mm / bc1) / (sqrtf(vv / bc2) + eps);
+__device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, float lr, float b1, float b2, float eps, float ibc1, float ibc2,
+                                         float grad_scale) {
+  const float gg = g * grad_scale;
+  m = b1 * m + (1.f - b1) * gg;
+  v = b2 * v + (1.f - b2) * gg * gg;
+  p -= lr * (m * ibc1) / (sqrtf(v * ibc2) + eps);
+}
+// 128-bit accesses, two independent vectors in flight per thread (28 bytes of traffic per parameter: HBM-bound)
+__global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
+                                                   long long n, float lr, float b1, float b2, float eps, float ibc1, float ibc2, float grad_scale) {
+  const long long n4 = n / 4, stride = (long long)gridDim.x * blockDim.x;
+  float4* p4 = reinterpret_cast<float4*>(p); const float4* g4 = reinterpret_cast<const float4*>(g);
+  float4* m4 = reinterpret_cast<float4*>(m); float4* v4 = reinterpret_cast<float4*>(v);
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += 2 * stride) {
+    const long long i1 = i + stride;
+    const bool two = i1 < n4;
+    float4 P0 = p4[i], G0 = g4[i], M0 = m4[i], V0 = v4[i], P1, G1, M1, V1;
+    if (two) { P1 = p4[i1]; G1 = g4[i1]; M1 = m4[i1]; V1 = v4[i1]; }
+    adam_one(P0.x, G0.x, M0.x, V0.x, lr, b1, b2, eps, ibc1, ibc2, grad_scale); adam_one(P0.y, G0.y, M0.y, V0.y, lr, b1, b2, eps, ibc1, ibc2, grad_scale);
+    adam_one(P0.z, G0.z, M0.z, V0.z, lr, b1, b2, eps, ibc1, ibc2, grad_scale); adam_one(P0.w, G0.w, M0.w, V0.w, lr, b1, b2, eps, ibc1, ibc2, grad_scale);
+    p4[i] = P0; m4[i] = M0; v4[i] = V0;
+    if (two) {
+      adam_one(P1.x, G1.x, M1.x, V1.x, lr, b1, b2, eps, ibc1, ibc2, grad_scale); adam_one(P1.y, G1.y, M1.y, V1.y, lr, b1, b2, eps, ibc1, ibc2, grad_scale);
+      adam_one(P1.z, G1.z, M1.z, V1.z, lr, b1, b2, eps, ibc1, ibc2, grad_scale); adam_one(P1.w, G1.w, M1.w, V1.w, lr, b1, b2, eps, ibc1, ibc2, grad_scale);
+      p4[i1] = P1; m4[i1] = M1; v4[i1] = V1;
+    }
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (int)(n - n4 * 4)) {
+    const long long i = n4 * 4 + threadIdx.x;
+    adam_one(p[i], g[i], m[i], v[i], lr, b1, b2, eps, ibc1, ibc2, grad_scale);
   }
 }
 
@@ -550,33 +572,70 @@ __device__ __forceinline__ int find_job(const PackJob* jobs, int n_jobs, long lo
   return lo;
 }
 
+// Weight repack, one 32 x 32 (x taps) tile of the [Co, Ci, taps] fp32 source per block: the tile is read with the
+// source's own contiguity (32*taps consecutive floats per output channel, 8 independent loads in flight per thread),
+// transposed through shared memory and written as 64-byte runs of bf16 in the destination layout (element-wise indexing
+// by destination made either the 36-byte-strided reads or the 2-byte scattered writes uncoalesced: 0.9 TB/s).
+// TAPS = 9 / 1 compile the index divisions to multiplies; 0 = any tap count <= 9 at run time.
+template <int TAPS>
+__device__ __forceinline__ void pack_tile(const PackJob& J, long long blk, float* tile) {
+  const float* __restrict__ w = J.src;
+  bf16* __restrict__ out = reinterpret_cast<bf16*>(J.dst);
+  const int taps = TAPS ? TAPS : J.taps, rl = 32 * taps, rs = rl + 1, n = 32 * rl;
+  // tile grid: x = input-channel tiles (mode 0: over the padded width Cpad), y = output-channel tiles (mode 1: over Cpad)
+  const int in_ext = J.mode == 0 ? J.Cpad : J.Ci, in_valid = J.mode == 0 ? J.cn : J.Ci;
+  const int tiles_in = (in_ext + 31) / 32;
+  const int c_in0 = (int)(blk % tiles_in) * 32, co0 = (int)(blk / tiles_in) * 32;
+  constexpr int U = 8;
+  for (int e0 = threadIdx.x; e0 < n; e0 += 256 * U) {
+    float v[U]; int idx[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int e = e0 + u * 256;
+      const int co_l = e / rl, r = e - co_l * rl, ci_l = r / taps;
+      const int co = co0 + co_l, ci = c_in0 + ci_l;
+      idx[u] = e < n ? e + co_l : -1;
+      v[u] = (e < n && co < J.Co && ci < in_valid) ? w[((long long)co * J.Ci + J.ci0 + c_in0) * taps + r] : 0.f;
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) if (idx[u] >= 0) tile[idx[u]] = v[u];
+  }
+  __syncthreads();
+  if (J.mode == 0) {          // out[co, k_off + tap*Cpad + cc]
+#pragma unroll 4
+    for (int e = threadIdx.x; e < n; e += 256) {
+      const int co_l = e / rl, r = e - co_l * rl, tap = r >> 5, cc_l = r & 31;
+      const int co = co0 + co_l, cc = c_in0 + cc_l;
+      if (co < J.Co && cc < J.Cpad) out[(long long)co * J.ld + J.k_off + (long long)tap * J.Cpad + cc] = __float2bfloat16(tile[co_l * rs + cc_l * taps + tap]);
+    }
+  } else {                    // mode 1: out[ci, k_off + tp*Cpad + co], taps flipped;  mode 2: out[(tap*Ci + ci), co]
+    const int co_ext = J.mode == 1 ? J.Cpad : J.Co;
+#pragma unroll 4
+    for (int e = threadIdx.x; e < n; e += 256) {
+      const int ci_l = e / rl, r = e - ci_l * rl, tp = r >> 5, co_l = r & 31;
+      const int ci = c_in0 + ci_l, co = co0 + co_l;
+      if (ci >= J.Ci || co >= co_ext) continue;
+      if (J.mode == 1) out[(long long)ci * J.ld + J.k_off + (long long)tp * J.Cpad + co] = __float2bfloat16(tile[co_l * rs + ci_l * taps + (taps - 1 - tp)]);
+      else out[((long long)tp * J.Ci + ci) * J.ld + co] = __float2bfloat16(tile[co_l * rs + ci_l * taps + tp]);
+    }
+  }
+}
+
 __global__ void __launch_bounds__(256) pack_multi_kernel(const PackJob* __restrict__ jobs, int n_jobs) {
+  __shared__ float tile[32 * (32 * 9 + 1)];
   const int j = find_job(jobs, n_jobs, blockIdx.x);
   const PackJob J = jobs[j];
-  const long long i0 = ((long long)blockIdx.x - J.block0) * 1024;
-  const float* w = J.src;
-  for (int k = 0; k < 4; ++k) {
-    const long long i = i0 + k * 256 + threadIdx.x;
-    if (i >= J.total) return;
-    if (J.mode == 3) { reinterpret_cast<float*>(J.dst)[i] = w[i]; continue; }
-    bf16* out = reinterpret_cast<bf16*>(J.dst);
-    float v = 0.f;
-    long long o;
-    if (J.mode == 0) {
-      const int cc = (int)(i % J.Cpad), tap = (int)((i / J.Cpad) % J.taps), co = (int)(i / ((long long)J.Cpad * J.taps));
-      if (cc < J.cn) v = w[((long long)co * J.Ci + J.ci0 + cc) * J.taps + tap];
-      o = (long long)co * J.ld + J.k_off + (long long)tap * J.Cpad + cc;
-    } else if (J.mode == 1) {
-      const int co = (int)(i % J.Cpad), tp = (int)((i / J.Cpad) % J.taps), ci = (int)(i / ((long long)J.Cpad * J.taps));
-      if (co < J.Co) v = w[((long long)co * J.Ci + ci) * J.taps + (J.taps - 1 - tp)];
-      o = (long long)ci * J.ld + J.k_off + (long long)tp * J.Cpad + co;
-    } else {
-      const int co = (int)(i % J.Co), ci = (int)((i / J.Co) % J.Ci), tap = (int)(i / ((long long)J.Co * J.Ci));
-      v = w[((long long)co * J.Ci + ci) * J.taps + tap];
-      o = ((long long)tap * J.Ci + ci) * J.ld + co;
+  const long long blk = (long long)blockIdx.x - J.block0;
+  if (J.mode == 3) {          // flat fp32 copy, 1024 values per block
+    for (int k = 0; k < 4; ++k) {
+      const long long i = blk * 1024 + k * 256 + threadIdx.x;
+      if (i < J.total) reinterpret_cast<float*>(J.dst)[i] = J.src[i];
     }
-    out[o] = __float2bfloat16(v);
+    return;
   }
+  if (J.taps == 9) pack_tile<9>(J, blk, tile);
+  else if (J.taps == 1) pack_tile<1>(J, blk, tile);
+  else pack_tile<0>(J, blk, tile);
 }
 
 __global__ void __launch_bounds__(256) unpack_multi_kernel(const PackJob* __restrict__ jobs, int n_jobs) {
@@ -793,7 +852,8 @@ extern "C" int b3d_adam(float* p, const float* g, float* m, float* v, int64_t n,
                         float grad_scale, void* stream) {
   B3D_CHECK_ARG(p && g && m && v && step >= 1, "adam: args");
   const float bc1 = 1.f - powf(beta1, (float)step), bc2 = 1.f - powf(beta2, (float)step);
-  adam_kernel<<<grid_for(n), kT, 0, STREAM>>>(p, g, m, v, n, lr, beta1, beta2, eps, bc1, bc2, grad_scale);
+  B3D_CHECK_ARG((((uintptr_t)p | (uintptr_t)g | (uintptr_t)m | (uintptr_t)v) & 15) == 0, "adam: arenas must be 16-byte aligned");
+  adam_kernel<<<148 * 8, 256, 0, STREAM>>>(p, g, m, v, n, lr, beta1, beta2, eps, 1.f / bc1, 1.f / bc2, grad_scale);
   DONE(1);
 }
 

@@ -107,7 +107,11 @@ class JobList:
         j.src, j.dst = src.data_ptr(), dst.data_ptr()
         j.Co, j.Ci, j.taps, j.mode, j.ci0, j.cn, j.Cpad, j.accumulate = Co, Ci, taps, mode, ci0, cn, Cpad or 0, int(accumulate)
         j.k_off, j.ld, j.total, j.block0 = k_off, ld, total, self.blocks
-        self.blocks += (total + 1023) // 1024
+        if self.kind == "pack" and mode != 3:      # one 32 x 32 (x taps) source tile per block (pack_multi_kernel)
+            t32 = lambda v: (v + 31) // 32
+            self.blocks += {0: t32(Co) * t32(j.Cpad), 1: t32(j.Cpad) * t32(Ci), 2: t32(Co) * t32(Ci)}[mode]
+        else:
+            self.blocks += (total + 1023) // 1024
         self.jobs.append(j)
         self.keep.append((src, dst))
         self.table = None
@@ -300,7 +304,7 @@ class CudaOps:
         Co, Ci = w.shape[0], w.shape[1]
         taps = w.numel() // (Co * Ci)
         cn = Ci if cn is None else cn
-        assert w.dtype == torch.float32 and w.is_contiguous() and out.dim() == 2 and out.stride(1) == 1
+        assert w.dtype == torch.float32 and w.is_contiguous() and out.dim() == 2 and out.stride(1) == 1 and taps <= 9
         total = Co * taps * Cpad if mode == 0 else (Ci * taps * Cpad if mode == 1 else Co * Ci * taps)
         jl.add(w, out, Co, Ci, taps, mode, ci0, cn, Cpad, k_off, out.stride(0), total)
 

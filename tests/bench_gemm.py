@@ -25,7 +25,49 @@ CASES = [
 ]
 
 
+SMALL = [
+    # the short-K / few-tile launches of the attention blocks: timed inside a CUDA graph (20 launches per replay) so the
+    # Python launch cost does not hide the kernel's own fixed costs
+    ("dense [65536,256]x[256,256]", gc.dense_case("d", 65536, 256, 256)),
+    ("dense [65536,256]x[768,256]", gc.dense_case("d", 65536, 256, 768)),
+    ("dense [16384,512]x[512,512]", gc.dense_case("d", 16384, 512, 512)),
+    ("dense [8192,256]x[256,256]", gc.dense_case("d", 8192, 256, 256)),
+    ("dense [1024,256]x[256,256]", gc.dense_case("d", 1024, 256, 256)),
+    ("dense [128,256]x[256,256]", gc.dense_case("d", 128, 256, 256)),
+    ("wgrad dense 256x256 over 65536 rows", gc.wgrad_case("w", 1, 1, 65536, 256, 256, 1)),
+    ("wgrad dense 512x512 over 16384 rows", gc.wgrad_case("w", 1, 1, 16384, 512, 512, 1)),
+]
+
+
+def small():
+    ops = CudaOps("cuda:0")
+    for name, case in SMALL:
+        d, outs = case.build(ops)
+        flop = ops.gemm_flop(d)
+        st = torch.cuda.Stream()
+        with torch.cuda.stream(st):
+            for _ in range(3):
+                ops.gemm(d)
+            st.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=st):
+                for _ in range(20):
+                    ops.gemm(d)
+            g.replay()
+            st.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(st)
+            for _ in range(5):
+                g.replay()
+            e1.record(st)
+            st.synchronize()
+        us = e0.elapsed_time(e1) / 100 * 1e3
+        print(f"{name:45s} {us:8.2f} us/launch  {flop / us / 1e6:8.1f} TFLOP/s", flush=True)
+
+
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "small":
+        return small()
     ops = CudaOps("cuda:0")
     sel = int(sys.argv[1]) if len(sys.argv) > 1 else None
     for i, (name, case) in enumerate(CASES):

@@ -303,6 +303,44 @@ __global__ void colsum_kernel(const bf16* __restrict__ in, long long ld, int C, 
   if (c + 1 < C) atomicAdd(out + g * out_ld + c + 1, s1);
 }
 
+// the same for C % 8 == 0, C <= 2048: 16-byte loads, 4 rows in flight per thread, one block-level reduction and C
+// atomics per block (the 2-channel-per-thread loop above keeps one 4-byte load in flight: latency-bound)
+__global__ void __launch_bounds__(256) colsum_vec_kernel(const bf16* __restrict__ in, long long ld, int C, long long rows_per_group,
+                                                         int rows_per_block, float* __restrict__ out, long long out_ld) {
+  extern __shared__ float sm[];   // [rows_par, C]
+  constexpr int U = 4;
+  const int vecs = C / 8, g = blockIdx.y;
+  const int rows_par = max(1, (int)blockDim.x / vecs);
+  const int v = threadIdx.x % vecs, rsub = threadIdx.x / vecs;
+  const long long r0 = (long long)blockIdx.x * rows_per_block, r1 = min(rows_per_group, r0 + rows_per_block);
+  const bf16* base = in + (long long)g * rows_per_group * ld + v * 8;
+  float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  if (rsub < rows_par) {
+    for (long long r = r0 + rsub; r < r1; r += (long long)rows_par * U) {
+      bf16x8 x[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long rr = r + (long long)u * rows_par;
+        x[u].u = rr < r1 ? reinterpret_cast<const bf16x8*>(base + rr * ld)->u : make_uint4(0u, 0u, 0u, 0u);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        float f[8]; b3d_unpack8(x[u], f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += f[j];
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) sm[rsub * C + v * 8 + j] = acc[j];
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float s = 0.f;
+    for (int r = 0; r < rows_par; ++r) s += sm[r * C + c];
+    atomicAdd(out + (long long)g * out_ld + c, s);
+  }
+}
+
 // out[f, p, c] = sum_b in[b, f, p, c]   (in: [B,2,P,C] bf16)   -- batch reduction per frame
 __global__ void batch_frame_sum_kernel(const bf16* __restrict__ in, bf16* __restrict__ out, int B, long long PCvec) {
   const long long total = 2 * PCvec;
@@ -733,6 +771,18 @@ extern "C" int b3d_add_scale(const void* a, const void* b, void* out, float scal
 }
 extern "C" int b3d_colsum(const void* in, int64_t ld, int C, int64_t rows_per_group, int groups, float* out, int64_t out_ld, void* stream) {
   B3D_CHECK_ARG(C % 2 == 0 && ld % 2 == 0, "colsum: even C/ld");
+  if (C % 8 == 0 && ld % 8 == 0 && C <= 2048 && (((uintptr_t)in) & 15) == 0) {
+    const int rows_par = 256 / (C / 8) > 0 ? 256 / (C / 8) : 1;
+    const int min_rows = rows_par * 4;
+    long long rpb = cdiv(rows_per_group * groups, 148LL * 8);      // about 8 blocks per SM over the launch
+    const long long amort = cdiv(32768, C);                        // >= 64 KB streamed per block of C atomics
+    if (rpb < amort) rpb = amort;
+    if (rpb < min_rows) rpb = min_rows;
+    rpb = (rpb + min_rows - 1) / min_rows * min_rows;
+    dim3 grid((unsigned)cdiv(rows_per_group, rpb), groups);
+    colsum_vec_kernel<<<grid, 256, (size_t)rows_par * C * sizeof(float), STREAM>>>((const bf16*)in, ld, C, rows_per_group, (int)rpb, out, out_ld);
+    DONE(1);
+  }
   int rpb = 256;
   while ((long long)cdiv(rows_per_group, rpb) * groups * cdiv(C, 256) > 148LL * 16 && rpb < rows_per_group) rpb *= 2;
   dim3 grid(cdiv(C / 2, 128), cdiv(rows_per_group, rpb), groups);

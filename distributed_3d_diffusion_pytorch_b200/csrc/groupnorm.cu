@@ -418,6 +418,13 @@ int pick_rows_per_block(int N, int HW, int C, int U, int blocks_per_sm, int wave
   if (per_img < 1) per_img = 1;
   int rpb = (HW + per_img - 1) / per_img;
   const int min_rows = rows_par * U;
+  // every block ends with O(C) fp32 atomics on per-channel sums shared by the whole launch: give it at least 64 KB of
+  // each tensor to stream (rows * C * 2 B), or small images drown in atomic traffic (8-row blocks at C = 1024 did)
+  // -- as long as the launch keeps two blocks per SM (tiny tensors are latency-bound: they want parallelism instead)
+  const int amort_rows = (32768 + C - 1) / C;
+  const long long par_rows = (long long)N * HW / (2 * b3d_num_sms());
+  const int want = (int)(amort_rows < par_rows ? amort_rows : par_rows);
+  if (rpb < want) rpb = want;
   if (rpb < min_rows) rpb = min_rows;
   rpb = (rpb + min_rows - 1) / min_rows * min_rows;
   if (rpb > HW) rpb = HW;

@@ -9,22 +9,32 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from distributed_3d_diffusion_pytorch_b200.ops import CudaOps  # noqa: E402
 
 
-def timeit(fn, iters=5):
-    fn()
-    torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(iters):
+def timeit(fn, iters=5, reps=10):
+    """ms per call, timed over CUDA-graph replays of `reps` calls (the Python launch cost would hide the small kernels)"""
+    st = torch.cuda.Stream()
+    with torch.cuda.stream(st):
         fn()
-    e1.record()
-    torch.cuda.synchronize()
-    return e0.elapsed_time(e1) / iters
+        st.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=st):
+            for _ in range(reps):
+                fn()
+        g.replay()
+        st.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(st)
+        for _ in range(iters):
+            g.replay()
+        e1.record(st)
+        st.synchronize()
+    return e0.elapsed_time(e1) / (iters * reps)
 
 
 def main():
     ops = CudaOps("cuda:0")
     dev = "cuda:0"
-    shapes = [(256, 4096, 128, 0), (256, 4096, 256, 128), (256, 1024, 256, 0), (256, 256, 256, 0), (256, 64, 512, 0), (256, 64, 512, 512)]
+    shapes = [(256, 4096, 128, 0), (256, 4096, 256, 128), (256, 1024, 256, 0), (256, 256, 256, 0), (256, 64, 512, 0), (256, 64, 512, 512),
+              (32, 4096, 128, 0), (32, 1024, 256, 0), (32, 256, 256, 0), (32, 64, 512, 0), (32, 64, 512, 512)]   # N = 32: the 8-GPU shard
     if len(sys.argv) > 1:
         shapes = shapes[:int(sys.argv[1])]
     for N, HW, C0, C1 in shapes:

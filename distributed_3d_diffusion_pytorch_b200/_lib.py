@@ -30,3 +30,8 @@ def check(rc, what):
 
 def launch_count():
     return int(load().b3d_launch_count())
+
+
+def set_pdl(on):
+    """programmatic dependent launch of the frequent kernels (include/b3d.h: b3d_set_pdl)"""
+    load().b3d_set_pdl(ctypes.c_int(1 if on else 0))

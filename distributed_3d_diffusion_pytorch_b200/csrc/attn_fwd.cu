@@ -52,6 +52,7 @@ __global__ void __launch_bounds__(kThreads, 1) attn_fwd_kernel(const __grid_cons
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_smem;
+  b3d_pdl_sync();   // launched with programmatic stream serialization: nothing above touches global memory
   const int dch = (p.d + 63) / 64, kch = (p.L + 63) / 64;
 
   if (warp == 0) {
@@ -254,7 +255,7 @@ extern "C" int b3d_attn_fwd(const void* qkv, int N, int L, int heads, int d, int
     attr_set = true;
   }
   const int grid = p.items < b3d_num_sms() ? p.items : b3d_num_sms();
-  attn_fwd_kernel<<<grid, kThreads, smem, stream>>>(p);
+  B3D_CUDA(b3d_launch_pdl(attn_fwd_kernel, dim3(grid), dim3(kThreads), smem, stream, p));
   B3D_LAUNCH_CHECK();
   b3d_count_launch(1);
   return B3D_OK;

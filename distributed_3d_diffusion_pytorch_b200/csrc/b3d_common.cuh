@@ -1,5 +1,6 @@
 // Shared helpers for the b3d sm_100a kernels (host error plumbing + small device utilities).
 #pragma once
+#include <cstring>
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -42,6 +43,30 @@ void b3d_set_error(const char* fmt, ...);
 int b3d_num_sms();
 
 typedef __nv_bfloat16 bf16;
+
+// ---- programmatic dependent launch (PDL): a kernel launched through b3d_launch_pdl may start while the previous kernel
+// in the stream is still draining; its blocks run their prologue and then block in b3d_pdl_sync() until that kernel has
+// completed and flushed.  Hides the launch latency between the ~1300 short, dependent launches of a step (the fork /
+// join structure survives stream capture as programmatic graph edges).  B3D_NO_PDL=1 in the environment turns it off.
+// Rule for kernels launched this way: no global-memory access before b3d_pdl_sync().
+__device__ __forceinline__ void b3d_pdl_sync() {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+#ifdef B3D_PDL_EARLY_TRIGGER
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+#endif
+}
+bool b3d_pdl_enabled();
+template <typename... KArgs, typename... Args>
+inline cudaError_t b3d_launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = b3d_pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
 
 __device__ __forceinline__ float b3d_silu(float x) { return __fdividef(x, 1.0f + __expf(-x)); }
 // d/dx silu(x) = s + x*s*(1-s), s = sigmoid(x)

@@ -223,6 +223,7 @@ __global__ void cast_kernel(const float* __restrict__ in, bf16* __restrict__ out
 // resampling on NHWC bf16 (xunet.py:17-28) and their adjoints
 // ---------------------------------------------------------------------------------------------
 __global__ void avgpool2_kernel(const bf16* __restrict__ in, bf16* __restrict__ out, int N, int H, int W, int C, float scale) {
+  b3d_pdl_sync();
   const int Ho = H / 2, Wo = W / 2, vecs = C / 8;
   const long long total = (long long)N * Ho * Wo * vecs;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -245,6 +246,7 @@ __global__ void avgpool2_kernel(const bf16* __restrict__ in, bf16* __restrict__ 
 }
 // out[n, y, x] = scale * in[n, y/2, x/2]  (nearest upsample; also the adjoint of avgpool with scale=1/4)
 __global__ void upsample2_kernel(const bf16* __restrict__ in, bf16* __restrict__ out, int N, int Ho, int Wo, int C, float scale) {
+  b3d_pdl_sync();
   const int H = Ho / 2, W = Wo / 2, vecs = C / 8;
   const long long total = (long long)N * Ho * Wo * vecs;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -263,6 +265,7 @@ __global__ void upsample2_kernel(const bf16* __restrict__ in, bf16* __restrict__
 // ---------------------------------------------------------------------------------------------
 // dx = dy * silu'(x)
 __global__ void silu_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x, bf16* __restrict__ dx, long long nvec) {
+  b3d_pdl_sync();
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nvec; i += (long long)gridDim.x * blockDim.x) {
     float a[8], b[8];
     b3d_unpack8(reinterpret_cast<const bf16x8*>(dy)[i], a);
@@ -307,6 +310,7 @@ __global__ void colsum_kernel(const bf16* __restrict__ in, long long ld, int C, 
 // atomics per block (the 2-channel-per-thread loop above keeps one 4-byte load in flight: latency-bound)
 __global__ void __launch_bounds__(256) colsum_vec_kernel(const bf16* __restrict__ in, long long ld, int C, long long rows_per_group,
                                                          int rows_per_block, float* __restrict__ out, long long out_ld) {
+  b3d_pdl_sync();
   extern __shared__ float sm[];   // [rows_par, C]
   constexpr int U = 4;
   const int vecs = C / 8, g = blockIdx.y;
@@ -343,6 +347,7 @@ __global__ void __launch_bounds__(256) colsum_vec_kernel(const bf16* __restrict_
 
 // out[f, p, c] = sum_b in[b, f, p, c]   (in: [B,2,P,C] bf16)   -- batch reduction per frame
 __global__ void batch_frame_sum_kernel(const bf16* __restrict__ in, bf16* __restrict__ out, int B, long long PCvec) {
+  b3d_pdl_sync();
   const long long total = 2 * PCvec;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
     float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -411,6 +416,7 @@ __global__ void softmax_kernel(const TIn* __restrict__ S, bf16* __restrict__ P, 
 template <typename TIn>
 __global__ void softmax_bwd_kernel(const bf16* __restrict__ P, const TIn* __restrict__ dP, bf16* __restrict__ dS, long long rows, int L,
                                    long long ld_p, long long ld_dp, long long ld_ds) {
+  b3d_pdl_sync();
   const long long row = (long long)blockIdx.x * (blockDim.x / 32) + (threadIdx.x >> 5);
   if (row >= rows) return;
   const int lane = threadIdx.x & 31;
@@ -553,6 +559,7 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
 // gradients that equal its column sums: conv2.bias, dense.bias, linear.bias)
 __global__ void __launch_bounds__(256) scale_colsum_kernel(const bf16* __restrict__ a, bf16* __restrict__ out, float scale, long long rows, int C,
                                                            int rows_per_block, float* __restrict__ colsum) {
+  b3d_pdl_sync();
   extern __shared__ float sm[];   // red [256*8] (plain stores: shared fp32 atomics are CAS spin loops)
   constexpr int U = 4;
   const int vecs = C / 8;
@@ -751,17 +758,17 @@ extern "C" int b3d_cast_bf16(const float* in, void* out, int64_t n, void* stream
 }
 extern "C" int b3d_avgpool2(const void* in, void* out, int N, int H, int W, int C, float scale, void* stream) {
   B3D_CHECK_ARG(C % 8 == 0 && H % 2 == 0 && W % 2 == 0, "avgpool2: C%%8, even H/W");
-  avgpool2_kernel<<<grid_for((long long)N * (H / 2) * (W / 2) * (C / 8)), kT, 0, STREAM>>>((const bf16*)in, (bf16*)out, N, H, W, C, scale);
+  B3D_CUDA(b3d_launch_pdl(avgpool2_kernel, dim3(grid_for((long long)N * (H / 2) * (W / 2) * (C / 8))), dim3(kT), 0, STREAM, (const bf16*)in, (bf16*)out, N, H, W, C, scale));
   DONE(1);
 }
 extern "C" int b3d_upsample2(const void* in, void* out, int N, int Ho, int Wo, int C, float scale, void* stream) {
   B3D_CHECK_ARG(C % 8 == 0 && Ho % 2 == 0 && Wo % 2 == 0, "upsample2: C%%8, even H/W");
-  upsample2_kernel<<<grid_for((long long)N * Ho * Wo * (C / 8)), kT, 0, STREAM>>>((const bf16*)in, (bf16*)out, N, Ho, Wo, C, scale);
+  B3D_CUDA(b3d_launch_pdl(upsample2_kernel, dim3(grid_for((long long)N * Ho * Wo * (C / 8))), dim3(kT), 0, STREAM, (const bf16*)in, (bf16*)out, N, Ho, Wo, C, scale));
   DONE(1);
 }
 extern "C" int b3d_silu_bwd(const void* dy, const void* x, void* dx, int64_t n, void* stream) {
   B3D_CHECK_ARG(n % 8 == 0, "silu_bwd: n%%8");
-  silu_bwd_kernel<<<grid_for(n / 8), kT, 0, STREAM>>>((const bf16*)dy, (const bf16*)x, (bf16*)dx, n / 8);
+  B3D_CUDA(b3d_launch_pdl(silu_bwd_kernel, dim3(grid_for(n / 8)), dim3(kT), 0, STREAM, (const bf16*)dy, (const bf16*)x, (bf16*)dx, n / 8));
   DONE(1);
 }
 extern "C" int b3d_add_scale(const void* a, const void* b, void* out, float scale, int64_t n, void* stream) {
@@ -780,7 +787,7 @@ extern "C" int b3d_colsum(const void* in, int64_t ld, int C, int64_t rows_per_gr
     if (rpb < min_rows) rpb = min_rows;
     rpb = (rpb + min_rows - 1) / min_rows * min_rows;
     dim3 grid((unsigned)cdiv(rows_per_group, rpb), groups);
-    colsum_vec_kernel<<<grid, 256, (size_t)rows_par * C * sizeof(float), STREAM>>>((const bf16*)in, ld, C, rows_per_group, (int)rpb, out, out_ld);
+    B3D_CUDA(b3d_launch_pdl(colsum_vec_kernel, dim3(grid), dim3(256), (size_t)rows_par * C * sizeof(float), STREAM, (const bf16*)in, ld, C, rows_per_group, (int)rpb, out, out_ld));
     DONE(1);
   }
   int rpb = 256;
@@ -791,7 +798,7 @@ extern "C" int b3d_colsum(const void* in, int64_t ld, int C, int64_t rows_per_gr
 }
 extern "C" int b3d_batch_frame_sum(const void* in, void* out, int B, int64_t per_frame_elems, void* stream) {
   B3D_CHECK_ARG(per_frame_elems % 8 == 0, "batch_frame_sum: %%8");
-  batch_frame_sum_kernel<<<grid_for(2 * per_frame_elems / 8), kT, 0, STREAM>>>((const bf16*)in, (bf16*)out, B, per_frame_elems / 8);
+  B3D_CUDA(b3d_launch_pdl(batch_frame_sum_kernel, dim3(grid_for(2 * per_frame_elems / 8)), dim3(kT), 0, STREAM, (const bf16*)in, (bf16*)out, B, per_frame_elems / 8));
   DONE(1);
 }
 extern "C" int b3d_conv_tap_scatter(const float* G, int64_t ldg, int C, int h, int w, int s, int H, int W, float* dP, int64_t ldp, int accumulate,
@@ -806,8 +813,8 @@ extern "C" int b3d_softmax(const void* S, int s_fp32, int64_t ld_s, void* P, int
 }
 extern "C" int b3d_softmax_bwd(const void* P, int64_t ld_p, const void* dP, int dp_fp32, int64_t ld_dp, void* dS, int64_t ld_ds, int64_t rows,
                                int L, void* stream) {
-  if (dp_fp32) softmax_bwd_kernel<float><<<cdiv(rows, 8), 256, 0, STREAM>>>((const bf16*)P, (const float*)dP, (bf16*)dS, rows, L, ld_p, ld_dp, ld_ds);
-  else softmax_bwd_kernel<bf16><<<cdiv(rows, 8), 256, 0, STREAM>>>((const bf16*)P, (const bf16*)dP, (bf16*)dS, rows, L, ld_p, ld_dp, ld_ds);
+  if (dp_fp32) B3D_CUDA(b3d_launch_pdl(softmax_bwd_kernel<float>, dim3(cdiv(rows, 8)), dim3(256), 0, STREAM, (const bf16*)P, (const float*)dP, (bf16*)dS, rows, L, ld_p, ld_dp, ld_ds));
+  else B3D_CUDA(b3d_launch_pdl(softmax_bwd_kernel<bf16>, dim3(cdiv(rows, 8)), dim3(256), 0, STREAM, (const bf16*)P, (const bf16*)dP, (bf16*)dS, rows, L, ld_p, ld_dp, ld_ds));
   DONE(1);
 }
 extern "C" int b3d_q_sample(const float* z, const float* noise, const float* logsnr, const float* x, const float* xrand, const uint8_t* mask,
@@ -914,7 +921,7 @@ extern "C" int b3d_scale_colsum(const void* a, void* out, float scale, int64_t r
   const int min_rows = rows_par * 4;
   if (rpb < min_rows) rpb = min_rows;
   rpb = (rpb + min_rows - 1) / min_rows * min_rows;
-  scale_colsum_kernel<<<cdiv(rows, rpb), 256, 2048 * sizeof(float), STREAM>>>((const bf16*)a, (bf16*)out, scale, rows, C, (int)rpb, colsum);
+  B3D_CUDA(b3d_launch_pdl(scale_colsum_kernel, dim3(cdiv(rows, rpb)), dim3(256), 2048 * sizeof(float), STREAM, (const bf16*)a, (bf16*)out, scale, rows, C, (int)rpb, colsum));
   DONE(1);
 }
 // jobs: device array of b3d_pack_job (include/b3d.h) whose block0 fields are the running sum of ceil(total/1024)

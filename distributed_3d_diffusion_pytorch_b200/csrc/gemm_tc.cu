@@ -131,11 +131,17 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
     for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 4); mbar_init(resid_bar(s), 1); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
+  if (threadIdx.x == 64) {      // descriptor fetches overlap the barrier init / TMEM allocation (short launches are latency-bound)
+    prefetch_tensormap(&p.tmA[0]);
+    prefetch_tensormap(&p.tmB);
+    if (p.epi_tma) prefetch_tensormap(&p.tmO);
+  }
   if (warp == 1) tmem_alloc(smem_u32(&tmem_base_smem), (uint32_t)p.tmem_cols);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_smem;
+  b3d_pdl_sync();   // everything above overlapped the previous kernel's tail; global memory is touched only below
 
   if (warp == 0) {
     // ===================================================================== TMA producer
@@ -767,7 +773,7 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
     attr_set = true;
   }
   int grid = p.tiles_total < b3d_num_sms() ? p.tiles_total : b3d_num_sms();
-  b3d_gemm_kernel<<<grid, kThreads, smem, stream>>>(p);
+  B3D_CUDA(b3d_launch_pdl(b3d_gemm_kernel, dim3(grid), dim3(kThreads), smem, stream, p));
   B3D_LAUNCH_CHECK();
   b3d_count_launch(1);
   return B3D_OK;

@@ -75,6 +75,7 @@ __device__ __forceinline__ void block_sum8(const float* vals, bool active, int v
 
 // ---- stats: raw (sum, sumsq) per (image, group) accumulated with fp32 atomics into ws[N,32,2] (pre-zeroed)
 __global__ void __launch_bounds__(kT) gn_stats_kernel(Src2 s, int HW, int rows_per_block, float* __restrict__ ws) {
+  b3d_pdl_sync();
   extern __shared__ float sm[];  // red [256*8] | sum [C] | sumsq [C]
   constexpr int U = 4;
   const int C = s.C0 + s.C1, cpg = C / G, n = blockIdx.y, vecs = C / 8;
@@ -159,6 +160,7 @@ constexpr int kBwdBlocks2 = B3D_GN_BWD2_BLOCKS;   // resident blocks per SM of t
 
 template <int MODE>
 __global__ void __launch_bounds__(kT, MODE == 2 ? 3 : 4) gn_apply_kernel(ApplyP p, int rows_per_block) {
+  b3d_pdl_sync();
   __shared__ float s_mean[G], s_rstd[G];
   constexpr int U = MODE == 2 ? kApplyU2 : kApplyU0;
   const int C = p.s.C0 + p.s.C1, cpg = C / G, n = blockIdx.y, vecs = C / 8;
@@ -252,6 +254,7 @@ __device__ __forceinline__ void bwd_dz(const Aff& ch, const float* f, const floa
 // (one image per block, so mean/rstd are block constants per group).
 template <int MODE>
 __global__ void __launch_bounds__(kT, MODE == 2 ? kBwdBlocks2 : kBwdBlocks1) gn_bwd_reduce_kernel(BwdP p, int rows_per_block) {
+  b3d_pdl_sync();
   extern __shared__ float sm[];  // red [256*8] | dgamma [C] | dbeta [C] | dscale-sum [C] | dshift-sum [C]
   __shared__ float s_mean[G], s_rstd[G];
   constexpr int U = MODE == 2 ? kBwdU2 : kBwdU1;
@@ -332,6 +335,7 @@ __global__ void __launch_bounds__(kT, MODE == 2 ? kBwdBlocks2 : kBwdBlocks1) gn_
 // pass 2: dx = rstd * (dz*gamma - (S1 + xhat*S2)/cnt) [+ add0] [+ add1]  =  dz*a + x*c1 + c0 per channel
 template <int MODE>
 __global__ void __launch_bounds__(kT, MODE == 2 ? kBwdBlocks2 : kBwdBlocks1) gn_bwd_apply_kernel(BwdP p, int rows_per_block) {
+  b3d_pdl_sync();
   extern __shared__ float sm[];   // red [256*8] | column sums of dx [C]   (used when p.dx_sum is set)
   __shared__ float s_mean[G], s_rstd[G], s_c1[G], s_c0[G];
   constexpr int U = kBwdApplyU;
@@ -448,7 +452,7 @@ extern "C" int b3d_gn_stats(const void* x0, int C0, int64_t ld0, const void* x1,
   Src2 s{(const bf16*)x0, (const bf16*)x1, C0, C1, ld0, ld1};
   const int C = C0 + C1, rpb = pick_rows_per_block(N, HW, C, 4, 8, 2);   // measured: 2 long waves beat 1, 4 and 8 (block epilogue cost)
   dim3 grid((HW + rpb - 1) / rpb, N);
-  gn_stats_kernel<<<grid, kT, (2048 + 2 * C) * sizeof(float), (cudaStream_t)stream>>>(s, HW, rpb, ws_sums);
+  B3D_CUDA(b3d_launch_pdl(gn_stats_kernel, dim3(grid), dim3(kT), (2048 + 2 * C) * sizeof(float), (cudaStream_t)stream, s, HW, rpb, ws_sums));
   B3D_LAUNCH_CHECK();
   b3d_count_launch(1);
   return B3D_OK;
@@ -467,9 +471,9 @@ extern "C" int b3d_gn_apply(const void* x0, int C0, int64_t ld0, const void* x1,
   p.ss = (const bf16*)ss; p.ld_ss = ld_ss; p.F = F; p.drop_p = drop_p; p.seed = seed; p.seed_ptr = (const unsigned long long*)seed_ptr;
   const int rpb = pick_rows_per_block(N, HW, C0 + C1, mode == 2 ? kApplyU2 : kApplyU0, mode == 2 ? 3 : 4);
   dim3 grid((HW + rpb - 1) / rpb, N);
-  if (mode == 0) gn_apply_kernel<0><<<grid, kT, 0, (cudaStream_t)stream>>>(p, rpb);
-  else if (mode == 1) gn_apply_kernel<1><<<grid, kT, 0, (cudaStream_t)stream>>>(p, rpb);
-  else gn_apply_kernel<2><<<grid, kT, 0, (cudaStream_t)stream>>>(p, rpb);
+  if (mode == 0) B3D_CUDA(b3d_launch_pdl(gn_apply_kernel<0>, dim3(grid), dim3(kT), 0, (cudaStream_t)stream, p, rpb));
+  else if (mode == 1) B3D_CUDA(b3d_launch_pdl(gn_apply_kernel<1>, dim3(grid), dim3(kT), 0, (cudaStream_t)stream, p, rpb));
+  else B3D_CUDA(b3d_launch_pdl(gn_apply_kernel<2>, dim3(grid), dim3(kT), 0, (cudaStream_t)stream, p, rpb));
   B3D_LAUNCH_CHECK();
   b3d_count_launch(1);
   return B3D_OK;
@@ -499,18 +503,18 @@ extern "C" int b3d_gn_bwd(const void* x0, int C0, int64_t ld0, const void* x1, i
     const int rpb = pick_rows_per_block(N, HW, C, mode == 2 ? kBwdU2 : kBwdU1, mode == 2 ? kBwdBlocks2 : kBwdBlocks1);
     dim3 grid((HW + rpb - 1) / rpb, N);
     const size_t smem = (2048 + 4 * C) * sizeof(float);
-    if (mode == 0) gn_bwd_reduce_kernel<0><<<grid, kT, smem, st>>>(p, rpb);
-    else if (mode == 1) gn_bwd_reduce_kernel<1><<<grid, kT, smem, st>>>(p, rpb);
-    else gn_bwd_reduce_kernel<2><<<grid, kT, smem, st>>>(p, rpb);
+    if (mode == 0) B3D_CUDA(b3d_launch_pdl(gn_bwd_reduce_kernel<0>, dim3(grid), dim3(kT), smem, st, p, rpb));
+    else if (mode == 1) B3D_CUDA(b3d_launch_pdl(gn_bwd_reduce_kernel<1>, dim3(grid), dim3(kT), smem, st, p, rpb));
+    else B3D_CUDA(b3d_launch_pdl(gn_bwd_reduce_kernel<2>, dim3(grid), dim3(kT), smem, st, p, rpb));
     B3D_LAUNCH_CHECK();
   }
   {
     const int rpb = pick_rows_per_block(N, HW, C, kBwdApplyU, mode == 2 ? kBwdBlocks2 : kBwdBlocks1);
     dim3 grid((HW + rpb - 1) / rpb, N);
     const size_t smem = (2048 + C) * sizeof(float);
-    if (mode == 0) gn_bwd_apply_kernel<0><<<grid, kT, smem, st>>>(p, rpb);
-    else if (mode == 1) gn_bwd_apply_kernel<1><<<grid, kT, smem, st>>>(p, rpb);
-    else gn_bwd_apply_kernel<2><<<grid, kT, smem, st>>>(p, rpb);
+    if (mode == 0) B3D_CUDA(b3d_launch_pdl(gn_bwd_apply_kernel<0>, dim3(grid), dim3(kT), smem, st, p, rpb));
+    else if (mode == 1) B3D_CUDA(b3d_launch_pdl(gn_bwd_apply_kernel<1>, dim3(grid), dim3(kT), smem, st, p, rpb));
+    else B3D_CUDA(b3d_launch_pdl(gn_bwd_apply_kernel<2>, dim3(grid), dim3(kT), smem, st, p, rpb));
     B3D_LAUNCH_CHECK();
   }
   b3d_count_launch(2);

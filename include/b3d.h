@@ -24,6 +24,9 @@ const char* b3d_last_error(void);
 int b3d_version(void);
 /* number of kernels launched by this library since process start (bench.py's gpu_launches) */
 int64_t b3d_launch_count(void);
+/* Programmatic dependent launch of the frequent kernels (hides launch latency between short dependent launches; pays off
+ * for small per-GPU batches).  On by default; B3D_NO_PDL=1 in the environment wins.  No reference counterpart. */
+void b3d_set_pdl(int on);
 
 /* ------------------------------------------------------------------------------------------
  * Tensor-core path: one tcgen05/TMEM/TMA kernel for every GEMM-shaped op of the model.

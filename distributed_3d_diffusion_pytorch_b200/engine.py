@@ -678,19 +678,23 @@ class Engine:
         do = self.tmp("do", (N, L, C))
         ops.gemm(G.dense_desc(do1, Wp[a + ".out_proj.weight.T"], do.view(M, C), C))
         # attention core
-        q, k, v = self._qkv_views(sa["qkv"], L, C)
         p = sa["p"]
-        dov = do.view(N, L, Hh, d).permute(0, 2, 1, 3)
-        Lp = (L + 7) // 8 * 8
-        dpl = self.tmp("logits", (N, Hh, L, Lp), torch.float32)[..., :L]
-        dp = self.tmp("ds", (N, Hh, L, Lp))[..., :L]
-        ops.gemm(G.attn_dp_desc(dov, v, dpl, s.cross))
-        ops.softmax_bwd(p, dpl, dp)
         dqkv = self.tmp("dqkv", (N, L, 3 * C))
-        dq, dk, dv = self._qkv_views(dqkv, L, C)
-        ops.gemm(G.attn_dv_desc(p, dov, dv, s.cross))
-        ops.gemm(G.attn_dq_desc(dp, k, dq, s.cross, alpha))
-        ops.gemm(G.attn_dk_desc(dp, q, dk, s.cross, alpha))
+        if ops.attn_bwd_supported(L, d):
+            # fused: dP, dS and the dK / dV accumulation over the query tiles stay on the SM
+            ops.attn_bwd(sa["qkv"], p, sa["o"], do, dqkv, Hh, s.cross, alpha)
+        else:
+            q, k, v = self._qkv_views(sa["qkv"], L, C)
+            dov = do.view(N, L, Hh, d).permute(0, 2, 1, 3)
+            Lp = (L + 7) // 8 * 8
+            dpl = self.tmp("logits", (N, Hh, L, Lp), torch.float32)[..., :L]
+            dp = self.tmp("ds", (N, Hh, L, Lp))[..., :L]
+            ops.gemm(G.attn_dp_desc(dov, v, dpl, s.cross))
+            ops.softmax_bwd(p, dpl, dp)
+            dq, dk, dv = self._qkv_views(dqkv, L, C)
+            ops.gemm(G.attn_dv_desc(p, dov, dv, s.cross))
+            ops.gemm(G.attn_dq_desc(dp, k, dq, s.cross, alpha))
+            ops.gemm(G.attn_dk_desc(dp, q, dk, s.cross, alpha))
         # in_proj
         dq2 = dqkv.view(M, 3 * C)
         with ops.side():

@@ -246,6 +246,17 @@ class CudaOps:
         self._call("b3d_attn_fwd", _ptr(qkv), c_i32(N), c_i32(L), c_i32(heads), c_i32(d), c_i32(int(cross)), c_f32(scale), _ptr(out),
                    _ptr(probs), c_i64(ld), self.stream())
 
+    def attn_bwd_supported(self, L, d):
+        return bool(self.lib.b3d_attn_bwd_supported(c_i32(L), c_i32(d)))
+
+    def attn_bwd(self, qkv, probs, o, dout, dqkv, heads, cross, scale):
+        """fused attention backward: qkv [N,L,3C], probs [N,heads,L,Lp] view (saved by attn_fwd), o / dout [N,L,C] -> dqkv [N,L,3C]"""
+        N, L, C3 = qkv.shape
+        d = C3 // 3 // heads
+        assert qkv.is_contiguous() and o.is_contiguous() and dout.is_contiguous() and dqkv.is_contiguous()
+        self._call("b3d_attn_bwd", _ptr(qkv), _ptr(probs), c_i64(probs.stride(2)), _ptr(o), _ptr(dout), _ptr(dqkv), c_i32(N), c_i32(L),
+                   c_i32(heads), c_i32(d), c_i32(int(cross)), c_f32(scale), self.stream())
+
     # ---- conditioning
     def pose_embedding(self, K, R, t, mask, pos_emb, first_emb, other_emb, out):
         B = K.shape[0]

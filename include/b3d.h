@@ -84,6 +84,14 @@ int b3d_gemm(const b3d_gemm_desc* d, void* stream);
  * Replaces the bmm / softmax / bmm inside nn.MultiheadAttention (xunet.py:161,175). */
 int b3d_attn_fwd(const void* qkv, int N, int L, int heads, int d, int cross, float scale, void* out, void* probs, int64_t ld_probs,
                  void* stream);
+/* Fused backward of the same op (autograd of the MultiheadAttention core, xunet.py:161,175,202-211): from the packed qkv,
+ * the probabilities the forward saved, the attention output o [N,L,C] and its gradient dout [N,L,C] it writes
+ * dqkv [N,L,3C] (dQ | dK | dV; cross: dK, dV go to image n ^ 1).  dP, dS never leave the SM.  Covers
+ * b3d_attn_bwd_supported(L, d) == 1 (L <= 256, head_dim <= 128 with the accumulators fitting 512 TMEM columns);
+ * other shapes use the b3d_gemm + b3d_softmax_bwd path. */
+int b3d_attn_bwd_supported(int L, int d);
+int b3d_attn_bwd(const void* qkv, const void* probs, int64_t ld_probs, const void* o, const void* dout, void* dqkv, int N, int L, int heads,
+                 int d, int cross, float scale, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * HBM-bound kernels (elementwise / normalisation / reductions).  bf16 NHWC unless noted.

@@ -174,6 +174,30 @@ class EmuOps:
             P = probs[..., :L].float()
         out.copy_((P @ v[idx]).permute(0, 2, 1, 3).reshape(N, L, C).to(out.dtype))
 
+    def attn_bwd_supported(self, L, d):
+        Lb2 = (L + 127) // 128 * 128
+        return 1 <= L <= 256 and 16 <= d <= 128 and d % 16 == 0 and Lb2 + 2 * (Lb2 // 128) * d <= 512 and d <= Lb2
+
+    def attn_bwd(self, qkv, probs, o, dout, dqkv, heads, cross, scale):
+        N, L, C3 = qkv.shape
+        C = C3 // 3
+        d = C // heads
+        q, k, v = (qkv.float().view(N, L, 3, heads, d)[:, :, i].permute(0, 2, 1, 3) for i in range(3))
+        idx = torch.arange(N) ^ int(cross)
+        P = probs[..., :L].float()
+        dO = dout.float().view(N, L, heads, d).permute(0, 2, 1, 3)
+        O = o.float().view(N, L, heads, d).permute(0, 2, 1, 3)
+        dP = dO @ v[idx].transpose(-1, -2)
+        D = (dO * O).sum(-1, keepdim=True)
+        dS = (P * (dP - D)).to(self.act_dtype).float()
+        dq = scale * (dS @ k[idx])
+        dk = torch.zeros_like(dq)
+        dv = torch.zeros_like(dq)
+        dk[idx] = scale * (dS.transpose(-1, -2) @ q)
+        dv[idx] = P.transpose(-1, -2) @ dO
+        out = torch.stack([t.permute(0, 2, 1, 3).reshape(N, L, C) for t in (dq, dk, dv)], 2).reshape(N, L, 3 * C)
+        dqkv.copy_(out.to(dqkv.dtype))
+
     # ------------------------------------------------------------------ conditioning
     def pose_embedding(self, K, R, t, mask, pos_emb, first_emb, other_emb, out):
         B = K.shape[0]

@@ -200,7 +200,14 @@ def attn_case(N, L, heads, d, cross, with_p, seed=0):
         Lp = (L + 7) // 8 * 8
         probs = ops.zeros((N, heads, L, Lp)) if with_p else None
         ops.attn_fwd(qkv, heads, cross, 1.0 / math.sqrt(d), out, probs[..., :L] if with_p else None)
-        return [out] + ([probs] if with_p else [])
+        outs = [out] + ([probs] if with_p else [])
+        if with_p and ops.attn_bwd_supported(L, d):
+            # fused backward from the probabilities / output the forward just produced
+            dout = _mk(ops, _r((N, L, C), g))
+            dqkv = ops.zeros((N, L, 3 * C))
+            ops.attn_bwd(qkv, probs[..., :L], out, dout, dqkv, heads, cross, 1.0 / math.sqrt(d))
+            outs.append(dqkv)
+        return outs
     return run
 
 

@@ -683,17 +683,41 @@ __global__ void __launch_bounds__(256) pack_multi_kernel(const PackJob* __restri
   else pack_tile<0>(J, blk, tile);
 }
 
+// Packed fp32 weight gradients [Co, k_off + tap*Cpad + cc] -> PyTorch layout [Co, Ci, taps], one 32 x 32 (x taps) tile per
+// block through shared memory: 128-byte runs on the read side, 32*taps consecutive floats per output channel on the write
+// side (indexing by destination element read with a 4*Cpad-byte stride between neighbouring threads).
 __global__ void __launch_bounds__(256) unpack_multi_kernel(const PackJob* __restrict__ jobs, int n_jobs) {
+  __shared__ float tile[32 * (32 * 9 + 1)];
   const int j = find_job(jobs, n_jobs, blockIdx.x);
   const PackJob J = jobs[j];
-  const long long i0 = ((long long)blockIdx.x - J.block0) * 1024;
-  float* dw = reinterpret_cast<float*>(J.dst);
-  for (int k = 0; k < 4; ++k) {
-    const long long i = i0 + k * 256 + threadIdx.x;
-    if (i >= J.total) return;
-    const int tap = (int)(i % J.taps), cc = (int)((i / J.taps) % J.cn), co = (int)(i / ((long long)J.taps * J.cn));
-    const float v = J.src[(long long)co * J.ld + J.k_off + (long long)tap * J.Cpad + cc];
-    float* d = dw + ((long long)co * J.Ci + J.ci0 + cc) * J.taps + tap;
+  const long long blk = (long long)blockIdx.x - J.block0;
+  const float* __restrict__ g = J.src;
+  float* __restrict__ dw = reinterpret_cast<float*>(J.dst);
+  const int taps = J.taps, rl = 32 * taps, rs = rl + 1, n = 32 * rl;
+  const int tiles_in = (J.cn + 31) / 32;
+  const int cc0 = (int)(blk % tiles_in) * 32, co0 = (int)(blk / tiles_in) * 32;
+  constexpr int U = 8;
+  for (int e0 = threadIdx.x; e0 < n; e0 += 256 * U) {
+    float v[U]; int idx[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int e = e0 + u * 256;
+      const int co_l = e / rl, r = e - co_l * rl, tap = r >> 5, cc_l = r & 31;
+      const int co = co0 + co_l, cc = cc0 + cc_l;
+      idx[u] = e < n ? co_l * rs + cc_l * taps + tap : -1;
+      v[u] = (e < n && co < J.Co && cc < J.cn) ? g[(long long)co * J.ld + J.k_off + (long long)tap * J.Cpad + cc] : 0.f;
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) if (idx[u] >= 0) tile[idx[u]] = v[u];
+  }
+  __syncthreads();
+#pragma unroll 4
+  for (int e = threadIdx.x; e < n; e += 256) {
+    const int co_l = e / rl, r = e - co_l * rl, cc_l = r / taps;
+    const int co = co0 + co_l, cc = cc0 + cc_l;
+    if (co >= J.Co || cc >= J.cn) continue;
+    float* d = dw + ((long long)co * J.Ci + J.ci0 + cc0) * taps + r;
+    const float v = tile[co_l * rs + r];
     *d = J.accumulate ? *d + v : v;
   }
 }

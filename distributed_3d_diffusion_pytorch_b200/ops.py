@@ -110,6 +110,8 @@ class JobList:
         if self.kind == "pack" and mode != 3:      # one 32 x 32 (x taps) source tile per block (pack_multi_kernel)
             t32 = lambda v: (v + 31) // 32
             self.blocks += {0: t32(Co) * t32(j.Cpad), 1: t32(j.Cpad) * t32(Ci), 2: t32(Co) * t32(Ci)}[mode]
+        elif self.kind == "unpack":                 # one 32 x 32 (x taps) destination tile per block (unpack_multi_kernel)
+            self.blocks += ((Co + 31) // 32) * ((cn + 31) // 32)
         else:
             self.blocks += (total + 1023) // 1024
         self.jobs.append(j)

@@ -122,8 +122,8 @@ int b3d_unpack_wgrad(const float* g, int64_t g_ld, int64_t k_off, int Cpad, int 
 int b3d_cast_bf16(const float* in, void* out, int64_t n, void* stream);
 /* The same conversions for MANY tensors in one launch (every parameter is repacked each step; one launch instead of
  * ~450).  `jobs` is a DEVICE array of b3d_pack_job; block0 = running sum of the jobs' block counts: ceil(total/1024) for
- * unpack jobs and mode-3 copies, one block per 32 x 32 (co x ci) source tile for pack modes 0/1/2 -- ceil(Co/32)*ceil(Cpad/32),
- * ceil(Cpad/32)*ceil(Ci/32), ceil(Co/32)*ceil(Ci/32).
+ * mode-3 copies, one block per 32 x 32 (co x ci) tile otherwise -- pack modes 0/1/2: ceil(Co/32)*ceil(Cpad/32),
+ * ceil(Cpad/32)*ceil(Ci/32), ceil(Co/32)*ceil(Ci/32); unpack: ceil(Co/32)*ceil(cn/32).  taps <= 9.
  * pack: mode 0/1/2 as b3d_pack_weight, mode 3 = fp32 copy of `total` values.  unpack: as b3d_unpack_wgrad. */
 typedef struct b3d_pack_job {
   const float* src; void* dst;

@@ -12,6 +12,7 @@
 
 `ops` is the kernel backend (ops.CudaOps); tests substitute a torch statement of the same ops to
 check this orchestration on CPU."""
+import contextlib
 import math
 
 import torch
@@ -271,15 +272,18 @@ class Engine:
         ops.pose_embedding(K, R, t, cond_mask, P.get(cp + "pos_emb") if cfg.use_pos_emb else None,
                            P[cp + "first_emb"].reshape(-1) if cfg.use_ref_pose_emb else None,
                            P[cp + "other_emb"].reshape(-1) if cfg.use_ref_pose_emb else None, pe)
+        # Level 0 on the main stream (the trunk needs it first); the coarser levels on the side stream, beside the stem and
+        # the level-0 blocks, joined where the trunk first reaches level 1.
         ss = []
         for l in range(cfg.num_resolutions):
             h, w = self.lvl_hw(l)
             pre = self.buf(f"emb_pre{l}", (N, h, w, E))
             sil = self.buf(f"emb_silu{l}", (N, h, w, E))
-            ops.gemm(G.conv_desc([pe], [9], Wp[cp + f"convs.{l}.weight"], E, pre, 2 ** l, bias=P[cp + f"convs.{l}.bias"],
-                                 rowvec=lemb, out2=sil))
             s_l = self.buf(f"ss{l}", (N * h * w, self.film_cols[l]))
-            ops.gemm(G.dense_desc(sil.view(N * h * w, E), Wp[f"film{l}"], s_l, self.film_cols[l], bias=self._bufs[f"b.film{l}"]))
+            with (ops.side() if l >= 1 else contextlib.nullcontext()):
+                ops.gemm(G.conv_desc([pe], [9], Wp[cp + f"convs.{l}.weight"], E, pre, 2 ** l, bias=P[cp + f"convs.{l}.bias"],
+                                     rowvec=lemb, out2=sil))
+                ops.gemm(G.dense_desc(sil.view(N * h * w, E), Wp[f"film{l}"], s_l, self.film_cols[l], bias=self._bufs[f"b.film{l}"]))
             ss.append(s_l)
 
         # ---- stem (xunet.py:493-495)
@@ -295,12 +299,15 @@ class Engine:
             elif kind == "pop":
                 skip = hs.pop()
             elif kind == "res":
+                if s.lvl >= 1:
+                    ops.join_side()            # FiLM operands of the coarser levels (no-op once joined)
                 h = self._res_fwd(s, h, skip if s.cat else None, ss[s.lvl], P, Wp, drop_p, seed * 1000 + bi)
                 skip = None
                 bi += 1
             else:
                 h = self._attn_fwd(s, h, P, Wp)
         assert not hs
+        ops.join_side()
 
         # ---- head (xunet.py:535-536)
         hh, ww, C = h.t.shape[1], h.t.shape[2], h.t.shape[3]
@@ -503,10 +510,11 @@ class Engine:
         stem = Act(self._bufs["stem"], "stem")
         dstem = self._grad_of(stem)
         xin = self._bufs["xin"]
-        ops.colsum(dstem.view(N * HW, cfg.ch), N * HW, Gr["conv.bias"])
-        gp = self.zbuf("bwd", "stem.gp", (cfg.ch, 9 * 64))
-        ops.gemm(G.wgrad_desc(dstem, xin, 9, gp, 0, 64))
-        self._unpack(gp, 0, 64, Gr["conv.weight"])
+        with ops.side():       # parameter gradients beside the data path (joined at the end of the phase)
+            ops.colsum(dstem.view(N * HW, cfg.ch), N * HW, Gr["conv.bias"])
+            gp = self.zbuf("bwd", "stem.gp", (cfg.ch, 9 * 64))
+            ops.gemm(G.wgrad_desc(dstem, xin, 9, gp, 0, 64))
+            self._unpack(gp, 0, 64, Gr["conv.weight"])
 
         # ---- conditioning: FiLM data gradient, conditioning convs, learned embeddings, logsnr MLP
         cp = "conditioningprocessor."
@@ -520,11 +528,12 @@ class Engine:
             de = self.buf(f"de{l}", (N, hh, ww, E))
             ops.gemm(G.dense_desc(dss[l], Wp[f"film{l}.T"], de.view(M, E), E))
             ops.silu_bwd(de, pre, de)
+            with ops.side():
+                ops.colsum(de.view(M, E), M, Gr[cp + f"convs.{l}.bias"])
+                gp = self.zbuf("bwd", f"cc{l}.gp", (E, 9 * 192))
+                ops.gemm(G.wgrad_desc(de, pe, 9, gp, 0, 192, 2 ** l))
+                self._unpack(gp, 0, 192, Gr[cp + f"convs.{l}.weight"])
             ops.colsum(de.view(M, E), hh * ww, dlemb)
-            ops.colsum(de.view(M, E), M, Gr[cp + f"convs.{l}.bias"])
-            gp = self.zbuf("bwd", f"cc{l}.gp", (E, 9 * 192))
-            ops.gemm(G.wgrad_desc(de, pe, 9, gp, 0, 192, 2 ** l))
-            self._unpack(gp, 0, 192, Gr[cp + f"convs.{l}.weight"])
             if cfg.use_pos_emb or cfg.use_ref_pose_emb:
                 des = self.buf(f"desum{l}", (2, hh, ww, E))
                 ops.batch_frame_sum(de, des)

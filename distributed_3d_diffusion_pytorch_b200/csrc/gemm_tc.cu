@@ -41,6 +41,8 @@ struct alignas(64) KP {
   int BN, b_chunks;
   int tiles_m, tiles_n, tiles_b, tiles_z, tiles_total;
   int bw, bh, bnn, tiles_x, tiles_y;
+  int m2, m2_dim, tbw, tbh, tbnn;   // two 128-row accumulators per tile sharing one B tile (see b3d_gemm); tile-origin strides
+  uint32_t a_bytes, acc_half;       // bytes of the A tile of a stage; TMEM column distance of the second accumulator
   int W, H, N;
   int stride, pad;
   int kbw, kbh, kbn, kblk_x, kblk_y, kblk_total;
@@ -84,9 +86,9 @@ __device__ __forceinline__ TileCoord decode_tile(const KP& p, int t) {
   if (p.a_major == 0) {
     int tx = c.tm % p.tiles_x;
     int r = c.tm / p.tiles_x;
-    c.x0 = tx * p.bw;
-    c.y0 = (r % p.tiles_y) * p.bh;
-    c.n0 = (r / p.tiles_y) * p.bnn;
+    c.x0 = tx * p.tbw;
+    c.y0 = (r % p.tiles_y) * p.tbh;
+    c.n0 = (r / p.tiles_y) * p.tbnn;
   } else {
     c.m0 = c.tm * BM;
     if (p.batched) { c.y0 = c.tb % p.H; c.n0 = c.tb / p.H; }
@@ -167,7 +169,7 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
               if (elect_one()) {
                 mbar_expect_tx(full_bar(stage), p.a_tx + p.b_tx);
                 tma_load_4d(sa, &p.tmA[sg.src], full_bar(stage), cb * BK, ax, ay, c.n0);
-                tma_load_4d(sa + kABytes, &p.tmB, full_bar(stage), sg.bk0 + cb * BK, ncol0, by, bn);
+                tma_load_4d(sa + p.a_bytes, &p.tmB, full_bar(stage), sg.bk0 + cb * BK, ncol0, by, bn);
               }
               advance();
             }
@@ -228,11 +230,17 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
           mbar_wait(full_bar(stage), phase);
           tc_fence_after();
           const uint32_t sa = smem_base + (uint32_t)stage * p.stage_bytes;
-          const uint64_t ad = a_desc0 + (uint64_t)(sa >> 4), bd = b_desc0 + (uint64_t)((sa + kABytes) >> 4);
+          const uint64_t ad = a_desc0 + (uint64_t)(sa >> 4), bd = b_desc0 + (uint64_t)((sa + p.a_bytes) >> 4);
           if (elect_one()) {
 #pragma unroll
             for (int k = 0; k < BK / 16; ++k)
               umma_bf16(d_tmem, ad + (uint64_t)(k * a_kstep), bd + (uint64_t)(k * b_kstep), idesc, (kb | k) != 0 ? 1u : 0u);
+            if (p.m2) {                     // rows 128..255 of the A tile against the same B tile, into the second accumulator
+#pragma unroll
+              for (int k = 0; k < BK / 16; ++k)
+                umma_bf16(d_tmem + p.acc_half, ad + (uint64_t)((kABytes >> 4) + k * a_kstep), bd + (uint64_t)(k * b_kstep), idesc,
+                          (kb | k) != 0 ? 1u : 0u);
+            }
             umma_commit(empty_bar(stage));  // frees the smem slot once these MMAs have read it
           }
           if (++stage == S) { stage = 0; phase ^= 1; }
@@ -347,19 +355,29 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
         cx = c.m0; cy = c.y0; cn = c.n0 ^ p.o_xor; img = c.n0;
       }
       const int nch = (min(p.BN, p.n_cols - c.tn * p.BN) + 63) / 64;
+      const int rounds = (1 + p.m2) * nch;      // (accumulator half, 64-column chunk), half-major
+      // output-box origin of a half: the second 128 rows of a doubled tile continue along m2_dim (x / y / image)
+      const int cx0 = cx, cy0 = cy, cn0 = cn, img0 = img;
+      const int hx = p.m2_dim == 0 ? p.bw : 0, hy = p.m2_dim == 1 ? p.bh : 0, hn = p.m2_dim == 2 ? p.bnn : 0;
       if (p.resid != nullptr && leader) {
         mbar_expect_tx(resid_bar(buf), rows_bytes);
         tma_load_4d(sx_base + buf * 16384, &p.tmR, resid_bar(buf), c.tn * p.BN, cx, cy, cn);
       }
       mbar_wait(tfull_bar(acc), acc_phase);
       tc_fence_after();
-      const uint32_t taddr = tmem_base + (uint32_t)(acc * p.acc_stride) + ((uint32_t)(quad * 32) << 16);
-      for (int ch = 0; ch < nch; ++ch) {
+      const uint32_t taddr0 = tmem_base + (uint32_t)(acc * p.acc_stride) + ((uint32_t)(quad * 32) << 16);
+      for (int rd = 0; rd < rounds; ++rd) {
+        const int half = rd >= nch ? 1 : 0, ch = rd - half * nch;
+        cx = cx0 + half * hx; cy = cy0 + half * hy; cn = cn0 + half * hn;
+        img = img0 + half * hn; if (img >= p.N) img = p.N - 1;
+        const uint32_t taddr = taddr0 + (uint32_t)half * p.acc_half;
         const int col0 = c.tn * p.BN + ch * 64;
         if (leader) {
-          if (p.resid != nullptr && ch + 1 < nch) {
+          if (p.resid != nullptr && rd + 1 < rounds) {
+            const int nh = rd + 1 >= nch ? 1 : 0, nc = rd + 1 - nh * nch;
             mbar_expect_tx(resid_bar(buf ^ 1), rows_bytes);
-            tma_load_4d(sx_base + (buf ^ 1) * 16384, &p.tmR, resid_bar(buf ^ 1), col0 + 64, cx, cy, cn);
+            tma_load_4d(sx_base + (buf ^ 1) * 16384, &p.tmR, resid_bar(buf ^ 1), c.tn * p.BN + nc * 64, cx0 + nh * hx, cy0 + nh * hy,
+                        cn0 + nh * hn);
           }
           tma_store_wait_read<1>();      // the store that last used this buffer has finished reading it
         }
@@ -437,7 +455,7 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
             }
           }
         }
-        if (ch == nch - 1) {             // accumulator fully read: hand the TMEM buffer back to the MMA warp
+        if (rd == rounds - 1) {          // accumulator(s) fully read: hand the TMEM buffer back to the MMA warp
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(tempty_bar(acc));
@@ -646,7 +664,6 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
   p.b_chunks = (BN + 63) / 64;
   p.b_bytes = d->b_major ? (uint32_t)p.b_chunks * 8192u : (uint32_t)((BN * 128 + 1023) / 1024 * 1024);
   p.b_tx = d->b_major ? (uint32_t)p.b_chunks * 8192u : (uint32_t)BN * 128u;
-  p.stage_bytes = kABytes + p.b_bytes;
   // bf16 outputs whose rows are 16-byte aligned leave through smem + TMA store (2 x 16 KB staging, + 2 x 16 KB for
   // the residual tile or the second output)
   const bool al16 = ((uintptr_t)d->out & 15) == 0;
@@ -658,11 +675,36 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
     p.epi_tma = (d->n_cols % 4 == 0 && d->out_stride[0] % 4 == 0 && d->out_stride[1] % 4 == 0 && d->out_stride[2] % 4 == 0 &&
                  d->out_tap_stride % 4 == 0 && al16 && d->resid == nullptr && d->out2 == nullptr) ? 1 : 0;
   const uint32_t epi_bytes = p.epi_tma ? ((d->resid || d->out2) ? 65536u : 32768u) : 0u;
+  // Narrow tiles (BN <= 128) of the convolution / dense form: 256 output rows per tile -- two 128-row accumulators fed
+  // by ONE B tile.  A 128 x 128 tile loads 32 KB of operands per 2.1 MFLOP and is bound by the L2 -> SM operand path
+  // (measured 1.0 PFLOP/s); 256 x 128 loads 48 KB per 4.2 MFLOP.  The doubled tile continues along the outermost
+  // dimension of the pixel box (rows, else images, else x for the dense form), so each half is an ordinary box for the
+  // epilogue's TMA stores.  Needs 4 * BN TMEM columns (double-buffered) and enough tiles to keep every SM busy.
+  p.a_bytes = kABytes; p.acc_half = 0;
+  int m2_bw = 0, m2_bh = 0, m2_bnn = 0;
+  if (d->a_major == 0 && d->b_major == 0 && !d->batched && s == 1 && p.epi_tma && !d->out_fp32 && BN <= 128) {
+    const int bw = d->W < BM ? d->W : BM;
+    int bh = BM / bw; if (bh > d->H) bh = d->H; if (bh < 1) bh = 1;
+    int bnn = (bh == d->H) ? BM / (bw * bh) : 1; if (bnn > d->N) bnn = d->N; if (bnn < 1) bnn = 1;
+    int dim = -1;
+    if (bw * bh * bnn == BM) {
+      if (bh < d->H) dim = 1;
+      else if (2 * bnn <= d->N) dim = 2;
+      else if (d->H == 1 && d->N == 1 && d->W >= 2 * BM) dim = 0;
+    }
+    if (dim >= 0) {
+      const int tbw = dim == 0 ? 2 * bw : bw, tbh = dim == 1 ? 2 * bh : bh, tbnn = dim == 2 ? 2 * bnn : bnn;
+      const long long tiles = (long long)((d->W + tbw - 1) / tbw) * ((d->H + tbh - 1) / tbh) * ((d->N + tbnn - 1) / tbnn) * p.tiles_n;
+      if (tiles >= 2LL * b3d_num_sms()) { p.m2 = 1; p.m2_dim = dim; m2_bw = tbw; m2_bh = tbh; m2_bnn = tbnn; p.a_bytes = 2 * kABytes; }
+    }
+  }
+  p.stage_bytes = p.a_bytes + p.b_bytes;
   p.num_stages = (int)((kMaxDynSmem - 1024 - epi_bytes) / p.stage_bytes);
   if (p.num_stages > 8) p.num_stages = 8;
   B3D_CHECK_ARG(p.num_stages >= 2, "b3d_gemm: not enough shared memory for a 2-stage pipeline");
   p.epi_off = (uint32_t)p.num_stages * p.stage_bytes;
   p.acc_stride = (BN + 31) / 32 * 32;
+  if (p.m2) { p.acc_half = (uint32_t)p.acc_stride; p.acc_stride *= 2; }
   p.tmem_cols = pow2_ceil(2 * p.acc_stride);
   if (p.tmem_cols < 32) p.tmem_cols = 32;
   // instruction descriptor: D fp32 (bit 4), A/B bf16 (bits 7,10), majors (15,16), N>>3 at 17, M>>4 at 24
@@ -678,13 +720,14 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
       p.bh = BM / p.bw; if (p.bh > d->H) p.bh = d->H; if (p.bh < 1) p.bh = 1;
       p.bnn = (p.bh == d->H) ? BM / (p.bw * p.bh) : 1; if (p.bnn > d->N) p.bnn = d->N; if (p.bnn < 1) p.bnn = 1;
     }
-    p.tiles_x = (d->W + p.bw - 1) / p.bw;
-    p.tiles_y = (d->H + p.bh - 1) / p.bh;
-    const int tiles_img = (d->N + p.bnn - 1) / p.bnn;
+    p.tbw = p.m2 ? m2_bw : p.bw; p.tbh = p.m2 ? m2_bh : p.bh; p.tbnn = p.m2 ? m2_bnn : p.bnn;
+    p.tiles_x = (d->W + p.tbw - 1) / p.tbw;
+    p.tiles_y = (d->H + p.tbh - 1) / p.tbh;
+    const int tiles_img = (d->N + p.tbnn - 1) / p.tbnn;
     p.tiles_m = p.tiles_x * p.tiles_y * tiles_img;
     p.tiles_b = 1; p.tiles_z = 1;
-    p.a_tx = (uint32_t)(p.bw * p.bh * p.bnn) * 128u;
-    const uint32_t boxA[4] = {64, (uint32_t)((p.bw - 1) * s + 1), (uint32_t)((p.bh - 1) * s + 1), (uint32_t)p.bnn};
+    p.a_tx = (uint32_t)(p.tbw * p.tbh * p.tbnn) * 128u;
+    const uint32_t boxA[4] = {64, (uint32_t)((p.tbw - 1) * s + 1), (uint32_t)((p.tbh - 1) * s + 1), (uint32_t)p.tbnn};
     const uint32_t esA[4] = {1, (uint32_t)s, (uint32_t)s, 1};
     if (d->b_major == 0) {
       B3D_CHECK_ARG(d->n_src >= 1 && d->n_src <= 3, "b3d_gemm: n_src");

@@ -151,6 +151,13 @@ def all_cases():
         dense_case("dense_1000x144x48", 1000, 144, 48),
         dense_case("dense_4096x1024x2048", 4096, 1024, 2048),
         dense_case("dense_512x256x384_bn192", 512, 256, 384),
+        # 256-row tiles (two accumulators per B tile): need >= 2 tiles per SM, hence the larger pixel counts
+        conv_case("conv_m2_rows_64x64_c64_128_resid", 20, 64, 64, [64], [9], 128, resid=True, out_scale=0.70710678, seed=11),
+        conv_case("conv_m2_rows_30x32_c32_96_rowvec_out2", 84, 30, 32, [32], [9], 96, rowvec=True, out2=True, seed=12),
+        conv_case("conv_m2_images_8x8_c64_64", 1210, 8, 8, [64], [9], 64, seed=13),
+        conv_case("conv_m2_1x1_two_src_64x64", 19, 64, 64, [64, 32], [1, 1], 128, seed=14),
+        dense_case("dense_m2_76000x192x128", 76000, 192, 128, seed=15),
+        dense_case("dense_m2_80001x64x72_silu", 80001, 64, 72, act=1, seed=16),
         conv_case("conv_16x16_c64_128", 2, 16, 16, [64], [9], 128),
         conv_case("conv_64x64_c128_128_resid", 2, 64, 64, [128], [9], 128, resid=True, out_scale=0.70710678),
         conv_case("conv_8x8_c512_512", 4, 8, 8, [512], [9], 512),

@@ -14,6 +14,7 @@
 #include <cuda.h>
 #include <stdarg.h>
 
+#include <cstdlib>
 #include "../../include/b3d.h"
 #include "b3d_common.cuh"
 #include "tc_ptx.cuh"
@@ -682,7 +683,8 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
   // epilogue's TMA stores.  Needs 4 * BN TMEM columns (double-buffered) and enough tiles to keep every SM busy.
   p.a_bytes = kABytes; p.acc_half = 0;
   int m2_bw = 0, m2_bh = 0, m2_bnn = 0;
-  if (d->a_major == 0 && d->b_major == 0 && !d->batched && s == 1 && p.epi_tma && !d->out_fp32 && BN <= 128) {
+  static const bool no_m2 = getenv("B3D_NO_M2") != nullptr;      // measurement switch
+  if (!no_m2 && d->a_major == 0 && d->b_major == 0 && !d->batched && s == 1 && p.epi_tma && !d->out_fp32 && BN <= 128) {
     const int bw = d->W < BM ? d->W : BM;
     int bh = BM / bw; if (bh > d->H) bh = d->H; if (bh < 1) bh = 1;
     int bnn = (bh == d->H) ? BM / (bw * bh) : 1; if (bnn > d->N) bnn = d->N; if (bnn < 1) bnn = 1;

@@ -48,6 +48,7 @@ struct alignas(64) KP {
   int stride, pad;
   int kbw, kbh, kbn, kblk_x, kblk_y, kblk_total;
   int split_k, b_taps;
+  int tpg, tap_groups, cpt;          // weight gradients: taps per tile (their Ci-wide slabs side by side in one N tile), tile groups, 64-chunks per tap
   int kchan_blocks;
   int m_rows, n_cols;
   int num_stages;
@@ -81,8 +82,8 @@ __device__ __forceinline__ TileCoord decode_tile(const KP& p, int t) {
   c.tn = t % p.tiles_n; t /= p.tiles_n;
   c.tm = t % p.tiles_m; t /= p.tiles_m;
   c.tb = t % p.tiles_b; c.tz = t / p.tiles_b;
-  c.tap = c.tz % p.b_taps;
-  c.split = c.tz / p.b_taps;
+  c.tap = c.tz % p.tap_groups;       // tap, or first-tap group when several taps share a tile (tpg > 1)
+  c.split = c.tz / p.tap_groups;
   c.m0 = 0; c.x0 = 0; c.y0 = 0; c.n0 = 0;
   if (p.a_major == 0) {
     int tx = c.tm % p.tiles_x;
@@ -187,8 +188,11 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
             advance();
           }
         } else {  // (1,1): K = pixels of both
-          const int dx = p.b_taps == 9 ? (c.tap % 3) - p.pad : 0;
-          const int dy = p.b_taps == 9 ? (c.tap / 3) - p.pad : 0;
+          const int tap0 = c.tap * p.tpg;
+          const int dx = p.b_taps == 9 ? (tap0 % 3) - p.pad : 0;
+          const int dy = p.b_taps == 9 ? (tap0 / 3) - p.pad : 0;
+          // several taps per tile: the B tile is the taps' shifted pixel windows side by side (cpt 64-channel chunks each)
+          const int nchunks = p.tpg > 1 ? min(p.b_chunks, (p.b_taps - tap0) * p.cpt) : p.b_chunks;
           for (int i = 0; i < nkb; ++i) {
             int kx, ky, kn;
             if (p.batched) { kx = i * p.kbw; ky = c.y0; kn = c.n0; }
@@ -199,12 +203,20 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
             }
             const uint32_t sa = acquire();
             if (elect_one()) {
-              mbar_expect_tx(full_bar(stage), p.a_tx + p.b_tx);
+              mbar_expect_tx(full_bar(stage), p.a_tx + (uint32_t)nchunks * 8192u);
               tma_load_4d(sa, &p.tmA[0], full_bar(stage), c.m0, kx, ky, kn);
               tma_load_4d(sa + 8192, &p.tmA[0], full_bar(stage), c.m0 + 64, kx, ky, kn);
-              for (int j = 0; j < p.b_chunks; ++j)
-                tma_load_4d(sa + kABytes + j * 8192, &p.tmB, full_bar(stage), ncol0 + j * 64, kx * p.stride + dx,
-                            ky * p.stride + dy, kn ^ p.b_xor);
+              if (p.tpg > 1) {
+                for (int j = 0; j < nchunks; ++j) {
+                  const int tp = tap0 + j / p.cpt;
+                  tma_load_4d(sa + kABytes + j * 8192, &p.tmB, full_bar(stage), (j % p.cpt) * 64, kx * p.stride + (tp % 3) - p.pad,
+                              ky * p.stride + (tp / 3) - p.pad, kn ^ p.b_xor);
+                }
+              } else {
+                for (int j = 0; j < p.b_chunks; ++j)
+                  tma_load_4d(sa + kABytes + j * 8192, &p.tmB, full_bar(stage), ncol0 + j * 64, kx * p.stride + dx,
+                              ky * p.stride + dy, kn ^ p.b_xor);
+              }
             }
             advance();
           }
@@ -272,7 +284,8 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
       } else {
         cx = c.m0; cy = c.y0; cn = c.n0 ^ p.o_xor; img = c.n0;
       }
-      const int ncols_tile = min(p.BN, p.n_cols - c.tn * p.BN);
+      const bool grouped = p.tpg > 1;    // the tile spans several whole taps: every column below ncols_tile is real
+      const int ncols_tile = grouped ? min(p.BN, (p.b_taps - c.tap * p.tpg) * p.n_cols) : min(p.BN, p.n_cols - c.tn * p.BN);
       const int nch = (ncols_tile + 31) / 32;
       mbar_wait(tfull_bar(acc), acc_phase);
       tc_fence_after();
@@ -286,7 +299,7 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
         float f[32];
 #pragma unroll
         for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]) * p.alpha;
-        const bool full = cc + 32 <= p.n_cols;
+        const bool full = grouped || cc + 32 <= p.n_cols;
         if (p.bias) {
 #pragma unroll
           for (int i = 0; i < 32; ++i) if (full || cc + i < p.n_cols) f[i] += __ldg(p.bias + cc + i);
@@ -321,7 +334,7 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
         fence_proxy_async();
         epi_bar_sync();
         if (leader) {
-          const int col = cc + c.tap * (int)p.os_tap;
+          const int col = cc + c.tap * p.tpg * (int)p.os_tap;     // grouped: os_tap == n_cols, the taps' slabs are contiguous
           if (p.out_atomic) tma_reduce_add_4d(&p.tmO, so_base + buf * 16384, col, cx, cy, cn);
           else tma_store_4d(&p.tmO, so_base + buf * 16384, col, cx, cy, cn);
           tma_store_commit();
@@ -642,7 +655,29 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
   p.split_k = d->split_k > 0 ? d->split_k : 1;
   B3D_CHECK_ARG(p.W > 0 && p.H > 0 && p.N > 0, "b3d_gemm: W/H/N");
 
-  int BN = d->bn_tile;
+  // bf16 outputs whose rows are 16-byte aligned leave through smem + TMA store (2 x 16 KB staging, + 2 x 16 KB for
+  // the residual tile or the second output)
+  const bool al16 = ((uintptr_t)d->out & 15) == 0;
+  if (!d->out_fp32)
+    p.epi_tma = (!d->out_atomic && d->n_cols % 8 == 0 && d->out_stride[0] % 8 == 0 && d->out_stride[1] % 8 == 0 && d->out_stride[2] % 8 == 0 &&
+                 d->out_tap_stride == 0 && al16 && (d->resid == nullptr || d->out2 == nullptr) &&
+                 (d->resid == nullptr || ((uintptr_t)d->resid & 15) == 0) && (d->out2 == nullptr || ((uintptr_t)d->out2 & 15) == 0)) ? 1 : 0;
+  else   // fp32: plain TMA store, or TMA reduce-add for the atomically accumulated (split-K) weight gradients
+    p.epi_tma = (d->n_cols % 4 == 0 && d->out_stride[0] % 4 == 0 && d->out_stride[1] % 4 == 0 && d->out_stride[2] % 4 == 0 &&
+                 d->out_tap_stride % 4 == 0 && al16 && d->resid == nullptr && d->out2 == nullptr) ? 1 : 0;
+
+  // Per-tap weight gradients of narrow layers (Ci = 64 / 128 with unpadded slabs): 256 / Ci taps share one tile -- the
+  // dy (A) tile is loaded once for all of them and the MMA runs at N = 256 (a 128 x 128 tile per tap was bound by the
+  // L2 -> SM operand path at 0.73 PFLOP/s).  Their slabs are adjacent in the packed gradient, so the epilogue is unchanged.
+  p.tpg = 1; p.cpt = 1;
+  static const bool no_tpg = getenv("B3D_NO_TAPGROUP") != nullptr;     // measurement switch
+  if (!no_tpg && d->a_major == 1 && d->b_major == 1 && !d->batched && p.b_taps == 9 && p.epi_tma && d->out_fp32 && d->n_cols % 64 == 0 &&
+      d->n_cols <= 128 && d->out_tap_stride == d->n_cols) {
+    p.tpg = 256 / d->n_cols; p.cpt = d->n_cols / 64;
+  }
+  p.tap_groups = (p.b_taps + p.tpg - 1) / p.tpg;
+
+  int BN = p.tpg > 1 ? p.tpg * d->n_cols : d->bn_tile;
   if (BN <= 0) {
     // number of tiles in all other grid dimensions, to see whether the launch can fill the GPU
     long long other;
@@ -661,20 +696,10 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
   }
   B3D_CHECK_ARG(BN % 16 == 0 && BN >= 16 && BN <= 256, "b3d_gemm: tile N %d must be a multiple of 16 in [16,256]", BN);
   p.BN = BN;
-  p.tiles_n = (d->n_cols + BN - 1) / BN;
+  p.tiles_n = p.tpg > 1 ? 1 : (d->n_cols + BN - 1) / BN;
   p.b_chunks = (BN + 63) / 64;
   p.b_bytes = d->b_major ? (uint32_t)p.b_chunks * 8192u : (uint32_t)((BN * 128 + 1023) / 1024 * 1024);
   p.b_tx = d->b_major ? (uint32_t)p.b_chunks * 8192u : (uint32_t)BN * 128u;
-  // bf16 outputs whose rows are 16-byte aligned leave through smem + TMA store (2 x 16 KB staging, + 2 x 16 KB for
-  // the residual tile or the second output)
-  const bool al16 = ((uintptr_t)d->out & 15) == 0;
-  if (!d->out_fp32)
-    p.epi_tma = (!d->out_atomic && d->n_cols % 8 == 0 && d->out_stride[0] % 8 == 0 && d->out_stride[1] % 8 == 0 && d->out_stride[2] % 8 == 0 &&
-                 d->out_tap_stride == 0 && al16 && (d->resid == nullptr || d->out2 == nullptr) &&
-                 (d->resid == nullptr || ((uintptr_t)d->resid & 15) == 0) && (d->out2 == nullptr || ((uintptr_t)d->out2 & 15) == 0)) ? 1 : 0;
-  else   // fp32: plain TMA store, or TMA reduce-add for the atomically accumulated (split-K) weight gradients
-    p.epi_tma = (d->n_cols % 4 == 0 && d->out_stride[0] % 4 == 0 && d->out_stride[1] % 4 == 0 && d->out_stride[2] % 4 == 0 &&
-                 d->out_tap_stride % 4 == 0 && al16 && d->resid == nullptr && d->out2 == nullptr) ? 1 : 0;
   const uint32_t epi_bytes = p.epi_tma ? ((d->resid || d->out2) ? 65536u : 32768u) : 0u;
   // Narrow tiles (BN <= 128) of the convolution / dense form: 256 output rows per tile -- two 128-row accumulators fed
   // by ONE B tile.  A 128 x 128 tile loads 32 KB of operands per 2.1 MFLOP and is bound by the L2 -> SM operand path
@@ -773,7 +798,7 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
     if (d->batched) p.split_k = 1;
     if (p.split_k > p.kblk_total) p.split_k = p.kblk_total;
     B3D_CHECK_ARG(p.split_k == 1 || d->out_atomic, "b3d_gemm: split_k > 1 needs out_atomic");
-    p.tiles_z = p.b_taps * p.split_k;
+    p.tiles_z = p.tap_groups * p.split_k;
     p.a_tx = 2 * 8192u;
     const uint32_t boxA[4] = {64, (uint32_t)p.kbw, (uint32_t)p.kbh, (uint32_t)p.kbn};
     rc = make_map(&p.tmA[0], d->a[0], boxA, ones); if (rc) return rc;

@@ -47,7 +47,9 @@ def wgrad_desc(dy, x, taps, out_packed, k_off, Cpad, stride=1, split_k=None):
     N, H, W, Co = dy.shape
     Ci = x.shape[-1]
     bn = min(256, (Ci + 15) // 16 * 16) if Ci <= 256 else 0
-    tiles = ((Co + 127) // 128) * max(1, math.ceil(Ci / 256)) * taps
+    # narrow unpadded slabs: b3d_gemm puts 256 // Ci taps side by side in one tile (csrc/gemm_tc.cu, "tpg")
+    tpg = 256 // Ci if (taps == 9 and Ci % 64 == 0 and Ci <= 128 and Cpad == Ci) else 1
+    tiles = ((Co + 127) // 128) * max(1, math.ceil(Ci / 256)) * math.ceil(taps / tpg)
     kblocks = max(1, (N * H * W) // 64)
     if split_k is None:
         split_k = pick_split_k(tiles, kblocks)

@@ -189,34 +189,36 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
           }
         } else {  // (1,1): K = pixels of both
           const int tap0 = c.tap * p.tpg;
-          const int dx = p.b_taps == 9 ? (tap0 % 3) - p.pad : 0;
-          const int dy = p.b_taps == 9 ? (tap0 / 3) - p.pad : 0;
           // several taps per tile: the B tile is the taps' shifted pixel windows side by side (cpt 64-channel chunks each)
           const int nchunks = p.tpg > 1 ? min(p.b_chunks, (p.b_taps - tap0) * p.cpt) : p.b_chunks;
+          // per-chunk channel offset and tap shift, hoisted out of the K loop (max 4 chunks per tile)
+          int ch_c[4], ch_dx[4], ch_dy[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int tp = p.tpg > 1 ? tap0 + j / p.cpt : tap0;
+            ch_c[j] = p.tpg > 1 ? (j % p.cpt) * 64 : ncol0 + j * 64;
+            ch_dx[j] = p.b_taps == 9 ? (tp % 3) - p.pad : 0;
+            ch_dy[j] = p.b_taps == 9 ? (tp / 3) - p.pad : 0;
+          }
+          // pixel-block counters advanced incrementally (a div/mod pair per K block made this warp the bottleneck)
+          int bx = 0, by = 0, bn = 0;
+          if (!p.batched) { int pb = kb0; bx = pb % p.kblk_x; pb /= p.kblk_x; by = pb % p.kblk_y; bn = pb / p.kblk_y; }
           for (int i = 0; i < nkb; ++i) {
             int kx, ky, kn;
             if (p.batched) { kx = i * p.kbw; ky = c.y0; kn = c.n0; }
             else {
-              int pb = kb0 + i;
-              kx = (pb % p.kblk_x) * p.kbw; pb /= p.kblk_x;
-              ky = (pb % p.kblk_y) * p.kbh; kn = (pb / p.kblk_y) * p.kbn;
+              kx = bx * p.kbw; ky = by * p.kbh; kn = bn * p.kbn;
+              if (++bx == p.kblk_x) { bx = 0; if (++by == p.kblk_y) { by = 0; ++bn; } }
             }
             const uint32_t sa = acquire();
             if (elect_one()) {
               mbar_expect_tx(full_bar(stage), p.a_tx + (uint32_t)nchunks * 8192u);
               tma_load_4d(sa, &p.tmA[0], full_bar(stage), c.m0, kx, ky, kn);
               tma_load_4d(sa + 8192, &p.tmA[0], full_bar(stage), c.m0 + 64, kx, ky, kn);
-              if (p.tpg > 1) {
-                for (int j = 0; j < nchunks; ++j) {
-                  const int tp = tap0 + j / p.cpt;
-                  tma_load_4d(sa + kABytes + j * 8192, &p.tmB, full_bar(stage), (j % p.cpt) * 64, kx * p.stride + (tp % 3) - p.pad,
-                              ky * p.stride + (tp / 3) - p.pad, kn ^ p.b_xor);
-                }
-              } else {
-                for (int j = 0; j < p.b_chunks; ++j)
-                  tma_load_4d(sa + kABytes + j * 8192, &p.tmB, full_bar(stage), ncol0 + j * 64, kx * p.stride + dx,
-                              ky * p.stride + dy, kn ^ p.b_xor);
-              }
+              const int sx = kx * p.stride, sy = ky * p.stride, nb = kn ^ p.b_xor;
+#pragma unroll
+              for (int j = 0; j < 4; ++j)
+                if (j < nchunks) tma_load_4d(sa + kABytes + j * 8192, &p.tmB, full_bar(stage), ch_c[j], sx + ch_dx[j], sy + ch_dy[j], nb);
             }
             advance();
           }

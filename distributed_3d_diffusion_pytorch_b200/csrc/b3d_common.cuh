@@ -56,16 +56,31 @@ __device__ __forceinline__ void b3d_pdl_sync() {
 #endif
 }
 bool b3d_pdl_enabled();
+// cluster_x > 1: thread-block clusters of that many CTAs along x (grid.x must be a multiple of it)
 template <typename... KArgs, typename... Args>
-inline cudaError_t b3d_launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+inline cudaError_t b3d_launch_cluster_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, int cluster_x,
+                                          Args&&... args) {
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
-  cudaLaunchAttribute at[1];
-  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  at[0].val.programmaticStreamSerializationAllowed = 1;
-  cfg.attrs = at; cfg.numAttrs = b3d_pdl_enabled() ? 1 : 0;
+  cudaLaunchAttribute at[2];
+  int na = 0;
+  if (b3d_pdl_enabled()) {
+    at[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  if (cluster_x > 1) {
+    at[na].id = cudaLaunchAttributeClusterDimension;
+    at[na].val.clusterDim.x = (unsigned)cluster_x; at[na].val.clusterDim.y = 1; at[na].val.clusterDim.z = 1;
+    ++na;
+  }
+  cfg.attrs = at; cfg.numAttrs = na;
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t b3d_launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  return b3d_launch_cluster_pdl(kernel, grid, block, smem, st, 1, static_cast<Args&&>(args)...);
 }
 
 __device__ __forceinline__ float b3d_silu(float x) { return __fdividef(x, 1.0f + __expf(-x)); }

@@ -42,6 +42,7 @@ struct alignas(64) KP {
   int BN, b_chunks;
   int tiles_m, tiles_n, tiles_b, tiles_z, tiles_total;
   int bw, bh, bnn, tiles_x, tiles_y;
+  int c2;                            // CTA pair (cta_group::2): the tile's two 128-row halves live in the two CTAs of a cluster
   int m2, m2_dim, tbw, tbh, tbnn;   // two 128-row accumulators per tile sharing one B tile (see b3d_gemm); tile-origin strides
   uint32_t a_bytes, acc_half;       // bytes of the A tile of a stage; TMEM column distance of the second accumulator
   int W, H, N;
@@ -113,6 +114,9 @@ __device__ __forceinline__ void k_range(const KP& p, const TileCoord& c, int& kb
   }
 }
 
+// kPair = true: the CTA-pair (cta_group::2) instantiation -- it must be launched as clusters of two (a kernel containing
+// cta_group::2 instructions is rejected at launch without them), so the single-CTA path is a separate instantiation.
+template <bool kPair>
 __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_constant__ KP p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t bars[2 * 8 + 4 + 2];
@@ -132,7 +136,7 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < S; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
-    for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 4); mbar_init(resid_bar(s), 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), kPair ? 8 : 4); mbar_init(resid_bar(s), 1); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (threadIdx.x == 64) {      // descriptor fetches overlap the barrier init / TMEM allocation (short launches are latency-bound)
@@ -140,19 +144,29 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
     prefetch_tensormap(&p.tmB);
     if (p.epi_tma) prefetch_tensormap(&p.tmO);
   }
-  if (warp == 1) tmem_alloc(smem_u32(&tmem_base_smem), (uint32_t)p.tmem_cols);
+  if (warp == 1) {
+    if constexpr (kPair) tmem_alloc2(smem_u32(&tmem_base_smem), (uint32_t)p.tmem_cols);
+    else tmem_alloc(smem_u32(&tmem_base_smem), (uint32_t)p.tmem_cols);
+  }
   tc_fence_before();
   __syncthreads();
+  if constexpr (kPair) cluster_sync_all();     // the peer's barriers are initialised before anything is signalled across the pair
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_smem;
   b3d_pdl_sync();   // everything above overlapped the previous kernel's tail; global memory is touched only below
+  // CTA pair: both CTAs walk the same tile sequence; rank 1 takes the second 128 rows (offset along m2_dim) and the
+  // second half of the B tile's rows, rank 0 issues the M = 256 MMAs for both
+  const uint32_t crank = kPair ? __shfl_sync(0xffffffffu, cluster_ctarank(), 0) : 0u;    // (shuffle: provably warp-uniform)
+  const int t_first = kPair ? (int)(blockIdx.x >> 1) : (int)blockIdx.x, t_step = kPair ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+  const int half_x = kPair && p.m2_dim == 0 ? (int)crank * p.bw : 0, half_y = kPair && p.m2_dim == 1 ? (int)crank * p.bh : 0,
+            half_n = kPair && p.m2_dim == 2 ? (int)crank * p.bnn : 0;
 
   if (warp == 0) {
     // ===================================================================== TMA producer
     // The whole warp walks the (warp-uniform) loops and polls the barriers; one elected lane issues the copies.
     {
       int stage = 0; uint32_t phase = 0;
-      for (int t = blockIdx.x; t < p.tiles_total; t += gridDim.x) {
+      for (int t = t_first; t < p.tiles_total; t += t_step) {
         const TileCoord c = decode_tile(p, t);
         int kb0, nkb; k_range(p, c, kb0, nkb);
         const int ncol0 = c.tn * p.BN;
@@ -165,13 +179,20 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
           const int by = p.batched ? c.y0 : 0, bn = p.batched ? (c.n0 ^ p.b_xor) : 0;
           for (int s = 0; s < p.nseg; ++s) {
             const Seg sg = p.seg[s];
-            const int ax = c.x0 * p.stride + sg.dx, ay = c.y0 * p.stride + sg.dy;
+            const int ax = (c.x0 + half_x) * p.stride + sg.dx, ay = (c.y0 + half_y) * p.stride + sg.dy, an = c.n0 + half_n;
             for (int cb = 0; cb < sg.ncb; ++cb) {
               const uint32_t sa = acquire();
               if (elect_one()) {
-                mbar_expect_tx(full_bar(stage), p.a_tx + p.b_tx);
-                tma_load_4d(sa, &p.tmA[sg.src], full_bar(stage), cb * BK, ax, ay, c.n0);
-                tma_load_4d(sa + p.a_bytes, &p.tmB, full_bar(stage), sg.bk0 + cb * BK, ncol0, by, bn);
+                if constexpr (kPair) {    // both CTAs' bytes are counted on the leader's barrier, armed by the leader for the pair
+                  const uint32_t lead_bar = mapa_shared(full_bar(stage), 0u);
+                  if (crank == 0) mbar_expect_tx(full_bar(stage), 2u * (p.a_tx + p.b_tx));
+                  tma_load_4d_pair(sa, &p.tmA[sg.src], lead_bar, cb * BK, ax, ay, an);
+                  tma_load_4d_pair(sa + p.a_bytes, &p.tmB, lead_bar, sg.bk0 + cb * BK, ncol0 + (int)crank * (p.BN / 2), by, bn);
+                } else {
+                  mbar_expect_tx(full_bar(stage), p.a_tx + p.b_tx);
+                  tma_load_4d(sa, &p.tmA[sg.src], full_bar(stage), cb * BK, ax, ay, an);
+                  tma_load_4d(sa + p.a_bytes, &p.tmB, full_bar(stage), sg.bk0 + cb * BK, ncol0, by, bn);
+                }
               }
               advance();
             }
@@ -228,14 +249,15 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
   } else if (warp == 1) {
     // ===================================================================== MMA issuer
     // Warp-uniform loop; the same elected lane issues every tcgen05.mma and the commits that track them.
-    {
+    // In a CTA pair only the leader issues (cta_group::2); its commits arrive on both CTAs' barriers.
+    if (crank == 0) {
       int stage = 0; uint32_t phase = 0;
       int acc = 0; uint32_t acc_phase = 0;
       const uint32_t a_kstep = p.a_major ? (2048u >> 4) : (32u >> 4), b_kstep = p.b_major ? (2048u >> 4) : (32u >> 4);
       const uint32_t a_lbo = p.a_major ? 8192u : 16u, b_lbo = p.b_major ? 8192u : 16u;
       const uint64_t a_desc0 = umma_desc(0u, a_lbo, 1024u), b_desc0 = umma_desc(0u, b_lbo, 1024u);
       const uint32_t idesc = p.idesc;
-      for (int t = blockIdx.x; t < p.tiles_total; t += gridDim.x) {
+      for (int t = t_first; t < p.tiles_total; t += t_step) {
         const TileCoord c = decode_tile(p, t);
         int kb0, nkb; k_range(p, c, kb0, nkb);
         mbar_wait(tempty_bar(acc), acc_phase ^ 1);
@@ -246,7 +268,14 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
           tc_fence_after();
           const uint32_t sa = smem_base + (uint32_t)stage * p.stage_bytes;
           const uint64_t ad = a_desc0 + (uint64_t)(sa >> 4), bd = b_desc0 + (uint64_t)((sa + p.a_bytes) >> 4);
-          if (elect_one()) {
+          if constexpr (kPair) {
+            if (elect_one()) {
+#pragma unroll
+              for (int k = 0; k < BK / 16; ++k)
+                umma_bf16_pair(d_tmem, ad + (uint64_t)(k * a_kstep), bd + (uint64_t)(k * b_kstep), idesc, (kb | k) != 0 ? 1u : 0u);
+              umma_commit_pair(empty_bar(stage));
+            }
+          } else if (elect_one()) {
 #pragma unroll
             for (int k = 0; k < BK / 16; ++k)
               umma_bf16(d_tmem, ad + (uint64_t)(k * a_kstep), bd + (uint64_t)(k * b_kstep), idesc, (kb | k) != 0 ? 1u : 0u);
@@ -260,7 +289,7 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
           }
           if (++stage == S) { stage = 0; phase ^= 1; }
         }
-        if (elect_one()) umma_commit(tfull_bar(acc));      // accumulator complete -> epilogue
+        if (elect_one()) { if constexpr (kPair) umma_commit_pair(tfull_bar(acc)); else umma_commit(tfull_bar(acc)); }   // accumulator complete -> epilogue
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
@@ -276,7 +305,7 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
     int acc = 0; uint32_t acc_phase = 0;
     int buf = 0;
     const uint32_t swz = (uint32_t)(r & 7);
-    for (int t = blockIdx.x; t < p.tiles_total; t += gridDim.x) {
+    for (int t = t_first; t < p.tiles_total; t += t_step) {
       const TileCoord c = decode_tile(p, t);
       int cx, cy, cn, img;
       if (p.a_major == 0) {
@@ -360,12 +389,12 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
     int acc = 0; uint32_t acc_phase = 0;
     int buf = 0; uint32_t rphase0 = 0, rphase1 = 0;
     const uint32_t swz = (uint32_t)(r & 7);
-    for (int t = blockIdx.x; t < p.tiles_total; t += gridDim.x) {
+    for (int t = t_first; t < p.tiles_total; t += t_step) {
       const TileCoord c = decode_tile(p, t);
       int cx, cy, cn, img;
       if (p.a_major == 0) {
-        cx = c.x0; cy = c.y0; cn = c.n0 ^ p.o_xor;
-        img = c.n0 + r / (p.bw * p.bh);
+        cx = c.x0 + half_x; cy = c.y0 + half_y; cn = (c.n0 + half_n) ^ p.o_xor;
+        img = c.n0 + half_n + r / (p.bw * p.bh);
         if (img >= p.N) img = p.N - 1;
       } else {
         cx = c.m0; cy = c.y0; cn = c.n0 ^ p.o_xor; img = c.n0;
@@ -471,10 +500,13 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
             }
           }
         }
-        if (rd == rounds - 1) {          // accumulator(s) fully read: hand the TMEM buffer back to the MMA warp
+        if (rd == rounds - 1) {          // accumulator(s) fully read: hand the TMEM buffer back to the (leader's) MMA warp
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(tempty_bar(acc));
+          if (lane == 0) {
+            if constexpr (kPair) mbar_arrive_cluster(mapa_shared(tempty_bar(acc), 0u));
+            else mbar_arrive(tempty_bar(acc));
+          }
         }
         fence_proxy_async();
         epi_bar_sync();
@@ -493,7 +525,7 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
     const int quad = warp & 3;  // TMEM lane quadrant this warp may access
     const int r = quad * 32 + lane;
     int acc = 0; uint32_t acc_phase = 0;
-    for (int t = blockIdx.x; t < p.tiles_total; t += gridDim.x) {
+    for (int t = t_first; t < p.tiles_total; t += t_step) {
       const TileCoord c = decode_tile(p, t);
       bool row_ok;
       long long off;
@@ -603,9 +635,11 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
 
   tc_fence_before();
   __syncthreads();
+  if constexpr (kPair) cluster_sync_all();     // neither CTA of a pair frees TMEM or exits while the other may still signal it
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, (uint32_t)p.tmem_cols);
+    if constexpr (kPair) tmem_dealloc2(tmem_base, (uint32_t)p.tmem_cols);
+    else tmem_dealloc(tmem_base, (uint32_t)p.tmem_cols);
   }
 }
 
@@ -727,6 +761,34 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
       if (tiles >= 2LL * b3d_num_sms()) { p.m2 = 1; p.m2_dim = dim; m2_bw = tbw; m2_bh = tbh; m2_bnn = tbnn; p.a_bytes = 2 * kABytes; }
     }
   }
+  // CTA pairs (cta_group::2): the same 256-row tile, but its halves live in the two CTAs of a cluster and ONE M = 256 MMA
+  // reads A from both and half of the B tile from each -- per SM half the B shared-memory traffic of a single-CTA tile
+  // (the 128 B/clk shared-memory read port is what keeps a lone CTA's M = 128 MMAs below the tensor pipe's rate).
+  // Measured (B200, batch 128): +7.6% on the 256 -> 256 convolutions (1.43 -> 1.54 PFLOP/s), +2% on the FiLM GEMM; for
+  // BN = 128 the single-CTA 256-row tile above is faster (1.12 vs 0.99 PFLOP/s) and the dual-output epilogue loses 5%,
+  // so pairs are used for full-width tiles with one output.  B3D_NO_C2=1 turns them off (measurement switch).
+  static const bool use_c2 = getenv("B3D_NO_C2") == nullptr;
+  if (use_c2 && d->a_major == 0 && d->b_major == 0 && !d->batched && s == 1 && p.epi_tma && !d->out_fp32 && BN == 256 &&
+      d->out2 == nullptr && b3d_num_sms() % 2 == 0) {
+    const int bw = d->W < BM ? d->W : BM;
+    int bh = BM / bw; if (bh > d->H) bh = d->H; if (bh < 1) bh = 1;
+    int bnn = (bh == d->H) ? BM / (bw * bh) : 1; if (bnn > d->N) bnn = d->N; if (bnn < 1) bnn = 1;
+    int dim = -1;
+    if (bw * bh * bnn == BM) {
+      if (bh < d->H) dim = 1;
+      else if (2 * bnn <= d->N) dim = 2;
+      else if (d->H == 1 && d->N == 1 && d->W >= 2 * BM) dim = 0;
+    }
+    if (dim >= 0) {
+      const int tbw = dim == 0 ? 2 * bw : bw, tbh = dim == 1 ? 2 * bh : bh, tbnn = dim == 2 ? 2 * bnn : bnn;
+      const long long tiles = (long long)((d->W + tbw - 1) / tbw) * ((d->H + tbh - 1) / tbh) * ((d->N + tbnn - 1) / tbnn) * p.tiles_n;
+      if (tiles >= (long long)b3d_num_sms()) {      // >= 2 tiles per pair
+        p.c2 = 1; p.m2 = 0; p.m2_dim = dim; m2_bw = tbw; m2_bh = tbh; m2_bnn = tbnn; p.a_bytes = kABytes;
+        p.b_bytes = (uint32_t)((BN / 2 * 128 + 1023) / 1024 * 1024);
+        p.b_tx = (uint32_t)(BN / 2) * 128u;
+      }
+    }
+  }
   p.stage_bytes = p.a_bytes + p.b_bytes;
   p.num_stages = (int)((kMaxDynSmem - 1024 - epi_bytes) / p.stage_bytes);
   if (p.num_stages > 8) p.num_stages = 8;
@@ -738,7 +800,7 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
   if (p.tmem_cols < 32) p.tmem_cols = 32;
   // instruction descriptor: D fp32 (bit 4), A/B bf16 (bits 7,10), majors (15,16), N>>3 at 17, M>>4 at 24
   p.idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)d->a_major << 15) | ((uint32_t)d->b_major << 16) | ((uint32_t)(BN >> 3) << 17) |
-            ((uint32_t)(BM >> 4) << 24);
+            ((uint32_t)((p.c2 ? 2 * BM : BM) >> 4) << 24);
 
   const uint32_t ones[4] = {1, 1, 1, 1};
   int rc;
@@ -749,14 +811,15 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
       p.bh = BM / p.bw; if (p.bh > d->H) p.bh = d->H; if (p.bh < 1) p.bh = 1;
       p.bnn = (p.bh == d->H) ? BM / (p.bw * p.bh) : 1; if (p.bnn > d->N) p.bnn = d->N; if (p.bnn < 1) p.bnn = 1;
     }
-    p.tbw = p.m2 ? m2_bw : p.bw; p.tbh = p.m2 ? m2_bh : p.bh; p.tbnn = p.m2 ? m2_bnn : p.bnn;
+    p.tbw = (p.m2 || p.c2) ? m2_bw : p.bw; p.tbh = (p.m2 || p.c2) ? m2_bh : p.bh; p.tbnn = (p.m2 || p.c2) ? m2_bnn : p.bnn;
     p.tiles_x = (d->W + p.tbw - 1) / p.tbw;
     p.tiles_y = (d->H + p.tbh - 1) / p.tbh;
     const int tiles_img = (d->N + p.tbnn - 1) / p.tbnn;
     p.tiles_m = p.tiles_x * p.tiles_y * tiles_img;
     p.tiles_b = 1; p.tiles_z = 1;
-    p.a_tx = (uint32_t)(p.tbw * p.tbh * p.tbnn) * 128u;
-    const uint32_t boxA[4] = {64, (uint32_t)((p.tbw - 1) * s + 1), (uint32_t)((p.tbh - 1) * s + 1), (uint32_t)p.tbnn};
+    const int abw = p.c2 ? p.bw : p.tbw, abh = p.c2 ? p.bh : p.tbh, abn = p.c2 ? p.bnn : p.tbnn;   // rows one CTA loads
+    p.a_tx = (uint32_t)(abw * abh * abn) * 128u;
+    const uint32_t boxA[4] = {64, (uint32_t)((abw - 1) * s + 1), (uint32_t)((abh - 1) * s + 1), (uint32_t)abn};
     const uint32_t esA[4] = {1, (uint32_t)s, (uint32_t)s, 1};
     if (d->b_major == 0) {
       B3D_CHECK_ARG(d->n_src >= 1 && d->n_src <= 3, "b3d_gemm: n_src");
@@ -775,7 +838,7 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
         }
       }
       B3D_CHECK_ARG(bk <= d->b.dim[0] + BK - 1, "b3d_gemm: B has K=%d but A enumerates %d", d->b.dim[0], bk);
-      const uint32_t boxB[4] = {64, (uint32_t)BN, 1, 1};
+      const uint32_t boxB[4] = {64, (uint32_t)(p.c2 ? BN / 2 : BN), 1, 1};
       rc = make_map(&p.tmB, d->b, boxB, ones); if (rc) return rc;
     } else {
       B3D_CHECK_ARG(d->batched && s == 1, "b3d_gemm: (a_major=0,b_major=1) is the batched attention form");
@@ -841,11 +904,17 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
   const size_t smem = (size_t)p.num_stages * p.stage_bytes + epi_bytes + 1024;
   static bool attr_set = false;
   if (!attr_set) {
-    B3D_CUDA(cudaFuncSetAttribute(b3d_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem));
+    B3D_CUDA(cudaFuncSetAttribute(b3d_gemm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem));
+    B3D_CUDA(cudaFuncSetAttribute(b3d_gemm_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem));
     attr_set = true;
   }
   int grid = p.tiles_total < b3d_num_sms() ? p.tiles_total : b3d_num_sms();
-  B3D_CUDA(b3d_launch_pdl(b3d_gemm_kernel, dim3(grid), dim3(kThreads), smem, stream, p));
+  if (p.c2) {
+    const int pairs = p.tiles_total < b3d_num_sms() / 2 ? p.tiles_total : b3d_num_sms() / 2;
+    grid = 2 * pairs;
+  }
+  if (p.c2) B3D_CUDA(b3d_launch_cluster_pdl(b3d_gemm_kernel<true>, dim3(grid), dim3(kThreads), smem, stream, 2, p));
+  else B3D_CUDA(b3d_launch_pdl(b3d_gemm_kernel<false>, dim3(grid), dim3(kThreads), smem, stream, p));
   B3D_LAUNCH_CHECK();
   b3d_count_launch(1);
   return B3D_OK;

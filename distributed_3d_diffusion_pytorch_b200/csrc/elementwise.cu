@@ -275,6 +275,54 @@ __global__ void silu_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restr
     reinterpret_cast<bf16x8*>(dx)[i] = b3d_pack8(a);
   }
 }
+// dx = dy * silu'(x) over contiguous [rows, C] AND, from the same pass, the column sums of dx per group of rows_per_group
+// rows (group_out[g, c] +=, e.g. d(logsnr embedding) per image) and over all rows (total_out[c] +=, the bias gradient of
+// the layer that produced x).  Replaces silu_bwd + two colsum passes over the 1024-channel conditioning tensors.
+__global__ void __launch_bounds__(256) silu_bwd_colsum_kernel(const bf16* dy, const bf16* __restrict__ x, bf16* dx, int C, long long rows_per_group,
+                                                              int rows_per_block, float* __restrict__ group_out, long long group_ld,
+                                                              float* __restrict__ total_out) {
+  b3d_pdl_sync();
+  extern __shared__ float sm[];   // [rows_par, C]
+  constexpr int U = 4;
+  const int vecs = C / 8, g = blockIdx.y;
+  const int rows_par = max(1, (int)blockDim.x / vecs);
+  const int v = threadIdx.x % vecs, rsub = threadIdx.x / vecs;
+  const long long r0 = (long long)blockIdx.x * rows_per_block, r1 = min(rows_per_group, r0 + rows_per_block);
+  const long long base = (long long)g * rows_per_group * C + v * 8;
+  float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  if (rsub < rows_par) {
+    for (long long r = r0 + rsub; r < r1; r += (long long)rows_par * U) {
+      bf16x8 a[U], b[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long rr = r + (long long)u * rows_par;
+        if (rr < r1) {
+          a[u].u = reinterpret_cast<const bf16x8*>(dy + base + rr * C)->u;
+          b[u].u = reinterpret_cast<const bf16x8*>(x + base + rr * C)->u;
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long rr = r + (long long)u * rows_par;
+        if (rr >= r1) break;
+        float f[8], z[8];
+        b3d_unpack8(a[u], f); b3d_unpack8(b[u], z);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { f[j] *= b3d_silu_grad(z[j]); acc[j] += f[j]; }
+        *reinterpret_cast<bf16x8*>(dx + base + rr * C) = b3d_pack8(f);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) sm[rsub * C + v * 8 + j] = acc[j];
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float s_ = 0.f;
+    for (int r = 0; r < rows_par; ++r) s_ += sm[r * C + c];
+    if (group_out) atomicAdd(group_out + (long long)g * group_ld + c, s_);
+    if (total_out) atomicAdd(total_out + c, s_);
+  }
+}
 // out = scale * (a + b)   (b optional)
 __global__ void add_scale_kernel(const bf16* __restrict__ a, const bf16* __restrict__ b, bf16* __restrict__ out, float scale, long long nvec) {
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nvec; i += (long long)gridDim.x * blockDim.x) {
@@ -793,6 +841,21 @@ extern "C" int b3d_upsample2(const void* in, void* out, int N, int Ho, int Wo, i
 extern "C" int b3d_silu_bwd(const void* dy, const void* x, void* dx, int64_t n, void* stream) {
   B3D_CHECK_ARG(n % 8 == 0, "silu_bwd: n%%8");
   B3D_CUDA(b3d_launch_pdl(silu_bwd_kernel, dim3(grid_for(n / 8)), dim3(kT), 0, STREAM, (const bf16*)dy, (const bf16*)x, (bf16*)dx, n / 8));
+  DONE(1);
+}
+extern "C" int b3d_silu_bwd_colsum(const void* dy, const void* x, void* dx, int C, int64_t rows_per_group, int groups, float* group_out,
+                                   int64_t group_ld, float* total_out, void* stream) {
+  B3D_CHECK_ARG(dy && x && dx && C % 8 == 0 && C <= 2048 && rows_per_group > 0 && groups > 0, "silu_bwd_colsum: args (C %% 8, C <= 2048)");
+  const int rows_par = 256 / (C / 8) > 0 ? 256 / (C / 8) : 1;
+  const int min_rows = rows_par * 4;
+  long long rpb = cdiv(rows_per_group * groups, 148LL * 8);
+  const long long amort = cdiv(32768, C);
+  if (rpb < amort) rpb = amort;
+  if (rpb < min_rows) rpb = min_rows;
+  rpb = (rpb + min_rows - 1) / min_rows * min_rows;
+  dim3 grid((unsigned)cdiv(rows_per_group, rpb), groups);
+  B3D_CUDA(b3d_launch_pdl(silu_bwd_colsum_kernel, grid, dim3(256), (size_t)rows_par * C * sizeof(float), STREAM, (const bf16*)dy, (const bf16*)x,
+                          (bf16*)dx, C, (long long)rows_per_group, (int)rpb, group_out, (long long)group_ld, total_out));
   DONE(1);
 }
 extern "C" int b3d_add_scale(const void* a, const void* b, void* out, float scale, int64_t n, void* stream) {

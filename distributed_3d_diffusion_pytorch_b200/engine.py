@@ -527,13 +527,12 @@ class Engine:
             pre = self._bufs[f"emb_pre{l}"]
             de = self.buf(f"de{l}", (N, hh, ww, E))
             ops.gemm(G.dense_desc(dss[l], Wp[f"film{l}.T"], de.view(M, E), E))
-            ops.silu_bwd(de, pre, de)
+            # silu'(pre) and, from the same pass, d(logsnr_emb) per image and the conv's bias gradient
+            ops.silu_bwd_colsum(de, pre, de, hh * ww, dlemb, Gr[cp + f"convs.{l}.bias"])
             with ops.side():
-                ops.colsum(de.view(M, E), M, Gr[cp + f"convs.{l}.bias"])
                 gp = self.zbuf("bwd", f"cc{l}.gp", (E, 9 * 192))
                 ops.gemm(G.wgrad_desc(de, pe, 9, gp, 0, 192, 2 ** l))
                 self._unpack(gp, 0, 192, Gr[cp + f"convs.{l}.weight"])
-            ops.colsum(de.view(M, E), hh * ww, dlemb)
             if cfg.use_pos_emb or cfg.use_ref_pose_emb:
                 des = self.buf(f"desum{l}", (2, hh, ww, E))
                 ops.batch_frame_sum(de, des)

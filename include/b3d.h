@@ -139,6 +139,11 @@ int b3d_avgpool2(const void* in, void* out, int N, int H, int W, int C, float sc
 int b3d_upsample2(const void* in, void* out, int N, int Ho, int Wo, int C, float scale, void* stream);
 /* dx = dy * silu'(x)  (autograd of F.silu, xunet.py:84) ; out = scale*(a+b) */
 int b3d_silu_bwd(const void* dy, const void* x, void* dx, int64_t n, void* stream);
+/* dx = dy * silu'(x) over contiguous [rows, C] plus, from the same pass, the column sums of dx per group of rows
+ * (group_out[g*group_ld + c] +=, may be null) and over all rows (total_out[c] +=, may be null); fp32, pre-zeroed by the caller.
+ * Autograd of F.silu(emb) (xunet.py:84) fused with d(logsnr_emb) (xunet.py:502) and the conditioning conv's bias gradient. */
+int b3d_silu_bwd_colsum(const void* dy, const void* x, void* dx, int C, int64_t rows_per_group, int groups, float* group_out,
+                        int64_t group_ld, float* total_out, void* stream);
 int b3d_add_scale(const void* a, const void* b, void* out, float scale, int64_t n, void* stream);
 /* out[g,c] += sum of rows of group g (bias gradients; d logsnr_emb per image, xunet.py:502); out fp32, pre-zeroed */
 int b3d_colsum(const void* in, int64_t ld, int C, int64_t rows_per_group, int groups, float* out, int64_t out_ld, void* stream);

@@ -323,6 +323,15 @@ class EmuOps:
     def silu_bwd(self, dy, x, dx):
         dx.copy_((dy.float() * _silu_grad(x.float())).to(dx.dtype))
 
+    def silu_bwd_colsum(self, dy, x, dx, rows_per_group, group_out, total_out):
+        C = dy.shape[-1]
+        v = (dy.float() * _silu_grad(x.float())).reshape(-1, rows_per_group, C)
+        dx.copy_(v.reshape(dx.shape).to(dx.dtype))
+        if group_out is not None:
+            group_out[:, :C].add_(v.sum(1))
+        if total_out is not None:
+            total_out[:C].add_(v.sum((0, 1)))
+
     def add_scale(self, a, b, out, scale):
         v = a.float() + (b.float() if b is not None else 0)
         out.copy_((v * scale).to(out.dtype))

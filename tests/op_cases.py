@@ -133,6 +133,11 @@ def misc_case(seed=0):
         # elementwise
         a, b = _mk(ops, _r((64, 128), g)), _mk(ops, _r((64, 128), g))
         sb = ops.zeros((64, 128)); ops.silu_bwd(a, b, sb); outs.append(sb)
+        # silu backward fused with per-group and total column sums (in place, ragged row count per block)
+        fd, fx = _mk(ops, _r((6 * 50, 1024), g)), _mk(ops, _r((6 * 50, 1024), g, 2.0))
+        fgo, fto = ops.zeros((6, 1024), torch.float32), ops.zeros((1024,), torch.float32)
+        ops.silu_bwd_colsum(fd, fx, fd, 50, fgo, fto)
+        outs += [fd, fgo, fto]
         ad = ops.zeros((64, 128)); ops.add_scale(a, b, ad, 0.7071); outs.append(ad)
         ad2 = ops.zeros((64, 128)); ops.add_scale(a, None, ad2, 0.5); outs.append(ad2)
         cs = ops.zeros((4, 96), torch.float32)

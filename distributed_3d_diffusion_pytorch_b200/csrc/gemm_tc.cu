@@ -768,8 +768,11 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
   // BN = 128 the single-CTA 256-row tile above is faster (1.12 vs 0.99 PFLOP/s) and the dual-output epilogue loses 5%,
   // so pairs are used for full-width tiles with one output.  B3D_NO_C2=1 turns them off (measurement switch).
   static const bool use_c2 = getenv("B3D_NO_C2") == nullptr;
+  int c2_kblocks = 0;       // K blocks per tile: short reductions (the K = 256 / 512 dense layers of the attention blocks) lose to
+  if (d->a_major == 0 && d->b_major == 0)   // the pair's extra synchronisation (23.5 -> 26.3 us at [65536,256]x[256,256])
+    for (int i = 0; i < d->n_src && i < 3; ++i) c2_kblocks += (d->a_taps[i] == 9 ? 9 : 1) * ((d->a[i].dim[0] + BK - 1) / BK);
   if (use_c2 && d->a_major == 0 && d->b_major == 0 && !d->batched && s == 1 && p.epi_tma && !d->out_fp32 && BN == 256 &&
-      d->out2 == nullptr && b3d_num_sms() % 2 == 0) {
+      d->out2 == nullptr && c2_kblocks >= 16 && b3d_num_sms() % 2 == 0) {
     const int bw = d->W < BM ? d->W : BM;
     int bh = BM / bw; if (bh > d->H) bh = d->H; if (bh < 1) bh = 1;
     int bnn = (bh == d->H) ? BM / (bw * bh) : 1; if (bnn > d->N) bnn = d->N; if (bnn < 1) bnn = 1;

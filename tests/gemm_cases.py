@@ -158,12 +158,12 @@ def all_cases():
         conv_case("conv_m2_1x1_two_src_64x64", 19, 64, 64, [64, 32], [1, 1], 128, seed=14),
         dense_case("dense_m2_76000x192x128", 76000, 192, 128, seed=15),
         dense_case("dense_m2_80001x64x72_silu", 80001, 64, 72, act=1, seed=16),
-        # CTA pairs (cta_group::2, M = 256 across two CTAs): full-width tiles (BN = 256) with >= 2 tiles per pair
-        conv_case("conv_pair_rows_32x32_c64_256_resid", 160, 32, 32, [64], [9], 256, resid=True, out_scale=0.70710678, seed=21),
-        conv_case("conv_pair_images_8x8_c64_512_rowvec", 1300, 8, 8, [64], [9], 512, rowvec=True, seed=22),
-        conv_case("conv_pair_two_src_1x1_20x20", 210, 20, 20, [64, 32], [1, 1], 256, act=1, seed=23),
-        dense_case("dense_pair_80001x128x256", 80001, 128, 256, seed=24),
-        dense_case("dense_pair_40000x64x768", 40000, 64, 768, seed=25),
+        # CTA pairs (cta_group::2, M = 256 across two CTAs): full-width tiles (BN = 256), >= 16 K blocks, >= 2 tiles per pair
+        conv_case("conv_pair_rows_32x32_c128_256_resid", 160, 32, 32, [128], [9], 256, resid=True, out_scale=0.70710678, seed=21),
+        conv_case("conv_pair_images_8x8_c128_512_rowvec", 1300, 8, 8, [128], [9], 512, rowvec=True, seed=22),
+        conv_case("conv_pair_two_src_1x1_20x20", 210, 20, 20, [640, 416], [1, 1], 256, act=1, seed=23),
+        dense_case("dense_pair_80001x1024x256", 80001, 1024, 256, seed=24),
+        dense_case("dense_pair_40000x1088x768", 40000, 1088, 768, seed=25),
         conv_case("conv_16x16_c64_128", 2, 16, 16, [64], [9], 128),
         conv_case("conv_64x64_c128_128_resid", 2, 64, 64, [128], [9], 128, resid=True, out_scale=0.70710678),
         conv_case("conv_8x8_c512_512", 4, 8, 8, [512], [9], 512),

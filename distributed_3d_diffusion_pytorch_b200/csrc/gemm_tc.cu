@@ -26,7 +26,7 @@ constexpr int BK = 64;  // bf16 elements = one 128-byte swizzle row
 constexpr int kThreads = 192;
 constexpr int kMaxSeg = 27;
 constexpr uint32_t kABytes = BM * BK * 2;  // 16 KB in both majors
-constexpr int kMaxDynSmem = 227 * 1024 - 1024;  // 227 KB per CTA minus the static barriers
+constexpr int kMaxDynSmem = 227 * 1024 - 2048;  // 227 KB per CTA minus the static barriers and bias slice
 
 struct Seg {
   int32_t src, dx, dy, ncb, bk0;
@@ -121,6 +121,7 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t bars[2 * 8 + 4 + 2];
   __shared__ uint32_t tmem_base_smem;
+  __shared__ __align__(16) float s_bias[256];   // bias slice of the current N tile (bf16 TMA epilogue)
 
   // warp index through a shuffle so the compiler knows it is warp-uniform: the producer and MMA loops below then run on
   // uniform registers (a `lane == 0` region made every TMA / MMA operand go through an ELECT + R2UR.BROADCAST loop, and
@@ -388,6 +389,7 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
     const uint32_t rows_bytes = p.a_major == 0 ? (uint32_t)(p.bw * p.bh * p.bnn) * 128u : 128u * 128u;
     int acc = 0; uint32_t acc_phase = 0;
     int buf = 0; uint32_t rphase0 = 0, rphase1 = 0;
+    int bias_tn = -1;
     const uint32_t swz = (uint32_t)(r & 7);
     for (int t = t_first; t < p.tiles_total; t += t_step) {
       const TileCoord c = decode_tile(p, t);
@@ -401,6 +403,12 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
       }
       const int nch = (min(p.BN, p.n_cols - c.tn * p.BN) + 63) / 64;
       const int rounds = (1 + p.m2) * nch;      // (accumulator half, 64-column chunk), half-major
+      if (p.bias && c.tn != bias_tn) {            // stage this N tile's bias slice in shared memory (zeros past n_cols): the
+        epi_bar_sync();                           // per-round __ldg's of it sat on the critical path of short-K tiles
+        for (int i = r; i < 256; i += 128) s_bias[i] = (i < p.BN && c.tn * p.BN + i < p.n_cols) ? __ldg(p.bias + c.tn * p.BN + i) : 0.f;
+        bias_tn = c.tn;
+        epi_bar_sync();
+      }
       // output-box origin of a half: the second 128 rows of a doubled tile continue along m2_dim (x / y / image)
       const int cx0 = cx, cy0 = cy, cn0 = cn, img0 = img;
       const int hx = p.m2_dim == 0 ? p.bw : 0, hy = p.m2_dim == 1 ? p.bh : 0, hn = p.m2_dim == 2 ? p.bnn : 0;
@@ -444,15 +452,11 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
           for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]) * p.alpha;
           const bool full = cc + 32 <= p.n_cols;
           if (p.bias) {
-            if (full) {
+            const float4* sb4 = reinterpret_cast<const float4*>(s_bias + ch * 64 + hf * 32);     // broadcast reads
 #pragma unroll
-              for (int g = 0; g < 8; ++g) {
-                const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + cc) + g);
-                f[4 * g] += b4.x; f[4 * g + 1] += b4.y; f[4 * g + 2] += b4.z; f[4 * g + 3] += b4.w;
-              }
-            } else {
-#pragma unroll
-              for (int i = 0; i < 32; ++i) if (cc + i < p.n_cols) f[i] += __ldg(p.bias + cc + i);
+            for (int g = 0; g < 8; ++g) {
+              const float4 b4 = sb4[g];
+              f[4 * g] += b4.x; f[4 * g + 1] += b4.y; f[4 * g + 2] += b4.z; f[4 * g + 3] += b4.w;
             }
           }
           if (p.rowvec) {

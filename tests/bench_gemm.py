@@ -22,6 +22,7 @@ CASES = [
     ("wgrad conv 128x(9x128) over 1M pixels", gc.wgrad_case("w", 256, 64, 64, 128, 128, 9)),
     ("wgrad conv 256x(9x256) over 262k pixels", gc.wgrad_case("w", 256, 32, 32, 256, 256, 9)),
     ("wgrad FiLM 256x1024 over 1M pixels", gc.wgrad_case("w", 1, 1, 1048576, 256, 1024, 1)),
+    ("attention-block dense [65536,256]x[256,256]", gc.dense_case("d", 65536, 256, 256)),
 ]
 
 

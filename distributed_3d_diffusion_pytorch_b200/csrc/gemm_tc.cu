@@ -2,13 +2,16 @@
 // the X-UNet (3x3/1x1 convolutions as implicit GEMM, FiLM / linear layers, attention matmuls),
 // forward, data-gradient and weight-gradient.
 //
-//   warp 0 (one lane)  TMA producer : 4-D tiled tensor maps, SWIZZLE_128B, zero fill out of bounds
-//                                      (3x3 halo = shifted box coordinates, strided conv = traversal
-//                                      strides; no im2col buffer ever exists)
-//   warp 1 (one lane)  MMA issuer   : tcgen05.mma cta_group::1 kind::f16, M=128, N=16..256, K=16,
-//                                      bf16 x bf16 -> fp32 accumulators in TMEM (double buffered)
-//   warps 2..5         epilogue     : tcgen05.ld 32x32b.x32 -> registers -> bias / per-image vector /
-//                                      residual / scale / SiLU -> bf16 or fp32 (optionally atomic) stores
+//   warp 0  TMA producer : 4-D tiled tensor maps, SWIZZLE_128B, zero fill out of bounds (3x3 halo = shifted box
+//                          coordinates, strided conv = traversal strides; no im2col buffer ever exists)
+//   warp 1  MMA issuer   : tcgen05.mma kind::f16, M = 128 (cta_group::1) or 256 across a CTA pair (cta_group::2),
+//                          N = 16..256, K = 16, bf16 x bf16 -> fp32 accumulators in TMEM (double buffered)
+//   warps 2..5 epilogue  : tcgen05.ld 32x32b.x32 -> registers -> bias / per-image vector / residual / scale / SiLU ->
+//                          swizzled smem tile -> TMA store (bf16, fp32) or TMA reduce-add (split-K weight gradients)
+//   Warps 0 and 1 run warp-uniform loops; one elected lane issues the TMA / MMA instructions.
+//
+// Tile shapes: 128 x BN; 256 x BN with two accumulators per B tile (BN <= 128); 256 x 256 over a CTA pair; weight-gradient
+// tiles spanning several taps of a narrow layer.  b3d_gemm() picks per launch (see the comments there).
 //
 // Operands may be K-major (K = channels, contiguous) or MN-major (K = pixels); see include/b3d.h.
 #include <cuda.h>
@@ -665,7 +668,11 @@ int choose_bn(int n_cols, int b_major, long long tiles_other) {
   // a half-empty GPU costs more than the lower MMA/shared-memory efficiency of a narrower tile
   const long long sms = b3d_num_sms();
   // (tiles stay multiples of 64 columns: the TMA-store epilogue writes 64-column boxes)
-  while (best >= 128 && (best / 2) % 64 == 0 && tiles_other * ((n_cols + best - 1) / best) < sms) best /= 2;
+  // -- but only while the narrower tiles still fit ONE wave: crossing the SM count turns one wave of wide tiles into two
+  // of narrow ones (measured, 32 images of 8x8, 1024 -> 1024: 128-wide 32 us, 64-wide 51 us, 256-wide 48 us)
+  while (best >= 128 && (best / 2) % 64 == 0 && tiles_other * ((n_cols + best - 1) / best) < sms &&
+         tiles_other * ((n_cols + best / 2 - 1) / (best / 2)) <= sms)
+    best /= 2;
   (void)b_major;
   return best;
 }

@@ -25,6 +25,12 @@ constexpr uint32_t kPBytes = 65536;               // P tile 128 x 256 bf16 = 4 c
 constexpr int kThreads = 192;
 constexpr uint32_t kTmemS = 0, kTmemO = 256;
 
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 struct alignas(64) AP {
   CUtensorMap tmQ, tmK, tmV, tmO, tmP;
   int N, L, Lb, heads, d, cross, qtiles, items, write_p;
@@ -134,22 +140,20 @@ __global__ void __launch_bounds__(kThreads, 1) attn_fwd_kernel(const __grid_cons
         for (int i = 0; i < 32; ++i) if (c * 32 + i < p.L) m = fmaxf(m, __uint_as_float(v[i]));
       }
       const float mb = m * p.scale_log2e;
-      float l = 0.f;
-      for (int c = 0; c < nch32; ++c) {
-        uint32_t v[32];
-        tmem_ld32(tmem_base + kTmemS + lane_addr + c * 32, v);
-#pragma unroll
-        for (int i = 0; i < 32; ++i) if (c * 32 + i < p.L) l += exp2f(__uint_as_float(v[i]) * p.scale_log2e - mb);
-      }
-      const float inv_l = 1.f / l;
       if (leader) tma_store_wait_read<0>();             // previous item's O / P stores have finished reading the tile
       epi_bar_sync();
+      // second sweep: e = 2^(s*scale*log2e - mb) ONCE per element (one MUFU.EX2; exp2f()'s range handling and a second
+      // exponential pass made this loop the kernel's bottleneck), written unnormalised as bf16 into the P tile, row sum in fp32
+      float l = 0.f;
       for (int c = 0; c < 2 * kch; ++c) {               // all 64-key chunks the PV MMAs will read (keys >= L are zero)
         uint32_t v[32];
         if (c < nch32) tmem_ld32(tmem_base + kTmemS + lane_addr + c * 32, v);
         float f[32];
 #pragma unroll
-        for (int i = 0; i < 32; ++i) f[i] = (c < nch32 && c * 32 + i < p.L) ? exp2f(__uint_as_float(v[i]) * p.scale_log2e - mb) * inv_l : 0.f;
+        for (int i = 0; i < 32; ++i) {
+          f[i] = (c < nch32 && c * 32 + i < p.L) ? ex2_approx(fmaf(__uint_as_float(v[i]), p.scale_log2e, -mb)) : 0.f;
+          l += f[i];
+        }
         const uint32_t row = p_base + (uint32_t)(c >> 1) * 16384u + (uint32_t)r * 128u;
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
@@ -157,6 +161,21 @@ __global__ void __launch_bounds__(kThreads, 1) attn_fwd_kernel(const __grid_cons
           q.x = pack_bf16x2(f[8 * g], f[8 * g + 1]); q.y = pack_bf16x2(f[8 * g + 2], f[8 * g + 3]);
           q.z = pack_bf16x2(f[8 * g + 4], f[8 * g + 5]); q.w = pack_bf16x2(f[8 * g + 6], f[8 * g + 7]);
           sts128(row + ((((uint32_t)((c & 1) * 4 + g)) ^ swz) << 4), q);
+        }
+      }
+      // third sweep, over shared memory only: normalise the row in place (each thread re-reads what it wrote)
+      const float inv_l = 1.f / l;
+      for (int c = 0; c < 2 * kch; ++c) {
+        const uint32_t row = p_base + (uint32_t)(c >> 1) * 16384u + (uint32_t)r * 128u;
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          const uint32_t a = row + ((((uint32_t)((c & 1) * 4 + g)) ^ swz) << 4);
+          uint4 q = lds128(a);
+          uint32_t* w = reinterpret_cast<uint32_t*>(&q);
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            w[i] = pack_bf16x2(__uint_as_float(w[i] << 16) * inv_l, __uint_as_float(w[i] & 0xffff0000u) * inv_l);
+          sts128(a, q);
         }
       }
       tc_fence_before();

@@ -27,10 +27,10 @@ using namespace b3d_tc;
 constexpr int kThreads = 192;
 
 struct alignas(64) BP {
-  CUtensorMap tmQ, tmK, tmV, tmDO, tmP;
+  CUtensorMap tmQ, tmK, tmV, tmDO, tmO, tmP;
   const bf16* o; const bf16* dout; bf16* dqkv;
   int N, L, Lb2, heads, d, C, cross, qtiles, items, dch, kch2;
-  uint32_t off_k, off_v, off_q, off_do, off_p;    // shared-memory offsets of the operand tiles
+  uint32_t off_k, off_v, off_q, off_do, off_o, off_p;    // shared-memory offsets of the operand tiles
   uint32_t col_k, col_v;                           // TMEM columns of the dK / dV accumulators (dP and dQ start at 0)
   float scale;
 };
@@ -62,7 +62,8 @@ __global__ void __launch_bounds__(kThreads, 1) attn_bwd_kernel(const __grid_cons
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_smem;
   b3d_pdl_sync();   // nothing above touches global memory
-  const uint32_t sK = smem_base + p.off_k, sV = smem_base + p.off_v, sQ = smem_base + p.off_q, sDO = smem_base + p.off_do, sP = smem_base + p.off_p;
+  const uint32_t sK = smem_base + p.off_k, sV = smem_base + p.off_v, sQ = smem_base + p.off_q, sDO = smem_base + p.off_do, sO = smem_base + p.off_o,
+                 sP = smem_base + p.off_p;
   const uint32_t kv_chunk = (uint32_t)p.Lb2 * 128u;      // bytes of one 64-wide head_dim chunk of K or V (all keys)
   const int halves = p.Lb2 / 128;
 
@@ -80,10 +81,11 @@ __global__ void __launch_bounds__(kThreads, 1) attn_bwd_kernel(const __grid_cons
               tma_load_4d(sV + j * kv_chunk, &p.tmV, kv_full, j * 64, 0, head, nk);
             }
           }
-          mbar_expect_tx(t_full, (uint32_t)(2 * p.dch + p.kch2) * 16384u);
+          mbar_expect_tx(t_full, (uint32_t)(3 * p.dch + p.kch2) * 16384u);
           for (int j = 0; j < p.dch; ++j) {
             tma_load_4d(sQ + j * 16384, &p.tmQ, t_full, j * 64, t * 128, head, n);
             tma_load_4d(sDO + j * 16384, &p.tmDO, t_full, j * 64, t * 128, head, n);
+            tma_load_4d(sO + j * 16384, &p.tmO, t_full, j * 64, t * 128, head, n);
           }
           for (int c = 0; c < p.kch2; ++c) tma_load_4d(sP + c * 16384, &p.tmP, t_full, c * 64, t * 128, head, n);
         }
@@ -144,12 +146,14 @@ __global__ void __launch_bounds__(kThreads, 1) attn_bwd_kernel(const __grid_cons
       for (int t = 0; t < p.qtiles; ++t, ++tiles) {
         const int q = t * 128 + r;
         const bool valid = q < p.L;
-        // D_i = dO_i . O_i (fp32), straight from global memory while the MMAs run
+        // D_i = dO_i . O_i (fp32) from the two tiles in shared memory (rows of 128 B, same swizzle, so 16-byte units pair up);
+        // reading them from global memory here put a full load latency on the serial chain of every tile
+        mbar_wait(t_full, tiles & 1);
         float D = 0.f;
-        if (valid) {
-          const uint4* po = reinterpret_cast<const uint4*>(p.o + ((long long)n * p.L + q) * p.C + head * p.d);
-          const uint4* pd = reinterpret_cast<const uint4*>(p.dout + ((long long)n * p.L + q) * p.C + head * p.d);
-          for (int i = 0; i < p.d / 8; ++i) D += dot8(__ldg(po + i), __ldg(pd + i));
+        for (int j = 0; j < p.dch; ++j) {
+          const uint32_t ro = sO + (uint32_t)j * 16384u + (uint32_t)r * 128u, rd = sDO + (uint32_t)j * 16384u + (uint32_t)r * 128u;
+#pragma unroll
+          for (int u = 0; u < 8; ++u) D += dot8(lds128(ro + ((((uint32_t)u) ^ swz) << 4)), lds128(rd + ((((uint32_t)u) ^ swz) << 4)));   // conflict-free order
         }
         mbar_wait(pre_full, tiles & 1);
         tc_fence_after();
@@ -247,7 +251,7 @@ extern "C" int b3d_attn_bwd_supported(int L, int d) {
   if (L < 1 || L > 256 || d < 16 || d > 128 || d % 16 != 0) return 0;
   const int Lb2 = (L + 127) / 128 * 128, halves = Lb2 / 128, dch = (d + 63) / 64;
   if (Lb2 + 2 * halves * d > 512 || d > Lb2) return 0;
-  const size_t smem = (size_t)2 * dch * Lb2 * 128 + (size_t)2 * dch * 16384 + (size_t)(Lb2 / 64) * 16384 + 1024;
+  const size_t smem = (size_t)2 * dch * Lb2 * 128 + (size_t)3 * dch * 16384 + (size_t)(Lb2 / 64) * 16384 + 1024;
   return smem <= 220 * 1024 ? 1 : 0;
 }
 
@@ -269,7 +273,7 @@ extern "C" int b3d_attn_bwd(const void* qkv, const void* probs, int64_t ld_probs
   p.dch = (d + 63) / 64; p.kch2 = p.Lb2 / 64;
   p.o = reinterpret_cast<const bf16*>(o); p.dout = reinterpret_cast<const bf16*>(dout); p.dqkv = reinterpret_cast<bf16*>(dqkv);
   const uint32_t kv_bytes = (uint32_t)p.dch * (uint32_t)p.Lb2 * 128u, qd_bytes = (uint32_t)p.dch * 16384u;
-  p.off_k = 0; p.off_v = kv_bytes; p.off_q = 2 * kv_bytes; p.off_do = p.off_q + qd_bytes; p.off_p = p.off_do + qd_bytes;
+  p.off_k = 0; p.off_v = kv_bytes; p.off_q = 2 * kv_bytes; p.off_do = p.off_q + qd_bytes; p.off_o = p.off_do + qd_bytes; p.off_p = p.off_o + qd_bytes;
   p.col_k = (uint32_t)p.Lb2; p.col_v = (uint32_t)(p.Lb2 + (p.Lb2 / 128) * d);
   const uint32_t ones[4] = {1, 1, 1, 1};
   b3d_view4 v;
@@ -285,6 +289,8 @@ extern "C" int b3d_attn_bwd(const void* qkv, const void* probs, int64_t ld_probs
   rc = make_map(&p.tmV, v, boxK, ones); if (rc) return rc;
   v.ptr = dout; v.stride[0] = C; v.stride[2] = (int64_t)L * C;
   rc = make_map(&p.tmDO, v, boxQ, ones); if (rc) return rc;
+  v.ptr = o;
+  rc = make_map(&p.tmO, v, boxQ, ones); if (rc) return rc;
   b3d_view4 pv;
   pv.ptr = probs; pv.dim[0] = L; pv.dim[1] = L; pv.dim[2] = heads; pv.dim[3] = N;
   pv.stride[0] = ld_probs; pv.stride[1] = (int64_t)L * ld_probs; pv.stride[2] = (int64_t)heads * L * ld_probs;

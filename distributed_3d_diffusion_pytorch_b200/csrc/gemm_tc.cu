@@ -162,8 +162,9 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
   // second half of the B tile's rows, rank 0 issues the M = 256 MMAs for both
   const uint32_t crank = kPair ? __shfl_sync(0xffffffffu, cluster_ctarank(), 0) : 0u;    // (shuffle: provably warp-uniform)
   const int t_first = kPair ? (int)(blockIdx.x >> 1) : (int)blockIdx.x, t_step = kPair ? (int)(gridDim.x >> 1) : (int)gridDim.x;
-  const int half_x = kPair && p.m2_dim == 0 ? (int)crank * p.bw : 0, half_y = kPair && p.m2_dim == 1 ? (int)crank * p.bh : 0,
-            half_n = kPair && p.m2_dim == 2 ? (int)crank * p.bnn : 0;
+  const int rstep = (int)crank * (p.m2 ? 2 : 1);      // boxes this CTA's rows start after (a CTA of a pair may itself hold two)
+  const int half_x = kPair && p.m2_dim == 0 ? rstep * p.bw : 0, half_y = kPair && p.m2_dim == 1 ? rstep * p.bh : 0,
+            half_n = kPair && p.m2_dim == 2 ? rstep * p.bnn : 0;
 
   if (warp == 0) {
     // ===================================================================== TMA producer
@@ -277,6 +278,12 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
 #pragma unroll
               for (int k = 0; k < BK / 16; ++k)
                 umma_bf16_pair(d_tmem, ad + (uint64_t)(k * a_kstep), bd + (uint64_t)(k * b_kstep), idesc, (kb | k) != 0 ? 1u : 0u);
+              if (p.m2) {                   // second 128 rows of each CTA's A tile, second accumulator
+#pragma unroll
+                for (int k = 0; k < BK / 16; ++k)
+                  umma_bf16_pair(d_tmem + p.acc_half, ad + (uint64_t)((kABytes >> 4) + k * a_kstep), bd + (uint64_t)(k * b_kstep), idesc,
+                                 (kb | k) != 0 ? 1u : 0u);
+              }
               umma_commit_pair(empty_bar(stage));
             }
           } else if (elect_one()) {
@@ -782,7 +789,10 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
   int c2_kblocks = 0;       // K blocks per tile: short reductions (the K = 256 / 512 dense layers of the attention blocks) lose to
   if (d->a_major == 0 && d->b_major == 0)   // the pair's extra synchronisation (23.5 -> 26.3 us at [65536,256]x[256,256])
     for (int i = 0; i < d->n_src && i < 3; ++i) c2_kblocks += (d->a_taps[i] == 9 ? 9 : 1) * ((d->a[i].dim[0] + BK - 1) / BK);
-  if (use_c2 && d->a_major == 0 && d->b_major == 0 && !d->batched && s == 1 && p.epi_tma && !d->out_fp32 && BN == 256 &&
+  // Narrow tiles (BN <= 128) combine both: each CTA of the pair keeps two accumulators (512 rows per pair tile).
+  static const bool use_c2m2 = getenv("B3D_NO_C2M2") == nullptr;
+  const bool pair_wide = BN == 256, pair_quad = use_c2m2 && BN <= 128 && BN % 32 == 0;
+  if (use_c2 && d->a_major == 0 && d->b_major == 0 && !d->batched && s == 1 && p.epi_tma && !d->out_fp32 && (pair_wide || pair_quad) &&
       d->out2 == nullptr && c2_kblocks >= 16 && b3d_num_sms() % 2 == 0) {
     const int bw = d->W < BM ? d->W : BM;
     int bh = BM / bw; if (bh > d->H) bh = d->H; if (bh < 1) bh = 1;
@@ -794,10 +804,12 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
       else if (d->H == 1 && d->N == 1 && d->W >= 2 * BM) dim = 0;
     }
     if (dim >= 0) {
-      const int tbw = dim == 0 ? 2 * bw : bw, tbh = dim == 1 ? 2 * bh : bh, tbnn = dim == 2 ? 2 * bnn : bnn;
+      const int mul = pair_wide ? 2 : 4;            // 128-row boxes per pair tile
+      const int tbw = dim == 0 ? mul * bw : bw, tbh = dim == 1 ? mul * bh : bh, tbnn = dim == 2 ? mul * bnn : bnn;
       const long long tiles = (long long)((d->W + tbw - 1) / tbw) * ((d->H + tbh - 1) / tbh) * ((d->N + tbnn - 1) / tbnn) * p.tiles_n;
-      if (tiles >= (long long)b3d_num_sms()) {      // >= 2 tiles per pair
-        p.c2 = 1; p.m2 = 0; p.m2_dim = dim; m2_bw = tbw; m2_bh = tbh; m2_bnn = tbnn; p.a_bytes = kABytes;
+      if (tiles >= (long long)b3d_num_sms() && (dim != 0 || tbw <= 512)) {      // >= 2 tiles per pair
+        p.c2 = 1; p.m2 = pair_wide ? 0 : 1; p.m2_dim = dim; m2_bw = tbw; m2_bh = tbh; m2_bnn = tbnn;
+        p.a_bytes = pair_wide ? kABytes : 2 * kABytes;
         p.b_bytes = (uint32_t)((BN / 2 * 128 + 1023) / 1024 * 1024);
         p.b_tx = (uint32_t)(BN / 2) * 128u;
       }
@@ -831,7 +843,9 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
     const int tiles_img = (d->N + p.tbnn - 1) / p.tbnn;
     p.tiles_m = p.tiles_x * p.tiles_y * tiles_img;
     p.tiles_b = 1; p.tiles_z = 1;
-    const int abw = p.c2 ? p.bw : p.tbw, abh = p.c2 ? p.bh : p.tbh, abn = p.c2 ? p.bnn : p.tbnn;   // rows one CTA loads
+    // rows one CTA loads: the whole tile, or its half of a pair tile
+    const int adiv = p.c2 ? 2 : 1;
+    const int abw = p.m2_dim == 0 ? p.tbw / adiv : p.tbw, abh = p.m2_dim == 1 ? p.tbh / adiv : p.tbh, abn = p.m2_dim == 2 ? p.tbnn / adiv : p.tbnn;
     p.a_tx = (uint32_t)(abw * abh * abn) * 128u;
     const uint32_t boxA[4] = {64, (uint32_t)((abw - 1) * s + 1), (uint32_t)((abh - 1) * s + 1), (uint32_t)abn};
     const uint32_t esA[4] = {1, (uint32_t)s, (uint32_t)s, 1};

@@ -164,6 +164,11 @@ def all_cases():
         conv_case("conv_pair_two_src_1x1_20x20", 210, 20, 20, [640, 416], [1, 1], 256, act=1, seed=23),
         dense_case("dense_pair_80001x1024x256", 80001, 1024, 256, seed=24),
         dense_case("dense_pair_40000x1088x768", 40000, 1088, 768, seed=25),
+        # CTA pairs whose CTAs keep two accumulators each (narrow tiles, 512 rows per pair tile)
+        conv_case("conv_pairquad_rows_64x64_c128_128_resid", 40, 64, 64, [128], [9], 128, resid=True, out_scale=0.70710678, seed=31),
+        conv_case("conv_pairquad_images_8x8_c128_64_rowvec", 2410, 8, 8, [128], [9], 64, rowvec=True, seed=32),
+        conv_case("conv_pairquad_rows_30x32_c256_96", 86, 30, 32, [256], [9], 96, act=1, seed=33),
+        dense_case("dense_pairquad_80001x1024x96", 80001, 1024, 96, seed=34),
         conv_case("conv_16x16_c64_128", 2, 16, 16, [64], [9], 128),
         conv_case("conv_64x64_c128_128_resid", 2, 64, 64, [128], [9], 128, resid=True, out_scale=0.70710678),
         conv_case("conv_8x8_c512_512", 4, 8, 8, [512], [9], 512),

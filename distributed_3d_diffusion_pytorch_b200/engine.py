@@ -106,6 +106,8 @@ class Engine:
         self.saved = None
         self._pack_cache = {}
         self._unpack_jl, self._copy_jl, self._unpack_sig, self._unpack_rec = None, None, None, False
+        # small batches: weight-gradient launches never block the data-gradient chain (see side_tmp)
+        self.defer_side = 2 * B * cfg.H * cfg.W <= 64 * 64 * 64
         self.seed_ptr = None      # optional int64 device scalar added to every dropout seed (see ops.gn_apply)
         for lvl in range(cfg.num_resolutions):
             assert cfg.H % (2 ** lvl) == 0 and cfg.W % (2 ** lvl) == 0
@@ -121,6 +123,18 @@ class Engine:
     def tmp(self, name, shape, dtype=None):
         """scratch reused by every block with the same shape (stream order makes the reuse safe)"""
         return self.buf(f"tmp.{name}:{tuple(shape)}", shape, dtype)
+
+    def side_tmp(self, block, name, shape, dtype=None):
+        """scratch that side-stream (weight-gradient) launches read.  Shared by every block of the same shape when the block
+        joins the side stream at its end; private to the block when the join is deferred to the end of the phase (small
+        batches: the main stream never waits for a weight gradient, at the price of one buffer per block)."""
+        if self.defer_side:
+            return self.buf(f"{block}.side.{name}", shape, dtype)
+        return self.tmp(name, shape, dtype)
+
+    def _block_join(self):
+        if not self.defer_side:
+            self.ops.join_side()
 
     def zbuf(self, phase, key, shape):
         """fp32 scratch that must be zero at the start of the phase: carved from one arena, one memset per phase"""
@@ -598,7 +612,7 @@ class Engine:
             ops.avgpool2(self._grad_of(sa["final"]), dout, 1.0)
         else:
             dout = self._grad_of(out)
-        gs = self.tmp("gs", (N, hh, ww, F))
+        gs = self.side_tmp(n, "gs", (N, hh, ww, F))
         ops.scale_colsum(dout, gs, RSQRT2, Gr[n + ".conv2.bias"])     # d(conv2.bias) = column sums of the scaled gradient
         gs2 = gs.view(M, F)
         # weight gradients of conv2 and the 1x1 skip: on the side stream, beside the data-gradient chain below (they only
@@ -635,7 +649,7 @@ class Engine:
         # GN1 + FiLM (+dropout)
         ssv = self.saved["ss"][s.lvl][:, s.film_off:s.film_off + 2 * F]
         dssv = dss_l[:, s.film_off:s.film_off + 2 * F]
-        dc1 = self.tmp("dc1", (N, hh, ww, F))
+        dc1 = self.side_tmp(n, "dc1", (N, hh, ww, F))
         ops.gn_bwd(sa["c1"].view(N, HW, F), None, sa["sums1"], P[n + ".groupnorm1.gn.weight"], P[n + ".groupnorm1.gn.bias"], 2,
                    da1.view(N, HW, F), Gr[n + ".groupnorm1.gn.weight"], Gr[n + ".groupnorm1.gn.bias"],
                    self.zbuf("bwd", n + ".ws1", (N, 32, 2)), dc1.view(N, HW, F), ss=ssv, F=F, dss=dssv, drop_p=drop_p, seed=sa["seed"],
@@ -660,7 +674,7 @@ class Engine:
         ops.gn_bwd(x0, x1, sa["sums0"], P[n + ".groupnorm0.gn.weight"], P[n + ".groupnorm0.gn.bias"], 1, da0.view(N, HW, s.cin),
                    Gr[n + ".groupnorm0.gn.weight"], Gr[n + ".groupnorm0.gn.bias"], self.zbuf("bwd", n + ".ws0", (N, 32, 2)), v3(g0), v3(g1),
                    add0=add0, add1a=v3(e0), add1b=v3(e1))
-        ops.join_side()
+        self._block_join()
 
     def _attn_bwd(self, s, P, Wp, Gr):
         ops, N, n, C = self.ops, self.N, s.name, s.c
@@ -672,13 +686,13 @@ class Engine:
         a = n + ".attn_layer.attn"
         alpha = 1.0 / math.sqrt(d)
         dout = self._grad_of(out)
-        gs4 = self.tmp("ags", (N, hh, ww, C))
+        gs4 = self.side_tmp(n, "ags", (N, hh, ww, C))
         ops.scale_colsum(dout, gs4, RSQRT2, Gr[n + ".linear.bias"])
         gs = gs4.view(M, C)
         # 1x1 `linear` and out_proj
         with ops.side():      # parameter gradients run beside the data-gradient chain (joined at the end of the block)
             ops.gemm(G.wgrad_dense_desc(gs, sa["o1"], Gr[n + ".linear.weight"].view(C, C)))
-        do1 = self.tmp("do1", (M, C))
+        do1 = self.side_tmp(n, "do1", (M, C))
         ops.gemm(G.dense_desc(gs, Wp[n + ".linear.weight.T"], do1, C))
         with ops.side():
             ops.colsum(do1, M, Gr[a + ".out_proj.bias"])
@@ -687,7 +701,7 @@ class Engine:
         ops.gemm(G.dense_desc(do1, Wp[a + ".out_proj.weight.T"], do.view(M, C), C))
         # attention core
         p = sa["p"]
-        dqkv = self.tmp("dqkv", (N, L, 3 * C))
+        dqkv = self.side_tmp(n, "dqkv", (N, L, 3 * C))
         if ops.attn_bwd_supported(L, d):
             # fused: dP, dS and the dK / dV accumulation over the query tiles stay on the SM
             ops.attn_bwd(sa["qkv"], p, sa["o"], do, dqkv, Hh, s.cross, alpha)
@@ -715,4 +729,4 @@ class Engine:
         ops.gn_bwd(h_in.t.view(N, L, C), None, sa["sums"], P[n + ".groupnorm.gn.weight"], P[n + ".groupnorm.gn.bias"], 0, dg,
                    Gr[n + ".groupnorm.gn.weight"], Gr[n + ".groupnorm.gn.bias"], self.zbuf("bwd", n + ".ws", (N, 32, 2)),
                    g0.view(N, L, C), None, add0=gs.view(N, L, C), add1a=e0.view(N, L, C) if e0 is not None else None)
-        ops.join_side()
+        self._block_join()

@@ -4,12 +4,12 @@
 //   per work item (image n, head), for each 128-query tile t:
 //       dP = dO_t V^T                     (tcgen05, accumulator in TMEM)
 //       dV += P_t^T dO_t                  (TMEM, accumulated over the tiles)
-//       dS = P_t o (dP - D),  D_i = dO_i . O_i   (four warps: TMEM + the P tile in shared memory -> bf16 dS IN PLACE of P)
+//       dS = P_t o (dP - D),  D_i = dO_i . O_i   (four warps: TMEM + the P, dO, O tiles in shared memory -> bf16 dS IN PLACE of P)
 //       dQ_t = scale dS K                 (TMEM, aliases the dP columns once dS is out)
 //       dK += scale dS^T Q_t              (TMEM, accumulated over the tiles)
 //
 // Nothing of size L x L leaves the SM: the unfused path wrote fp32 dP and bf16 dS to HBM and launched five GEMMs and a
-// softmax-backward kernel per block.  K and V stay in shared memory for the whole item; P (saved by the forward), Q_t and
+// softmax-backward kernel per block.  K and V stay in shared memory for the whole item; P (saved by the forward), Q_t, O_t and
 // dO_t arrive by TMA straight from the packed [N, L, 3C] / [N, L, C] activations; the cross-frame variant reads K, V of
 // image n ^ 1 and writes dK, dV there.  The same 128B-swizzled tiles serve as K-major and as MN-major UMMA operands
 // (P_t^T and dS^T are the MN-major views of the row-major tile), so no transposed copy exists.
@@ -28,7 +28,7 @@ constexpr int kThreads = 192;
 
 struct alignas(64) BP {
   CUtensorMap tmQ, tmK, tmV, tmDO, tmO, tmP;
-  const bf16* o; const bf16* dout; bf16* dqkv;
+  bf16* dqkv;
   int N, L, Lb2, heads, d, C, cross, qtiles, items, dch, kch2;
   uint32_t off_k, off_v, off_q, off_do, off_o, off_p;    // shared-memory offsets of the operand tiles
   uint32_t col_k, col_v;                           // TMEM columns of the dK / dV accumulators (dP and dQ start at 0)
@@ -271,7 +271,7 @@ extern "C" int b3d_attn_bwd(const void* qkv, const void* probs, int64_t ld_probs
   p.qtiles = (L + 127) / 128;
   p.items = N * heads;
   p.dch = (d + 63) / 64; p.kch2 = p.Lb2 / 64;
-  p.o = reinterpret_cast<const bf16*>(o); p.dout = reinterpret_cast<const bf16*>(dout); p.dqkv = reinterpret_cast<bf16*>(dqkv);
+  p.dqkv = reinterpret_cast<bf16*>(dqkv);
   const uint32_t kv_bytes = (uint32_t)p.dch * (uint32_t)p.Lb2 * 128u, qd_bytes = (uint32_t)p.dch * 16384u;
   p.off_k = 0; p.off_v = kv_bytes; p.off_q = 2 * kv_bytes; p.off_do = p.off_q + qd_bytes; p.off_o = p.off_do + qd_bytes; p.off_p = p.off_o + qd_bytes;
   p.col_k = (uint32_t)p.Lb2; p.col_v = (uint32_t)(p.Lb2 + (p.Lb2 / 128) * d);

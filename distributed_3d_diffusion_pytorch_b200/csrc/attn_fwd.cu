@@ -165,17 +165,18 @@ __global__ void __launch_bounds__(kThreads, 1) attn_fwd_kernel(const __grid_cons
       }
       // third sweep, over shared memory only: normalise the row in place (each thread re-reads what it wrote)
       const float inv_l = 1.f / l;
-      for (int c = 0; c < 2 * kch; ++c) {
-        const uint32_t row = p_base + (uint32_t)(c >> 1) * 16384u + (uint32_t)r * 128u;
+      for (int c = 0; c < kch; ++c) {                    // one 64-key chunk (a 128-byte row segment) per iteration: 8 loads in flight
+        const uint32_t row = p_base + (uint32_t)c * 16384u + (uint32_t)r * 128u;
+        uint4 q[8];
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          const uint32_t a = row + ((((uint32_t)((c & 1) * 4 + g)) ^ swz) << 4);
-          uint4 q = lds128(a);
-          uint32_t* w = reinterpret_cast<uint32_t*>(&q);
+        for (int u = 0; u < 8; ++u) q[u] = lds128(row + ((((uint32_t)u) ^ swz) << 4));      // (u ^ swz: conflict-free across the rows of a quarter warp)
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          uint32_t* w = reinterpret_cast<uint32_t*>(&q[u]);
 #pragma unroll
           for (int i = 0; i < 4; ++i)
             w[i] = pack_bf16x2(__uint_as_float(w[i] << 16) * inv_l, __uint_as_float(w[i] & 0xffff0000u) * inv_l);
-          sts128(a, q);
+          sts128(row + ((((uint32_t)u) ^ swz) << 4), q[u]);
         }
       }
       tc_fence_before();

@@ -4,7 +4,8 @@
 //   per work item (image n, head, 128-query tile):   S = Q K^T   ->   P = softmax(S / sqrt(d))   ->   O = P V
 //
 // S never leaves the SM: it is accumulated in TMEM by tcgen05.mma, read back by the softmax warps with tcgen05.ld,
-// normalised in fp32 registers, written as bf16 P into a 128B-swizzled shared-memory tile that is directly the A
+// exponentiated once in fp32 registers, written as bf16 into a 128B-swizzled shared-memory tile (normalised there in a
+// second sweep) that is directly the A
 // operand of the second tcgen05.mma (O in TMEM), and O leaves through shared memory + TMA store.  Q, K, V arrive by TMA
 // straight from the packed in_proj output [N, L, 3C] (no head split / transpose copies); the cross-frame variant reads
 // K, V of image n ^ 1.  When the backward pass will follow, P (bf16, normalised) is also written out by TMA.
@@ -130,7 +131,7 @@ __global__ void __launch_bounds__(kThreads, 1) attn_fwd_kernel(const __grid_cons
       const int qt = it % p.qtiles, head = (it / p.qtiles) % p.heads, n = it / (p.qtiles * p.heads);
       mbar_wait(s_full, iph);
       tc_fence_after();
-      // ---- softmax over the L keys of this query row (three sweeps over TMEM: max, sum, write)
+      // ---- softmax over the L keys of this query row: max sweep over TMEM, exp sweep TMEM -> smem, normalisation sweep over smem
       const int nch32 = (p.L + 31) / 32;
       float m = -INFINITY;
       for (int c = 0; c < nch32; ++c) {

@@ -68,6 +68,8 @@ struct alignas(64) KP {
   long long os_x, os_y, os_n, os_tap;
   float alpha, out_scale;
   int act, out_fp32, out_atomic;
+  float* gn_sums;       // optional: GroupNorm (sum, sumsq) of the stored bf16 output, fp32 [images, 32, 2], accumulated
+  int gn_cpg, gn_rpi;   // channels per group (4 / 8 / 16 / 32); rows per image of the dense form (0: conv form)
   int epi_tma;          // bf16 outputs leave through shared memory + TMA store (coalesced, no LSU global traffic)
   uint32_t epi_off;     // byte offset of the epilogue staging buffers inside dynamic smem
 };
@@ -529,6 +531,53 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
           if (p.out2) tma_store_4d(&p.tmO2, sx_base + buf * 16384, col0, cx, cy, cn);
           tma_store_commit();
         }
+        if (p.gn_sums != nullptr) {
+          // GroupNorm statistics of the tile just staged (the consumer's gn_stats pass over HBM disappears): thread t sums
+          // the cpg columns of group g over its slice of rows straight from the swizzled tile, slices of one (group, image)
+          // are adjacent lanes and combine by shuffles, one lane per (group, image) adds to the global sums.
+          const int cpg = p.gn_cpg, ng = 64 / cpg, lpg = 128 / ng, g = r / lpg, sl = r % lpg, rps = ng;
+          const uint32_t tile = so_base + (uint32_t)buf * 16384u;
+          float s1 = 0.f, s2 = 0.f;
+          for (int i = 0; i < rps; ++i) {
+            const int row = sl * rps + i;
+            const uint32_t rb = tile + (uint32_t)row * 128u, rz = (uint32_t)(row & 7);
+            if (cpg == 4) {
+              const uint32_t a = rb + ((((uint32_t)(g >> 1)) ^ rz) << 4) + (uint32_t)(g & 1) * 8u;
+              uint32_t w0, w1;
+              asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(w0), "=r"(w1) : "r"(a));
+              const float v0 = __uint_as_float(w0 << 16), v1 = __uint_as_float(w0 & 0xffff0000u), v2 = __uint_as_float(w1 << 16),
+                          v3 = __uint_as_float(w1 & 0xffff0000u);
+              s1 += (v0 + v1) + (v2 + v3);
+              s2 = fmaf(v0, v0, fmaf(v1, v1, fmaf(v2, v2, fmaf(v3, v3, s2))));
+            } else {
+              const int upr = cpg >> 3;                        // 16-byte units of this group per row
+              for (int u = 0; u < upr; ++u) {
+                const uint4 q = lds128(rb + ((((uint32_t)(g * upr + u)) ^ rz) << 4));
+                const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                  const float v0 = __uint_as_float(w[k] << 16), v1 = __uint_as_float(w[k] & 0xffff0000u);
+                  s1 += v0 + v1;
+                  s2 = fmaf(v0, v0, fmaf(v1, v1, s2));
+                }
+              }
+            }
+          }
+          const int rpib = p.gn_rpi > 0 ? min(128, p.gn_rpi) : min(128, p.bw * p.bh);     // rows of one image in this box
+          const int spi = rpib / rps;                                                      // slices (lanes) per image
+          const int seg = min(spi, 32);
+          for (int o = seg >> 1; o > 0; o >>= 1) {
+            s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+            s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+          }
+          if ((sl & (seg - 1)) == 0) {
+            const int row0 = sl * rps;
+            const int im = p.gn_rpi > 0 ? (cx + row0) / p.gn_rpi : cn + row0 / (p.bw * p.bh);
+            float* dst = p.gn_sums + ((long long)im * 32 + (col0 / cpg + g)) * 2;
+            atomicAdd(dst, s1);
+            atomicAdd(dst + 1, s2);
+          }
+        }
         buf ^= 1;
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
@@ -690,6 +739,28 @@ static int64_t g_launches = 0;
 extern "C" int64_t b3d_launch_count(void) { return g_launches; }
 void b3d_count_launch(int n) { g_launches += n; }
 
+// GroupNorm statistics in the epilogue: convolution / dense form, bf16 TMA-store output, n_cols = 32 * cpg, every
+// 128-row box full and made of whole row slices of single images.
+static bool gn_stats_ok(const b3d_gemm_desc* d) {
+  if (d->a_major != 0 || d->b_major != 0 || d->batched || d->out_fp32 || d->out_atomic || d->out_tap_stride != 0) return false;
+  const int cpg = d->gn_cpg;
+  if (!(cpg == 4 || cpg == 8 || cpg == 16 || cpg == 32) || d->n_cols != 32 * cpg) return false;
+  if (d->out_stride[0] % 8 || d->out_stride[1] % 8 || d->out_stride[2] % 8 || ((uintptr_t)d->out & 15)) return false;
+  if (d->resid && d->out2) return false;
+  const int bw = d->W < BM ? d->W : BM;
+  int bh = BM / bw; if (bh > d->H) bh = d->H; if (bh < 1) bh = 1;
+  int bnn = (bh == d->H) ? BM / (bw * bh) : 1; if (bnn > d->N) bnn = d->N; if (bnn < 1) bnn = 1;
+  if (bw * bh * bnn != BM || d->W % bw || d->H % bh || d->N % bnn) return false;
+  const int rps = 64 / cpg;                                      // rows per thread slice
+  const int rpi = d->gn_rows_per_image > 0 ? d->gn_rows_per_image : bw * bh;
+  if (d->gn_rows_per_image > 0 && !(d->H == 1 && d->N == 1)) return false;
+  const int rpib = rpi < BM ? rpi : BM;                          // rows of one image inside a box
+  if (rpib % rps || BM % rpib || (rpi > BM && rpi % BM)) return false;
+  const int spi = rpib / rps;
+  return (spi & (spi - 1)) == 0;
+}
+extern "C" int b3d_gemm_stats_supported(const b3d_gemm_desc* d) { return d && gn_stats_ok(d) ? 1 : 0; }
+
 extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   B3D_CHECK_ARG(d != nullptr && d->out != nullptr, "b3d_gemm: null descriptor/output");
@@ -776,7 +847,8 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
     if (dim >= 0) {
       const int tbw = dim == 0 ? 2 * bw : bw, tbh = dim == 1 ? 2 * bh : bh, tbnn = dim == 2 ? 2 * bnn : bnn;
       const long long tiles = (long long)((d->W + tbw - 1) / tbw) * ((d->H + tbh - 1) / tbh) * ((d->N + tbnn - 1) / tbnn) * p.tiles_n;
-      if (tiles >= 2LL * b3d_num_sms()) { p.m2 = 1; p.m2_dim = dim; m2_bw = tbw; m2_bh = tbh; m2_bnn = tbnn; p.a_bytes = 2 * kABytes; }
+      const bool fits = d->gn_sums == nullptr || (d->W % tbw == 0 && d->H % tbh == 0 && d->N % tbnn == 0);   // statistics need full tiles
+      if (fits && tiles >= 2LL * b3d_num_sms()) { p.m2 = 1; p.m2_dim = dim; m2_bw = tbw; m2_bh = tbh; m2_bnn = tbnn; p.a_bytes = 2 * kABytes; }
     }
   }
   // CTA pairs (cta_group::2): the same 256-row tile, but its halves live in the two CTAs of a cluster and ONE M = 256 MMA
@@ -807,7 +879,8 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
       const int mul = pair_wide ? 2 : 4;            // 128-row boxes per pair tile
       const int tbw = dim == 0 ? mul * bw : bw, tbh = dim == 1 ? mul * bh : bh, tbnn = dim == 2 ? mul * bnn : bnn;
       const long long tiles = (long long)((d->W + tbw - 1) / tbw) * ((d->H + tbh - 1) / tbh) * ((d->N + tbnn - 1) / tbnn) * p.tiles_n;
-      if (tiles >= (long long)b3d_num_sms() && (dim != 0 || tbw <= 512)) {      // >= 2 tiles per pair
+      const bool fits = d->gn_sums == nullptr || (d->W % tbw == 0 && d->H % tbh == 0 && d->N % tbnn == 0);
+      if (fits && tiles >= (long long)b3d_num_sms() && (dim != 0 || tbw <= 512)) {      // >= 2 tiles per pair
         p.c2 = 1; p.m2 = pair_wide ? 0 : 1; p.m2_dim = dim; m2_bw = tbw; m2_bh = tbh; m2_bnn = tbnn;
         p.a_bytes = pair_wide ? kABytes : 2 * kABytes;
         p.b_bytes = (uint32_t)((BN / 2 * 128 + 1023) / 1024 * 1024);
@@ -923,6 +996,10 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
   p.tiles_total = p.tiles_m * p.tiles_n * p.tiles_b * p.tiles_z;
   B3D_CHECK_ARG(p.tiles_total > 0, "b3d_gemm: empty problem");
 
+  if (d->gn_sums != nullptr) {
+    B3D_CHECK_ARG(p.epi_tma && gn_stats_ok(d), "b3d_gemm: gn_sums cannot be honoured for this descriptor (see b3d_gemm_stats_supported)");
+    p.gn_sums = d->gn_sums; p.gn_cpg = d->gn_cpg; p.gn_rpi = d->gn_rows_per_image;
+  }
   p.out = d->out; p.out2 = d->out2; p.bias = d->bias; p.rowvec = d->rowvec; p.rowvec_ld = d->rowvec_ld;
   p.resid = reinterpret_cast<const bf16*>(d->resid);
   p.os_x = d->out_stride[0]; p.os_y = d->out_stride[1]; p.os_n = d->out_stride[2]; p.os_tap = d->out_tap_stride;

@@ -35,6 +35,7 @@ class _GemmDesc(ctypes.Structure):
         ("out", c_void), ("out_fp32", c_i32), ("out_stride", c_i64 * 3), ("out_tap_stride", c_i64),
         ("out2", c_void), ("bias", c_void), ("rowvec", c_void), ("rowvec_ld", c_i64), ("resid", c_void),
         ("alpha", c_f32), ("out_scale", c_f32), ("act", c_i32), ("out_atomic", c_i32), ("bn_tile", c_i32),
+        ("gn_sums", c_void), ("gn_cpg", c_i32), ("gn_rows_per_image", c_i32),
     ]
 
 
@@ -70,6 +71,10 @@ class GemmDesc:
     act: int = 0
     out_atomic: bool = False
     bn_tile: int = 0
+    # GroupNorm (sum, sumsq) of the bf16 output taken in the epilogue: fp32 [images, 32, 2], accumulated (see include/b3d.h)
+    gn_sums: Optional[torch.Tensor] = None
+    gn_cpg: int = 0
+    gn_rows_per_image: int = 0
 
 
 def _ptr(t):
@@ -196,7 +201,11 @@ class CudaOps:
         return 2.0 * d.m_rows * d.n_cols * d.N * d.H * d.W * d.b_taps
 
     # ---- tensor-core path
-    def gemm(self, d: GemmDesc):
+    def gemm_stats_supported(self, d: GemmDesc):
+        """can b3d_gemm take the GroupNorm statistics of d.out in its epilogue (d.gn_cpg / d.gn_rows_per_image set)?"""
+        return bool(self.lib.b3d_gemm_stats_supported(ctypes.byref(self._cdesc(d))))
+
+    def _cdesc(self, d: GemmDesc):
         cd = _GemmDesc()
         assert 1 <= len(d.a) <= 3
         for i, t in enumerate(d.a):
@@ -232,6 +241,15 @@ class CudaOps:
             cd.resid = d.resid.data_ptr()
         cd.alpha, cd.out_scale, cd.act = d.alpha, d.out_scale, d.act
         cd.out_atomic, cd.bn_tile = int(d.out_atomic), d.bn_tile
+        cd.gn_cpg, cd.gn_rows_per_image = d.gn_cpg, d.gn_rows_per_image
+        if d.gn_sums is not None:
+            assert d.gn_sums.dtype == torch.float32 and d.gn_sums.is_contiguous()
+            cd.gn_sums = d.gn_sums.data_ptr()
+        return cd
+
+    def gemm(self, d: GemmDesc):
+        cd = self._cdesc(d)
+        o = d.out
         if self.prof is not None:
             self._flop = self.gemm_flop(d)
             self._info = (f"maj{d.a_major}{d.b_major} WHN={d.W}x{d.H}x{d.N} rows={d.m_rows} cols={d.n_cols} "

@@ -73,9 +73,18 @@ typedef struct b3d_gemm_desc {
   int32_t act;           /* 0 none, 1 silu */
   int32_t out_atomic;    /* fp32 atomicAdd into out */
   int32_t bn_tile;       /* 0 = auto */
+  /* Optional GroupNorm statistics of the bf16 output, taken in the epilogue (saves the consumer's b3d_gn_stats pass):
+   * gn_sums fp32 [images, 32, 2] (sum, sumsq) is ACCUMULATED (caller zeroes it); n_cols must be 32 * gn_cpg with
+   * gn_cpg in {4, 8, 16, 32}.  Convolution / dense form with bf16 TMA-store output only; every tile must be full
+   * (see b3d_gemm_stats_supported).  gn_rows_per_image: rows of one image for the dense form (H = N = 1), else 0. */
+  float* gn_sums;
+  int32_t gn_cpg;
+  int32_t gn_rows_per_image;
 } b3d_gemm_desc;
 
 int b3d_gemm(const b3d_gemm_desc* d, void* stream);
+/* 1 when b3d_gemm can honour d->gn_sums for this descriptor (pure host code) */
+int b3d_gemm_stats_supported(const b3d_gemm_desc* d);
 
 /* Fused attention forward for L <= 256 tokens, head_dim <= 256 (all attention levels of CFG-64; the deepest of CFG-128):
  * softmax(Q K^T * scale) V per (image, head) with S and O in TMEM, P through shared memory, operands by TMA straight

@@ -40,9 +40,11 @@ class EmuOps:
     act_dtype = torch.float32
     name = "emu"
 
-    def __init__(self, device="cpu", act_dtype=torch.float32):
+    def __init__(self, device="cpu", act_dtype=torch.float32, stats_dtype=None):
         self.device = torch.device(device)
         self.act_dtype = act_dtype
+        # epilogue GroupNorm statistics are taken over the STORED output: per-kernel GPU comparisons round it like the GPU does
+        self.stats_dtype = stats_dtype
 
     def side(self):
         import contextlib
@@ -122,6 +124,37 @@ class EmuOps:
                 D = outs
             img = None
         self._epilogue(d, D, img)
+        if getattr(d, "gn_sums", None) is not None:
+            # statistics of the STORED output (after the rounding of the activation dtype), per image and group of gn_cpg channels
+            o = d.out[..., :d.n_cols]
+            o = (o.to(self.stats_dtype) if self.stats_dtype is not None else o).float()
+            if d.gn_rows_per_image > 0:
+                o = o.reshape(-1, d.gn_rows_per_image, d.n_cols)
+            else:
+                o = o.reshape(o.shape[0], -1, d.n_cols)
+            g = o.reshape(o.shape[0], o.shape[1], 32, d.gn_cpg)
+            d.gn_sums[..., 0] += g.sum((1, 3))
+            d.gn_sums[..., 1] += (g * g).sum((1, 3))
+
+    def gemm_stats_supported(self, d):
+        if d.a_major != 0 or d.b_major != 0 or d.batched or d.gn_cpg not in (4, 8, 16, 32):      # (the emu's activations are fp32)
+            return False
+        if d.n_cols != 32 * d.gn_cpg or (d.resid is not None and d.out2 is not None):
+            return False
+        bw = min(d.W, 128)
+        bh = max(1, min(128 // bw, d.H))
+        bnn = max(1, min(128 // (bw * bh), d.N)) if bh == d.H else 1
+        if bw * bh * bnn != 128 or d.W % bw or d.H % bh or d.N % bnn:
+            return False
+        rps = 64 // d.gn_cpg
+        rpi = d.gn_rows_per_image if d.gn_rows_per_image > 0 else bw * bh
+        if d.gn_rows_per_image > 0 and not (d.H == 1 and d.N == 1):
+            return False
+        rpib = min(rpi, 128)
+        if rpib % rps or 128 % rpib or (rpi > 128 and rpi % 128):
+            return False
+        spi = rpib // rps
+        return spi & (spi - 1) == 0
 
     def _epilogue(self, d, D, img):
         def finish(v, dst, dst2, resid, rowvec):

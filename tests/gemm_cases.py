@@ -21,8 +21,16 @@ def _mk(ops, t, dtype=None):
     return t.to(device=ops.device, dtype=dtype or ops.act_dtype).contiguous()
 
 
+def _with_stats(ops, d, outs, gn_cpg, rows_per_image, n_images):
+    """ask for the GroupNorm statistics of the output in the epilogue (cases are chosen so that it is supported)"""
+    d.gn_cpg, d.gn_rows_per_image = gn_cpg, rows_per_image
+    assert ops.gemm_stats_supported(d), "test case must be eligible for epilogue statistics"
+    d.gn_sums = ops.zeros((n_images, 32, 2), torch.float32)
+    return d, outs + [d.gn_sums]
+
+
 def conv_case(name, N, H, W, Cs, taps, Co, stride=1, bias=True, resid=False, rowvec=False, act=0, out2=False, alpha=1.0, out_scale=1.0,
-              fp32_out=False, bn=0, seed=0):
+              fp32_out=False, bn=0, seed=0, gn_cpg=0):
     def build(ops):
         g = torch.Generator().manual_seed(seed)
         Ho, Wo = (H + stride - 1) // stride if 9 in taps else H // stride, (W + stride - 1) // stride if 9 in taps else W // stride
@@ -48,11 +56,13 @@ def conv_case(name, N, H, W, Cs, taps, Co, stride=1, bias=True, resid=False, row
         if out2:
             epi["out2"] = o2
         d = G.conv_desc(srcs, taps, wp, Co, out, stride, **epi)
+        if gn_cpg:
+            return _with_stats(ops, d, [out] + ([o2] if out2 else []), gn_cpg, 0, N)
         return d, [out] + ([o2] if out2 else [])
     return Case(name, build)
 
 
-def dense_case(name, M, K, Ncols, seed=0, **kw):
+def dense_case(name, M, K, Ncols, seed=0, gn_cpg=0, rows_per_image=0, **kw):
     def build(ops):
         g = torch.Generator().manual_seed(seed)
         x = _mk(ops, _rand((M, K), g))
@@ -63,7 +73,10 @@ def dense_case(name, M, K, Ncols, seed=0, **kw):
         out = ops.zeros((M, ldo))
         epi = dict(kw)
         epi["bias"] = _mk(ops, torch.randn(Ncols, generator=g), torch.float32)
-        return G.dense_desc(x, wp, out, Ncols, **epi), [out]
+        d = G.dense_desc(x, wp, out, Ncols, **epi)
+        if gn_cpg:
+            return _with_stats(ops, d, [out], gn_cpg, rows_per_image, M // rows_per_image)
+        return d, [out]
     return Case(name, build)
 
 
@@ -169,6 +182,16 @@ def all_cases():
         conv_case("conv_pairquad_images_8x8_c128_64_rowvec", 2410, 8, 8, [128], [9], 64, rowvec=True, seed=32),
         conv_case("conv_pairquad_rows_30x32_c256_96", 86, 30, 32, [256], [9], 96, act=1, seed=33),
         dense_case("dense_pairquad_80001x1024x96", 80001, 1024, 96, seed=34),
+        # GroupNorm statistics of the output taken in the epilogue (plain, 256-row, pair and pair-quad tiles; 1..2 images per box)
+        conv_case("conv_stats_64x64_c64_128_cpg4", 2, 64, 64, [64], [9], 128, gn_cpg=4, seed=41),
+        conv_case("conv_stats_8x8_c64_256_cpg8_resid", 6, 8, 8, [64], [9], 256, gn_cpg=8, resid=True, out_scale=0.70710678, seed=42),
+        conv_case("conv_stats_16x16_c64_512_cpg16", 3, 16, 16, [64], [9], 512, gn_cpg=16, seed=43),
+        conv_case("conv_stats_8x8_c32_1024_cpg32", 4, 8, 8, [32], [9], 1024, gn_cpg=32, seed=44),
+        conv_case("conv_stats_m2_64x64_c64_128", 20, 64, 64, [64], [9], 128, gn_cpg=4, seed=45),
+        conv_case("conv_stats_pair_32x32_c128_256", 160, 32, 32, [128], [9], 256, gn_cpg=8, seed=46),
+        conv_case("conv_stats_pairquad_8x8_c128_128", 2432, 8, 8, [128], [9], 128, gn_cpg=4, seed=47),
+        dense_case("dense_stats_2048x256x256_L64", 2048, 256, 256, gn_cpg=8, rows_per_image=64, seed=48),
+        dense_case("dense_stats_81920x1024x256_L256_pair", 81920, 1024, 256, gn_cpg=8, rows_per_image=256, seed=49),
         conv_case("conv_16x16_c64_128", 2, 16, 16, [64], [9], 128),
         conv_case("conv_64x64_c128_128_resid", 2, 64, 64, [128], [9], 128, resid=True, out_scale=0.70710678),
         conv_case("conv_8x8_c512_512", 4, 8, 8, [512], [9], 512),

@@ -52,7 +52,7 @@ def run_op_case(fn, cuda, emu):
 
 def main():
     flt = sys.argv[1] if len(sys.argv) > 1 else ""
-    cuda, emu = CudaOps("cuda:0"), EmuOps("cpu")
+    cuda, emu = CudaOps("cuda:0"), EmuOps("cpu", stats_dtype=torch.bfloat16)
     summary = {}
     nfail = 0
     items = [(c.name, lambda c=c: run_gemm_case(c, cuda, emu)) for c in gemm_cases.all_cases()]

@@ -13,7 +13,7 @@ pytestmark = pytest.mark.gpu
 def backends():
     from distributed_3d_diffusion_pytorch_b200.ops import CudaOps
     from emu_ops import EmuOps
-    return CudaOps("cuda:0"), EmuOps("cpu")
+    return CudaOps("cuda:0"), EmuOps("cpu", stats_dtype=torch.bfloat16)
 
 
 def _cmp(a, b):

@@ -77,8 +77,8 @@ def cpu_reference_step_time(B, steps, warmup, threads=None):
     """the reference algorithm (oracle port, fp32, torch CPU) on the host cores: one training step = fwd + loss + bwd"""
     from oracle import diffusion_ref as dr, xunet_ref as xr
     from distributed_3d_diffusion_pytorch_b200 import synthetic
-    if threads:
-        torch.set_num_threads(threads)
+    # all host cores: torchrun exports OMP_NUM_THREADS=1, which would cripple this arm at N > 1
+    torch.set_num_threads(threads or os.cpu_count() or 1)
     cfg = xr.Cfg(**MODEL_KW)
     sd = {k: v.requires_grad_(True) for k, v in xr.init_state_dict(cfg, seed=0).items()}
     img, R, T, K = synthetic.make_views(B, MODEL_KW["H"], seed=1)
@@ -98,6 +98,85 @@ def cpu_reference_step_time(B, steps, warmup, threads=None):
         if it >= warmup:
             times.append(time.time() - t0)
     return sum(times) / len(times), torch.get_num_threads()
+
+
+def gpu_eager_baseline(dev, batch=64, steps=5, warmup=2):
+    """The bar that matters beside the CPU number: the reference's eager PyTorch path
+    on the SAME B200 -- the pinned port of its module (oracle/xunet_ref.xunet_forward, plain torch ops on cuDNN / cuBLAS)
+    + loss + autograd backward, (i) fp32 with TF32 off, (ii) under torch.autocast(bfloat16).  /root/reference itself does
+    not travel to the GPU box, hence kind "port".  Batch: the largest power of two <= `batch` that fits."""
+    from oracle import diffusion_ref as dr, xunet_ref as xr
+    from distributed_3d_diffusion_pytorch_b200 import synthetic
+    cfg = xr.Cfg(**MODEL_KW)
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    out = {"kind": "port", "unit": UNIT, "steps": steps, "warmup": warmup,
+           "what": "oracle port of xunet.py + mse + autograd backward, eager torch on cuDNN/cuBLAS, no optimizer step"}
+    sd = {k: v.to(dev).requires_grad_(True) for k, v in xr.init_state_dict(cfg, seed=0).items()}
+    for key, autocast in (("fp32", False), ("bf16_autocast", True)):
+        B = batch
+        while B >= 1:
+            try:
+                img, R, T, K = synthetic.make_views(B, MODEL_KW["H"], seed=1, device=dev)
+                g = torch.Generator(device=dev).manual_seed(2)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                for it in range(warmup + steps):
+                    if it == warmup:
+                        torch.cuda.synchronize()
+                        e0.record()
+                    logsnr = dr.logsnr_schedule_cosine(torch.rand(B, generator=g, device=dev))
+                    noise = torch.randn(img[:, 0].shape, generator=g, device=dev)
+                    cm = torch.rand(B, generator=g, device=dev) > 0.1
+                    x = torch.where(cm[:, None, None, None], img[:, 0], torch.randn(img[:, 0].shape, generator=g, device=dev))
+                    b_ = dr.make_batch(x, logsnr, dr.q_sample(img[:, 1], logsnr, noise), R, T, K)
+                    for v in sd.values():
+                        v.grad = None
+                    with torch.autocast("cuda", dtype=torch.bfloat16, enabled=autocast):
+                        eps = xr.xunet_forward(sd, cfg, b_, cm, training=True)
+                    loss = dr.loss_fn(noise, eps.float())
+                    loss.backward()
+                e1.record()
+                torch.cuda.synchronize()
+                ms = e0.elapsed_time(e1) / steps
+                out[key] = {"value": B / (ms / 1e3), "ms_per_step": ms, "batch": B}
+                break
+            except torch.cuda.OutOfMemoryError:
+                B //= 2
+            finally:
+                for v in sd.values():
+                    v.grad = None
+                torch.cuda.empty_cache()
+        else:
+            out[key] = None
+    return out
+
+
+def bench_cfg128(dev, args, batch=32, steps=3, warmup=3):
+    """BASELINE configs[2] on one GPU: XUNet() defaults (H=W=128, ch=256), bf16, the same training step, at the largest
+    per-GPU batch of the 8-GPU run that matters here (32 = global 128 over 4 GPUs fits one B200 with room to spare)."""
+    from distributed_3d_diffusion_pytorch_b200 import synthetic
+    from distributed_3d_diffusion_pytorch_b200.trainer import Trainer
+    kw = dict(H=128, W=128, ch=256)
+    tr = Trainer(kw, batch, dev, world=1, seed=4321, use_graph=not args.no_graph)
+    res = [tuple(t.to(dev) for t in synthetic.make_views(batch, 128, seed=50 + i)) for i in range(2)]
+    for i in range(warmup):
+        tr.step_resident(res[i % 2])
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        tr.step_resident(res[i % 2])
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    prof = tr.profile_step(res[0])
+    achieved = prof["b3d_gemm"]["flop"] / (prof["b3d_gemm"]["ms"] / 1e3) / 1e12
+    pk = peaks()
+    out = {"metric": "xunet_train_samples_per_sec_128", "value": batch / (ms / 1e3), "unit": UNIT, "ms_per_step": ms, "batch": batch, "steps": steps,
+           "warmup": warmup, "whole_step_tflops": 8921e9 * batch / (ms / 1e3) / 1e12, "gemm_tflops": achieved, "gemm_frac_of_sustained_peak": achieved / pk["tf_sustained"],
+           "breakdown_ms": {k: round(v["ms"], 3) for k, v in prof.items() if isinstance(v, dict)}, "loss": float(tr.loss.item())}
+    del tr, res
+    return out
 
 
 def run_reference(args):
@@ -124,11 +203,12 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b3d")
     ap.add_argument("--global-batch", type=int, default=128)
-    ap.add_argument("--ref-batch", type=int, default=2)
+    ap.add_argument("--ref-batch", type=int, default=4, help="BASELINE configs[0]: batch 4 on the CPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-profile", action="store_true")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-sampler", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the CFG-128 extra line and the eager-GPU baseline (N = 1 only)")
     ap.add_argument("--model", default="cfg64", choices=["cfg64", "cfg128"], help="cfg128 = XUNet() defaults (H=W=128, ch=256), BASELINE configs[2]")
     ap.add_argument("--profile-json", default=None, help="dump the per-launch CUDA-event table of the profiled step")
     args = ap.parse_args()
@@ -151,7 +231,7 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
     assert world == args.gpus, (world, args.gpus)
     B = args.global_batch // world
-    tr = Trainer(MODEL_KW, B, dev, world=world, seed=1234 + rank, use_graph=not args.no_graph)
+    tr = Trainer(MODEL_KW, B, dev, world=world, seed=1234, use_graph=not args.no_graph)      # (the trainer adds the rank to the seed)
 
     # synthetic SRN-shaped data: a pool of host batches (pinned) and device-resident copies of the same
     pool = [synthetic.make_views(B, MODEL_KW["H"], seed=100 * rank + i) for i in range(4)]
@@ -201,6 +281,16 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_value = args.global_batch * args.steps / (t.item() / 1e3)
 
+    # ---------------- every rank must hold the same parameters after the timed steps (outside the timed region): the proof
+    # that the three all-reduced gradient ranges cover the whole arena and that the ranks never drifted apart
+    checksum_equal = None
+    if world > 1:
+        cs = tr.model.flat_parameters().double().sum().reshape(1)
+        allcs = [torch.zeros_like(cs) for _ in range(world)]
+        dist.all_gather(allcs, cs)
+        checksum_equal = bool(all(torch.equal(c, allcs[0]) for c in allcs))
+        assert checksum_equal, f"rank parameters diverged: {[c.item() for c in allcs]}"
+
     # ---------------- roofline of the dominant kernel (tcgen05 implicit GEMM), measured live with CUDA events
     roof = None
     pk = peaks()
@@ -214,13 +304,14 @@ def main():
         if os.path.exists(tp):
             traffic = json.load(open(tp)).get("gemm_dram_bytes_per_launch")
         roof = {"bound": "tensor", "achieved": achieved, "peak": pk["tf_sustained"], "unit": "TFLOP/s", "frac": achieved / pk["tf_sustained"],
-                "traffic": traffic, "kernel": "b3d_gemm_kernel", "launches_per_step": prof["b3d_gemm"]["n"],
+                "traffic": traffic, "traffic_source": "profiles/roofline_traffic.json (one ncu --set full capture of one conv launch, offline; NOT measured by this run)",
+                "kernel": "b3d_gemm_kernel", "launches_per_step": prof["b3d_gemm"]["n"],
                 "kernel_share_of_step": gemm_ms / prof["total_ms"], "peak_source": pk["src"] + " (sustained cuBLAS bf16)",
                 "whole_step_tflops": TRAIN_FLOP_PER_SAMPLE * B / (ms / args.steps / 1e3) / 1e12,
                 "breakdown_ms": {k: round(v["ms"], 3) for k, v in prof.items() if isinstance(v, dict)}}
 
     # ---------------- second half of the metric: stochastic-conditioning sampler, denoise steps/s (one object per rank)
-    sampler = None
+    sampler, gs = None, None
     if not args.no_sampler:
         from distributed_3d_diffusion_pytorch_b200.sampling import GraphSampler
         gs = GraphSampler(tr.model, 8)
@@ -245,6 +336,19 @@ def main():
         sampler = {"metric": "sampler_denoise_steps_per_sec_64", "value": world * nst / (t.item() / 1e3), "unit": "steps/s",
                    "ms_per_step": t.item() / nst, "config": "one object per GPU, 8 guidance weights x (cond, uncond) = one batch-16 forward + fused update, CUDA graph, dropout on (as sampling.py)"}
 
+    # ---------------- N = 1 extras, after the trainer's memory is released: BASELINE configs[2] (CFG-128 train step) and the
+    # reference's eager GPU path on this same B200
+    eager, cfg128 = None, None
+    if rank == 0 and world == 1 and args.model == "cfg64" and not args.no_extras:
+        del gs, tr, resident
+        import gc
+        gc.collect()
+        torch.cuda.empty_cache()
+        cfg128 = bench_cfg128(dev, args)
+        gc.collect()
+        torch.cuda.empty_cache()
+        eager = gpu_eager_baseline(dev)
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         tcpu, cores = cpu_reference_step_time(args.ref_batch, 2, 1)
@@ -262,6 +366,7 @@ def main():
                        "baseline_note": "vs_baseline = value / 29.9 samples/s (README.md:39, 8x RTX 3090, derived)"},
             "clocks": clk, "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4, "last_loss": loss_val},
             "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cpu, "sampler": sampler,
+            "param_checksum_equal": checksum_equal, "gpu_eager_baseline": eager, "cfg128": cfg128,
         }))
     if world > 1:
         dist.destroy_process_group()

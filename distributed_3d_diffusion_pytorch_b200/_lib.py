@@ -35,3 +35,8 @@ def launch_count():
 def set_pdl(on):
     """programmatic dependent launch of the frequent kernels (include/b3d.h: b3d_set_pdl)"""
     load().b3d_set_pdl(ctypes.c_int(1 if on else 0))
+
+
+def set_gn_chunk_mb(mb):
+    """per-chunk budget of the image-chunked GroupNorm launches (include/b3d.h: b3d_set_gn_chunk_mb); 0 = off"""
+    load().b3d_set_gn_chunk_mb(ctypes.c_int(int(mb)))

@@ -108,6 +108,8 @@ __device__ __forceinline__ float b3d_warp_sum(float v) {
 // Counter-based dropout bits, recomputable in backward: one 32-bit hash per PAIR of consecutive elements (16 bits
 // each; element 2k takes the low half).  key = seed * golden ratio + (element index >> 1).  An element is dropped when
 // its 16-bit field is below b3d_drop_thr16(p).  (tests/emu_ops.py mirrors both functions bit for bit.)
+// stride of the device-side step counter inside a dropout seed (2^40 + 435): host seeds (block index, rank) stay far below it
+#define B3D_SEED_STEP_STRIDE 0x100000001B3ULL
 __host__ __device__ __forceinline__ uint32_t b3d_drop_pair(uint64_t key) {
   uint32_t x = (uint32_t)key ^ ((uint32_t)(key >> 32) * 0x9E3779B9u);
   x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;

@@ -23,28 +23,25 @@ inline int grid_for(long long n, int per_block = kT, int max_blocks = 148 * 32) 
 // Replaces visu3d rays + xunet.py:311-336.  One block = 32 consecutive pixels of one image row.
 // ---------------------------------------------------------------------------------------------
 template <typename OutT>
-__global__ void pose_embedding_kernel(const double* __restrict__ Kmat, const double* __restrict__ R, const double* __restrict__ t,
-                                      const uint8_t* __restrict__ mask, const float* __restrict__ pos_emb,
-                                      const float* __restrict__ first_emb, const float* __restrict__ other_emb, OutT* __restrict__ out,
-                                      long long ld, int H, int W) {
-  __shared__ float s_pe[144][33];
+__global__ void __launch_bounds__(256) pose_embedding_kernel(const double* __restrict__ Kmat, const double* __restrict__ R,
+                                                             const double* __restrict__ t, const uint8_t* __restrict__ mask,
+                                                             const float* __restrict__ pos_emb, const float* __restrict__ first_emb,
+                                                             const float* __restrict__ other_emb, OutT* __restrict__ out, long long ld, int H,
+                                                             int W, int vec_ok) {
+  // The 32-pixel x 144-channel tile is assembled in shared memory (phase A: one value per thread-iteration, pixel index
+  // fastest, so the learned embedding pos_emb[c,y,x] is read coalesced along x) and leaves as 16-byte stores of 8 channels
+  // (phase B: consecutive threads -> consecutive 16-byte pieces of the 288-byte pixel rows).  Scalar 2-byte stores with a
+  // div/mod pair per element ran this kernel at 8 % of the HBM rate.
+  constexpr int kPitch = 148;                       // floats per pixel row of the tile (16-byte aligned rows)
+  __shared__ __align__(16) float s_out[32 * kPitch];
   __shared__ float s_posch[93];
   __shared__ float s_dir[32][3];
+  __shared__ float s_mul[51], s_ph[51];             // direction channels 93..143: multiplier 2^d, phase (0 or pi/2)
+  __shared__ int s_ax[51];                          //   axis; -1 - axis for the three raw components
   __shared__ double s_M[9];
   const int n = blockIdx.z, y = blockIdx.y, x0 = blockIdx.x * 32;
   const int b = n >> 1, f = n & 1;
   const bool cond = mask[b] != 0;
-  // learned per-pixel embedding tile, read coalesced along x
-  for (int i = threadIdx.x; i < 144 * 32; i += blockDim.x) {
-    const int c = i >> 5, xx = i & 31;
-    float v = 0.f;
-    if (x0 + xx < W) {
-      if (pos_emb) v = pos_emb[((long long)c * H + y) * W + x0 + xx];
-      const float* fe = f == 0 ? first_emb : other_emb;
-      if (fe) v += fe[c];
-    }
-    s_pe[c][xx] = v;
-  }
   if (threadIdx.x == 0) {
     // M = R * inv(K)   (world_from_px for directions)
     const double* k = Kmat + b * 9;
@@ -70,6 +67,13 @@ __global__ void pose_embedding_kernel(const double* __restrict__ Kmat, const dou
       v = sinf(xb);
     }
     s_posch[c] = cond ? v : 0.f;
+  } else if (threadIdx.x >= 128 && threadIdx.x < 128 + 51) {
+    const int cc = threadIdx.x - 128;               // direction channels: [dir(3), sin(dir*2^d) (d-major, 8 octaves), sin(. + pi/2)]
+    if (cc < 3) { s_ax[cc] = -1 - cc; s_mul[cc] = 1.f; s_ph[cc] = 0.f; }
+    else {
+      const int j = (cc - 3) % 24, d = j / 3;
+      s_ax[cc] = j % 3; s_mul[cc] = (float)(1 << d); s_ph[cc] = cc - 3 >= 24 ? 1.5707963705062866f : 0.f;
+    }
   }
   __syncthreads();
   if (threadIdx.x < 32) {
@@ -83,24 +87,52 @@ __global__ void pose_embedding_kernel(const double* __restrict__ Kmat, const dou
     s_dir[threadIdx.x][2] = (float)(dz * inv_n);
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < 32 * 144; i += blockDim.x) {
-    const int xx = i / 144, c = i % 144;
-    if (x0 + xx >= W) continue;
+  // phase A: 256 threads = 8 channels x 32 pixels per iteration
+  const int xx = threadIdx.x & 31;
+  const bool in_x = x0 + xx < W;
+  const float* fe = f == 0 ? first_emb : other_emb;
+  for (int c = threadIdx.x >> 5; c < 144; c += 8) {
     float v;
     if (c < 93) v = s_posch[c];
+    else if (!cond) v = 0.f;
     else {
-      const int cc = c - 93;
-      if (!cond) v = 0.f;
-      else if (cc < 3) v = s_dir[xx][cc];
+      const int cc = c - 93, ax = s_ax[cc];
+      if (ax < 0) v = s_dir[xx][-1 - ax];
       else {
-        const int j = (cc - 3) % 24, d = j / 3, ax = j % 3;
-        float xb = s_dir[xx][ax] * (float)(1 << d);
-        if (cc - 3 >= 24) xb = xb + 1.5707963705062866f;
+        float xb = s_dir[xx][ax] * s_mul[cc];       // same fp32 operation order as posenc_nerf (xunet.py:49-59): x*2^d, + pi/2, sin
+        if (cc - 3 >= 24) xb = xb + s_ph[cc];
         v = sinf(xb);
       }
     }
-    v += s_pe[c][xx];
-    out[(((long long)n * H + y) * W + x0 + xx) * ld + c] = (OutT)v;
+    if (in_x) {
+      if (pos_emb) v += pos_emb[((long long)c * H + y) * W + x0 + xx];
+      if (fe) v += fe[c];
+    }
+    s_out[xx * kPitch + c] = v;
+  }
+  __syncthreads();
+  // phase B
+  OutT* orow = out + (((long long)n * H + y) * W + x0) * ld;
+  if (vec_ok) {
+    for (int i = threadIdx.x; i < 32 * 18; i += blockDim.x) {
+      const int px = i / 18, c8 = i - px * 18;
+      if (x0 + px >= W) break;
+      const float4 lo = *reinterpret_cast<const float4*>(&s_out[px * kPitch + c8 * 8]);
+      const float4 hi = *reinterpret_cast<const float4*>(&s_out[px * kPitch + c8 * 8 + 4]);
+      OutT* dst = orow + (long long)px * ld + c8 * 8;
+      if constexpr (sizeof(OutT) == 2) {
+        const float f8[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+        *reinterpret_cast<bf16x8*>(dst) = b3d_pack8(f8);
+      } else {
+        *reinterpret_cast<float4*>(dst) = lo;
+        *reinterpret_cast<float4*>(dst + 4) = hi;
+      }
+    }
+  } else {
+    for (int i = threadIdx.x; i < 32 * 144; i += blockDim.x) {
+      const int px = i / 144, c = i - px * 144;
+      if (x0 + px < W) orow[(long long)px * ld + c] = (OutT)s_out[px * kPitch + c];
+    }
   }
 }
 
@@ -576,29 +608,37 @@ __device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, 
   v = b2 * v + (1.f - b2) * gg * gg;
   p -= lr * (m * ibc1) / (sqrtf(v * ibc2) + eps);
 }
-// 128-bit accesses, two independent vectors in flight per thread (28 bytes of traffic per parameter: HBM-bound)
+// 128-bit accesses, two independent vectors in flight per thread (28 bytes of traffic per parameter: HBM-bound).
+// kEma: also ema = decay * ema + (1 - decay) * p_new (the parameter average lightning/diff3d.py:11-19 describes), +8 bytes.
+template <bool kEma>
 __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
-                                                   long long n, float lr, float b1, float b2, float eps, float ibc1, float ibc2, float grad_scale) {
+                                                   float* __restrict__ ema, long long n, float lr, float b1, float b2, float eps, float ibc1,
+                                                   float ibc2, float grad_scale, float decay) {
   const long long n4 = n / 4, stride = (long long)gridDim.x * blockDim.x;
   float4* p4 = reinterpret_cast<float4*>(p); const float4* g4 = reinterpret_cast<const float4*>(g);
-  float4* m4 = reinterpret_cast<float4*>(m); float4* v4 = reinterpret_cast<float4*>(v);
+  float4* m4 = reinterpret_cast<float4*>(m); float4* v4 = reinterpret_cast<float4*>(v); float4* e4 = reinterpret_cast<float4*>(ema);
+  const float omd = 1.f - decay;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += 2 * stride) {
     const long long i1 = i + stride;
     const bool two = i1 < n4;
-    float4 P0 = p4[i], G0 = g4[i], M0 = m4[i], V0 = v4[i], P1, G1, M1, V1;
-    if (two) { P1 = p4[i1]; G1 = g4[i1]; M1 = m4[i1]; V1 = v4[i1]; }
+    float4 P0 = p4[i], G0 = g4[i], M0 = m4[i], V0 = v4[i], P1, G1, M1, V1, E0, E1;
+    if (kEma) E0 = e4[i];
+    if (two) { P1 = p4[i1]; G1 = g4[i1]; M1 = m4[i1]; V1 = v4[i1]; if (kEma) E1 = e4[i1]; }
     adam_one(P0.x, G0.x, M0.x, V0.x, lr, b1, b2, eps, ibc1, ibc2, grad_scale); adam_one(P0.y, G0.y, M0.y, V0.y, lr, b1, b2, eps, ibc1, ibc2, grad_scale);
     adam_one(P0.z, G0.z, M0.z, V0.z, lr, b1, b2, eps, ibc1, ibc2, grad_scale); adam_one(P0.w, G0.w, M0.w, V0.w, lr, b1, b2, eps, ibc1, ibc2, grad_scale);
     p4[i] = P0; m4[i] = M0; v4[i] = V0;
+    if (kEma) e4[i] = make_float4(decay * E0.x + omd * P0.x, decay * E0.y + omd * P0.y, decay * E0.z + omd * P0.z, decay * E0.w + omd * P0.w);
     if (two) {
       adam_one(P1.x, G1.x, M1.x, V1.x, lr, b1, b2, eps, ibc1, ibc2, grad_scale); adam_one(P1.y, G1.y, M1.y, V1.y, lr, b1, b2, eps, ibc1, ibc2, grad_scale);
       adam_one(P1.z, G1.z, M1.z, V1.z, lr, b1, b2, eps, ibc1, ibc2, grad_scale); adam_one(P1.w, G1.w, M1.w, V1.w, lr, b1, b2, eps, ibc1, ibc2, grad_scale);
       p4[i1] = P1; m4[i1] = M1; v4[i1] = V1;
+      if (kEma) e4[i1] = make_float4(decay * E1.x + omd * P1.x, decay * E1.y + omd * P1.y, decay * E1.z + omd * P1.z, decay * E1.w + omd * P1.w);
     }
   }
   if (blockIdx.x == 0 && threadIdx.x < (int)(n - n4 * 4)) {
     const long long i = n4 * 4 + threadIdx.x;
     adam_one(p[i], g[i], m[i], v[i], lr, b1, b2, eps, ibc1, ibc2, grad_scale);
+    if (kEma) ema[i] = decay * ema[i] + omd * p[i];
   }
 }
 
@@ -781,8 +821,9 @@ extern "C" int b3d_pose_embedding(const double* K, const double* R, const double
   B3D_CHECK_ARG(K && R && t && cond_mask && out, "pose_embedding: null pointer");
   B3D_CHECK_ARG(ld >= 144 && B > 0 && H > 0 && W > 0, "pose_embedding: bad sizes");
   dim3 grid(cdiv(W, 32), H, 2 * B);
-  if (out_fp32) pose_embedding_kernel<float><<<grid, kT, 0, STREAM>>>(K, R, t, cond_mask, pos_emb, first_emb, other_emb, (float*)out, ld, H, W);
-  else pose_embedding_kernel<bf16><<<grid, kT, 0, STREAM>>>(K, R, t, cond_mask, pos_emb, first_emb, other_emb, (bf16*)out, ld, H, W);
+  const int vec_ok = (ld % 8 == 0 && ((uintptr_t)out & 15) == 0) ? 1 : 0;      // 16-byte stores of 8 channels
+  if (out_fp32) pose_embedding_kernel<float><<<grid, 256, 0, STREAM>>>(K, R, t, cond_mask, pos_emb, first_emb, other_emb, (float*)out, ld, H, W, vec_ok);
+  else pose_embedding_kernel<bf16><<<grid, 256, 0, STREAM>>>(K, R, t, cond_mask, pos_emb, first_emb, other_emb, (bf16*)out, ld, H, W, vec_ok);
   DONE(1);
 }
 extern "C" int b3d_pose_embedding_bwd(const float* dP, int64_t ld, int H, int W, float* dpos_emb, float* dfirst, float* dother, void* stream) {
@@ -997,7 +1038,15 @@ extern "C" int b3d_adam(float* p, const float* g, float* m, float* v, int64_t n,
   B3D_CHECK_ARG(p && g && m && v && step >= 1, "adam: args");
   const float bc1 = 1.f - powf(beta1, (float)step), bc2 = 1.f - powf(beta2, (float)step);
   B3D_CHECK_ARG((((uintptr_t)p | (uintptr_t)g | (uintptr_t)m | (uintptr_t)v) & 15) == 0, "adam: arenas must be 16-byte aligned");
-  adam_kernel<<<148 * 8, 256, 0, STREAM>>>(p, g, m, v, n, lr, beta1, beta2, eps, 1.f / bc1, 1.f / bc2, grad_scale);
+  adam_kernel<false><<<148 * 8, 256, 0, STREAM>>>(p, g, m, v, nullptr, n, lr, beta1, beta2, eps, 1.f / bc1, 1.f / bc2, grad_scale, 0.f);
+  DONE(1);
+}
+extern "C" int b3d_adam_ema(float* p, const float* g, float* m, float* v, float* ema, int64_t n, float lr, float beta1, float beta2, float eps,
+                            int step, float grad_scale, float ema_decay, void* stream) {
+  B3D_CHECK_ARG(p && g && m && v && ema && step >= 1 && ema_decay >= 0.f && ema_decay <= 1.f, "adam_ema: args");
+  const float bc1 = 1.f - powf(beta1, (float)step), bc2 = 1.f - powf(beta2, (float)step);
+  B3D_CHECK_ARG((((uintptr_t)p | (uintptr_t)g | (uintptr_t)m | (uintptr_t)v | (uintptr_t)ema) & 15) == 0, "adam_ema: arenas must be 16-byte aligned");
+  adam_kernel<true><<<148 * 8, 256, 0, STREAM>>>(p, g, m, v, ema, n, lr, beta1, beta2, eps, 1.f / bc1, 1.f / bc2, grad_scale, ema_decay);
   DONE(1);
 }
 

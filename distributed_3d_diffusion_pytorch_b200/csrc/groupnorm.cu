@@ -74,11 +74,11 @@ __device__ __forceinline__ void block_sum8(const float* vals, bool active, int v
 }
 
 // ---- stats: raw (sum, sumsq) per (image, group) accumulated with fp32 atomics into ws[N,32,2] (pre-zeroed)
-__global__ void __launch_bounds__(kT) gn_stats_kernel(Src2 s, int HW, int rows_per_block, float* __restrict__ ws) {
+__global__ void __launch_bounds__(kT) gn_stats_kernel(Src2 s, int HW, int rows_per_block, float* __restrict__ ws, int n0) {
   b3d_pdl_sync();
   extern __shared__ float sm[];  // red [256*8] | sum [C] | sumsq [C]
   constexpr int U = 4;
-  const int C = s.C0 + s.C1, cpg = C / G, n = blockIdx.y, vecs = C / 8;
+  const int C = s.C0 + s.C1, cpg = C / G, n = blockIdx.y + n0, vecs = C / 8;
   float* red = sm; float* r_a = sm + 2048; float* r_b = r_a + C;
   const int r0 = blockIdx.x * rows_per_block, r1 = min(HW, r0 + rows_per_block);
   const int rows_par = max(1, (int)blockDim.x / vecs);
@@ -115,13 +115,15 @@ __global__ void __launch_bounds__(kT) gn_stats_kernel(Src2 s, int HW, int rows_p
 // ---- dropout keep-mask of one 8-channel vector: b3d_drop_pair (b3d_common.cuh) hashes (seed, pair index) to 32 bits,
 // 16 per element; an element is dropped when its field is below thr16 = round(p * 65536).
 struct Drop {
-  unsigned long long seedmix;   // (seed + *seed_ptr) * golden ratio
+  unsigned long long seedmix;   // (seed + *seed_ptr * B3D_SEED_STEP_STRIDE) * golden ratio
   unsigned thr_hi;              // thr16 << 16
   float keep;                   // 1 / (1 - p)
 };
 __device__ __forceinline__ Drop make_drop(float p, unsigned long long seed, const unsigned long long* seed_ptr) {
   Drop d;
-  d.seedmix = (seed + (seed_ptr ? *seed_ptr : 0ULL)) * 0x9E3779B97F4A7C15ULL;
+  // the step counter enters with a stride far above any host seed (those number the blocks of a step and the ranks), so
+  // no (block, step) pair shares its mask with another one
+  d.seedmix = (seed + (seed_ptr ? *seed_ptr * B3D_SEED_STEP_STRIDE : 0ULL)) * 0x9E3779B97F4A7C15ULL;
   d.thr_hi = b3d_drop_thr16(p) << 16;
   d.keep = 1.f / (1.f - p);
   return d;
@@ -142,8 +144,9 @@ struct ApplyP {
   const float* gamma; const float* beta;
   bf16* out; long long ld_out;
   int HW, mode;  // 0 plain, 1 silu, 2 film
+  int n0;        // first image of this launch (image-chunked launches, see gn_chunk_images)
   const bf16* ss; long long ld_ss; int F;  // film: scale = ss[row, c], shift = ss[row, F + c]
-  float drop_p; unsigned long long seed; const unsigned long long* seed_ptr;  // effective seed = seed + *seed_ptr (device step counter)
+  float drop_p; unsigned long long seed; const unsigned long long* seed_ptr;  // effective seed = seed + *seed_ptr * B3D_SEED_STEP_STRIDE (device step counter)
 };
 
 constexpr int kApplyU0 = 4, kApplyU2 = 2;   // rows in flight per thread (mode 0/1: one 16 B load per row; film: three)
@@ -163,7 +166,7 @@ __global__ void __launch_bounds__(kT, MODE == 2 ? 3 : 4) gn_apply_kernel(ApplyP 
   b3d_pdl_sync();
   __shared__ float s_mean[G], s_rstd[G];
   constexpr int U = MODE == 2 ? kApplyU2 : kApplyU0;
-  const int C = p.s.C0 + p.s.C1, cpg = C / G, n = blockIdx.y, vecs = C / 8;
+  const int C = p.s.C0 + p.s.C1, cpg = C / G, n = blockIdx.y + p.n0, vecs = C / 8;
   block_stats(p.stats, n, cpg, p.HW, s_mean, s_rstd);
   __syncthreads();
   const int r0 = blockIdx.x * rows_per_block, r1 = min(p.HW, r0 + rows_per_block);
@@ -218,6 +221,7 @@ struct BwdP {
   const float* stats; const float* gamma; const float* beta;
   const bf16* dy; long long ld_dy;
   int HW, mode;
+  int n0;                           // first image of this launch (image-chunked launches, see gn_chunk_images)
   const bf16* ss; long long ld_ss; int F;
   bf16* dss; long long ld_dss;      // film: d(scale) at [row, c], d(shift) at [row, F + c]
   float drop_p; unsigned long long seed; const unsigned long long* seed_ptr;
@@ -258,7 +262,7 @@ __global__ void __launch_bounds__(kT, MODE == 2 ? kBwdBlocks2 : kBwdBlocks1) gn_
   extern __shared__ float sm[];  // red [256*8] | dgamma [C] | dbeta [C] | dscale-sum [C] | dshift-sum [C]
   __shared__ float s_mean[G], s_rstd[G];
   constexpr int U = MODE == 2 ? kBwdU2 : kBwdU1;
-  const int C = p.s.C0 + p.s.C1, cpg = C / G, n = blockIdx.y, vecs = C / 8;
+  const int C = p.s.C0 + p.s.C1, cpg = C / G, n = blockIdx.y + p.n0, vecs = C / 8;
   float* red = sm; float* r_g = sm + 2048; float* r_b = r_g + C; float* r_sc = r_b + C; float* r_sh = r_sc + C;
   const bool want_ss = MODE == 2 && p.dss_sum != nullptr;
   block_stats(p.stats, n, cpg, p.HW, s_mean, s_rstd);
@@ -339,7 +343,7 @@ __global__ void __launch_bounds__(kT, MODE == 2 ? kBwdBlocks2 : kBwdBlocks1) gn_
   extern __shared__ float sm[];   // red [256*8] | column sums of dx [C]   (used when p.dx_sum is set)
   __shared__ float s_mean[G], s_rstd[G], s_c1[G], s_c0[G];
   constexpr int U = kBwdApplyU;
-  const int C = p.s.C0 + p.s.C1, cpg = C / G, n = blockIdx.y, vecs = C / 8;
+  const int C = p.s.C0 + p.s.C1, cpg = C / G, n = blockIdx.y + p.n0, vecs = C / 8;
   block_stats(p.stats, n, cpg, p.HW, s_mean, s_rstd);
   if (threadIdx.x < G) {
     // same thread wrote s_mean/s_rstd[threadIdx.x] above
@@ -435,6 +439,25 @@ int pick_rows_per_block(int N, int HW, int C, int U, int blocks_per_sm, int wave
   return rpb;
 }
 
+// Image-chunked launches: the two passes of a GroupNorm (statistics then apply; reduce then apply in the backward) run over
+// `chunk` images at a time, so the second pass re-reads the tensors from L2 instead of HBM.  gn_chunk_bytes is the budget
+// for the tensors BOTH passes read (0 = one launch pair over all images).
+long long g_gn_chunk_bytes = -1;
+int gn_chunk_images(int N, int HW, int C, int bytes_per_elem) {
+  if (g_gn_chunk_bytes < 0) {
+    const char* e = getenv("B3D_GN_CHUNK_MB");
+    g_gn_chunk_bytes = e ? atoll(e) * (1LL << 20) : 0;
+  }
+  if (g_gn_chunk_bytes <= 0) return N;
+  const long long per_img = (long long)HW * C * bytes_per_elem;
+  long long c = g_gn_chunk_bytes / (per_img > 0 ? per_img : 1);
+  if (c >= N) return N;
+  if (c < 2) c = 2;                 // images come in (cond, target) pairs
+  if (c > 1) c &= ~1LL;
+  // a chunk must still fill the GPU: at least ~4 MB per tensor in flight, else launch latencies dominate
+  return (int)(c < N ? c : N);
+}
+
 int check_src(const void* x0, int C0, const void* x1, int C1) {
   const int C = C0 + C1;
   B3D_CHECK_ARG(x0 != nullptr && C0 > 0, "groupnorm: null input");
@@ -446,21 +469,24 @@ int check_src(const void* x0, int C0, const void* x1, int C1) {
 
 }  // namespace
 
+extern "C" void b3d_set_gn_chunk_mb(int mb) { g_gn_chunk_bytes = (long long)mb * (1LL << 20); }
+
 extern "C" int b3d_gn_stats(const void* x0, int C0, int64_t ld0, const void* x1, int C1, int64_t ld1, int N, int HW, float* ws_sums,
                             void* stream) {
   if (int rc = check_src(x0, C0, x1, C1)) return rc;
   Src2 s{(const bf16*)x0, (const bf16*)x1, C0, C1, ld0, ld1};
   const int C = C0 + C1, rpb = pick_rows_per_block(N, HW, C, 4, 8, 2);   // measured: 2 long waves beat 1, 4 and 8 (block epilogue cost)
   dim3 grid((HW + rpb - 1) / rpb, N);
-  B3D_CUDA(b3d_launch_pdl(gn_stats_kernel, dim3(grid), dim3(kT), (2048 + 2 * C) * sizeof(float), (cudaStream_t)stream, s, HW, rpb, ws_sums));
+  B3D_CUDA(b3d_launch_pdl(gn_stats_kernel, dim3(grid), dim3(kT), (2048 + 2 * C) * sizeof(float), (cudaStream_t)stream, s, HW, rpb, ws_sums, 0));
   B3D_LAUNCH_CHECK();
   b3d_count_launch(1);
   return B3D_OK;
 }
 
-extern "C" int b3d_gn_apply(const void* x0, int C0, int64_t ld0, const void* x1, int C1, int64_t ld1, int N, int HW, const float* sums,
-                            const float* gamma, const float* beta, int mode, const void* ss, int64_t ld_ss, int F, float drop_p,
-                            uint64_t seed, const uint64_t* seed_ptr, void* out, int64_t ld_out, void* stream) {
+static int gn_apply_impl(const void* x0, int C0, int64_t ld0, const void* x1, int C1, int64_t ld1, int N, int HW, float* ws_sums, int with_stats,
+                         const float* gamma, const float* beta, int mode, const void* ss, int64_t ld_ss, int F, float drop_p,
+                         uint64_t seed, const uint64_t* seed_ptr, void* out, int64_t ld_out, void* stream) {
+  const float* sums = ws_sums;
   if (int rc = check_src(x0, C0, x1, C1)) return rc;
   B3D_CHECK_ARG(mode >= 0 && mode <= 2, "gn_apply: mode");
   B3D_CHECK_ARG(mode != 2 || (ss != nullptr && F == C0 + C1), "gn_apply: film needs ss and F == C");
@@ -469,14 +495,44 @@ extern "C" int b3d_gn_apply(const void* x0, int C0, int64_t ld0, const void* x1,
   p.s = Src2{(const bf16*)x0, (const bf16*)x1, C0, C1, ld0, ld1};
   p.stats = sums; p.gamma = gamma; p.beta = beta; p.out = (bf16*)out; p.ld_out = ld_out; p.HW = HW; p.mode = mode;
   p.ss = (const bf16*)ss; p.ld_ss = ld_ss; p.F = F; p.drop_p = drop_p; p.seed = seed; p.seed_ptr = (const unsigned long long*)seed_ptr;
-  const int rpb = pick_rows_per_block(N, HW, C0 + C1, mode == 2 ? kApplyU2 : kApplyU0, mode == 2 ? 3 : 4);
-  dim3 grid((HW + rpb - 1) / rpb, N);
-  if (mode == 0) B3D_CUDA(b3d_launch_pdl(gn_apply_kernel<0>, dim3(grid), dim3(kT), 0, (cudaStream_t)stream, p, rpb));
-  else if (mode == 1) B3D_CUDA(b3d_launch_pdl(gn_apply_kernel<1>, dim3(grid), dim3(kT), 0, (cudaStream_t)stream, p, rpb));
-  else B3D_CUDA(b3d_launch_pdl(gn_apply_kernel<2>, dim3(grid), dim3(kT), 0, (cudaStream_t)stream, p, rpb));
-  B3D_LAUNCH_CHECK();
-  b3d_count_launch(1);
+  // with_stats: statistics pass and apply pass of the same images back to back, chunk by chunk (the apply pass then reads
+  // the chunk from L2); without: one apply launch over all images
+  const int C = C0 + C1;
+  const int chunk = with_stats ? gn_chunk_images(N, HW, C, 2) : N;
+  int launches = 0;
+  for (int n0 = 0; n0 < N; n0 += chunk) {
+    const int nn = N - n0 < chunk ? N - n0 : chunk;
+    p.n0 = n0;
+    if (with_stats) {
+      const int rpb = pick_rows_per_block(nn, HW, C, 4, 8, 2);   // measured: 2 long waves beat 1, 4 and 8 (block epilogue cost)
+      dim3 grid((HW + rpb - 1) / rpb, nn);
+      B3D_CUDA(b3d_launch_pdl(gn_stats_kernel, dim3(grid), dim3(kT), (2048 + 2 * C) * sizeof(float), (cudaStream_t)stream, p.s, HW, rpb, ws_sums, n0));
+      B3D_LAUNCH_CHECK();
+      ++launches;
+    }
+    const int rpb = pick_rows_per_block(nn, HW, C, mode == 2 ? kApplyU2 : kApplyU0, mode == 2 ? 3 : 4);
+    dim3 grid((HW + rpb - 1) / rpb, nn);
+    if (mode == 0) B3D_CUDA(b3d_launch_pdl(gn_apply_kernel<0>, dim3(grid), dim3(kT), 0, (cudaStream_t)stream, p, rpb));
+    else if (mode == 1) B3D_CUDA(b3d_launch_pdl(gn_apply_kernel<1>, dim3(grid), dim3(kT), 0, (cudaStream_t)stream, p, rpb));
+    else B3D_CUDA(b3d_launch_pdl(gn_apply_kernel<2>, dim3(grid), dim3(kT), 0, (cudaStream_t)stream, p, rpb));
+    B3D_LAUNCH_CHECK();
+    ++launches;
+  }
+  b3d_count_launch(launches);
   return B3D_OK;
+}
+
+extern "C" int b3d_gn_apply(const void* x0, int C0, int64_t ld0, const void* x1, int C1, int64_t ld1, int N, int HW, const float* sums,
+                            const float* gamma, const float* beta, int mode, const void* ss, int64_t ld_ss, int F, float drop_p,
+                            uint64_t seed, const uint64_t* seed_ptr, void* out, int64_t ld_out, void* stream) {
+  return gn_apply_impl(x0, C0, ld0, x1, C1, ld1, N, HW, const_cast<float*>(sums), 0, gamma, beta, mode, ss, ld_ss, F, drop_p, seed, seed_ptr, out,
+                       ld_out, stream);
+}
+
+extern "C" int b3d_gn_stats_apply(const void* x0, int C0, int64_t ld0, const void* x1, int C1, int64_t ld1, int N, int HW, float* ws_sums,
+                                  const float* gamma, const float* beta, int mode, const void* ss, int64_t ld_ss, int F, float drop_p,
+                                  uint64_t seed, const uint64_t* seed_ptr, void* out, int64_t ld_out, void* stream) {
+  return gn_apply_impl(x0, C0, ld0, x1, C1, ld1, N, HW, ws_sums, 1, gamma, beta, mode, ss, ld_ss, F, drop_p, seed, seed_ptr, out, ld_out, stream);
 }
 
 extern "C" int b3d_gn_bwd(const void* x0, int C0, int64_t ld0, const void* x1, int C1, int64_t ld1, int N, int HW, const float* sums,
@@ -499,24 +555,32 @@ extern "C" int b3d_gn_bwd(const void* x0, int C0, int64_t ld0, const void* x1, i
   p.add1a = (const bf16*)add1a; p.add1b = (const bf16*)add1b; p.ld_add1a = ld_add1a; p.ld_add1b = ld_add1b;
   const int C = C0 + C1;
   cudaStream_t st = (cudaStream_t)stream;
-  {
-    const int rpb = pick_rows_per_block(N, HW, C, mode == 2 ? kBwdU2 : kBwdU1, mode == 2 ? kBwdBlocks2 : kBwdBlocks1);
-    dim3 grid((HW + rpb - 1) / rpb, N);
-    const size_t smem = (2048 + 4 * C) * sizeof(float);
-    if (mode == 0) B3D_CUDA(b3d_launch_pdl(gn_bwd_reduce_kernel<0>, dim3(grid), dim3(kT), smem, st, p, rpb));
-    else if (mode == 1) B3D_CUDA(b3d_launch_pdl(gn_bwd_reduce_kernel<1>, dim3(grid), dim3(kT), smem, st, p, rpb));
-    else B3D_CUDA(b3d_launch_pdl(gn_bwd_reduce_kernel<2>, dim3(grid), dim3(kT), smem, st, p, rpb));
-    B3D_LAUNCH_CHECK();
+  // bytes both passes read per element: x, dy (+ the FiLM scale)
+  const int chunk = gn_chunk_images(N, HW, C, mode == 2 ? 6 : 4);
+  int launches = 0;
+  for (int n0 = 0; n0 < N; n0 += chunk) {
+    const int nn = N - n0 < chunk ? N - n0 : chunk;
+    p.n0 = n0;
+    {
+      const int rpb = pick_rows_per_block(nn, HW, C, mode == 2 ? kBwdU2 : kBwdU1, mode == 2 ? kBwdBlocks2 : kBwdBlocks1);
+      dim3 grid((HW + rpb - 1) / rpb, nn);
+      const size_t smem = (2048 + 4 * C) * sizeof(float);
+      if (mode == 0) B3D_CUDA(b3d_launch_pdl(gn_bwd_reduce_kernel<0>, dim3(grid), dim3(kT), smem, st, p, rpb));
+      else if (mode == 1) B3D_CUDA(b3d_launch_pdl(gn_bwd_reduce_kernel<1>, dim3(grid), dim3(kT), smem, st, p, rpb));
+      else B3D_CUDA(b3d_launch_pdl(gn_bwd_reduce_kernel<2>, dim3(grid), dim3(kT), smem, st, p, rpb));
+      B3D_LAUNCH_CHECK();
+    }
+    {
+      const int rpb = pick_rows_per_block(nn, HW, C, kBwdApplyU, mode == 2 ? kBwdBlocks2 : kBwdBlocks1);
+      dim3 grid((HW + rpb - 1) / rpb, nn);
+      const size_t smem = (2048 + C) * sizeof(float);
+      if (mode == 0) B3D_CUDA(b3d_launch_pdl(gn_bwd_apply_kernel<0>, dim3(grid), dim3(kT), smem, st, p, rpb));
+      else if (mode == 1) B3D_CUDA(b3d_launch_pdl(gn_bwd_apply_kernel<1>, dim3(grid), dim3(kT), smem, st, p, rpb));
+      else B3D_CUDA(b3d_launch_pdl(gn_bwd_apply_kernel<2>, dim3(grid), dim3(kT), smem, st, p, rpb));
+      B3D_LAUNCH_CHECK();
+    }
+    launches += 2;
   }
-  {
-    const int rpb = pick_rows_per_block(N, HW, C, kBwdApplyU, mode == 2 ? kBwdBlocks2 : kBwdBlocks1);
-    dim3 grid((HW + rpb - 1) / rpb, N);
-    const size_t smem = (2048 + C) * sizeof(float);
-    if (mode == 0) B3D_CUDA(b3d_launch_pdl(gn_bwd_apply_kernel<0>, dim3(grid), dim3(kT), smem, st, p, rpb));
-    else if (mode == 1) B3D_CUDA(b3d_launch_pdl(gn_bwd_apply_kernel<1>, dim3(grid), dim3(kT), smem, st, p, rpb));
-    else B3D_CUDA(b3d_launch_pdl(gn_bwd_apply_kernel<2>, dim3(grid), dim3(kT), smem, st, p, rpb));
-    B3D_LAUNCH_CHECK();
-  }
-  b3d_count_launch(2);
+  b3d_count_launch(launches);
   return B3D_OK;
 }

@@ -118,31 +118,132 @@ def warmup(optimizer, step, last_step, last_lr):
 
 class FusedAdam:
     """Adam(lr, betas=(0.9, 0.99)) (train.py:235, lightning/diff3d.py:106) as ONE kernel over the model's flat
-    fp32 parameter arena; exposes `param_groups[0]['lr']` so `warmup` works unchanged."""
+    fp32 parameter arena; exposes `param_groups[0]['lr']` so `warmup` works unchanged.
 
-    def __init__(self, model: XUNet, lr=1e-4, betas=(0.9, 0.99), eps=1e-8):
+    ema_decay (optional): the exponential moving average of the parameters that the reference only describes
+    (lightning/diff3d.py:11-19), kept in a second flat arena by the same kernel (`ema_state_dict()` gives it under the
+    model's parameter names).
+
+    Checkpoints: `state_dict()` emits, and `load_state_dict()` accepts, the layout of `torch.optim.Adam.state_dict()` that
+    the reference stores under ckpt['optim'] (train.py:247-251,289,298): per-parameter `exp_avg` / `exp_avg_sq` / `step` in
+    parameter-registration order.  The compact flat layout {step, m, v, lr} of earlier versions still loads."""
+
+    def __init__(self, model: XUNet, lr=1e-4, betas=(0.9, 0.99), eps=1e-8, ema_decay=None):
         self.model = model
         self.param_groups = [{"lr": lr, "betas": betas, "eps": eps, "params": list(model.parameters())}]
         self.step_count = 0
         self.m = self.v = None
+        self.ema_decay, self.ema = ema_decay, None
 
     def zero_grad(self, set_to_none=True):
         pass                                    # the engine overwrites the flat gradient arena every backward
 
-    def step(self, grad_scale=1.0):
-        flat, g = self.model.flat_parameters(), self.model.flat_gradients()
+    def _arenas(self):
+        flat = self.model.flat_parameters()
         if self.m is None or self.m.shape != flat.shape or self.m.device != flat.device:
             self.m, self.v = torch.zeros_like(flat), torch.zeros_like(flat)
+        if self.ema_decay is not None and (self.ema is None or self.ema.shape != flat.shape or self.ema.device != flat.device):
+            self.ema = flat.clone()
+        return flat
+
+    def step(self, grad_scale=1.0):
+        flat, g = self._arenas(), self.model.flat_gradients()
         self.step_count += 1
         pg = self.param_groups[0]
-        _ops(flat.device).adam(flat, g, self.m, self.v, pg["lr"], pg["betas"][0], pg["betas"][1], pg["eps"], self.step_count, grad_scale)
+        _ops(flat.device).adam(flat, g, self.m, self.v, pg["lr"], pg["betas"][0], pg["betas"][1], pg["eps"], self.step_count, grad_scale,
+                               ema=self.ema, ema_decay=self.ema_decay or 0.0)
 
-    def state_dict(self):
-        return {"step": self.step_count, "m": self.m, "v": self.v, "lr": self.param_groups[0]["lr"]}
+    def ema_state_dict(self):
+        """EMA weights under the model's state_dict names (load them into an XUNet to sample with them)"""
+        assert self.ema is not None, "FusedAdam was built without ema_decay"
+        m = self.model
+        return {n: self.ema[o:o + p.numel()].view(p.shape).clone() for n, p, o in zip(m._names, m._plist, m._offs)}
+
+    def state_dict(self, torch_format=True):
+        m = self.model
+        flat = self._arenas()
+        if not torch_format:
+            return {"step": self.step_count, "m": self.m, "v": self.v, "lr": self.param_groups[0]["lr"], "ema": self.ema}
+        pg = self.param_groups[0]
+        state = {}
+        if self.step_count > 0:
+            for i, (p, o) in enumerate(zip(m._plist, m._offs)):
+                state[i] = {"step": torch.tensor(float(self.step_count)), "exp_avg": self.m[o:o + p.numel()].view(p.shape).clone(),
+                            "exp_avg_sq": self.v[o:o + p.numel()].view(p.shape).clone()}
+        group = {"lr": pg["lr"], "betas": tuple(pg["betas"]), "eps": pg["eps"], "weight_decay": 0, "amsgrad": False, "maximize": False,
+                 "foreach": None, "capturable": False, "differentiable": False, "fused": None, "params": list(range(len(m._plist)))}
+        sd = {"state": state, "param_groups": [group]}
+        if self.ema is not None:
+            sd["b3d_ema"] = self.ema.clone()          # extra key: ignored by torch.optim.Adam.load_state_dict
+        return sd
 
     def load_state_dict(self, sd):
-        self.step_count, self.m, self.v = sd["step"], sd["m"], sd["v"]
-        self.param_groups[0]["lr"] = sd["lr"]
+        m = self.model
+        flat = self._arenas()
+        if isinstance(sd, dict) and "m" in sd and "v" in sd:                      # compact flat layout
+            self.step_count = int(sd["step"])
+            self.m.copy_(sd["m"])
+            self.v.copy_(sd["v"])
+            self.param_groups[0]["lr"] = sd["lr"]
+            if sd.get("ema") is not None and self.ema is not None:
+                self.ema.copy_(sd["ema"])
+            return
+        if not (isinstance(sd, dict) and "state" in sd and "param_groups" in sd):
+            raise ValueError("FusedAdam.load_state_dict: expected a torch.optim.Adam state_dict ({'state', 'param_groups'}) or the flat "
+                             f"{{'step','m','v','lr'}} layout, got keys {sorted(sd.keys()) if isinstance(sd, dict) else type(sd)}")
+        groups = sd["param_groups"]
+        ids = [i for g_ in groups for i in g_["params"]]
+        if len(ids) != len(m._plist):
+            raise ValueError(f"optimizer state covers {len(ids)} parameters, the model has {len(m._plist)}")
+        steps = set()
+        self.m.zero_()
+        self.v.zero_()
+        for pid, p, o, name in zip(ids, m._plist, m._offs, m._names):
+            st = sd["state"].get(pid)
+            if st is None:
+                continue                                   # parameter that never received a gradient: zero moments
+            if tuple(st["exp_avg"].shape) != tuple(p.shape):
+                raise ValueError(f"optimizer state of {name}: shape {tuple(st['exp_avg'].shape)} != parameter shape {tuple(p.shape)}")
+            self.m[o:o + p.numel()].view(p.shape).copy_(st["exp_avg"])
+            self.v[o:o + p.numel()].view(p.shape).copy_(st["exp_avg_sq"])
+            steps.add(int(float(st["step"])))
+        if len(steps) > 1:
+            raise ValueError(f"per-parameter Adam step counts differ ({sorted(steps)}): one fused step count cannot represent them")
+        self.step_count = steps.pop() if steps else 0
+        g0 = groups[0]
+        self.param_groups[0]["lr"] = g0["lr"]
+        self.param_groups[0]["betas"] = tuple(g0.get("betas", self.param_groups[0]["betas"]))
+        self.param_groups[0]["eps"] = g0.get("eps", self.param_groups[0]["eps"])
+        if g0.get("weight_decay", 0) != 0 or g0.get("amsgrad", False):
+            raise ValueError("FusedAdam implements the reference's plain Adam (no weight decay, no amsgrad)")
+        if sd.get("b3d_ema") is not None and self.ema is not None:
+            self.ema.copy_(sd["b3d_ema"])
+
+
+def save_checkpoint(path, model, optimizer, step, epoch=None, module_prefix=False):
+    """The reference's checkpoint file (train.py:289,298): {'optim': Adam state_dict, 'model': state_dict, 'step'[, 'epoch']}.
+    module_prefix=True writes the `module.`-prefixed keys of a checkpoint saved from DataParallel/DDP (what the public
+    pretrained checkpoint and sampling.py:52-56 use)."""
+    msd = {("module." + k if module_prefix else k): v.detach().cpu().clone() for k, v in model.state_dict().items()}
+    osd = optimizer.state_dict()
+    if "state" in osd:
+        osd = {**osd, "state": {i: {k: v.cpu() if torch.is_tensor(v) else v for k, v in st.items()} for i, st in osd["state"].items()}}
+        if osd.get("b3d_ema") is not None:
+            osd["b3d_ema"] = osd["b3d_ema"].cpu()
+    ckpt = {"optim": osd, "model": msd, "step": step}
+    if epoch is not None:
+        ckpt["epoch"] = epoch
+    torch.save(ckpt, path)
+    return ckpt
+
+
+def load_checkpoint(path, model, optimizer=None, map_location="cpu"):
+    """train.py:246-251: restores model (with or without the `module.` prefix), optimizer state and returns the step"""
+    ckpt = torch.load(path, map_location=map_location, weights_only=False)
+    model.load_state_dict(ckpt["model"])
+    if optimizer is not None and ckpt.get("optim") is not None:
+        optimizer.load_state_dict(ckpt["optim"])
+    return ckpt.get("step", 0)
 
 
 try:                                            # Lightning is optional (not in this image)
@@ -169,7 +270,7 @@ class Diff3D(_Base):
         self.xunet_denoiser = XUNet(H=self.image_size, W=self.image_size, ch=128)
         if pretrained_model is not None:
             print('[-] Loading pre-trained model: ', pretrained_model)
-            ckpt = torch.load(pretrained_model)
+            ckpt = torch.load(pretrained_model, map_location="cpu", weights_only=False)
             self.xunet_denoiser.load_state_dict(ckpt['model'])
             self.pretrained_optim = ckpt['optim']
 
@@ -226,7 +327,7 @@ class Diff3D(_Base):
         """lightning/diff3d.py:104-116; the optimizer is the fused flat-arena Adam."""
         self.xunet_denoiser.fused_grads = True
         optimizer = FusedAdam(self.xunet_denoiser, lr=self.lr, betas=(0.9, 0.99))
-        if self.pretrained_optim is not None and "m" in self.pretrained_optim:
+        if self.pretrained_optim is not None:          # torch Adam layout (the reference's ckpt['optim']) or the flat one; else raises
             optimizer.load_state_dict(self.pretrained_optim)
         if self.use_scheduler:
             self._scheduler = _CosineLR(optimizer, T_max=300)

@@ -343,9 +343,8 @@ class Engine:
         hh, ww, C = h.t.shape[1], h.t.shape[2], h.t.shape[3]
         sums = self.zbuf("fwd", "lastgn.sums", (N, 32, 2))
         x3 = h.t.view(N, hh * ww, C)
-        ops.gn_stats(x3, None, sums)
         al = self.buf("lastgn.a", (N, hh * ww, C))
-        ops.gn_apply(x3, None, sums, P["lastgn.gn.weight"], P["lastgn.gn.bias"], 1, al)
+        ops.gn_stats_apply(x3, None, sums, P["lastgn.gn.weight"], P["lastgn.gn.bias"], 1, al)
         y = self.buf("lastconv.y", (N, H, Wd, 16))
         ops.gemm(G.conv_desc([al.view(N, H, Wd, C)], [9], Wp["lastconv.weight"], 3, y, bias=self._bufs["lastconv.b16"]))
         eps = self.buf("eps", (B, 3, H, Wd), torch.float32)
@@ -377,19 +376,17 @@ class Engine:
         x0 = h_in.t.view(N, HW, -1)
         x1 = skip.t.view(N, HW, -1) if skip is not None else None
         sums0 = self.zbuf("fwd", n + ".s0", (N, 32, 2))
-        ops.gn_stats(x0, x1, sums0)
         a0 = self.buf(n + ".a0", (N, HW, s.cin))
-        ops.gn_apply(x0, x1, sums0, P[n + ".groupnorm0.gn.weight"], P[n + ".groupnorm0.gn.bias"], 1, a0)
+        ops.gn_stats_apply(x0, x1, sums0, P[n + ".groupnorm0.gn.weight"], P[n + ".groupnorm0.gn.bias"], 1, a0)
         c1 = self.buf(n + ".c1", (N, hh, ww, F))
         sums1 = self.zbuf("fwd", n + ".s1", (N, 32, 2))
         c13 = c1.view(N, HW, F)
         # conv1's epilogue also sums the GroupNorm statistics of its output when the tile geometry allows it
-        if not self._gemm_stats(G.conv_desc([a0.view(N, hh, ww, s.cin)], [9], Wp[n + ".conv1.weight"], F, c1, bias=P[n + ".conv1.bias"]),
-                                sums1, F):
-            ops.gn_stats(c13, None, sums1)
+        fused = self._gemm_stats(G.conv_desc([a0.view(N, hh, ww, s.cin)], [9], Wp[n + ".conv1.weight"], F, c1, bias=P[n + ".conv1.bias"]),
+                                 sums1, F)
         a1 = self.buf(n + ".a1", (N, HW, F))
         ssv = ss_l[:, s.film_off:s.film_off + 2 * F]
-        ops.gn_apply(c13, None, sums1, P[n + ".groupnorm1.gn.weight"], P[n + ".groupnorm1.gn.bias"], 2, a1, ss=ssv, F=F, drop_p=drop_p,
+        (ops.gn_apply if fused else ops.gn_stats_apply)(c13, None, sums1, P[n + ".groupnorm1.gn.weight"], P[n + ".groupnorm1.gn.bias"], 2, a1, ss=ssv, F=F, drop_p=drop_p,
                      seed=seed, seed_ptr=self.seed_ptr)
         if s.cin != F:
             sk = self.buf(n + ".sk", (N, hh, ww, F))
@@ -428,9 +425,8 @@ class Engine:
         a = n + ".attn_layer.attn"
         x3 = h_in.t.view(N, L, C)
         sums = self.zbuf("fwd", n + ".s", (N, 32, 2))
-        ops.gn_stats(x3, None, sums)
         g = self.buf(n + ".g", (N, L, C))
-        ops.gn_apply(x3, None, sums, P[n + ".groupnorm.gn.weight"], P[n + ".groupnorm.gn.bias"], 0, g)
+        ops.gn_stats_apply(x3, None, sums, P[n + ".groupnorm.gn.weight"], P[n + ".groupnorm.gn.bias"], 0, g)
         qkv = self.buf(n + ".qkv", (N, L, 3 * C))
         ops.gemm(G.dense_desc(g.view(N * L, C), Wp[a + ".in_proj_weight"], qkv.view(N * L, 3 * C), 3 * C, bias=P[a + ".in_proj_bias"]))
         q, k, v = self._qkv_views(qkv, L, C)

@@ -450,6 +450,13 @@ class CudaOps:
                    _ptr(ss), c_i64(ss.stride(0) if ss is not None else 0), c_i32(F), c_f32(drop_p), ctypes.c_uint64(seed), _ptr(seed_ptr),
                    _ptr(out), c_i64(out.stride(1)), self.stream())
 
+    def gn_stats_apply(self, x0, x1, sums, gamma, beta, mode, out, ss=None, F=0, drop_p=0.0, seed=0, seed_ptr=None):
+        """gn_stats + gn_apply of the same input as one call (image-chunked for L2 reuse when a chunk budget is set)"""
+        N, HW, _ = x0.shape
+        self._call("b3d_gn_stats_apply", *self._src(x0), *self._src(x1), c_i32(N), c_i32(HW), _ptr(sums), _ptr(gamma), _ptr(beta), c_i32(mode),
+                   _ptr(ss), c_i64(ss.stride(0) if ss is not None else 0), c_i32(F), c_f32(drop_p), ctypes.c_uint64(seed), _ptr(seed_ptr),
+                   _ptr(out), c_i64(out.stride(1)), self.stream())
+
     def gn_bwd(self, x0, x1, sums, gamma, beta, mode, dy, dgamma, dbeta, ws, dx0, dx1=None, ss=None, F=0, dss=None, drop_p=0.0, seed=0,
                add0=None, add1a=None, add1b=None, seed_ptr=None, dss_sum=None, dx_sum=None):
         N, HW, _ = x0.shape
@@ -477,15 +484,23 @@ class CudaOps:
 
     def sampler_update(self, z, eps_c, eps_u, w, noise, out, logsnr, logsnr_next):
         B = z.shape[0]
+        assert w.dtype == torch.float32 and w.is_contiguous() and w.numel() == B, "w: one fp32 guidance weight per image"
         self._call("b3d_sampler_update", _ptr(z), _ptr(eps_c), _ptr(eps_u), _ptr(w), _ptr(noise), _ptr(out), c_f32(float(logsnr)),
                    c_f32(float(logsnr_next)), c_i32(B), c_i64(z.numel() // B), self.stream())
 
     def sampler_update_dev(self, z, eps_c, eps_u, w, noise, out, sched):
         B = z.shape[0]
         assert sched.dtype == torch.float32 and sched.numel() >= 2
+        assert w.dtype == torch.float32 and w.is_contiguous() and w.numel() == B, "w: one fp32 guidance weight per image"
         self._call("b3d_sampler_update_dev", _ptr(z), _ptr(eps_c), _ptr(eps_u), _ptr(w), _ptr(noise), _ptr(out), _ptr(sched), c_i32(B),
                    c_i64(z.numel() // B), self.stream())
 
-    def adam(self, p, g, m, v, lr, beta1, beta2, eps, step, grad_scale=1.0):
-        self._call("b3d_adam", _ptr(p), _ptr(g), _ptr(m), _ptr(v), c_i64(p.numel()), c_f32(lr), c_f32(beta1), c_f32(beta2), c_f32(eps),
-                   c_i32(step), c_f32(grad_scale), self.stream())
+    def adam(self, p, g, m, v, lr, beta1, beta2, eps, step, grad_scale=1.0, ema=None, ema_decay=0.0):
+        """ema (optional, fp32 like p): ema = ema_decay * ema + (1 - ema_decay) * p_new, in the same pass"""
+        if ema is None:
+            self._call("b3d_adam", _ptr(p), _ptr(g), _ptr(m), _ptr(v), c_i64(p.numel()), c_f32(lr), c_f32(beta1), c_f32(beta2), c_f32(eps),
+                       c_i32(step), c_f32(grad_scale), self.stream())
+        else:
+            assert ema.dtype == torch.float32 and ema.numel() == p.numel()
+            self._call("b3d_adam_ema", _ptr(p), _ptr(g), _ptr(m), _ptr(v), _ptr(ema), c_i64(p.numel()), c_f32(lr), c_f32(beta1), c_f32(beta2),
+                       c_f32(eps), c_i32(step), c_f32(grad_scale), c_f32(ema_decay), self.stream())

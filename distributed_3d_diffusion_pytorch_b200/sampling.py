@@ -28,6 +28,16 @@ def _t(a, dev, dtype):
     return a.to(device=dev, dtype=dtype)
 
 
+def _guidance(w, b, dev):
+    """guidance weights as fp32 [b]: the update kernel reads w[i] for image i, so a python scalar (the reference's `w=2.0`
+    default, lightning/diff3d.py:200) is broadcast and any other length is refused here -- the C ABI cannot see the length"""
+    w = _t(w, dev, torch.float32)
+    if w.dim() == 0:
+        w = w.expand(b)
+    assert w.dim() == 1 and w.numel() == b, f"guidance weights: expected {b} values (one per image), got shape {tuple(w.shape)}"
+    return w.contiguous()
+
+
 def xt2batch(x, logsnr, z, R, T, K):
     """sampling.py:65-76 (K is one [3,3] matrix repeated over the batch)."""
     b = x.shape[0]
@@ -74,7 +84,7 @@ def p_mean_variance(model, x, z, R, T, K, logsnr, logsnr_next, w):
     mean = torch.empty_like(z)
     # the same kernel as p_sample with a zero noise tensor gives the mean alone
     zero = torch.zeros_like(z) if float(logsnr_next) != 0.0 else None
-    _ops(dev).sampler_update(z.contiguous(), eps_c.contiguous(), eps_u.contiguous(), _t(w, dev, torch.float32), zero, mean, float(logsnr),
+    _ops(dev).sampler_update(z.contiguous(), eps_c.contiguous(), eps_u.contiguous(), _guidance(w, z.shape[0], dev), zero, mean, float(logsnr),
                              float(logsnr_next))
     lam, lam_n = torch.as_tensor(float(logsnr)), torch.as_tensor(float(logsnr_next))
     var = (-lam_n).sigmoid() * (-torch.special.expm1(lam - lam_n))
@@ -90,7 +100,7 @@ def p_sample(model, z, x, R, T, K, logsnr, logsnr_next, w, noise=None, generator
     if noise is None and float(logsnr_next) != 0.0:
         noise = torch.randn(z.shape, device=dev, dtype=torch.float32, generator=generator)
     out = torch.empty_like(z)
-    _ops(dev).sampler_update(z, eps_c.contiguous(), eps_u.contiguous(), _t(w, dev, torch.float32),
+    _ops(dev).sampler_update(z, eps_c.contiguous(), eps_u.contiguous(), _guidance(w, z.shape[0], dev),
                              _t(noise, dev, torch.float32).contiguous() if noise is not None else None, out, float(logsnr), float(logsnr_next))
     return out
 
@@ -100,9 +110,9 @@ def sample(model, record, target_R, target_T, K, w, timesteps=256, generator=Non
     """sampling.py:130-155: 256-step ancestral loop; each step conditions on a random entry of `record`
     (python `random.choice`, as the reference).  Returns np.ndarray [b,3,H,W]."""
     dev = _dev(model)
-    w = _t(w, dev, torch.float32)
-    b = w.shape[0]
     first = _t(record[0][0], dev, torch.float32)
+    b = first.shape[0]
+    w = _guidance(w, b, dev)
     img = torch.randn(first.shape, device=dev, dtype=torch.float32, generator=generator)
     logsnrs = logsnr_schedule_cosine(torch.linspace(1., 0., timesteps + 1)[:-1])
     logsnr_nexts = logsnr_schedule_cosine(torch.linspace(1., 0., timesteps + 1)[1:])
@@ -182,8 +192,21 @@ class GraphSampler:
         self.logsnr2[:, 0] = float(logsnr_schedule_cosine(torch.zeros(1))[0])
         self.mask = torch.cat([torch.ones(b, dtype=torch.uint8), torch.zeros(b, dtype=torch.uint8)]).to(self.dev)
         self.out = torch.zeros(b, 3, H, W, **f32)
-        self.engine = m._engine(2 * b)
+        # a private engine: its buffers (and, while training goes on elsewhere, the saved activations of the model's own
+        # engines) are never shared with a training step of the same batch size
+        m._engine(2 * b)                                       # makes sure the model's kernel backend exists (raises on CPU)
+        from .engine import Engine
+        self.engine = Engine(m.cfg, m._ops, 2 * b)
         self.use_graph, self.graph, self.steps_done = use_graph, None, 0
+        self._weights_fresh = False
+
+    def refresh_weights(self):
+        """repack the bf16 GEMM operands from the model's current fp32 parameters (the captured step only READS them).
+        `sample()` does this at the start of every call, so training or load_state_dict between calls is picked up."""
+        P = dict(zip(self.model._names, self.model._plist))
+        self.engine._assign_cat_sources()
+        self.engine._pack_weights(P, False, True)
+        self._weights_fresh = True
 
     def _compute(self):
         b = self.b
@@ -194,7 +217,7 @@ class GraphSampler:
         self.logsnr2[:, 1].copy_(self.sched[0].expand(2 * b))
         P = dict(zip(self.model._names, self.model._plist))
         eps = self.engine.forward(P, self.x, self.xz, self.logsnr2, self.R, self.T, self.K, self.mask, training=self.model.training,
-                                  need_bwd=False, seed=0, repack=self.steps_done == 0)     # weights are frozen while sampling
+                                  need_bwd=False, seed=0, repack=False)     # operands packed by refresh_weights()
         self.ops.sampler_update_dev(self.z, eps[:b], eps[b:], self.w, self.noise, self.out, self.sched)
         self.z.copy_(self.out)
 
@@ -211,6 +234,8 @@ class GraphSampler:
     def step(self, logsnr, logsnr_next):
         self.sched[0] = float(logsnr)
         self.sched[1] = float(logsnr_next)
+        if not self._weights_fresh:
+            self.refresh_weights()
         if self.use_graph and self.graph is None and self.steps_done >= 1:
             torch.cuda.synchronize()
             g = torch.cuda.CUDAGraph()
@@ -226,7 +251,8 @@ class GraphSampler:
     @torch.no_grad()
     def sample(self, record, target_R, target_T, K, w, timesteps=256):
         """sampling.py:130-155 on the captured step"""
-        self.w.copy_(_t(w, self.dev, torch.float32))
+        self.refresh_weights()
+        self.w.copy_(_guidance(w, self.b, self.dev))
         self.z.normal_()
         ts = torch.linspace(1., 0., timesteps + 1)
         logsnrs, logsnr_nexts = logsnr_schedule_cosine(ts[:-1]), logsnr_schedule_cosine(ts[1:])

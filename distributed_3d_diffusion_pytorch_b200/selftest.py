@@ -23,6 +23,16 @@ def parity_metrics(model_kw, B, seed, cond_mask, device="cuda:0"):
     x_cond = torch.where(cm[:, None, None, None], img[:, 0], xrep)
     batch = dr.make_batch(x_cond, logsnr, z_noisy, R, T, K)
 
+    # the CUDA path first (the b3d kernels are the first launches a profiler or launch capture of this function sees)
+    model = XUNet(**model_kw).to(device)
+    model.load_state_dict(sd)
+    model.eval()                                   # dropout off on both sides (H2)
+    bd = {k: v.to(device) for k, v in batch.items()}
+    eps = model(bd, cond_mask=cm.to(device))
+    loss = diffusion_loss(noise.to(device), eps)
+    loss.backward()
+    torch.cuda.synchronize()
+
     # oracle (fp32, on the GPU when the model is large, TF32 off)
     odev = torch.device(device if model_kw["H"] >= 32 else "cpu")
     torch.backends.cudnn.allow_tf32 = False
@@ -32,15 +42,6 @@ def parity_metrics(model_kw, B, seed, cond_mask, device="cuda:0"):
     eps_o = xr.xunet_forward(sdo, ocfg, bo, cm.to(odev))
     loss_o = dr.loss_fn(noise.to(odev), eps_o)
     loss_o.backward()
-
-    model = XUNet(**model_kw).to(device)
-    model.load_state_dict(sd)
-    model.eval()                                   # dropout off on both sides (H2)
-    bd = {k: v.to(device) for k, v in batch.items()}
-    eps = model(bd, cond_mask=cm.to(device))
-    loss = diffusion_loss(noise.to(device), eps)
-    loss.backward()
-    torch.cuda.synchronize()
 
     eo = eps_o.detach().float().cpu()
     e = eps.detach().float().cpu()

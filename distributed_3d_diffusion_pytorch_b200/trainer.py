@@ -19,17 +19,36 @@ from .ops import CudaOps
 from .xunet import XUNet
 
 
+def phase_ranges(names, offs, numel, prefixes):
+    """Element ranges [lo, hi) of the flat gradient arena that each backward phase finalises (engine.PHASE_PREFIXES).
+    The arena is laid out in parameter-registration order: conditioningprocessor, conv (phase 2) | xunetblocks, middle
+    (phase 1) | upsample, lastgn, lastconv (phase 0).  Refuses any layout in which the phases are not three contiguous runs
+    covering [0, numel) exactly once: a gap would leave gradients un-reduced, silently."""
+    def phase_of(n):
+        hits = [ph for ph, pre in enumerate(prefixes) if n.startswith(pre)]
+        assert len(hits) == 1, f"parameter {n} belongs to {len(hits)} backward phases"
+        return hits[0]
+    seq = [phase_of(n) for n in names]
+    runs = [(ph, o) for i, (ph, o) in enumerate(zip(seq, offs)) if i == 0 or seq[i - 1] != ph]
+    assert [ph for ph, _ in runs] == [2, 1, 0], f"flat arena is not ordered phase 2 | phase 1 | phase 0: {[ph for ph, _ in runs]}"
+    assert runs[0][1] == 0
+    return {2: (0, runs[1][1]), 1: (runs[1][1], runs[2][1]), 0: (runs[2][1], numel)}
+
+
 class Trainer:
-    def __init__(self, model_kw, B, device, world=1, seed=0, use_graph=True, lr=1e-4, cond_prob=0.1, init_sd=None):
+    def __init__(self, model_kw, B, device, world=1, seed=0, use_graph=True, lr=1e-4, cond_prob=0.1, init_sd=None, ema_decay=None):
         self.B, self.dev, self.world = B, torch.device(device), world
-        torch.manual_seed(seed)
+        # every rank draws its own noise / logsnr / cond-mask / dropout streams (SURVEY 8e): the rank enters the seed here, so
+        # callers pass the same `seed` on all ranks (the initial weights are rank 0's, broadcast below)
+        self.seed = int(seed) + parallel.rank()
+        torch.manual_seed(self.seed)
         self.model = XUNet(**model_kw).to(self.dev)
         if init_sd is not None:
             self.model.load_state_dict(init_sd)
         parallel.broadcast_parameters(self.model.flat_parameters())   # DDP's rank-0 broadcast (train.py:230)
         self.model.train()
         self.model.fused_grads = True
-        self.opt = FusedAdam(self.model, lr=lr, betas=(0.9, 0.99))
+        self.opt = FusedAdam(self.model, lr=lr, betas=(0.9, 0.99), ema_decay=ema_decay)
         self.ops = CudaOps(self.dev)
         # launch-latency hiding pays for small per-GPU batches only (measured: +1.9% at 16 pairs, -0.6% at 128 of 64x64)
         from . import _lib
@@ -82,7 +101,7 @@ class Trainer:
         self.logsnr2[:, 1].copy_(self.logsnr)
         P = dict(zip(self.model._names, self.model._plist))
         eps = self.engine.forward(P, self.x_cond, self.z_noisy, self.logsnr2, self.R, self.T, self.K, self.mask, training=True, need_bwd=True,
-                                  seed=0)
+                                  seed=self.seed % 1000003)
         self.ops.loss(self.noise, eps, self.deps, 0, self.scratch, self.loss)
 
     def _backward(self, phase=None):
@@ -93,16 +112,8 @@ class Trainer:
         self._backward()
 
     def _phase_ranges(self):
-        """element ranges of the flat gradient arena that each backward phase finalises (engine.PHASE_PREFIXES)"""
         m = self.model
-        first = {}
-        for n, o in zip(m._names, m._offs):
-            for ph, pre in enumerate(self.engine.PHASE_PREFIXES):
-                if n.startswith(pre) and ph not in first:
-                    first[ph] = o
-        end = m._grad_flat.numel()
-        # arena order: conditioningprocessor, conv (phase 2) | xunetblocks, middle (phase 1) | upsample, lastgn, lastconv (phase 0)
-        return {2: (0, first[1]), 1: (first[1], first[0]), 0: (first[0], end)}
+        return phase_ranges(m._names, m._offs, m._grad_flat.numel(), self.engine.PHASE_PREFIXES)
 
     def _finish(self):
         parallel.allreduce_mean_(self.model._grad_flat)

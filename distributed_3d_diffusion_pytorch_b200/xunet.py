@@ -94,12 +94,20 @@ class _XUNetFn(torch.autograd.Function):
         eng = model._engine(x.shape[0])
         P = dict(zip(model._names, params))
         eps = eng.forward(P, x, z, logsnr, R, t, K, cond_mask, training=model.training, need_bwd=need_bwd, seed=seed)
-        ctx.model, ctx.eng = model, eng
+        # the activations a backward needs live in the engine (one set per batch size), not in ctx: remember which forward
+        # they belong to, so a backward that arrives after another forward of the same batch size fails instead of silently
+        # using the other call's activations
+        eng.generation = getattr(eng, "generation", 0) + 1
+        ctx.model, ctx.eng, ctx.generation = model, eng, eng.generation
         return eps.clone()
 
     @staticmethod
     def backward(ctx, deps):
         model, eng = ctx.model, ctx.eng
+        if ctx.generation != eng.generation:
+            raise RuntimeError("XUNet backward: another forward with the same batch size ran since this one; the engine keeps ONE set of "
+                               "saved activations per batch size (run backward before the next forward, or use different batch sizes). "
+                               "Gradients are also overwritten, not accumulated, by every backward.")
         Gr = model._grad_views()
         eng.backward(Gr, deps.contiguous().float(), grad_flat=model._grad_flat)
         if model.fused_grads:

@@ -179,6 +179,15 @@ int b3d_gn_stats(const void* x0, int C0, int64_t ld0, const void* x1, int C1, in
 int b3d_gn_apply(const void* x0, int C0, int64_t ld0, const void* x1, int C1, int64_t ld1, int N, int HW, const float* sums,
                  const float* gamma, const float* beta, int mode, const void* ss, int64_t ld_ss, int F, float drop_p, uint64_t seed, const uint64_t* seed_ptr,
                  void* out, int64_t ld_out, void* stream);
+/* b3d_gn_stats followed by b3d_gn_apply on the same input (ws_sums pre-zeroed by the caller, left holding the sums for the
+ * backward pass).  Both passes run over a chunk of images at a time when a chunk budget is set, so the apply pass reads
+ * the chunk from L2 rather than from HBM; b3d_gn_bwd chunks its reduce / apply passes the same way. */
+int b3d_gn_stats_apply(const void* x0, int C0, int64_t ld0, const void* x1, int C1, int64_t ld1, int N, int HW, float* ws_sums,
+                       const float* gamma, const float* beta, int mode, const void* ss, int64_t ld_ss, int F, float drop_p, uint64_t seed,
+                       const uint64_t* seed_ptr, void* out, int64_t ld_out, void* stream);
+/* budget (MB) for the tensors both passes of a GroupNorm read per image chunk; 0 = no chunking.  Default: the
+ * environment's B3D_GN_CHUNK_MB, else 0.  A tuning knob of this library, no reference counterpart. */
+void b3d_set_gn_chunk_mb(int mb);
 int b3d_gn_bwd(const void* x0, int C0, int64_t ld0, const void* x1, int C1, int64_t ld1, int N, int HW, const float* sums,
                const float* gamma, const float* beta, int mode, const void* dy, int64_t ld_dy, const void* ss, int64_t ld_ss, int F,
                void* dss, int64_t ld_dss, float drop_p, uint64_t seed, const uint64_t* seed_ptr, float* dgamma, float* dbeta, float* dss_sum,
@@ -218,6 +227,10 @@ int b3d_sampler_update_dev(const float* z, const float* eps_c, const float* eps_
 /* torch.optim.Adam(lr, betas) step over a flat fp32 arena: train.py:235,278 / lightning/diff3d.py:106 */
 int b3d_adam(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2, float eps, int step,
              float grad_scale, void* stream);
+/* the same step plus the exponential moving average of the parameters that lightning/diff3d.py:11-19 describes (and never
+ * implements): ema = ema_decay * ema + (1 - ema_decay) * p_new, in the same pass (36 instead of 28 bytes per parameter) */
+int b3d_adam_ema(float* p, const float* g, float* m, float* v, float* ema, int64_t n, float lr, float beta1, float beta2, float eps,
+                 int step, float grad_scale, float ema_decay, void* stream);
 
 #ifdef __cplusplus
 }

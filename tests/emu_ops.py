@@ -20,6 +20,9 @@ def _ceil64(c):
     return (c + 63) // 64 * 64
 
 
+SEED_STEP_STRIDE = 0x100000001B3      # B3D_SEED_STEP_STRIDE in csrc/b3d_common.cuh
+
+
 def drop_keep(seed, idx, drop_p):
     """bit-exact mirror of the dropout keep decision (b3d_drop_pair / b3d_drop_thr16 in csrc/b3d_common.cuh, drop_mask8
     in csrc/groupnorm.cu) on an int64 tensor of flat element indices: True where the element is kept."""
@@ -431,7 +434,7 @@ class EmuOps:
         return torch.where(keep, torch.full(shape, 1.0 / (1.0 - drop_p)), torch.zeros(shape))
 
     def gn_apply(self, x0, x1, sums, gamma, beta, mode, out, ss=None, F=0, drop_p=0.0, seed=0, seed_ptr=None):
-        seed = seed + (int(seed_ptr.item()) if seed_ptr is not None else 0)
+        seed = (seed + (int(seed_ptr.item()) * SEED_STEP_STRIDE if seed_ptr is not None else 0)) & ((1 << 64) - 1)
         x = self._cat(x0, x1)
         xh, _ = self._norm(x, sums)
         y = xh * gamma.float() + beta.float()
@@ -444,9 +447,13 @@ class EmuOps:
             y = (y * (1 + sc) + sh) * self._mask(y.shape, drop_p, seed)
         out.copy_(y.to(out.dtype))
 
+    def gn_stats_apply(self, x0, x1, sums, gamma, beta, mode, out, **kw):
+        self.gn_stats(x0, x1, sums)
+        self.gn_apply(x0, x1, sums, gamma, beta, mode, out, **kw)
+
     def gn_bwd(self, x0, x1, sums, gamma, beta, mode, dy, dgamma, dbeta, ws, dx0, dx1=None, ss=None, F=0, dss=None, drop_p=0.0, seed=0,
                add0=None, add1a=None, add1b=None, seed_ptr=None, dss_sum=None, dx_sum=None):
-        seed = seed + (int(seed_ptr.item()) if seed_ptr is not None else 0)
+        seed = (seed + (int(seed_ptr.item()) * SEED_STEP_STRIDE if seed_ptr is not None else 0)) & ((1 << 64) - 1)
         x = self._cat(x0, x1)
         N, HW, C = x.shape
         xh, rstd_c = self._norm(x, sums)

@@ -29,9 +29,11 @@ def pose_case(B, H, W, fp32, seed=0):
     return run
 
 
-def gn_case(N, HW, C0, C1, mode, drop_p=0.0, seed=0):
+def gn_case(N, HW, C0, C1, mode, drop_p=0.0, seed=0, step=None):
     def run(ops):
         g = torch.Generator().manual_seed(seed)
+        # device-side step counter mixed into the dropout seed (what a captured training graph uses)
+        sp = _mk(ops, torch.tensor([step]), torch.int64) if step is not None else None
         C = C0 + C1
         x0 = _mk(ops, (_r((N, HW, C0), g) + 0.3).to(torch.bfloat16).float())
         x1 = _mk(ops, (_r((N, HW, C1), g) * 2 - 0.5).to(torch.bfloat16).float()) if C1 else None
@@ -44,7 +46,7 @@ def gn_case(N, HW, C0, C1, mode, drop_p=0.0, seed=0):
         ssw[:, 32:32 + 2 * F] = _mk(ops, _r((N * HW, 2 * F), g, 0.5))
         ss = ssw[:, 32:32 + 2 * F] if mode == 2 else None
         out = ops.zeros((N, HW, C))
-        ops.gn_apply(x0, x1, sums, gamma, beta, mode, out, ss=ss, F=F, drop_p=drop_p, seed=77)
+        ops.gn_apply(x0, x1, sums, gamma, beta, mode, out, ss=ss, F=F, drop_p=drop_p, seed=77, seed_ptr=sp)
         dy = _mk(ops, _r((N, HW, C), g))
         dgamma, dbeta = ops.zeros((C,), torch.float32), ops.zeros((C,), torch.float32)
         ws = ops.zeros((N, 32, 2), torch.float32)
@@ -54,7 +56,7 @@ def gn_case(N, HW, C0, C1, mode, drop_p=0.0, seed=0):
         add0 = _mk(ops, _r((N, HW, C), g))
         add1a = _mk(ops, _r((N, HW, C0), g))
         ops.gn_bwd(x0, x1, sums, gamma, beta, mode, dy, dgamma, dbeta, ws, dx0, dx1, ss=ss, F=F, dss=dss, drop_p=drop_p, seed=77,
-                   add0=add0, add1a=add1a)
+                   add0=add0, add1a=add1a, seed_ptr=sp)
         outs = [sums, out, dgamma, dbeta, ws, dx0]
         if C1:
             outs.append(dx1)
@@ -234,4 +236,5 @@ def all_cases():
         (2, 16, 32, 0, 1, 0.0), (2, 36, 64, 32, 2, 0.0), (3, 64, 256, 0, 2, 0.1), (2, 64, 1024, 1024, 1, 0.0),
     ]):
         c[f"gn_{N}x{HW}x{C0}+{C1}_m{mode}_p{dp}"] = gn_case(N, HW, C0, C1, mode, dp, seed=i)
+    c["gn_3x64x256+0_m2_p0.1_step5"] = gn_case(3, 64, 256, 0, 2, 0.1, seed=9, step=5)
     return c

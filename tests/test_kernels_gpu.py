@@ -9,11 +9,14 @@ import op_cases
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(scope="module")
-def backends():
+@pytest.fixture(scope="module", params=["fp32", "fp32_stats_of_stored_bf16"])
+def backends(request):
+    """Every case runs against TWO checkers: the pure fp32 statement of the op, and the one whose epilogue GroupNorm
+    statistics are taken over the bf16-ROUNDED output (which is what the kernel is specified to sum: the statistics of the
+    tensor it stores).  Both are held to the same tolerances."""
     from distributed_3d_diffusion_pytorch_b200.ops import CudaOps
     from emu_ops import EmuOps
-    return CudaOps("cuda:0"), EmuOps("cpu", stats_dtype=torch.bfloat16)
+    return CudaOps("cuda:0"), EmuOps("cpu", stats_dtype=torch.bfloat16 if request.param != "fp32" else None)
 
 
 def _cmp(a, b):
@@ -46,3 +49,45 @@ def test_op(name, backends):
         if name.startswith("pose_fp32"):
             tol = 1e-5           # north_star: ray / posenc outputs within 1e-5 relative
         assert _cmp(a, b) <= tol, (name, i)
+
+
+def test_gn_image_chunked_launches_equal_unchunked():
+    """b3d_gn_stats_apply / b3d_gn_bwd run their two passes over a chunk of images at a time when a chunk budget is set (so
+    the second pass reads L2, not HBM): same results as one launch pair over all images"""
+    from distributed_3d_diffusion_pytorch_b200 import _lib
+    from distributed_3d_diffusion_pytorch_b200.ops import CudaOps
+    ops = CudaOps("cuda:0")
+    g = torch.Generator().manual_seed(5)
+    N, HW, C = 10, 1024, 256
+    mk = lambda *shape, dt=torch.bfloat16: torch.randn(*shape, generator=g).to("cuda:0", dt)
+    x, dy = mk(N, HW, C), mk(N, HW, C)
+    ss = mk(N * HW, 2 * C) * 0.5
+    gamma, beta = 1 + 0.1 * mk(C, dt=torch.float32), 0.1 * mk(C, dt=torch.float32)
+    res = {}
+    for mb in (0, 1):         # 1 MB budget -> two images (1 MB of x) per chunk
+        _lib.set_gn_chunk_mb(mb)
+        try:
+            for mode in (1, 2):
+                sums = torch.zeros(N, 32, 2, device="cuda:0")
+                out = torch.zeros(N, HW, C, device="cuda:0", dtype=torch.bfloat16)
+                n0 = _lib.launch_count()
+                ops.gn_stats_apply(x, None, sums, gamma, beta, mode, out, ss=ss if mode == 2 else None, F=C if mode == 2 else 0, drop_p=0.1 if mode == 2 else 0.0, seed=3)
+                launches = _lib.launch_count() - n0
+                dgamma, dbeta, ws = torch.zeros(C, device="cuda:0"), torch.zeros(C, device="cuda:0"), torch.zeros(N, 32, 2, device="cuda:0")
+                dx = torch.zeros_like(out)
+                dss = torch.zeros_like(ss) if mode == 2 else None
+                ops.gn_bwd(x, None, sums, gamma, beta, mode, dy, dgamma, dbeta, ws, dx, ss=ss if mode == 2 else None, F=C if mode == 2 else 0, dss=dss,
+                           drop_p=0.1 if mode == 2 else 0.0, seed=3)
+                torch.cuda.synchronize()
+                res[(mb, mode)] = (launches, sums, out, dx, dss, ws, dgamma, dbeta)
+        finally:
+            _lib.set_gn_chunk_mb(0)
+    for mode in (1, 2):
+        a, b = res[(0, mode)], res[(1, mode)]
+        assert a[0] == 2 and b[0] > 2                       # really chunked
+        # the same arithmetic with the fp32 partial sums combined in another order (blocks per image differ with the chunk)
+        for i in (1, 5, 6, 7):
+            assert torch.allclose(a[i], b[i], rtol=1e-4, atol=1e-3), (mode, i)
+        for i in (2, 3, 4):
+            if a[i] is not None:
+                assert _cmp(b[i], a[i]) <= 1e-3, (mode, i)

@@ -19,9 +19,7 @@ def _model(kw, seed, dev="cuda:0"):
     return m
 
 
-@pytest.mark.parametrize("name", ["tiny16", "tiny24", "small32"])
-def test_golden_fixture_parity(name):
-    """against the fixtures produced by the reference's own code"""
+def _fixture_run(name):
     from distributed_3d_diffusion_pytorch_b200.diff3d import diffusion_loss, q_sample
     G = load_golden(name)
     dev = "cuda:0"
@@ -33,30 +31,46 @@ def test_golden_fixture_parity(name):
     batch = {"x": x_cond, "z": z_noisy, "logsnr": G["batch_logsnr"].to(dev), "R": G["R"].to(dev), "t": G["T"].to(dev), "K": G["K"].to(dev)}
     eps = m(batch, cond_mask=cm)
     rel = ((eps.cpu() - G["eps"]).norm() / G["eps"].norm()).item()
-    # ch=32 puts ONE channel in each GroupNorm group and the deepest level is 2x2 (3x3) pixels: statistics over 4-9
-    # values amplify bf16 rounding (the same algorithm in torch with bf16 buffers gives 2.5e-2).
-    # Structure check here; the 2e-2 bar of north_star is asserted on CFG-64 below.
-    strict = G["kw"]["ch"] >= 64
-    assert rel <= (OUT_TOL if strict else 3 * OUT_TOL), rel
     loss = diffusion_loss(G["noise"].to(dev), eps)
-    assert abs(loss.item() - G["loss"].item()) <= (1 if strict else 3) * LOSS_TOL * abs(G["loss"].item())
+    loss_rel = abs(loss.item() - G["loss"].item()) / abs(G["loss"].item())
     loss.backward()
     grads = dict((n, p.grad.float().cpu()) for n, p in m.named_parameters())
-    # gradients: only the tensors computed FIRST in the backward pass are compared here.  Deeper in the network this
-    # fixture is numerically degenerate in bf16 (see the comment above; the same algorithm in torch with bf16 buffers
-    # reaches a global cosine of only ~0.87), so the full gradient is checked exactly (fp32) by tests/test_engine_cpu.py
-    # on this very fixture, and at the 0.999 bar on CFG-64 below.
-    for k in (G["grads"].keys() if strict else ("lastconv.weight",)):
-        g = G["grads"][k]
+    assert all(torch.isfinite(g).all() for g in grads.values())
+    return G, rel, loss_rel, grads, [n for n, _ in m.named_parameters()]
+
+
+def _cos(a, b):
+    return torch.nn.functional.cosine_similarity(a.double().flatten(), b.double().flatten(), dim=0).item()
+
+
+@pytest.mark.parametrize("name", ["small16", "small24", "small32"])
+def test_golden_fixture_parity(name):
+    """against fixtures produced by the reference's own code, at north_star's bars: output 2e-2, loss 1e-3, gradient
+    cosine 0.999 (on a seeded 262 144-element sample of the whole flat gradient stored in the fixture), plus every stored
+    gradient tensor individually and the norm of the whole gradient"""
+    G, rel, loss_rel, grads, names = _fixture_run(name)
+    assert rel <= OUT_TOL, rel
+    assert loss_rel <= LOSS_TOL, loss_rel
+    flat = torch.cat([grads[n].flatten() for n in names])
+    assert _cos(flat[G["grad_sample_idx"].long()], G["grad_sample"]) >= COS_TOL
+    assert abs(flat.double().norm().item() - G["grad_total_norm"]) <= 2e-2 * G["grad_total_norm"]
+    for k, g in G["grads"].items():
         if g.norm() < 1e-5:
             continue
-        cos = torch.nn.functional.cosine_similarity(grads[k].double().flatten(), g.double().flatten(), dim=0).item()
-        assert cos >= (0.995 if strict else 0.99), (k, cos)
-    if strict:      # norm of the whole gradient against the reference's
-        tot_ref = sum(v ** 2 for v in G["grad_norms"].values()) ** 0.5
-        tot = sum(g.double().norm().item() ** 2 for g in grads.values()) ** 0.5
-        assert abs(tot - tot_ref) <= 2e-2 * tot_ref, (tot, tot_ref)
-    assert all(torch.isfinite(g).all() for g in grads.values())
+        assert _cos(grads[k], g) >= 0.995, (k, _cos(grads[k], g))       # single small tensors (biases, 144-vectors) in bf16
+
+
+@pytest.mark.parametrize("name", ["tiny16", "tiny24"])
+def test_degenerate_fixture_structure_only_loosened_bars(name):
+    """NOT a north_star-tolerance test.  ch=32 puts ONE channel in each GroupNorm group and the deepest level is 2x2 (3x3)
+    pixels: statistics over 4-9 values amplify bf16 rounding (the same algorithm in torch with bf16 buffers gives 2.5e-2 /
+    gradient cosine 0.79 on the worst tensor).  These files are the exact fp32 orchestration fixtures of
+    tests/test_engine_cpu.py; on the GPU they only check that nothing is structurally wrong (3x looser output / loss bars,
+    the first gradient computed in the backward pass).  The strict bars are asserted on small16 / small24 / small32 above."""
+    G, rel, loss_rel, grads, _ = _fixture_run(name)
+    assert rel <= 3 * OUT_TOL, rel
+    assert loss_rel <= 3 * LOSS_TOL, loss_rel
+    assert _cos(grads["lastconv.weight"], G["grads"]["lastconv.weight"]) >= 0.99
 
 
 def test_pose_embedding_matches_reference_fixture():

@@ -36,6 +36,11 @@ def _run_model_case(name):
             continue
         cos = torch.nn.functional.cosine_similarity(sd[k].grad.flatten(), g.flatten(), dim=0)
         assert cos > 0.99999, (k, cos)
+    if "grad_sample" in G:        # seeded sample of the whole flat gradient (registration order)
+        flat = torch.cat([sd[k].grad.flatten() for k in xr.param_shapes(cfg)])
+        s = flat[G["grad_sample_idx"].long()]
+        assert torch.nn.functional.cosine_similarity(s.double(), G["grad_sample"].double(), dim=0) > 0.99999
+        assert abs(flat.double().norm().item() - G["grad_total_norm"]) <= 2e-4 * G["grad_total_norm"]
 
 
 def test_oracle_matches_reference_tiny16():
@@ -48,6 +53,14 @@ def test_oracle_matches_reference_tiny24():
 
 def test_oracle_matches_reference_small32():
     _run_model_case("small32")
+
+
+def test_oracle_matches_reference_small16():
+    _run_model_case("small16")
+
+
+def test_oracle_matches_reference_small24():
+    _run_model_case("small24")
 
 
 def test_schedule_and_sampler_update_match_reference():

@@ -22,26 +22,31 @@ inline int grid_for(long long n, int per_block = kT, int max_blocks = 148 * 32) 
 //     + cond-mask + pos_emb + first/other_emb  ->  [2B, H, W, ld] (bf16 or fp32), channels 0..143.
 // Replaces visu3d rays + xunet.py:311-336.  One block = 32 consecutive pixels of one image row.
 // ---------------------------------------------------------------------------------------------
+constexpr int kPoseRows = 8;   // image rows per block
 template <typename OutT>
 __global__ void __launch_bounds__(256) pose_embedding_kernel(const double* __restrict__ Kmat, const double* __restrict__ R,
                                                              const double* __restrict__ t, const uint8_t* __restrict__ mask,
                                                              const float* __restrict__ pos_emb, const float* __restrict__ first_emb,
                                                              const float* __restrict__ other_emb, OutT* __restrict__ out, long long ld, int H,
                                                              int W, int vec_ok) {
-  // The 32-pixel x 144-channel tile is assembled in shared memory (phase A: one value per thread-iteration, pixel index
-  // fastest, so the learned embedding pos_emb[c,y,x] is read coalesced along x) and leaves as 16-byte stores of 8 channels
-  // (phase B: consecutive threads -> consecutive 16-byte pieces of the 288-byte pixel rows).  Scalar 2-byte stores with a
-  // div/mod pair per element ran this kernel at 8 % of the HBM rate.
+  // One block = 32 pixels x kPoseRows rows of one image.  Per row the 32-pixel x 144-channel tile is assembled in shared
+  // memory (phase A: one value per thread-iteration, pixel index fastest, so the learned embedding pos_emb[c,y,x] is read
+  // coalesced along x; the channel is warp-uniform, so the sinf path does not diverge) and leaves as 16-byte stores of 8
+  // channels (phase B: consecutive threads -> consecutive 16-byte pieces of the 288-byte pixel rows).  The per-image set-up
+  // (R * inv(K) in fp64, the 93 position channels) is paid once per block, not once per row.  History: scalar 2-byte stores
+  // with a div/mod pair per element ran at 0.45 TB/s, one row per block at 0.71 TB/s (instruction- and set-up-bound).
   constexpr int kPitch = 148;                       // floats per pixel row of the tile (16-byte aligned rows)
-  __shared__ __align__(16) float s_out[32 * kPitch];
-  __shared__ float s_posch[93];
-  __shared__ float s_dir[32][3];
+  __shared__ __align__(16) float s_out[2][32 * kPitch];
+  __shared__ float s_posf[93];                      // position channel + first/other embedding (constant over the image)
+  __shared__ float s_fe[51];                        // first/other embedding of the direction channels
+  __shared__ float s_dir[2][32][3];
   __shared__ float s_mul[51], s_ph[51];             // direction channels 93..143: multiplier 2^d, phase (0 or pi/2)
   __shared__ int s_ax[51];                          //   axis; -1 - axis for the three raw components
   __shared__ double s_M[9];
-  const int n = blockIdx.z, y = blockIdx.y, x0 = blockIdx.x * 32;
+  const int n = blockIdx.z, y0 = blockIdx.y * kPoseRows, x0 = blockIdx.x * 32;
   const int b = n >> 1, f = n & 1;
   const bool cond = mask[b] != 0;
+  const float* fe = f == 0 ? first_emb : other_emb;
   if (threadIdx.x == 0) {
     // M = R * inv(K)   (world_from_px for directions)
     const double* k = Kmat + b * 9;
@@ -66,7 +71,7 @@ __global__ void __launch_bounds__(256) pose_embedding_kernel(const double* __res
       if (c - 3 >= 45) xb = xb + 1.5707963705062866f;
       v = sinf(xb);
     }
-    s_posch[c] = cond ? v : 0.f;
+    s_posf[c] = cond ? v : 0.f;                     // (the learned embeddings are added per element below, in the reference's order)
   } else if (threadIdx.x >= 128 && threadIdx.x < 128 + 51) {
     const int cc = threadIdx.x - 128;               // direction channels: [dir(3), sin(dir*2^d) (d-major, 8 octaves), sin(. + pi/2)]
     if (cc < 3) { s_ax[cc] = -1 - cc; s_mul[cc] = 1.f; s_ph[cc] = 0.f; }
@@ -74,64 +79,81 @@ __global__ void __launch_bounds__(256) pose_embedding_kernel(const double* __res
       const int j = (cc - 3) % 24, d = j / 3;
       s_ax[cc] = j % 3; s_mul[cc] = (float)(1 << d); s_ph[cc] = cc - 3 >= 24 ? 1.5707963705062866f : 0.f;
     }
+    s_fe[cc] = fe ? fe[93 + cc] : 0.f;
   }
   __syncthreads();
-  if (threadIdx.x < 32) {
-    const double u = (double)(x0 + threadIdx.x) + 0.5, v = (double)y + 0.5;
-    double dx = s_M[0] * u + s_M[1] * v + s_M[2];
-    double dy = s_M[3] * u + s_M[4] * v + s_M[5];
-    double dz = s_M[6] * u + s_M[7] * v + s_M[8];
-    const double inv_n = 1.0 / sqrt(dx * dx + dy * dy + dz * dz);
-    s_dir[threadIdx.x][0] = (float)(dx * inv_n);
-    s_dir[threadIdx.x][1] = (float)(dy * inv_n);
-    s_dir[threadIdx.x][2] = (float)(dz * inv_n);
-  }
-  __syncthreads();
-  // phase A: 256 threads = 8 channels x 32 pixels per iteration
-  const int xx = threadIdx.x & 31;
+  const int xx = threadIdx.x & 31, w8 = threadIdx.x >> 5;
   const bool in_x = x0 + xx < W;
-  const float* fe = f == 0 ? first_emb : other_emb;
-  for (int c = threadIdx.x >> 5; c < 144; c += 8) {
-    float v;
-    if (c < 93) v = s_posch[c];
-    else if (!cond) v = 0.f;
-    else {
-      const int cc = c - 93, ax = s_ax[cc];
-      if (ax < 0) v = s_dir[xx][-1 - ax];
-      else {
-        float xb = s_dir[xx][ax] * s_mul[cc];       // same fp32 operation order as posenc_nerf (xunet.py:49-59): x*2^d, + pi/2, sin
-        if (cc - 3 >= 24) xb = xb + s_ph[cc];
-        v = sinf(xb);
+  const int rows = min(kPoseRows, H - y0);
+  // ray directions of all rows of the block: 256 threads = 8 rows x 32 pixels, fp64 like the reference's camera maths
+  // (two halves of s_dir when kPoseRows rows do not fit one buffer -- here they do: s_dir is indexed [row & 1] per row, so
+  // compute them row by row inside the loop by the warp that owns the row parity)
+  for (int ry = 0; ry < rows; ++ry) {
+    const int y = y0 + ry, pb = ry & 1;
+    if (w8 == 0) {
+      const double u = (double)(x0 + xx) + 0.5, v = (double)y + 0.5;
+      double dx = s_M[0] * u + s_M[1] * v + s_M[2];
+      double dy = s_M[3] * u + s_M[4] * v + s_M[5];
+      double dz = s_M[6] * u + s_M[7] * v + s_M[8];
+      const double inv_n = 1.0 / sqrt(dx * dx + dy * dy + dz * dz);
+      s_dir[pb][xx][0] = (float)(dx * inv_n);
+      s_dir[pb][xx][1] = (float)(dy * inv_n);
+      s_dir[pb][xx][2] = (float)(dz * inv_n);
+    }
+    __syncthreads();
+    float* tile = s_out[pb];
+    const float* pe_row = pos_emb ? pos_emb + (long long)y * W + x0 + xx : nullptr;
+    const long long cstride = (long long)H * W;
+    // position channels: constant + learned embeddings
+    for (int c = w8; c < 93; c += 8) {
+      float v = s_posf[c];
+      if (in_x) {
+        if (pe_row) v += pe_row[c * cstride];
+        if (fe) v += __ldg(fe + c);
       }
+      tile[xx * kPitch + c] = v;
     }
-    if (in_x) {
-      if (pos_emb) v += pos_emb[((long long)c * H + y) * W + x0 + xx];
-      if (fe) v += fe[c];
-    }
-    s_out[xx * kPitch + c] = v;
-  }
-  __syncthreads();
-  // phase B
-  OutT* orow = out + (((long long)n * H + y) * W + x0) * ld;
-  if (vec_ok) {
-    for (int i = threadIdx.x; i < 32 * 18; i += blockDim.x) {
-      const int px = i / 18, c8 = i - px * 18;
-      if (x0 + px >= W) break;
-      const float4 lo = *reinterpret_cast<const float4*>(&s_out[px * kPitch + c8 * 8]);
-      const float4 hi = *reinterpret_cast<const float4*>(&s_out[px * kPitch + c8 * 8 + 4]);
-      OutT* dst = orow + (long long)px * ld + c8 * 8;
-      if constexpr (sizeof(OutT) == 2) {
-        const float f8[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
-        *reinterpret_cast<bf16x8*>(dst) = b3d_pack8(f8);
-      } else {
-        *reinterpret_cast<float4*>(dst) = lo;
-        *reinterpret_cast<float4*>(dst + 4) = hi;
+    // direction channels
+    for (int cc = w8; cc < 51; cc += 8) {
+      float v = 0.f;
+      if (cond) {
+        const int ax = s_ax[cc];
+        if (ax < 0) v = s_dir[pb][xx][-1 - ax];
+        else {
+          float xb = s_dir[pb][xx][ax] * s_mul[cc];   // same fp32 operation order as posenc_nerf (xunet.py:49-59): x*2^d, + pi/2, sin
+          if (cc >= 27) xb = xb + s_ph[cc];
+          v = sinf(xb);
+        }
       }
+      if (in_x) {
+        if (pe_row) v += pe_row[(93 + cc) * cstride];
+        v += s_fe[cc];
+      }
+      tile[xx * kPitch + 93 + cc] = v;
     }
-  } else {
-    for (int i = threadIdx.x; i < 32 * 144; i += blockDim.x) {
-      const int px = i / 144, c = i - px * 144;
-      if (x0 + px < W) orow[(long long)px * ld + c] = (OutT)s_out[px * kPitch + c];
+    __syncthreads();
+    // phase B (the next row's phase A writes the other tile buffer, so no barrier is needed after the stores)
+    OutT* orow = out + (((long long)n * H + y) * W + x0) * ld;
+    if (vec_ok) {
+      for (int i = threadIdx.x; i < 32 * 18; i += blockDim.x) {
+        const int px = i / 18, c8 = i - px * 18;
+        if (x0 + px >= W) break;
+        const float4 lo = *reinterpret_cast<const float4*>(&tile[px * kPitch + c8 * 8]);
+        const float4 hi = *reinterpret_cast<const float4*>(&tile[px * kPitch + c8 * 8 + 4]);
+        OutT* dst = orow + (long long)px * ld + c8 * 8;
+        if constexpr (sizeof(OutT) == 2) {
+          const float f8[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+          *reinterpret_cast<bf16x8*>(dst) = b3d_pack8(f8);
+        } else {
+          *reinterpret_cast<float4*>(dst) = lo;
+          *reinterpret_cast<float4*>(dst + 4) = hi;
+        }
+      }
+    } else {
+      for (int i = threadIdx.x; i < 32 * 144; i += blockDim.x) {
+        const int px = i / 144, c = i - px * 144;
+        if (x0 + px < W) orow[(long long)px * ld + c] = (OutT)tile[px * kPitch + c];
+      }
     }
   }
 }
@@ -600,6 +622,24 @@ __global__ void sampler_update_dev_kernel(const float* __restrict__ z, const flo
   }
 }
 
+// Sampler: out[j, p, :] = silu(c[j, p, :] + lemb[row[j], :]) for the D distinct conditionings of a batch.  c is the cached,
+// step-invariant part of the conditioning path (conv_l(pose_emb) + bias, xunet.py:340-349, fp32 so that the sum below is the
+// same fp32 value the conditioning conv's epilogue forms), lemb the per-step logsnr embedding (xunet.py:502).
+__global__ void __launch_bounds__(256) cond_silu_kernel(const float* __restrict__ c, const float* __restrict__ lemb, const int* __restrict__ row,
+                                                        bf16* __restrict__ out, long long per_image, int E, long long total8) {
+  b3d_pdl_sync();
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total8; i += (long long)gridDim.x * blockDim.x) {
+    const long long e0 = i * 8;
+    const int j = (int)(e0 / per_image), ch = (int)(e0 % E);
+    const float4 a0 = *reinterpret_cast<const float4*>(c + e0), a1 = *reinterpret_cast<const float4*>(c + e0 + 4);
+    const float* lr = lemb + (long long)__ldg(row + j) * E + ch;
+    const float4 b0 = __ldg(reinterpret_cast<const float4*>(lr)), b1 = __ldg(reinterpret_cast<const float4*>(lr) + 1);
+    const float f[8] = {b3d_silu(a0.x + b0.x), b3d_silu(a0.y + b0.y), b3d_silu(a0.z + b0.z), b3d_silu(a0.w + b0.w),
+                        b3d_silu(a1.x + b1.x), b3d_silu(a1.y + b1.y), b3d_silu(a1.z + b1.z), b3d_silu(a1.w + b1.w)};
+    *reinterpret_cast<bf16x8*>(out + e0) = b3d_pack8(f);
+  }
+}
+
 // fused Adam over one flat fp32 parameter arena (train.py:235: lr 1e-4, betas (0.9, 0.99), eps 1e-8)
 __device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, float lr, float b1, float b2, float eps, float ibc1, float ibc2,
                                          float grad_scale) {
@@ -820,7 +860,7 @@ extern "C" int b3d_pose_embedding(const double* K, const double* R, const double
                                   void* stream) {
   B3D_CHECK_ARG(K && R && t && cond_mask && out, "pose_embedding: null pointer");
   B3D_CHECK_ARG(ld >= 144 && B > 0 && H > 0 && W > 0, "pose_embedding: bad sizes");
-  dim3 grid(cdiv(W, 32), H, 2 * B);
+  dim3 grid(cdiv(W, 32), cdiv(H, kPoseRows), 2 * B);
   const int vec_ok = (ld % 8 == 0 && ((uintptr_t)out & 15) == 0) ? 1 : 0;      // 16-byte stores of 8 channels
   if (out_fp32) pose_embedding_kernel<float><<<grid, 256, 0, STREAM>>>(K, R, t, cond_mask, pos_emb, first_emb, other_emb, (float*)out, ld, H, W, vec_ok);
   else pose_embedding_kernel<bf16><<<grid, 256, 0, STREAM>>>(K, R, t, cond_mask, pos_emb, first_emb, other_emb, (bf16*)out, ld, H, W, vec_ok);
@@ -1031,6 +1071,14 @@ extern "C" int b3d_sampler_update_dev(const float* z, const float* eps_c, const 
   B3D_CHECK_ARG(z && eps_c && eps_u && w && noise && out && sched_dev, "sampler_update_dev: null");
   sampler_update_dev_kernel<<<grid_for((long long)B * per_sample), kT, 0, STREAM>>>(z, eps_c, eps_u, w, noise, out, sched_dev, per_sample,
                                                                                   (long long)B * per_sample);
+  DONE(1);
+}
+extern "C" int b3d_cond_silu(const float* c, const float* lemb, const int32_t* lemb_row, void* out, int D, int64_t rows_per_image, int E,
+                             void* stream) {
+  B3D_CHECK_ARG(c && lemb && lemb_row && out && D > 0 && rows_per_image > 0 && E % 8 == 0, "cond_silu: args (E %% 8)");
+  B3D_CHECK_ARG((((uintptr_t)c | (uintptr_t)lemb | (uintptr_t)out) & 15) == 0, "cond_silu: 16-byte aligned tensors");
+  const long long per_image = rows_per_image * E, total8 = (long long)D * per_image / 8;
+  B3D_CUDA(b3d_launch_pdl(cond_silu_kernel, dim3(grid_for(total8)), dim3(256), 0, STREAM, c, lemb, (const int*)lemb_row, (bf16*)out, per_image, E, total8));
   DONE(1);
 }
 extern "C" int b3d_adam(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2, float eps, int step,

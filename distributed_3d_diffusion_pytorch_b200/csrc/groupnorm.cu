@@ -146,6 +146,7 @@ struct ApplyP {
   int HW, mode;  // 0 plain, 1 silu, 2 film
   int n0;        // first image of this launch (image-chunked launches, see gn_chunk_images)
   const bf16* ss; long long ld_ss; int F;  // film: scale = ss[row, c], shift = ss[row, F + c]
+  const int* ss_image;                     // optional [N]: image n reads the ss rows of image ss_image[n] (images that share their conditioning)
   float drop_p; unsigned long long seed; const unsigned long long* seed_ptr;  // effective seed = seed + *seed_ptr * B3D_SEED_STEP_STRIDE (device step counter)
 };
 
@@ -176,6 +177,7 @@ __global__ void __launch_bounds__(kT, MODE == 2 ? 3 : 4) gn_apply_kernel(ApplyP 
   Aff ch; load_aff(ch, p.gamma, p.beta, c0, cpg, s_mean, s_rstd);
   const RowPtr rp = src_ptr(p.s, c0);
   const long long img = (long long)n * p.HW;
+  const long long ss_off = (MODE == 2 && p.ss_image != nullptr) ? ((long long)p.ss_image[n] - n) * p.HW : 0;   // row offset into ss
   const bool drop = MODE == 2 && p.drop_p > 0.f;
   Drop dr{};
   if (drop) dr = make_drop(p.drop_p, p.seed, p.seed_ptr);
@@ -187,8 +189,8 @@ __global__ void __launch_bounds__(kT, MODE == 2 ? 3 : 4) gn_apply_kernel(ApplyP 
       const bool ok = r + u * rows_par < r1;
       x[u] = ok ? ld8(rp.p + row * rp.ld) : zero8();
       if (MODE == 2) {
-        sc[u] = ok ? ld8(p.ss + row * p.ld_ss + c0) : zero8();
-        sh[u] = ok ? ld8(p.ss + row * p.ld_ss + p.F + c0) : zero8();
+        sc[u] = ok ? ld8(p.ss + (row + ss_off) * p.ld_ss + c0) : zero8();
+        sh[u] = ok ? ld8(p.ss + (row + ss_off) * p.ld_ss + p.F + c0) : zero8();
       }
     }
 #pragma unroll
@@ -485,7 +487,7 @@ extern "C" int b3d_gn_stats(const void* x0, int C0, int64_t ld0, const void* x1,
 
 static int gn_apply_impl(const void* x0, int C0, int64_t ld0, const void* x1, int C1, int64_t ld1, int N, int HW, float* ws_sums, int with_stats,
                          const float* gamma, const float* beta, int mode, const void* ss, int64_t ld_ss, int F, float drop_p,
-                         uint64_t seed, const uint64_t* seed_ptr, void* out, int64_t ld_out, void* stream) {
+                         uint64_t seed, const uint64_t* seed_ptr, void* out, int64_t ld_out, const int32_t* ss_image, void* stream) {
   const float* sums = ws_sums;
   if (int rc = check_src(x0, C0, x1, C1)) return rc;
   B3D_CHECK_ARG(mode >= 0 && mode <= 2, "gn_apply: mode");
@@ -495,6 +497,7 @@ static int gn_apply_impl(const void* x0, int C0, int64_t ld0, const void* x1, in
   p.s = Src2{(const bf16*)x0, (const bf16*)x1, C0, C1, ld0, ld1};
   p.stats = sums; p.gamma = gamma; p.beta = beta; p.out = (bf16*)out; p.ld_out = ld_out; p.HW = HW; p.mode = mode;
   p.ss = (const bf16*)ss; p.ld_ss = ld_ss; p.F = F; p.drop_p = drop_p; p.seed = seed; p.seed_ptr = (const unsigned long long*)seed_ptr;
+  p.ss_image = ss_image;
   // with_stats: statistics pass and apply pass of the same images back to back, chunk by chunk (the apply pass then reads
   // the chunk from L2); without: one apply launch over all images
   const int C = C0 + C1;
@@ -524,15 +527,16 @@ static int gn_apply_impl(const void* x0, int C0, int64_t ld0, const void* x1, in
 
 extern "C" int b3d_gn_apply(const void* x0, int C0, int64_t ld0, const void* x1, int C1, int64_t ld1, int N, int HW, const float* sums,
                             const float* gamma, const float* beta, int mode, const void* ss, int64_t ld_ss, int F, float drop_p,
-                            uint64_t seed, const uint64_t* seed_ptr, void* out, int64_t ld_out, void* stream) {
+                            uint64_t seed, const uint64_t* seed_ptr, void* out, int64_t ld_out, const int32_t* ss_image, void* stream) {
   return gn_apply_impl(x0, C0, ld0, x1, C1, ld1, N, HW, const_cast<float*>(sums), 0, gamma, beta, mode, ss, ld_ss, F, drop_p, seed, seed_ptr, out,
-                       ld_out, stream);
+                       ld_out, ss_image, stream);
 }
 
 extern "C" int b3d_gn_stats_apply(const void* x0, int C0, int64_t ld0, const void* x1, int C1, int64_t ld1, int N, int HW, float* ws_sums,
                                   const float* gamma, const float* beta, int mode, const void* ss, int64_t ld_ss, int F, float drop_p,
-                                  uint64_t seed, const uint64_t* seed_ptr, void* out, int64_t ld_out, void* stream) {
-  return gn_apply_impl(x0, C0, ld0, x1, C1, ld1, N, HW, ws_sums, 1, gamma, beta, mode, ss, ld_ss, F, drop_p, seed, seed_ptr, out, ld_out, stream);
+                                  uint64_t seed, const uint64_t* seed_ptr, void* out, int64_t ld_out, const int32_t* ss_image, void* stream) {
+  return gn_apply_impl(x0, C0, ld0, x1, C1, ld1, N, HW, ws_sums, 1, gamma, beta, mode, ss, ld_ss, F, drop_p, seed, seed_ptr, out, ld_out, ss_image,
+                       stream);
 }
 
 extern "C" int b3d_gn_bwd(const void* x0, int C0, int64_t ld0, const void* x1, int C1, int64_t ld1, int N, int HW, const float* sums,

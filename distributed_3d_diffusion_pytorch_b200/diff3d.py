@@ -149,6 +149,7 @@ class FusedAdam:
     def step(self, grad_scale=1.0):
         flat, g = self._arenas(), self.model.flat_gradients()
         self.step_count += 1
+        self.model._param_version = getattr(self.model, "_param_version", 0) + 1
         pg = self.param_groups[0]
         _ops(flat.device).adam(flat, g, self.m, self.v, pg["lr"], pg["betas"][0], pg["betas"][1], pg["eps"], self.step_count, grad_scale,
                                ema=self.ema, ema_decay=self.ema_decay or 0.0)

@@ -269,9 +269,33 @@ class Engine:
         return W, jl
 
     # ------------------------------------------------------------------ forward
-    def forward(self, P, x, z, logsnr, R, t, K, cond_mask, training=False, need_bwd=None, seed=0, repack=True):
+    def cond_features(self, P, R, t, K, cond_mask, repack=True):
+        """The step-invariant part of the conditioning path (xunet.py:311-349 without `+ logsnr_emb`): conv_l(pose_emb) + bias
+        per level, fp32 [2B, h_l, w_l, emb_ch], for the pairs of this engine's batch.  It depends on K / R / t / cond_mask
+        only, so a sampler evaluates it once per (camera, frame role) and reuses it for all denoising steps.
+        The tensors are this engine's buffers: copy what must outlive the next call."""
+        ops, cfg, N = self.ops, self.cfg, self.N
+        self._assign_cat_sources()
+        Wp = self._pack_weights(P, False, repack)
+        cp = "conditioningprocessor."
+        pe = self.buf("pose_emb", (N, cfg.H, cfg.W, 144))
+        ops.pose_embedding(K, R, t, cond_mask, P.get(cp + "pos_emb") if cfg.use_pos_emb else None,
+                           P[cp + "first_emb"].reshape(-1) if cfg.use_ref_pose_emb else None,
+                           P[cp + "other_emb"].reshape(-1) if cfg.use_ref_pose_emb else None, pe)
+        out = []
+        for l in range(cfg.num_resolutions):
+            h, w = self.lvl_hw(l)
+            c = self.buf(f"cond_c{l}", (N, h, w, cfg.emb_ch), torch.float32)
+            ops.gemm(G.conv_desc([pe], [9], Wp[cp + f"convs.{l}.weight"], cfg.emb_ch, c, 2 ** l, bias=P[cp + f"convs.{l}.bias"]))
+            out.append(c)
+        return out
+
+    def forward(self, P, x, z, logsnr, R, t, K, cond_mask, training=False, need_bwd=None, seed=0, repack=True, cond=None):
         """P: dict name -> fp32 param.  x,z: fp32 [B,3,H,W]; logsnr [B,2]; R [B,2,3,3], t [B,2,3], K [B,3,3] fp64;
-        cond_mask [B].  Returns eps_hat fp32 [B,3,H,W] (frame 1).  Keeps what backward needs in self.saved."""
+        cond_mask [B].  Returns eps_hat fp32 [B,3,H,W] (frame 1).  Keeps what backward needs in self.saved.
+        cond (inference only): cached conditioning -- dict(c=[fp32 [D,h_l,w_l,E] per level] from cond_features, image=int32 [N]
+        (image n uses conditioning image[n]), rep=int32 [D] (an image n that uses conditioning j: its logsnr embedding is
+        taken)); R / t / K / cond_mask are then not read, and FiLM is evaluated for the D distinct conditionings only."""
         ops, cfg, B, N = self.ops, self.cfg, self.B, self.N
         H, Wd = cfg.H, cfg.W
         assert x.shape == (B, 3, H, Wd), (x.shape, (B, 3, H, Wd))
@@ -297,15 +321,30 @@ class Engine:
         lemb = self.buf("lemb", (N, E), torch.float32)
         ops.gemm(G.dense_desc(h1s, Wp[cp + "logsnr_emb_emb.2.weight"], lemb, E, bias=P[cp + "logsnr_emb_emb.2.bias"]))
 
+        self._ss_image = None
+        ss = []
+        if cond is not None:
+            assert not need_bwd, "cached conditioning is an inference path"
+            self._ss_image = cond["image"]
+            D = cond["rep"].numel()
+            for l in range(cfg.num_resolutions):
+                h, w = self.lvl_hw(l)
+                sil = self.buf(f"emb_silu_c{l}", (D, h, w, E))
+                s_l = self.buf(f"ss_c{l}", (D * h * w, self.film_cols[l]))
+                with (ops.side() if l >= 1 else contextlib.nullcontext()):
+                    ops.cond_silu(cond["c"][l], lemb, cond["rep"], sil)
+                    ops.gemm(G.dense_desc(sil.view(D * h * w, E), Wp[f"film{l}"], s_l, self.film_cols[l], bias=self._bufs[f"b.film{l}"]))
+                ss.append(s_l)
+
         # ---- pose embedding (K1) and the four strided conditioning convs (+ logsnr_emb, SiLU for FiLM)
-        pe = self.buf("pose_emb", (N, H, Wd, 144))
-        ops.pose_embedding(K, R, t, cond_mask, P.get(cp + "pos_emb") if cfg.use_pos_emb else None,
-                           P[cp + "first_emb"].reshape(-1) if cfg.use_ref_pose_emb else None,
-                           P[cp + "other_emb"].reshape(-1) if cfg.use_ref_pose_emb else None, pe)
+        pe = self.buf("pose_emb", (N, H, Wd, 144)) if cond is None else None
+        if cond is None:
+            ops.pose_embedding(K, R, t, cond_mask, P.get(cp + "pos_emb") if cfg.use_pos_emb else None,
+                               P[cp + "first_emb"].reshape(-1) if cfg.use_ref_pose_emb else None,
+                               P[cp + "other_emb"].reshape(-1) if cfg.use_ref_pose_emb else None, pe)
         # Level 0 on the main stream (the trunk needs it first); the coarser levels on the side stream, beside the stem and
         # the level-0 blocks, joined where the trunk first reaches level 1.
-        ss = []
-        for l in range(cfg.num_resolutions):
+        for l in range(cfg.num_resolutions if cond is None else 0):
             h, w = self.lvl_hw(l)
             pre = self.buf(f"emb_pre{l}", (N, h, w, E))
             sil = self.buf(f"emb_silu{l}", (N, h, w, E))
@@ -387,7 +426,7 @@ class Engine:
         a1 = self.buf(n + ".a1", (N, HW, F))
         ssv = ss_l[:, s.film_off:s.film_off + 2 * F]
         (ops.gn_apply if fused else ops.gn_stats_apply)(c13, None, sums1, P[n + ".groupnorm1.gn.weight"], P[n + ".groupnorm1.gn.bias"], 2, a1, ss=ssv, F=F, drop_p=drop_p,
-                     seed=seed, seed_ptr=self.seed_ptr)
+                     seed=seed, seed_ptr=self.seed_ptr, ss_image=self._ss_image)
         if s.cin != F:
             sk = self.buf(n + ".sk", (N, hh, ww, F))
             srcs = [h_in.t] + ([skip.t] if skip is not None else [])

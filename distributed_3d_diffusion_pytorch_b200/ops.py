@@ -442,20 +442,20 @@ class CudaOps:
         N, HW, _ = x0.shape
         self._call("b3d_gn_stats", *self._src(x0), *self._src(x1), c_i32(N), c_i32(HW), _ptr(sums), self.stream())
 
-    def gn_apply(self, x0, x1, sums, gamma, beta, mode, out, ss=None, F=0, drop_p=0.0, seed=0, seed_ptr=None):
+    def gn_apply(self, x0, x1, sums, gamma, beta, mode, out, ss=None, F=0, drop_p=0.0, seed=0, seed_ptr=None, ss_image=None):
         """seed_ptr: optional int64 device scalar added to `seed` (a step counter that lives on the device, so a
         captured CUDA graph draws a fresh dropout mask on every replay)"""
         N, HW, _ = x0.shape
         self._call("b3d_gn_apply", *self._src(x0), *self._src(x1), c_i32(N), c_i32(HW), _ptr(sums), _ptr(gamma), _ptr(beta), c_i32(mode),
                    _ptr(ss), c_i64(ss.stride(0) if ss is not None else 0), c_i32(F), c_f32(drop_p), ctypes.c_uint64(seed), _ptr(seed_ptr),
-                   _ptr(out), c_i64(out.stride(1)), self.stream())
+                   _ptr(out), c_i64(out.stride(1)), _ptr(ss_image), self.stream())
 
-    def gn_stats_apply(self, x0, x1, sums, gamma, beta, mode, out, ss=None, F=0, drop_p=0.0, seed=0, seed_ptr=None):
+    def gn_stats_apply(self, x0, x1, sums, gamma, beta, mode, out, ss=None, F=0, drop_p=0.0, seed=0, seed_ptr=None, ss_image=None):
         """gn_stats + gn_apply of the same input as one call (image-chunked for L2 reuse when a chunk budget is set)"""
         N, HW, _ = x0.shape
         self._call("b3d_gn_stats_apply", *self._src(x0), *self._src(x1), c_i32(N), c_i32(HW), _ptr(sums), _ptr(gamma), _ptr(beta), c_i32(mode),
                    _ptr(ss), c_i64(ss.stride(0) if ss is not None else 0), c_i32(F), c_f32(drop_p), ctypes.c_uint64(seed), _ptr(seed_ptr),
-                   _ptr(out), c_i64(out.stride(1)), self.stream())
+                   _ptr(out), c_i64(out.stride(1)), _ptr(ss_image), self.stream())
 
     def gn_bwd(self, x0, x1, sums, gamma, beta, mode, dy, dgamma, dbeta, ws, dx0, dx1=None, ss=None, F=0, dss=None, drop_p=0.0, seed=0,
                add0=None, add1a=None, add1b=None, seed_ptr=None, dss_sum=None, dx_sum=None):
@@ -494,6 +494,12 @@ class CudaOps:
         assert w.dtype == torch.float32 and w.is_contiguous() and w.numel() == B, "w: one fp32 guidance weight per image"
         self._call("b3d_sampler_update_dev", _ptr(z), _ptr(eps_c), _ptr(eps_u), _ptr(w), _ptr(noise), _ptr(out), _ptr(sched), c_i32(B),
                    c_i64(z.numel() // B), self.stream())
+
+    def cond_silu(self, c, lemb, lemb_row, out):
+        """out[j] = silu(c[j] + lemb[lemb_row[j]]): c fp32 [D, h, w, E] (cached conditioning conv + bias), lemb fp32 [N, E], out bf16"""
+        D, E = c.shape[0], c.shape[-1]
+        assert c.dtype == torch.float32 and c.is_contiguous() and out.is_contiguous() and lemb.is_contiguous() and lemb_row.dtype == torch.int32
+        self._call("b3d_cond_silu", _ptr(c), _ptr(lemb), _ptr(lemb_row), _ptr(out), c_i32(D), c_i64(c.numel() // (D * E)), c_i32(E), self.stream())
 
     def adam(self, p, g, m, v, lr, beta1, beta2, eps, step, grad_scale=1.0, ema=None, ema_decay=0.0):
         """ema (optional, fp32 like p): ema = ema_decay * ema + (1 - ema_decay) * p_new, in the same pass"""

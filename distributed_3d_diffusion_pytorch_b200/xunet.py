@@ -163,6 +163,7 @@ class XUNet(torch.nn.Module):
         self._ops = None
         self._flat = self._grad_flat = None
         self._step_seed = 0
+        self._param_version = 0     # bumped whenever the parameters change through this package (samplers key their caches on it)
         self._flatten()
 
     # ---- one flat fp32 arena for parameters (and one for gradients): allreduce / Adam run on a single tensor
@@ -183,6 +184,7 @@ class XUNet(torch.nn.Module):
             self._grad_flat = None
             self._engines = {}
             self._ops = None
+            self._param_version = getattr(self, "_param_version", 0) + 1
         self._plist = ps
 
     def _apply(self, fn, recurse=True):
@@ -232,4 +234,5 @@ class XUNet(torch.nn.Module):
     def load_state_dict(self, state_dict, strict=True, **kw):
         """accepts checkpoints saved from nn.DataParallel (`module.` prefix, sampling.py:52-56)"""
         sd = {(k[7:] if k.startswith("module.") else k): v for k, v in state_dict.items()}
+        self._param_version += 1
         return super().load_state_dict(sd, strict=strict, **kw)

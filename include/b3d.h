@@ -170,7 +170,8 @@ int b3d_softmax_bwd(const void* P, int64_t ld_p, const void* dP, int dp_fp32, in
 /* GroupNorm(32, C, eps 1e-5) per image (xunet.py:61-71) on the channel-concat of up to two tensors.
  * b3d_gn_stats accumulates raw (sum, sumsq) into ws_sums fp32 [N,32,2] (caller zeroes it).
  * b3d_gn_apply: mode 0 plain (AttnBlock :198), 1 +SiLU (:140,:535), 2 +FiLM(+dropout) (:87,:143-145) with
- *   scale = ss[row, c], shift = ss[row, F + c].
+ *   scale = ss[row, c], shift = ss[row, F + c]; ss_image (optional int32 [N], device): image n takes the ss rows of image
+ *   ss_image[n] -- the sampler's batch holds only four distinct conditionings, so FiLM is evaluated for four images.
  * b3d_gn_bwd: autograd of the same lines; writes d(scale,shift) to dss, accumulates dgamma/dbeta (fp32),
  *   uses ws_s12 fp32 [N,32,2] (caller zeroes it), writes dx0/dx1 (+ add0 + add1a/add1b when given).  Optional fused
  *   reductions (fp32, accumulated): dss_sum [2F] = column sums of dss (FiLM dense bias gradient, xunet.py:80),
@@ -178,13 +179,13 @@ int b3d_softmax_bwd(const void* P, int64_t ld_p, const void* dP, int dp_fp32, in
 int b3d_gn_stats(const void* x0, int C0, int64_t ld0, const void* x1, int C1, int64_t ld1, int N, int HW, float* ws_sums, void* stream);
 int b3d_gn_apply(const void* x0, int C0, int64_t ld0, const void* x1, int C1, int64_t ld1, int N, int HW, const float* sums,
                  const float* gamma, const float* beta, int mode, const void* ss, int64_t ld_ss, int F, float drop_p, uint64_t seed, const uint64_t* seed_ptr,
-                 void* out, int64_t ld_out, void* stream);
+                 void* out, int64_t ld_out, const int32_t* ss_image, void* stream);
 /* b3d_gn_stats followed by b3d_gn_apply on the same input (ws_sums pre-zeroed by the caller, left holding the sums for the
  * backward pass).  Both passes run over a chunk of images at a time when a chunk budget is set, so the apply pass reads
  * the chunk from L2 rather than from HBM; b3d_gn_bwd chunks its reduce / apply passes the same way. */
 int b3d_gn_stats_apply(const void* x0, int C0, int64_t ld0, const void* x1, int C1, int64_t ld1, int N, int HW, float* ws_sums,
                        const float* gamma, const float* beta, int mode, const void* ss, int64_t ld_ss, int F, float drop_p, uint64_t seed,
-                       const uint64_t* seed_ptr, void* out, int64_t ld_out, void* stream);
+                       const uint64_t* seed_ptr, void* out, int64_t ld_out, const int32_t* ss_image, void* stream);
 /* budget (MB) for the tensors both passes of a GroupNorm read per image chunk; 0 = no chunking.  Default: the
  * environment's B3D_GN_CHUNK_MB, else 0.  A tuning knob of this library, no reference counterpart. */
 void b3d_set_gn_chunk_mb(int mb);
@@ -224,6 +225,11 @@ int b3d_sampler_update(const float* z, const float* eps_c, const float* eps_u, c
 /* the same update with (logsnr, logsnr_next) read from two device floats: one captured graph serves all 256 steps */
 int b3d_sampler_update_dev(const float* z, const float* eps_c, const float* eps_u, const float* w, const float* noise, float* out,
                            const float* sched_dev, int B, int64_t per_sample, void* stream);
+/* Sampler-side caching of the conditioning path: conv_l(pose_emb) + bias of xunet.py:340-349 depends only on
+ * K/R/t/cond_mask, not on the denoising step.  c: that cached part, fp32 [D, rows_per_image, E] for the D distinct
+ * conditionings of a batch; lemb fp32 [*, E] the per-step logsnr embedding, of which conditioning j takes row lemb_row[j]
+ * (device int32 [D]).  out bf16 [D, rows_per_image, E] = silu(c + lemb), the FiLM GEMM's operand (xunet.py:84,502). */
+int b3d_cond_silu(const float* c, const float* lemb, const int32_t* lemb_row, void* out, int D, int64_t rows_per_image, int E, void* stream);
 /* torch.optim.Adam(lr, betas) step over a flat fp32 arena: train.py:235,278 / lightning/diff3d.py:106 */
 int b3d_adam(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2, float eps, int step,
              float grad_scale, void* stream);

@@ -433,7 +433,7 @@ class EmuOps:
         keep = drop_keep(seed, idx, drop_p)
         return torch.where(keep, torch.full(shape, 1.0 / (1.0 - drop_p)), torch.zeros(shape))
 
-    def gn_apply(self, x0, x1, sums, gamma, beta, mode, out, ss=None, F=0, drop_p=0.0, seed=0, seed_ptr=None):
+    def gn_apply(self, x0, x1, sums, gamma, beta, mode, out, ss=None, F=0, drop_p=0.0, seed=0, seed_ptr=None, ss_image=None):
         seed = (seed + (int(seed_ptr.item()) * SEED_STEP_STRIDE if seed_ptr is not None else 0)) & ((1 << 64) - 1)
         x = self._cat(x0, x1)
         xh, _ = self._norm(x, sums)
@@ -442,10 +442,15 @@ class EmuOps:
             y = torch.nn.functional.silu(y)
         elif mode == 2:
             N, HW, C = x.shape
-            sc = ss[:, :F].float().reshape(N, HW, F)
-            sh = ss[:, F:2 * F].float().reshape(N, HW, F)
+            sc = ss[:, :F].float().reshape(-1, HW, F)
+            sh = ss[:, F:2 * F].float().reshape(-1, HW, F)
+            if ss_image is not None:          # image n takes the ss rows of image ss_image[n]
+                sc, sh = sc[ss_image.long()], sh[ss_image.long()]
             y = (y * (1 + sc) + sh) * self._mask(y.shape, drop_p, seed)
         out.copy_(y.to(out.dtype))
+
+    def cond_silu(self, c, lemb, lemb_row, out):
+        out.copy_(F.silu(c.float() + lemb.float()[lemb_row.long()][:, None, None, :]).to(out.dtype))
 
     def gn_stats_apply(self, x0, x1, sums, gamma, beta, mode, out, **kw):
         self.gn_stats(x0, x1, sums)

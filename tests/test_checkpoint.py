@@ -1,6 +1,8 @@
 """Checkpoint compatibility with the reference (train.py:246-251,289,298; lightning/diff3d.py:40-45,107-108): the file is
 {'model': state_dict (optionally `module.`-prefixed), 'optim': torch.optim.Adam state_dict, 'step'[, 'epoch']}.
 CPU part: layout conversions in both directions.  GPU part: a run resumed here continues exactly like torch's Adam."""
+import copy
+
 import pytest
 import torch
 
@@ -86,7 +88,7 @@ def test_resumed_run_continues_like_torch_adam():
     ref_params = [torch.nn.Parameter(p.detach().clone()) for p in model._plist]
     grads = _random_grads(model, 3, seed=2)
     topt = _torch_adam_run(ref_params, grads[:2])
-    sd_opt = topt.state_dict()
+    sd_opt = copy.deepcopy(topt.state_dict())        # (state_dict() hands out the live moment tensors)
     sd_model = {n: p.detach().clone() for n, p in zip(model._names, ref_params)}
     _torch_adam_run_more = topt
     for p, g in zip(ref_params, grads[2]):

@@ -208,3 +208,44 @@ def test_no_cpu_fallback():
     with pytest.raises(_lib.B3DError):
         m({"x": torch.zeros(1, 3, 16, 16), "z": torch.zeros(1, 3, 16, 16), "logsnr": torch.zeros(1, 2), "R": torch.eye(3).repeat(1, 2, 1, 1).double(),
            "t": torch.zeros(1, 2, 3).double(), "K": torch.eye(3)[None].double()}, cond_mask=torch.tensor([True]))
+
+
+def test_cached_conditioning_is_bit_identical_and_follows_parameter_updates():
+    """GraphSampler(cache_conditioning=True) -- conditioning convs evaluated once per camera, FiLM for the 4 distinct
+    conditionings -- gives bit-for-bit the z of the uncached sampler over a growing record, and a parameter change between
+    sample() calls is picked up (the packed operands and the cache are keyed on the model's parameter version)."""
+    import random
+    from distributed_3d_diffusion_pytorch_b200 import sampling, synthetic
+    dev = "cuda:0"
+    m = _model(dict(H=32, W=32, ch=64), 6).eval()
+    b = 4
+    img, R, T, K = synthetic.make_views(3, 32, seed=2)
+    w = torch.tensor([0.0, 1.0, 2.0, 3.0])
+    rec0 = [[img[0, 0][None].repeat(b, 1, 1, 1).numpy(), R[0, 0].numpy(), T[0, 0].numpy()],
+            [img[1, 0][None].repeat(b, 1, 1, 1).numpy(), R[1, 0].numpy(), T[1, 0].numpy()]]
+    outs = {}
+    for cache in (False, True):
+        gs = sampling.GraphSampler(m, b, cache_conditioning=cache)
+        res = []
+        for view in range(2):                      # two target views, the record grows in between
+            rec = rec0[:1 + view]
+            random.seed(5 + view)
+            torch.manual_seed(50 + view)
+            res.append(gs.sample(rec, R[2, view], T[2, view], K[0], w, timesteps=6))
+        outs[cache] = res
+        if cache:
+            assert len(gs._entries) == 2 and all(e["c"] is not None for e in gs._entries.values())
+            # parameters change -> next sample() must differ from a stale-weights replay and equal a fresh sampler's result
+            with torch.no_grad():
+                m.flat_parameters().mul_(1.01)
+            m._param_version += 1
+            random.seed(5)
+            torch.manual_seed(50)
+            after = gs.sample(rec0[:1], R[2, 0], T[2, 0], K[0], w, timesteps=6)
+            fresh = sampling.GraphSampler(m, b, cache_conditioning=True)
+            random.seed(5)
+            torch.manual_seed(50)
+            assert (after == fresh.sample(rec0[:1], R[2, 0], T[2, 0], K[0], w, timesteps=6)).all()
+            assert not (after == res[0]).all()
+    for a, c in zip(outs[False], outs[True]):
+        assert (a == c).all(), float(abs(a - c).max())

@@ -35,6 +35,7 @@ __device__ __forceinline__ float ex2_approx(float x) {
 struct alignas(64) AP {
   CUtensorMap tmQ, tmK, tmV, tmO, tmP;
   int N, L, Lb, heads, d, cross, qtiles, items, write_p;
+  int v_one_stage;      // all V chunks of an item fit the B part of ONE pipeline stage (kch * dch * 8 KB <= 32 KB)
   float scale_log2e;
 };
 
@@ -76,12 +77,25 @@ __global__ void __launch_bounds__(kThreads, 1) attn_fwd_kernel(const __grid_cons
           tma_load_4d(sa + 16384, &p.tmK, full_bar(stage), dc * 64, 0, head, nk);
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
-        for (int kc = 0; kc < kch; ++kc) {            // O = P V, reduction over keys in 64-key chunks
+        if (p.v_one_stage) {
+          // O = P V: the whole V of this (image, head) in one stage.  With one 64-key chunk per 48 KB stage (the general form
+          // below) the three stages ran out inside an item: the last V chunk and the next item's Q / K were requested only
+          // after PV MMAs had freed a stage, and their load latency sat on the serial chain (ncu: the softmax warps spent
+          // 39 % of their time waiting for O).
           mbar_wait(empty_bar(stage), phase ^ 1);
-          mbar_expect_tx(full_bar(stage), (uint32_t)dch * 8192u);
+          mbar_expect_tx(full_bar(stage), (uint32_t)(kch * dch) * 8192u);
           const uint32_t sb = smem_base + stage * kStageBytes + 16384;
-          for (int j = 0; j < dch; ++j) tma_load_4d(sb + j * 8192, &p.tmV, full_bar(stage), j * 64, kc * 64, head, nk);
+          for (int kc = 0; kc < kch; ++kc)
+            for (int j = 0; j < dch; ++j) tma_load_4d(sb + (kc * dch + j) * 8192, &p.tmV, full_bar(stage), j * 64, kc * 64, head, nk);
           if (++stage == kStages) { stage = 0; phase ^= 1; }
+        } else {
+          for (int kc = 0; kc < kch; ++kc) {            // O = P V, reduction over keys in 64-key chunks
+            mbar_wait(empty_bar(stage), phase ^ 1);
+            mbar_expect_tx(full_bar(stage), (uint32_t)dch * 8192u);
+            const uint32_t sb = smem_base + stage * kStageBytes + 16384;
+            for (int j = 0; j < dch; ++j) tma_load_4d(sb + j * 8192, &p.tmV, full_bar(stage), j * 64, kc * 64, head, nk);
+            if (++stage == kStages) { stage = 0; phase ^= 1; }
+          }
         }
       }
     }
@@ -106,15 +120,19 @@ __global__ void __launch_bounds__(kThreads, 1) attn_fwd_kernel(const __grid_cons
         mbar_wait(p_ready, iph);                       // P tile written (and S fully read) by the softmax warps
         tc_fence_after();
         for (int kc = 0; kc < kch; ++kc) {
-          mbar_wait(full_bar(stage), phase);
-          tc_fence_after();
-          const uint32_t sb = smem_base + stage * kStageBytes + 16384;
+          if (!p.v_one_stage || kc == 0) {
+            mbar_wait(full_bar(stage), phase);
+            tc_fence_after();
+          }
+          const uint32_t sb = smem_base + stage * kStageBytes + 16384 + (p.v_one_stage ? (uint32_t)(kc * dch) * 8192u : 0u);
           const int ksteps = min(4, (p.L - kc * 64 + 15) / 16);
           for (int k = 0; k < ksteps; ++k)
             umma_bf16(tmem_base + kTmemO, umma_desc(p_base + kc * 16384 + k * 32, 16, 1024), umma_desc(sb + k * 2048, 8192, 1024), idesc_pv,
                       (kc | k) != 0 ? 1u : 0u);
-          umma_commit(empty_bar(stage));
-          if (++stage == kStages) { stage = 0; phase ^= 1; }
+          if (!p.v_one_stage || kc == kch - 1) {
+            umma_commit(empty_bar(stage));
+            if (++stage == kStages) { stage = 0; phase ^= 1; }
+          }
         }
         umma_commit(o_full);
         iph ^= 1;
@@ -248,6 +266,7 @@ extern "C" int b3d_attn_fwd(const void* qkv, int N, int L, int heads, int d, int
   p.qtiles = (L + 127) / 128;
   p.items = N * heads * p.qtiles;
   p.write_p = probs != nullptr;
+  p.v_one_stage = ((L + 63) / 64) * ((d + 63) / 64) * 8192 <= 32768 ? 1 : 0;
   p.scale_log2e = scale * 1.4426950408889634f;
   const uint32_t ones[4] = {1, 1, 1, 1};
   b3d_view4 v;

@@ -38,7 +38,7 @@ __global__ void __launch_bounds__(256) pose_embedding_kernel(const double* __res
   constexpr int kPitch = 148;                       // floats per pixel row of the tile (16-byte aligned rows)
   __shared__ __align__(16) float s_out[2][32 * kPitch];
   __shared__ float s_posf[93];                      // position channel + first/other embedding (constant over the image)
-  __shared__ float s_fe[51];                        // first/other embedding of the direction channels
+  __shared__ float s_fe[144];                       // first / other embedding of this frame role
   __shared__ float s_dir[2][32][3];
   __shared__ float s_mul[51], s_ph[51];             // direction channels 93..143: multiplier 2^d, phase (0 or pi/2)
   __shared__ int s_ax[51];                          //   axis; -1 - axis for the three raw components
@@ -79,8 +79,8 @@ __global__ void __launch_bounds__(256) pose_embedding_kernel(const double* __res
       const int j = (cc - 3) % 24, d = j / 3;
       s_ax[cc] = j % 3; s_mul[cc] = (float)(1 << d); s_ph[cc] = cc - 3 >= 24 ? 1.5707963705062866f : 0.f;
     }
-    s_fe[cc] = fe ? fe[93 + cc] : 0.f;
   }
+  if (threadIdx.x < 144) s_fe[threadIdx.x] = fe ? fe[threadIdx.x] : 0.f;
   __syncthreads();
   const int xx = threadIdx.x & 31, w8 = threadIdx.x >> 5;
   const bool in_x = x0 + xx < W;
@@ -90,46 +90,47 @@ __global__ void __launch_bounds__(256) pose_embedding_kernel(const double* __res
   // compute them row by row inside the loop by the warp that owns the row parity)
   for (int ry = 0; ry < rows; ++ry) {
     const int y = y0 + ry, pb = ry & 1;
-    if (w8 == 0) {
-      const double u = (double)(x0 + xx) + 0.5, v = (double)y + 0.5;
-      double dx = s_M[0] * u + s_M[1] * v + s_M[2];
-      double dy = s_M[3] * u + s_M[4] * v + s_M[5];
-      double dz = s_M[6] * u + s_M[7] * v + s_M[8];
-      const double inv_n = 1.0 / sqrt(dx * dx + dy * dy + dz * dz);
-      s_dir[pb][xx][0] = (float)(dx * inv_n);
-      s_dir[pb][xx][1] = (float)(dy * inv_n);
-      s_dir[pb][xx][2] = (float)(dz * inv_n);
+    float* tile = s_out[pb];
+    // phase 0: the learned embeddings of the tile -- 18 independent, coalesced loads per thread in flight (ncu: with one
+    // load -> add -> store chain per element the warps sat on the load latency) -- while warp 0's lanes also do the
+    // fp64 ray directions of the row
+    {
+      const float* pe_row = pos_emb ? pos_emb + (long long)y * W + x0 + xx : nullptr;
+      const long long cstride = (long long)H * W;
+      float pe[18];
+#pragma unroll
+      for (int k = 0; k < 18; ++k) pe[k] = (in_x && pe_row) ? __ldg(pe_row + (w8 + 8 * k) * cstride) : 0.f;
+      if (w8 == 0) {
+        const double u = (double)(x0 + xx) + 0.5, v = (double)y + 0.5;
+        double dx = s_M[0] * u + s_M[1] * v + s_M[2];
+        double dy = s_M[3] * u + s_M[4] * v + s_M[5];
+        double dz = s_M[6] * u + s_M[7] * v + s_M[8];
+        const double inv_n = 1.0 / sqrt(dx * dx + dy * dy + dz * dz);
+        s_dir[pb][xx][0] = (float)(dx * inv_n);
+        s_dir[pb][xx][1] = (float)(dy * inv_n);
+        s_dir[pb][xx][2] = (float)(dz * inv_n);
+      }
+#pragma unroll
+      for (int k = 0; k < 18; ++k) {          // position channels are constants of the image: they go in here
+        const int c = w8 + 8 * k;
+        tile[xx * kPitch + c] = (c < 93 ? s_posf[c] : 0.f) + (in_x ? pe[k] + s_fe[c] : 0.f);
+      }
     }
     __syncthreads();
-    float* tile = s_out[pb];
-    const float* pe_row = pos_emb ? pos_emb + (long long)y * W + x0 + xx : nullptr;
-    const long long cstride = (long long)H * W;
-    // position channels: constant + learned embeddings
-    for (int c = w8; c < 93; c += 8) {
-      float v = s_posf[c];
-      if (in_x) {
-        if (pe_row) v += pe_row[c * cstride];
-        if (fe) v += __ldg(fe + c);
-      }
-      tile[xx * kPitch + c] = v;
-    }
-    // direction channels
-    for (int cc = w8; cc < 51; cc += 8) {
-      float v = 0.f;
-      if (cond) {
+    // phase A: the direction channels (sinf)
+    if (cond) {
+#pragma unroll 1
+      for (int cc = w8; cc < 51; cc += 8) {
         const int ax = s_ax[cc];
+        float v;
         if (ax < 0) v = s_dir[pb][xx][-1 - ax];
         else {
           float xb = s_dir[pb][xx][ax] * s_mul[cc];   // same fp32 operation order as posenc_nerf (xunet.py:49-59): x*2^d, + pi/2, sin
           if (cc >= 27) xb = xb + s_ph[cc];
           v = sinf(xb);
         }
+        tile[xx * kPitch + 93 + cc] += v;
       }
-      if (in_x) {
-        if (pe_row) v += pe_row[(93 + cc) * cstride];
-        v += s_fe[cc];
-      }
-      tile[xx * kPitch + 93 + cc] = v;
     }
     __syncthreads();
     // phase B (the next row's phase A writes the other tile buffer, so no barrier is needed after the stores)
@@ -393,7 +394,7 @@ __global__ void add_scale_kernel(const bf16* __restrict__ a, const bf16* __restr
 
 // out[g, c] (+)= sum over rows of group g of in[row, c];  rows_per_group rows per group   (bias / logsnr-emb grads)
 __global__ void colsum_kernel(const bf16* __restrict__ in, long long ld, int C, long long rows_per_group, int rows_per_block,
-                              float* __restrict__ out, long long out_ld) {
+                              float* __restrict__ out, long long out_ld, float scale) {
   const int g = blockIdx.z;
   const int c = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
   if (c >= C) return;
@@ -404,14 +405,14 @@ __global__ void colsum_kernel(const bf16* __restrict__ in, long long ld, int C, 
     const float2 v = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(base + r * ld));
     s0 += v.x; s1 += v.y;
   }
-  atomicAdd(out + g * out_ld + c, s0);
-  if (c + 1 < C) atomicAdd(out + g * out_ld + c + 1, s1);
+  atomicAdd(out + g * out_ld + c, s0 * scale);
+  if (c + 1 < C) atomicAdd(out + g * out_ld + c + 1, s1 * scale);
 }
 
 // the same for C % 8 == 0, C <= 2048: 16-byte loads, 4 rows in flight per thread, one block-level reduction and C
 // atomics per block (the 2-channel-per-thread loop above keeps one 4-byte load in flight: latency-bound)
 __global__ void __launch_bounds__(256) colsum_vec_kernel(const bf16* __restrict__ in, long long ld, int C, long long rows_per_group,
-                                                         int rows_per_block, float* __restrict__ out, long long out_ld) {
+                                                         int rows_per_block, float* __restrict__ out, long long out_ld, float scale) {
   b3d_pdl_sync();
   extern __shared__ float sm[];   // [rows_par, C]
   constexpr int U = 4;
@@ -443,7 +444,7 @@ __global__ void __launch_bounds__(256) colsum_vec_kernel(const bf16* __restrict_
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
     float s = 0.f;
     for (int r = 0; r < rows_par; ++r) s += sm[r * C + c];
-    atomicAdd(out + (long long)g * out_ld + c, s);
+    atomicAdd(out + (long long)g * out_ld + c, s * scale);
   }
 }
 
@@ -944,7 +945,8 @@ extern "C" int b3d_add_scale(const void* a, const void* b, void* out, float scal
   add_scale_kernel<<<grid_for(n / 8), kT, 0, STREAM>>>((const bf16*)a, (const bf16*)b, (bf16*)out, scale, n / 8);
   DONE(1);
 }
-extern "C" int b3d_colsum(const void* in, int64_t ld, int C, int64_t rows_per_group, int groups, float* out, int64_t out_ld, void* stream) {
+extern "C" int b3d_colsum(const void* in, int64_t ld, int C, int64_t rows_per_group, int groups, float* out, int64_t out_ld, float scale,
+                          void* stream) {
   B3D_CHECK_ARG(C % 2 == 0 && ld % 2 == 0, "colsum: even C/ld");
   if (C % 8 == 0 && ld % 8 == 0 && C <= 2048 && (((uintptr_t)in) & 15) == 0) {
     const int rows_par = 256 / (C / 8) > 0 ? 256 / (C / 8) : 1;
@@ -955,13 +957,13 @@ extern "C" int b3d_colsum(const void* in, int64_t ld, int C, int64_t rows_per_gr
     if (rpb < min_rows) rpb = min_rows;
     rpb = (rpb + min_rows - 1) / min_rows * min_rows;
     dim3 grid((unsigned)cdiv(rows_per_group, rpb), groups);
-    B3D_CUDA(b3d_launch_pdl(colsum_vec_kernel, dim3(grid), dim3(256), (size_t)rows_par * C * sizeof(float), STREAM, (const bf16*)in, ld, C, rows_per_group, (int)rpb, out, out_ld));
+    B3D_CUDA(b3d_launch_pdl(colsum_vec_kernel, dim3(grid), dim3(256), (size_t)rows_par * C * sizeof(float), STREAM, (const bf16*)in, ld, C, rows_per_group, (int)rpb, out, out_ld, scale));
     DONE(1);
   }
   int rpb = 256;
   while ((long long)cdiv(rows_per_group, rpb) * groups * cdiv(C, 256) > 148LL * 16 && rpb < rows_per_group) rpb *= 2;
   dim3 grid(cdiv(C / 2, 128), cdiv(rows_per_group, rpb), groups);
-  colsum_kernel<<<grid, 128, 0, STREAM>>>((const bf16*)in, ld, C, rows_per_group, rpb, out, out_ld);
+  colsum_kernel<<<grid, 128, 0, STREAM>>>((const bf16*)in, ld, C, rows_per_group, rpb, out, out_ld, scale);
   DONE(1);
 }
 extern "C" int b3d_batch_frame_sum(const void* in, void* out, int B, int64_t per_frame_elems, void* stream) {

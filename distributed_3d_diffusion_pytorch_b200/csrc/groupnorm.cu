@@ -233,7 +233,8 @@ struct BwdP {
   float* ws;                        // [N,32,2] (S1, S2), pre-zeroed
   // pass 2 outputs
   bf16* dx0; bf16* dx1; long long ld_dx0, ld_dx1;
-  const bf16* add0; long long ld_add0;   // optional, full C wide, added to dx
+  const bf16* add0; long long ld_add0;   // optional, full C wide, added to dx times add0_scale
+  float add0_scale;
   const bf16* add1a; const bf16* add1b; long long ld_add1a, ld_add1b;  // optional second addend, split like the sources
 };
 
@@ -407,7 +408,7 @@ __global__ void __launch_bounds__(kT, MODE == 2 ? kBwdBlocks2 : kBwdBlocks1) gn_
         for (int j = 0; j < 8; ++j) {
           const float g = fmaf(dz[j], ch.a[j], fmaf(f[j], k1[j], k0[j]));
           acc[j] += g;
-          d[j] = g + t0[j] + t1[j];
+          d[j] = fmaf(t0[j], p.add0_scale, g) + t1[j];
         }
         *reinterpret_cast<bf16x8*>(dxp + row * ld_dx + c1) = b3d_pack8(d);
       }
@@ -544,7 +545,7 @@ extern "C" int b3d_gn_bwd(const void* x0, int C0, int64_t ld0, const void* x1, i
                           int F, void* dss, int64_t ld_dss, float drop_p, uint64_t seed, const uint64_t* seed_ptr, float* dgamma, float* dbeta,
                           float* dss_sum, float* dx_sum, float* ws_s12,
                           void* dx0, int64_t ld_dx0, void* dx1, int64_t ld_dx1, const void* add0, int64_t ld_add0, const void* add1a,
-                          int64_t ld_add1a, const void* add1b, int64_t ld_add1b, void* stream) {
+                          int64_t ld_add1a, const void* add1b, int64_t ld_add1b, float add0_scale, void* stream) {
   if (int rc = check_src(x0, C0, x1, C1)) return rc;
   B3D_CHECK_ARG(mode >= 0 && mode <= 2, "gn_bwd: mode");
   B3D_CHECK_ARG(mode != 2 || (ss && dss && F == C0 + C1), "gn_bwd: film needs ss, dss, F == C");
@@ -555,7 +556,7 @@ extern "C" int b3d_gn_bwd(const void* x0, int C0, int64_t ld0, const void* x1, i
   p.ss = (const bf16*)ss; p.ld_ss = ld_ss; p.F = F; p.dss = (bf16*)dss; p.ld_dss = ld_dss; p.drop_p = drop_p; p.seed = seed; p.seed_ptr = (const unsigned long long*)seed_ptr;
   p.dgamma = dgamma; p.dbeta = dbeta; p.ws = ws_s12; p.dss_sum = dss_sum; p.dx_sum = dx_sum;
   p.dx0 = (bf16*)dx0; p.dx1 = (bf16*)dx1; p.ld_dx0 = ld_dx0; p.ld_dx1 = ld_dx1;
-  p.add0 = (const bf16*)add0; p.ld_add0 = ld_add0;
+  p.add0 = (const bf16*)add0; p.ld_add0 = ld_add0; p.add0_scale = add0_scale;
   p.add1a = (const bf16*)add1a; p.add1b = (const bf16*)add1b; p.ld_add1a = ld_add1a; p.ld_add1b = ld_add1b;
   const int C = C0 + C1;
   cudaStream_t st = (cudaStream_t)stream;

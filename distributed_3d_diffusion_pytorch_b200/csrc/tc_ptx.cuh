@@ -99,8 +99,12 @@ __device__ __forceinline__ uint32_t mapa_shared(uint32_t local, uint32_t rank) {
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(local), "r"(rank));
   return ra;
 }
+// Arrive on a barrier of another CTA of the cluster.  CTA-scope release (the default) on purpose: what this hands over is
+// TMEM already read by tcgen05.ld (ordered by tcgen05.wait::ld + fence::before_thread_sync), not generic memory.  With
+// `.release.cluster` the compiler emits MEMBAR.ALL.GPU + ERRBAR in front of the arrive; ncu's stall sampling put 9 % of the
+// pair kernel's samples (14 % of the epilogue warps' time) on exactly those two instructions.
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 // TMA load of this CTA's part of a pair tile; the bytes are counted on the barrier at `bar_cluster_addr` (the leader's)
 __device__ __forceinline__ void tma_load_4d_pair(uint32_t dst, const CUtensorMap* tm, uint32_t bar_cluster_addr, int c0, int c1, int c2, int c3) {

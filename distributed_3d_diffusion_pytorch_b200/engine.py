@@ -635,12 +635,12 @@ class Engine:
                     out.append(a)
         return out
 
-    def _conv_wgrad(self, wname, dy, x, gw, co_alloc=None, stride=1):
+    def _conv_wgrad(self, wname, dy, x, gw, co_alloc=None, stride=1, alpha=1.0):
         """3x3 weight gradient: packed fp32 [Co, 9*Cpad] through split-K atomics, then back to [Co,Ci,3,3]."""
         Co, Ci = gw.shape[0], gw.shape[1]
         cp = G.ceil64(Ci)
         gp = self.zbuf("bwd", "gp." + wname, (co_alloc or Co, 9 * cp))
-        self.ops.gemm(G.wgrad_desc(dy, x, 9, gp, 0, cp, stride))
+        self.ops.gemm(G.wgrad_desc(dy, x, 9, gp, 0, cp, stride, alpha=alpha))
         self._unpack(gp, 0, cp, gw)
 
     def _take_grad(self, act):
@@ -665,40 +665,42 @@ class Engine:
             ops.avgpool2(self._grad_of(sa["final"]), dout, 1.0)
         else:
             dout = self._grad_of(out)
-        gs = self.side_tmp(n, "gs", (N, hh, ww, F))
-        ops.scale_colsum(dout, gs, RSQRT2, Gr[n + ".conv2.bias"])     # d(conv2.bias) = column sums of the scaled gradient
-        gs2 = gs.view(M, F)
-        # weight gradients of conv2 and the 1x1 skip: on the side stream, beside the data-gradient chain below (they only
-        # read gs and saved activations; joined at the end of the block, before gs is rewritten)
+        # The block's output was (h + h_in) / sqrt(2) (xunet.py:152): that factor is the alpha of every GEMM that reads dout and
+        # the scale of the skip-path addend below -- a scaled copy of dout (one more pass over HBM, one more launch on the
+        # data-gradient chain) is never made.  Bias gradients = column sums of dout, beside the chain.
+        dout2 = dout.view(M, F)
+        # weight gradients of conv2 and the 1x1 skip, d(conv2.bias): on the side stream, beside the data-gradient chain below
+        # (they only read dout and saved activations)
         with ops.side():
-            self._conv_wgrad(n + ".conv2.weight", gs, sa["a1"].view(N, hh, ww, F), Gr[n + ".conv2.weight"])
+            ops.colsum(dout2, M, Gr[n + ".conv2.bias"], scale=RSQRT2)
+            self._conv_wgrad(n + ".conv2.weight", dout, sa["a1"].view(N, hh, ww, F), Gr[n + ".conv2.weight"], alpha=RSQRT2)
             if s.cin != F:
                 gw = Gr[n + ".dense.weight"].view(F, s.cin)
                 srcs = [h_in] + ([skip] if skip is not None else [])
                 koff = 0
                 if len(srcs) == 1:
-                    ops.gemm(G.wgrad_dense_desc(gs2, h_in.t.view(M, s.cin), gw))
+                    ops.gemm(G.wgrad_dense_desc(dout2, h_in.t.view(M, s.cin), gw, alpha=RSQRT2))
                 else:
                     gp = self.zbuf("bwd", "gp." + n + ".dense", (F, sum(G.ceil64(a.t.shape[3]) for a in srcs)))
                     ci0 = 0
                     for a in srcs:
                         c = a.t.shape[3]
-                        ops.gemm(G.wgrad_desc(gs, a.t, 1, gp, koff, G.ceil64(c)))
+                        ops.gemm(G.wgrad_desc(dout, a.t, 1, gp, koff, G.ceil64(c), alpha=RSQRT2))
                         self._unpack(gp, koff, G.ceil64(c), Gr[n + ".dense.weight"], ci0=ci0, cn=c)
                         koff += G.ceil64(c)
                         ci0 += c
         # conv2 data gradient
         da1 = self.tmp("da1", (N, hh, ww, F))
-        ops.gemm(G.conv_desc([gs], [9], Wp[n + ".conv2.weight.T"], F, da1))
+        ops.gemm(G.conv_desc([dout], [9], Wp[n + ".conv2.weight.T"], F, da1, alpha=RSQRT2))
         # 1x1 skip
         if s.cin != F:
             if self._unpack_rec:       # d(dense.bias) = the same column sums as d(conv2.bias): copied at the end of backward
                 ops.record_copy(self._copy_jl[self._cur_phase], Gr[n + ".conv2.bias"], Gr[n + ".dense.bias"])
             dskip = self.tmp("dskip", (N, HW, s.cin))
-            ops.gemm(G.dense_desc(gs2, Wp[n + ".dense.weight.T"], dskip.view(M, s.cin), s.cin))
-            add0 = dskip
+            ops.gemm(G.dense_desc(dout2, Wp[n + ".dense.weight.T"], dskip.view(M, s.cin), s.cin, alpha=RSQRT2))
+            add0, add0_scale = dskip, 1.0
         else:
-            add0 = gs.view(N, HW, F)
+            add0, add0_scale = dout.view(N, HW, F), RSQRT2
         # GN1 + FiLM (+dropout)
         ssv = self.saved["ss"][s.lvl][:, s.film_off:s.film_off + 2 * F]
         dssv = dss_l[:, s.film_off:s.film_off + 2 * F]
@@ -726,7 +728,7 @@ class Engine:
         v3 = lambda t_: t_.view(N, HW, -1) if t_ is not None else None
         ops.gn_bwd(x0, x1, sa["sums0"], P[n + ".groupnorm0.gn.weight"], P[n + ".groupnorm0.gn.bias"], 1, da0.view(N, HW, s.cin),
                    Gr[n + ".groupnorm0.gn.weight"], Gr[n + ".groupnorm0.gn.bias"], self.zbuf("bwd", n + ".ws0", (N, 32, 2)), v3(g0), v3(g1),
-                   add0=add0, add1a=v3(e0), add1b=v3(e1))
+                   add0=add0, add1a=v3(e0), add1b=v3(e1), add0_scale=add0_scale)
         self._block_join()
 
     def _attn_bwd(self, s, P, Wp, Gr):
@@ -739,14 +741,13 @@ class Engine:
         a = n + ".attn_layer.attn"
         alpha = 1.0 / math.sqrt(d)
         dout = self._grad_of(out)
-        gs4 = self.side_tmp(n, "ags", (N, hh, ww, C))
-        ops.scale_colsum(dout, gs4, RSQRT2, Gr[n + ".linear.bias"])
-        gs = gs4.view(M, C)
+        gs = dout.view(M, C)      # the (h + h_in) / sqrt(2) of xunet.py:220 is folded into the consumers of dout (see _res_bwd)
         # 1x1 `linear` and out_proj
         with ops.side():      # parameter gradients run beside the data-gradient chain (joined at the end of the block)
-            ops.gemm(G.wgrad_dense_desc(gs, sa["o1"], Gr[n + ".linear.weight"].view(C, C)))
+            ops.colsum(gs, M, Gr[n + ".linear.bias"], scale=RSQRT2)
+            ops.gemm(G.wgrad_dense_desc(gs, sa["o1"], Gr[n + ".linear.weight"].view(C, C), alpha=RSQRT2))
         do1 = self.side_tmp(n, "do1", (M, C))
-        ops.gemm(G.dense_desc(gs, Wp[n + ".linear.weight.T"], do1, C))
+        ops.gemm(G.dense_desc(gs, Wp[n + ".linear.weight.T"], do1, C, alpha=RSQRT2))
         with ops.side():
             ops.colsum(do1, M, Gr[a + ".out_proj.bias"])
             ops.gemm(G.wgrad_dense_desc(do1, sa["o"].view(M, C), Gr[a + ".out_proj.weight"]))
@@ -781,5 +782,5 @@ class Engine:
         g0, e0 = self._take_grad(h_in)
         ops.gn_bwd(h_in.t.view(N, L, C), None, sa["sums"], P[n + ".groupnorm.gn.weight"], P[n + ".groupnorm.gn.bias"], 0, dg,
                    Gr[n + ".groupnorm.gn.weight"], Gr[n + ".groupnorm.gn.bias"], self.zbuf("bwd", n + ".ws", (N, 32, 2)),
-                   g0.view(N, L, C), None, add0=gs.view(N, L, C), add1a=e0.view(N, L, C) if e0 is not None else None)
+                   g0.view(N, L, C), None, add0=gs.view(N, L, C), add1a=e0.view(N, L, C) if e0 is not None else None, add0_scale=RSQRT2)
         self._block_join()

@@ -42,7 +42,7 @@ def pick_split_k(tiles, kblocks):
     return max(1, s)
 
 
-def wgrad_desc(dy, x, taps, out_packed, k_off, Cpad, stride=1, split_k=None):
+def wgrad_desc(dy, x, taps, out_packed, k_off, Cpad, stride=1, split_k=None, alpha=1.0):
     """out_packed[co, k_off + tap*Cpad + ci] += sum_pixels dy[p, co] * x[p*stride + tap - pad, ci]  (fp32, atomic)."""
     N, H, W, Co = dy.shape
     Ci = x.shape[-1]
@@ -55,11 +55,11 @@ def wgrad_desc(dy, x, taps, out_packed, k_off, Cpad, stride=1, split_k=None):
         split_k = pick_split_k(tiles, kblocks)
     o = out_packed[:, k_off:][None, None]
     return GemmDesc(a=[dy], b=x, out=o, n_cols=Ci, m_rows=Co, a_major=1, b_major=1, conv_stride=stride, pad=1 if taps == 9 else 0,
-                    b_taps=taps, W=W, H=H, N=N, split_k=split_k, out_tap_stride=Cpad, out_atomic=True, bn_tile=bn)
+                    b_taps=taps, W=W, H=H, N=N, split_k=split_k, out_tap_stride=Cpad, out_atomic=True, bn_tile=bn, alpha=alpha)
 
 
-def wgrad_dense_desc(dy2d, x2d, out_packed, k_off=0, split_k=None):
-    return wgrad_desc(dy2d[None, None], x2d[None, None], 1, out_packed, k_off, ceil64(x2d.shape[1]), 1, split_k)
+def wgrad_dense_desc(dy2d, x2d, out_packed, k_off=0, split_k=None, alpha=1.0):
+    return wgrad_desc(dy2d[None, None], x2d[None, None], 1, out_packed, k_off, ceil64(x2d.shape[1]), 1, split_k, alpha)
 
 
 # ---- attention (nn.MultiheadAttention internals); q/k/v/o: [N, heads, L, d] views, s/p: [N, heads, Lq, Lk]

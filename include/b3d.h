@@ -154,8 +154,9 @@ int b3d_silu_bwd(const void* dy, const void* x, void* dx, int64_t n, void* strea
 int b3d_silu_bwd_colsum(const void* dy, const void* x, void* dx, int C, int64_t rows_per_group, int groups, float* group_out,
                         int64_t group_ld, float* total_out, void* stream);
 int b3d_add_scale(const void* a, const void* b, void* out, float scale, int64_t n, void* stream);
-/* out[g,c] += sum of rows of group g (bias gradients; d logsnr_emb per image, xunet.py:502); out fp32, pre-zeroed */
-int b3d_colsum(const void* in, int64_t ld, int C, int64_t rows_per_group, int groups, float* out, int64_t out_ld, void* stream);
+/* out[g,c] += scale * sum of rows of group g (bias gradients -- scale folds the 1/sqrt2 of xunet.py:152,220; d logsnr_emb
+ * per image, xunet.py:502); out fp32, pre-zeroed */
+int b3d_colsum(const void* in, int64_t ld, int C, int64_t rows_per_group, int groups, float* out, int64_t out_ld, float scale, void* stream);
 /* out[f,...] = sum_b in[b,f,...]  (gradient of the batch-shared learned embeddings, xunet.py:334-336) */
 int b3d_batch_frame_sum(const void* in, void* out, int B, int64_t per_frame_elems, void* stream);
 /* adjoint of the strided conditioning convs w.r.t. their input from per-tap GEMM products, xunet.py:340-349 */
@@ -173,7 +174,8 @@ int b3d_softmax_bwd(const void* P, int64_t ld_p, const void* dP, int dp_fp32, in
  *   scale = ss[row, c], shift = ss[row, F + c]; ss_image (optional int32 [N], device): image n takes the ss rows of image
  *   ss_image[n] -- the sampler's batch holds only four distinct conditionings, so FiLM is evaluated for four images.
  * b3d_gn_bwd: autograd of the same lines; writes d(scale,shift) to dss, accumulates dgamma/dbeta (fp32),
- *   uses ws_s12 fp32 [N,32,2] (caller zeroes it), writes dx0/dx1 (+ add0 + add1a/add1b when given).  Optional fused
+ *   uses ws_s12 fp32 [N,32,2] (caller zeroes it), writes dx0/dx1 (+ add0_scale * add0 + add1a/add1b when given: the
+ *   residual branch's gradient joins here with its 1/sqrt2, xunet.py:152,220).  Optional fused
  *   reductions (fp32, accumulated): dss_sum [2F] = column sums of dss (FiLM dense bias gradient, xunet.py:80),
  *   dx_sum [C] = column sums of dx before the addends (bias gradient of the layer that produced x). */
 int b3d_gn_stats(const void* x0, int C0, int64_t ld0, const void* x1, int C1, int64_t ld1, int N, int HW, float* ws_sums, void* stream);
@@ -194,7 +196,7 @@ int b3d_gn_bwd(const void* x0, int C0, int64_t ld0, const void* x1, int C1, int6
                void* dss, int64_t ld_dss, float drop_p, uint64_t seed, const uint64_t* seed_ptr, float* dgamma, float* dbeta, float* dss_sum,
                float* dx_sum, float* ws_s12, void* dx0,
                int64_t ld_dx0, void* dx1, int64_t ld_dx1, const void* add0, int64_t ld_add0, const void* add1a, int64_t ld_add1a,
-               const void* add1b, int64_t ld_add1b, void* stream);
+               const void* add1b, int64_t ld_add1b, float add0_scale, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Diffusion glue (fp32 NCHW, as the reference holds these tensors)

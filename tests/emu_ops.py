@@ -372,9 +372,9 @@ class EmuOps:
         v = a.float() + (b.float() if b is not None else 0)
         out.copy_((v * scale).to(out.dtype))
 
-    def colsum(self, x2d, rows_per_group, out):
+    def colsum(self, x2d, rows_per_group, out, scale=1.0):
         rows, C = x2d.shape
-        out.view(-1, out.shape[-1])[:, :C].add_(x2d.float().reshape(rows // rows_per_group, rows_per_group, C).sum(1))
+        out.view(-1, out.shape[-1])[:, :C].add_(x2d.float().reshape(rows // rows_per_group, rows_per_group, C).sum(1) * scale)
 
     def batch_frame_sum(self, x, out):
         B = x.shape[0] // 2
@@ -457,7 +457,7 @@ class EmuOps:
         self.gn_apply(x0, x1, sums, gamma, beta, mode, out, **kw)
 
     def gn_bwd(self, x0, x1, sums, gamma, beta, mode, dy, dgamma, dbeta, ws, dx0, dx1=None, ss=None, F=0, dss=None, drop_p=0.0, seed=0,
-               add0=None, add1a=None, add1b=None, seed_ptr=None, dss_sum=None, dx_sum=None):
+               add0=None, add1a=None, add1b=None, seed_ptr=None, dss_sum=None, dx_sum=None, add0_scale=1.0):
         seed = (seed + (int(seed_ptr.item()) * SEED_STEP_STRIDE if seed_ptr is not None else 0)) & ((1 << 64) - 1)
         x = self._cat(x0, x1)
         N, HW, C = x.shape
@@ -489,7 +489,7 @@ class EmuOps:
         if dx_sum is not None:
             dx_sum += dx.sum((0, 1))
         if add0 is not None:
-            dx = dx + add0.float()
+            dx = dx + add0.float() * add0_scale
         C0 = x0.shape[-1]
         if add1a is not None:
             dx[..., :C0] += add1a.float()

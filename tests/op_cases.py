@@ -56,7 +56,7 @@ def gn_case(N, HW, C0, C1, mode, drop_p=0.0, seed=0, step=None):
         add0 = _mk(ops, _r((N, HW, C), g))
         add1a = _mk(ops, _r((N, HW, C0), g))
         ops.gn_bwd(x0, x1, sums, gamma, beta, mode, dy, dgamma, dbeta, ws, dx0, dx1, ss=ss, F=F, dss=dss, drop_p=drop_p, seed=77,
-                   add0=add0, add1a=add1a, seed_ptr=sp)
+                   add0=add0, add1a=add1a, seed_ptr=sp, add0_scale=0.7071067811865476 if (seed % 2) else 1.0)
         outs = [sums, out, dgamma, dbeta, ws, dx0]
         if C1:
             outs.append(dx1)
@@ -146,7 +146,7 @@ def misc_case(seed=0):
         big = _mk(ops, _r((4 * 300, 128), g))
         ops.colsum(big[:, 16:112], 300, cs); outs.append(cs)
         cs1 = ops.zeros((96,), torch.float32)
-        ops.colsum(big[:, 16:112], 1200, cs1); outs.append(cs1)
+        ops.colsum(big[:, 16:112], 1200, cs1, scale=0.7071067811865476); outs.append(cs1)
         bf = _mk(ops, _r((10, 4, 4, 64), g))
         bo = ops.zeros((2, 4, 4, 64)); ops.batch_frame_sum(bf, bo); outs.append(bo)
         for s_, h_ in ((1, 8), (2, 4), (4, 2), (8, 1)):

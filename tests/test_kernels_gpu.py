@@ -34,7 +34,10 @@ def test_gemm(case, backends):
     torch.cuda.synchronize()
     emu.gemm(d_e)
     for a, b in zip(outs_c, outs_e):
-        assert _cmp(a, b) <= (8e-3 if a.dtype == torch.bfloat16 else 2e-4)
+        tol = 8e-3 if a.dtype == torch.bfloat16 else 2e-4
+        if "stats" in case.name and a.dtype == torch.float32 and emu.stats_dtype is None:
+            tol = 1e-3       # the kernel sums the bf16 values it STORES; the pure-fp32 checker sums unrounded ones (measured 2.4-3.3e-4)
+        assert _cmp(a, b) <= tol, (case.name, _cmp(a, b))
 
 
 @pytest.mark.parametrize("name", list(op_cases.all_cases().keys()))

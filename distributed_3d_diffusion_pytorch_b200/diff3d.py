@@ -146,13 +146,18 @@ class FusedAdam:
             self.ema = flat.clone()
         return flat
 
-    def step(self, grad_scale=1.0):
+    def step(self, grad_scale=1.0, lo=None, hi=None, first=True):
+        """One Adam step.  (lo, hi): update only that element range of the arena -- a data-parallel trainer steps each gradient
+        range as soon as its all-reduce has finished, beside the rest of the backward pass; `first` marks the first range of a
+        step (the step count advances once per step)."""
         flat, g = self._arenas(), self.model.flat_gradients()
-        self.step_count += 1
-        self.model._param_version = getattr(self.model, "_param_version", 0) + 1
+        if first:
+            self.step_count += 1
+            self.model._param_version = getattr(self.model, "_param_version", 0) + 1
         pg = self.param_groups[0]
-        _ops(flat.device).adam(flat, g, self.m, self.v, pg["lr"], pg["betas"][0], pg["betas"][1], pg["eps"], self.step_count, grad_scale,
-                               ema=self.ema, ema_decay=self.ema_decay or 0.0)
+        sl = slice(lo, hi)
+        _ops(flat.device).adam(flat[sl], g[sl], self.m[sl], self.v[sl], pg["lr"], pg["betas"][0], pg["betas"][1], pg["eps"], self.step_count,
+                               grad_scale, ema=self.ema[sl] if self.ema is not None else None, ema_decay=self.ema_decay or 0.0)
 
     def ema_state_dict(self):
         """EMA weights under the model's state_dict names (load them into an XUNet to sample with them)"""

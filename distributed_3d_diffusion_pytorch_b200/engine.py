@@ -176,9 +176,12 @@ class Engine:
         return self.cfg.H >> lvl, self.cfg.W >> lvl
 
     # ------------------------------------------------------------------ weights
-    def _pack_weights(self, P, training, repack=True):
+    def _pack_weights(self, P, training, repack=True, overlap=False):
         """fp32 PyTorch-layout parameters -> bf16 K-major operands (per forward: parameters change every step).
-        The ~450 conversions are recorded once (all addresses are static) and then run as ONE kernel launch per step."""
+        The ~450 conversions are recorded once (all addresses are static) and then run as TWO kernel launches per step: the
+        operands the forward needs first (logsnr MLP, level-0 conditioning conv and FiLM, stem, level-0 down blocks), and all
+        the others.  overlap=True puts the second, large launch (HBM-bound, ~1 GB) on the side stream, beside the tensor-bound
+        level-0 work; the caller joins the side stream before the first use of any other operand."""
         sig = (training, len(P), tuple(P[k].data_ptr() for k in list(P.keys())[:8]))
         cached = self._pack_cache.get(training)
         if cached is None or cached[0] != sig:
@@ -186,12 +189,24 @@ class Engine:
             self._pack_cache[training] = cached
             repack = True
         if repack:
-            self.ops.run_jobs(cached[2])
+            first, rest = cached[2]
+            self.ops.run_jobs(first)
+            if overlap:
+                with self.ops.side():
+                    self.ops.run_jobs(rest)
+            else:
+                self.ops.run_jobs(rest)
         return cached[1]
+
+    @staticmethod
+    def _needed_first(name):
+        cp = "conditioningprocessor."
+        return name.startswith((cp + "logsnr_emb_emb", cp + "convs.0.", "conv.", "xunetblocks.0.", "film0"))
 
     def _record_pack(self, P, training):
         ops, cfg, W = self.ops, self.cfg, {}
-        jl = JobList("pack")
+        jl_first, jl_rest = JobList("pack"), JobList("pack")
+        pick = lambda name: jl_first if self._needed_first(name) else jl_rest      # (backward-only operands always go to jl_rest)
 
         def conv3(name, w, Co_alloc=None):
             Co, Ci = w.shape[0], w.shape[1]
@@ -199,12 +214,12 @@ class Engine:
             f = self.buf("w.f." + name, (Co_alloc or Co, 9 * cp))
             if Co_alloc:
                 f.zero_()
-            ops.record_pack_weight(jl, w, 0, f, Cpad=cp)
+            ops.record_pack_weight(pick(name), w, 0, f, Cpad=cp)
             W[name] = f
             if training:
                 cop = G.ceil64(Co)
                 t = self.buf("w.t." + name, (Ci, 9 * cop))
-                ops.record_pack_weight(jl, w, 1, t, Cpad=cop)
+                ops.record_pack_weight(jl_rest, w, 1, t, Cpad=cop)
                 W[name + ".T"] = t
 
         def lin(name, w, srcs=None):
@@ -213,13 +228,13 @@ class Engine:
             f = self.buf("w.f." + name, (Co, sum(G.ceil64(c) for c in srcs)))
             ci0 = koff = 0
             for c in srcs:
-                ops.record_pack_weight(jl, w, 0, f, ci0=ci0, cn=c, Cpad=G.ceil64(c), k_off=koff)
+                ops.record_pack_weight(pick(name), w, 0, f, ci0=ci0, cn=c, Cpad=G.ceil64(c), k_off=koff)
                 ci0 += c
                 koff += G.ceil64(c)
             W[name] = f
             if training:
                 t = self.buf("w.t." + name, (Ci, G.ceil64(Co)))
-                ops.record_pack_weight(jl, w, 1, t, Cpad=G.ceil64(Co))
+                ops.record_pack_weight(jl_rest, w, 1, t, Cpad=G.ceil64(Co))
                 W[name + ".T"] = t
 
         cp = "conditioningprocessor."
@@ -228,20 +243,20 @@ class Engine:
         for l in range(cfg.num_resolutions):
             w = P[cp + f"convs.{l}.weight"]
             f = self.buf(f"w.f.cc{l}", (cfg.emb_ch, 9 * 192))
-            ops.record_pack_weight(jl, w, 0, f, Cpad=192)
+            ops.record_pack_weight(pick(cp + f"convs.{l}."), w, 0, f, Cpad=192)
             W[cp + f"convs.{l}.weight"] = f
             if training:
                 t = self.buf(f"w.r.cc{l}", (9 * 144, cfg.emb_ch))
-                ops.record_pack_weight(jl, w, 2, t)
+                ops.record_pack_weight(jl_rest, w, 2, t)
                 W[cp + f"convs.{l}.weight.R"] = t
         # stem: the packed input tensor has 8 channels (3 real)
         f = self.buf("w.f.stem", (cfg.ch, 9 * 64))
-        ops.record_pack_weight(jl, P["conv.weight"], 0, f, Cpad=64)
+        ops.record_pack_weight(jl_first, P["conv.weight"], 0, f, Cpad=64)
         W["conv.weight"] = f
         conv3("lastconv.weight", P["lastconv.weight"], Co_alloc=16)
         lb = self.buf("lastconv.b16", (16,), torch.float32)
         lb.zero_()
-        ops.record_copy(jl, P["lastconv.bias"], lb[:3])
+        ops.record_copy(jl_rest, P["lastconv.bias"], lb[:3])
         # FiLM: one [sum 2F, 1024] operand per level (+ its transpose for the data gradient)
         for l in range(cfg.num_resolutions):
             W[f"film{l}"] = self.buf(f"w.f.film{l}", (self.film_cols[l], 1024))
@@ -257,16 +272,16 @@ class Engine:
                 if s.cin != s.f:
                     lin(n + ".dense.weight", P[n + ".dense.weight"], s.srcs_c if s.cat else None)
                 fw = P[n + ".film.dense.weight"]
-                ops.record_pack_weight(jl, fw, 0, W[f"film{s.lvl}"][s.film_off:s.film_off + 2 * s.f], Cpad=1024)
-                ops.record_copy(jl, P[n + ".film.dense.bias"], self._bufs[f"b.film{s.lvl}"][s.film_off:s.film_off + 2 * s.f])
+                ops.record_pack_weight(pick(f"film{s.lvl}"), fw, 0, W[f"film{s.lvl}"][s.film_off:s.film_off + 2 * s.f], Cpad=1024)
+                ops.record_copy(pick(f"film{s.lvl}"), P[n + ".film.dense.bias"], self._bufs[f"b.film{s.lvl}"][s.film_off:s.film_off + 2 * s.f])
                 if training:
-                    ops.record_pack_weight(jl, fw, 1, W[f"film{s.lvl}.T"], Cpad=2 * s.f, k_off=s.film_off)
+                    ops.record_pack_weight(jl_rest, fw, 1, W[f"film{s.lvl}.T"], Cpad=2 * s.f, k_off=s.film_off)
             elif kind == "attn":
                 a = s.name + ".attn_layer.attn"
                 lin(a + ".in_proj_weight", P[a + ".in_proj_weight"])
                 lin(a + ".out_proj.weight", P[a + ".out_proj.weight"])
                 lin(s.name + ".linear.weight", P[s.name + ".linear.weight"])
-        return W, jl
+        return W, (jl_first, jl_rest)
 
     # ------------------------------------------------------------------ forward
     def cond_features(self, P, R, t, K, cond_mask, repack=True):
@@ -304,7 +319,7 @@ class Engine:
             self._zero_cap["bwd"] = int(sum(p.numel() for p in P.values()) * 1.4) + (1 << 23)
         self._zero_phase("fwd")
         need_bwd = training if need_bwd is None else need_bwd
-        Wp = self._pack_weights(P, need_bwd, repack)      # repack=False: parameters unchanged since the last call (sampling)
+        Wp = self._pack_weights(P, need_bwd, repack, overlap=True)      # repack=False: parameters unchanged since the last call (sampling)
         drop_p = float(cfg.dropout) if training else 0.0
         sv = self.saved = {"P": P, "W": Wp, "need_bwd": need_bwd, "drop_p": drop_p, "seed": seed, "acts": {}}
         cp = "conditioningprocessor."
@@ -368,12 +383,13 @@ class Engine:
             elif kind == "pop":
                 skip = hs.pop()
             elif kind == "res":
-                if s.lvl >= 1:
-                    ops.join_side()            # FiLM operands of the coarser levels (no-op once joined)
+                if s.lvl >= 1 or not self._needed_first(s.name):
+                    ops.join_side()            # FiLM operands of the coarser levels, the second weight-pack launch (no-op once joined)
                 h = self._res_fwd(s, h, skip if s.cat else None, ss[s.lvl], P, Wp, drop_p, seed * 1000 + bi)
                 skip = None
                 bi += 1
             else:
+                ops.join_side()
                 h = self._attn_fwd(s, h, P, Wp)
         assert not hs
         ops.join_side()

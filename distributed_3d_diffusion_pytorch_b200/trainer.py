@@ -166,8 +166,10 @@ class Trainer:
             lo, hi = self.ranges[ph]
             with torch.cuda.stream(self.comm):
                 parallel.allreduce_mean_(g[lo:hi])                     # NCCL over NVLink, concurrent with the next phase
-        main.wait_stream(self.comm)
-        self.opt.step()
+                # ... and so is this range's Adam step: the later phases read packed bf16 operands and the fp32 GroupNorm
+                # parameters of THEIR OWN blocks only, never a parameter of a range that is already reduced
+                self.opt.step(lo=lo, hi=hi, first=ph == 0)
+        main.wait_stream(self.comm)                                    # the next forward repacks the updated parameters
         self.step_idx += 1
 
     def step_e2e(self, host_batch):

@@ -214,9 +214,10 @@ def test_no_cpu_fallback():
 
 def test_cached_conditioning_matches_uncached_and_follows_parameter_updates():
     """GraphSampler(cache_conditioning=True) -- conditioning convs evaluated once per camera, FiLM for the 4 distinct
-    conditionings -- computes the same arithmetic as the uncached sampler (one forward: equal up to the order of the fp32
-    atomics of the GroupNorm statistics; over a growing record: the same trajectory), and a parameter change between
-    sample() calls is picked up (the packed operands and the cache are keyed on the model's parameter version)."""
+    conditionings -- computes the same arithmetic as the uncached sampler: single denoise steps from identical states agree up
+    to the order of the fp32 atomics of the GroupNorm statistics, also when the conditioning entry / the target view change
+    and the cache is hit; a parameter change between calls is picked up (the packed operands and the cache are keyed on the
+    model's parameter version).  Whole trajectories are not compared: see test_glue_gpu.py on why they are chaotic."""
     import random
     from distributed_3d_diffusion_pytorch_b200 import sampling, synthetic
     dev = "cuda:0"
@@ -224,42 +225,33 @@ def test_cached_conditioning_matches_uncached_and_follows_parameter_updates():
     b = 4
     img, R, T, K = synthetic.make_views(3, 32, seed=2)
     w = torch.tensor([0.0, 1.0, 2.0, 3.0])
-    rec0 = [[img[0, 0][None].repeat(b, 1, 1, 1).numpy(), R[0, 0].numpy(), T[0, 0].numpy()],
-            [img[1, 0][None].repeat(b, 1, 1, 1).numpy(), R[1, 0].numpy(), T[1, 0].numpy()]]
-    outs = {}
-    for cache in (False, True):
-        gs = sampling.GraphSampler(m, b, cache_conditioning=cache)
-        res = []
-        for view in range(2):                      # two target views, the record grows in between
-            rec = rec0[:1 + view]
-            random.seed(5 + view)
-            torch.manual_seed(50 + view)
-            res.append(gs.sample(rec, R[2, view], T[2, view], K[0], w, timesteps=6))
-        outs[cache] = res
-        if cache:
-            assert len(gs._entries) == 2 and all(e["c"] is not None for e in gs._entries.values())
-            # parameters change -> next sample() must differ from a stale-weights replay and equal a fresh sampler's result
-            with torch.no_grad():
-                m.flat_parameters().mul_(1.01)
-            m._param_version += 1
-            random.seed(5)
-            torch.manual_seed(50)
-            after = gs.sample(rec0[:1], R[2, 0], T[2, 0], K[0], w, timesteps=6)
-            fresh = sampling.GraphSampler(m, b, cache_conditioning=True)
-            random.seed(5)
-            torch.manual_seed(50)
-            ref = fresh.sample(rec0[:1], R[2, 0], T[2, 0], K[0], w, timesteps=6)
-            rel = lambda a, c: float(((a - c) ** 2).sum() ** 0.5 / ((c ** 2).sum() ** 0.5))
-            assert rel(after, ref) <= 2e-2, rel(after, ref)
-            assert rel(after, res[0]) > 5 * rel(after, ref) + 1e-3          # really the new weights
-    for a, c in zip(outs[False], outs[True]):
-        assert rel(a, c) <= 2e-2, rel(a, c)
-    # one forward, cached against uncached, on identical inputs: only atomic-order noise may differ
-    ga, gb = sampling.GraphSampler(m, b, use_graph=False, cache_conditioning=False), sampling.GraphSampler(m, b, use_graph=False, cache_conditioning=True)
-    for gs in (ga, gb):
+    rec = [[img[i, 0][None].repeat(b, 1, 1, 1).numpy(), R[i, 0].numpy(), T[i, 0].numpy()] for i in range(2)]
+    rel = lambda a, c: float((a - c).norm() / c.norm())
+    ga, gb = sampling.GraphSampler(m, b, cache_conditioning=False), sampling.GraphSampler(m, b, cache_conditioning=True)
+
+    def one_step(gs, entry, view, seed, lam=-0.5):
         gs.w.copy_(w.to(dev))
-        gs.set_views(rec0[0][0], rec0[0][1], rec0[0][2], R[2, 0], T[2, 0], K[0], cond_key="a", target_key="t")
-        torch.manual_seed(3)
+        gs.set_views(rec[entry][0], rec[entry][1], rec[entry][2], R[2, view], T[2, view], K[0], cond_key=entry, target_key=view)
+        torch.manual_seed(seed)
         gs.z.normal_()
-        gs.step(torch.tensor(-0.5), torch.tensor(-0.4))
-    assert rel(ga.z.cpu().numpy(), gb.z.cpu().numpy()) <= 2e-3
+        gs.step(torch.tensor(lam), torch.tensor(lam + 0.1))
+        return gs.z.clone()
+
+    # eager step, captured step, cache misses and hits, both conditioning entries, both target views
+    for i, (entry, view) in enumerate([(0, 0), (1, 0), (0, 0), (1, 1), (0, 1), (1, 1)]):
+        za, zb = one_step(ga, entry, view, 100 + i), one_step(gb, entry, view, 100 + i)
+        assert rel(zb, za) <= 3e-3, (i, rel(zb, za))
+    assert len(gb._entries) == 2 and all(e["c"] is not None for e in gb._entries.values())
+    before = one_step(gb, 0, 0, 7)
+    # parameters change: the next step must use them (not the stale packed operands / cached conditioning)
+    with torch.no_grad():
+        m.flat_parameters().mul_(1.02)
+    m._param_version += 1
+    after = one_step(gb, 0, 0, 7)
+    fresh = one_step(sampling.GraphSampler(m, b, cache_conditioning=True), 0, 0, 7)
+    assert rel(after, fresh) <= 3e-3, rel(after, fresh)
+    assert rel(after, before) > 10 * rel(after, fresh) + 1e-3
+    # and the public loop runs on the cached sampler over a growing record
+    random.seed(5)
+    out = gb.sample(rec[:1], R[2, 0], T[2, 0], K[0], w, timesteps=4)
+    assert out.shape == (b, 3, 32, 32) and bool((out == out).all())

@@ -245,12 +245,12 @@ def test_cached_conditioning_matches_uncached_and_follows_parameter_updates():
     before = one_step(gb, 0, 0, 7)
     # parameters change: the next step must use them (not the stale packed operands / cached conditioning)
     with torch.no_grad():
-        m.flat_parameters().mul_(1.02)
+        m.flat_parameters().mul_(1.3)
     m._param_version += 1
     after = one_step(gb, 0, 0, 7)
     fresh = one_step(sampling.GraphSampler(m, b, cache_conditioning=True), 0, 0, 7)
     assert rel(after, fresh) <= 3e-3, rel(after, fresh)
-    assert rel(after, before) > 10 * rel(after, fresh) + 1e-3
+    assert rel(after, before) > 5 * rel(after, fresh) + 1e-3, (rel(after, before), rel(after, fresh))
     # and the public loop runs on the cached sampler over a growing record
     random.seed(5)
     out = gb.sample(rec[:1], R[2, 0], T[2, 0], K[0], w, timesteps=4)

@@ -40,3 +40,8 @@ def set_pdl(on):
 def set_gn_chunk_mb(mb):
     """per-chunk budget of the image-chunked GroupNorm launches (include/b3d.h: b3d_set_gn_chunk_mb); 0 = off"""
     load().b3d_set_gn_chunk_mb(ctypes.c_int(int(mb)))
+
+
+def set_gn_fuse_mb(mb):
+    """largest input (MB) for which GroupNorm runs as one cluster-fused launch (include/b3d.h: b3d_set_gn_fuse_mb); 0 = never"""
+    load().b3d_set_gn_fuse_mb(ctypes.c_int(int(mb)))

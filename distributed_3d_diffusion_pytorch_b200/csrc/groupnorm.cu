@@ -4,6 +4,8 @@
 // Replaces nn.GroupNorm / F.silu / FiLM apply / Dropout: xunet.py:61-71,87,140,143-145,198,535.
 // HBM-bound: every pass is 16-byte vectorised over channels and reads each tensor once.
 #include "../../include/b3d.h"
+#include <cooperative_groups.h>
+
 #include "b3d_common.cuh"
 
 void b3d_count_launch(int n);
@@ -74,13 +76,15 @@ __device__ __forceinline__ void block_sum8(const float* vals, bool active, int v
 }
 
 // ---- stats: raw (sum, sumsq) per (image, group) accumulated with fp32 atomics into ws[N,32,2] (pre-zeroed)
-__global__ void __launch_bounds__(kT) gn_stats_kernel(Src2 s, int HW, int rows_per_block, float* __restrict__ ws, int n0) {
-  b3d_pdl_sync();
-  extern __shared__ float sm[];  // red [256*8] | sum [C] | sumsq [C]
+// (s_part != nullptr: the block's partial (sum, sumsq) of group g go to s_part[2g], s_part[2g+1] in shared memory instead -- the
+// cluster-fused kernels below combine them across the blocks of an image)
+__device__ __forceinline__ void stats_body(const Src2& s, int HW, int rows_per_block, int n, int bx, float* sm, float* __restrict__ ws,
+                                           float* s_part) {
+  // sm: red [256*8] | sum [C] | sumsq [C]
   constexpr int U = 4;
-  const int C = s.C0 + s.C1, cpg = C / G, n = blockIdx.y + n0, vecs = C / 8;
+  const int C = s.C0 + s.C1, cpg = C / G, vecs = C / 8;
   float* red = sm; float* r_a = sm + 2048; float* r_b = r_a + C;
-  const int r0 = blockIdx.x * rows_per_block, r1 = min(HW, r0 + rows_per_block);
+  const int r0 = bx * rows_per_block, r1 = min(HW, r0 + rows_per_block);
   const int rows_par = max(1, (int)blockDim.x / vecs);
   const int v = threadIdx.x % vecs, rsub = threadIdx.x / vecs;
   const bool active = rsub < rows_par;
@@ -107,9 +111,17 @@ __global__ void __launch_bounds__(kT) gn_stats_kernel(Src2 s, int HW, int rows_p
   for (int g = threadIdx.x; g < G; g += blockDim.x) {
     float sa = 0.f, sb = 0.f;
     for (int c = g * cpg; c < (g + 1) * cpg; ++c) { sa += r_a[c]; sb += r_b[c]; }
-    atomicAdd(&ws[((long long)n * G + g) * 2], sa);
-    atomicAdd(&ws[((long long)n * G + g) * 2 + 1], sb);
+    if (s_part != nullptr) { s_part[2 * g] = sa; s_part[2 * g + 1] = sb; }
+    else {
+      atomicAdd(&ws[((long long)n * G + g) * 2], sa);
+      atomicAdd(&ws[((long long)n * G + g) * 2 + 1], sb);
+    }
   }
+}
+__global__ void __launch_bounds__(kT) gn_stats_kernel(Src2 s, int HW, int rows_per_block, float* __restrict__ ws, int n0) {
+  b3d_pdl_sync();
+  extern __shared__ float sm[];
+  stats_body(s, HW, rows_per_block, blockIdx.y + n0, blockIdx.x, sm, ws, nullptr);
 }
 
 // ---- dropout keep-mask of one 8-channel vector: b3d_drop_pair (b3d_common.cuh) hashes (seed, pair index) to 32 bits,
@@ -163,14 +175,10 @@ constexpr int kBwdBlocks1 = B3D_GN_BWD1_BLOCKS;
 constexpr int kBwdBlocks2 = B3D_GN_BWD2_BLOCKS;   // resident blocks per SM of the film-mode backward kernels
 
 template <int MODE>
-__global__ void __launch_bounds__(kT, MODE == 2 ? 3 : 4) gn_apply_kernel(ApplyP p, int rows_per_block) {
-  b3d_pdl_sync();
-  __shared__ float s_mean[G], s_rstd[G];
+__device__ __forceinline__ void apply_body(const ApplyP& p, int rows_per_block, int n, int bx, const float* s_mean, const float* s_rstd) {
   constexpr int U = MODE == 2 ? kApplyU2 : kApplyU0;
-  const int C = p.s.C0 + p.s.C1, cpg = C / G, n = blockIdx.y + p.n0, vecs = C / 8;
-  block_stats(p.stats, n, cpg, p.HW, s_mean, s_rstd);
-  __syncthreads();
-  const int r0 = blockIdx.x * rows_per_block, r1 = min(p.HW, r0 + rows_per_block);
+  const int C = p.s.C0 + p.s.C1, cpg = C / G, vecs = C / 8;
+  const int r0 = bx * rows_per_block, r1 = min(p.HW, r0 + rows_per_block);
   const int rows_par = max(1, (int)blockDim.x / vecs);
   const int v = threadIdx.x % vecs, rsub = threadIdx.x / vecs, c0 = v * 8;
   if (rsub >= rows_par) return;
@@ -217,6 +225,16 @@ __global__ void __launch_bounds__(kT, MODE == 2 ? 3 : 4) gn_apply_kernel(ApplyP 
     }
   }
 }
+template <int MODE>
+__global__ void __launch_bounds__(kT, MODE == 2 ? 3 : 4) gn_apply_kernel(ApplyP p, int rows_per_block) {
+  b3d_pdl_sync();
+  __shared__ float s_mean[G], s_rstd[G];
+  const int C = p.s.C0 + p.s.C1, n = blockIdx.y + p.n0;
+  block_stats(p.stats, n, C / G, p.HW, s_mean, s_rstd);
+  __syncthreads();
+  apply_body<MODE>(p, rows_per_block, n, blockIdx.x, s_mean, s_rstd);
+}
+
 
 struct BwdP {
   Src2 s;
@@ -259,18 +277,17 @@ __device__ __forceinline__ void bwd_dz(const Aff& ch, const float* f, const floa
 // pass 1: d_scale/d_shift (film), dgamma/dbeta, per-(image,group) S1 = sum dz*gamma, S2 = sum dz*gamma*xhat.
 // The loop accumulates sum dz*x and sum dz per channel; xhat = (x - mean)*rstd is applied to the block's partial sums
 // (one image per block, so mean/rstd are block constants per group).
+// (s_part != nullptr: the block's partial S1, S2 of group g go to s_part[2g], s_part[2g+1] in shared memory instead of the
+// global workspace -- see the cluster-fused kernels)
 template <int MODE>
-__global__ void __launch_bounds__(kT, MODE == 2 ? kBwdBlocks2 : kBwdBlocks1) gn_bwd_reduce_kernel(BwdP p, int rows_per_block) {
-  b3d_pdl_sync();
-  extern __shared__ float sm[];  // red [256*8] | dgamma [C] | dbeta [C] | dscale-sum [C] | dshift-sum [C]
-  __shared__ float s_mean[G], s_rstd[G];
+__device__ __forceinline__ void bwd_reduce_body(const BwdP& p, int rows_per_block, int n, int bx, float* sm, const float* s_mean,
+                                                const float* s_rstd, float* s_part) {
+  // sm: red [256*8] | dgamma [C] | dbeta [C] | dscale-sum [C] | dshift-sum [C]
   constexpr int U = MODE == 2 ? kBwdU2 : kBwdU1;
-  const int C = p.s.C0 + p.s.C1, cpg = C / G, n = blockIdx.y + p.n0, vecs = C / 8;
+  const int C = p.s.C0 + p.s.C1, cpg = C / G, vecs = C / 8;
   float* red = sm; float* r_g = sm + 2048; float* r_b = r_g + C; float* r_sc = r_b + C; float* r_sh = r_sc + C;
   const bool want_ss = MODE == 2 && p.dss_sum != nullptr;
-  block_stats(p.stats, n, cpg, p.HW, s_mean, s_rstd);
-  __syncthreads();
-  const int r0 = blockIdx.x * rows_per_block, r1 = min(p.HW, r0 + rows_per_block);
+  const int r0 = bx * rows_per_block, r1 = min(p.HW, r0 + rows_per_block);
   const int rows_par = max(1, (int)blockDim.x / vecs);
   const int v = threadIdx.x % vecs, rsub = threadIdx.x / vecs, c0 = v * 8;
   const bool active = rsub < rows_par;
@@ -334,30 +351,41 @@ __global__ void __launch_bounds__(kT, MODE == 2 ? kBwdBlocks2 : kBwdBlocks1) gn_
   if (threadIdx.x < G) {
     float s1 = 0.f, s2 = 0.f;
     for (int c = threadIdx.x * cpg; c < (threadIdx.x + 1) * cpg; ++c) { const float gam = p.gamma[c]; s1 += r_b[c] * gam; s2 += r_g[c] * gam; }
-    atomicAdd(&p.ws[((long long)n * G + threadIdx.x) * 2], s1);
-    atomicAdd(&p.ws[((long long)n * G + threadIdx.x) * 2 + 1], s2);
+    if (s_part != nullptr) { s_part[2 * threadIdx.x] = s1; s_part[2 * threadIdx.x + 1] = s2; }
+    else {
+      atomicAdd(&p.ws[((long long)n * G + threadIdx.x) * 2], s1);
+      atomicAdd(&p.ws[((long long)n * G + threadIdx.x) * 2 + 1], s2);
+    }
   }
+}
+template <int MODE>
+__global__ void __launch_bounds__(kT, MODE == 2 ? kBwdBlocks2 : kBwdBlocks1) gn_bwd_reduce_kernel(BwdP p, int rows_per_block) {
+  b3d_pdl_sync();
+  extern __shared__ float sm[];
+  __shared__ float s_mean[G], s_rstd[G];
+  const int C = p.s.C0 + p.s.C1, n = blockIdx.y + p.n0;
+  block_stats(p.stats, n, C / G, p.HW, s_mean, s_rstd);
+  __syncthreads();
+  bwd_reduce_body<MODE>(p, rows_per_block, n, blockIdx.x, sm, s_mean, s_rstd, nullptr);
 }
 
 // pass 2: dx = rstd * (dz*gamma - (S1 + xhat*S2)/cnt) [+ add0] [+ add1]  =  dz*a + x*c1 + c0 per channel
+// group constants of pass 2 from the group totals S1, S2 (thread g < 32 handles group g; it wrote s_mean / s_rstd[g] itself)
+__device__ __forceinline__ void bwd_group_consts(float S1, float S2, int cpg, int HW, const float* s_mean, const float* s_rstd, float* s_c1,
+                                                 float* s_c0) {
+  const float cnt = (float)cpg * (float)HW;
+  const float s1 = S1 / cnt, s2 = S2 / cnt;
+  const float rstd = s_rstd[threadIdx.x], c1 = -rstd * rstd * s2;
+  s_c1[threadIdx.x] = c1;
+  s_c0[threadIdx.x] = -rstd * s1 - c1 * s_mean[threadIdx.x];
+}
 template <int MODE>
-__global__ void __launch_bounds__(kT, MODE == 2 ? kBwdBlocks2 : kBwdBlocks1) gn_bwd_apply_kernel(BwdP p, int rows_per_block) {
-  b3d_pdl_sync();
-  extern __shared__ float sm[];   // red [256*8] | column sums of dx [C]   (used when p.dx_sum is set)
-  __shared__ float s_mean[G], s_rstd[G], s_c1[G], s_c0[G];
+__device__ __forceinline__ void bwd_apply_body(const BwdP& p, int rows_per_block, int n, int bx, float* sm, const float* s_mean,
+                                               const float* s_rstd, const float* s_c1, const float* s_c0) {
+  // sm: red [256*8] | column sums of dx [C]   (used when p.dx_sum is set)
   constexpr int U = kBwdApplyU;
-  const int C = p.s.C0 + p.s.C1, cpg = C / G, n = blockIdx.y + p.n0, vecs = C / 8;
-  block_stats(p.stats, n, cpg, p.HW, s_mean, s_rstd);
-  if (threadIdx.x < G) {
-    // same thread wrote s_mean/s_rstd[threadIdx.x] above
-    const float cnt = (float)cpg * (float)p.HW;
-    const float s1 = p.ws[((long long)n * G + threadIdx.x) * 2] / cnt, s2 = p.ws[((long long)n * G + threadIdx.x) * 2 + 1] / cnt;
-    const float rstd = s_rstd[threadIdx.x], c1 = -rstd * rstd * s2;
-    s_c1[threadIdx.x] = c1;
-    s_c0[threadIdx.x] = -rstd * s1 - c1 * s_mean[threadIdx.x];
-  }
-  __syncthreads();
-  const int r0 = blockIdx.x * rows_per_block, r1 = min(p.HW, r0 + rows_per_block);
+  const int C = p.s.C0 + p.s.C1, cpg = C / G, vecs = C / 8;
+  const int r0 = bx * rows_per_block, r1 = min(p.HW, r0 + rows_per_block);
   const int rows_par = max(1, (int)blockDim.x / vecs);
   const int v = threadIdx.x % vecs, rsub = threadIdx.x / vecs, c0 = v * 8;
   const bool active = rsub < rows_par;
@@ -419,6 +447,73 @@ __global__ void __launch_bounds__(kT, MODE == 2 ? kBwdBlocks2 : kBwdBlocks1) gn_
     for (int c = threadIdx.x; c < C; c += blockDim.x) atomicAdd(&p.dx_sum[c], sm[2048 + c]);
   }
 }
+template <int MODE>
+__global__ void __launch_bounds__(kT, MODE == 2 ? kBwdBlocks2 : kBwdBlocks1) gn_bwd_apply_kernel(BwdP p, int rows_per_block) {
+  b3d_pdl_sync();
+  extern __shared__ float sm[];
+  __shared__ float s_mean[G], s_rstd[G], s_c1[G], s_c0[G];
+  const int C = p.s.C0 + p.s.C1, cpg = C / G, n = blockIdx.y + p.n0;
+  block_stats(p.stats, n, cpg, p.HW, s_mean, s_rstd);
+  if (threadIdx.x < G)
+    bwd_group_consts(p.ws[((long long)n * G + threadIdx.x) * 2], p.ws[((long long)n * G + threadIdx.x) * 2 + 1], cpg, p.HW, s_mean, s_rstd, s_c1,
+                     s_c0);
+  __syncthreads();
+  bwd_apply_body<MODE>(p, rows_per_block, n, blockIdx.x, sm, s_mean, s_rstd, s_c1, s_c0);
+}
+
+// ---- Cluster-fused variants for tensors that stay in L2 between the passes (small per-GPU batches, the sampler): ONE launch
+// per GroupNorm instead of two.  The blocks of an image form a thread-block cluster; each block runs pass 1 over its rows,
+// the per-group partial sums meet through distributed shared memory (no global atomics, no workspace round trip), and after
+// the cluster barrier each block runs pass 2 over the same rows, which it re-reads from L2.  At 16 pairs per GPU the model's
+// 404 GroupNorm launches per step sit on the serial data-dependency chain; this halves them.
+__device__ __forceinline__ void cluster_totals(const float* s_part, float* s_tot) {
+  namespace cg = cooperative_groups;
+  cg::cluster_group cl = cg::this_cluster();
+  cl.sync();                                             // every block's partials are in its shared memory
+  if (threadIdx.x < 2 * G) {
+    float t = 0.f;
+    const unsigned nb = cl.num_blocks();
+    for (unsigned r = 0; r < nb; ++r) t += cl.map_shared_rank(s_part, r)[threadIdx.x];
+    s_tot[threadIdx.x] = t;
+  }
+  cl.sync();                                             // nobody reads a peer's shared memory after this point
+}
+template <int MODE>
+__global__ void __launch_bounds__(kT, MODE == 2 ? 3 : 4) gn_fwd_fused_kernel(ApplyP p, float* __restrict__ ws, int rows_per_block) {
+  b3d_pdl_sync();
+  extern __shared__ float sm[];
+  __shared__ float s_part[2 * G], s_tot[2 * G], s_mean[G], s_rstd[G];
+  const int C = p.s.C0 + p.s.C1, cpg = C / G, n = blockIdx.y + p.n0;
+  stats_body(p.s, p.HW, rows_per_block, n, blockIdx.x, sm, nullptr, s_part);
+  cluster_totals(s_part, s_tot);
+  if (threadIdx.x < G) {
+    const float cnt = (float)cpg * (float)p.HW;
+    const float sum = s_tot[2 * threadIdx.x], sq = s_tot[2 * threadIdx.x + 1];
+    const float mean = sum / cnt;
+    s_mean[threadIdx.x] = mean;
+    s_rstd[threadIdx.x] = rsqrtf(fmaxf(sq / cnt - mean * mean, 0.f) + 1e-5f);
+    if (blockIdx.x == 0) {                               // the raw sums stay available to the backward pass
+      ws[((long long)n * G + threadIdx.x) * 2] = sum;
+      ws[((long long)n * G + threadIdx.x) * 2 + 1] = sq;
+    }
+  }
+  __syncthreads();
+  apply_body<MODE>(p, rows_per_block, n, blockIdx.x, s_mean, s_rstd);
+}
+template <int MODE>
+__global__ void __launch_bounds__(kT, MODE == 2 ? kBwdBlocks2 : kBwdBlocks1) gn_bwd_fused_kernel(BwdP p, int rows_per_block) {
+  b3d_pdl_sync();
+  extern __shared__ float sm[];
+  __shared__ float s_part[2 * G], s_tot[2 * G], s_mean[G], s_rstd[G], s_c1[G], s_c0[G];
+  const int C = p.s.C0 + p.s.C1, cpg = C / G, n = blockIdx.y + p.n0;
+  block_stats(p.stats, n, cpg, p.HW, s_mean, s_rstd);
+  __syncthreads();
+  bwd_reduce_body<MODE>(p, rows_per_block, n, blockIdx.x, sm, s_mean, s_rstd, s_part);
+  cluster_totals(s_part, s_tot);
+  if (threadIdx.x < G) bwd_group_consts(s_tot[2 * threadIdx.x], s_tot[2 * threadIdx.x + 1], cpg, p.HW, s_mean, s_rstd, s_c1, s_c0);
+  __syncthreads();
+  bwd_apply_body<MODE>(p, rows_per_block, n, blockIdx.x, sm, s_mean, s_rstd, s_c1, s_c0);
+}
 
 // rows of one image per block: about `waves` full waves of `blocks_per_sm` resident blocks per SM over the whole launch
 // (many short waves keep the last, partial one cheap), but never fewer rows than one unrolled sweep of the block
@@ -461,6 +556,26 @@ int gn_chunk_images(int N, int HW, int C, int bytes_per_elem) {
   return (int)(c < N ? c : N);
 }
 
+// Cluster-fused single-launch GroupNorm (gn_fwd_fused_kernel / gn_bwd_fused_kernel): used when the input tensor is small enough
+// to still be in L2 for the second pass.  Returns the cluster size (blocks per image, 1..8) or 0 for the two-launch path.
+long long g_gn_fuse_bytes = -1;
+int gn_fuse_cluster(int N, int HW, int C, int U, int* rows_per_block) {
+  if (g_gn_fuse_bytes < 0) {
+    const char* e = getenv("B3D_GN_FUSE_MB");
+    g_gn_fuse_bytes = (e ? atoll(e) : 40) * (1LL << 20);
+  }
+  if ((long long)N * HW * C * 2 > g_gn_fuse_bytes) return 0;
+  const int vecs = C / 8;
+  const int rows_par = 256 / vecs > 0 ? 256 / vecs : 1;
+  const int min_rows = rows_par * U;
+  int cl = 8;
+  while (cl > 1 && (HW + cl - 1) / cl < min_rows) cl >>= 1;          // every block keeps at least one unrolled sweep of rows
+  int rpb = (HW + cl - 1) / cl;
+  rpb = (rpb + rows_par - 1) / rows_par * rows_par;
+  *rows_per_block = rpb;
+  return cl;
+}
+
 int check_src(const void* x0, int C0, const void* x1, int C1) {
   const int C = C0 + C1;
   B3D_CHECK_ARG(x0 != nullptr && C0 > 0, "groupnorm: null input");
@@ -473,6 +588,7 @@ int check_src(const void* x0, int C0, const void* x1, int C1) {
 }  // namespace
 
 extern "C" void b3d_set_gn_chunk_mb(int mb) { g_gn_chunk_bytes = (long long)mb * (1LL << 20); }
+extern "C" void b3d_set_gn_fuse_mb(int mb) { g_gn_fuse_bytes = (long long)mb * (1LL << 20); }
 
 extern "C" int b3d_gn_stats(const void* x0, int C0, int64_t ld0, const void* x1, int C1, int64_t ld1, int N, int HW, float* ws_sums,
                             void* stream) {
@@ -502,6 +618,22 @@ static int gn_apply_impl(const void* x0, int C0, int64_t ld0, const void* x1, in
   // with_stats: statistics pass and apply pass of the same images back to back, chunk by chunk (the apply pass then reads
   // the chunk from L2); without: one apply launch over all images
   const int C = C0 + C1;
+  if (with_stats) {
+    int rpb = 0;
+    const int cl = gn_fuse_cluster(N, HW, C, mode == 2 ? kApplyU2 : 4, &rpb);
+    if (cl > 0) {
+      p.n0 = 0;
+      dim3 grid(cl, N);
+      const size_t smem = (2048 + 2 * C) * sizeof(float);
+      cudaStream_t st = (cudaStream_t)stream;
+      if (mode == 0) B3D_CUDA(b3d_launch_cluster_pdl(gn_fwd_fused_kernel<0>, dim3(grid), dim3(kT), smem, st, cl, p, ws_sums, rpb));
+      else if (mode == 1) B3D_CUDA(b3d_launch_cluster_pdl(gn_fwd_fused_kernel<1>, dim3(grid), dim3(kT), smem, st, cl, p, ws_sums, rpb));
+      else B3D_CUDA(b3d_launch_cluster_pdl(gn_fwd_fused_kernel<2>, dim3(grid), dim3(kT), smem, st, cl, p, ws_sums, rpb));
+      B3D_LAUNCH_CHECK();
+      b3d_count_launch(1);
+      return B3D_OK;
+    }
+  }
   const int chunk = with_stats ? gn_chunk_images(N, HW, C, 2) : N;
   int launches = 0;
   for (int n0 = 0; n0 < N; n0 += chunk) {
@@ -560,6 +692,21 @@ extern "C" int b3d_gn_bwd(const void* x0, int C0, int64_t ld0, const void* x1, i
   p.add1a = (const bf16*)add1a; p.add1b = (const bf16*)add1b; p.ld_add1a = ld_add1a; p.ld_add1b = ld_add1b;
   const int C = C0 + C1;
   cudaStream_t st = (cudaStream_t)stream;
+  {
+    int rpb = 0;
+    const int cl = gn_fuse_cluster(N, HW, C, mode == 2 ? kBwdU2 : kBwdU1, &rpb);
+    if (cl > 0) {
+      p.n0 = 0;
+      dim3 grid(cl, N);
+      const size_t smem = (2048 + 4 * C) * sizeof(float);
+      if (mode == 0) B3D_CUDA(b3d_launch_cluster_pdl(gn_bwd_fused_kernel<0>, dim3(grid), dim3(kT), smem, st, cl, p, rpb));
+      else if (mode == 1) B3D_CUDA(b3d_launch_cluster_pdl(gn_bwd_fused_kernel<1>, dim3(grid), dim3(kT), smem, st, cl, p, rpb));
+      else B3D_CUDA(b3d_launch_cluster_pdl(gn_bwd_fused_kernel<2>, dim3(grid), dim3(kT), smem, st, cl, p, rpb));
+      B3D_LAUNCH_CHECK();
+      b3d_count_launch(1);
+      return B3D_OK;
+    }
+  }
   // bytes both passes read per element: x, dy (+ the FiLM scale)
   const int chunk = gn_chunk_images(N, HW, C, mode == 2 ? 6 : 4);
   int launches = 0;

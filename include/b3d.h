@@ -191,6 +191,11 @@ int b3d_gn_stats_apply(const void* x0, int C0, int64_t ld0, const void* x1, int 
 /* budget (MB) for the tensors both passes of a GroupNorm read per image chunk; 0 = no chunking.  Default: the
  * environment's B3D_GN_CHUNK_MB, else 0.  A tuning knob of this library, no reference counterpart. */
 void b3d_set_gn_chunk_mb(int mb);
+/* b3d_gn_stats_apply and b3d_gn_bwd run as ONE cluster-fused launch (the blocks of an image exchange their partial sums through
+ * distributed shared memory; the second pass re-reads the image from L2) when the input tensor is at most this many MB --
+ * small per-GPU batches and the sampler, where the launches, not the bytes, are what costs.  Default 40 (B3D_GN_FUSE_MB in the
+ * environment overrides); 0 = always two launches.  No reference counterpart. */
+void b3d_set_gn_fuse_mb(int mb);
 int b3d_gn_bwd(const void* x0, int C0, int64_t ld0, const void* x1, int C1, int64_t ld1, int N, int HW, const float* sums,
                const float* gamma, const float* beta, int mode, const void* dy, int64_t ld_dy, const void* ss, int64_t ld_ss, int F,
                void* dss, int64_t ld_dss, float drop_p, uint64_t seed, const uint64_t* seed_ptr, float* dgamma, float* dbeta, float* dss_sum,

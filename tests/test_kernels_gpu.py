@@ -67,6 +67,7 @@ def test_gn_image_chunked_launches_equal_unchunked():
     ss = mk(N * HW, 2 * C) * 0.5
     gamma, beta = 1 + 0.1 * mk(C, dt=torch.float32), 0.1 * mk(C, dt=torch.float32)
     res = {}
+    _lib.set_gn_fuse_mb(0)    # (small tensors would otherwise take the cluster-fused single launch)
     for mb in (0, 1):         # 1 MB budget -> two images (1 MB of x) per chunk
         _lib.set_gn_chunk_mb(mb)
         try:
@@ -85,6 +86,7 @@ def test_gn_image_chunked_launches_equal_unchunked():
                 res[(mb, mode)] = (launches, sums, out, dx, dss, ws, dgamma, dbeta)
         finally:
             _lib.set_gn_chunk_mb(0)
+    _lib.set_gn_fuse_mb(40)
     for mode in (1, 2):
         a, b = res[(0, mode)], res[(1, mode)]
         assert a[0] == 2 and b[0] > 2                       # really chunked
@@ -94,3 +96,51 @@ def test_gn_image_chunked_launches_equal_unchunked():
         for i in (2, 3, 4):
             if a[i] is not None:
                 assert _cmp(b[i], a[i]) <= 1e-3, (mode, i)
+
+
+@pytest.mark.parametrize("N,HW,C0,C1", [(4, 4096, 128, 0), (6, 1024, 256, 128), (3, 64, 512, 512), (2, 36, 64, 32), (5, 16, 32, 0)])
+def test_gn_cluster_fused_launch_equals_two_launches(N, HW, C0, C1):
+    """small tensors: b3d_gn_stats_apply / b3d_gn_bwd as ONE launch (thread-block cluster per image, partial sums exchanged
+    through distributed shared memory) against the two-launch path, all modes, with and without a second source"""
+    from distributed_3d_diffusion_pytorch_b200 import _lib
+    from distributed_3d_diffusion_pytorch_b200.ops import CudaOps
+    ops, dev = CudaOps("cuda:0"), "cuda:0"
+    g = torch.Generator().manual_seed(N * HW + C0)
+    C = C0 + C1
+    mk = lambda *shape, dt=torch.bfloat16: torch.randn(*shape, generator=g).to(dev, dt)
+    x0, x1 = mk(N, HW, C0) + 0.3, (mk(N, HW, C1) * 2 - 0.5 if C1 else None)
+    dy, add0, add1a = mk(N, HW, C), mk(N, HW, C), mk(N, HW, C0)
+    ss = mk(N * HW, 2 * C) * 0.5
+    gamma, beta = 1 + 0.1 * mk(C, dt=torch.float32), 0.1 * mk(C, dt=torch.float32)
+    res = {}
+    try:
+        for fuse in (0, 40):
+            _lib.set_gn_fuse_mb(fuse)
+            for mode in (0, 1, 2):
+                film = dict(ss=ss, F=C, drop_p=0.1, seed=5) if mode == 2 else {}
+                sums = torch.zeros(N, 32, 2, device=dev)
+                out = torch.zeros(N, HW, C, device=dev, dtype=torch.bfloat16)
+                n0 = _lib.launch_count()
+                ops.gn_stats_apply(x0, x1, sums, gamma, beta, mode, out, **film)
+                l_fwd = _lib.launch_count() - n0
+                dgamma, dbeta, ws = torch.zeros(C, device=dev), torch.zeros(C, device=dev), torch.zeros(N, 32, 2, device=dev)
+                dx0 = torch.zeros(N, HW, C0, device=dev, dtype=torch.bfloat16)
+                dx1 = torch.zeros(N, HW, C1, device=dev, dtype=torch.bfloat16) if C1 else None
+                dss = torch.zeros_like(ss) if mode == 2 else None
+                dss_sum = torch.zeros(2 * C, device=dev) if mode == 2 else None
+                dx_sum = torch.zeros(C, device=dev)
+                n0 = _lib.launch_count()
+                ops.gn_bwd(x0, x1, sums, gamma, beta, mode, dy, dgamma, dbeta, ws, dx0, dx1, dss=dss, add0=add0, add1a=add1a, add0_scale=0.5,
+                           dss_sum=dss_sum, dx_sum=dx_sum, **film)
+                l_bwd = _lib.launch_count() - n0
+                torch.cuda.synchronize()
+                res[(fuse, mode)] = (l_fwd, l_bwd, [sums, out, dx0, dx1, dss, dgamma, dbeta, dss_sum, dx_sum])
+    finally:
+        _lib.set_gn_fuse_mb(40)
+    for mode in (0, 1, 2):
+        (lf0, lb0, a), (lf1, lb1, b) = res[(0, mode)], res[(40, mode)]
+        assert (lf0, lb0) == (2, 2) and (lf1, lb1) == (1, 1)
+        for i, (u, v) in enumerate(zip(a, b)):
+            if u is not None:
+                tol = 2e-3 if u.dtype == torch.bfloat16 else 2e-4        # same arithmetic, partial sums combined in another order
+                assert _cmp(v, u) <= tol, (mode, i, _cmp(v, u))

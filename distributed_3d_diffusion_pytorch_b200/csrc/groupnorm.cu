@@ -510,7 +510,13 @@ __global__ void __launch_bounds__(kT, MODE == 2 ? kBwdBlocks2 : kBwdBlocks1) gn_
   __syncthreads();
   bwd_reduce_body<MODE>(p, rows_per_block, n, blockIdx.x, sm, s_mean, s_rstd, s_part);
   cluster_totals(s_part, s_tot);
-  if (threadIdx.x < G) bwd_group_consts(s_tot[2 * threadIdx.x], s_tot[2 * threadIdx.x + 1], cpg, p.HW, s_mean, s_rstd, s_c1, s_c0);
+  if (threadIdx.x < G) {
+    bwd_group_consts(s_tot[2 * threadIdx.x], s_tot[2 * threadIdx.x + 1], cpg, p.HW, s_mean, s_rstd, s_c1, s_c0);
+    if (blockIdx.x == 0 && p.ws != nullptr) {            // the workspace ends up holding (S1, S2) like after the two-launch path
+      p.ws[((long long)n * G + threadIdx.x) * 2] = s_tot[2 * threadIdx.x];
+      p.ws[((long long)n * G + threadIdx.x) * 2 + 1] = s_tot[2 * threadIdx.x + 1];
+    }
+  }
   __syncthreads();
   bwd_apply_body<MODE>(p, rows_per_block, n, blockIdx.x, sm, s_mean, s_rstd, s_c1, s_c0);
 }

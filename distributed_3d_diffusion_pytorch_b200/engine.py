@@ -567,6 +567,7 @@ class Engine:
         h.has_grad = True
 
         self._bwd_blocks(Gr, lambda name: name.startswith("upsample."))
+        self._film_wgrad(Gr, lambda name: name.startswith("upsample."))
 
     def _bwd_blocks(self, Gr, select):
         sv = self.saved
@@ -581,6 +582,30 @@ class Engine:
 
     def _bwd_phase1(self, Gr, deps, grad_flat):
         self._bwd_blocks(Gr, lambda name: not name.startswith("upsample."))
+        self._film_wgrad(Gr, lambda name: not name.startswith("upsample."))
+
+    def _film_wgrad(self, Gr, select):
+        """Weight gradients of FiLM's Linear(1024 -> 2F) (xunet.py:80,84) of all the selected blocks of a level as ONE GEMM
+        dss[:, cols]^T silu(emb): the level's silu(emb) -- 2 GB at 64x64 for batch 128 -- is read once per (level, phase)
+        instead of once per block (the per-block GEMMs were HBM-bound on exactly that operand).  The blocks of a phase own a
+        contiguous column range of the level-wide dss (plan order: down path, then up path); the rows of the result are
+        copied to the per-block parameter gradients by the phase's copy job list."""
+        ops, N = self.ops, self.N
+        for l in range(self.cfg.num_resolutions):
+            specs = [s for kind, s in self.plan if kind == "res" and s.lvl == l and select(s.name)]
+            if not specs:
+                continue
+            c0, c1 = min(s.film_off for s in specs), max(s.film_off + 2 * s.f for s in specs)
+            assert sum(2 * s.f for s in specs) == c1 - c0, "FiLM columns of a phase are not contiguous"
+            hh, ww = self.lvl_hw(l)
+            M = N * hh * ww
+            sil = self._bufs[f"emb_silu{l}"].view(M, 1024)
+            gp = self.zbuf("bwd", f"gp.film{l}.{self._cur_phase}", (c1 - c0, 1024))
+            with ops.side():
+                ops.gemm(G.wgrad_dense_desc(self._dss[l][:, c0:c1], sil, gp))
+            if self._unpack_rec:
+                for s in specs:
+                    ops.record_copy(self._copy_jl[self._cur_phase], gp[s.film_off - c0:s.film_off - c0 + 2 * s.f], Gr[s.name + ".film.dense.weight"])
 
     def _bwd_phase2(self, Gr, deps, grad_flat):
         ops, cfg, B, N = self.ops, self.cfg, self.B, self.N
@@ -725,10 +750,8 @@ class Engine:
                    da1.view(N, HW, F), Gr[n + ".groupnorm1.gn.weight"], Gr[n + ".groupnorm1.gn.bias"],
                    self.zbuf("bwd", n + ".ws1", (N, 32, 2)), dc1.view(N, HW, F), ss=ssv, F=F, dss=dssv, drop_p=drop_p, seed=sa["seed"],
                    seed_ptr=self.seed_ptr, dss_sum=Gr[n + ".film.dense.bias"], dx_sum=Gr[n + ".conv1.bias"])
-        # FiLM dense parameters (xunet.py:80,84): per block, straight into the parameter gradients
-        sil = self._bufs[f"emb_silu{s.lvl}"].view(M, 1024)
+        # (the FiLM dense weight gradients, xunet.py:80,84, are taken per level and phase in _film_wgrad)
         with ops.side():
-            ops.gemm(G.wgrad_dense_desc(dssv, sil, Gr[n + ".film.dense.weight"]))
             # conv1 (its bias gradient and the FiLM bias gradient were reduced inside the GroupNorm backward above)
             self._conv_wgrad(n + ".conv1.weight", dc1, sa["a0"].view(N, hh, ww, s.cin), Gr[n + ".conv1.weight"])
         da0 = self.tmp("da0", (N, hh, ww, s.cin))

@@ -271,6 +271,16 @@ class Engine:
                 conv3(n + ".conv2.weight", P[n + ".conv2.weight"])
                 if s.cin != s.f:
                     lin(n + ".dense.weight", P[n + ".dense.weight"], s.srcs_c if s.cat else None)
+                    # conv2 and the 1x1 skip as ONE implicit GEMM (forward): [conv2 taps | dense per source] along K
+                    srcs_c, cpF = (s.srcs_c if s.cat else [s.cin]), G.ceil64(s.f)
+                    f = self.buf("w.f." + n + ".conv2+dense", (s.f, 9 * cpF + sum(G.ceil64(c) for c in srcs_c)))
+                    ops.record_pack_weight(pick(n), P[n + ".conv2.weight"], 0, f, Cpad=cpF)
+                    ci0, koff = 0, 9 * cpF
+                    for c in srcs_c:
+                        ops.record_pack_weight(pick(n), P[n + ".dense.weight"], 0, f, ci0=ci0, cn=c, Cpad=G.ceil64(c), k_off=koff)
+                        ci0 += c
+                        koff += G.ceil64(c)
+                    W[n + ".conv2+dense"] = f
                 fw = P[n + ".film.dense.weight"]
                 ops.record_pack_weight(pick(f"film{s.lvl}"), fw, 0, W[f"film{s.lvl}"][s.film_off:s.film_off + 2 * s.f], Cpad=1024)
                 ops.record_copy(pick(f"film{s.lvl}"), P[n + ".film.dense.bias"], self._bufs[f"b.film{s.lvl}"][s.film_off:s.film_off + 2 * s.f])
@@ -443,16 +453,18 @@ class Engine:
         ssv = ss_l[:, s.film_off:s.film_off + 2 * F]
         (ops.gn_apply if fused else ops.gn_stats_apply)(c13, None, sums1, P[n + ".groupnorm1.gn.weight"], P[n + ".groupnorm1.gn.bias"], 2, a1, ss=ssv, F=F, drop_p=drop_p,
                      seed=seed, seed_ptr=self.seed_ptr, ss_image=self._ss_image)
+        out = self.buf(n + ".out", (N, hh, ww, F))
         if s.cin != F:
-            sk = self.buf(n + ".sk", (N, hh, ww, F))
-            srcs = [h_in.t] + ([skip.t] if skip is not None else [])
-            ops.gemm(G.conv_desc(srcs, [1] * len(srcs), Wp[n + ".dense.weight"], F, sk, bias=P[n + ".dense.bias"]))
+            # the 1x1 `dense` skip (xunet.py:148-150) rides in conv2's K loop as extra 1-tap segments over h_in (and the skip
+            # tensor): one launch, and its output never goes through HBM to come back as the residual.  Its bias enters as
+            # a per-image vector with image stride 0.
+            srcs = [a1.view(N, hh, ww, F), h_in.t] + ([skip.t] if skip is not None else [])
+            ops.gemm(G.conv_desc(srcs, [9] + [1] * (len(srcs) - 1), Wp[n + ".conv2+dense"], F, out, bias=P[n + ".conv2.bias"],
+                                 rowvec=P[n + ".dense.bias"].view(1, F).expand(N, F), out_scale=RSQRT2))
         else:
             assert skip is None
-            sk = h_in.t
-        out = self.buf(n + ".out", (N, hh, ww, F))
-        ops.gemm(G.conv_desc([a1.view(N, hh, ww, F)], [9], Wp[n + ".conv2.weight"], F, out, bias=P[n + ".conv2.bias"], resid=sk,
-                             out_scale=RSQRT2))
+            ops.gemm(G.conv_desc([a1.view(N, hh, ww, F)], [9], Wp[n + ".conv2.weight"], F, out, bias=P[n + ".conv2.bias"], resid=h_in.t,
+                                 out_scale=RSQRT2))
         o = Act(out, n + ".out")
         self.saved["acts"][n] = dict(h_in=h_in, skip=skip, sums0=sums0, a0=a0, c1=c1, sums1=sums1, a1=a1, out=o, seed=seed)
         if s.resample == "down":

@@ -208,6 +208,7 @@ def main():
     ap.add_argument("--no-profile", action="store_true")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-sampler", action="store_true")
+    ap.add_argument("--fp32-allreduce", action="store_true", help="all-reduce the gradients in fp32 (default: bf16 payload)")
     ap.add_argument("--no-extras", action="store_true", help="skip the CFG-128 extra line and the eager-GPU baseline (N = 1 only)")
     ap.add_argument("--model", default="cfg64", choices=["cfg64", "cfg128"], help="cfg128 = XUNet() defaults (H=W=128, ch=256), BASELINE configs[2]")
     ap.add_argument("--profile-json", default=None, help="dump the per-launch CUDA-event table of the profiled step")
@@ -231,7 +232,8 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
     assert world == args.gpus, (world, args.gpus)
     B = args.global_batch // world
-    tr = Trainer(MODEL_KW, B, dev, world=world, seed=1234, use_graph=not args.no_graph)      # (the trainer adds the rank to the seed)
+    tr = Trainer(MODEL_KW, B, dev, world=world, seed=1234, use_graph=not args.no_graph,
+                 grad_comm_dtype=torch.float32 if args.fp32_allreduce else torch.bfloat16)      # (the trainer adds the rank to the seed)
 
     # synthetic SRN-shaped data: a pool of host batches (pinned) and device-resident copies of the same
     pool = [synthetic.make_views(B, MODEL_KW["H"], seed=100 * rank + i) for i in range(4)]
@@ -366,7 +368,7 @@ def main():
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": value / 29.9,
             "dtype": "bf16", "data": "synthetic",
             "config": {"workload": args.model + "_train_step", "model": "XUNet(H=%d,W=%d,ch=%d)" % (MODEL_KW["H"], MODEL_KW["W"], MODEL_KW["ch"]), "global_batch": args.global_batch, "per_gpu_batch": B,
-                       "parallelism": f"dp{world}", "dropout": 0.1, "optimizer": "fused Adam", "cuda_graph": graphed,
+                       "parallelism": f"dp{world}", "grad_allreduce": ("fp32" if args.fp32_allreduce else "bf16") if world > 1 else None, "dropout": 0.1, "optimizer": "fused Adam", "cuda_graph": graphed,
                        "l2": "no flush needed: per-step working set (activations) is GBs, far above the 126 MB L2",
                        "baseline_note": "vs_baseline = value / 29.9 samples/s (README.md:39, 8x RTX 3090, derived)"},
             "clocks": clk, "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4, "last_loss": loss_val},

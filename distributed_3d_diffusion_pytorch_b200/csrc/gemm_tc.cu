@@ -33,6 +33,7 @@ constexpr int kMaxDynSmem = 227 * 1024 - 2048;  // 227 KB per CTA minus the stat
 
 struct Seg {
   int32_t src, dx, dy, ncb, bk0;
+  int32_t klast;   // K = 16 steps of the LAST 64-channel block of the segment that hold real channels (1..4): the zero-filled rest is not multiplied
 };
 
 struct alignas(64) KP {
@@ -270,7 +271,16 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
         mbar_wait(tempty_bar(acc), acc_phase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(acc * p.acc_stride);
+        // convolution / dense form: the last 64-channel block of a K segment may hold fewer than 64 real channels (the
+        // 144-channel conditioning input, the 8-channel stem input): only its real 16-channel steps are issued
+        const bool segk = p.a_major == 0 && p.b_major == 0;
+        int sidx = 0, cbi = 0, ncb_cur = segk ? p.seg[0].ncb : 0x7fffffff;
         for (int kb = 0; kb < nkb; ++kb) {
+          int ksteps = BK / 16;
+          if (segk) {
+            if (cbi == ncb_cur - 1) ksteps = p.seg[sidx].klast;
+            if (++cbi == ncb_cur) { cbi = 0; ++sidx; ncb_cur = sidx < p.nseg ? p.seg[sidx].ncb : 0x7fffffff; }
+          }
           mbar_wait(full_bar(stage), phase);
           tc_fence_after();
           const uint32_t sa = smem_base + (uint32_t)stage * p.stage_bytes;
@@ -279,24 +289,26 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
             if (elect_one()) {
 #pragma unroll
               for (int k = 0; k < BK / 16; ++k)
-                umma_bf16_pair(d_tmem, ad + (uint64_t)(k * a_kstep), bd + (uint64_t)(k * b_kstep), idesc, (kb | k) != 0 ? 1u : 0u);
+                if (k < ksteps) umma_bf16_pair(d_tmem, ad + (uint64_t)(k * a_kstep), bd + (uint64_t)(k * b_kstep), idesc, (kb | k) != 0 ? 1u : 0u);
               if (p.m2) {                   // second 128 rows of each CTA's A tile, second accumulator
 #pragma unroll
                 for (int k = 0; k < BK / 16; ++k)
-                  umma_bf16_pair(d_tmem + p.acc_half, ad + (uint64_t)((kABytes >> 4) + k * a_kstep), bd + (uint64_t)(k * b_kstep), idesc,
-                                 (kb | k) != 0 ? 1u : 0u);
+                  if (k < ksteps)
+                    umma_bf16_pair(d_tmem + p.acc_half, ad + (uint64_t)((kABytes >> 4) + k * a_kstep), bd + (uint64_t)(k * b_kstep), idesc,
+                                   (kb | k) != 0 ? 1u : 0u);
               }
               umma_commit_pair(empty_bar(stage));
             }
           } else if (elect_one()) {
 #pragma unroll
             for (int k = 0; k < BK / 16; ++k)
-              umma_bf16(d_tmem, ad + (uint64_t)(k * a_kstep), bd + (uint64_t)(k * b_kstep), idesc, (kb | k) != 0 ? 1u : 0u);
+              if (k < ksteps) umma_bf16(d_tmem, ad + (uint64_t)(k * a_kstep), bd + (uint64_t)(k * b_kstep), idesc, (kb | k) != 0 ? 1u : 0u);
             if (p.m2) {                     // rows 128..255 of the A tile against the same B tile, into the second accumulator
 #pragma unroll
               for (int k = 0; k < BK / 16; ++k)
-                umma_bf16(d_tmem + p.acc_half, ad + (uint64_t)((kABytes >> 4) + k * a_kstep), bd + (uint64_t)(k * b_kstep), idesc,
-                          (kb | k) != 0 ? 1u : 0u);
+                if (k < ksteps)
+                  umma_bf16(d_tmem + p.acc_half, ad + (uint64_t)((kABytes >> 4) + k * a_kstep), bd + (uint64_t)(k * b_kstep), idesc,
+                            (kb | k) != 0 ? 1u : 0u);
             }
             umma_commit(empty_bar(stage));  // frees the smem slot once these MMAs have read it
           }
@@ -933,6 +945,7 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
           B3D_CHECK_ARG(p.nseg < kMaxSeg, "b3d_gemm: too many K segments");
           Seg& sg = p.seg[p.nseg++];
           sg.src = i; sg.ncb = ncb; sg.bk0 = bk;
+          { const int rem = d->a[i].dim[0] - (ncb - 1) * BK; sg.klast = (rem + 15) / 16; if (sg.klast < 1) sg.klast = 1; if (sg.klast > BK / 16) sg.klast = BK / 16; }
           sg.dx = taps == 9 ? (tp % 3) - d->pad : 0;
           sg.dy = taps == 9 ? (tp / 3) - d->pad : 0;
           bk += ncb * BK;

@@ -205,6 +205,8 @@ def all_cases():
         conv_case("conv_s8_c144", 2, 64, 64, [144], [9], 128, stride=8),
         conv_case("conv_cat_256+128_1x1", 2, 16, 16, [256, 128], [1, 1], 128),
         conv_case("conv_fused_skip_3src", 2, 16, 16, [128, 64, 64], [9, 1, 1], 128, resid=False),
+        conv_case("conv_partial_blocks_3src", 2, 16, 16, [88, 40, 72], [9, 1, 1], 128, rowvec=True),     # last 64-channel blocks with 2 / 3 / 1 real K steps
+        conv_case("conv_c144_s1_pairwide", 4, 64, 64, [144], [9], 256),
         conv_case("conv_fp32out_alpha", 1, 16, 16, [64], [9], 64, fp32_out=True, alpha=0.5),
         wgrad_case("wgrad_dense_like", 1, 1, 4096, 256, 128, 1),
         wgrad_case("wgrad_16x16_c128_64", 2, 16, 16, 128, 64, 9),

@@ -33,8 +33,15 @@ struct alignas(64) BP {
   uint32_t off_k, off_v, off_q, off_do, off_o, off_p;    // shared-memory offsets of the operand tiles
   uint32_t col_k, col_v;                           // TMEM columns of the dK / dV accumulators (dP and dQ start at 0)
   float scale;
+  const float* lse;      // != nullptr: P is recomputed from Q, K and these row statistics (no P tensor is read)
+  float scale_log2e;
 };
 
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 __device__ __forceinline__ float dot8(const uint4& a, const uint4& b) {
   const __nv_bfloat162* x = reinterpret_cast<const __nv_bfloat162*>(&a);
   const __nv_bfloat162* y = reinterpret_cast<const __nv_bfloat162*>(&b);
@@ -46,14 +53,16 @@ __device__ __forceinline__ float dot8(const uint4& a, const uint4& b) {
 
 __global__ void __launch_bounds__(kThreads, 1) attn_bwd_kernel(const __grid_constant__ BP p) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ uint64_t bars[6];
+  __shared__ uint64_t bars[8];
   __shared__ uint32_t tmem_base_smem;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t kv_full = smem_u32(&bars[0]), t_full = smem_u32(&bars[1]), pre_full = smem_u32(&bars[2]), ds_ready = smem_u32(&bars[3]),
-                 post_full = smem_u32(&bars[4]), acc_read = smem_u32(&bars[5]);
+                 post_full = smem_u32(&bars[4]), acc_read = smem_u32(&bars[5]), s_full = smem_u32(&bars[6]), p_ready = smem_u32(&bars[7]);
+  const bool recompute = p.lse != nullptr;
   if (threadIdx.x == 0) {
     mbar_init(kv_full, 1); mbar_init(t_full, 1); mbar_init(pre_full, 1); mbar_init(ds_ready, 4); mbar_init(post_full, 1); mbar_init(acc_read, 4);
+    mbar_init(s_full, 1); mbar_init(p_ready, 4);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) tmem_alloc(smem_u32(&tmem_base_smem), 512u);
@@ -81,13 +90,14 @@ __global__ void __launch_bounds__(kThreads, 1) attn_bwd_kernel(const __grid_cons
               tma_load_4d(sV + j * kv_chunk, &p.tmV, kv_full, j * 64, 0, head, nk);
             }
           }
-          mbar_expect_tx(t_full, (uint32_t)(3 * p.dch + p.kch2) * 16384u);
+          mbar_expect_tx(t_full, (uint32_t)(3 * p.dch + (recompute ? 0 : p.kch2)) * 16384u);
           for (int j = 0; j < p.dch; ++j) {
             tma_load_4d(sQ + j * 16384, &p.tmQ, t_full, j * 64, t * 128, head, n);
             tma_load_4d(sDO + j * 16384, &p.tmDO, t_full, j * 64, t * 128, head, n);
             tma_load_4d(sO + j * 16384, &p.tmO, t_full, j * 64, t * 128, head, n);
           }
-          for (int c = 0; c < p.kch2; ++c) tma_load_4d(sP + c * 16384, &p.tmP, t_full, c * 64, t * 128, head, n);
+          if (!recompute)
+            for (int c = 0; c < p.kch2; ++c) tma_load_4d(sP + c * 16384, &p.tmP, t_full, c * 64, t * 128, head, n);
         }
       }
     }
@@ -105,6 +115,18 @@ __global__ void __launch_bounds__(kThreads, 1) attn_bwd_kernel(const __grid_cons
           mbar_wait(t_full, tiles & 1);
           if (tiles > 0) mbar_wait(acc_read, (tiles - 1) & 1);      // dQ (and, across items, dK / dV) drained from TMEM
           tc_fence_after();
+          if (recompute) {
+            // S = Q_t K^T into the dP columns; the four warps turn it into the bf16 P tile in shared memory, then dP may overwrite it
+            for (int j = 0; j < p.dch; ++j) {
+              const int ksteps = min(4, (p.d - j * 64 + 15) / 16);
+              for (int k = 0; k < ksteps; ++k)
+                umma_bf16(tmem_base, umma_desc(sQ + j * 16384 + k * 32, 16, 1024), umma_desc(sK + j * kv_chunk + k * 32, 16, 1024), idesc_dp,
+                          (j | k) != 0 ? 1u : 0u);
+            }
+            umma_commit(s_full);
+            mbar_wait(p_ready, tiles & 1);
+            tc_fence_after();
+          }
           // dP = dO_t V^T : M = 128 queries, N = Lb2 keys, K = head_dim
           for (int j = 0; j < p.dch; ++j) {
             const int ksteps = min(4, (p.d - j * 64 + 15) / 16);
@@ -154,6 +176,33 @@ __global__ void __launch_bounds__(kThreads, 1) attn_bwd_kernel(const __grid_cons
           const uint32_t ro = sO + (uint32_t)j * 16384u + (uint32_t)r * 128u, rd = sDO + (uint32_t)j * 16384u + (uint32_t)r * 128u;
 #pragma unroll
           for (int u = 0; u < 8; ++u) D += dot8(lds128(ro + ((((uint32_t)u) ^ swz) << 4)), lds128(rd + ((((uint32_t)u) ^ swz) << 4)));   // conflict-free order
+        }
+        if (recompute) {
+          // P_ij = 2^(s_ij * scale * log2e - lse_i) as bf16 into the P tile (the layout a TMA load of the saved P would give);
+          // rows past L and keys past L are zero, like the zero fill of that load
+          const float l2 = valid ? __ldg(p.lse + ((long long)n * p.heads + head) * p.L + q) : 0.f;
+          mbar_wait(s_full, tiles & 1);
+          tc_fence_after();
+          for (int c = 0; c < p.Lb2 / 32; ++c) {
+            uint32_t v[32];
+            tmem_ld32(tmem_base + lane_addr + c * 32, v);
+            float f[32];
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              f[i] = (valid && c * 32 + i < p.L) ? ex2_approx(fmaf(__uint_as_float(v[i]), p.scale_log2e, -l2)) : 0.f;
+            const uint32_t row = sP + (uint32_t)(c >> 1) * 16384u + (uint32_t)r * 128u;
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+              uint4 o4;
+              o4.x = pack_bf16x2(f[8 * g], f[8 * g + 1]); o4.y = pack_bf16x2(f[8 * g + 2], f[8 * g + 3]);
+              o4.z = pack_bf16x2(f[8 * g + 4], f[8 * g + 5]); o4.w = pack_bf16x2(f[8 * g + 6], f[8 * g + 7]);
+              sts128(row + ((((uint32_t)((c & 1) * 4 + g)) ^ swz) << 4), o4);
+            }
+          }
+          tc_fence_before();
+          fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(p_ready);
         }
         mbar_wait(pre_full, tiles & 1);
         tc_fence_after();
@@ -255,18 +304,20 @@ extern "C" int b3d_attn_bwd_supported(int L, int d) {
   return smem <= 220 * 1024 ? 1 : 0;
 }
 
-extern "C" int b3d_attn_bwd(const void* qkv, const void* probs, int64_t ld_probs, const void* o, const void* dout, void* dqkv, int N, int L,
-                            int heads, int d, int cross, float scale, void* stream_) {
+extern "C" int b3d_attn_bwd(const void* qkv, const void* probs, int64_t ld_probs, const float* lse, const void* o, const void* dout, void* dqkv,
+                            int N, int L, int heads, int d, int cross, float scale, void* stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
-  B3D_CHECK_ARG(qkv && probs && o && dout && dqkv && N > 0 && heads > 0, "attn_bwd: null / empty");
+  B3D_CHECK_ARG(qkv && o && dout && dqkv && N > 0 && heads > 0, "attn_bwd: null / empty");
+  B3D_CHECK_ARG((probs != nullptr) != (lse != nullptr), "attn_bwd: pass either the saved probabilities or the saved row statistics (lse)");
   B3D_CHECK_ARG(b3d_attn_bwd_supported(L, d), "attn_bwd: L = %d, head_dim = %d is outside the fused path (use the b3d_gemm path)", L, d);
   B3D_CHECK_ARG(!cross || N % 2 == 0, "attn_bwd: cross-frame attention needs an even number of images");
-  B3D_CHECK_ARG(ld_probs % 8 == 0 && ld_probs >= L, "attn_bwd: probs row stride must be a multiple of 8 and >= L");
+  B3D_CHECK_ARG(probs == nullptr || (ld_probs % 8 == 0 && ld_probs >= L), "attn_bwd: probs row stride must be a multiple of 8 and >= L");
   const int C = heads * d;
   B3D_CHECK_ARG(((((uintptr_t)o) | ((uintptr_t)dout) | ((uintptr_t)dqkv)) & 15) == 0, "attn_bwd: o / dout / dqkv must be 16-byte aligned");
   BP p;
   memset(&p, 0, sizeof(p));
   p.N = N; p.L = L; p.heads = heads; p.d = d; p.C = C; p.cross = cross ? 1 : 0; p.scale = scale;
+  p.lse = lse; p.scale_log2e = scale * 1.4426950408889634f;
   p.Lb2 = (L + 127) / 128 * 128;
   p.qtiles = (L + 127) / 128;
   p.items = N * heads;
@@ -291,10 +342,12 @@ extern "C" int b3d_attn_bwd(const void* qkv, const void* probs, int64_t ld_probs
   rc = make_map(&p.tmDO, v, boxQ, ones); if (rc) return rc;
   v.ptr = o;
   rc = make_map(&p.tmO, v, boxQ, ones); if (rc) return rc;
-  b3d_view4 pv;
-  pv.ptr = probs; pv.dim[0] = L; pv.dim[1] = L; pv.dim[2] = heads; pv.dim[3] = N;
-  pv.stride[0] = ld_probs; pv.stride[1] = (int64_t)L * ld_probs; pv.stride[2] = (int64_t)heads * L * ld_probs;
-  rc = make_map(&p.tmP, pv, boxQ, ones); if (rc) return rc;
+  if (probs != nullptr) {
+    b3d_view4 pv;
+    pv.ptr = probs; pv.dim[0] = L; pv.dim[1] = L; pv.dim[2] = heads; pv.dim[3] = N;
+    pv.stride[0] = ld_probs; pv.stride[1] = (int64_t)L * ld_probs; pv.stride[2] = (int64_t)heads * L * ld_probs;
+    rc = make_map(&p.tmP, pv, boxQ, ones); if (rc) return rc;
+  }
   const size_t smem = (size_t)p.off_p + (size_t)p.kch2 * 16384 + 1024;
   static size_t attr_smem = 0;
   if (smem > attr_smem) {

@@ -35,6 +35,7 @@ __device__ __forceinline__ float ex2_approx(float x) {
 struct alignas(64) AP {
   CUtensorMap tmQ, tmK, tmV, tmO, tmP;
   int N, L, Lb, heads, d, cross, qtiles, items, write_p;
+  float* lse;           // optional fp32 [N, heads, L]: log2-domain log-sum-exp of the scaled scores (the backward recomputes P from it)
   int v_one_stage;      // all V chunks of an item fit the B part of ONE pipeline stage (kch * dch * 8 KB <= 32 KB)
   float scale_log2e;
 };
@@ -182,6 +183,8 @@ __global__ void __launch_bounds__(kThreads, 1) attn_fwd_kernel(const __grid_cons
           sts128(row + ((((uint32_t)((c & 1) * 4 + g)) ^ swz) << 4), q);
         }
       }
+      // row statistic for a backward pass that recomputes P instead of reading it back: P_ij = 2^(s_ij*scale*log2e - lse_i)
+      if (p.lse != nullptr && qt * 128 + r < p.L) p.lse[((long long)n * p.heads + head) * p.L + qt * 128 + r] = mb + __log2f(l);
       // third sweep, over shared memory only: normalise the row in place (each thread re-reads what it wrote)
       const float inv_l = 1.f / l;
       for (int c = 0; c < kch; ++c) {                    // one 64-key chunk (a 128-byte row segment) per iteration: 8 loads in flight
@@ -251,7 +254,7 @@ __global__ void __launch_bounds__(kThreads, 1) attn_fwd_kernel(const __grid_cons
 }  // namespace
 
 extern "C" int b3d_attn_fwd(const void* qkv, int N, int L, int heads, int d, int cross, float scale, void* out, void* probs, int64_t ld_probs,
-                            void* stream_) {
+                            float* lse, void* stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   B3D_CHECK_ARG(qkv && out && N > 0 && heads > 0, "attn_fwd: null / empty");
   B3D_CHECK_ARG(L >= 1 && L <= 256, "attn_fwd: L = %d tokens (fused path covers L <= 256; longer sequences use the b3d_gemm path)", L);
@@ -266,6 +269,7 @@ extern "C" int b3d_attn_fwd(const void* qkv, int N, int L, int heads, int d, int
   p.qtiles = (L + 127) / 128;
   p.items = N * heads * p.qtiles;
   p.write_p = probs != nullptr;
+  p.lse = lse;
   p.v_one_stage = ((L + 63) / 64) * ((d + 63) / 64) * 8192 <= 32768 ? 1 : 0;
   p.scale_log2e = scale * 1.4426950408889634f;
   const uint32_t ones[4] = {1, 1, 1, 1};

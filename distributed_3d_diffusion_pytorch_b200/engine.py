@@ -499,11 +499,14 @@ class Engine:
         q, k, v = self._qkv_views(qkv, L, C)
         Lp = (L + 7) // 8 * 8
         need_p = self.saved["need_bwd"]
-        p = self.buf(n + ".p", (N, Hh, L, Lp))[..., :L] if (need_p or L > 256) else None
+        # flash-style where the fused backward covers the shape: the forward keeps one fp32 per query row and the backward
+        # recomputes P; otherwise P itself is kept for the unfused backward
+        lse = self.buf(n + ".lse", (N, Hh, L), torch.float32) if (need_p and ops.attn_bwd_supported(L, d)) else None
+        p = self.buf(n + ".p", (N, Hh, L, Lp))[..., :L] if ((need_p and lse is None) or L > 256) else None
         o = self.buf(n + ".o", (N, L, C))
         if L <= 256 and d % 16 == 0 and d <= 256:
-            # fused: S and O stay in TMEM, P goes through shared memory (written out only when backward follows)
-            ops.attn_fwd(qkv, Hh, s.cross, 1.0 / math.sqrt(d), o, probs=p if need_p else None)
+            # fused: S and O stay in TMEM, P goes through shared memory (written out only for an unfused backward)
+            ops.attn_fwd(qkv, Hh, s.cross, 1.0 / math.sqrt(d), o, probs=p if (need_p and lse is None) else None, lse=lse)
         else:
             logits = self.tmp("logits", (N, Hh, L, Lp), torch.float32)[..., :L]      # fp32: never rounded before the softmax
             ops.gemm(G.attn_qk_desc(q, k, logits, s.cross, 1.0 / math.sqrt(d)))
@@ -515,7 +518,7 @@ class Engine:
         ops.gemm(G.dense_desc(o1, Wp[n + ".linear.weight"], out.view(N * L, C), C, bias=P[n + ".linear.bias"], resid=h_in.t.view(N * L, C),
                               out_scale=RSQRT2))
         oa = Act(out, n + ".out")
-        self.saved["acts"][n] = dict(h_in=h_in, sums=sums, g=g, qkv=qkv, p=p, o=o, o1=o1, out=oa)
+        self.saved["acts"][n] = dict(h_in=h_in, sums=sums, g=g, qkv=qkv, p=p, lse=lse, o=o, o1=o1, out=oa)
         return oa
 
     # ------------------------------------------------------------------ backward
@@ -809,7 +812,7 @@ class Engine:
         dqkv = self.side_tmp(n, "dqkv", (N, L, 3 * C))
         if ops.attn_bwd_supported(L, d):
             # fused: dP, dS and the dK / dV accumulation over the query tiles stay on the SM
-            ops.attn_bwd(sa["qkv"], p, sa["o"], do, dqkv, Hh, s.cross, alpha)
+            ops.attn_bwd(sa["qkv"], None, sa["o"], do, dqkv, Hh, s.cross, alpha, lse=sa["lse"])
         else:
             q, k, v = self._qkv_views(sa["qkv"], L, C)
             dov = do.view(N, L, Hh, d).permute(0, 2, 1, 3)

@@ -257,25 +257,29 @@ class CudaOps:
                           f"split={d.split_k} bn={d.bn_tile} batched={int(d.batched)} fp32={int(o.dtype == torch.float32)}")
         self._call("b3d_gemm", ctypes.byref(cd), self.stream())
 
-    def attn_fwd(self, qkv, heads, cross, scale, out, probs=None):
-        """fused softmax(QK^T*scale)V; qkv [N,L,3C] bf16 -> out [N,L,C]; probs (optional) [N,heads,L,Lp] view with Lp % 8 == 0"""
+    def attn_fwd(self, qkv, heads, cross, scale, out, probs=None, lse=None):
+        """fused softmax(QK^T*scale)V; qkv [N,L,3C] bf16 -> out [N,L,C]; probs (optional) [N,heads,L,Lp] view with Lp % 8 == 0;
+        lse (optional) fp32 [N,heads,L]: the row statistics a P-recomputing backward needs"""
         N, L, C3 = qkv.shape
         d = C3 // 3 // heads
         assert qkv.is_contiguous() and out.is_contiguous() and qkv.dtype == torch.bfloat16
+        assert lse is None or (lse.dtype == torch.float32 and lse.is_contiguous() and lse.shape == (N, heads, L))
         ld = probs.stride(2) if probs is not None else 0
         self._call("b3d_attn_fwd", _ptr(qkv), c_i32(N), c_i32(L), c_i32(heads), c_i32(d), c_i32(int(cross)), c_f32(scale), _ptr(out),
-                   _ptr(probs), c_i64(ld), self.stream())
+                   _ptr(probs), c_i64(ld), _ptr(lse), self.stream())
 
     def attn_bwd_supported(self, L, d):
         return bool(self.lib.b3d_attn_bwd_supported(c_i32(L), c_i32(d)))
 
-    def attn_bwd(self, qkv, probs, o, dout, dqkv, heads, cross, scale):
-        """fused attention backward: qkv [N,L,3C], probs [N,heads,L,Lp] view (saved by attn_fwd), o / dout [N,L,C] -> dqkv [N,L,3C]"""
+    def attn_bwd(self, qkv, probs, o, dout, dqkv, heads, cross, scale, lse=None):
+        """fused attention backward: qkv [N,L,3C], o / dout [N,L,C] -> dqkv [N,L,3C]; from probs [N,heads,L,Lp] view (saved by
+        attn_fwd) or, probs=None, from lse [N,heads,L] (P is recomputed)"""
         N, L, C3 = qkv.shape
         d = C3 // 3 // heads
         assert qkv.is_contiguous() and o.is_contiguous() and dout.is_contiguous() and dqkv.is_contiguous()
-        self._call("b3d_attn_bwd", _ptr(qkv), _ptr(probs), c_i64(probs.stride(2)), _ptr(o), _ptr(dout), _ptr(dqkv), c_i32(N), c_i32(L),
-                   c_i32(heads), c_i32(d), c_i32(int(cross)), c_f32(scale), self.stream())
+        assert (probs is None) != (lse is None)
+        self._call("b3d_attn_bwd", _ptr(qkv), _ptr(probs), c_i64(probs.stride(2) if probs is not None else 0), _ptr(lse), _ptr(o), _ptr(dout),
+                   _ptr(dqkv), c_i32(N), c_i32(L), c_i32(heads), c_i32(d), c_i32(int(cross)), c_f32(scale), self.stream())
 
     # ---- conditioning
     def pose_embedding(self, K, R, t, mask, pos_emb, first_emb, other_emb, out):

@@ -89,18 +89,22 @@ int b3d_gemm_stats_supported(const b3d_gemm_desc* d);
 /* Fused attention forward for L <= 256 tokens, head_dim <= 256 (all attention levels of CFG-64; the deepest of CFG-128):
  * softmax(Q K^T * scale) V per (image, head) with S and O in TMEM, P through shared memory, operands by TMA straight
  * from the packed in_proj output qkv [N, L, 3*heads*d] (bf16).  cross = 1 reads K, V of image n ^ 1 (xunet.py:206-211).
- * out: bf16 [N, L, heads*d].  probs: optional bf16 [N, heads, L, ld_probs] (normalised P, kept for the backward pass).
+ * out: bf16 [N, L, heads*d].  probs: optional bf16 [N, heads, L, ld_probs] (normalised P, for a backward pass that reads P).
+ * lse: optional fp32 [N, heads, L], per query row log2(sum_j 2^(s_ij*scale*log2e)): all a flash-style backward needs, it
+ * recomputes P_ij = 2^(s_ij*scale*log2e - lse_i) from Q and K (8 B per row instead of 2*L).
  * Replaces the bmm / softmax / bmm inside nn.MultiheadAttention (xunet.py:161,175). */
 int b3d_attn_fwd(const void* qkv, int N, int L, int heads, int d, int cross, float scale, void* out, void* probs, int64_t ld_probs,
-                 void* stream);
+                 float* lse, void* stream);
 /* Fused backward of the same op (autograd of the MultiheadAttention core, xunet.py:161,175,202-211): from the packed qkv,
- * the probabilities the forward saved, the attention output o [N,L,C] and its gradient dout [N,L,C] it writes
+ * either the probabilities the forward saved (probs) or -- probs = NULL -- the row statistics lse it saved (P is then recomputed
+ * tile by tile: one more QK^T on the tensor cores and one exponential per score, no L x L tensor in HBM at all),
+ * the attention output o [N,L,C] and its gradient dout [N,L,C] it writes
  * dqkv [N,L,3C] (dQ | dK | dV; cross: dK, dV go to image n ^ 1).  dP, dS never leave the SM.  Covers
  * b3d_attn_bwd_supported(L, d) == 1 (L <= 256, head_dim <= 128 with the accumulators fitting 512 TMEM columns);
  * other shapes use the b3d_gemm + b3d_softmax_bwd path. */
 int b3d_attn_bwd_supported(int L, int d);
-int b3d_attn_bwd(const void* qkv, const void* probs, int64_t ld_probs, const void* o, const void* dout, void* dqkv, int N, int L, int heads,
-                 int d, int cross, float scale, void* stream);
+int b3d_attn_bwd(const void* qkv, const void* probs, int64_t ld_probs, const float* lse, const void* o, const void* dout, void* dqkv, int N, int L,
+                 int heads, int d, int cross, float scale, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * HBM-bound kernels (elementwise / normalisation / reductions).  bf16 NHWC unless noted.

@@ -46,8 +46,11 @@ def main():
         t0 = timeit(lambda: ops.attn_fwd(qkv, heads, True, sc, out, probs=None))
         t1 = timeit(lambda: ops.attn_fwd(qkv, heads, True, sc, out, probs=probs[..., :L]))
         t2 = timeit(lambda: ops.attn_bwd(qkv, probs[..., :L], out, dout, dqkv, heads, True, sc))
-        print(f"N={N} L={L} heads={heads} d={d}: fwd {t0:7.1f} us ({flop_f / t0 / 1e6:6.1f} TF/s)  fwd+P {t1:7.1f} us  bwd {t2:7.1f} us "
-              f"({2.5 * flop_f / t2 / 1e6:6.1f} TF/s)", flush=True)
+        lse = torch.empty(N, heads, L, device=dev)
+        t3 = timeit(lambda: ops.attn_fwd(qkv, heads, True, sc, out, lse=lse))
+        t4 = timeit(lambda: ops.attn_bwd(qkv, None, out, dout, dqkv, heads, True, sc, lse=lse))
+        print(f"N={N} L={L} heads={heads} d={d}: fwd {t0:7.1f} us ({flop_f / t0 / 1e6:6.1f} TF/s)  fwd+P {t1:7.1f} us  bwd(P) {t2:7.1f} us "
+              f"({2.5 * flop_f / t2 / 1e6:6.1f} TF/s)  fwd+lse {t3:7.1f} us  bwd(lse, P recomputed) {t4:7.1f} us", flush=True)
 
 
 if __name__ == "__main__":

@@ -198,13 +198,16 @@ class EmuOps:
         if d.out2 is not None:
             d.out2[:, :, :rows, :d.n_cols][n_idx] = tmp2.to(d.out2.dtype)
 
-    def attn_fwd(self, qkv, heads, cross, scale, out, probs=None):
+    def attn_fwd(self, qkv, heads, cross, scale, out, probs=None, lse=None):
         N, L, C3 = qkv.shape
         C = C3 // 3
         d = C // heads
         q, k, v = (qkv.float().view(N, L, 3, heads, d)[:, :, i].permute(0, 2, 1, 3) for i in range(3))
         idx = torch.arange(N) ^ int(cross)
-        P = torch.softmax((q @ k[idx].transpose(-1, -2)) * scale, -1)
+        S = (q @ k[idx].transpose(-1, -2)) * scale
+        P = torch.softmax(S, -1)
+        if lse is not None:          # log2-domain log-sum-exp of the scaled scores
+            lse.copy_(torch.logsumexp(S, -1) * 1.4426950408889634)
         if probs is not None:
             probs[..., :L] = P.to(probs.dtype)
             P = probs[..., :L].float()
@@ -214,13 +217,16 @@ class EmuOps:
         Lb2 = (L + 127) // 128 * 128
         return 1 <= L <= 256 and 16 <= d <= 128 and d % 16 == 0 and Lb2 + 2 * (Lb2 // 128) * d <= 512 and d <= Lb2
 
-    def attn_bwd(self, qkv, probs, o, dout, dqkv, heads, cross, scale):
+    def attn_bwd(self, qkv, probs, o, dout, dqkv, heads, cross, scale, lse=None):
         N, L, C3 = qkv.shape
         C = C3 // 3
         d = C // heads
         q, k, v = (qkv.float().view(N, L, 3, heads, d)[:, :, i].permute(0, 2, 1, 3) for i in range(3))
         idx = torch.arange(N) ^ int(cross)
-        P = probs[..., :L].float()
+        if probs is not None:
+            P = probs[..., :L].float()
+        else:                        # recomputed from the row statistics, rounded like the tile the kernel builds
+            P = torch.exp2((q @ k[idx].transpose(-1, -2)) * (scale * 1.4426950408889634) - lse.float()[..., None]).to(self.act_dtype).float()
         dO = dout.float().view(N, L, heads, d).permute(0, 2, 1, 3)
         O = o.float().view(N, L, heads, d).permute(0, 2, 1, 3)
         dP = dO @ v[idx].transpose(-1, -2)

@@ -205,7 +205,14 @@ def attn_case(N, L, heads, d, cross, with_p, seed=0):
         qkv = _mk(ops, _r((N, L, 3 * C), g))
         out = ops.zeros((N, L, C))
         Lp = (L + 7) // 8 * 8
-        probs = ops.zeros((N, heads, L, Lp)) if with_p else None
+        probs = ops.zeros((N, heads, L, Lp)) if with_p is True else None
+        if with_p == "lse":          # flash-style: the forward keeps 4 bytes per query row, the backward recomputes P
+            lse = ops.zeros((N, heads, L), torch.float32)
+            ops.attn_fwd(qkv, heads, cross, 1.0 / math.sqrt(d), out, lse=lse)
+            dout = _mk(ops, _r((N, L, C), g))
+            dqkv = ops.zeros((N, L, 3 * C))
+            ops.attn_bwd(qkv, None, out, dout, dqkv, heads, cross, 1.0 / math.sqrt(d), lse=lse)
+            return [out, lse, dqkv]
         ops.attn_fwd(qkv, heads, cross, 1.0 / math.sqrt(d), out, probs[..., :L] if with_p else None)
         outs = [out] + ([probs] if with_p else [])
         if with_p and ops.attn_bwd_supported(L, d):
@@ -226,6 +233,11 @@ def all_cases():
         "attn_fused_L16_d16_self": attn_case(2, 16, 4, 16, False, True, seed=3),
         "attn_fused_L36_d32_cross": attn_case(2, 36, 2, 32, True, True, seed=4),
         "attn_fused_L200_d64_many": attn_case(64, 200, 4, 64, True, True, seed=5),
+        "attn_lse_L256_d64_self": attn_case(4, 256, 4, 64, False, "lse", seed=6),
+        "attn_lse_L64_d128_cross": attn_case(4, 64, 4, 128, True, "lse", seed=7),
+        "attn_lse_L36_d32_cross": attn_case(2, 36, 2, 32, True, "lse", seed=8),
+        "attn_lse_L200_d64_many": attn_case(64, 200, 4, 64, True, "lse", seed=9),
+        "attn_lse_L16_d16_self": attn_case(2, 16, 4, 16, False, "lse", seed=10),
         "pose_fp32_64": pose_case(3, 64, 64, True),
         "pose_fp32_24": pose_case(2, 24, 24, True, seed=3),
         "pose_bf16_16": pose_case(2, 16, 16, False, seed=4),

@@ -112,6 +112,9 @@ class Engine:
         # GroupNorm statistics of conv1's output from its own epilogue (measured in-run: +0.5% at batch 128, -0.4% at batch 16,
         # where the extra epilogue work costs more than the small gn_stats launch: large batches only; B3D_NO_FUSE_STATS=1 = off)
         self.fuse_stats = os.environ.get("B3D_NO_FUSE_STATS") != "1" and 2 * B * cfg.H * cfg.W > 64 * 64 * 64
+        # attention backward: recompute P from the saved row log-sum-exp (no L x L tensor in HBM, 134 MB less per 16x16 block at
+        # batch 128) instead of reading back the P the forward wrote; B3D_ATTN_SAVE_P=1 selects the latter (measurement switch)
+        self.attn_recompute = os.environ.get("B3D_ATTN_SAVE_P") != "1"
         self.seed_ptr = None      # optional int64 device scalar added to every dropout seed (see ops.gn_apply)
         for lvl in range(cfg.num_resolutions):
             assert cfg.H % (2 ** lvl) == 0 and cfg.W % (2 ** lvl) == 0
@@ -501,7 +504,7 @@ class Engine:
         need_p = self.saved["need_bwd"]
         # flash-style where the fused backward covers the shape: the forward keeps one fp32 per query row and the backward
         # recomputes P; otherwise P itself is kept for the unfused backward
-        lse = self.buf(n + ".lse", (N, Hh, L), torch.float32) if (need_p and ops.attn_bwd_supported(L, d)) else None
+        lse = self.buf(n + ".lse", (N, Hh, L), torch.float32) if (need_p and self.attn_recompute and ops.attn_bwd_supported(L, d)) else None
         p = self.buf(n + ".p", (N, Hh, L, Lp))[..., :L] if ((need_p and lse is None) or L > 256) else None
         o = self.buf(n + ".o", (N, L, C))
         if L <= 256 and d % 16 == 0 and d <= 256:
@@ -812,7 +815,10 @@ class Engine:
         dqkv = self.side_tmp(n, "dqkv", (N, L, 3 * C))
         if ops.attn_bwd_supported(L, d):
             # fused: dP, dS and the dK / dV accumulation over the query tiles stay on the SM
-            ops.attn_bwd(sa["qkv"], None, sa["o"], do, dqkv, Hh, s.cross, alpha, lse=sa["lse"])
+            if sa["lse"] is not None:
+                ops.attn_bwd(sa["qkv"], None, sa["o"], do, dqkv, Hh, s.cross, alpha, lse=sa["lse"])
+            else:
+                ops.attn_bwd(sa["qkv"], p, sa["o"], do, dqkv, Hh, s.cross, alpha)
         else:
             q, k, v = self._qkv_views(sa["qkv"], L, C)
             dov = do.view(N, L, Hh, d).permute(0, 2, 1, 3)

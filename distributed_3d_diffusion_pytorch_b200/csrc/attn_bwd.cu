@@ -33,6 +33,8 @@ struct alignas(64) BP {
   uint32_t off_k, off_v, off_q, off_do, off_o, off_p;    // shared-memory offsets of the operand tiles
   uint32_t col_k, col_v;                           // TMEM columns of the dK / dV accumulators (dP and dQ start at 0)
   float scale;
+  int nbuf;              // 1 or 2 sets of per-tile operand buffers (Q, dO, O): with 2 the next tile's loads overlap this tile's work
+  uint32_t tile_bytes;   // bytes of one set
   const float* lse;      // != nullptr: P is recomputed from Q, K and these row statistics (no P tensor is read)
   float scale_log2e;
 };
@@ -53,15 +55,20 @@ __device__ __forceinline__ float dot8(const uint4& a, const uint4& b) {
 
 __global__ void __launch_bounds__(kThreads, 1) attn_bwd_kernel(const __grid_constant__ BP p) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ uint64_t bars[8];
+  __shared__ uint64_t bars[10];
   __shared__ uint32_t tmem_base_smem;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t kv_full = smem_u32(&bars[0]), t_full = smem_u32(&bars[1]), pre_full = smem_u32(&bars[2]), ds_ready = smem_u32(&bars[3]),
-                 post_full = smem_u32(&bars[4]), acc_read = smem_u32(&bars[5]), s_full = smem_u32(&bars[6]), p_ready = smem_u32(&bars[7]);
+  // t_full[b] / post_full[b]: per operand-buffer set b (a tile T uses set T % nbuf, phase (T / nbuf) & 1); the others are per tile
+  const uint32_t kv_full = smem_u32(&bars[0]), pre_full = smem_u32(&bars[2]), ds_ready = smem_u32(&bars[3]),
+                 acc_read = smem_u32(&bars[5]), s_full = smem_u32(&bars[6]), p_ready = smem_u32(&bars[7]);
+  auto t_full = [&](uint32_t T) { return smem_u32(&bars[T % p.nbuf == 0 ? 1 : 8]); };
+  auto post_full = [&](uint32_t T) { return smem_u32(&bars[T % p.nbuf == 0 ? 4 : 9]); };
+  auto tpar = [&](uint32_t T) { return (T / p.nbuf) & 1u; };
   const bool recompute = p.lse != nullptr;
   if (threadIdx.x == 0) {
-    mbar_init(kv_full, 1); mbar_init(t_full, 1); mbar_init(pre_full, 1); mbar_init(ds_ready, 4); mbar_init(post_full, 1); mbar_init(acc_read, 4);
+    mbar_init(kv_full, 1); mbar_init(smem_u32(&bars[1]), 1); mbar_init(smem_u32(&bars[8]), 1); mbar_init(pre_full, 1); mbar_init(ds_ready, 4);
+    mbar_init(smem_u32(&bars[4]), 1); mbar_init(smem_u32(&bars[9]), 1); mbar_init(acc_read, 4);
     mbar_init(s_full, 1); mbar_init(p_ready, 4);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -71,8 +78,8 @@ __global__ void __launch_bounds__(kThreads, 1) attn_bwd_kernel(const __grid_cons
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_smem;
   b3d_pdl_sync();   // nothing above touches global memory
-  const uint32_t sK = smem_base + p.off_k, sV = smem_base + p.off_v, sQ = smem_base + p.off_q, sDO = smem_base + p.off_do, sO = smem_base + p.off_o,
-                 sP = smem_base + p.off_p;
+  const uint32_t sK = smem_base + p.off_k, sV = smem_base + p.off_v, sP = smem_base + p.off_p;
+  const uint32_t sQ0 = smem_base + p.off_q, sDO0 = smem_base + p.off_do, sO0 = smem_base + p.off_o;
   const uint32_t kv_chunk = (uint32_t)p.Lb2 * 128u;      // bytes of one 64-wide head_dim chunk of K or V (all keys)
   const int halves = p.Lb2 / 128;
 
@@ -82,22 +89,27 @@ __global__ void __launch_bounds__(kThreads, 1) attn_bwd_kernel(const __grid_cons
       for (int it = blockIdx.x; it < p.items; it += gridDim.x) {
         const int head = it % p.heads, n = it / p.heads, nk = n ^ p.cross;
         for (int t = 0; t < p.qtiles; ++t, ++tiles) {
-          if (tiles > 0) mbar_wait(post_full, (tiles - 1) & 1);      // the previous tile's MMAs have finished reading shared memory
-          if (t == 0) {
+          // this tile's operand set is free once the MMAs of the tile that used it last have finished reading shared memory;
+          // K and V of a new item additionally wait for the previous item's last tile
+          if (tiles >= (uint32_t)p.nbuf) mbar_wait(post_full(tiles - p.nbuf), tpar(tiles - p.nbuf));
+          const uint32_t bo = (tiles % p.nbuf) * p.tile_bytes, sQ = sQ0 + bo, sDO = sDO0 + bo, sO = sO0 + bo;
+          const uint32_t tf = t_full(tiles);
+          mbar_expect_tx(tf, (uint32_t)(3 * p.dch + (recompute ? 0 : p.kch2)) * 16384u);
+          for (int j = 0; j < p.dch; ++j) {
+            tma_load_4d(sQ + j * 16384, &p.tmQ, tf, j * 64, t * 128, head, n);
+            tma_load_4d(sDO + j * 16384, &p.tmDO, tf, j * 64, t * 128, head, n);
+            tma_load_4d(sO + j * 16384, &p.tmO, tf, j * 64, t * 128, head, n);
+          }
+          if (!recompute)
+            for (int c = 0; c < p.kch2; ++c) tma_load_4d(sP + c * 16384, &p.tmP, tf, c * 64, t * 128, head, n);
+          if (t == 0) {      // (after the tile's own loads: with two operand sets those are already in flight while this waits)
+            if (tiles > 0 && p.nbuf > 1) mbar_wait(post_full(tiles - 1), tpar(tiles - 1));
             mbar_expect_tx(kv_full, 2u * (uint32_t)p.dch * kv_chunk);
             for (int j = 0; j < p.dch; ++j) {
               tma_load_4d(sK + j * kv_chunk, &p.tmK, kv_full, j * 64, 0, head, nk);
               tma_load_4d(sV + j * kv_chunk, &p.tmV, kv_full, j * 64, 0, head, nk);
             }
           }
-          mbar_expect_tx(t_full, (uint32_t)(3 * p.dch + (recompute ? 0 : p.kch2)) * 16384u);
-          for (int j = 0; j < p.dch; ++j) {
-            tma_load_4d(sQ + j * 16384, &p.tmQ, t_full, j * 64, t * 128, head, n);
-            tma_load_4d(sDO + j * 16384, &p.tmDO, t_full, j * 64, t * 128, head, n);
-            tma_load_4d(sO + j * 16384, &p.tmO, t_full, j * 64, t * 128, head, n);
-          }
-          if (!recompute)
-            for (int c = 0; c < p.kch2; ++c) tma_load_4d(sP + c * 16384, &p.tmP, t_full, c * 64, t * 128, head, n);
         }
       }
     }
@@ -112,9 +124,10 @@ __global__ void __launch_bounds__(kThreads, 1) attn_bwd_kernel(const __grid_cons
       for (int it = blockIdx.x; it < p.items; it += gridDim.x, ++items) {
         mbar_wait(kv_full, items & 1);
         for (int t = 0; t < p.qtiles; ++t, ++tiles) {
-          mbar_wait(t_full, tiles & 1);
+          mbar_wait(t_full(tiles), tpar(tiles));
           if (tiles > 0) mbar_wait(acc_read, (tiles - 1) & 1);      // dQ (and, across items, dK / dV) drained from TMEM
           tc_fence_after();
+          const uint32_t bo = (tiles % p.nbuf) * p.tile_bytes, sQ = sQ0 + bo, sDO = sDO0 + bo;
           if (recompute) {
             // S = Q_t K^T into the dP columns; the four warps turn it into the bf16 P tile in shared memory, then dP may overwrite it
             for (int j = 0; j < p.dch; ++j) {
@@ -152,7 +165,7 @@ __global__ void __launch_bounds__(kThreads, 1) attn_bwd_kernel(const __grid_cons
             for (int kq = 0; kq < 8; ++kq)
               umma_bf16(tmem_base + p.col_k + h * p.d, umma_desc(sP + (2 * h) * 16384 + kq * 2048, 16384, 1024),
                         umma_desc(sQ + kq * 2048, 16384, 1024), idesc_tt, (t | kq) != 0 ? 1u : 0u);
-          umma_commit(post_full);
+          umma_commit(post_full(tiles));
         }
       }
     }
@@ -170,7 +183,8 @@ __global__ void __launch_bounds__(kThreads, 1) attn_bwd_kernel(const __grid_cons
         const bool valid = q < p.L;
         // D_i = dO_i . O_i (fp32) from the two tiles in shared memory (rows of 128 B, same swizzle, so 16-byte units pair up);
         // reading them from global memory here put a full load latency on the serial chain of every tile
-        mbar_wait(t_full, tiles & 1);
+        mbar_wait(t_full(tiles), tpar(tiles));
+        const uint32_t bo = (tiles % p.nbuf) * p.tile_bytes, sDO = sDO0 + bo, sO = sO0 + bo;
         float D = 0.f;
         for (int j = 0; j < p.dch; ++j) {
           const uint32_t ro = sO + (uint32_t)j * 16384u + (uint32_t)r * 128u, rd = sDO + (uint32_t)j * 16384u + (uint32_t)r * 128u;
@@ -232,7 +246,7 @@ __global__ void __launch_bounds__(kThreads, 1) attn_bwd_kernel(const __grid_cons
         fence_proxy_async();
         __syncwarp();
         if (lane == 0) mbar_arrive(ds_ready);
-        mbar_wait(post_full, tiles & 1);
+        mbar_wait(post_full(tiles), tpar(tiles));
         tc_fence_after();
         // dQ rows of this tile
         for (int c = 0; c < p.d / 32 + ((p.d & 31) ? 1 : 0); ++c) {
@@ -324,7 +338,11 @@ extern "C" int b3d_attn_bwd(const void* qkv, const void* probs, int64_t ld_probs
   p.dch = (d + 63) / 64; p.kch2 = p.Lb2 / 64;
   p.dqkv = reinterpret_cast<bf16*>(dqkv);
   const uint32_t kv_bytes = (uint32_t)p.dch * (uint32_t)p.Lb2 * 128u, qd_bytes = (uint32_t)p.dch * 16384u;
-  p.off_k = 0; p.off_v = kv_bytes; p.off_q = 2 * kv_bytes; p.off_do = p.off_q + qd_bytes; p.off_o = p.off_do + qd_bytes; p.off_p = p.off_o + qd_bytes;
+  // two sets of per-tile operand buffers when P is recomputed (no P load to wait for) and they fit beside K, V and the P / dS tile
+  p.tile_bytes = 3 * qd_bytes;
+  p.nbuf = (lse != nullptr && (size_t)2 * kv_bytes + 2 * (size_t)p.tile_bytes + (size_t)p.kch2 * 16384 + 1024 <= 227 * 1024) ? 2 : 1;
+  p.off_k = 0; p.off_v = kv_bytes; p.off_q = 2 * kv_bytes; p.off_do = p.off_q + qd_bytes; p.off_o = p.off_do + qd_bytes;
+  p.off_p = p.off_q + (uint32_t)p.nbuf * p.tile_bytes;
   p.col_k = (uint32_t)p.Lb2; p.col_v = (uint32_t)(p.Lb2 + (p.Lb2 / 128) * d);
   const uint32_t ones[4] = {1, 1, 1, 1};
   b3d_view4 v;

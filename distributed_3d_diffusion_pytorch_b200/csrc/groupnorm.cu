@@ -248,6 +248,8 @@ struct BwdP {
   float* dgamma; float* dbeta;      // fp32 [C], accumulated
   float* dss_sum;                   // optional fp32 [2F]: column sums of dss (the FiLM dense bias gradient)
   float* dx_sum;                    // optional fp32 [C]: column sums of dx before the addends (the producer's bias gradient)
+  float* out_sum0; float* out_sum1; // optional fp32 [C0] / [C1]: out_sum_scale * column sums of the values STORED to dx0 / dx1 (addends included):
+  float out_sum_scale;              //   when this call completes the gradient of a block's output, that is the block's output-bias gradient
   float* ws;                        // [N,32,2] (S1, S2), pre-zeroed
   // pass 2 outputs
   bf16* dx0; bf16* dx1; long long ld_dx0, ld_dx1;
@@ -389,9 +391,9 @@ __device__ __forceinline__ void bwd_apply_body(const BwdP& p, int rows_per_block
   const int rows_par = max(1, (int)blockDim.x / vecs);
   const int v = threadIdx.x % vecs, rsub = threadIdx.x / vecs, c0 = v * 8;
   const bool active = rsub < rows_par;
-  float acc[8];
+  float acc[8], acco[8];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+  for (int j = 0; j < 8; ++j) { acc[j] = 0.f; acco[j] = 0.f; }
   if (active) {
     Aff ch; load_aff(ch, p.gamma, p.beta, c0, cpg, s_mean, s_rstd);
     float k1[8], k0[8];
@@ -437,6 +439,7 @@ __device__ __forceinline__ void bwd_apply_body(const BwdP& p, int rows_per_block
           const float g = fmaf(dz[j], ch.a[j], fmaf(f[j], k1[j], k0[j]));
           acc[j] += g;
           d[j] = fmaf(t0[j], p.add0_scale, g) + t1[j];
+          acco[j] += d[j];
         }
         *reinterpret_cast<bf16x8*>(dxp + row * ld_dx + c1) = b3d_pack8(d);
       }
@@ -445,6 +448,13 @@ __device__ __forceinline__ void bwd_apply_body(const BwdP& p, int rows_per_block
   if (p.dx_sum) {
     block_sum8(acc, active, v, rsub, rows_par, C, sm, sm + 2048);
     for (int c = threadIdx.x; c < C; c += blockDim.x) atomicAdd(&p.dx_sum[c], sm[2048 + c]);
+  }
+  if (p.out_sum0 != nullptr || p.out_sum1 != nullptr) {
+    block_sum8(acco, active, v, rsub, rows_par, C, sm, sm + 2048);
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+      float* dst = c < p.s.C0 ? (p.out_sum0 ? p.out_sum0 + c : nullptr) : (p.out_sum1 ? p.out_sum1 + (c - p.s.C0) : nullptr);
+      if (dst != nullptr) atomicAdd(dst, sm[2048 + c] * p.out_sum_scale);
+    }
   }
 }
 template <int MODE>
@@ -683,7 +693,8 @@ extern "C" int b3d_gn_bwd(const void* x0, int C0, int64_t ld0, const void* x1, i
                           int F, void* dss, int64_t ld_dss, float drop_p, uint64_t seed, const uint64_t* seed_ptr, float* dgamma, float* dbeta,
                           float* dss_sum, float* dx_sum, float* ws_s12,
                           void* dx0, int64_t ld_dx0, void* dx1, int64_t ld_dx1, const void* add0, int64_t ld_add0, const void* add1a,
-                          int64_t ld_add1a, const void* add1b, int64_t ld_add1b, float add0_scale, void* stream) {
+                          int64_t ld_add1a, const void* add1b, int64_t ld_add1b, float add0_scale, float* out_sum0, float* out_sum1, float out_sum_scale,
+                          void* stream) {
   if (int rc = check_src(x0, C0, x1, C1)) return rc;
   B3D_CHECK_ARG(mode >= 0 && mode <= 2, "gn_bwd: mode");
   B3D_CHECK_ARG(mode != 2 || (ss && dss && F == C0 + C1), "gn_bwd: film needs ss, dss, F == C");
@@ -695,6 +706,7 @@ extern "C" int b3d_gn_bwd(const void* x0, int C0, int64_t ld0, const void* x1, i
   p.dgamma = dgamma; p.dbeta = dbeta; p.ws = ws_s12; p.dss_sum = dss_sum; p.dx_sum = dx_sum;
   p.dx0 = (bf16*)dx0; p.dx1 = (bf16*)dx1; p.ld_dx0 = ld_dx0; p.ld_dx1 = ld_dx1;
   p.add0 = (const bf16*)add0; p.ld_add0 = ld_add0; p.add0_scale = add0_scale;
+  p.out_sum0 = out_sum0; p.out_sum1 = out_sum1; p.out_sum_scale = out_sum_scale;
   p.add1a = (const bf16*)add1a; p.add1b = (const bf16*)add1b; p.ld_add1a = ld_add1a; p.ld_add1b = ld_add1b;
   const int C = C0 + C1;
   cudaStream_t st = (cudaStream_t)stream;

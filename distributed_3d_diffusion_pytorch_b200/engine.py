@@ -93,8 +93,11 @@ def build_plan(cfg):
 class Act:
     """an activation tensor [N, h, w, C] with its (lazily created) gradient buffer"""
 
-    def __init__(self, t, key):
+    def __init__(self, t, key, bias=None):
         self.t, self.key, self.has_grad = t, key, False
+        # bias: name of the output bias of the block that produced this tensor through a (value + residual) / sqrt(2) epilogue;
+        # its gradient = column sums of d(this tensor) / sqrt(2), taken by whichever GroupNorm backward completes that gradient
+        self.bias, self.uses, self.left, self.bias_done = bias, 0, 0, False
 
 
 class Engine:
@@ -395,7 +398,9 @@ class Engine:
                 hs.append(h)
             elif kind == "pop":
                 skip = hs.pop()
+                skip.uses += 1
             elif kind == "res":
+                h.uses += 1
                 if s.lvl >= 1 or not self._needed_first(s.name):
                     ops.join_side()            # FiLM operands of the coarser levels, the second weight-pack launch (no-op once joined)
                 h = self._res_fwd(s, h, skip if s.cat else None, ss[s.lvl], P, Wp, drop_p, seed * 1000 + bi)
@@ -403,8 +408,10 @@ class Engine:
                 bi += 1
             else:
                 ops.join_side()
+                h.uses += 1
                 h = self._attn_fwd(s, h, P, Wp)
         assert not hs
+        h.uses += 1          # the head
         ops.join_side()
 
         # ---- head (xunet.py:535-536)
@@ -468,7 +475,7 @@ class Engine:
             assert skip is None
             ops.gemm(G.conv_desc([a1.view(N, hh, ww, F)], [9], Wp[n + ".conv2.weight"], F, out, bias=P[n + ".conv2.bias"], resid=h_in.t,
                                  out_scale=RSQRT2))
-        o = Act(out, n + ".out")
+        o = Act(out, n + ".out", bias=n + ".conv2.bias")
         self.saved["acts"][n] = dict(h_in=h_in, skip=skip, sums0=sums0, a0=a0, c1=c1, sums1=sums1, a1=a1, out=o, seed=seed)
         if s.resample == "down":
             r = self.buf(n + ".rs", (N, hh // 2, ww // 2, F))
@@ -520,7 +527,7 @@ class Engine:
         out = self.buf(n + ".out", (N, hh, ww, C))
         ops.gemm(G.dense_desc(o1, Wp[n + ".linear.weight"], out.view(N * L, C), C, bias=P[n + ".linear.bias"], resid=h_in.t.view(N * L, C),
                               out_scale=RSQRT2))
-        oa = Act(out, n + ".out")
+        oa = Act(out, n + ".out", bias=n + ".linear.bias")
         self.saved["acts"][n] = dict(h_in=h_in, sums=sums, g=g, qkv=qkv, p=p, lse=lse, o=o, o1=o1, out=oa)
         return oa
 
@@ -562,7 +569,7 @@ class Engine:
             for g in Gr.values():
                 g.zero_()
         for a in self._all_acts():
-            a.has_grad = False
+            a.has_grad, a.left, a.bias_done = False, a.uses, False
         self._dss = [self.buf(f"dss{l}", (N * (H >> l) * (Wd >> l), self.film_cols[l])) for l in range(cfg.num_resolutions)]
 
         # ---- head
@@ -578,11 +585,10 @@ class Engine:
         self._conv_wgrad("lastconv.weight", dy, al.view(N, H, Wd, C), Gr["lastconv.weight"], co_alloc=16)
         da = self.buf("lastgn.da", (N, H, Wd, C))
         ops.gemm(G.conv_desc([dy], [9], Wp["lastconv.weight.T"], C, da))
-        dh = self._grad_of(h)
+        dh, _ = self._take_grad(h)
         ops.gn_bwd(h.t.view(N, HW, C), None, self.zbuf("fwd", "lastgn.sums", (N, 32, 2)), P["lastgn.gn.weight"], P["lastgn.gn.bias"], 1,
                    da.view(N, HW, C), Gr["lastgn.gn.weight"], Gr["lastgn.gn.bias"], self.zbuf("bwd", "lastgn.ws", (N, 32, 2)),
-                   dh.view(N, HW, C))
-        h.has_grad = True
+                   dh.view(N, HW, C), out_sum0=self._bias_sum(h, Gr), out_sum_scale=RSQRT2)
 
         self._bwd_blocks(Gr, lambda name: name.startswith("upsample."))
         self._film_wgrad(Gr, lambda name: name.startswith("upsample."))
@@ -707,7 +713,16 @@ class Engine:
         g = self._grad_of(act)
         had = act.has_grad
         act.has_grad = True
+        act.left -= 1
         return g, (g if had else None)
+
+    def _bias_sum(self, act, Gr):
+        """the bias-gradient tensor that the GroupNorm backward writing `act`'s gradient should accumulate the column sums of its
+        output into: set when that write is the last contribution (the gradient is then complete), else None"""
+        if act.bias is None or act.left != 0:
+            return None
+        act.bias_done = True
+        return Gr[act.bias]
 
     def _res_bwd(self, s, P, Wp, Gr, dss_l, drop_p):
         ops, N, n = self.ops, self.N, s.name
@@ -731,7 +746,8 @@ class Engine:
         # weight gradients of conv2 and the 1x1 skip, d(conv2.bias): on the side stream, beside the data-gradient chain below
         # (they only read dout and saved activations)
         with ops.side():
-            ops.colsum(dout2, M, Gr[n + ".conv2.bias"], scale=RSQRT2)
+            if not out.bias_done:      # (else the GroupNorm backward that completed dout has already summed its columns)
+                ops.colsum(dout2, M, Gr[n + ".conv2.bias"], scale=RSQRT2)
             self._conv_wgrad(n + ".conv2.weight", dout, sa["a1"].view(N, hh, ww, F), Gr[n + ".conv2.weight"], alpha=RSQRT2)
             if s.cin != F:
                 gw = Gr[n + ".dense.weight"].view(F, s.cin)
@@ -785,7 +801,8 @@ class Engine:
         v3 = lambda t_: t_.view(N, HW, -1) if t_ is not None else None
         ops.gn_bwd(x0, x1, sa["sums0"], P[n + ".groupnorm0.gn.weight"], P[n + ".groupnorm0.gn.bias"], 1, da0.view(N, HW, s.cin),
                    Gr[n + ".groupnorm0.gn.weight"], Gr[n + ".groupnorm0.gn.bias"], self.zbuf("bwd", n + ".ws0", (N, 32, 2)), v3(g0), v3(g1),
-                   add0=add0, add1a=v3(e0), add1b=v3(e1), add0_scale=add0_scale)
+                   add0=add0, add1a=v3(e0), add1b=v3(e1), add0_scale=add0_scale, out_sum0=self._bias_sum(h_in, Gr),
+                   out_sum1=self._bias_sum(skip, Gr) if skip is not None else None, out_sum_scale=RSQRT2)
         self._block_join()
 
     def _attn_bwd(self, s, P, Wp, Gr):
@@ -801,7 +818,8 @@ class Engine:
         gs = dout.view(M, C)      # the (h + h_in) / sqrt(2) of xunet.py:220 is folded into the consumers of dout (see _res_bwd)
         # 1x1 `linear` and out_proj
         with ops.side():      # parameter gradients run beside the data-gradient chain (joined at the end of the block)
-            ops.colsum(gs, M, Gr[n + ".linear.bias"], scale=RSQRT2)
+            if not out.bias_done:
+                ops.colsum(gs, M, Gr[n + ".linear.bias"], scale=RSQRT2)
             ops.gemm(G.wgrad_dense_desc(gs, sa["o1"], Gr[n + ".linear.weight"].view(C, C), alpha=RSQRT2))
         do1 = self.side_tmp(n, "do1", (M, C))
         ops.gemm(G.dense_desc(gs, Wp[n + ".linear.weight.T"], do1, C, alpha=RSQRT2))
@@ -842,5 +860,6 @@ class Engine:
         g0, e0 = self._take_grad(h_in)
         ops.gn_bwd(h_in.t.view(N, L, C), None, sa["sums"], P[n + ".groupnorm.gn.weight"], P[n + ".groupnorm.gn.bias"], 0, dg,
                    Gr[n + ".groupnorm.gn.weight"], Gr[n + ".groupnorm.gn.bias"], self.zbuf("bwd", n + ".ws", (N, 32, 2)),
-                   g0.view(N, L, C), None, add0=gs.view(N, L, C), add1a=e0.view(N, L, C) if e0 is not None else None, add0_scale=RSQRT2)
+                   g0.view(N, L, C), None, add0=gs.view(N, L, C), add1a=e0.view(N, L, C) if e0 is not None else None, add0_scale=RSQRT2,
+                   out_sum0=self._bias_sum(h_in, Gr), out_sum_scale=RSQRT2)
         self._block_join()

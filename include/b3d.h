@@ -181,7 +181,9 @@ int b3d_softmax_bwd(const void* P, int64_t ld_p, const void* dP, int dp_fp32, in
  *   uses ws_s12 fp32 [N,32,2] (caller zeroes it), writes dx0/dx1 (+ add0_scale * add0 + add1a/add1b when given: the
  *   residual branch's gradient joins here with its 1/sqrt2, xunet.py:152,220).  Optional fused
  *   reductions (fp32, accumulated): dss_sum [2F] = column sums of dss (FiLM dense bias gradient, xunet.py:80),
- *   dx_sum [C] = column sums of dx before the addends (bias gradient of the layer that produced x). */
+ *   dx_sum [C] = column sums of dx before the addends (bias gradient of the layer that produced x),
+ *   out_sum0 [C0] / out_sum1 [C1] = out_sum_scale * column sums of the values stored to dx0 / dx1, addends included (when the
+ *   call completes the gradient of a block's output: that block's output-bias gradient, xunet.py:146,217 with the 1/sqrt2). */
 int b3d_gn_stats(const void* x0, int C0, int64_t ld0, const void* x1, int C1, int64_t ld1, int N, int HW, float* ws_sums, void* stream);
 int b3d_gn_apply(const void* x0, int C0, int64_t ld0, const void* x1, int C1, int64_t ld1, int N, int HW, const float* sums,
                  const float* gamma, const float* beta, int mode, const void* ss, int64_t ld_ss, int F, float drop_p, uint64_t seed, const uint64_t* seed_ptr,
@@ -205,7 +207,7 @@ int b3d_gn_bwd(const void* x0, int C0, int64_t ld0, const void* x1, int C1, int6
                void* dss, int64_t ld_dss, float drop_p, uint64_t seed, const uint64_t* seed_ptr, float* dgamma, float* dbeta, float* dss_sum,
                float* dx_sum, float* ws_s12, void* dx0,
                int64_t ld_dx0, void* dx1, int64_t ld_dx1, const void* add0, int64_t ld_add0, const void* add1a, int64_t ld_add1a,
-               const void* add1b, int64_t ld_add1b, float add0_scale, void* stream);
+               const void* add1b, int64_t ld_add1b, float add0_scale, float* out_sum0, float* out_sum1, float out_sum_scale, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Diffusion glue (fp32 NCHW, as the reference holds these tensors)

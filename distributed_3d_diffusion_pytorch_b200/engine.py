@@ -98,6 +98,7 @@ class Act:
         # bias: name of the output bias of the block that produced this tensor through a (value + residual) / sqrt(2) epilogue;
         # its gradient = column sums of d(this tensor) / sqrt(2), taken by whichever GroupNorm backward completes that gradient
         self.bias, self.uses, self.left, self.bias_done = bias, 0, 0, False
+        self.sums = None     # GroupNorm (sum, sumsq) [N,32,2] of this tensor at C/32 channels per group, when its producer's epilogue took them
 
 
 class Engine:
@@ -157,6 +158,13 @@ class Engine:
             d.gn_cpg = d.gn_rows_per_image = 0
         self.ops.gemm(d)
         return ok
+
+    def _producer_stats(self, d, act, C, rows_per_image=0):
+        """launch the GEMM that produces `act`; when its epilogue can, it also leaves the GroupNorm statistics of the output in
+        act.sums, so that a single-source GroupNorm reading `act` skips its statistics pass"""
+        sums = self.zbuf("fwd", act.key + ".osum", (self.N, 32, 2))
+        if self._gemm_stats(d, sums, C, rows_per_image):
+            act.sums = sums
 
     def zbuf(self, phase, key, shape):
         """fp32 scratch that must be zero at the start of the phase: carved from one arena, one memset per phase"""
@@ -390,7 +398,7 @@ class Engine:
         xin = self.buf("xin", (N, H, Wd, 8))
         ops.pack_input(x, z, xin)
         h = Act(self.buf("stem", (N, H, Wd, cfg.ch)), "stem")
-        ops.gemm(G.conv_desc([xin], [9], Wp["conv.weight"], cfg.ch, h.t, bias=P["conv.bias"]))
+        self._producer_stats(G.conv_desc([xin], [9], Wp["conv.weight"], cfg.ch, h.t, bias=P["conv.bias"]), h, cfg.ch)
 
         hs, skip, bi = [], None, 0
         for kind, s in self.plan:
@@ -450,9 +458,13 @@ class Engine:
         HW, F = hh * ww, s.f
         x0 = h_in.t.view(N, HW, -1)
         x1 = skip.t.view(N, HW, -1) if skip is not None else None
-        sums0 = self.zbuf("fwd", n + ".s0", (N, 32, 2))
         a0 = self.buf(n + ".a0", (N, HW, s.cin))
-        ops.gn_stats_apply(x0, x1, sums0, P[n + ".groupnorm0.gn.weight"], P[n + ".groupnorm0.gn.bias"], 1, a0)
+        if skip is None and h_in.sums is not None:      # statistics already taken by the epilogue of the GEMM that produced h_in
+            sums0 = h_in.sums
+            ops.gn_apply(x0, None, sums0, P[n + ".groupnorm0.gn.weight"], P[n + ".groupnorm0.gn.bias"], 1, a0)
+        else:
+            sums0 = self.zbuf("fwd", n + ".s0", (N, 32, 2))
+            ops.gn_stats_apply(x0, x1, sums0, P[n + ".groupnorm0.gn.weight"], P[n + ".groupnorm0.gn.bias"], 1, a0)
         c1 = self.buf(n + ".c1", (N, hh, ww, F))
         sums1 = self.zbuf("fwd", n + ".s1", (N, 32, 2))
         c13 = c1.view(N, HW, F)
@@ -469,13 +481,17 @@ class Engine:
             # tensor): one launch, and its output never goes through HBM to come back as the residual.  Its bias enters as
             # a per-image vector with image stride 0.
             srcs = [a1.view(N, hh, ww, F), h_in.t] + ([skip.t] if skip is not None else [])
-            ops.gemm(G.conv_desc(srcs, [9] + [1] * (len(srcs) - 1), Wp[n + ".conv2+dense"], F, out, bias=P[n + ".conv2.bias"],
-                                 rowvec=P[n + ".dense.bias"].view(1, F).expand(N, F), out_scale=RSQRT2))
+            d2 = G.conv_desc(srcs, [9] + [1] * (len(srcs) - 1), Wp[n + ".conv2+dense"], F, out, bias=P[n + ".conv2.bias"],
+                             rowvec=P[n + ".dense.bias"].view(1, F).expand(N, F), out_scale=RSQRT2)
         else:
             assert skip is None
-            ops.gemm(G.conv_desc([a1.view(N, hh, ww, F)], [9], Wp[n + ".conv2.weight"], F, out, bias=P[n + ".conv2.bias"], resid=h_in.t,
-                                 out_scale=RSQRT2))
+            d2 = G.conv_desc([a1.view(N, hh, ww, F)], [9], Wp[n + ".conv2.weight"], F, out, bias=P[n + ".conv2.bias"], resid=h_in.t,
+                             out_scale=RSQRT2)
         o = Act(out, n + ".out", bias=n + ".conv2.bias")
+        if s.resample is None:
+            self._producer_stats(d2, o, F)        # (a resampled output is normalised after the resampling: no use for these)
+        else:
+            ops.gemm(d2)
         self.saved["acts"][n] = dict(h_in=h_in, skip=skip, sums0=sums0, a0=a0, c1=c1, sums1=sums1, a1=a1, out=o, seed=seed)
         if s.resample == "down":
             r = self.buf(n + ".rs", (N, hh // 2, ww // 2, F))
@@ -501,9 +517,13 @@ class Engine:
         d = C // Hh
         a = n + ".attn_layer.attn"
         x3 = h_in.t.view(N, L, C)
-        sums = self.zbuf("fwd", n + ".s", (N, 32, 2))
         g = self.buf(n + ".g", (N, L, C))
-        ops.gn_stats_apply(x3, None, sums, P[n + ".groupnorm.gn.weight"], P[n + ".groupnorm.gn.bias"], 0, g)
+        if h_in.sums is not None:
+            sums = h_in.sums
+            ops.gn_apply(x3, None, sums, P[n + ".groupnorm.gn.weight"], P[n + ".groupnorm.gn.bias"], 0, g)
+        else:
+            sums = self.zbuf("fwd", n + ".s", (N, 32, 2))
+            ops.gn_stats_apply(x3, None, sums, P[n + ".groupnorm.gn.weight"], P[n + ".groupnorm.gn.bias"], 0, g)
         qkv = self.buf(n + ".qkv", (N, L, 3 * C))
         ops.gemm(G.dense_desc(g.view(N * L, C), Wp[a + ".in_proj_weight"], qkv.view(N * L, 3 * C), 3 * C, bias=P[a + ".in_proj_bias"]))
         q, k, v = self._qkv_views(qkv, L, C)
@@ -525,9 +545,9 @@ class Engine:
         o1 = self.buf(n + ".o1", (N * L, C))
         ops.gemm(G.dense_desc(o.view(N * L, C), Wp[a + ".out_proj.weight"], o1, C, bias=P[a + ".out_proj.bias"]))
         out = self.buf(n + ".out", (N, hh, ww, C))
-        ops.gemm(G.dense_desc(o1, Wp[n + ".linear.weight"], out.view(N * L, C), C, bias=P[n + ".linear.bias"], resid=h_in.t.view(N * L, C),
-                              out_scale=RSQRT2))
         oa = Act(out, n + ".out", bias=n + ".linear.bias")
+        self._producer_stats(G.dense_desc(o1, Wp[n + ".linear.weight"], out.view(N * L, C), C, bias=P[n + ".linear.bias"],
+                                          resid=h_in.t.view(N * L, C), out_scale=RSQRT2), oa, C, rows_per_image=L)
         self.saved["acts"][n] = dict(h_in=h_in, sums=sums, g=g, qkv=qkv, p=p, lse=lse, o=o, o1=o1, out=oa)
         return oa
 

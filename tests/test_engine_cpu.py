@@ -12,7 +12,7 @@ from oracle import diffusion_ref as dr
 from oracle import xunet_ref as xr
 
 
-def _run(name, training_dropout=False):
+def _run(name, training_dropout=False, fuse_stats=False):
     G = load_golden(name)
     kw = G["kw"]
     cfg = Cfg(**kw)
@@ -23,6 +23,7 @@ def _run(name, training_dropout=False):
     B = img.shape[0]
     x_cond = torch.where(cm[:, None, None, None], img[:, 0], G["x_replace"])
     eng = Engine(cfg, EmuOps(), B)
+    eng.fuse_stats = fuse_stats        # GroupNorm statistics from the producing GEMM's epilogue wherever it can take them
     eps = eng.forward(sd, x_cond, G["z_noisy"], G["batch_logsnr"], G["R"], G["T"], G["K"], cm, training=False, need_bwd=True)
     assert (eps - G["eps"]).abs().max() < 5e-5, (eps - G["eps"]).abs().max()
     n = G["noise"].numel()
@@ -51,6 +52,22 @@ def test_engine_orchestration_tiny16():
 
 def test_engine_orchestration_tiny24():
     _run("tiny24")
+
+
+def test_engine_orchestration_with_epilogue_statistics():
+    from distributed_3d_diffusion_pytorch_b200 import engine as E
+    taken, orig = [], E.Engine._gemm_stats
+
+    def spy(self, d, sums, C, rows_per_image=0):
+        ok = orig(self, d, sums, C, rows_per_image)
+        taken.append(ok)
+        return ok
+    E.Engine._gemm_stats = spy
+    try:
+        _run("small16", fuse_stats=True)
+    finally:
+        E.Engine._gemm_stats = orig
+    assert sum(taken) >= 20, (sum(taken), len(taken))          # conv1, conv2 / attention-linear producers with >= 4 channels per group
 
 
 def test_cached_conditioning_forward_equals_uncached():

@@ -353,7 +353,7 @@ __global__ void __launch_bounds__(256) silu_bwd_colsum_kernel(const bf16* dy, co
         const long long rr = r + (long long)u * rows_par;
         if (rr < r1) {
           a[u].u = reinterpret_cast<const bf16x8*>(dy + base + rr * C)->u;
-          b[u].u = reinterpret_cast<const bf16x8*>(x + base + rr * C)->u;
+          if (x != nullptr) b[u].u = reinterpret_cast<const bf16x8*>(x + base + rr * C)->u;
         }
       }
 #pragma unroll
@@ -361,10 +361,15 @@ __global__ void __launch_bounds__(256) silu_bwd_colsum_kernel(const bf16* dy, co
         const long long rr = r + (long long)u * rows_par;
         if (rr >= r1) break;
         float f[8], z[8];
-        b3d_unpack8(a[u], f); b3d_unpack8(b[u], z);
+        b3d_unpack8(a[u], f);
+        if (x != nullptr) {
+          b3d_unpack8(b[u], z);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) { f[j] *= b3d_silu_grad(z[j]); acc[j] += f[j]; }
-        *reinterpret_cast<bf16x8*>(dx + base + rr * C) = b3d_pack8(f);
+          for (int j = 0; j < 8; ++j) f[j] *= b3d_silu_grad(z[j]);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += f[j];
+        if (dx != nullptr) *reinterpret_cast<bf16x8*>(dx + base + rr * C) = b3d_pack8(f);
       }
     }
 #pragma unroll
@@ -927,7 +932,8 @@ extern "C" int b3d_silu_bwd(const void* dy, const void* x, void* dx, int64_t n, 
 }
 extern "C" int b3d_silu_bwd_colsum(const void* dy, const void* x, void* dx, int C, int64_t rows_per_group, int groups, float* group_out,
                                    int64_t group_ld, float* total_out, void* stream) {
-  B3D_CHECK_ARG(dy && x && dx && C % 8 == 0 && C <= 2048 && rows_per_group > 0 && groups > 0, "silu_bwd_colsum: args (C %% 8, C <= 2048)");
+  B3D_CHECK_ARG(dy && ((x && dx) || (!x && !dx)) && C % 8 == 0 && C <= 2048 && rows_per_group > 0 && groups > 0,
+                "silu_bwd_colsum: args (C %% 8, C <= 2048; x and dx both or neither)");
   const int rows_par = 256 / (C / 8) > 0 ? 256 / (C / 8) : 1;
   const int min_rows = rows_par * 4;
   long long rpb = cdiv(rows_per_group * groups, 148LL * 8);

@@ -502,7 +502,11 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
               const uint4 q = lds128(xrow + ((((uint32_t)(hf * 4 + g)) ^ swz) << 4));
               const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&q);
 #pragma unroll
-              for (int i = 0; i < 4; ++i) { const float2 t2 = __bfloat1622float2(h2[i]); f[8 * g + 2 * i] += t2.x; f[8 * g + 2 * i + 1] += t2.y; }
+              for (int i = 0; i < 4; ++i) {
+                const float2 t2 = __bfloat1622float2(h2[i]);
+                if (p.act == 2) { f[8 * g + 2 * i] *= b3d_silu_grad(t2.x); f[8 * g + 2 * i + 1] *= b3d_silu_grad(t2.y); }   // resid = pre-activation
+                else { f[8 * g + 2 * i] += t2.x; f[8 * g + 2 * i + 1] += t2.y; }
+              }
             }
           }
 #pragma unroll
@@ -651,11 +655,11 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
                 bf16x8 pk = *reinterpret_cast<const bf16x8*>(rp + g * 8);
                 float t8[8]; b3d_unpack8(pk, t8);
 #pragma unroll
-                for (int i = 0; i < 8; ++i) f[g * 8 + i] += t8[i];
+                for (int i = 0; i < 8; ++i) { if (p.act == 2) f[g * 8 + i] *= b3d_silu_grad(t8[i]); else f[g * 8 + i] += t8[i]; }
               }
             } else {
 #pragma unroll
-              for (int i = 0; i < 32; ++i) if (i < ncol) f[i] += __bfloat162float(rp[i]);
+              for (int i = 0; i < 32; ++i) if (i < ncol) { if (p.act == 2) f[i] *= b3d_silu_grad(__bfloat162float(rp[i])); else f[i] += __bfloat162float(rp[i]); }
             }
           }
 #pragma unroll
@@ -1018,6 +1022,7 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
   p.os_x = d->out_stride[0]; p.os_y = d->out_stride[1]; p.os_n = d->out_stride[2]; p.os_tap = d->out_tap_stride;
   p.alpha = d->alpha; p.out_scale = d->out_scale; p.act = d->act; p.out_fp32 = d->out_fp32; p.out_atomic = d->out_atomic;
   B3D_CHECK_ARG(!d->out_atomic || d->out_fp32, "b3d_gemm: out_atomic needs fp32 output");
+  B3D_CHECK_ARG(d->act != 2 || (d->resid != nullptr && !d->out_fp32 && d->out2 == nullptr), "b3d_gemm: act 2 (times silu'(resid)) needs resid, a bf16 output and no out2");
 
   const size_t smem = (size_t)p.num_stages * p.stage_bytes + epi_bytes + 1024;
   static bool attr_set = false;

@@ -678,9 +678,11 @@ class Engine:
             M = N * hh * ww
             pre = self._bufs[f"emb_pre{l}"]
             de = self.buf(f"de{l}", (N, hh, ww, E))
-            ops.gemm(G.dense_desc(dss[l], Wp[f"film{l}.T"], de.view(M, E), E))
-            # silu'(pre) and, from the same pass, d(logsnr_emb) per image and the conv's bias gradient
-            ops.silu_bwd_colsum(de, pre, de, hh * ww, dlemb, Gr[cp + f"convs.{l}.bias"])
+            # the FiLM data-gradient GEMM multiplies by silu'(pre) in its epilogue (pre arrives as the residual tile): the gradient
+            # of the conditioning conv's output is written once; d(logsnr_emb) per image and the conv's bias gradient are its
+            # column sums, one read
+            ops.gemm(G.dense_desc(dss[l], Wp[f"film{l}.T"], de.view(M, E), E, resid=pre.view(M, E), act=2))
+            ops.silu_bwd_colsum(de, None, None, hh * ww, dlemb, Gr[cp + f"convs.{l}.bias"])
             with ops.side():
                 gp = self.zbuf("bwd", f"cc{l}.gp", (E, 9 * 192))
                 ops.gemm(G.wgrad_desc(de, pe, 9, gp, 0, 192, 2 ** l))

@@ -386,10 +386,11 @@ class CudaOps:
         self._call("b3d_silu_bwd", _ptr(dy), _ptr(x), _ptr(dx), c_i64(dy.numel()), self.stream())
 
     def silu_bwd_colsum(self, dy, x, dx, rows_per_group, group_out, total_out):
-        """dx = dy*silu'(x) on [rows, C] views; group_out [groups, C] += per-group column sums, total_out [C] += all rows"""
+        """dx = dy*silu'(x) on [rows, C] views; group_out [groups, C] += per-group column sums, total_out [C] += all rows.
+        x = dx = None: the two sums of dy alone"""
         C = dy.shape[-1]
         rows = dy.numel() // C
-        assert dy.is_contiguous() and x.is_contiguous() and dx.is_contiguous()
+        assert dy.is_contiguous() and (x is None) == (dx is None) and (x is None or (x.is_contiguous() and dx.is_contiguous()))
         self._call("b3d_silu_bwd_colsum", _ptr(dy), _ptr(x), _ptr(dx), c_i32(C), c_i64(rows_per_group), c_i32(rows // rows_per_group),
                    _ptr(group_out), c_i64(group_out.stride(0) if group_out is not None else 0), _ptr(total_out), self.stream())
 

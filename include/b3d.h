@@ -70,7 +70,8 @@ typedef struct b3d_gemm_desc {
   int64_t rowvec_ld;
   const void* resid;     /* bf16, addressed like out: value = (acc + bias + resid) * out_scale */
   float alpha, out_scale;
-  int32_t act;           /* 0 none, 1 silu */
+  int32_t act;           /* 0 none, 1 silu, 2: value = (acc + bias) * silu'(resid) * out_scale -- resid is then the pre-activation
+                          * whose SiLU the forward took (autograd of F.silu fused into the data-gradient GEMM, xunet.py:84) */
   int32_t out_atomic;    /* fp32 atomicAdd into out */
   int32_t bn_tile;       /* 0 = auto */
   /* Optional GroupNorm statistics of the bf16 output, taken in the epilogue (saves the consumer's b3d_gn_stats pass):
@@ -152,7 +153,8 @@ int b3d_avgpool2(const void* in, void* out, int N, int H, int W, int C, float sc
 int b3d_upsample2(const void* in, void* out, int N, int Ho, int Wo, int C, float scale, void* stream);
 /* dx = dy * silu'(x)  (autograd of F.silu, xunet.py:84) ; out = scale*(a+b) */
 int b3d_silu_bwd(const void* dy, const void* x, void* dx, int64_t n, void* stream);
-/* dx = dy * silu'(x) over contiguous [rows, C] plus, from the same pass, the column sums of dx per group of rows
+/* (x = NULL and dx = NULL: the two column sums of dy alone.)
+ * dx = dy * silu'(x) over contiguous [rows, C] plus, from the same pass, the column sums of dx per group of rows
  * (group_out[g*group_ld + c] +=, may be null) and over all rows (total_out[c] +=, may be null); fp32, pre-zeroed by the caller.
  * Autograd of F.silu(emb) (xunet.py:84) fused with d(logsnr_emb) (xunet.py:502) and the conditioning conv's bias gradient. */
 int b3d_silu_bwd_colsum(const void* dy, const void* x, void* dx, int C, int64_t rows_per_group, int groups, float* group_out,

@@ -167,7 +167,7 @@ class EmuOps:
             if rowvec is not None:
                 v = v + rowvec
             if resid is not None:
-                v = v + resid.float()
+                v = v * _silu_grad(resid.float()) if d.act == 2 else v + resid.float()
             v = v * d.out_scale
             if d.act == 1 and dst2 is None:
                 v = F.silu(v)
@@ -367,8 +367,9 @@ class EmuOps:
 
     def silu_bwd_colsum(self, dy, x, dx, rows_per_group, group_out, total_out):
         C = dy.shape[-1]
-        v = (dy.float() * _silu_grad(x.float())).reshape(-1, rows_per_group, C)
-        dx.copy_(v.reshape(dx.shape).to(dx.dtype))
+        v = (dy.float() * _silu_grad(x.float()) if x is not None else dy.float()).reshape(-1, rows_per_group, C)
+        if dx is not None:
+            dx.copy_(v.reshape(dx.shape).to(dx.dtype))
         if group_out is not None:
             group_out[:, :C].add_(v.sum(1))
         if total_out is not None:

@@ -207,6 +207,8 @@ def all_cases():
         conv_case("conv_fused_skip_3src", 2, 16, 16, [128, 64, 64], [9, 1, 1], 128, resid=False),
         conv_case("conv_partial_blocks_3src", 2, 16, 16, [88, 40, 72], [9, 1, 1], 128, rowvec=True),     # last 64-channel blocks with 2 / 3 / 1 real K steps
         conv_case("conv_c144_s1_pairwide", 4, 64, 64, [144], [9], 256),
+        conv_case("conv_silu_grad_of_resid", 2, 32, 32, [128], [1], 256, resid=True, act=2, bias=False),      # value * silu'(resid): the FiLM data gradient
+        conv_case("conv_silu_grad_of_resid_wide", 8, 64, 64, [512], [1], 1024, resid=True, act=2, bias=False),
         conv_case("conv_fp32out_alpha", 1, 16, 16, [64], [9], 64, fp32_out=True, alpha=0.5),
         wgrad_case("wgrad_dense_like", 1, 1, 4096, 256, 128, 1),
         wgrad_case("wgrad_16x16_c128_64", 2, 16, 16, 128, 64, 9),

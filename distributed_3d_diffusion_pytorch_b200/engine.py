@@ -119,6 +119,7 @@ class Engine:
         # attention backward: recompute P from the saved row log-sum-exp (no L x L tensor in HBM, 134 MB less per 16x16 block at
         # batch 128) instead of reading back the P the forward wrote; B3D_ATTN_SAVE_P=1 selects the latter (measurement switch)
         self.attn_recompute = os.environ.get("B3D_ATTN_SAVE_P") != "1"
+        self.fuse_bias = os.environ.get("B3D_NO_FUSE_BIAS") != "1"     # output-bias gradients inside the GroupNorm backward (measurement switch)
         self.seed_ptr = None      # optional int64 device scalar added to every dropout seed (see ops.gn_apply)
         for lvl in range(cfg.num_resolutions):
             assert cfg.H % (2 ** lvl) == 0 and cfg.W % (2 ** lvl) == 0
@@ -741,7 +742,7 @@ class Engine:
     def _bias_sum(self, act, Gr):
         """the bias-gradient tensor that the GroupNorm backward writing `act`'s gradient should accumulate the column sums of its
         output into: set when that write is the last contribution (the gradient is then complete), else None"""
-        if act.bias is None or act.left != 0:
+        if act.bias is None or act.left != 0 or not self.fuse_bias:
             return None
         act.bias_done = True
         return Gr[act.bias]

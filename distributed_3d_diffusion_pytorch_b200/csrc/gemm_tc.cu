@@ -950,6 +950,7 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
           Seg& sg = p.seg[p.nseg++];
           sg.src = i; sg.ncb = ncb; sg.bk0 = bk;
           { const int rem = d->a[i].dim[0] - (ncb - 1) * BK; sg.klast = (rem + 15) / 16; if (sg.klast < 1) sg.klast = 1; if (sg.klast > BK / 16) sg.klast = BK / 16; }
+          { static const bool no_ks = getenv("B3D_NO_KSTEPS") != nullptr; if (no_ks) sg.klast = BK / 16; }      // measurement switch
           sg.dx = taps == 9 ? (tp % 3) - d->pad : 0;
           sg.dy = taps == 9 ? (tp / 3) - d->pad : 0;
           bk += ncb * BK;

@@ -144,7 +144,7 @@ def misc_case(seed=0):
         ops.silu_bwd_colsum(fd, fx, fd, 50, fgo, fto)
         outs += [fd, fgo, fto]
         fgo2, fto2 = ops.zeros((6, 1024), torch.float32), ops.zeros((1024,), torch.float32)
-        ops.silu_bwd_colsum(fd, None, None, 50, fgo2, fto2)          # pure two-level column sums
+        ops.silu_bwd_colsum(fx, None, None, 50, fgo2, fto2)          # pure two-level column sums (of an input: bf16-exact on both sides)
         outs += [fgo2, fto2]
         ad = ops.zeros((64, 128)); ops.add_scale(a, b, ad, 0.7071); outs.append(ad)
         ad2 = ops.zeros((64, 128)); ops.add_scale(a, None, ad2, 0.5); outs.append(ad2)

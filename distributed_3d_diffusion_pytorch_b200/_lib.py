@@ -45,3 +45,8 @@ def set_gn_chunk_mb(mb):
 def set_gn_fuse_mb(mb):
     """largest input (MB) for which GroupNorm runs as one cluster-fused launch (include/b3d.h: b3d_set_gn_fuse_mb); 0 = never"""
     load().b3d_set_gn_fuse_mb(ctypes.c_int(int(mb)))
+
+
+def set_gn_fuse_bwd_mb(mb):
+    """the same threshold for the GroupNorm backward (0 by default: the fused backward measured slower)"""
+    load().b3d_set_gn_fuse_bwd_mb(ctypes.c_int(int(mb)))

@@ -248,8 +248,6 @@ struct BwdP {
   float* dgamma; float* dbeta;      // fp32 [C], accumulated
   float* dss_sum;                   // optional fp32 [2F]: column sums of dss (the FiLM dense bias gradient)
   float* dx_sum;                    // optional fp32 [C]: column sums of dx before the addends (the producer's bias gradient)
-  float* out_sum0; float* out_sum1; // optional fp32 [C0] / [C1]: out_sum_scale * column sums of the values STORED to dx0 / dx1 (addends included):
-  float out_sum_scale;              //   when this call completes the gradient of a block's output, that is the block's output-bias gradient
   float* ws;                        // [N,32,2] (S1, S2), pre-zeroed
   // pass 2 outputs
   bf16* dx0; bf16* dx1; long long ld_dx0, ld_dx1;
@@ -391,9 +389,9 @@ __device__ __forceinline__ void bwd_apply_body(const BwdP& p, int rows_per_block
   const int rows_par = max(1, (int)blockDim.x / vecs);
   const int v = threadIdx.x % vecs, rsub = threadIdx.x / vecs, c0 = v * 8;
   const bool active = rsub < rows_par;
-  float acc[8], acco[8];
+  float acc[8];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) { acc[j] = 0.f; acco[j] = 0.f; }
+  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
   if (active) {
     Aff ch; load_aff(ch, p.gamma, p.beta, c0, cpg, s_mean, s_rstd);
     float k1[8], k0[8];
@@ -439,7 +437,6 @@ __device__ __forceinline__ void bwd_apply_body(const BwdP& p, int rows_per_block
           const float g = fmaf(dz[j], ch.a[j], fmaf(f[j], k1[j], k0[j]));
           acc[j] += g;
           d[j] = fmaf(t0[j], p.add0_scale, g) + t1[j];
-          acco[j] += d[j];
         }
         *reinterpret_cast<bf16x8*>(dxp + row * ld_dx + c1) = b3d_pack8(d);
       }
@@ -448,13 +445,6 @@ __device__ __forceinline__ void bwd_apply_body(const BwdP& p, int rows_per_block
   if (p.dx_sum) {
     block_sum8(acc, active, v, rsub, rows_par, C, sm, sm + 2048);
     for (int c = threadIdx.x; c < C; c += blockDim.x) atomicAdd(&p.dx_sum[c], sm[2048 + c]);
-  }
-  if (p.out_sum0 != nullptr || p.out_sum1 != nullptr) {
-    block_sum8(acco, active, v, rsub, rows_par, C, sm, sm + 2048);
-    for (int c = threadIdx.x; c < C; c += blockDim.x) {
-      float* dst = c < p.s.C0 ? (p.out_sum0 ? p.out_sum0 + c : nullptr) : (p.out_sum1 ? p.out_sum1 + (c - p.s.C0) : nullptr);
-      if (dst != nullptr) atomicAdd(dst, sm[2048 + c] * p.out_sum_scale);
-    }
   }
 }
 template <int MODE>
@@ -574,13 +564,20 @@ int gn_chunk_images(int N, int HW, int C, int bytes_per_elem) {
 
 // Cluster-fused single-launch GroupNorm (gn_fwd_fused_kernel / gn_bwd_fused_kernel): used when the input tensor is small enough
 // to still be in L2 for the second pass.  Returns the cluster size (blocks per image, 1..8) or 0 for the two-launch path.
-long long g_gn_fuse_bytes = -1;
-int gn_fuse_cluster(int N, int HW, int C, int U, int* rows_per_block) {
+// The forward uses it by default (+3 % on the sampler's denoise step); the backward does not: at 16 pairs per GPU the fused
+// backward measured 2 % SLOWER than the two launches (20.73 vs 21.12 ms per step) -- its two passes per block leave fewer
+// independent blocks in flight than the separately sized launches.
+long long g_gn_fuse_bytes = -1, g_gn_fuse_bwd_bytes = -1;
+int gn_fuse_cluster(int N, int HW, int C, int U, int* rows_per_block, bool bwd = false) {
   if (g_gn_fuse_bytes < 0) {
     const char* e = getenv("B3D_GN_FUSE_MB");
     g_gn_fuse_bytes = (e ? atoll(e) : 40) * (1LL << 20);
   }
-  if ((long long)N * HW * C * 2 > g_gn_fuse_bytes) return 0;
+  if (g_gn_fuse_bwd_bytes < 0) {
+    const char* e = getenv("B3D_GN_FUSE_BWD_MB");
+    g_gn_fuse_bwd_bytes = (e ? atoll(e) : 0) * (1LL << 20);
+  }
+  if ((long long)N * HW * C * 2 > (bwd ? g_gn_fuse_bwd_bytes : g_gn_fuse_bytes)) return 0;
   const int vecs = C / 8;
   const int rows_par = 256 / vecs > 0 ? 256 / vecs : 1;
   const int min_rows = rows_par * U;
@@ -605,6 +602,7 @@ int check_src(const void* x0, int C0, const void* x1, int C1) {
 
 extern "C" void b3d_set_gn_chunk_mb(int mb) { g_gn_chunk_bytes = (long long)mb * (1LL << 20); }
 extern "C" void b3d_set_gn_fuse_mb(int mb) { g_gn_fuse_bytes = (long long)mb * (1LL << 20); }
+extern "C" void b3d_set_gn_fuse_bwd_mb(int mb) { g_gn_fuse_bwd_bytes = (long long)mb * (1LL << 20); }
 
 extern "C" int b3d_gn_stats(const void* x0, int C0, int64_t ld0, const void* x1, int C1, int64_t ld1, int N, int HW, float* ws_sums,
                             void* stream) {
@@ -693,8 +691,7 @@ extern "C" int b3d_gn_bwd(const void* x0, int C0, int64_t ld0, const void* x1, i
                           int F, void* dss, int64_t ld_dss, float drop_p, uint64_t seed, const uint64_t* seed_ptr, float* dgamma, float* dbeta,
                           float* dss_sum, float* dx_sum, float* ws_s12,
                           void* dx0, int64_t ld_dx0, void* dx1, int64_t ld_dx1, const void* add0, int64_t ld_add0, const void* add1a,
-                          int64_t ld_add1a, const void* add1b, int64_t ld_add1b, float add0_scale, float* out_sum0, float* out_sum1, float out_sum_scale,
-                          void* stream) {
+                          int64_t ld_add1a, const void* add1b, int64_t ld_add1b, float add0_scale, void* stream) {
   if (int rc = check_src(x0, C0, x1, C1)) return rc;
   B3D_CHECK_ARG(mode >= 0 && mode <= 2, "gn_bwd: mode");
   B3D_CHECK_ARG(mode != 2 || (ss && dss && F == C0 + C1), "gn_bwd: film needs ss, dss, F == C");
@@ -706,13 +703,12 @@ extern "C" int b3d_gn_bwd(const void* x0, int C0, int64_t ld0, const void* x1, i
   p.dgamma = dgamma; p.dbeta = dbeta; p.ws = ws_s12; p.dss_sum = dss_sum; p.dx_sum = dx_sum;
   p.dx0 = (bf16*)dx0; p.dx1 = (bf16*)dx1; p.ld_dx0 = ld_dx0; p.ld_dx1 = ld_dx1;
   p.add0 = (const bf16*)add0; p.ld_add0 = ld_add0; p.add0_scale = add0_scale;
-  p.out_sum0 = out_sum0; p.out_sum1 = out_sum1; p.out_sum_scale = out_sum_scale;
   p.add1a = (const bf16*)add1a; p.add1b = (const bf16*)add1b; p.ld_add1a = ld_add1a; p.ld_add1b = ld_add1b;
   const int C = C0 + C1;
   cudaStream_t st = (cudaStream_t)stream;
   {
     int rpb = 0;
-    const int cl = gn_fuse_cluster(N, HW, C, mode == 2 ? kBwdU2 : kBwdU1, &rpb);
+    const int cl = gn_fuse_cluster(N, HW, C, mode == 2 ? kBwdU2 : kBwdU1, &rpb, true);
     if (cl > 0) {
       p.n0 = 0;
       dim3 grid(cl, N);

@@ -93,11 +93,8 @@ def build_plan(cfg):
 class Act:
     """an activation tensor [N, h, w, C] with its (lazily created) gradient buffer"""
 
-    def __init__(self, t, key, bias=None):
+    def __init__(self, t, key):
         self.t, self.key, self.has_grad = t, key, False
-        # bias: name of the output bias of the block that produced this tensor through a (value + residual) / sqrt(2) epilogue;
-        # its gradient = column sums of d(this tensor) / sqrt(2), taken by whichever GroupNorm backward completes that gradient
-        self.bias, self.uses, self.left, self.bias_done = bias, 0, 0, False
         self.sums = None     # GroupNorm (sum, sumsq) [N,32,2] of this tensor at C/32 channels per group, when its producer's epilogue took them
 
 
@@ -119,9 +116,6 @@ class Engine:
         # attention backward: recompute P from the saved row log-sum-exp (no L x L tensor in HBM, 134 MB less per 16x16 block at
         # batch 128) instead of reading back the P the forward wrote; B3D_ATTN_SAVE_P=1 selects the latter (measurement switch)
         self.attn_recompute = os.environ.get("B3D_ATTN_SAVE_P") != "1"
-        # output-bias gradients inside the GroupNorm backward that completes the output gradient: measured 1 % SLOWER at 16 pairs per GPU
-        # and 0.2 % slower at 128 than the column-sum launches beside the chain: off (B3D_FUSE_BIAS=1 turns it on)
-        self.fuse_bias = os.environ.get("B3D_FUSE_BIAS") == "1"
         self.seed_ptr = None      # optional int64 device scalar added to every dropout seed (see ops.gn_apply)
         for lvl in range(cfg.num_resolutions):
             assert cfg.H % (2 ** lvl) == 0 and cfg.W % (2 ** lvl) == 0
@@ -409,9 +403,7 @@ class Engine:
                 hs.append(h)
             elif kind == "pop":
                 skip = hs.pop()
-                skip.uses += 1
             elif kind == "res":
-                h.uses += 1
                 if s.lvl >= 1 or not self._needed_first(s.name):
                     ops.join_side()            # FiLM operands of the coarser levels, the second weight-pack launch (no-op once joined)
                 h = self._res_fwd(s, h, skip if s.cat else None, ss[s.lvl], P, Wp, drop_p, seed * 1000 + bi)
@@ -419,10 +411,8 @@ class Engine:
                 bi += 1
             else:
                 ops.join_side()
-                h.uses += 1
                 h = self._attn_fwd(s, h, P, Wp)
         assert not hs
-        h.uses += 1          # the head
         ops.join_side()
 
         # ---- head (xunet.py:535-536)
@@ -490,7 +480,7 @@ class Engine:
             assert skip is None
             d2 = G.conv_desc([a1.view(N, hh, ww, F)], [9], Wp[n + ".conv2.weight"], F, out, bias=P[n + ".conv2.bias"], resid=h_in.t,
                              out_scale=RSQRT2)
-        o = Act(out, n + ".out", bias=n + ".conv2.bias")
+        o = Act(out, n + ".out")
         if s.resample is None:
             self._producer_stats(d2, o, F)        # (a resampled output is normalised after the resampling: no use for these)
         else:
@@ -548,7 +538,7 @@ class Engine:
         o1 = self.buf(n + ".o1", (N * L, C))
         ops.gemm(G.dense_desc(o.view(N * L, C), Wp[a + ".out_proj.weight"], o1, C, bias=P[a + ".out_proj.bias"]))
         out = self.buf(n + ".out", (N, hh, ww, C))
-        oa = Act(out, n + ".out", bias=n + ".linear.bias")
+        oa = Act(out, n + ".out")
         self._producer_stats(G.dense_desc(o1, Wp[n + ".linear.weight"], out.view(N * L, C), C, bias=P[n + ".linear.bias"],
                                           resid=h_in.t.view(N * L, C), out_scale=RSQRT2), oa, C, rows_per_image=L)
         self.saved["acts"][n] = dict(h_in=h_in, sums=sums, g=g, qkv=qkv, p=p, lse=lse, o=o, o1=o1, out=oa)
@@ -592,7 +582,7 @@ class Engine:
             for g in Gr.values():
                 g.zero_()
         for a in self._all_acts():
-            a.has_grad, a.left, a.bias_done = False, a.uses, False
+            a.has_grad = False
         self._dss = [self.buf(f"dss{l}", (N * (H >> l) * (Wd >> l), self.film_cols[l])) for l in range(cfg.num_resolutions)]
 
         # ---- head
@@ -608,10 +598,11 @@ class Engine:
         self._conv_wgrad("lastconv.weight", dy, al.view(N, H, Wd, C), Gr["lastconv.weight"], co_alloc=16)
         da = self.buf("lastgn.da", (N, H, Wd, C))
         ops.gemm(G.conv_desc([dy], [9], Wp["lastconv.weight.T"], C, da))
-        dh, _ = self._take_grad(h)
+        dh = self._grad_of(h)
         ops.gn_bwd(h.t.view(N, HW, C), None, self.zbuf("fwd", "lastgn.sums", (N, 32, 2)), P["lastgn.gn.weight"], P["lastgn.gn.bias"], 1,
                    da.view(N, HW, C), Gr["lastgn.gn.weight"], Gr["lastgn.gn.bias"], self.zbuf("bwd", "lastgn.ws", (N, 32, 2)),
-                   dh.view(N, HW, C), out_sum0=self._bias_sum(h, Gr), out_sum_scale=RSQRT2)
+                   dh.view(N, HW, C))
+        h.has_grad = True
 
         self._bwd_blocks(Gr, lambda name: name.startswith("upsample."))
         self._film_wgrad(Gr, lambda name: name.startswith("upsample."))
@@ -738,16 +729,7 @@ class Engine:
         g = self._grad_of(act)
         had = act.has_grad
         act.has_grad = True
-        act.left -= 1
         return g, (g if had else None)
-
-    def _bias_sum(self, act, Gr):
-        """the bias-gradient tensor that the GroupNorm backward writing `act`'s gradient should accumulate the column sums of its
-        output into: set when that write is the last contribution (the gradient is then complete), else None"""
-        if act.bias is None or act.left != 0 or not self.fuse_bias:
-            return None
-        act.bias_done = True
-        return Gr[act.bias]
 
     def _res_bwd(self, s, P, Wp, Gr, dss_l, drop_p):
         ops, N, n = self.ops, self.N, s.name
@@ -771,8 +753,7 @@ class Engine:
         # weight gradients of conv2 and the 1x1 skip, d(conv2.bias): on the side stream, beside the data-gradient chain below
         # (they only read dout and saved activations)
         with ops.side():
-            if not out.bias_done:      # (else the GroupNorm backward that completed dout has already summed its columns)
-                ops.colsum(dout2, M, Gr[n + ".conv2.bias"], scale=RSQRT2)
+            ops.colsum(dout2, M, Gr[n + ".conv2.bias"], scale=RSQRT2)
             self._conv_wgrad(n + ".conv2.weight", dout, sa["a1"].view(N, hh, ww, F), Gr[n + ".conv2.weight"], alpha=RSQRT2)
             if s.cin != F:
                 gw = Gr[n + ".dense.weight"].view(F, s.cin)
@@ -826,8 +807,7 @@ class Engine:
         v3 = lambda t_: t_.view(N, HW, -1) if t_ is not None else None
         ops.gn_bwd(x0, x1, sa["sums0"], P[n + ".groupnorm0.gn.weight"], P[n + ".groupnorm0.gn.bias"], 1, da0.view(N, HW, s.cin),
                    Gr[n + ".groupnorm0.gn.weight"], Gr[n + ".groupnorm0.gn.bias"], self.zbuf("bwd", n + ".ws0", (N, 32, 2)), v3(g0), v3(g1),
-                   add0=add0, add1a=v3(e0), add1b=v3(e1), add0_scale=add0_scale, out_sum0=self._bias_sum(h_in, Gr),
-                   out_sum1=self._bias_sum(skip, Gr) if skip is not None else None, out_sum_scale=RSQRT2)
+                   add0=add0, add1a=v3(e0), add1b=v3(e1), add0_scale=add0_scale)
         self._block_join()
 
     def _attn_bwd(self, s, P, Wp, Gr):
@@ -843,8 +823,7 @@ class Engine:
         gs = dout.view(M, C)      # the (h + h_in) / sqrt(2) of xunet.py:220 is folded into the consumers of dout (see _res_bwd)
         # 1x1 `linear` and out_proj
         with ops.side():      # parameter gradients run beside the data-gradient chain (joined at the end of the block)
-            if not out.bias_done:
-                ops.colsum(gs, M, Gr[n + ".linear.bias"], scale=RSQRT2)
+            ops.colsum(gs, M, Gr[n + ".linear.bias"], scale=RSQRT2)
             ops.gemm(G.wgrad_dense_desc(gs, sa["o1"], Gr[n + ".linear.weight"].view(C, C), alpha=RSQRT2))
         do1 = self.side_tmp(n, "do1", (M, C))
         ops.gemm(G.dense_desc(gs, Wp[n + ".linear.weight.T"], do1, C, alpha=RSQRT2))
@@ -885,6 +864,5 @@ class Engine:
         g0, e0 = self._take_grad(h_in)
         ops.gn_bwd(h_in.t.view(N, L, C), None, sa["sums"], P[n + ".groupnorm.gn.weight"], P[n + ".groupnorm.gn.bias"], 0, dg,
                    Gr[n + ".groupnorm.gn.weight"], Gr[n + ".groupnorm.gn.bias"], self.zbuf("bwd", n + ".ws", (N, 32, 2)),
-                   g0.view(N, L, C), None, add0=gs.view(N, L, C), add1a=e0.view(N, L, C) if e0 is not None else None, add0_scale=RSQRT2,
-                   out_sum0=self._bias_sum(h_in, Gr), out_sum_scale=RSQRT2)
+                   g0.view(N, L, C), None, add0=gs.view(N, L, C), add1a=e0.view(N, L, C) if e0 is not None else None, add0_scale=RSQRT2)
         self._block_join()

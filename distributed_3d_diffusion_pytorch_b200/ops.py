@@ -463,16 +463,14 @@ class CudaOps:
                    _ptr(out), c_i64(out.stride(1)), _ptr(ss_image), self.stream())
 
     def gn_bwd(self, x0, x1, sums, gamma, beta, mode, dy, dgamma, dbeta, ws, dx0, dx1=None, ss=None, F=0, dss=None, drop_p=0.0, seed=0,
-               add0=None, add1a=None, add1b=None, seed_ptr=None, dss_sum=None, dx_sum=None, add0_scale=1.0, out_sum0=None, out_sum1=None,
-               out_sum_scale=1.0):
+               add0=None, add1a=None, add1b=None, seed_ptr=None, dss_sum=None, dx_sum=None, add0_scale=1.0):
         N, HW, _ = x0.shape
         ld = lambda t, i=1: c_i64(t.stride(i) if t is not None else 0)
         self._call("b3d_gn_bwd", *self._src(x0), *self._src(x1), c_i32(N), c_i32(HW), _ptr(sums), _ptr(gamma), _ptr(beta), c_i32(mode),
                    _ptr(dy), ld(dy), _ptr(ss), ld(ss, 0), c_i32(F), _ptr(dss), ld(dss, 0), c_f32(drop_p), ctypes.c_uint64(seed),
                    _ptr(seed_ptr), _ptr(dgamma), _ptr(dbeta), _ptr(dss_sum), _ptr(dx_sum), _ptr(ws), _ptr(dx0), ld(dx0), _ptr(dx1), ld(dx1),
                    _ptr(add0), ld(add0),
-                   _ptr(add1a), ld(add1a), _ptr(add1b), ld(add1b), c_f32(add0_scale), _ptr(out_sum0), _ptr(out_sum1), c_f32(out_sum_scale),
-                   self.stream())
+                   _ptr(add1a), ld(add1a), _ptr(add1b), ld(add1b), c_f32(add0_scale), self.stream())
 
     # ---- diffusion glue
     def q_sample(self, z, noise, logsnr, z_out, x=None, xrand=None, mask=None, x_out=None):

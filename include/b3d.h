@@ -183,9 +183,7 @@ int b3d_softmax_bwd(const void* P, int64_t ld_p, const void* dP, int dp_fp32, in
  *   uses ws_s12 fp32 [N,32,2] (caller zeroes it), writes dx0/dx1 (+ add0_scale * add0 + add1a/add1b when given: the
  *   residual branch's gradient joins here with its 1/sqrt2, xunet.py:152,220).  Optional fused
  *   reductions (fp32, accumulated): dss_sum [2F] = column sums of dss (FiLM dense bias gradient, xunet.py:80),
- *   dx_sum [C] = column sums of dx before the addends (bias gradient of the layer that produced x),
- *   out_sum0 [C0] / out_sum1 [C1] = out_sum_scale * column sums of the values stored to dx0 / dx1, addends included (when the
- *   call completes the gradient of a block's output: that block's output-bias gradient, xunet.py:146,217 with the 1/sqrt2). */
+ *   dx_sum [C] = column sums of dx before the addends (bias gradient of the layer that produced x). */
 int b3d_gn_stats(const void* x0, int C0, int64_t ld0, const void* x1, int C1, int64_t ld1, int N, int HW, float* ws_sums, void* stream);
 int b3d_gn_apply(const void* x0, int C0, int64_t ld0, const void* x1, int C1, int64_t ld1, int N, int HW, const float* sums,
                  const float* gamma, const float* beta, int mode, const void* ss, int64_t ld_ss, int F, float drop_p, uint64_t seed, const uint64_t* seed_ptr,
@@ -199,17 +197,19 @@ int b3d_gn_stats_apply(const void* x0, int C0, int64_t ld0, const void* x1, int 
 /* budget (MB) for the tensors both passes of a GroupNorm read per image chunk; 0 = no chunking.  Default: the
  * environment's B3D_GN_CHUNK_MB, else 0.  A tuning knob of this library, no reference counterpart. */
 void b3d_set_gn_chunk_mb(int mb);
-/* b3d_gn_stats_apply and b3d_gn_bwd run as ONE cluster-fused launch (the blocks of an image exchange their partial sums through
+/* b3d_gn_stats_apply (and, with b3d_set_gn_fuse_bwd_mb, b3d_gn_bwd) run as ONE cluster-fused launch (the blocks of an image exchange their partial sums through
  * distributed shared memory; the second pass re-reads the image from L2) when the input tensor is at most this many MB --
  * small per-GPU batches and the sampler, where the launches, not the bytes, are what costs.  Default 40 (B3D_GN_FUSE_MB in the
- * environment overrides); 0 = always two launches.  No reference counterpart. */
+ * environment overrides); 0 = always two launches.  The backward's threshold is separate and 0 by default
+ * (B3D_GN_FUSE_BWD_MB): the fused backward measured slower than its two launches.  No reference counterpart. */
 void b3d_set_gn_fuse_mb(int mb);
+void b3d_set_gn_fuse_bwd_mb(int mb);
 int b3d_gn_bwd(const void* x0, int C0, int64_t ld0, const void* x1, int C1, int64_t ld1, int N, int HW, const float* sums,
                const float* gamma, const float* beta, int mode, const void* dy, int64_t ld_dy, const void* ss, int64_t ld_ss, int F,
                void* dss, int64_t ld_dss, float drop_p, uint64_t seed, const uint64_t* seed_ptr, float* dgamma, float* dbeta, float* dss_sum,
                float* dx_sum, float* ws_s12, void* dx0,
                int64_t ld_dx0, void* dx1, int64_t ld_dx1, const void* add0, int64_t ld_add0, const void* add1a, int64_t ld_add1a,
-               const void* add1b, int64_t ld_add1b, float add0_scale, float* out_sum0, float* out_sum1, float out_sum_scale, void* stream);
+               const void* add1b, int64_t ld_add1b, float add0_scale, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Diffusion glue (fp32 NCHW, as the reference holds these tensors)

@@ -464,8 +464,7 @@ class EmuOps:
         self.gn_apply(x0, x1, sums, gamma, beta, mode, out, **kw)
 
     def gn_bwd(self, x0, x1, sums, gamma, beta, mode, dy, dgamma, dbeta, ws, dx0, dx1=None, ss=None, F=0, dss=None, drop_p=0.0, seed=0,
-               add0=None, add1a=None, add1b=None, seed_ptr=None, dss_sum=None, dx_sum=None, add0_scale=1.0, out_sum0=None, out_sum1=None,
-               out_sum_scale=1.0):
+               add0=None, add1a=None, add1b=None, seed_ptr=None, dss_sum=None, dx_sum=None, add0_scale=1.0):
         seed = (seed + (int(seed_ptr.item()) * SEED_STEP_STRIDE if seed_ptr is not None else 0)) & ((1 << 64) - 1)
         x = self._cat(x0, x1)
         N, HW, C = x.shape
@@ -506,10 +505,6 @@ class EmuOps:
         dx0.copy_(dx[..., :C0].to(dx0.dtype))
         if dx1 is not None:
             dx1.copy_(dx[..., C0:].to(dx1.dtype))
-        if out_sum0 is not None:
-            out_sum0 += dx[..., :C0].sum((0, 1)) * out_sum_scale
-        if out_sum1 is not None:
-            out_sum1 += dx[..., C0:].sum((0, 1)) * out_sum_scale
 
     # ------------------------------------------------------------------ diffusion glue
     def q_sample(self, z, noise, logsnr, z_out, x=None, xrand=None, mask=None, x_out=None):

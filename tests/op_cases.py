@@ -55,12 +55,9 @@ def gn_case(N, HW, C0, C1, mode, drop_p=0.0, seed=0, step=None):
         dss = ops.zeros((N * HW, 2 * F)) if mode == 2 else None
         add0 = _mk(ops, _r((N, HW, C), g))
         add1a = _mk(ops, _r((N, HW, C0), g))
-        os0 = ops.zeros((C0,), torch.float32)
-        os1 = ops.zeros((C1,), torch.float32) if C1 else None
         ops.gn_bwd(x0, x1, sums, gamma, beta, mode, dy, dgamma, dbeta, ws, dx0, dx1, ss=ss, F=F, dss=dss, drop_p=drop_p, seed=77,
-                   add0=add0, add1a=add1a, seed_ptr=sp, add0_scale=0.7071067811865476 if (seed % 2) else 1.0, out_sum0=os0, out_sum1=os1,
-                   out_sum_scale=0.5)
-        outs = [sums, out, dgamma, dbeta, ws, dx0, os0] + ([os1] if C1 else [])
+                   add0=add0, add1a=add1a, seed_ptr=sp, add0_scale=0.7071067811865476 if (seed % 2) else 1.0)
+        outs = [sums, out, dgamma, dbeta, ws, dx0]
         if C1:
             outs.append(dx1)
         if mode == 2:

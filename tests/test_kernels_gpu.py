@@ -116,6 +116,7 @@ def test_gn_cluster_fused_launch_equals_two_launches(N, HW, C0, C1):
     try:
         for fuse in (0, 40):
             _lib.set_gn_fuse_mb(fuse)
+            _lib.set_gn_fuse_bwd_mb(fuse)
             for mode in (0, 1, 2):
                 film = dict(ss=ss, F=C, drop_p=0.1, seed=5) if mode == 2 else {}
                 sums = torch.zeros(N, 32, 2, device=dev)
@@ -137,6 +138,7 @@ def test_gn_cluster_fused_launch_equals_two_launches(N, HW, C0, C1):
                 res[(fuse, mode)] = (l_fwd, l_bwd, [sums, out, dx0, dx1, dss, dgamma, dbeta, dss_sum, dx_sum])
     finally:
         _lib.set_gn_fuse_mb(40)
+        _lib.set_gn_fuse_bwd_mb(0)
     for mode in (0, 1, 2):
         (lf0, lb0, a), (lf1, lb1, b) = res[(0, mode)], res[(40, mode)]
         assert (lf0, lb0) == (2, 2) and (lf1, lb1) == (1, 1)

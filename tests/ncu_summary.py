@@ -100,5 +100,30 @@ def sass(lib, out):
     print(out)
 
 
+def launches(csv_path, out, title=""):
+    """ncu --metrics gpu__time_duration.sum --csv launch list -> per-kernel totals and shares"""
+    rows = [r for r in csv.reader(open(csv_path)) if len(r) > 10]
+    hdr = rows[0]
+    ix = {n: i for i, n in enumerate(hdr)}
+    agg = {}
+    for r in rows[1:]:
+        if r[ix["Metric Name"]] != "gpu__time_duration.sum":
+            continue
+        name = re.sub(r"\(.*", "", r[ix["Kernel Name"]]).replace("void ", "").replace("<unnamed>::", "")
+        v = float(r[ix["Metric Value"]].replace(",", ""))
+        unit = r[ix["Metric Unit"]]
+        ms = v / 1e6 if unit in ("ns", "nsecond") else v / 1e3 if unit in ("us", "usecond") else v
+        a = agg.setdefault(name, [0, 0.0])
+        a[0] += 1
+        a[1] += ms
+    tot = sum(v[1] for v in agg.values())
+    with open(out, "w") as fh:
+        fh.write(f"{title}\n{sum(v[0] for v in agg.values())} launches, {tot:.1f} ms total (serialised, cold caches: shares, not absolutes, compare with bench.py)\n")
+        for k, v in sorted(agg.items(), key=lambda kv: -kv[1][1]):
+            fh.write(f"{v[1]:10.3f} ms  {100 * v[1] / tot:5.1f}%  n={v[0]:4d}  {k}\n")
+    print(out, tot)
+
+
 if __name__ == "__main__":
-    {"raw": raw, "stalls": stalls, "sass": sass}[sys.argv[1]](*sys.argv[2:])
+    {"raw": raw, "stalls": stalls, "sass": sass, "launches": launches}[sys.argv[1]](*sys.argv[2:])
+

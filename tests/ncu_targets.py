@@ -25,6 +25,9 @@ def main():
         dqkv = torch.empty(N, L, 3 * C, device=dev, dtype=bf)
         ops.attn_fwd(qkv, heads, True, 1.0 / math.sqrt(d), out, probs=probs)
         ops.attn_bwd(qkv, probs, out, dout, dqkv, heads, True, 1.0 / math.sqrt(d))
+        lse = torch.empty(N, heads, L, device=dev)                     # flash-style: row statistics out, P recomputed in the backward
+        ops.attn_fwd(qkv, heads, True, 1.0 / math.sqrt(d), out, lse=lse)
+        ops.attn_bwd(qkv, None, out, dout, dqkv, heads, True, 1.0 / math.sqrt(d), lse=lse)
     # GroupNorm family at the 64x64 level, 128 channels
     N, HW, C = 256, 4096, 128
     x = torch.randn(N, HW, C, device=dev).to(bf)

@@ -50,3 +50,8 @@ def set_gn_fuse_mb(mb):
 def set_gn_fuse_bwd_mb(mb):
     """the same threshold for the GroupNorm backward (0 by default: the fused backward measured slower)"""
     load().b3d_set_gn_fuse_bwd_mb(ctypes.c_int(int(mb)))
+
+
+def set_conv_halo(on):
+    """halo-patch form of the stride-1 3x3 convolutions (include/b3d.h: b3d_set_conv_halo)"""
+    load().b3d_set_conv_halo(ctypes.c_int(int(on)))

@@ -71,6 +71,12 @@ struct alignas(64) KP {
   int act, out_fp32, out_atomic;
   float* gn_sums;       // optional: GroupNorm (sum, sumsq) of the stored bf16 output, fp32 [images, 32, 2], accumulated
   int gn_cpg, gn_rpi;   // channels per group (4 / 8 / 16 / 32); rows per image of the dense form (0: conv form)
+  // Halo-patch form of a stride-1 3x3 convolution: per 64-channel block ONE (8+2) x (rows+2)-pixel patch of the input is loaded
+  // (rows of 10 pixels at a 16-pixel pitch) and the nine taps' MMAs read it through shifted A descriptors -- 6x less
+  // A traffic from L2 than nine shifted tile loads.  Separate rings for the patches (a_stages) and the weight tiles.
+  struct HSrc { int32_t src, taps, ncb, bk0, klast; } hsrc[3];
+  int halo, n_hsrc, h_accs, h_rows, a_stages, b_stages;
+  uint32_t h_stage_bytes, b_ring_off, h_bo_mode, h_pitch;   // h_pitch: bytes between patch rows (1280 = packed, one TMA load per patch; 2048 = one load per row)
   int epi_tma;          // bf16 outputs leave through shared memory + TMA store (coalesced, no LSU global traffic)
   uint32_t epi_off;     // byte offset of the epilogue staging buffers inside dynamic smem
 };
@@ -126,6 +132,7 @@ template <bool kPair>
 __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_constant__ KP p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t bars[2 * 8 + 4 + 2];
+  __shared__ uint64_t abars[2 * 3];                  // halo form: full / empty barriers of the patch ring
   __shared__ uint32_t tmem_base_smem;
   __shared__ __align__(16) float s_bias[256];   // bias slice of the current N tile (bf16 TMA epilogue)
 
@@ -140,9 +147,12 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
   auto tfull_bar = [&](int s) { return smem_u32(&bars[16 + s]); };
   auto tempty_bar = [&](int s) { return smem_u32(&bars[18 + s]); };
   auto resid_bar = [&](int s) { return smem_u32(&bars[20 + s]); };
+  auto afull_bar = [&](int s) { return smem_u32(&abars[s]); };
+  auto aempty_bar = [&](int s) { return smem_u32(&abars[3 + s]); };
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < S; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    for (int s = 0; s < (p.halo ? p.b_stages : S); ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    for (int s = 0; s < 3; ++s) { mbar_init(afull_bar(s), 1); mbar_init(aempty_bar(s), 1); }
     for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), kPair ? 8 : 4); mbar_init(resid_bar(s), 1); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -174,6 +184,7 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
     // The whole warp walks the (warp-uniform) loops and polls the barriers; one elected lane issues the copies.
     {
       int stage = 0; uint32_t phase = 0;
+      int hs = 0; uint32_t hphase = 0;
       for (int t = t_first; t < p.tiles_total; t += t_step) {
         const TileCoord c = decode_tile(p, t);
         int kb0, nkb; k_range(p, c, kb0, nkb);
@@ -183,7 +194,56 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
           return smem_base + (uint32_t)stage * p.stage_bytes;
         };
         auto advance = [&]() { if (++stage == S) { stage = 0; phase ^= 1; } };
-        if (p.a_major == 0 && p.b_major == 0) {
+        if (p.halo) {
+          // (stage / phase above are the weight-tile ring's; hs / hphase the patch ring's -- both persist across tiles)
+          const int px = c.x0 - 1, py = c.y0 + half_y - 1, pn = c.n0;
+          const uint32_t a_bytes_patch = (uint32_t)p.h_rows * 1280u, a_bytes_center = (uint32_t)(p.h_rows - 2) * 1280u;
+          for (int q = 0; q < p.n_hsrc; ++q) {
+            const auto hq = p.hsrc[q];
+            for (int cb = 0; cb < hq.ncb; ++cb) {
+              mbar_wait(aempty_bar(hs), hphase ^ 1);
+              const uint32_t da = smem_base + (uint32_t)hs * p.h_stage_bytes;
+              if (elect_one()) {
+                const uint32_t nb = hq.taps == 9 ? a_bytes_patch : a_bytes_center;
+                const int r0 = hq.taps == 9 ? 0 : 1, r1 = hq.taps == 9 ? p.h_rows : p.h_rows - 1;
+                if (p.h_pitch == 1280u) {       // packed rows: the whole patch is one box (1-tap sources load it too: same map)
+                  if constexpr (kPair) {
+                    const uint32_t lead_bar = mapa_shared(afull_bar(hs), 0u);
+                    if (crank == 0) mbar_expect_tx(afull_bar(hs), 2u * a_bytes_patch);
+                    tma_load_4d_pair(da, &p.tmA[hq.src], lead_bar, cb * BK, px, py, pn);
+                  } else {
+                    mbar_expect_tx(afull_bar(hs), a_bytes_patch);
+                    tma_load_4d(da, &p.tmA[hq.src], afull_bar(hs), cb * BK, px, py, pn);
+                  }
+                } else if constexpr (kPair) {
+                  const uint32_t lead_bar = mapa_shared(afull_bar(hs), 0u);
+                  if (crank == 0) mbar_expect_tx(afull_bar(hs), 2u * nb);
+                  for (int r = r0; r < r1; ++r) tma_load_4d_pair(da + (uint32_t)r * 2048u, &p.tmA[hq.src], lead_bar, cb * BK, px, py + r, pn);
+                } else {
+                  mbar_expect_tx(afull_bar(hs), nb);
+                  for (int r = r0; r < r1; ++r) tma_load_4d(da + (uint32_t)r * 2048u, &p.tmA[hq.src], afull_bar(hs), cb * BK, px, py + r, pn);
+                }
+              }
+              for (int tp = 0; tp < hq.taps; ++tp) {
+                mbar_wait(empty_bar(stage), phase ^ 1);
+                const uint32_t db = smem_base + p.b_ring_off + (uint32_t)stage * p.b_bytes;
+                if (elect_one()) {
+                  const int bk = hq.bk0 + (tp * hq.ncb + cb) * BK;
+                  if constexpr (kPair) {
+                    const uint32_t lead_bar = mapa_shared(full_bar(stage), 0u);
+                    if (crank == 0) mbar_expect_tx(full_bar(stage), 2u * p.b_tx);
+                    tma_load_4d_pair(db, &p.tmB, lead_bar, bk, ncol0 + (int)crank * (p.BN / 2), 0, 0);
+                  } else {
+                    mbar_expect_tx(full_bar(stage), p.b_tx);
+                    tma_load_4d(db, &p.tmB, full_bar(stage), bk, ncol0, 0, 0);
+                  }
+                }
+                if (++stage == p.b_stages) { stage = 0; phase ^= 1; }
+              }
+              if (++hs == p.a_stages) { hs = 0; hphase ^= 1; }
+            }
+          }
+        } else if (p.a_major == 0 && p.b_major == 0) {
           const int by = p.batched ? c.y0 : 0, bn = p.batched ? (c.n0 ^ p.b_xor) : 0;
           for (int s = 0; s < p.nseg; ++s) {
             const Seg sg = p.seg[s];
@@ -260,6 +320,7 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
     // In a CTA pair only the leader issues (cta_group::2); its commits arrive on both CTAs' barriers.
     if (crank == 0) {
       int stage = 0; uint32_t phase = 0;
+      int hs = 0; uint32_t hphase = 0;
       int acc = 0; uint32_t acc_phase = 0;
       const uint32_t a_kstep = p.a_major ? (2048u >> 4) : (32u >> 4), b_kstep = p.b_major ? (2048u >> 4) : (32u >> 4);
       const uint32_t a_lbo = p.a_major ? 8192u : 16u, b_lbo = p.b_major ? 8192u : 16u;
@@ -275,7 +336,48 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
         // 144-channel conditioning input, the 8-channel stem input): only its real 16-channel steps are issued
         const bool segk = p.a_major == 0 && p.b_major == 0;
         int sidx = 0, cbi = 0, ncb_cur = segk ? p.seg[0].ncb : 0x7fffffff;
-        for (int kb = 0; kb < nkb; ++kb) {
+        if (p.halo) {
+          // per 64-channel block: one patch, nine (or one) weight tiles; tap (dx, dy) of accumulator a reads the patch from row
+          // a*16 + dy + 1, pixel dx + 1 on: groups of 8 pixels (one image row of the tile) 2048 bytes apart
+          bool first = true;
+          for (int q = 0; q < p.n_hsrc; ++q) {
+            const auto hq = p.hsrc[q];
+            for (int cb = 0; cb < hq.ncb; ++cb) {
+              const int ksteps = cb == hq.ncb - 1 ? hq.klast : BK / 16;
+              mbar_wait(afull_bar(hs), hphase);
+              tc_fence_after();
+              const uint32_t pa = smem_base + (uint32_t)hs * p.h_stage_bytes;
+              for (int tp = 0; tp < hq.taps; ++tp) {
+                const int dx = hq.taps == 9 ? tp % 3 - 1 : 0, dy = hq.taps == 9 ? tp / 3 - 1 : 0;
+                mbar_wait(full_bar(stage), phase);
+                tc_fence_after();
+                const uint32_t sb = smem_base + p.b_ring_off + (uint32_t)stage * p.b_bytes;
+                const uint64_t bd = b_desc0 + (uint64_t)(sb >> 4);
+                if (elect_one()) {
+                  for (int a = 0; a < p.h_accs; ++a) {
+                    const uint32_t sa = pa + (uint32_t)(a * 16 + dy + 1) * p.h_pitch + (uint32_t)(dx + 1) * 128u;
+                    // (no base offset: the 128-byte swizzle of TMA and UMMA is a function of the absolute shared-memory address
+                    // bits, measured -- a start shifted by whole rows reads what TMA wrote there; with base_offset = start row
+                    // mod 8 the results were wrong)
+                    const uint64_t ad = umma_desc(sa, 16u, p.h_pitch, p.h_bo_mode ? (uint32_t)(dx + 1) : 0u);
+#pragma unroll
+                    for (int k = 0; k < BK / 16; ++k)
+                      if (k < ksteps) {
+                        if constexpr (kPair) umma_bf16_pair(d_tmem + (uint32_t)a * p.acc_half, ad + (uint64_t)(k * 2), bd + (uint64_t)(k * 2), idesc, (first && k == 0) ? 0u : 1u);
+                        else umma_bf16(d_tmem + (uint32_t)a * p.acc_half, ad + (uint64_t)(k * 2), bd + (uint64_t)(k * 2), idesc, (first && k == 0) ? 0u : 1u);
+                      }
+                  }
+                  if constexpr (kPair) umma_commit_pair(empty_bar(stage)); else umma_commit(empty_bar(stage));
+                }
+                first = false;
+                if (++stage == p.b_stages) { stage = 0; phase ^= 1; }
+              }
+              if (elect_one()) { if constexpr (kPair) umma_commit_pair(aempty_bar(hs)); else umma_commit(aempty_bar(hs)); }
+              if (++hs == p.a_stages) { hs = 0; hphase ^= 1; }
+            }
+          }
+        }
+        for (int kb = 0; kb < (p.halo ? 0 : nkb); ++kb) {
           int ksteps = BK / 16;
           if (segk) {
             if (cbi == ncb_cur - 1) ksteps = p.seg[sidx].klast;
@@ -751,6 +853,8 @@ int choose_bn(int n_cols, int b_major, long long tiles_other) {
 
 }  // namespace
 
+static int g_halo = -1;
+extern "C" void b3d_set_conv_halo(int on) { g_halo = on; }      // 1: patch rows at a 2048-byte pitch, 2: packed rows (1280 bytes)
 static int64_t g_launches = 0;
 extern "C" int64_t b3d_launch_count(void) { return g_launches; }
 void b3d_count_launch(int n) { g_launches += n; }
@@ -904,11 +1008,33 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
       }
     }
   }
+  // Halo-patch form (see KP): stride-1 3x3 convolutions whose image tiles into 8 x (16 * accumulators * CTAs) pixel tiles
+  if (g_halo < 0) g_halo = getenv("B3D_HALO") ? atoi(getenv("B3D_HALO")) : 2;
+  static const int halo_bo = getenv("B3D_HALO_BO") ? atoi(getenv("B3D_HALO_BO")) : 0;
+  if (g_halo && d->a_major == 0 && d->b_major == 0 && !d->batched && s == 1 && d->pad == 1 && p.epi_tma && !d->out_fp32) {
+    bool any9 = false, ok = d->n_src >= 1 && d->n_src <= 3;
+    for (int i = 0; ok && i < d->n_src; ++i) { if (d->a_taps[i] == 9) any9 = true; else if (d->a_taps[i] != 1) ok = false; }
+    const int accs = p.m2 ? 2 : 1, th = 16 * accs * (p.c2 ? 2 : 1);
+    const uint32_t hpitch = g_halo == 2 ? 1280u : 2048u;
+    const uint32_t hbytes = ((uint32_t)(16 * accs + 2) * hpitch + 1023u) / 1024u * 1024u;
+    const long long room = (long long)kMaxDynSmem - 1024 - epi_bytes - 2LL * hbytes;
+    if (ok && any9 && d->W % 8 == 0 && d->H % th == 0 && room >= 2LL * p.b_bytes) {
+      p.halo = 1; p.h_accs = accs; p.h_rows = 16 * accs + 2; p.h_stage_bytes = hbytes; p.a_stages = 2; p.h_bo_mode = (uint32_t)halo_bo; p.h_pitch = hpitch;
+      p.b_stages = (int)(room / p.b_bytes); if (p.b_stages > 8) p.b_stages = 8;
+      if (room - (long long)p.b_stages * p.b_bytes >= (long long)hbytes && p.b_stages >= 4) { p.a_stages = 3; }      // a third patch when it is free
+      else if (p.b_stages > 4 && room - 4LL * p.b_bytes >= (long long)hbytes) { p.a_stages = 3; p.b_stages = (int)((room - hbytes) / p.b_bytes); if (p.b_stages > 8) p.b_stages = 8; }
+      m2_bw = 8; m2_bh = th; m2_bnn = 1; p.m2_dim = 1;
+    }
+  }
   p.stage_bytes = p.a_bytes + p.b_bytes;
   p.num_stages = (int)((kMaxDynSmem - 1024 - epi_bytes) / p.stage_bytes);
   if (p.num_stages > 8) p.num_stages = 8;
   B3D_CHECK_ARG(p.num_stages >= 2, "b3d_gemm: not enough shared memory for a 2-stage pipeline");
   p.epi_off = (uint32_t)p.num_stages * p.stage_bytes;
+  if (p.halo) {
+    p.b_ring_off = (uint32_t)p.a_stages * p.h_stage_bytes;
+    p.epi_off = p.b_ring_off + (uint32_t)p.b_stages * p.b_bytes;
+  }
   p.acc_stride = (BN + 31) / 32 * 32;
   if (p.m2) { p.acc_half = (uint32_t)p.acc_stride; p.acc_stride *= 2; }
   p.tmem_cols = pow2_ceil(2 * p.acc_stride);
@@ -926,6 +1052,7 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
       p.bh = BM / p.bw; if (p.bh > d->H) p.bh = d->H; if (p.bh < 1) p.bh = 1;
       p.bnn = (p.bh == d->H) ? BM / (p.bw * p.bh) : 1; if (p.bnn > d->N) p.bnn = d->N; if (p.bnn < 1) p.bnn = 1;
     }
+    if (p.halo) { p.bw = 8; p.bh = 16; p.bnn = 1; }
     p.tbw = (p.m2 || p.c2) ? m2_bw : p.bw; p.tbh = (p.m2 || p.c2) ? m2_bh : p.bh; p.tbnn = (p.m2 || p.c2) ? m2_bnn : p.bnn;
     p.tiles_x = (d->W + p.tbw - 1) / p.tbw;
     p.tiles_y = (d->H + p.tbh - 1) / p.tbh;
@@ -936,7 +1063,8 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
     const int adiv = p.c2 ? 2 : 1;
     const int abw = p.m2_dim == 0 ? p.tbw / adiv : p.tbw, abh = p.m2_dim == 1 ? p.tbh / adiv : p.tbh, abn = p.m2_dim == 2 ? p.tbnn / adiv : p.tbnn;
     p.a_tx = (uint32_t)(abw * abh * abn) * 128u;
-    const uint32_t boxA[4] = {64, (uint32_t)((abw - 1) * s + 1), (uint32_t)((abh - 1) * s + 1), (uint32_t)abn};
+    uint32_t boxA[4] = {64, (uint32_t)((abw - 1) * s + 1), (uint32_t)((abh - 1) * s + 1), (uint32_t)abn};
+    if (p.halo) { boxA[1] = 10; boxA[2] = p.h_pitch == 1280u ? (uint32_t)p.h_rows : 1u; boxA[3] = 1; }      // a whole patch, or one 10-pixel row of it, per TMA load
     const uint32_t esA[4] = {1, (uint32_t)s, (uint32_t)s, 1};
     if (d->b_major == 0) {
       B3D_CHECK_ARG(d->n_src >= 1 && d->n_src <= 3, "b3d_gemm: n_src");
@@ -945,6 +1073,12 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
         rc = make_map(&p.tmA[i], d->a[i], boxA, esA); if (rc) return rc;
         const int taps = d->a_taps[i] == 9 ? 9 : 1;
         const int ncb = (d->a[i].dim[0] + BK - 1) / BK;
+        if (p.halo) {
+          auto& hq = p.hsrc[p.n_hsrc++];
+          hq.src = i; hq.taps = taps; hq.ncb = ncb; hq.bk0 = bk;
+          const int rem = d->a[i].dim[0] - (ncb - 1) * BK;
+          hq.klast = (rem + 15) / 16; if (hq.klast < 1) hq.klast = 1; if (hq.klast > BK / 16) hq.klast = BK / 16;
+        }
         for (int tp = 0; tp < taps; ++tp) {
           B3D_CHECK_ARG(p.nseg < kMaxSeg, "b3d_gemm: too many K segments");
           Seg& sg = p.seg[p.nseg++];
@@ -1025,7 +1159,7 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
   B3D_CHECK_ARG(!d->out_atomic || d->out_fp32, "b3d_gemm: out_atomic needs fp32 output");
   B3D_CHECK_ARG(d->act != 2 || (d->resid != nullptr && !d->out_fp32 && d->out2 == nullptr), "b3d_gemm: act 2 (times silu'(resid)) needs resid, a bf16 output and no out2");
 
-  const size_t smem = (size_t)p.num_stages * p.stage_bytes + epi_bytes + 1024;
+  const size_t smem = (p.halo ? (size_t)p.epi_off : (size_t)p.num_stages * p.stage_bytes) + epi_bytes + 1024;
   static bool attr_set = false;
   if (!attr_set) {
     B3D_CUDA(cudaFuncSetAttribute(b3d_gemm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem));

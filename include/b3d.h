@@ -84,6 +84,11 @@ typedef struct b3d_gemm_desc {
 } b3d_gemm_desc;
 
 int b3d_gemm(const b3d_gemm_desc* d, void* stream);
+/* Stride-1 3x3 convolutions in the halo-patch form (one (8+2) x (rows+2)-pixel input patch per 64-channel block in shared
+ * memory, the nine taps read it through shifted UMMA descriptors) instead of nine shifted tile loads.  Same results.
+ * 0 = off, 1 = patch rows at a 2048-byte pitch (one TMA load per row), 2 = packed rows (one load per patch; the default).
+ * The environment's B3D_HALO sets the initial value.  A tuning switch of this library, no reference counterpart. */
+void b3d_set_conv_halo(int on);
 /* 1 when b3d_gemm can honour d->gn_sums for this descriptor (pure host code) */
 int b3d_gemm_stats_supported(const b3d_gemm_desc* d);
 

@@ -76,7 +76,7 @@ struct alignas(64) KP {
   // A traffic from L2 than nine shifted tile loads.  Separate rings for the patches (a_stages) and the weight tiles.
   struct HSrc { int32_t src, taps, ncb, bk0, klast; } hsrc[3];
   int halo, n_hsrc, h_accs, h_rows, a_stages, b_stages;
-  uint32_t h_stage_bytes, b_ring_off, h_bo_mode, h_pitch;   // h_pitch: bytes between patch rows (1280 = packed, one TMA load per patch; 2048 = one load per row)
+  uint32_t h_stage_bytes, b_ring_off, h_pitch;   // h_pitch: bytes between patch rows (1280 = packed, one TMA load per patch; 2048 = one load per row)
   int epi_tma;          // bf16 outputs leave through shared memory + TMA store (coalesced, no LSU global traffic)
   uint32_t epi_off;     // byte offset of the epilogue staging buffers inside dynamic smem
 };
@@ -357,9 +357,9 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
                   for (int a = 0; a < p.h_accs; ++a) {
                     const uint32_t sa = pa + (uint32_t)(a * 16 + dy + 1) * p.h_pitch + (uint32_t)(dx + 1) * 128u;
                     // (no base offset: the 128-byte swizzle of TMA and UMMA is a function of the absolute shared-memory address
-                    // bits, measured -- a start shifted by whole rows reads what TMA wrote there; with base_offset = start row
-                    // mod 8 the results were wrong)
-                    const uint64_t ad = umma_desc(sa, 16u, p.h_pitch, p.h_bo_mode ? (uint32_t)(dx + 1) : 0u);
+                    // bits, measured -- a start shifted by whole rows, and groups 1280 bytes apart, read what TMA wrote there; with
+                    // the descriptor's base_offset set to the start row mod 8 the results were wrong)
+                    const uint64_t ad = umma_desc(sa, 16u, p.h_pitch);
 #pragma unroll
                     for (int k = 0; k < BK / 16; ++k)
                       if (k < ksteps) {
@@ -1010,7 +1010,6 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
   }
   // Halo-patch form (see KP): stride-1 3x3 convolutions whose image tiles into 8 x (16 * accumulators * CTAs) pixel tiles
   if (g_halo < 0) g_halo = getenv("B3D_HALO") ? atoi(getenv("B3D_HALO")) : 2;
-  static const int halo_bo = getenv("B3D_HALO_BO") ? atoi(getenv("B3D_HALO_BO")) : 0;
   if (g_halo && d->a_major == 0 && d->b_major == 0 && !d->batched && s == 1 && d->pad == 1 && p.epi_tma && !d->out_fp32) {
     bool any9 = false, ok = d->n_src >= 1 && d->n_src <= 3;
     for (int i = 0; ok && i < d->n_src; ++i) { if (d->a_taps[i] == 9) any9 = true; else if (d->a_taps[i] != 1) ok = false; }
@@ -1019,7 +1018,7 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
     const uint32_t hbytes = ((uint32_t)(16 * accs + 2) * hpitch + 1023u) / 1024u * 1024u;
     const long long room = (long long)kMaxDynSmem - 1024 - epi_bytes - 2LL * hbytes;
     if (ok && any9 && d->W % 8 == 0 && d->H % th == 0 && room >= 2LL * p.b_bytes) {
-      p.halo = 1; p.h_accs = accs; p.h_rows = 16 * accs + 2; p.h_stage_bytes = hbytes; p.a_stages = 2; p.h_bo_mode = (uint32_t)halo_bo; p.h_pitch = hpitch;
+      p.halo = 1; p.h_accs = accs; p.h_rows = 16 * accs + 2; p.h_stage_bytes = hbytes; p.a_stages = 2; p.h_pitch = hpitch;
       p.b_stages = (int)(room / p.b_bytes); if (p.b_stages > 8) p.b_stages = 8;
       if (room - (long long)p.b_stages * p.b_bytes >= (long long)hbytes && p.b_stages >= 4) { p.a_stages = 3; }      // a third patch when it is free
       else if (p.b_stages > 4 && room - 4LL * p.b_bytes >= (long long)hbytes) { p.a_stages = 3; p.b_stages = (int)((room - hbytes) / p.b_bytes); if (p.b_stages > 8) p.b_stages = 8; }

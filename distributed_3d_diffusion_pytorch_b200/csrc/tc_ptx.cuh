@@ -160,15 +160,15 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* v) {
 // UMMA shared-memory descriptor (sm_100): start>>4 [0,14) | LBO>>4 [16,30) | SBO>>4 [32,46) | version=1 [46,48)
 // | layout SWIZZLE_128B=2 [61,64).  K-major: SBO = 8 rows * 128 B; LBO unused.  MN-major: LBO = byte stride
 // between 64-element chunks of the M/N extent, SBO = 8 K-rows * 128 B.
-// base_offset [49,52): (start address >> 7) & 7 when the matrix does not start on a 1024-byte boundary of the swizzle pattern
-// (the halo-patch convolution reads its A operand from a start shifted by whole 128-byte rows).
-__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t base_offset = 0) {
+// The start address may be any 16-byte-aligned address and SBO any multiple of 16: the 128-byte swizzle is taken from the
+// absolute shared-memory address bits (measured with the halo-patch convolution, which starts its A operand on whole
+// 128-byte rows inside a TMA-written patch and steps 1280 bytes between 8-row groups; base_offset stays 0).
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
   uint64_t d = 0;
   d |= (uint64_t)((saddr >> 4) & 0x3FFF);
   d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
   d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
   d |= (uint64_t)1 << 46;
-  d |= (uint64_t)(base_offset & 7u) << 49;
   d |= (uint64_t)2 << 61;
   return d;
 }

@@ -146,3 +146,30 @@ def test_gn_cluster_fused_launch_equals_two_launches(N, HW, C0, C1):
             if u is not None:
                 tol = 2e-3 if u.dtype == torch.bfloat16 else 2e-4        # same arithmetic, partial sums combined in another order
                 assert _cmp(v, u) <= tol, (mode, i, _cmp(v, u))
+
+
+@pytest.mark.parametrize("idx", [0, 2, 3, 4, 5, 7, 9])
+def test_conv_halo_patch_form_equals_tile_load_form(idx):
+    """stride-1 3x3 convolutions: the halo-patch form (one input patch per 64-channel block in shared memory, nine taps through
+    shifted UMMA descriptors; packed rows = mode 2, 2048-byte row pitch = mode 1) against nine shifted tile loads (mode 0) on the
+    same descriptor -- single CTA, two accumulators, CTA pairs, several sources with 9 and 1 taps, partial channel blocks"""
+    import check_halo
+    from distributed_3d_diffusion_pytorch_b200 import _lib
+    from distributed_3d_diffusion_pytorch_b200.ops import CudaOps
+    ops = CudaOps("cuda:0")
+    name, case = check_halo.CASES[idx]
+    d, outs = case.build(ops)
+    res = {}
+    try:
+        for mode in (0, 1, 2):
+            _lib.set_conv_halo(mode)
+            for o in outs:
+                o.zero_()
+            ops.gemm(d)
+            torch.cuda.synchronize()
+            res[mode] = [o.clone() for o in outs]
+    finally:
+        _lib.set_conv_halo(2)
+    for mode in (1, 2):
+        for a, b in zip(res[mode], res[0]):
+            assert _cmp(a, b) <= 1e-3, (name, mode, _cmp(a, b))        # same products, summed channel block by channel block instead of tap by tap

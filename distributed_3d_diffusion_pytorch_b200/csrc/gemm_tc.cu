@@ -196,7 +196,7 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
         auto advance = [&]() { if (++stage == S) { stage = 0; phase ^= 1; } };
         if (p.halo) {
           // (stage / phase above are the weight-tile ring's; hs / hphase the patch ring's -- both persist across tiles)
-          const int px = c.x0 - 1, py = c.y0 + half_y - 1, pn = c.n0;
+          const int px = c.x0 - 1, py = c.y0 + half_y - 1, pn = c.n0 + half_n;
           const uint32_t a_bytes_patch = (uint32_t)p.h_rows * 1280u, a_bytes_center = (uint32_t)(p.h_rows - 2) * 1280u;
           for (int q = 0; q < p.n_hsrc; ++q) {
             const auto hq = p.hsrc[q];
@@ -1017,12 +1017,15 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
     const uint32_t hpitch = g_halo == 2 ? 1280u : 2048u;
     const uint32_t hbytes = ((uint32_t)(16 * accs + 2) * hpitch + 1023u) / 1024u * 1024u;
     const long long room = (long long)kMaxDynSmem - 1024 - epi_bytes - 2LL * hbytes;
-    if (ok && any9 && d->W % 8 == 0 && d->H % th == 0 && room >= 2LL * p.b_bytes) {
+    // a CTA pair whose tile would be taller than the image takes two images instead (16 x 16 level): rank 1 = image n + 1
+    const bool pair_images = p.c2 && !p.m2 && d->H % th != 0 && d->H % 16 == 0 && d->N % 2 == 0;
+    if (ok && any9 && d->W % 8 == 0 && (d->H % th == 0 || pair_images) && room >= 2LL * p.b_bytes) {
       p.halo = 1; p.h_accs = accs; p.h_rows = 16 * accs + 2; p.h_stage_bytes = hbytes; p.a_stages = 2; p.h_pitch = hpitch;
       p.b_stages = (int)(room / p.b_bytes); if (p.b_stages > 8) p.b_stages = 8;
       if (room - (long long)p.b_stages * p.b_bytes >= (long long)hbytes && p.b_stages >= 4) { p.a_stages = 3; }      // a third patch when it is free
       else if (p.b_stages > 4 && room - 4LL * p.b_bytes >= (long long)hbytes) { p.a_stages = 3; p.b_stages = (int)((room - hbytes) / p.b_bytes); if (p.b_stages > 8) p.b_stages = 8; }
       m2_bw = 8; m2_bh = th; m2_bnn = 1; p.m2_dim = 1;
+      if (pair_images) { m2_bh = 16; m2_bnn = 2; p.m2_dim = 2; }
     }
   }
   p.stage_bytes = p.a_bytes + p.b_bytes;

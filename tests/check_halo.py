@@ -21,6 +21,8 @@ CASES = [
     ("pair x2 256+128 -> 128 @64x64 N=256", gc.conv_case("c", 256, 64, 64, [256, 128], [9, 9], 128)),
     ("pair wide 256->256 @32x32 N=256", gc.conv_case("c", 256, 32, 32, [256], [9], 256)),
     ("pair wide 128->256 @64x64 N=256", gc.conv_case("c", 256, 64, 64, [128], [9], 256)),
+    ("pair wide over 2 images 256->256 @16x16 N=256", gc.conv_case("c", 256, 16, 16, [256], [9], 256)),
+    ("pair wide over 2 images 768->256 @16x16 N=256", gc.conv_case("c", 256, 16, 16, [512, 256], [9, 9], 256)),
     ("pair x2 conv2+skip [9,1,1] 128 @64x64 N=256", gc.conv_case("c", 256, 64, 64, [128, 256, 128], [9, 1, 1], 128, rowvec=True, out_scale=0.7071)),
 ]
 

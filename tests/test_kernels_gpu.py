@@ -148,7 +148,7 @@ def test_gn_cluster_fused_launch_equals_two_launches(N, HW, C0, C1):
                 assert _cmp(v, u) <= tol, (mode, i, _cmp(v, u))
 
 
-@pytest.mark.parametrize("idx", [0, 2, 3, 4, 5, 7, 9])
+@pytest.mark.parametrize("idx", [0, 2, 3, 4, 5, 7, 9, 10, 11])
 def test_conv_halo_patch_form_equals_tile_load_form(idx):
     """stride-1 3x3 convolutions: the halo-patch form (one input patch per 64-channel block in shared memory, nine taps through
     shifted UMMA descriptors; packed rows = mode 2, 2048-byte row pitch = mode 1) against nine shifted tile loads (mode 0) on the

@@ -4,7 +4,7 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb3d.so")
+LIB_PATH = os.environ.get("B3D_LIB") or os.path.join(_HERE, "libb3d.so")      # (B3D_LIB: A/B measurements against another build)
 _lib = None
 
 

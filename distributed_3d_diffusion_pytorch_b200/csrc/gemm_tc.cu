@@ -26,10 +26,10 @@ namespace {
 
 constexpr int BM = 128;
 constexpr int BK = 64;  // bf16 elements = one 128-byte swizzle row
-constexpr int kThreads = 192;
+constexpr int kThreads = 320;   // warp 0 TMA, warp 1 MMA, warps 2..5 and 6..9: two epilogue groups
 constexpr int kMaxSeg = 27;
 constexpr uint32_t kABytes = BM * BK * 2;  // 16 KB in both majors
-constexpr int kMaxDynSmem = 227 * 1024 - 2048;  // 227 KB per CTA minus the static barriers and bias slice
+constexpr int kMaxDynSmem = 227 * 1024 - 3072;  // 227 KB per CTA minus the static barriers and the two bias slices
 
 struct Seg {
   int32_t src, dx, dy, ncb, bk0;
@@ -134,7 +134,7 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
   __shared__ uint64_t bars[2 * 8 + 4 + 2];
   __shared__ uint64_t abars[2 * 3];                  // halo form: full / empty barriers of the patch ring
   __shared__ uint32_t tmem_base_smem;
-  __shared__ __align__(16) float s_bias[256];   // bias slice of the current N tile (bf16 TMA epilogue)
+  __shared__ __align__(16) float s_bias2[2][256];   // bias slice of the current N tile, one copy per epilogue group (bf16 TMA epilogue)
 
   // warp index through a shuffle so the compiler knows it is warp-uniform: the producer and MMA loops below then run on
   // uniform registers (a `lane == 0` region made every TMA / MMA operand go through an ELECT + R2UR.BROADCAST loop, and
@@ -153,7 +153,7 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
   if (threadIdx.x == 0) {
     for (int s = 0; s < (p.halo ? p.b_stages : S); ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
     for (int s = 0; s < 3; ++s) { mbar_init(afull_bar(s), 1); mbar_init(aempty_bar(s), 1); }
-    for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), kPair ? 8 : 4); mbar_init(resid_bar(s), 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), (kPair ? 2u : 1u) * ((p.epi_tma && !p.out_fp32) ? 8u : 4u)); mbar_init(resid_bar(s), 1); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (threadIdx.x == 64) {      // descriptor fetches overlap the barrier init / TMEM allocation (short launches are latency-bound)
@@ -420,6 +420,8 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
+  } else if (warp >= 6 && !(p.epi_tma && !p.out_fp32)) {
+    // (the second epilogue group only works in the bf16 TMA-store epilogue)
   } else if (p.epi_tma && p.out_fp32) {
     // ===================================================================== epilogue, fp32 outputs through TMA (warps 2..5)
     // 32 fp32 columns (one 128-byte row) per round: TMEM -> registers -> epilogue math -> swizzled smem tile -> TMA store,
@@ -507,16 +509,31 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
     // TMEM -> registers -> (bias / per-image vector / residual / scale / SiLU) -> bf16 -> 128B-swizzled smem tile
     // -> TMA store.  The residual tile arrives by TMA load.  64 output columns (one 128-byte row) per round,
     // double buffered, so global memory sees only full-line bulk transfers and the LSU only shared memory.
+    // Two groups of four warps (2..5 and 6..9; a warp reads the TMEM lanes of its quadrant warp & 3): the 64-column rounds of a
+    // tile alternate between them, each group with its own staging tile, residual tile, barrier and TMA-issuing leader.  With
+    // one group the epilogue of the 128-column tiles was as long as their mainloop; a single warp per scheduler cannot hide
+    // its own TMEM / shared-memory latencies.
     const int quad = warp & 3;
     const int r = quad * 32 + lane;
-    const bool leader = threadIdx.x == 64;
-    const uint32_t so_base = smem_base + p.epi_off;
-    const uint32_t sx_base = so_base + 2 * 16384;
+    const int grp = (warp - 2) >> 2;
+    const bool leader = threadIdx.x == 64 + grp * 128;
+    float* s_bias = s_bias2[grp];
+    auto grp_sync = [&]() { asm volatile("bar.sync %0, 128;" ::"r"(1 + grp) : "memory"); };
+    const uint32_t so_base = smem_base + p.epi_off + (uint32_t)grp * 16384u;
+    const uint32_t sx_base = smem_base + p.epi_off + 2 * 16384 + (uint32_t)grp * 16384u;
     const uint32_t rows_bytes = p.a_major == 0 ? (uint32_t)(p.bw * p.bh * p.bnn) * 128u : 128u * 128u;
     int acc = 0; uint32_t acc_phase = 0;
-    int buf = 0; uint32_t rphase0 = 0, rphase1 = 0;
+    uint32_t rphase = 0;
     int bias_tn = -1;
     const uint32_t swz = (uint32_t)(r & 7);
+    auto arrive_tempty = [&]() {       // this warp has read all it needs of the accumulator(s)
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        if constexpr (kPair) mbar_arrive_cluster(mapa_shared(tempty_bar(acc), 0u));
+        else mbar_arrive(tempty_bar(acc));
+      }
+    };
     for (int t = t_first; t < p.tiles_total; t += t_step) {
       const TileCoord c = decode_tile(p, t);
       int cx, cy, cn, img;
@@ -528,43 +545,39 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
         cx = c.m0; cy = c.y0; cn = c.n0 ^ p.o_xor; img = c.n0;
       }
       const int nch = (min(p.BN, p.n_cols - c.tn * p.BN) + 63) / 64;
-      const int rounds = (1 + p.m2) * nch;      // (accumulator half, 64-column chunk), half-major
+      const int rounds = (1 + p.m2) * nch;      // (accumulator half, 64-column chunk), half-major; round rd belongs to group rd & 1
       if (p.bias && c.tn != bias_tn) {            // stage this N tile's bias slice in shared memory (zeros past n_cols): the
-        epi_bar_sync();                           // per-round __ldg's of it sat on the critical path of short-K tiles
+        grp_sync();                               // per-round __ldg's of it sat on the critical path of short-K tiles
         for (int i = r; i < 256; i += 128) s_bias[i] = (i < p.BN && c.tn * p.BN + i < p.n_cols) ? __ldg(p.bias + c.tn * p.BN + i) : 0.f;
         bias_tn = c.tn;
-        epi_bar_sync();
+        grp_sync();
       }
       // output-box origin of a half: the second 128 rows of a doubled tile continue along m2_dim (x / y / image)
       const int cx0 = cx, cy0 = cy, cn0 = cn, img0 = img;
       const int hx = p.m2_dim == 0 ? p.bw : 0, hy = p.m2_dim == 1 ? p.bh : 0, hn = p.m2_dim == 2 ? p.bnn : 0;
-      if (p.resid != nullptr && leader) {
-        mbar_expect_tx(resid_bar(buf), rows_bytes);
-        tma_load_4d(sx_base + buf * 16384, &p.tmR, resid_bar(buf), c.tn * p.BN, cx, cy, cn);
-      }
+      auto load_resid = [&](int rd) {             // (leader) residual tile of round rd into this group's tile
+        const int nh = rd >= nch ? 1 : 0, nc = rd - nh * nch;
+        mbar_expect_tx(resid_bar(grp), rows_bytes);
+        tma_load_4d(sx_base, &p.tmR, resid_bar(grp), c.tn * p.BN + nc * 64, cx0 + nh * hx, cy0 + nh * hy, cn0 + nh * hn);
+      };
+      if (p.resid != nullptr && leader && grp < rounds) load_resid(grp);
       mbar_wait(tfull_bar(acc), acc_phase);
       tc_fence_after();
       const uint32_t taddr0 = tmem_base + (uint32_t)(acc * p.acc_stride) + ((uint32_t)(quad * 32) << 16);
-      for (int rd = 0; rd < rounds; ++rd) {
+      if (grp >= rounds) arrive_tempty();         // a one-round tile: nothing to read for the second group
+      for (int rd = grp; rd < rounds; rd += 2) {
         const int half = rd >= nch ? 1 : 0, ch = rd - half * nch;
         cx = cx0 + half * hx; cy = cy0 + half * hy; cn = cn0 + half * hn;
         img = img0 + half * hn; if (img >= p.N) img = p.N - 1;
         const uint32_t taddr = taddr0 + (uint32_t)half * p.acc_half;
         const int col0 = c.tn * p.BN + ch * 64;
-        if (leader) {
-          if (p.resid != nullptr && rd + 1 < rounds) {
-            const int nh = rd + 1 >= nch ? 1 : 0, nc = rd + 1 - nh * nch;
-            mbar_expect_tx(resid_bar(buf ^ 1), rows_bytes);
-            tma_load_4d(sx_base + (buf ^ 1) * 16384, &p.tmR, resid_bar(buf ^ 1), c.tn * p.BN + nc * 64, cx0 + nh * hx, cy0 + nh * hy,
-                        cn0 + nh * hn);
-          }
-          tma_store_wait_read<1>();      // the store that last used this buffer has finished reading it
-        }
-        epi_bar_sync();
+        if (leader) tma_store_wait_read<0>();      // the store that last used this group's tile(s) has finished reading
+        grp_sync();
         if (p.resid != nullptr) {
-          mbar_wait(resid_bar(buf), buf ? rphase1 : rphase0);
-          if (buf) rphase1 ^= 1; else rphase0 ^= 1;
+          mbar_wait(resid_bar(grp), rphase);
+          rphase ^= 1;
         }
+        constexpr int buf = 0;
         const uint32_t orow = so_base + buf * 16384 + (uint32_t)r * 128u;
         const uint32_t xrow = sx_base + buf * 16384 + (uint32_t)r * 128u;
 #pragma unroll
@@ -634,20 +647,14 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
             }
           }
         }
-        if (rd == rounds - 1) {          // accumulator(s) fully read: hand the TMEM buffer back to the (leader's) MMA warp
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) {
-            if constexpr (kPair) mbar_arrive_cluster(mapa_shared(tempty_bar(acc), 0u));
-            else mbar_arrive(tempty_bar(acc));
-          }
-        }
+        if (rd + 2 >= rounds) arrive_tempty();      // this group's last round of the tile: hand the TMEM buffer back to the MMA warp
         fence_proxy_async();
-        epi_bar_sync();
+        grp_sync();
         if (leader) {
           tma_store_4d(&p.tmO, so_base + buf * 16384, col0, cx, cy, cn);
           if (p.out2) tma_store_4d(&p.tmO2, sx_base + buf * 16384, col0, cx, cy, cn);
           tma_store_commit();
+          if (p.resid != nullptr && rd + 2 < rounds) load_resid(rd + 2);     // (the group has finished reading its residual tile)
         }
         if (p.gn_sums != nullptr) {
           // GroupNorm statistics of the tile just staged (the consumer's gn_stats pass over HBM disappears): thread t sums
@@ -696,7 +703,6 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
             atomicAdd(dst + 1, s2);
           }
         }
-        buf ^= 1;
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }

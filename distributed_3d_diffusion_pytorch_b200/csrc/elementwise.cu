@@ -751,19 +751,31 @@ __device__ __forceinline__ int find_job(const PackJob* jobs, int n_jobs, long lo
   return lo;
 }
 
-// Weight repack, one 32 x 32 (x taps) tile of the [Co, Ci, taps] fp32 source per block: the tile is read with the
-// source's own contiguity (32*taps consecutive floats per output channel, 8 independent loads in flight per thread),
-// transposed through shared memory and written as 64-byte runs of bf16 in the destination layout (element-wise indexing
-// by destination made either the 36-byte-strided reads or the 2-byte scattered writes uncoalesced: 0.9 TB/s).
-// TAPS = 9 / 1 compile the index divisions to multiplies; 0 = any tap count <= 9 at run time.
+// The per-step repack of ALL parameters: one launch over a table of groups.  A group = one fp32 source tensor [Co, Ci, taps]
+// and up to kMaxPackDst destinations built from it (forward operand, per-source column ranges of a concatenated input,
+// the [conv2 | skip] operand, the transposed operand of the data gradient ...): each 32 x 32 (x taps) source tile is read
+// ONCE, with the source's own contiguity, and written to every destination from shared memory as 4-byte bf16 pairs (128
+// contiguous bytes per warp).  Pad columns / rows of the destinations are never written: the caller zeroes the operands once.
+// block -> group through a table (a binary search over block0 cost ~9 dependent L2 reads per block, 40 % of a block's life).
+constexpr int kMaxPackDst = 8;
+struct PackDst { void* dst; int mode, ci0, cn, Cpad; long long k_off, ld; };
+struct PackGroup {
+  const float* src;
+  int Co, Ci, taps, n_dst;
+  long long total, block0;      // total: element count of a mode-3 copy group
+  PackDst d[kMaxPackDst];
+};
+
+__device__ __forceinline__ void store_pair(bf16* o, float v0, float v1, bool ok0, bool ok1) {
+  if (ok0 && ok1 && (reinterpret_cast<uintptr_t>(o) & 3) == 0) *reinterpret_cast<__nv_bfloat162*>(o) = __floats2bfloat162_rn(v0, v1);
+  else { if (ok0) o[0] = __float2bfloat16(v0); if (ok1) o[1] = __float2bfloat16(v1); }
+}
+
 template <int TAPS>
-__device__ __forceinline__ void pack_tile(const PackJob& J, long long blk, float* tile) {
-  const float* __restrict__ w = J.src;
-  bf16* __restrict__ out = reinterpret_cast<bf16*>(J.dst);
-  const int taps = TAPS ? TAPS : J.taps, rl = 32 * taps, rs = rl + 1, n = 32 * rl;
-  // tile grid: x = input-channel tiles (mode 0: over the padded width Cpad), y = output-channel tiles (mode 1: over Cpad)
-  const int in_ext = J.mode == 0 ? J.Cpad : J.Ci, in_valid = J.mode == 0 ? J.cn : J.Ci;
-  const int tiles_in = (in_ext + 31) / 32;
+__device__ __forceinline__ void pack_group_tile(const PackGroup& G, long long blk, float* tile) {
+  const float* __restrict__ w = G.src;
+  const int taps = TAPS ? TAPS : G.taps, rl = 32 * taps, rs = rl + 1, n = 32 * rl, Co = G.Co, Ci = G.Ci;
+  const int tiles_in = (Ci + 31) / 32;
   const int c_in0 = (int)(blk % tiles_in) * 32, co0 = (int)(blk / tiles_in) * 32;
   constexpr int U = 8;
   for (int e0 = threadIdx.x; e0 < n; e0 += 256 * U) {
@@ -772,57 +784,64 @@ __device__ __forceinline__ void pack_tile(const PackJob& J, long long blk, float
     for (int u = 0; u < U; ++u) {
       const int e = e0 + u * 256;
       const int co_l = e / rl, r = e - co_l * rl, ci_l = r / taps;
-      const int co = co0 + co_l, ci = c_in0 + ci_l;
       idx[u] = e < n ? e + co_l : -1;
-      v[u] = (e < n && co < J.Co && ci < in_valid) ? w[((long long)co * J.Ci + J.ci0 + c_in0) * taps + r] : 0.f;
+      v[u] = (e < n && co0 + co_l < Co && c_in0 + ci_l < Ci) ? w[((long long)(co0 + co_l) * Ci + c_in0) * taps + r] : 0.f;
     }
 #pragma unroll
     for (int u = 0; u < U; ++u) if (idx[u] >= 0) tile[idx[u]] = v[u];
   }
   __syncthreads();
-  if (J.mode == 0) {          // out[co, k_off + tap*Cpad + cc]
-#pragma unroll 4
-    for (int e = threadIdx.x; e < n; e += 256) {
-      const int co_l = e / rl, r = e - co_l * rl, tap = r >> 5, cc_l = r & 31;
-      const int co = co0 + co_l, cc = c_in0 + cc_l;
-      if (co < J.Co && cc < J.Cpad) out[(long long)co * J.ld + J.k_off + (long long)tap * J.Cpad + cc] = __float2bfloat16(tile[co_l * rs + cc_l * taps + tap]);
-    }
-  } else {                    // mode 1: out[ci, k_off + tp*Cpad + co], taps flipped;  mode 2: out[(tap*Ci + ci), co]
-    const int co_ext = J.mode == 1 ? J.Cpad : J.Co;
-#pragma unroll 4
-    for (int e = threadIdx.x; e < n; e += 256) {
-      const int ci_l = e / rl, r = e - ci_l * rl, tp = r >> 5, co_l = r & 31;
-      const int ci = c_in0 + ci_l, co = co0 + co_l;
-      if (ci >= J.Ci || co >= co_ext) continue;
-      if (J.mode == 1) out[(long long)ci * J.ld + J.k_off + (long long)tp * J.Cpad + co] = __float2bfloat16(tile[co_l * rs + ci_l * taps + (taps - 1 - tp)]);
-      else out[((long long)tp * J.Ci + ci) * J.ld + co] = __float2bfloat16(tile[co_l * rs + ci_l * taps + tp]);
+  const int hl = 16 * taps;            // pairs per tile row
+  for (int k = 0; k < G.n_dst; ++k) {
+    const PackDst D = G.d[k];
+    bf16* __restrict__ out = reinterpret_cast<bf16*>(D.dst);
+    if (D.mode == 0) {        // out[co, k_off + tap*Cpad + (ci - ci0)] for ci in [ci0, ci0 + cn)
+      if (c_in0 + 32 <= D.ci0 || c_in0 >= D.ci0 + D.cn) continue;
+#pragma unroll 2
+      for (int e = threadIdx.x; e < 32 * hl; e += 256) {
+        const int co_l = e / hl, r = e - co_l * hl, tap = r >> 4, cp = (r & 15) * 2;
+        const int co = co0 + co_l, cc = c_in0 + cp - D.ci0;
+        if (co >= Co) continue;
+        const float* t = tile + co_l * rs + cp * taps + tap;
+        store_pair(out + (long long)co * D.ld + D.k_off + (long long)tap * D.Cpad + cc, t[0], t[taps], cc >= 0 && cc < D.cn, cc + 1 >= 0 && cc + 1 < D.cn);
+      }
+    } else {                  // mode 1: out[ci, k_off + tp*Cpad + co], taps flipped;  mode 2: out[(tp*Ci + ci), co]
+#pragma unroll 2
+      for (int e = threadIdx.x; e < 32 * hl; e += 256) {
+        const int ci_l = e / hl, r = e - ci_l * hl, tp = r >> 4, cp = (r & 15) * 2;
+        const int ci = c_in0 + ci_l, co = co0 + cp;
+        if (ci >= Ci) continue;
+        const float* t = tile + cp * rs + ci_l * taps + (D.mode == 1 ? taps - 1 - tp : tp);
+        bf16* o = D.mode == 1 ? out + (long long)ci * D.ld + D.k_off + (long long)tp * D.Cpad + co : out + ((long long)tp * Ci + ci) * D.ld + co;
+        store_pair(o, t[0], t[rs], co < Co, co + 1 < Co);
+      }
     }
   }
 }
 
-__global__ void __launch_bounds__(256) pack_multi_kernel(const PackJob* __restrict__ jobs, int n_jobs) {
+__global__ void __launch_bounds__(256) pack_groups_kernel(const PackGroup* __restrict__ groups, const int* __restrict__ block_group) {
   __shared__ float tile[32 * (32 * 9 + 1)];
-  const int j = find_job(jobs, n_jobs, blockIdx.x);
-  const PackJob J = jobs[j];
-  const long long blk = (long long)blockIdx.x - J.block0;
-  if (J.mode == 3) {          // flat fp32 copy, 1024 values per block
+  const PackGroup& G = groups[block_group[blockIdx.x]];
+  const long long blk = (long long)blockIdx.x - G.block0;
+  if (G.d[0].mode == 3) {     // flat fp32 copy, 1024 values per block
+    float* dst = reinterpret_cast<float*>(G.d[0].dst);
     for (int k = 0; k < 4; ++k) {
       const long long i = blk * 1024 + k * 256 + threadIdx.x;
-      if (i < J.total) reinterpret_cast<float*>(J.dst)[i] = J.src[i];
+      if (i < G.total) dst[i] = G.src[i];
     }
     return;
   }
-  if (J.taps == 9) pack_tile<9>(J, blk, tile);
-  else if (J.taps == 1) pack_tile<1>(J, blk, tile);
-  else pack_tile<0>(J, blk, tile);
+  if (G.taps == 9) pack_group_tile<9>(G, blk, tile);
+  else if (G.taps == 1) pack_group_tile<1>(G, blk, tile);
+  else pack_group_tile<0>(G, blk, tile);
 }
 
 // Packed fp32 weight gradients [Co, k_off + tap*Cpad + cc] -> PyTorch layout [Co, Ci, taps], one 32 x 32 (x taps) tile per
 // block through shared memory: 128-byte runs on the read side, 32*taps consecutive floats per output channel on the write
 // side (indexing by destination element read with a 4*Cpad-byte stride between neighbouring threads).
-__global__ void __launch_bounds__(256) unpack_multi_kernel(const PackJob* __restrict__ jobs, int n_jobs) {
+__global__ void __launch_bounds__(256) unpack_multi_kernel(const PackJob* __restrict__ jobs, int n_jobs, const int* __restrict__ block_job) {
   __shared__ float tile[32 * (32 * 9 + 1)];
-  const int j = find_job(jobs, n_jobs, blockIdx.x);
+  const int j = block_job ? block_job[blockIdx.x] : find_job(jobs, n_jobs, blockIdx.x);
   const PackJob J = jobs[j];
   const long long blk = (long long)blockIdx.x - J.block0;
   const float* __restrict__ g = J.src;
@@ -1116,14 +1135,15 @@ extern "C" int b3d_scale_colsum(const void* a, void* out, float scale, int64_t r
   B3D_CUDA(b3d_launch_pdl(scale_colsum_kernel, dim3(cdiv(rows, rpb)), dim3(256), 2048 * sizeof(float), STREAM, (const bf16*)a, (bf16*)out, scale, rows, C, (int)rpb, colsum));
   DONE(1);
 }
-// jobs: device array of b3d_pack_job (include/b3d.h) whose block0 fields are the running sum of ceil(total/1024)
-extern "C" int b3d_pack_weights_multi(const void* jobs, int n_jobs, int64_t total_blocks, void* stream) {
-  B3D_CHECK_ARG(jobs && n_jobs > 0 && total_blocks > 0, "pack_weights_multi: args");
-  pack_multi_kernel<<<(unsigned)total_blocks, 256, 0, STREAM>>>((const PackJob*)jobs, n_jobs);
+// groups: device array of b3d_pack_group (include/b3d.h); block_group: device array, group index of every block
+extern "C" int b3d_pack_weights_multi(const void* groups, int n_groups, const int32_t* block_group, int64_t total_blocks, void* stream) {
+  B3D_CHECK_ARG(groups && block_group && n_groups > 0 && total_blocks > 0, "pack_weights_multi: args");
+  static_assert(sizeof(PackGroup) == sizeof(b3d_pack_group), "b3d_pack_group layout");
+  pack_groups_kernel<<<(unsigned)total_blocks, 256, 0, STREAM>>>((const PackGroup*)groups, block_group);
   DONE(1);
 }
-extern "C" int b3d_unpack_wgrads_multi(const void* jobs, int n_jobs, int64_t total_blocks, void* stream) {
+extern "C" int b3d_unpack_wgrads_multi(const void* jobs, int n_jobs, const int32_t* block_job, int64_t total_blocks, void* stream) {
   B3D_CHECK_ARG(jobs && n_jobs > 0 && total_blocks > 0, "unpack_wgrads_multi: args");
-  unpack_multi_kernel<<<(unsigned)total_blocks, 256, 0, STREAM>>>((const PackJob*)jobs, n_jobs);
+  unpack_multi_kernel<<<(unsigned)total_blocks, 256, 0, STREAM>>>((const PackJob*)jobs, n_jobs, block_job);
   DONE(1);
 }

@@ -77,6 +77,7 @@ struct alignas(64) KP {
   struct HSrc { int32_t src, taps, ncb, bk0, klast; } hsrc[3];
   int halo, n_hsrc, h_accs, h_rows, a_stages, b_stages;
   uint32_t h_stage_bytes, b_ring_off, h_pitch;   // h_pitch: bytes between patch rows (1280 = packed, one TMA load per patch; 2048 = one load per row)
+  int resid2;           // two residual tiles per epilogue group (the next round's residual loads while this round computes)
   int epi_tma;          // bf16 outputs leave through shared memory + TMA store (coalesced, no LSU global traffic)
   uint32_t epi_off;     // byte offset of the epilogue staging buffers inside dynamic smem
 };
@@ -131,7 +132,7 @@ __device__ __forceinline__ void k_range(const KP& p, const TileCoord& c, int& kb
 template <bool kPair>
 __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_constant__ KP p) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ uint64_t bars[2 * 8 + 4 + 2];
+  __shared__ uint64_t bars[2 * 8 + 4 + 4];
   __shared__ uint64_t abars[2 * 3];                  // halo form: full / empty barriers of the patch ring
   __shared__ uint32_t tmem_base_smem;
   __shared__ __align__(16) float s_bias2[2][256];   // bias slice of the current N tile, one copy per epilogue group (bf16 TMA epilogue)
@@ -153,7 +154,7 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
   if (threadIdx.x == 0) {
     for (int s = 0; s < (p.halo ? p.b_stages : S); ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
     for (int s = 0; s < 3; ++s) { mbar_init(afull_bar(s), 1); mbar_init(aempty_bar(s), 1); }
-    for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), (kPair ? 2u : 1u) * ((p.epi_tma && !p.out_fp32) ? 8u : 4u)); mbar_init(resid_bar(s), 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), (kPair ? 2u : 1u) * ((p.epi_tma && !p.out_fp32) ? 8u : 4u)); mbar_init(resid_bar(s), 1); mbar_init(resid_bar(2 + s), 1); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (threadIdx.x == 64) {      // descriptor fetches overlap the barrier init / TMEM allocation (short launches are latency-bound)
@@ -523,7 +524,9 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
     const uint32_t sx_base = smem_base + p.epi_off + 2 * 16384 + (uint32_t)grp * 16384u;
     const uint32_t rows_bytes = p.a_major == 0 ? (uint32_t)(p.bw * p.bh * p.bnn) * 128u : 128u * 128u;
     int acc = 0; uint32_t acc_phase = 0;
-    uint32_t rphase = 0;
+    uint32_t rph0 = 0, rph1 = 0;
+    int rb = 0;                                  // residual buffer of this group's current round
+    const uint32_t rstride = p.resid2 ? 2u * 16384u : 0u;
     int bias_tn = -1;
     const uint32_t swz = (uint32_t)(r & 7);
     auto arrive_tempty = [&]() {       // this warp has read all it needs of the accumulator(s)
@@ -555,12 +558,13 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
       // output-box origin of a half: the second 128 rows of a doubled tile continue along m2_dim (x / y / image)
       const int cx0 = cx, cy0 = cy, cn0 = cn, img0 = img;
       const int hx = p.m2_dim == 0 ? p.bw : 0, hy = p.m2_dim == 1 ? p.bh : 0, hn = p.m2_dim == 2 ? p.bnn : 0;
-      auto load_resid = [&](int rd) {             // (leader) residual tile of round rd into this group's tile
+      auto load_resid = [&](int rd, int b) {      // (leader) residual tile of round rd into buffer b of this group
         const int nh = rd >= nch ? 1 : 0, nc = rd - nh * nch;
-        mbar_expect_tx(resid_bar(grp), rows_bytes);
-        tma_load_4d(sx_base, &p.tmR, resid_bar(grp), c.tn * p.BN + nc * 64, cx0 + nh * hx, cy0 + nh * hy, cn0 + nh * hn);
+        mbar_expect_tx(resid_bar(grp * 2 + b), rows_bytes);
+        tma_load_4d(sx_base + (uint32_t)b * rstride, &p.tmR, resid_bar(grp * 2 + b), c.tn * p.BN + nc * 64, cx0 + nh * hx, cy0 + nh * hy,
+                    cn0 + nh * hn);
       };
-      if (p.resid != nullptr && leader && grp < rounds) load_resid(grp);
+      if (p.resid != nullptr && leader && grp < rounds) load_resid(grp, rb);
       mbar_wait(tfull_bar(acc), acc_phase);
       tc_fence_after();
       const uint32_t taddr0 = tmem_base + (uint32_t)(acc * p.acc_stride) + ((uint32_t)(quad * 32) << 16);
@@ -571,15 +575,18 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
         img = img0 + half * hn; if (img >= p.N) img = p.N - 1;
         const uint32_t taddr = taddr0 + (uint32_t)half * p.acc_half;
         const int col0 = c.tn * p.BN + ch * 64;
-        if (leader) tma_store_wait_read<0>();      // the store that last used this group's tile(s) has finished reading
+        if (leader) {
+          tma_store_wait_read<0>();                // the store that last used this group's tile(s) has finished reading
+          if (p.resid2 && rd + 2 < rounds) load_resid(rd + 2, rb ^ 1);      // next round's residual, into the other buffer
+        }
         grp_sync();
         if (p.resid != nullptr) {
-          mbar_wait(resid_bar(grp), rphase);
-          rphase ^= 1;
+          mbar_wait(resid_bar(grp * 2 + rb), rb ? rph1 : rph0);
+          if (rb) rph1 ^= 1; else rph0 ^= 1;
         }
         constexpr int buf = 0;
         const uint32_t orow = so_base + buf * 16384 + (uint32_t)r * 128u;
-        const uint32_t xrow = sx_base + buf * 16384 + (uint32_t)r * 128u;
+        const uint32_t xrow = sx_base + (uint32_t)rb * rstride + (uint32_t)r * 128u;
 #pragma unroll
         for (int hf = 0; hf < 2; ++hf) {
           const int cc = col0 + hf * 32;
@@ -654,8 +661,9 @@ __global__ void __launch_bounds__(kThreads, 1) b3d_gemm_kernel(const __grid_cons
           tma_store_4d(&p.tmO, so_base + buf * 16384, col0, cx, cy, cn);
           if (p.out2) tma_store_4d(&p.tmO2, sx_base + buf * 16384, col0, cx, cy, cn);
           tma_store_commit();
-          if (p.resid != nullptr && rd + 2 < rounds) load_resid(rd + 2);     // (the group has finished reading its residual tile)
+          if (p.resid != nullptr && !p.resid2 && rd + 2 < rounds) load_resid(rd + 2, 0);     // (the group has finished reading its residual tile)
         }
+        if (p.resid2) rb ^= 1;
         if (p.gn_sums != nullptr) {
           // GroupNorm statistics of the tile just staged (the consumer's gn_stats pass over HBM disappears): thread t sums
           // the cpg columns of group g over its slice of rows straight from the swizzled tile, slices of one (group, image)
@@ -951,7 +959,7 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
   p.b_chunks = (BN + 63) / 64;
   p.b_bytes = d->b_major ? (uint32_t)p.b_chunks * 8192u : (uint32_t)((BN * 128 + 1023) / 1024 * 1024);
   p.b_tx = d->b_major ? (uint32_t)p.b_chunks * 8192u : (uint32_t)BN * 128u;
-  const uint32_t epi_bytes = p.epi_tma ? ((d->resid || d->out2) ? 65536u : 32768u) : 0u;
+  uint32_t epi_bytes = p.epi_tma ? ((d->resid || d->out2) ? 65536u : 32768u) : 0u;
   // Narrow tiles (BN <= 128) of the convolution / dense form: 256 output rows per tile -- two 128-row accumulators fed
   // by ONE B tile.  A 128 x 128 tile loads 32 KB of operands per 2.1 MFLOP and is bound by the L2 -> SM operand path
   // (measured 1.0 PFLOP/s); 256 x 128 loads 48 KB per 4.2 MFLOP.  The doubled tile continues along the outermost
@@ -1022,10 +1030,15 @@ extern "C" int b3d_gemm(const b3d_gemm_desc* d, void* stream_) {
     const int accs = p.m2 ? 2 : 1, th = 16 * accs * (p.c2 ? 2 : 1);
     const uint32_t hpitch = g_halo == 2 ? 1280u : 2048u;
     const uint32_t hbytes = ((uint32_t)(16 * accs + 2) * hpitch + 1023u) / 1024u * 1024u;
-    const long long room = (long long)kMaxDynSmem - 1024 - epi_bytes - 2LL * hbytes;
+    // two residual tiles per epilogue group when the B ring keeps at least 4 stages with them (measurement switch B3D_NO_RESID2)
+    static const bool no_r2 = getenv("B3D_NO_RESID2") != nullptr;
+    const uint32_t r2_bytes = (d->resid && !d->out2 && !no_r2 &&
+                               (long long)kMaxDynSmem - 1024 - epi_bytes - 32768 - 2LL * hbytes >= 4LL * p.b_bytes) ? 32768u : 0u;
+    const long long room = (long long)kMaxDynSmem - 1024 - epi_bytes - r2_bytes - 2LL * hbytes;
     // a CTA pair whose tile would be taller than the image takes two images instead (16 x 16 level): rank 1 = image n + 1
     const bool pair_images = p.c2 && !p.m2 && d->H % th != 0 && d->H % 16 == 0 && d->N % 2 == 0;
     if (ok && any9 && d->W % 8 == 0 && (d->H % th == 0 || pair_images) && room >= 2LL * p.b_bytes) {
+      if (r2_bytes) { p.resid2 = 1; epi_bytes += r2_bytes; }
       p.halo = 1; p.h_accs = accs; p.h_rows = 16 * accs + 2; p.h_stage_bytes = hbytes; p.a_stages = 2; p.h_pitch = hpitch;
       p.b_stages = (int)(room / p.b_bytes); if (p.b_stages > 8) p.b_stages = 8;
       if (room - (long long)p.b_stages * p.b_bytes >= (long long)hbytes && p.b_stages >= 4) { p.a_stages = 3; }      // a third patch when it is free

@@ -526,6 +526,8 @@ __global__ void __launch_bounds__(kT, MODE == 2 ? kBwdBlocks2 : kBwdBlocks1) gn_
 int pick_rows_per_block(int N, int HW, int C, int U, int blocks_per_sm, int waves = 8) {
   const int vecs = C / 8;
   const int rows_par = 256 / vecs > 0 ? 256 / vecs : 1;
+  static const int forced = getenv("B3D_GN_RPB") ? atoi(getenv("B3D_GN_RPB")) : 0;      // measurement switch
+  if (forced > 0) { int r = (forced + rows_par - 1) / rows_par * rows_par; return r > HW ? HW : r; }
   int per_img = (b3d_num_sms() * blocks_per_sm * waves + N - 1) / N;
   if (per_img < 1) per_img = 1;
   int rpb = (HW + per_img - 1) / per_img;

@@ -215,9 +215,29 @@ class Engine:
         return name.startswith((cp + "logsnr_emb_emb", cp + "convs.0.", "conv.", "xunetblocks.0.", "film0"))
 
     def _record_pack(self, P, training):
+        """Every job is recorded twice: in the (first, rest) lists a forward runs, and in the list of its parameter's group --
+        0 / 1 / 2 = the backward phase that finalises the parameter's gradient (PHASE_PREFIXES), 3 = the level-wide FiLM
+        operands, which phase 2's data-gradient GEMM still reads.  A trainer repacks group g right behind the Adam step of
+        that range, beside the later backward phases (pack_group), and runs its forwards with repack=False."""
         ops, cfg, W = self.ops, self.cfg, {}
         jl_first, jl_rest = JobList("pack"), JobList("pack")
+        groups = [JobList("pack") for _ in range(4)]
         pick = lambda name: jl_first if self._needed_first(name) else jl_rest      # (backward-only operands always go to jl_rest)
+
+        def group_of(name):
+            if name.startswith("film"):
+                return 3
+            hits = [ph for ph, pre in enumerate(self.PHASE_PREFIXES) if name.startswith(pre)]
+            assert len(hits) == 1, name
+            return hits[0]
+
+        def rec(name, jl, *a, **k):
+            ops.record_pack_weight(jl, *a, **k)
+            ops.record_pack_weight(groups[group_of(name)], *a, **k)
+
+        def rec_copy(name, jl, src, dst):
+            ops.record_copy(jl, src, dst)
+            ops.record_copy(groups[group_of(name)], src, dst)
 
         def conv3(name, w, Co_alloc=None):
             Co, Ci = w.shape[0], w.shape[1]
@@ -225,12 +245,12 @@ class Engine:
             f = self.buf("w.f." + name, (Co_alloc or Co, 9 * cp))
             if Co_alloc:
                 f.zero_()
-            ops.record_pack_weight(pick(name), w, 0, f, Cpad=cp)
+            rec(name, pick(name), w, 0, f, Cpad=cp)
             W[name] = f
             if training:
                 cop = G.ceil64(Co)
                 t = self.buf("w.t." + name, (Ci, 9 * cop))
-                ops.record_pack_weight(jl_rest, w, 1, t, Cpad=cop)
+                rec(name, jl_rest, w, 1, t, Cpad=cop)
                 W[name + ".T"] = t
 
         def lin(name, w, srcs=None):
@@ -239,13 +259,13 @@ class Engine:
             f = self.buf("w.f." + name, (Co, sum(G.ceil64(c) for c in srcs)))
             ci0 = koff = 0
             for c in srcs:
-                ops.record_pack_weight(pick(name), w, 0, f, ci0=ci0, cn=c, Cpad=G.ceil64(c), k_off=koff)
+                rec(name, pick(name), w, 0, f, ci0=ci0, cn=c, Cpad=G.ceil64(c), k_off=koff)
                 ci0 += c
                 koff += G.ceil64(c)
             W[name] = f
             if training:
                 t = self.buf("w.t." + name, (Ci, G.ceil64(Co)))
-                ops.record_pack_weight(jl_rest, w, 1, t, Cpad=G.ceil64(Co))
+                rec(name, jl_rest, w, 1, t, Cpad=G.ceil64(Co))
                 W[name + ".T"] = t
 
         cp = "conditioningprocessor."
@@ -254,20 +274,20 @@ class Engine:
         for l in range(cfg.num_resolutions):
             w = P[cp + f"convs.{l}.weight"]
             f = self.buf(f"w.f.cc{l}", (cfg.emb_ch, 9 * 192))
-            ops.record_pack_weight(pick(cp + f"convs.{l}."), w, 0, f, Cpad=192)
+            rec(cp, pick(cp + f"convs.{l}."), w, 0, f, Cpad=192)
             W[cp + f"convs.{l}.weight"] = f
             if training:
                 t = self.buf(f"w.r.cc{l}", (9 * 144, cfg.emb_ch))
-                ops.record_pack_weight(jl_rest, w, 2, t)
+                rec(cp, jl_rest, w, 2, t)
                 W[cp + f"convs.{l}.weight.R"] = t
         # stem: the packed input tensor has 8 channels (3 real)
         f = self.buf("w.f.stem", (cfg.ch, 9 * 64))
-        ops.record_pack_weight(jl_first, P["conv.weight"], 0, f, Cpad=64)
+        rec("conv.", jl_first, P["conv.weight"], 0, f, Cpad=64)
         W["conv.weight"] = f
         conv3("lastconv.weight", P["lastconv.weight"], Co_alloc=16)
         lb = self.buf("lastconv.b16", (16,), torch.float32)
         lb.zero_()
-        ops.record_copy(jl_rest, P["lastconv.bias"], lb[:3])
+        rec_copy("lastconv.", jl_rest, P["lastconv.bias"], lb[:3])
         # FiLM: one [sum 2F, 1024] operand per level (+ its transpose for the data gradient)
         for l in range(cfg.num_resolutions):
             W[f"film{l}"] = self.buf(f"w.f.film{l}", (self.film_cols[l], 1024))
@@ -285,24 +305,34 @@ class Engine:
                     # conv2 and the 1x1 skip as ONE implicit GEMM (forward): [conv2 taps | dense per source] along K
                     srcs_c, cpF = (s.srcs_c if s.cat else [s.cin]), G.ceil64(s.f)
                     f = self.buf("w.f." + n + ".conv2+dense", (s.f, 9 * cpF + sum(G.ceil64(c) for c in srcs_c)))
-                    ops.record_pack_weight(pick(n), P[n + ".conv2.weight"], 0, f, Cpad=cpF)
+                    rec(n, pick(n), P[n + ".conv2.weight"], 0, f, Cpad=cpF)
                     ci0, koff = 0, 9 * cpF
                     for c in srcs_c:
-                        ops.record_pack_weight(pick(n), P[n + ".dense.weight"], 0, f, ci0=ci0, cn=c, Cpad=G.ceil64(c), k_off=koff)
+                        rec(n, pick(n), P[n + ".dense.weight"], 0, f, ci0=ci0, cn=c, Cpad=G.ceil64(c), k_off=koff)
                         ci0 += c
                         koff += G.ceil64(c)
                     W[n + ".conv2+dense"] = f
                 fw = P[n + ".film.dense.weight"]
-                ops.record_pack_weight(pick(f"film{s.lvl}"), fw, 0, W[f"film{s.lvl}"][s.film_off:s.film_off + 2 * s.f], Cpad=1024)
-                ops.record_copy(pick(f"film{s.lvl}"), P[n + ".film.dense.bias"], self._bufs[f"b.film{s.lvl}"][s.film_off:s.film_off + 2 * s.f])
+                fl = f"film{s.lvl}"
+                rec(fl, pick(fl), fw, 0, W[fl][s.film_off:s.film_off + 2 * s.f], Cpad=1024)
+                rec_copy(fl, pick(fl), P[n + ".film.dense.bias"], self._bufs[f"b.film{s.lvl}"][s.film_off:s.film_off + 2 * s.f])
                 if training:
-                    ops.record_pack_weight(jl_rest, fw, 1, W[f"film{s.lvl}.T"], Cpad=2 * s.f, k_off=s.film_off)
+                    rec(fl, jl_rest, fw, 1, W[fl + ".T"], Cpad=2 * s.f, k_off=s.film_off)
             elif kind == "attn":
                 a = s.name + ".attn_layer.attn"
                 lin(a + ".in_proj_weight", P[a + ".in_proj_weight"])
                 lin(a + ".out_proj.weight", P[a + ".out_proj.weight"])
                 lin(s.name + ".linear.weight", P[s.name + ".linear.weight"])
-        return W, (jl_first, jl_rest)
+        return W, (jl_first, jl_rest), groups
+
+    def pack_group(self, g, training=True):
+        """Repack the operands of parameter group g (0 / 1 / 2 = backward phase, 3 = FiLM) on the current stream; needs a
+        forward that has recorded the jobs (see _record_pack)."""
+        cached = self._pack_cache.get(training)
+        if cached is None:
+            from ._lib import B3DError
+            raise B3DError("pack_group before the first forward of this engine")
+        self.ops.run_jobs(cached[3][g])
 
     # ------------------------------------------------------------------ forward
     def cond_features(self, P, R, t, K, cond_mask, repack=True):

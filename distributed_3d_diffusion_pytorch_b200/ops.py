@@ -100,12 +100,48 @@ class _PackJob(ctypes.Structure):
                 ("cn", c_i32), ("Cpad", c_i32), ("accumulate", c_i32), ("k_off", c_i64), ("ld", c_i64), ("total", c_i64), ("block0", c_i64)]
 
 
+class _PackDst(ctypes.Structure):
+    _fields_ = [("dst", c_void), ("mode", c_i32), ("ci0", c_i32), ("cn", c_i32), ("Cpad", c_i32), ("k_off", c_i64), ("ld", c_i64)]
+
+
+class _PackGroup(ctypes.Structure):
+    _fields_ = [("src", c_void), ("Co", c_i32), ("Ci", c_i32), ("taps", c_i32), ("n_dst", c_i32), ("total", c_i64), ("block0", c_i64),
+                ("d", _PackDst * 8)]
+
+
 class JobList:
     """Recorded pack / unpack jobs (see b3d_pack_job) that run as ONE kernel launch.  Built once per engine: parameter,
-    gradient and staging buffers have fixed addresses, so the device-side table is reused every step."""
+    gradient and staging buffers have fixed addresses, so the device-side table is reused every step.
+    Pack lists: the jobs that read the same source tensor become one b3d_pack_group (the source is read once for all its
+    destinations); pad columns are not written by the kernel, so the recorder zeroes every destination once (`zero_pads`)."""
 
     def __init__(self, kind):
         self.kind, self.jobs, self.keep, self.table, self.blocks = kind, [], [], None, 0
+        self.block_table, self.n_entries, self.zeroed = None, 0, set()
+
+    def groups(self):
+        """(ctypes array of _PackGroup, block -> group list): jobs grouped by source, first-appearance order, <= 8 each"""
+        by_src, order = {}, []
+        for j in self.jobs:
+            key = (j.src, j.Co, j.Ci, j.taps) if j.mode != 3 else ("copy", len(order))
+            lst = by_src.get(key)
+            if lst is None or len(lst[-1]) == 8:
+                if lst is None:
+                    by_src[key] = lst = []
+                lst.append([])
+                order.append(lst[-1])
+            lst[-1].append(j)
+        out, block_group, blocks = [], [], 0
+        for gi, js in enumerate(order):
+            g, j0 = _PackGroup(), js[0]
+            g.src, g.Co, g.Ci, g.taps, g.n_dst, g.total, g.block0 = j0.src, j0.Co, j0.Ci, j0.taps, len(js), j0.total, blocks
+            for k, j in enumerate(js):
+                g.d[k].dst, g.d[k].mode, g.d[k].ci0, g.d[k].cn, g.d[k].Cpad, g.d[k].k_off, g.d[k].ld = j.dst, j.mode, j.ci0, j.cn, j.Cpad, j.k_off, j.ld
+            nb = (j0.total + 1023) // 1024 if j0.mode == 3 else ((j0.Co + 31) // 32) * ((j0.Ci + 31) // 32)
+            block_group += [gi] * nb
+            blocks += nb
+            out.append(g)
+        return (_PackGroup * len(out))(*out), block_group
 
     def add(self, src, dst, Co, Ci, taps, mode, ci0, cn, Cpad, k_off, ld, total, accumulate=0):
         j = _PackJob()
@@ -341,6 +377,12 @@ class CudaOps:
         cn = Ci if cn is None else cn
         assert w.dtype == torch.float32 and w.is_contiguous() and out.dim() == 2 and out.stride(1) == 1 and taps <= 9
         total = Co * taps * Cpad if mode == 0 else (Ci * taps * Cpad if mode == 1 else Co * Ci * taps)
+        if jl.kind == "pack" and id(out) not in jl.zeroed:      # pad columns / rows are never written by the grouped kernel
+            base = out._base if out._base is not None else out
+            if id(base) not in jl.zeroed:
+                base.zero_()
+                jl.zeroed.add(id(base))
+            jl.zeroed.add(id(out))
         jl.add(w, out, Co, Ci, taps, mode, ci0, cn, Cpad, k_off, out.stride(0), total)
 
     def record_copy(self, jl, src, dst):
@@ -358,11 +400,18 @@ class CudaOps:
         if not jl.jobs:
             return
         if jl.table is None:
-            arr = (_PackJob * len(jl.jobs))(*jl.jobs)
+            if jl.kind == "pack":
+                arr, block_of = jl.groups()
+            else:
+                arr, block_of = (_PackJob * len(jl.jobs))(*jl.jobs), []
+                for i, j in enumerate(jl.jobs):
+                    nxt = jl.jobs[i + 1].block0 if i + 1 < len(jl.jobs) else jl.blocks
+                    block_of += [i] * (nxt - j.block0)
             host = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8)
-            jl.table = host.to(self.device)
+            jl.table, jl.n_entries = host.to(self.device), len(arr)
+            jl.block_table = torch.tensor(block_of, dtype=torch.int32).to(self.device)
         name = "b3d_pack_weights_multi" if jl.kind == "pack" else "b3d_unpack_wgrads_multi"
-        self._call(name, _ptr(jl.table), c_i32(len(jl.jobs)), c_i64(jl.blocks), self.stream())
+        self._call(name, _ptr(jl.table), c_i32(jl.n_entries), _ptr(jl.block_table), c_i64(jl.block_table.numel()), self.stream())
 
     def scale_colsum(self, a, out, scale, colsum):
         C = a.shape[-1]

@@ -85,11 +85,16 @@ class Trainer:
         self._lam0 = float(-2.0 * np.log(np.tan(self._b)))        # schedule(0) = +20 for the clean conditioning frame
         self.use_graph, self.graph, self.graphed = use_graph, None, False
         self.launches_per_step = 0
+        self._packed = False
         self.step_idx = 0
 
     # ------------------------------------------------------------------ one step, device resident
     def _draws_forward_loss(self):
         """draws + forward + loss on the static buffers (graph-capturable: no allocation, no sync)"""
+        self._draws()
+        self._forward_loss()
+
+    def _draws(self):
         self.step_ctr.add_(1)
         self.u.uniform_()                                            # logsnr = schedule(rand(B))      (train.py:272)
         torch.log(torch.tan(self.u * self._a + self._b), out=self.logsnr)
@@ -98,14 +103,17 @@ class Trainer:
         self.u.uniform_()                                            # cond_mask = rand(B) > cond_prob (train.py:95)
         self.mask.copy_(self.u > self.cond_prob)
         self.xrand.normal_()                                         # randn_like(x) for uncond rows   (train.py:96)
+
+    def _forward_loss(self):
         self.xi.copy_(self.img[:, 0])
         self.zi.copy_(self.img[:, 1])
         self.ops.q_sample(self.zi, self.noise, self.logsnr, self.z_noisy, self.xi, self.xrand, self.mask, self.x_cond)
         self.logsnr2[:, 0].fill_(self._lam0)                         # xt2batch                        (train.py:36-46)
         self.logsnr2[:, 1].copy_(self.logsnr)
         P = dict(zip(self.model._names, self.model._plist))
+        # the bf16 operands were repacked behind the previous step's Adam (see _update): only the very first forward packs
         eps = self.engine.forward(P, self.x_cond, self.z_noisy, self.logsnr2, self.R, self.T, self.K, self.mask, training=True, need_bwd=True,
-                                  seed=self.seed % 1000003)
+                                  seed=self.seed % 1000003, repack=not self._packed)
         self.ops.loss(self.noise, eps, self.deps, 0, self.scratch, self.loss)
 
     def _backward(self, phase=None):
@@ -122,7 +130,36 @@ class Trainer:
     def _finish(self):
         parallel.allreduce_mean_(self.model._grad_flat)
         self.opt.step()
+        self.repack()
         self.step_idx += 1
+
+    def repack(self):
+        """bf16 GEMM operands <- fp32 parameters, all groups, on the current stream (after every un-graphed step; call it after
+        editing parameters by hand)"""
+        for g in range(4):
+            self.engine.pack_group(g)
+        self._packed = True
+
+    def _update(self, ph, lo, hi):
+        """(communication stream) all-reduce of gradient range [lo, hi), its Adam step, and the repack of the operands built
+        from those parameters -- all beside the later backward phases, which read packed operands and fp32 GroupNorm
+        parameters of THEIR OWN blocks only.  The level-wide FiLM operands are the exception (phase 2's data gradient reads
+        all of them): they are repacked after the last phase."""
+        g = self.model._grad_flat
+        if self.world > 1:
+            if self.grad_comm_dtype == torch.float32:
+                parallel.allreduce_mean_(g[lo:hi])                     # NCCL over NVLink, concurrent with the next phase
+            else:
+                if self._gcomm is None:
+                    self._gcomm = torch.empty(max(h_ - l_ for l_, h_ in self.ranges.values()), dtype=self.grad_comm_dtype, device=self.dev)
+                gb = self._gcomm[:hi - lo]
+                gb.copy_(g[lo:hi])
+                parallel.allreduce_mean_(gb)
+                g[lo:hi].copy_(gb)
+        self.opt.step(lo=lo, hi=hi, first=ph == 0)
+        self.engine.pack_group(ph)
+        if ph == 2:
+            self.engine.pack_group(3)
 
     def _set_batch(self, batch):
         img, R, T, K = batch
@@ -144,44 +181,26 @@ class Trainer:
         if self.use_graph and self.graph is None and self.step_idx >= 1:
             torch.cuda.synchronize()
             n0 = _lib.launch_count()
-            if self.world == 1:
-                self.graph = [self._capture(self._compute)]
-            else:       # three graphs: the all-reduce of each finished gradient range overlaps the next backward phase
-                self.model._grad_views()
-                self.graph = [self._capture(lambda: (self._draws_forward_loss(), self._backward(0))),
-                              self._capture(lambda: self._backward(1)), self._capture(lambda: self._backward(2))]
-                self.ranges = self._phase_ranges()
-                self.comm = torch.cuda.Stream(self.dev)
-            self.launches_per_step = _lib.launch_count() - n0 + 1     # + Adam
+            # three graphs: the update of each finished gradient range (all-reduce, Adam, repack) overlaps the next phase
+            self.model._grad_views()
+            self.graph = [self._capture(lambda: (self._draws_forward_loss(), self._backward(0))),
+                          self._capture(lambda: self._backward(1)), self._capture(lambda: self._backward(2))]
+            self.ranges = self._phase_ranges()
+            self.comm = torch.cuda.Stream(self.dev)
+            self.launches_per_step = _lib.launch_count() - n0 + 3 + 4     # + Adam per range + the four repack launches
             self.graphed = True
         if self.graph is None:
             self._compute()
             self._finish()
             return
-        if self.world == 1:
-            self.graph[0].replay()
-            self._finish()
-            return
         main = torch.cuda.current_stream(self.dev)
-        g = self.model._grad_flat
         for ph in (0, 1, 2):
             self.graph[ph].replay()
             self.comm.wait_stream(main)                                # gradients of this phase are final
             lo, hi = self.ranges[ph]
             with torch.cuda.stream(self.comm):
-                if self.grad_comm_dtype == torch.float32:
-                    parallel.allreduce_mean_(g[lo:hi])                 # NCCL over NVLink, concurrent with the next phase
-                else:
-                    if self._gcomm is None:
-                        self._gcomm = torch.empty(max(h_ - l_ for l_, h_ in self.ranges.values()), dtype=self.grad_comm_dtype, device=self.dev)
-                    gb = self._gcomm[:hi - lo]
-                    gb.copy_(g[lo:hi])
-                    parallel.allreduce_mean_(gb)
-                    g[lo:hi].copy_(gb)
-                # ... and so is this range's Adam step: the later phases read packed bf16 operands and the fp32 GroupNorm
-                # parameters of THEIR OWN blocks only, never a parameter of a range that is already reduced
-                self.opt.step(lo=lo, hi=hi, first=ph == 0)
-        main.wait_stream(self.comm)                                    # the next forward repacks the updated parameters
+                self._update(ph, lo, hi)
+        main.wait_stream(self.comm)                                    # the next forward reads the repacked operands
         self.step_idx += 1
 
     def step_e2e(self, host_batch):

@@ -140,17 +140,33 @@ int b3d_unpack_wgrad(const float* g, int64_t g_ld, int64_t k_off, int Cpad, int 
                      int accumulate, void* stream);
 int b3d_cast_bf16(const float* in, void* out, int64_t n, void* stream);
 /* The same conversions for MANY tensors in one launch (every parameter is repacked each step; one launch instead of
- * ~450).  `jobs` is a DEVICE array of b3d_pack_job; block0 = running sum of the jobs' block counts: ceil(total/1024) for
- * mode-3 copies, one block per 32 x 32 (co x ci) tile otherwise -- pack modes 0/1/2: ceil(Co/32)*ceil(Cpad/32),
- * ceil(Cpad/32)*ceil(Ci/32), ceil(Co/32)*ceil(Ci/32); unpack: ceil(Co/32)*ceil(cn/32).  taps <= 9.
- * pack: mode 0/1/2 as b3d_pack_weight, mode 3 = fp32 copy of `total` values.  unpack: as b3d_unpack_wgrad. */
+ * ~450).
+ * pack: `groups` is a DEVICE array of b3d_pack_group -- one fp32 source [Co, Ci, taps] (taps <= 9) and the n_dst <= 8
+ * destinations built from it, so that the source is read once: mode 0 = out[co, k_off + tap*Cpad + (ci - ci0)] for ci in
+ * [ci0, ci0 + cn), mode 1 = out[ci, k_off + (taps-1-tap)*Cpad + co], mode 2 = out[tap*Ci + ci, co] (as b3d_pack_weight);
+ * pad columns / rows are NOT written (zero the operands once).  A group whose d[0].mode is 3 is an fp32 copy of `total`
+ * values.  Blocks: ceil(Co/32)*ceil(Ci/32) per group (copies: ceil(total/1024)); block0 = running sum, and `block_group`
+ * (DEVICE array, total_blocks entries) names the group of every block.
+ * unpack: `jobs` is a DEVICE array of b3d_pack_job, semantics of b3d_unpack_wgrad, ceil(Co/32)*ceil(cn/32) blocks per job,
+ * block0 = running sum; `block_job` as above, or NULL (binary search over block0). */
 typedef struct b3d_pack_job {
   const float* src; void* dst;
   int32_t Co, Ci, taps, mode, ci0, cn, Cpad, accumulate;
   int64_t k_off, ld, total, block0;
 } b3d_pack_job;
-int b3d_pack_weights_multi(const void* jobs, int n_jobs, int64_t total_blocks, void* stream);
-int b3d_unpack_wgrads_multi(const void* jobs, int n_jobs, int64_t total_blocks, void* stream);
+typedef struct b3d_pack_dst {
+  void* dst;
+  int32_t mode, ci0, cn, Cpad;
+  int64_t k_off, ld;
+} b3d_pack_dst;
+typedef struct b3d_pack_group {
+  const float* src;
+  int32_t Co, Ci, taps, n_dst;
+  int64_t total, block0;
+  b3d_pack_dst d[8];
+} b3d_pack_group;
+int b3d_pack_weights_multi(const void* groups, int n_groups, const int32_t* block_group, int64_t total_blocks, void* stream);
+int b3d_unpack_wgrads_multi(const void* jobs, int n_jobs, const int32_t* block_job, int64_t total_blocks, void* stream);
 /* out = scale*a (bf16 [rows,C]) and colsum[c] += column sums of out (bias gradients fused with the 1/sqrt2 of xunet.py:152,220) */
 int b3d_scale_colsum(const void* a, void* out, float scale, int64_t rows, int C, float* colsum, void* stream);
 /* avgpool_downsample / nearest_neighbor_upsample, xunet.py:17-28 (scale folds the adjoint's 1/4) */

@@ -875,6 +875,39 @@ __global__ void __launch_bounds__(256) unpack_multi_kernel(const PackJob* __rest
   }
 }
 
+// y = W v (+ add) for fp32 W [R, C] (transpose = 0: one warp per row) or y = W^T v (+ add) (transpose = 1: one thread per
+// column, rows streamed with coalesced reads).  Weight-space helper of the composed attention output projection.
+__global__ void __launch_bounds__(256) matvec_kernel(const float* __restrict__ W, int R, int C, const float* __restrict__ v,
+                                                     const float* __restrict__ add, float* __restrict__ y, int transpose) {
+  if (!transpose) {
+    const int r = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (r >= R) return;
+    float s = 0.f;
+    for (int c = lane; c < C; c += 32) s += W[(long long)r * C + c] * v[c];
+    s = b3d_warp_sum(s);
+    if (lane == 0) y[r] = s + (add ? add[r] : 0.f);
+  } else {
+    const int c = blockIdx.x * 256 + threadIdx.x;
+    if (c >= C) return;
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    int r = 0;
+    for (; r + 4 <= R; r += 4) {
+      s0 += W[(long long)r * C + c] * v[r]; s1 += W[(long long)(r + 1) * C + c] * v[r + 1];
+      s2 += W[(long long)(r + 2) * C + c] * v[r + 2]; s3 += W[(long long)(r + 3) * C + c] * v[r + 3];
+    }
+    for (; r < R; ++r) s0 += W[(long long)r * C + c] * v[r];
+    y[c] = (s0 + s1) + (s2 + s3) + (add ? add[c] : 0.f);
+  }
+}
+
+// A[r, c] += u[r] * v[c]   (fp32 [R, C]; the b_out term of d W_lin in the composed attention output projection)
+__global__ void __launch_bounds__(256) rank1_add_kernel(float* __restrict__ A, int R, int C, const float* __restrict__ u, const float* __restrict__ v) {
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i >= (long long)R * C) return;
+  const int r = (int)(i / C), c = (int)(i - (long long)r * C);
+  A[i] += u[r] * v[c];
+}
+
 }  // namespace
 
 #define STREAM ((cudaStream_t)stream)
@@ -932,6 +965,16 @@ extern "C" int b3d_unpack_wgrad(const float* g, int64_t g_ld, int64_t k_off, int
 }
 extern "C" int b3d_cast_bf16(const float* in, void* out, int64_t n, void* stream) {
   cast_kernel<<<grid_for(n), kT, 0, STREAM>>>(in, (bf16*)out, n);
+  DONE(1);
+}
+extern "C" int b3d_matvec(const float* W, int R, int C, const float* v, const float* add, float* y, int transpose, void* stream) {
+  B3D_CHECK_ARG(W && v && y && R > 0 && C > 0, "matvec: args");
+  matvec_kernel<<<transpose ? cdiv(C, 256) : cdiv(R, 8), 256, 0, STREAM>>>(W, R, C, v, add, y, transpose);
+  DONE(1);
+}
+extern "C" int b3d_rank1_add(float* A, int R, int C, const float* u, const float* v, void* stream) {
+  B3D_CHECK_ARG(A && u && v && R > 0 && C > 0, "rank1_add: args");
+  rank1_add_kernel<<<cdiv((long long)R * C, 256), 256, 0, STREAM>>>(A, R, C, u, v);
   DONE(1);
 }
 extern "C" int b3d_avgpool2(const void* in, void* out, int N, int H, int W, int C, float scale, void* stream) {

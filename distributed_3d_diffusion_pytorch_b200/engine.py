@@ -110,6 +110,10 @@ class Engine:
         self._unpack_jl, self._copy_jl, self._unpack_sig, self._unpack_rec = None, None, None, False
         # small batches: weight-gradient launches never block the data-gradient chain (see side_tmp)
         self.defer_side = 2 * B * cfg.H * cfg.W <= 64 * 64 * 64
+        # ... and then the side work is itself a serial chain of small launches as long as the main one: spread its regions
+        # (one `with ops.side():` each, independent of each other) over several streams
+        if self.defer_side and hasattr(self.ops, "n_side"):
+            self.ops.n_side = max(self.ops.n_side, int(os.environ.get("B3D_SIDE_STREAMS", "2")))
         # GroupNorm statistics of conv1's output from its own epilogue (measured in-run: +0.5% at batch 128, -0.4% at batch 16,
         # where the extra epilogue work costs more than the small gn_stats launch: large batches only; B3D_NO_FUSE_STATS=1 = off)
         self.fuse_stats = os.environ.get("B3D_NO_FUSE_STATS") != "1" and 2 * B * cfg.H * cfg.W > 64 * 64 * 64
@@ -196,17 +200,16 @@ class Engine:
         sig = (training, len(P), tuple(P[k].data_ptr() for k in list(P.keys())[:8]))
         cached = self._pack_cache.get(training)
         if cached is None or cached[0] != sig:
-            cached = (sig,) + self._record_pack(P, training)
+            cached = (sig,) + self._record_pack(P, training) + (P,)
             self._pack_cache[training] = cached
             repack = True
         if repack:
             first, rest = cached[2]
             self.ops.run_jobs(first)
-            if overlap:
-                with self.ops.side():
-                    self.ops.run_jobs(rest)
-            else:
+            with (self.ops.side() if overlap else contextlib.nullcontext()):
                 self.ops.run_jobs(rest)
+                for specs in cached[4]:
+                    self._compose(P, cached[1], specs, training)
         return cached[1]
 
     @staticmethod
@@ -222,6 +225,7 @@ class Engine:
         ops, cfg, W = self.ops, self.cfg, {}
         jl_first, jl_rest = JobList("pack"), JobList("pack")
         groups = [JobList("pack") for _ in range(4)]
+        compose = [[] for _ in range(4)]       # attention blocks whose composed output projection follows group g's repack
         pick = lambda name: jl_first if self._needed_first(name) else jl_rest      # (backward-only operands always go to jl_rest)
 
         def group_of(name):
@@ -253,7 +257,8 @@ class Engine:
                 rec(name, jl_rest, w, 1, t, Cpad=cop)
                 W[name + ".T"] = t
 
-        def lin(name, w, srcs=None):
+        def lin(name, w, srcs=None, need_t=None):
+            need_t = training if need_t is None else need_t
             Co, Ci = w.shape[0], w.shape[1]
             srcs = srcs or [Ci]
             f = self.buf("w.f." + name, (Co, sum(G.ceil64(c) for c in srcs)))
@@ -263,7 +268,7 @@ class Engine:
                 ci0 += c
                 koff += G.ceil64(c)
             W[name] = f
-            if training:
+            if need_t:
                 t = self.buf("w.t." + name, (Ci, G.ceil64(Co)))
                 rec(name, jl_rest, w, 1, t, Cpad=G.ceil64(Co))
                 W[name + ".T"] = t
@@ -321,9 +326,31 @@ class Engine:
             elif kind == "attn":
                 a = s.name + ".attn_layer.attn"
                 lin(a + ".in_proj_weight", P[a + ".in_proj_weight"])
-                lin(a + ".out_proj.weight", P[a + ".out_proj.weight"])
-                lin(s.name + ".linear.weight", P[s.name + ".linear.weight"])
-        return W, (jl_first, jl_rest), groups
+                # out_proj and the block's `linear` follow each other with nothing in between (xunet.py:211-219): the engine
+                # applies them as ONE layer, W_m = W_lin W_out, b_m = W_lin b_out + b_lin, composed from the packed operands
+                # after every repack (_compose); the backward maps the gradient of W_m back onto both (see _attn_bwd)
+                lin(a + ".out_proj.weight", P[a + ".out_proj.weight"], need_t=True)
+                lin(s.name + ".linear.weight", P[s.name + ".linear.weight"], need_t=False)
+                C = s.c
+                assert C % 64 == 0
+                W[s.name + ".merged"] = self.buf("w.f." + s.name + ".merged", (C, C))
+                if training:
+                    W[s.name + ".merged.T"] = self.buf("w.t." + s.name + ".merged", (C, C))
+                self.buf(s.name + ".bm", (C,), torch.float32)
+                compose[group_of(s.name)].append(s)
+        return W, (jl_first, jl_rest), groups, compose
+
+    def _compose(self, P, W, specs, training):
+        """W_m = W_lin W_out (bf16, from the packed bf16 operands, fp32 accumulation), its transpose for the data gradient, and
+        b_m = W_lin b_out + b_lin (fp32) for the attention blocks in `specs`: three small launches per block."""
+        ops = self.ops
+        for s in specs:
+            n, a, C = s.name, s.name + ".attn_layer.attn", s.c
+            wl, wo, wot = W[n + ".linear.weight"], W[a + ".out_proj.weight"], W[a + ".out_proj.weight.T"]
+            ops.gemm(G.dense_desc(wl, wot, W[n + ".merged"], C))                   # [i, j] = sum_k W_lin[i, k] W_out[k, j]
+            if training:
+                ops.gemm(G.dense_desc(wot, wl, W[n + ".merged.T"], C))             # [j, i]
+            ops.matvec(P[n + ".linear.weight"].view(C, C), P[a + ".out_proj.bias"], self._bufs[n + ".bm"], add=P[n + ".linear.bias"])
 
     def pack_group(self, g, training=True):
         """Repack the operands of parameter group g (0 / 1 / 2 = backward phase, 3 = FiLM) on the current stream; needs a
@@ -333,6 +360,7 @@ class Engine:
             from ._lib import B3DError
             raise B3DError("pack_group before the first forward of this engine")
         self.ops.run_jobs(cached[3][g])
+        self._compose(cached[5], cached[1], cached[4][g], training)
 
     # ------------------------------------------------------------------ forward
     def cond_features(self, P, R, t, K, cond_mask, repack=True):
@@ -565,13 +593,12 @@ class Engine:
             ops.gemm(G.attn_qk_desc(q, k, logits, s.cross, 1.0 / math.sqrt(d)))
             ops.softmax(logits, p)
             ops.gemm(G.attn_pv_desc(p, v, o.view(N, L, Hh, d).permute(0, 2, 1, 3), s.cross))
-        o1 = self.buf(n + ".o1", (N * L, C))
-        ops.gemm(G.dense_desc(o.view(N * L, C), Wp[a + ".out_proj.weight"], o1, C, bias=P[a + ".out_proj.bias"]))
+        # out_proj and `linear` as the one composed layer (see _record_pack / _compose)
         out = self.buf(n + ".out", (N, hh, ww, C))
         oa = Act(out, n + ".out")
-        self._producer_stats(G.dense_desc(o1, Wp[n + ".linear.weight"], out.view(N * L, C), C, bias=P[n + ".linear.bias"],
+        self._producer_stats(G.dense_desc(o.view(N * L, C), Wp[n + ".merged"], out.view(N * L, C), C, bias=self._bufs[n + ".bm"],
                                           resid=h_in.t.view(N * L, C), out_scale=RSQRT2), oa, C, rows_per_image=L)
-        self.saved["acts"][n] = dict(h_in=h_in, sums=sums, g=g, qkv=qkv, p=p, lse=lse, o=o, o1=o1, out=oa)
+        self.saved["acts"][n] = dict(h_in=h_in, sums=sums, g=g, qkv=qkv, p=p, lse=lse, o=o, out=oa)
         return oa
 
     # ------------------------------------------------------------------ backward
@@ -851,17 +878,21 @@ class Engine:
         alpha = 1.0 / math.sqrt(d)
         dout = self._grad_of(out)
         gs = dout.view(M, C)      # the (h + h_in) / sqrt(2) of xunet.py:220 is folded into the consumers of dout (see _res_bwd)
-        # 1x1 `linear` and out_proj
-        with ops.side():      # parameter gradients run beside the data-gradient chain (joined at the end of the block)
-            ops.colsum(gs, M, Gr[n + ".linear.bias"], scale=RSQRT2)
-            ops.gemm(G.wgrad_dense_desc(gs, sa["o1"], Gr[n + ".linear.weight"].view(C, C), alpha=RSQRT2))
-        do1 = self.side_tmp(n, "do1", (M, C))
-        ops.gemm(G.dense_desc(gs, Wp[n + ".linear.weight.T"], do1, C, alpha=RSQRT2))
+        # the composed out_proj + `linear` layer y = o W_m^T + b_m, W_m = W_lin W_out: with Gm = dy^T o,
+        #   d W_lin = Gm W_out^T + d b_lin b_out^T,  d W_out = W_lin^T Gm,  d b_lin = colsum(dy),  d b_out = W_lin^T d b_lin
+        # (weight-space products of C x C matrices, beside the data-gradient chain; joined at the end of the block)
         with ops.side():
-            ops.colsum(do1, M, Gr[a + ".out_proj.bias"])
-            ops.gemm(G.wgrad_dense_desc(do1, sa["o"].view(M, C), Gr[a + ".out_proj.weight"]))
+            ops.colsum(gs, M, Gr[n + ".linear.bias"], scale=RSQRT2)
+            Gm = self.zbuf("bwd", n + ".Gm", (C, C))
+            ops.gemm(G.wgrad_dense_desc(gs, sa["o"].view(M, C), Gm, alpha=RSQRT2))
+            Gb = self.side_tmp(n, "Gb", (C, C))
+            ops.cast(Gm, Gb)
+            ops.gemm(G.dense_desc(Gb, Wp[a + ".out_proj.weight"], Gr[n + ".linear.weight"].view(C, C), C))
+            ops.rank1_add(Gr[n + ".linear.weight"].view(C, C), Gr[n + ".linear.bias"], P[a + ".out_proj.bias"])
+            ops.gemm(G.wgrad_dense_desc(Wp[n + ".linear.weight"], Gb, Gr[a + ".out_proj.weight"]))
+            ops.matvec(P[n + ".linear.weight"].view(C, C), Gr[n + ".linear.bias"], Gr[a + ".out_proj.bias"], transpose=True)
         do = self.tmp("do", (N, L, C))
-        ops.gemm(G.dense_desc(do1, Wp[a + ".out_proj.weight.T"], do.view(M, C), C))
+        ops.gemm(G.dense_desc(gs, Wp[n + ".merged.T"], do.view(M, C), C, alpha=RSQRT2))
         # attention core
         p = sa["p"]
         dqkv = self.side_tmp(n, "dqkv", (N, L, 3 * C))

@@ -189,26 +189,33 @@ class CudaOps:
     # gradients): they overlap the data-gradient chain, filling SMs that small or tail-end launches leave idle.
     # Works eagerly and under stream capture (the fork/join become graph edges).
     use_side = True
-    _side, _side_dirty = None, False
+    n_side = 1            # side streams used round-robin, one `with side():` region each (regions are independent of each other)
+    _sides, _side_dirty, _side_rr = None, None, 0
 
     @contextlib.contextmanager
     def side(self):
-        """launches inside run on the side stream, after everything issued so far on the current stream"""
+        """launches inside run on a side stream, after everything issued so far on the current stream"""
         if self.prof is not None or not self.use_side:
             yield
             return
-        if self._side is None:
-            self._side = torch.cuda.Stream(self.device)
-        self._side.wait_stream(torch.cuda.current_stream(self.device))
-        with torch.cuda.stream(self._side):
+        if self._sides is None or len(self._sides) < self.n_side:
+            self._sides = (self._sides or []) + [torch.cuda.Stream(self.device) for _ in range(self.n_side - len(self._sides or []))]
+            self._side_dirty = (self._side_dirty or []) + [False] * (self.n_side - len(self._side_dirty or []))
+        i = self._side_rr % self.n_side
+        self._side_rr += 1
+        st = self._sides[i]
+        st.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(st):
             yield
-        self._side_dirty = True
+        self._side_dirty[i] = True
 
     def join_side(self):
-        """the current stream waits for everything issued on the side stream"""
+        """the current stream waits for everything issued on the side streams"""
         if self._side_dirty:
-            torch.cuda.current_stream(self.device).wait_stream(self._side)
-            self._side_dirty = False
+            for i, dirty in enumerate(self._side_dirty):
+                if dirty:
+                    torch.cuda.current_stream(self.device).wait_stream(self._sides[i])
+                    self._side_dirty[i] = False
 
     prof = None          # when a list: (name, start_event, end_event, flop, info) per launch (bench.py's profiled step)
     _flop, _info = 0.0, ""
@@ -417,6 +424,20 @@ class CudaOps:
         C = a.shape[-1]
         assert a.is_contiguous() and out.is_contiguous() and colsum.dtype == torch.float32
         self._call("b3d_scale_colsum", _ptr(a), _ptr(out), c_f32(scale), c_i64(a.numel() // C), c_i32(C), _ptr(colsum), self.stream())
+
+    def matvec(self, W, v, out, transpose=False, add=None):
+        """out = W v (+ add), or W^T v (+ add): fp32, W [R, C] contiguous"""
+        R, C = W.shape
+        assert W.dtype == torch.float32 and W.is_contiguous() and v.dtype == torch.float32 and out.dtype == torch.float32
+        assert v.numel() == (R if transpose else C) and out.numel() == (C if transpose else R) and v.is_contiguous() and out.is_contiguous()
+        self._call("b3d_matvec", _ptr(W), c_i32(R), c_i32(C), _ptr(v), _ptr(add) if add is not None else None, _ptr(out), c_i32(int(transpose)),
+                   self.stream())
+
+    def rank1_add(self, A, u, v):
+        """A += outer(u, v): fp32, A [R, C] contiguous"""
+        R, C = A.shape
+        assert A.dtype == torch.float32 and A.is_contiguous() and u.numel() == R and v.numel() == C and u.dtype == v.dtype == torch.float32
+        self._call("b3d_rank1_add", _ptr(A), c_i32(R), c_i32(C), _ptr(u), _ptr(v), self.stream())
 
     def cast(self, src, out):
         assert src.dtype == torch.float32 and src.is_contiguous() and out.is_contiguous()

@@ -139,6 +139,13 @@ int b3d_pack_weight(const float* w, int Co, int Ci, int taps, int mode, int ci0,
 int b3d_unpack_wgrad(const float* g, int64_t g_ld, int64_t k_off, int Cpad, int Co, int Ci, int taps, int ci0, int cn, float* dw,
                      int accumulate, void* stream);
 int b3d_cast_bf16(const float* in, void* out, int64_t n, void* stream);
+/* fp32 matrix-vector product on W [R, C]: y[R] = W v (+ add) (transpose 0) or y[C] = W^T v (+ add) (transpose 1); add may be
+ * NULL.  Weight-space arithmetic of AttnBlock's two back-to-back Linear layers (xunet.py:211-219: out_proj inside
+ * nn.MultiheadAttention, then `linear`), which the engine applies as ONE composed layer: bias W_lin b_out + b_lin in the
+ * forward, d(b_out) = W_lin^T d(b_lin) in the backward. */
+int b3d_matvec(const float* W, int R, int C, const float* v, const float* add, float* y, int transpose, void* stream);
+/* A[r, c] += u[r] * v[c] on fp32 A [R, C]: the bias term of d W_lin = (dy^T o) W_out^T + d(b_lin) b_out^T of the same composed layer */
+int b3d_rank1_add(float* A, int R, int C, const float* u, const float* v, void* stream);
 /* The same conversions for MANY tensors in one launch (every parameter is repacked each step; one launch instead of
  * ~450).
  * pack: `groups` is a DEVICE array of b3d_pack_group -- one fp32 source [Co, Ci, taps] (taps <= 9) and the n_dst <= 8

@@ -354,6 +354,13 @@ class EmuOps:
     def cast(self, src, out):
         out.copy_(src.to(out.dtype))
 
+    def rank1_add(self, A, u, v):
+        A.add_(torch.outer(u.reshape(-1), v.reshape(-1)))
+
+    def matvec(self, W, v, out, transpose=False, add=None):
+        y = (W.t() if transpose else W).double() @ v.double()
+        out.copy_((y + (add.double() if add is not None else 0.0)).float())
+
     # ------------------------------------------------------------------ resampling / elementwise
     def avgpool2(self, x, out, scale=0.25):
         N, H, W, C = x.shape

@@ -192,6 +192,12 @@ def misc_case(seed=0):
             so2 = ops.zeros((Bq, 3, 8, 8), torch.float32)
             ops.sampler_update_dev(zz, nz, xx, wv, xr, so2, torch.tensor([l0, l1], dtype=torch.float32).to(dev))
             outs.append(so2)
+        Wm, vr, vc = torch.randn(70, 300, generator=g).to(dev), torch.randn(70, generator=g).to(dev), torch.randn(300, generator=g).to(dev)
+        y0, y1 = ops.zeros((70,), torch.float32), ops.zeros((300,), torch.float32)
+        ops.matvec(Wm, vc, y0, add=vr)
+        ops.matvec(Wm, vr, y1, transpose=True)
+        ops.rank1_add(Wm, vr, vc)
+        outs += [y0, y1, Wm]
         pa, ga = torch.randn(1000, generator=g).to(dev), torch.randn(1000, generator=g).to(dev)
         ma, va = ops.zeros((1000,), torch.float32), ops.zeros((1000,), torch.float32)
         for st in (1, 2, 3):

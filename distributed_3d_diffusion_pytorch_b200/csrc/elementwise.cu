@@ -875,28 +875,41 @@ __global__ void __launch_bounds__(256) unpack_multi_kernel(const PackJob* __rest
   }
 }
 
-// y = W v (+ add) for fp32 W [R, C] (transpose = 0: one warp per row) or y = W^T v (+ add) (transpose = 1: one thread per
-// column, rows streamed with coalesced reads).  Weight-space helper of the composed attention output projection.
+// y = W v (+ add) for fp32 W [R, C] (transpose = 0: one warp per row) or y = W^T v (+ add) (transpose = 1: a block covers 32
+// columns, its 8 warps stride the rows -- 128-byte coalesced reads, 4 independent loads in flight -- and are summed through
+// shared memory).  Weight-space helper of the composed attention output projection.
 __global__ void __launch_bounds__(256) matvec_kernel(const float* __restrict__ W, int R, int C, const float* __restrict__ v,
                                                      const float* __restrict__ add, float* __restrict__ y, int transpose) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (!transpose) {
-    const int r = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    const int r = blockIdx.x * 8 + warp;
     if (r >= R) return;
-    float s = 0.f;
-    for (int c = lane; c < C; c += 32) s += W[(long long)r * C + c] * v[c];
-    s = b3d_warp_sum(s);
+    float s0 = 0.f, s1 = 0.f;
+    int c = lane;
+    for (; c + 32 < C; c += 64) { s0 += W[(long long)r * C + c] * v[c]; s1 += W[(long long)r * C + c + 32] * v[c + 32]; }
+    if (c < C) s0 += W[(long long)r * C + c] * v[c];
+    const float s = b3d_warp_sum(s0 + s1);
     if (lane == 0) y[r] = s + (add ? add[r] : 0.f);
   } else {
-    const int c = blockIdx.x * 256 + threadIdx.x;
-    if (c >= C) return;
+    __shared__ float part[8][33];
+    const int c = blockIdx.x * 32 + lane;
     float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-    int r = 0;
-    for (; r + 4 <= R; r += 4) {
-      s0 += W[(long long)r * C + c] * v[r]; s1 += W[(long long)(r + 1) * C + c] * v[r + 1];
-      s2 += W[(long long)(r + 2) * C + c] * v[r + 2]; s3 += W[(long long)(r + 3) * C + c] * v[r + 3];
+    if (c < C) {
+      int r = warp;
+      for (; r + 24 < R; r += 32) {
+        s0 += W[(long long)r * C + c] * v[r]; s1 += W[(long long)(r + 8) * C + c] * v[r + 8];
+        s2 += W[(long long)(r + 16) * C + c] * v[r + 16]; s3 += W[(long long)(r + 24) * C + c] * v[r + 24];
+      }
+      for (; r < R; r += 8) s0 += W[(long long)r * C + c] * v[r];
     }
-    for (; r < R; ++r) s0 += W[(long long)r * C + c] * v[r];
-    y[c] = (s0 + s1) + (s2 + s3) + (add ? add[c] : 0.f);
+    part[warp][lane] = (s0 + s1) + (s2 + s3);
+    __syncthreads();
+    if (warp == 0 && c < C) {
+      float s = 0.f;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) s += part[k][lane];
+      y[c] = s + (add ? add[c] : 0.f);
+    }
   }
 }
 
@@ -969,7 +982,7 @@ extern "C" int b3d_cast_bf16(const float* in, void* out, int64_t n, void* stream
 }
 extern "C" int b3d_matvec(const float* W, int R, int C, const float* v, const float* add, float* y, int transpose, void* stream) {
   B3D_CHECK_ARG(W && v && y && R > 0 && C > 0, "matvec: args");
-  matvec_kernel<<<transpose ? cdiv(C, 256) : cdiv(R, 8), 256, 0, STREAM>>>(W, R, C, v, add, y, transpose);
+  matvec_kernel<<<transpose ? cdiv(C, 32) : cdiv(R, 8), 256, 0, STREAM>>>(W, R, C, v, add, y, transpose);
   DONE(1);
 }
 extern "C" int b3d_rank1_add(float* A, int R, int C, const float* u, const float* v, void* stream) {

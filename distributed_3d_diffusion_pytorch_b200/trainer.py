@@ -5,8 +5,11 @@ one process per GPU:
     -> gradient all-reduce over NCCL (N>1; the reference's DDP never armed it) -> fused Adam
 
 The compute part (everything up to the gradients) works on static device buffers and is captured once
-in a CUDA graph; draws (logsnr, noise, cond mask, dropout) are made on the device inside the graph
-(dropout through a device-side step counter), so replays are fresh steps, not repeats."""
+in three CUDA graphs (forward + backward phase 0 | phase 1 | phase 2); draws (logsnr, noise, cond mask, dropout) are made
+on the device inside the graph (dropout through a device-side step counter), so replays are fresh steps, not repeats.
+The UPDATE of each gradient range -- all-reduce (N>1), Adam, and the repack of the bf16 GEMM operands built from those
+parameters -- runs on a second stream as soon as the phase that finalises the range has finished, beside the later
+phases; the next forward packs nothing."""
 import math
 
 import numpy as np
@@ -86,6 +89,7 @@ class Trainer:
         self.use_graph, self.graph, self.graphed = use_graph, None, False
         self.launches_per_step = 0
         self._packed = False
+        self._count_update = False
         self.step_idx = 0
 
     # ------------------------------------------------------------------ one step, device resident
@@ -187,13 +191,15 @@ class Trainer:
                           self._capture(lambda: self._backward(1)), self._capture(lambda: self._backward(2))]
             self.ranges = self._phase_ranges()
             self.comm = torch.cuda.Stream(self.dev)
-            self.launches_per_step = _lib.launch_count() - n0 + 3 + 4     # + Adam per range + the four repack launches
+            self.launches_per_step = _lib.launch_count() - n0     # + the un-captured update launches, counted on the first replay
+            self._count_update = True
             self.graphed = True
         if self.graph is None:
             self._compute()
             self._finish()
             return
         main = torch.cuda.current_stream(self.dev)
+        n_up = _lib.launch_count()
         for ph in (0, 1, 2):
             self.graph[ph].replay()
             self.comm.wait_stream(main)                                # gradients of this phase are final
@@ -201,6 +207,9 @@ class Trainer:
             with torch.cuda.stream(self.comm):
                 self._update(ph, lo, hi)
         main.wait_stream(self.comm)                                    # the next forward reads the repacked operands
+        if self._count_update:                                         # Adam per range, repack per group, composed attention operands
+            self.launches_per_step += _lib.launch_count() - n_up
+            self._count_update = False
         self.step_idx += 1
 
     def step_e2e(self, host_batch):

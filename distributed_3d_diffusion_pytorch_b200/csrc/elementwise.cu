@@ -656,20 +656,28 @@ __device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, 
 }
 // 128-bit accesses, two independent vectors in flight per thread (28 bytes of traffic per parameter: HBM-bound).
 // kEma: also ema = decay * ema + (1 - decay) * p_new (the parameter average lightning/diff3d.py:11-19 describes), +8 bytes.
-template <bool kEma>
-__global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
+// kG16: the gradient is bf16 (the all-reduced communication buffer of a data-parallel step, read in place: 26 bytes per parameter)
+template <bool kG16>
+__device__ __forceinline__ float4 adam_load_g(const void* g, long long i4) {
+  if (!kG16) return reinterpret_cast<const float4*>(g)[i4];
+  const uint2 r = reinterpret_cast<const uint2*>(g)[i4];
+  const float2 a = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&r.x)), b = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&r.y));
+  return make_float4(a.x, a.y, b.x, b.y);
+}
+template <bool kEma, bool kG16 = false>
+__global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const void* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
                                                    float* __restrict__ ema, long long n, float lr, float b1, float b2, float eps, float ibc1,
                                                    float ibc2, float grad_scale, float decay) {
   const long long n4 = n / 4, stride = (long long)gridDim.x * blockDim.x;
-  float4* p4 = reinterpret_cast<float4*>(p); const float4* g4 = reinterpret_cast<const float4*>(g);
+  float4* p4 = reinterpret_cast<float4*>(p);
   float4* m4 = reinterpret_cast<float4*>(m); float4* v4 = reinterpret_cast<float4*>(v); float4* e4 = reinterpret_cast<float4*>(ema);
   const float omd = 1.f - decay;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += 2 * stride) {
     const long long i1 = i + stride;
     const bool two = i1 < n4;
-    float4 P0 = p4[i], G0 = g4[i], M0 = m4[i], V0 = v4[i], P1, G1, M1, V1, E0, E1;
+    float4 P0 = p4[i], G0 = adam_load_g<kG16>(g, i), M0 = m4[i], V0 = v4[i], P1, G1, M1, V1, E0, E1;
     if (kEma) E0 = e4[i];
-    if (two) { P1 = p4[i1]; G1 = g4[i1]; M1 = m4[i1]; V1 = v4[i1]; if (kEma) E1 = e4[i1]; }
+    if (two) { P1 = p4[i1]; G1 = adam_load_g<kG16>(g, i1); M1 = m4[i1]; V1 = v4[i1]; if (kEma) E1 = e4[i1]; }
     adam_one(P0.x, G0.x, M0.x, V0.x, lr, b1, b2, eps, ibc1, ibc2, grad_scale); adam_one(P0.y, G0.y, M0.y, V0.y, lr, b1, b2, eps, ibc1, ibc2, grad_scale);
     adam_one(P0.z, G0.z, M0.z, V0.z, lr, b1, b2, eps, ibc1, ibc2, grad_scale); adam_one(P0.w, G0.w, M0.w, V0.w, lr, b1, b2, eps, ibc1, ibc2, grad_scale);
     p4[i] = P0; m4[i] = M0; v4[i] = V0;
@@ -683,7 +691,8 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
   }
   if (blockIdx.x == 0 && threadIdx.x < (int)(n - n4 * 4)) {
     const long long i = n4 * 4 + threadIdx.x;
-    adam_one(p[i], g[i], m[i], v[i], lr, b1, b2, eps, ibc1, ibc2, grad_scale);
+    const float gi = kG16 ? __bfloat162float(reinterpret_cast<const bf16*>(g)[i]) : reinterpret_cast<const float*>(g)[i];
+    adam_one(p[i], gi, m[i], v[i], lr, b1, b2, eps, ibc1, ibc2, grad_scale);
     if (kEma) ema[i] = decay * ema[i] + omd * p[i];
   }
 }
@@ -1178,6 +1187,17 @@ extern "C" int b3d_adam_ema(float* p, const float* g, float* m, float* v, float*
   const float bc1 = 1.f - powf(beta1, (float)step), bc2 = 1.f - powf(beta2, (float)step);
   B3D_CHECK_ARG((((uintptr_t)p | (uintptr_t)g | (uintptr_t)m | (uintptr_t)v | (uintptr_t)ema) & 15) == 0, "adam_ema: arenas must be 16-byte aligned");
   adam_kernel<true><<<148 * 8, 256, 0, STREAM>>>(p, g, m, v, ema, n, lr, beta1, beta2, eps, 1.f / bc1, 1.f / bc2, grad_scale, ema_decay);
+  DONE(1);
+}
+
+extern "C" int b3d_adam_bf16grad(float* p, const void* g_bf16, float* m, float* v, float* ema, int64_t n, float lr, float beta1, float beta2,
+                                 float eps, int step, float grad_scale, float ema_decay, void* stream) {
+  B3D_CHECK_ARG(p && g_bf16 && m && v && step >= 1 && ema_decay >= 0.f && ema_decay <= 1.f, "adam_bf16grad: args");
+  const float bc1 = 1.f - powf(beta1, (float)step), bc2 = 1.f - powf(beta2, (float)step);
+  B3D_CHECK_ARG((((uintptr_t)p | (uintptr_t)m | (uintptr_t)v | (uintptr_t)ema) & 15) == 0 && ((uintptr_t)g_bf16 & 7) == 0,
+                "adam_bf16grad: fp32 arenas must be 16-byte aligned, the gradient 8-byte aligned");
+  if (ema) adam_kernel<true, true><<<148 * 8, 256, 0, STREAM>>>(p, g_bf16, m, v, ema, n, lr, beta1, beta2, eps, 1.f / bc1, 1.f / bc2, grad_scale, ema_decay);
+  else adam_kernel<false, true><<<148 * 8, 256, 0, STREAM>>>(p, g_bf16, m, v, nullptr, n, lr, beta1, beta2, eps, 1.f / bc1, 1.f / bc2, grad_scale, 0.f);
   DONE(1);
 }
 

@@ -146,17 +146,20 @@ class FusedAdam:
             self.ema = flat.clone()
         return flat
 
-    def step(self, grad_scale=1.0, lo=None, hi=None, first=True):
+    def step(self, grad_scale=1.0, lo=None, hi=None, first=True, grad=None):
         """One Adam step.  (lo, hi): update only that element range of the arena -- a data-parallel trainer steps each gradient
         range as soon as its all-reduce has finished, beside the rest of the backward pass; `first` marks the first range of a
-        step (the step count advances once per step)."""
+        step (the step count advances once per step).  grad: the gradient of that range in a buffer of its own (fp32 or bf16:
+        the all-reduced communication buffer, read in place) instead of the model's flat gradient arena."""
         flat, g = self._arenas(), self.model.flat_gradients()
         if first:
             self.step_count += 1
             self.model._param_version = getattr(self.model, "_param_version", 0) + 1
         pg = self.param_groups[0]
         sl = slice(lo, hi)
-        _ops(flat.device).adam(flat[sl], g[sl], self.m[sl], self.v[sl], pg["lr"], pg["betas"][0], pg["betas"][1], pg["eps"], self.step_count,
+        gs = g[sl] if grad is None else grad
+        assert gs.numel() == flat[sl].numel()
+        _ops(flat.device).adam(flat[sl], gs, self.m[sl], self.v[sl], pg["lr"], pg["betas"][0], pg["betas"][1], pg["eps"], self.step_count,
                                grad_scale, ema=self.ema[sl] if self.ema is not None else None, ema_decay=self.ema_decay or 0.0)
 
     def ema_state_dict(self):

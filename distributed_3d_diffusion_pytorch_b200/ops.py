@@ -577,8 +577,12 @@ class CudaOps:
         self._call("b3d_cond_silu", _ptr(c), _ptr(lemb), _ptr(lemb_row), _ptr(out), c_i32(D), c_i64(c.numel() // (D * E)), c_i32(E), self.stream())
 
     def adam(self, p, g, m, v, lr, beta1, beta2, eps, step, grad_scale=1.0, ema=None, ema_decay=0.0):
-        """ema (optional, fp32 like p): ema = ema_decay * ema + (1 - ema_decay) * p_new, in the same pass"""
-        if ema is None:
+        """ema (optional, fp32 like p): ema = ema_decay * ema + (1 - ema_decay) * p_new, in the same pass; g: fp32 or bf16"""
+        if g.dtype == torch.bfloat16:
+            assert g.numel() == p.numel() and g.is_contiguous()
+            self._call("b3d_adam_bf16grad", _ptr(p), _ptr(g), _ptr(m), _ptr(v), _ptr(ema) if ema is not None else None, c_i64(p.numel()),
+                       c_f32(lr), c_f32(beta1), c_f32(beta2), c_f32(eps), c_i32(step), c_f32(grad_scale), c_f32(ema_decay), self.stream())
+        elif ema is None:
             self._call("b3d_adam", _ptr(p), _ptr(g), _ptr(m), _ptr(v), c_i64(p.numel()), c_f32(lr), c_f32(beta1), c_f32(beta2), c_f32(eps),
                        c_i32(step), c_f32(grad_scale), self.stream())
         else:

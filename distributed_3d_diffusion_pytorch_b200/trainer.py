@@ -149,18 +149,17 @@ class Trainer:
         from those parameters -- all beside the later backward phases, which read packed operands and fp32 GroupNorm
         parameters of THEIR OWN blocks only.  The level-wide FiLM operands are the exception (phase 2's data gradient reads
         all of them): they are repacked after the last phase."""
-        g = self.model._grad_flat
+        g, gb = self.model._grad_flat, None
         if self.world > 1:
             if self.grad_comm_dtype == torch.float32:
                 parallel.allreduce_mean_(g[lo:hi])                     # NCCL over NVLink, concurrent with the next phase
-            else:
+            else:       # the Adam kernel reads the reduced bf16 buffer in place (the fp32 arena keeps this rank's own gradients)
                 if self._gcomm is None:
                     self._gcomm = torch.empty(max(h_ - l_ for l_, h_ in self.ranges.values()), dtype=self.grad_comm_dtype, device=self.dev)
                 gb = self._gcomm[:hi - lo]
                 gb.copy_(g[lo:hi])
                 parallel.allreduce_mean_(gb)
-                g[lo:hi].copy_(gb)
-        self.opt.step(lo=lo, hi=hi, first=ph == 0)
+        self.opt.step(lo=lo, hi=hi, first=ph == 0, grad=gb)
         self.engine.pack_group(ph)
         if ph == 2:
             self.engine.pack_group(3)

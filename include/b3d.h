@@ -280,6 +280,10 @@ int b3d_adam(float* p, const float* g, float* m, float* v, int64_t n, float lr, 
  * implements): ema = ema_decay * ema + (1 - ema_decay) * p_new, in the same pass (36 instead of 28 bytes per parameter) */
 int b3d_adam_ema(float* p, const float* g, float* m, float* v, float* ema, int64_t n, float lr, float beta1, float beta2, float eps,
                  int step, float grad_scale, float ema_decay, void* stream);
+/* the same step (ema may be NULL) reading a bf16 gradient: a data-parallel trainer all-reduces a bf16 copy of the gradient
+ * range and steps straight from that buffer instead of casting it back into the fp32 arena */
+int b3d_adam_bf16grad(float* p, const void* g_bf16, float* m, float* v, float* ema, int64_t n, float lr, float beta1, float beta2,
+                      float eps, int step, float grad_scale, float ema_decay, void* stream);
 
 #ifdef __cplusplus
 }

@@ -549,7 +549,7 @@ class EmuOps:
         self.sampler_update(z, eps_c, eps_u, w, noise, out, float(sched[0]), float(sched[1]))
 
     def adam(self, p, g, m, v, lr, beta1, beta2, eps, step, grad_scale=1.0):
-        gg = g * grad_scale
+        gg = g.float() * grad_scale
         m.mul_(beta1).add_(gg, alpha=1 - beta1)
         v.mul_(beta2).addcmul_(gg, gg, value=1 - beta2)
         p.sub_(lr * (m / (1 - beta1 ** step)) / ((v / (1 - beta2 ** step)).sqrt() + eps))

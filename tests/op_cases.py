@@ -203,6 +203,12 @@ def misc_case(seed=0):
         for st in (1, 2, 3):
             ops.adam(pa, ga, ma, va, 1e-2, 0.9, 0.99, 1e-8, st)
         outs += [pa, ma, va]
+        # the same step from a bf16 gradient buffer (data-parallel trainer: the all-reduced communication buffer, read in place)
+        pb, gb16 = torch.randn(1003, generator=g).to(dev), torch.randn(1003, generator=g).to(dev).to(torch.bfloat16)
+        mb, vb = ops.zeros((1003,), torch.float32), ops.zeros((1003,), torch.float32)
+        for st in (1, 2):
+            ops.adam(pb, gb16, mb, vb, 1e-2, 0.9, 0.99, 1e-8, st)
+        outs += [pb, mb, vb]
         return outs
     return run
 

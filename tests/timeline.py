@@ -20,10 +20,14 @@ from distributed_3d_diffusion_pytorch_b200.trainer import Trainer  # noqa: E402
 
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 16
 out = sys.argv[2] if len(sys.argv) > 2 else None
-dev = torch.device("cuda", 0)
-torch.cuda.set_device(0)
+rank, world, local = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
+dev = torch.device("cuda", local)
+torch.cuda.set_device(local)
+if world > 1:          # under torchrun: the data-parallel step (B pairs per rank); rank 0 writes the trace
+    import torch.distributed as dist
+    dist.init_process_group("nccl", device_id=dev)
 kw = dict(H=64, W=64, ch=128)          # bench.py's CFG-64
-tr = Trainer(kw, B, dev, world=1, seed=1234, use_graph=True)
+tr = Trainer(kw, B, dev, world=world, seed=1234, use_graph=True)
 res = [tuple(t.to(dev) for t in synthetic.make_views(B, kw["H"], seed=i)) for i in range(2)]
 for i in range(4):
     tr.step_resident(res[i % 2])
@@ -32,6 +36,10 @@ with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
     for i in range(2):
         tr.step_resident(res[i % 2])
         torch.cuda.synchronize()
+if rank != 0:
+    if world > 1:
+        dist.barrier()
+    sys.exit(0)
 tmp = out or "/tmp/b3d_timeline.json"
 prof.export_chrome_trace(tmp)
 ev = json.load(open(tmp))["traceEvents"]
@@ -83,4 +91,6 @@ mk = [e for e in ks if e["args"].get("stream", e.get("tid")) == main]
 short = [e for e in mk if e["dur"] < 8]
 print(f"main stream {main}: {len(mk)} kernels, {len(short)} shorter than 8 us ({sum(e['dur'] for e in short) / 1e3:.3f} ms)")
 g2 = [mk[i + 1]["ts"] - (mk[i]["ts"] + mk[i]["dur"]) for i in range(len(mk) - 1)]
+if world > 1:
+    dist.barrier()
 print(f"main-stream gaps: total {sum(g for g in g2 if g > 0) / 1e3:.3f} ms, median {sorted(g2)[len(g2) // 2]:.2f} us")

@@ -614,13 +614,19 @@ class Engine:
     def backward(self, Gr, deps, grad_flat=None, phase=None):
         """Gr: dict name -> fp32 grad tensor (PyTorch layout), overwritten.  deps: fp32 [B,3,H,W] = dL/d eps_hat.
         grad_flat: optional flat tensor that all of Gr are views of (zeroed with one memset).
-        phase: None = whole backward; 0, 1, 2 = one phase (must be called in that order)."""
+        phase: None = whole backward; 0, 1, 2 = one phase (must be called in that order).  Phase 2 may be given as its two parts
+        "2a" (the last reads of the level-wide FiLM operands: a trainer may repack those as soon as it has finished) and "2b"."""
         for ph in ((0, 1, 2) if phase is None else (phase,)):
-            self._cur_phase = ph
-            (self._bwd_phase0, self._bwd_phase1, self._bwd_phase2)[ph](Gr, deps, grad_flat)
+            base, part = (2, {"2a": 0, "2b": 1}[ph]) if ph in ("2a", "2b") else (ph, None)
+            self._cur_phase = base
+            if base == 2:
+                self._bwd_phase2(Gr, deps, grad_flat, part)
+            else:
+                (self._bwd_phase0, self._bwd_phase1)[base](Gr, deps, grad_flat)
             self.ops.join_side()
-            self.ops.run_jobs(self._unpack_jl[ph])     # packed fp32 weight gradients of this phase -> PyTorch layout, one launch
-            self.ops.run_jobs(self._copy_jl[ph])
+            if part != 0:
+                self.ops.run_jobs(self._unpack_jl[base])     # packed fp32 weight gradients of this phase -> PyTorch layout, one launch
+                self.ops.run_jobs(self._copy_jl[base])
 
     def _bwd_phase0(self, Gr, deps, grad_flat):
         ops, cfg, B, N = self.ops, self.cfg, self.B, self.N
@@ -702,37 +708,43 @@ class Engine:
                 for s in specs:
                     ops.record_copy(self._copy_jl[self._cur_phase], gp[s.film_off - c0:s.film_off - c0 + 2 * s.f], Gr[s.name + ".film.dense.weight"])
 
-    def _bwd_phase2(self, Gr, deps, grad_flat):
+    def _bwd_phase2(self, Gr, deps, grad_flat, part=None):
         ops, cfg, B, N = self.ops, self.cfg, self.B, self.N
         sv = self.saved
         P, Wp = sv["P"], sv["W"]
         H, Wd, E = cfg.H, cfg.W, cfg.emb_ch
         HW = H * Wd
         dss = self._dss
-        # ---- stem
-        stem = Act(self._bufs["stem"], "stem")
-        dstem = self._grad_of(stem)
-        xin = self._bufs["xin"]
-        with ops.side():       # parameter gradients beside the data path (joined at the end of the phase)
-            ops.colsum(dstem.view(N * HW, cfg.ch), N * HW, Gr["conv.bias"])
-            gp = self.zbuf("bwd", "stem.gp", (cfg.ch, 9 * 64))
-            ops.gemm(G.wgrad_desc(dstem, xin, 9, gp, 0, 64))
-            self._unpack(gp, 0, 64, Gr["conv.weight"])
-
-        # ---- conditioning: FiLM data gradient, conditioning convs, learned embeddings, logsnr MLP
         cp = "conditioningprocessor."
+        if part in (None, 0):
+            # ---- stem
+            stem = Act(self._bufs["stem"], "stem")
+            dstem = self._grad_of(stem)
+            xin = self._bufs["xin"]
+            with ops.side():       # parameter gradients beside the data path (joined at the end of the part)
+                ops.colsum(dstem.view(N * HW, cfg.ch), N * HW, Gr["conv.bias"])
+                gp = self.zbuf("bwd", "stem.gp", (cfg.ch, 9 * 64))
+                ops.gemm(G.wgrad_desc(dstem, xin, 9, gp, 0, 64))
+                self._unpack(gp, 0, 64, Gr["conv.weight"])
+            # ---- FiLM data gradient of every level: the gradient of the conditioning convs' outputs.  The GEMM multiplies by
+            # silu'(pre) in its epilogue (pre arrives as the residual tile), so that gradient is written once
+            for l in range(cfg.num_resolutions):
+                hh, ww = self.lvl_hw(l)
+                M = N * hh * ww
+                de = self.buf(f"de{l}", (N, hh, ww, E))
+                ops.gemm(G.dense_desc(dss[l], Wp[f"film{l}.T"], de.view(M, E), E, resid=self._bufs[f"emb_pre{l}"].view(M, E), act=2))
+        if part == 0:
+            return
+
+        # ---- conditioning convs, learned embeddings, logsnr MLP
         dlemb = self.zbuf("bwd", "dlemb", (N, E))
         dP = self.buf("dP", (2, H, Wd, 144), torch.float32)
         pe = self._bufs["pose_emb"]
         for l in range(cfg.num_resolutions):
             hh, ww = self.lvl_hw(l)
             M = N * hh * ww
-            pre = self._bufs[f"emb_pre{l}"]
-            de = self.buf(f"de{l}", (N, hh, ww, E))
-            # the FiLM data-gradient GEMM multiplies by silu'(pre) in its epilogue (pre arrives as the residual tile): the gradient
-            # of the conditioning conv's output is written once; d(logsnr_emb) per image and the conv's bias gradient are its
-            # column sums, one read
-            ops.gemm(G.dense_desc(dss[l], Wp[f"film{l}.T"], de.view(M, E), E, resid=pre.view(M, E), act=2))
+            de = self._bufs[f"de{l}"]
+            # d(logsnr_emb) per image and the conv's bias gradient are column sums of de, one read
             ops.silu_bwd_colsum(de, None, None, hh * ww, dlemb, Gr[cp + f"convs.{l}.bias"])
             with ops.side():
                 gp = self.zbuf("bwd", f"cc{l}.gp", (E, 9 * 192))

@@ -36,6 +36,13 @@ def allreduce_mean_(flat, async_op=False):
     return None
 
 
+def allreduce_sum_(flat):
+    """in-place SUM over ranks (the caller folds the 1/world into its consumer, e.g. Adam's grad_scale: a plain sum keeps every
+    NCCL algorithm eligible, an AVG is a pre-multiplied sum)"""
+    if world() > 1:
+        dist.all_reduce(flat, op=dist.ReduceOp.SUM)
+
+
 def shard_batch(batch, rank_, world_):
     """contiguous shard of a global batch (tuple of tensors with leading batch dim) for this rank"""
     B = batch[0].shape[0]

@@ -5,7 +5,7 @@ one process per GPU:
     -> gradient all-reduce over NCCL (N>1; the reference's DDP never armed it) -> fused Adam
 
 The compute part (everything up to the gradients) works on static device buffers and is captured once
-in three CUDA graphs (forward + backward phase 0 | phase 1 | phase 2); draws (logsnr, noise, cond mask, dropout) are made
+in four CUDA graphs (forward + backward phase 0 | phase 1 | phase 2a | 2b); draws (logsnr, noise, cond mask, dropout) are made
 on the device inside the graph (dropout through a device-side step counter), so replays are fresh steps, not repeats.
 The UPDATE of each gradient range -- all-reduce (N>1), Adam, and the repack of the bf16 GEMM operands built from those
 parameters -- runs on a second stream as soon as the phase that finalises the range has finished, beside the later
@@ -88,7 +88,7 @@ class Trainer:
         self._lam0 = float(-2.0 * np.log(np.tan(self._b)))        # schedule(0) = +20 for the clean conditioning frame
         self.use_graph, self.graph, self.graphed = use_graph, None, False
         self.launches_per_step = 0
-        self._packed = False
+        self._packed, self._pv = False, 0
         self._count_update = False
         self.step_idx = 0
 
@@ -143,13 +143,14 @@ class Trainer:
         for g in range(4):
             self.engine.pack_group(g)
         self._packed = True
+        self._pv = getattr(self.model, "_param_version", 0)
 
     def _update(self, ph, lo, hi):
         """(communication stream) all-reduce of gradient range [lo, hi), its Adam step, and the repack of the operands built
         from those parameters -- all beside the later backward phases, which read packed operands and fp32 GroupNorm
-        parameters of THEIR OWN blocks only.  The level-wide FiLM operands are the exception (phase 2's data gradient reads
-        all of them): they are repacked after the last phase."""
-        g, gb = self.model._grad_flat, None
+        parameters of THEIR OWN blocks only.  The level-wide FiLM operands are the exception (the first part of phase 2, the
+        FiLM data gradient, reads all of them): step_resident repacks them when that part has finished."""
+        g, gb, scale = self.model._grad_flat, None, 1.0
         if self.world > 1:
             if self.grad_comm_dtype == torch.float32:
                 parallel.allreduce_mean_(g[lo:hi])                     # NCCL over NVLink, concurrent with the next phase
@@ -158,11 +159,10 @@ class Trainer:
                     self._gcomm = torch.empty(max(h_ - l_ for l_, h_ in self.ranges.values()), dtype=self.grad_comm_dtype, device=self.dev)
                 gb = self._gcomm[:hi - lo]
                 gb.copy_(g[lo:hi])
-                parallel.allreduce_mean_(gb)
-        self.opt.step(lo=lo, hi=hi, first=ph == 0, grad=gb)
+                parallel.allreduce_sum_(gb)                            # the 1/world is Adam's grad_scale
+                scale = 1.0 / self.world
+        self.opt.step(grad_scale=scale, lo=lo, hi=hi, first=ph == 0, grad=gb)
         self.engine.pack_group(ph)
-        if ph == 2:
-            self.engine.pack_group(3)
 
     def _set_batch(self, batch):
         img, R, T, K = batch
@@ -181,13 +181,15 @@ class Trainer:
         """batch already lives in HBM (device tensors)"""
         from . import _lib
         self._set_batch(batch)
+        if self._packed and getattr(self.model, "_param_version", 0) != self._pv:
+            self.repack()          # the parameters changed outside this trainer's own update (load_state_dict, a foreign optimizer)
         if self.use_graph and self.graph is None and self.step_idx >= 1:
             torch.cuda.synchronize()
             n0 = _lib.launch_count()
             # three graphs: the update of each finished gradient range (all-reduce, Adam, repack) overlaps the next phase
             self.model._grad_views()
-            self.graph = [self._capture(lambda: (self._draws_forward_loss(), self._backward(0))),
-                          self._capture(lambda: self._backward(1)), self._capture(lambda: self._backward(2))]
+            self.graph = [self._capture(lambda: (self._draws_forward_loss(), self._backward(0))), self._capture(lambda: self._backward(1)),
+                          self._capture(lambda: self._backward("2a")), self._capture(lambda: self._backward("2b"))]
             self.ranges = self._phase_ranges()
             self.comm = torch.cuda.Stream(self.dev)
             self.launches_per_step = _lib.launch_count() - n0     # + the un-captured update launches, counted on the first replay
@@ -202,10 +204,16 @@ class Trainer:
         for ph in (0, 1, 2):
             self.graph[ph].replay()
             self.comm.wait_stream(main)                                # gradients of this phase are final
+            if ph == 2:       # "2a" held the last reads of the level-wide FiLM operands: repack them beside "2b"
+                with torch.cuda.stream(self.comm):
+                    self.engine.pack_group(3)
+                self.graph[3].replay()
+                self.comm.wait_stream(main)
             lo, hi = self.ranges[ph]
             with torch.cuda.stream(self.comm):
                 self._update(ph, lo, hi)
         main.wait_stream(self.comm)                                    # the next forward reads the repacked operands
+        self._pv = getattr(self.model, "_param_version", 0)            # (FusedAdam.step bumped it: this update's operands are current)
         if self._count_update:                                         # Adam per range, repack per group, composed attention operands
             self.launches_per_step += _lib.launch_count() - n_up
             self._count_update = False

@@ -86,3 +86,28 @@ def test_graphed_step_gradients_and_update_equal_the_plain_sequence():
     want = p0 - 1e-3 * (m1 / (1 - 0.9 ** t)) / ((v1 / (1 - 0.99 ** t)).sqrt() + 1e-8)
     assert float((p1 - want).abs().max()) < 2e-6 + 1e-5 * float(want.abs().max())
     assert torch.allclose(a.opt.m, m1, rtol=1e-5, atol=1e-9) and torch.allclose(a.opt.v, v1, rtol=1e-5, atol=1e-12)
+
+
+def test_parameters_changed_from_outside_are_repacked_before_the_next_step():
+    """load_state_dict between steps bumps model._param_version: the trainer's forward, which no longer packs, must not run on
+    the operands of the old weights"""
+    tr = _trainer(True)
+    bs = _batches(2)
+    for i in range(3):
+        tr.step_resident(bs[i % 2])
+    calls = []
+    orig = tr.repack
+    tr.repack = lambda: (calls.append(1), orig())[1]
+    tr.step_resident(bs[1])
+    assert not calls                                   # its own update keeps the operands current
+    sd = {k: v.clone() * 1.5 for k, v in tr.model.state_dict().items()}
+    tr.model.load_state_dict(sd)
+    torch.cuda.synchronize()
+    eng = tr.engine
+    W = eng._pack_cache[True][1]
+    k0 = next(k for k in W if k.endswith("conv1.weight"))
+    before = W[k0].clone()
+    tr.step_resident(bs[0])
+    torch.cuda.synchronize()
+    assert calls == [1]
+    assert not torch.equal(before, W[k0])

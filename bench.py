@@ -368,7 +368,7 @@ def main():
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": value / 29.9,
             "dtype": "bf16", "data": "synthetic",
             "config": {"workload": args.model + "_train_step", "model": "XUNet(H=%d,W=%d,ch=%d)" % (MODEL_KW["H"], MODEL_KW["W"], MODEL_KW["ch"]), "global_batch": args.global_batch, "per_gpu_batch": B,
-                       "parallelism": f"dp{world}", "grad_allreduce": ("fp32" if args.fp32_allreduce else "bf16") if world > 1 else None, "dropout": 0.1, "optimizer": "fused Adam", "cuda_graph": graphed,
+                       "parallelism": f"dp{world}", "grad_allreduce": ("fp32 avg" if args.fp32_allreduce else "bf16 sum (1/N in Adam's gradient scale)") if world > 1 else None, "dropout": 0.1, "optimizer": "fused Adam", "cuda_graph": graphed,
                        "l2": "no flush needed: per-step working set (activations) is GBs, far above the 126 MB L2",
                        "baseline_note": "vs_baseline = value / 29.9 samples/s (README.md:39, 8x RTX 3090, derived)"},
             "clocks": clk, "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4, "last_loss": loss_val},

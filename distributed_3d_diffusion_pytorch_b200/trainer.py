@@ -186,7 +186,7 @@ class Trainer:
         if self.use_graph and self.graph is None and self.step_idx >= 1:
             torch.cuda.synchronize()
             n0 = _lib.launch_count()
-            # three graphs: the update of each finished gradient range (all-reduce, Adam, repack) overlaps the next phase
+            # four graphs: the update of each finished gradient range (all-reduce, Adam, repack) overlaps the next phase
             self.model._grad_views()
             self.graph = [self._capture(lambda: (self._draws_forward_loss(), self._backward(0))), self._capture(lambda: self._backward(1)),
                           self._capture(lambda: self._backward("2a")), self._capture(lambda: self._backward("2b"))]

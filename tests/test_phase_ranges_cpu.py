@@ -58,3 +58,15 @@ def test_each_backward_phase_finalises_exactly_its_range():
                 assert torch.equal(flat[lo:hi], full[lo:hi]), (ph, q)
             else:                  # not started: still the zeros phase 0 wrote
                 assert flat[lo:hi].abs().sum() == 0, (ph, q)
+    # phase 2 in its two parts ("2a": stem + the FiLM data gradient, the last reads of the level-wide FiLM operands; "2b": the
+    # rest) gives the same gradients, and "2a" alone leaves range 2 unfinished (its unpack / copy jobs run at the end of "2b")
+    eng.forward(sd, img[:, 0], img[:, 1], logsnr, R, T, K, cm, training=False, need_bwd=True)
+    flat2 = torch.zeros(numel)
+    gv2 = views(flat2)
+    for ph in (0, 1, "2a"):
+        eng.backward(gv2, deps, grad_flat=flat2, phase=ph)
+    lo, hi = r[2]
+    assert not torch.equal(flat2[lo:hi], full[lo:hi])
+    assert torch.equal(flat2[hi:], full[hi:])
+    eng.backward(gv2, deps, grad_flat=flat2, phase="2b")
+    assert torch.equal(flat2, full)

@@ -56,7 +56,33 @@ def _worker(rank, world, port, out):
     w0 = torch.full((3,), float(rank))
     parallel.broadcast_parameters(w0)
     assert torch.equal(w0, torch.zeros(3))
+    # the trainer's per-range update (trainer._update): a bf16 copy of each gradient range is SUM-reduced and Adam reads it in
+    # place with grad_scale = 1 / world -- the same step as Adam on the fp32 mean gradient, up to the bf16 rounding of the payload
+    from distributed_3d_diffusion_pytorch_b200.engine import Cfg, Engine
+    from distributed_3d_diffusion_pytorch_b200.trainer import phase_ranges
+    from distributed_3d_diffusion_pytorch_b200.xunet import param_shapes
+    from emu_ops import EmuOps
+    shapes = param_shapes(Cfg(H=8, W=8, ch=32))
+    names, offs, tot = list(shapes.keys()), [], 0
+    for k in names:
+        offs.append(tot)
+        tot += int(torch.Size(shapes[k]).numel())
+    ranges = phase_ranges(names, offs, tot, Engine.PHASE_PREFIXES)
+    local = flat.clone()
+    p_a, m_a, v_a = torch.zeros(tot), torch.zeros(tot), torch.zeros(tot)
+    for ph in (0, 1, 2):
+        lo, hi = ranges[ph]
+        gb = local[lo:hi].to(torch.bfloat16)
+        parallel.allreduce_sum_(gb)
+        EmuOps().adam(p_a[lo:hi], gb, m_a[lo:hi], v_a[lo:hi], 1e-3, 0.9, 0.99, 1e-8, 1, grad_scale=1.0 / world)
     parallel.allreduce_mean_(flat)
+    p_b, m_b, v_b = torch.zeros(tot), torch.zeros(tot), torch.zeros(tot)
+    EmuOps().adam(p_b, flat, m_b, v_b, 1e-3, 0.9, 0.99, 1e-8, 1)
+    assert float((m_a - m_b).norm() / m_b.norm()) < 5e-3                # 2^-9 per rounded summand
+    # first Adam step: the update is lr * g / (|g| + eps), i.e. the SIGN of the mean gradient wherever it is above eps: the
+    # two can differ only where the ranks' gradients nearly cancel and the bf16 rounding decides the sign
+    assert float(((p_a - p_b).abs() > 1e-5).float().mean()) < 5e-3
+    assert float(p_b.abs().max()) > 5e-4 and float((v_a - v_b).norm() / v_b.norm()) < 1e-2
     if rank == 0:
         torch.save(flat, out)
     dist.destroy_process_group()

@@ -363,6 +363,7 @@ def main():
                "sample": f"CFG-64 fp32 fwd+bwd, batch {args.ref_batch}, 2 timed steps after 1 warm-up (oracle port of the reference path)"}
 
     if rank == 0:
+        print("peak device memory: %.1f GB" % (torch.cuda.max_memory_allocated(dev) / 2 ** 30), file=sys.stderr)
         print(json.dumps({
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": value / 29.9,

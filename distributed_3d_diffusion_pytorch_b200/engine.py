@@ -108,8 +108,13 @@ class Engine:
         self.saved = None
         self._pack_cache = {}
         self._unpack_jl, self._copy_jl, self._unpack_sig, self._unpack_rec = None, None, None, False
-        # small batches: weight-gradient launches never block the data-gradient chain (see side_tmp)
-        self.defer_side = 2 * B * cfg.H * cfg.W <= 64 * 64 * 64
+        # weight-gradient launches never block the data-gradient chain (see side_tmp): their inputs live in block-private buffers
+        # and the side streams join at the end of a phase only.  Costs memory (+5 GB at batch 128 of CFG-64, 63.5 GB in all;
+        # measured 117.86 -> 117.22 ms per step there, more for small batches), so it stops where the private buffers would
+        # outgrow that: 2^27 elements per level-0 activation tensor
+        self.defer_side = 2 * B * cfg.H * cfg.W * cfg.ch <= 64 * 64 * 256 * 128
+        if os.environ.get("B3D_DEFER_SIDE") is not None:      # measurement switch
+            self.defer_side = os.environ["B3D_DEFER_SIDE"] == "1"
         # ... and then the side work is itself a serial chain of small launches as long as the main one: spread its regions
         # (one `with ops.side():` each, independent of each other) over several streams
         if self.defer_side and hasattr(self.ops, "n_side"):

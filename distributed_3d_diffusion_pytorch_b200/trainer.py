@@ -11,6 +11,7 @@ The UPDATE of each gradient range -- all-reduce (N>1), Adam, and the repack of t
 parameters -- runs on a second stream as soon as the phase that finalises the range has finished, beside the later
 phases; the next forward packs nothing."""
 import math
+import os
 
 import numpy as np
 import torch
@@ -56,7 +57,10 @@ class Trainer:
         self.ops = CudaOps(self.dev)
         # launch-latency hiding pays for small per-GPU batches only (measured: +1.9% at 16 pairs, -0.6% at 128 of 64x64)
         from . import _lib
-        _lib.set_pdl(2 * B * model_kw["H"] * model_kw["W"] <= 64 * 64 * 64)
+        pdl = 2 * B * model_kw["H"] * model_kw["W"] <= 64 * 64 * 64
+        if os.environ.get("B3D_PDL") is not None:         # measurement switch
+            pdl = os.environ["B3D_PDL"] == "1"
+        _lib.set_pdl(pdl)
         self.cond_prob = cond_prob
         # payload of the gradient all-reduce: bf16 halves the bytes on NVLink (273 instead of 547 MB at CFG-64); the fp32 arena is
         # cast on the communication stream, reduced, and cast back before that range's Adam step.  torch.float32 = exact sum.

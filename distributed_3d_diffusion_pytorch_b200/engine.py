@@ -118,7 +118,8 @@ class Engine:
         # ... and then the side work is itself a serial chain of small launches as long as the main one: spread its regions
         # (one `with ops.side():` each, independent of each other) over several streams
         if self.defer_side and hasattr(self.ops, "n_side"):
-            self.ops.n_side = max(self.ops.n_side, int(os.environ.get("B3D_SIDE_STREAMS", "2")))
+            self.ops.n_side = max(self.ops.n_side, int(os.environ.get("B3D_SIDE_STREAMS", "3")))      # measured: 1 / 2 / 3 / 4 streams
+            # = 20.80 / 20.36 / 20.29 / 20.34 ms per step at 16 pairs, 116.80 / 116.4 / 115.8 / - at 128
         # GroupNorm statistics of conv1's output from its own epilogue (measured in-run: +0.5% at batch 128, -0.4% at batch 16,
         # where the extra epilogue work costs more than the small gn_stats launch: large batches only; B3D_NO_FUSE_STATS=1 = off)
         self.fuse_stats = os.environ.get("B3D_NO_FUSE_STATS") != "1" and 2 * B * cfg.H * cfg.W > 64 * 64 * 64
